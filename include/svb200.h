@@ -1,0 +1,235 @@
+/*
+ * svb200.h — C ABI of the B200 (sm_100a) provider for Sparse-vLLM's decode-time
+ * sparse-attention hot path (Quest page selection + sparse paged GQA decode
+ * attention, H2O scored decode).
+ *
+ * Conventions
+ *   - Every pointer is a DEVICE pointer unless the parameter name ends in _host.
+ *   - All tensors are bf16 (uint16 storage) / fp32 / int32 as stated; head_dim is
+ *     fixed at 128, quest page size at 16.
+ *   - Every call is asynchronous on `stream` (a cudaStream_t passed as void*), does
+ *     no allocation and no host synchronisation, and is CUDA-graph capturable.
+ *   - Return value: 0 on success; SVB200_E* on validation failure; 1000 + cudaError_t
+ *     when a launch failed.  svb200_last_error() returns a thread-local message.
+ *   - No ownership transfer: buffers belong to the caller and must outlive the call.
+ *
+ * "Reference" below is CURRENTF/Sparse-vLLM, paths relative to its src/sparsevllm/.
+ */
+#ifndef SVB200_H_
+#define SVB200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVB200_ABI_VERSION 1
+
+enum {
+  SVB200_OK = 0,
+  SVB200_EINVAL = 1,      /* bad shape / alignment / null pointer            */
+  SVB200_EUNSUPPORTED = 2 /* head_dim != 128, page != 16, group size > 16 …  */
+};
+
+#define SVB200_HEAD_DIM 128
+#define SVB200_PAGE 16
+
+/* ABI / build introspection. */
+int svb200_abi_version(void);
+const char* svb200_last_error(void);
+/* Number of SMs of the current device (cached); used by hosts to size split-K. */
+int svb200_sm_count(void);
+
+/*
+ * Bytes of scratch the attention entry point needs besides mid_o / mid_lse:
+ * one int32 arrival ticket per (batch row, kv-head group).  The buffer must be
+ * zero-initialised once; kernels leave it zeroed.
+ * Replaces nothing in the reference (its stage2 is a separate launch).
+ */
+int64_t svb200_workspace_bytes(int32_t batch, int32_t num_kv_heads);
+
+/* ------------------------------------------------------------------------- *
+ * Quest page bounds ("metadata").  Layout owned by this provider:
+ *   bounds[L][num_pages][2][Hkv][128] bf16, [..][0] = max, [..][1] = min
+ * (the reference keeps two separate planes metadata_cache[2][L][P][Hkv][D],
+ *  engine/cache_manager/quest.py:96-105; interleaving per page makes one page's
+ *  bounds a single contiguous 512*Hkv-byte record for the scoring scan).
+ * ------------------------------------------------------------------------- */
+
+/*
+ * Recompute min/max of every page COMPLETED by the tokens in slot_mapping
+ * (slot % 16 == 15, slot >= 0) from the K cache of one layer.
+ * Replaces QuestCacheManager.on_kv_stored / _on_kv_stored_prefill_capture
+ * (engine/cache_manager/quest.py:1608-1716): K rows were already stored, so
+ * full pages and pages completed across chunks are the same scan.
+ *   k_cache      [num_slots][Hkv][128] bf16 (one layer)
+ *   bounds_layer [num_pages][2][Hkv][128] bf16 (one layer)
+ *   slot_mapping [n_tokens] int32 (-1 = padding)
+ */
+int svb200_quest_page_minmax(const void* k_cache, void* bounds_layer,
+                             const int32_t* slot_mapping, int32_t n_tokens,
+                             int32_t num_kv_heads, int64_t num_slots,
+                             void* stream);
+
+/*
+ * Decode-time page completion for ALL layers in one launch: for every batch row
+ * whose length after this step is a positive multiple of 16, rebuild the bounds
+ * of page (len/16 - 1) in each layer.
+ * Replaces QuestCacheManager.on_forward_end (quest.py:1719-1771, a Python loop
+ * over layers with three launches each).
+ *   k_cache_all  [L][num_slots][Hkv][128] bf16, bounds_all [L][num_pages][2][Hkv][128]
+ *   page_table   [rows][page_table_stride] int32, req_rows [batch] int32,
+ *   seq_lens     [batch] int32 (length INCLUDING the token just stored)
+ */
+int svb200_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
+                                      const int32_t* page_table,
+                                      int64_t page_table_stride,
+                                      const int32_t* req_rows,
+                                      const int32_t* seq_lens, int32_t batch,
+                                      int32_t num_layers, int32_t num_kv_heads,
+                                      int64_t num_slots, int64_t num_pages,
+                                      void* stream);
+
+/*
+ * Page scores for one layer: score[b][p] for p in [0, n_cols) where
+ *   score = amax over all local q heads of
+ *           bf16( bf16(sum_d q+[d]*max[p][d]) + bf16(sum_d q-[d]*min[p][d]) )
+ * (fp32 accumulation, three bf16 roundings — exactly the rounding structure of
+ *  QuestCacheManager._score_pages_batched, quest.py:1773-1802), columns
+ * p >= ceil(ctx/16) - 1 are -inf (quest.py:1883-1885).  The gather of
+ * quest.py:1870-1881 is fused: bounds are read through the page table.
+ *   q            [batch][Hq][128] bf16, row stride q_stride_b elements
+ *   page_table   [rows][page_table_stride] int32 (-1 empty)
+ *   req_rows     [batch] int32 row of each batch entry in page_table
+ *   context_lens [batch] int32
+ *   scores       [batch][score_stride] bf16 out, score_stride >= n_cols
+ */
+int svb200_quest_page_score(const void* q, int64_t q_stride_b,
+                            const void* bounds_layer, const int32_t* page_table,
+                            int64_t page_table_stride, const int32_t* req_rows,
+                            const int32_t* context_lens, void* scores,
+                            int64_t score_stride, int32_t batch, int32_t num_q_heads,
+                            int32_t num_kv_heads, int32_t n_cols, void* stream);
+
+/*
+ * Top-k page selection + slot packing for one layer (quest.py:1887-1913):
+ * picks the prev_budget highest-scoring columns (ties: lowest page index first),
+ * appends the last page, expands page slots to token slots.
+ *   packed_slots [batch][out_stride] int32, out_stride >= (prev_budget+1)*16
+ *   sparse_lens  [batch] int32 = prev_budget*16 + (ctx - (ceil(ctx/16)-1)*16)
+ *   selected_pages [batch][prev_budget+1] int32 or NULL (logical page ids, ascending
+ *                  then the last page; for tests / debugging)
+ * If dense_token_table != NULL (batch is not long-text, quest.py:1866-1868,
+ * 1903-1911) rows with ctx <= token_budget or ceil(ctx/16) <= page_budget_base take
+ * the first out_width entries of their dense row instead and keep ctx as length;
+ * out_width = max_keep >= (prev_budget+1)*16 columns are written.
+ */
+int svb200_quest_select_pack(const void* scores, int64_t score_stride,
+                             int32_t n_cols, const int32_t* page_table,
+                             int64_t page_table_stride, const int32_t* req_rows,
+                             const int32_t* context_lens, int32_t batch,
+                             int32_t prev_budget, int32_t* packed_slots,
+                             int64_t out_stride, int32_t* sparse_lens,
+                             int32_t* selected_pages,
+                             const int32_t* dense_token_table,
+                             int64_t dense_table_stride, int32_t token_budget,
+                             int32_t page_budget_base, int32_t out_width,
+                             void* stream);
+
+/*
+ * Fused score + select + pack: same results as the two calls above with one
+ * launch (the last CTA of each row performs the selection).
+ *   tickets [batch] int32 zero-initialised scratch (left zeroed).
+ */
+int svb200_quest_score_select_pack(
+    const void* q, int64_t q_stride_b, const void* bounds_layer,
+    const int32_t* page_table, int64_t page_table_stride, const int32_t* req_rows,
+    const int32_t* context_lens, void* scores, int64_t score_stride, int32_t batch,
+    int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols, int32_t prev_budget,
+    int32_t* packed_slots, int64_t out_stride, int32_t* sparse_lens,
+    int32_t* selected_pages, int32_t* tickets, void* stream);
+
+/*
+ * Sparse paged GQA decode attention with split-K and fused combine.
+ * Replaces gqa_flash_decode_stage1(+_with_score 2D) and flash_decode_stage2
+ * (kernels/triton/gqa_flash_decoding_stage1.py:6-121,211-295,
+ *  kernels/triton/flash_decoding_stage2.py:8-46) behind
+ * TritonAttentionBackend.run_decode (layers/attention_backend.py:217-349).
+ *   q          [batch][Hq][128] bf16 (row stride q_stride_b elements)
+ *   k_cache, v_cache [num_slots][Hkv][128] bf16, identical layout
+ *   slot_table [rows][slot_table_stride] int32 token slots; entries < 0 are
+ *              treated as masked tokens
+ *   req_rows   [batch] int32, seq_lens [batch] int32 (tokens visible per row)
+ *   mid_o      [batch][Hq][num_splits][128] fp32, mid_lse [batch][Hq][num_splits] fp32
+ *   out        [batch][Hq][128] bf16 (row stride out_stride_b elements)
+ *   attn_score NULL (Quest) or fp32 [batch][score_stride] pre-filled by the caller
+ *              (reference: -1e20); entry n is max-updated with the raw, unscaled
+ *              max over local q heads of q.k[n]  (H2O / SnapKV 2D score).
+ *   split_tokens tokens per split (multiple of 16); num_splits*split_tokens must
+ *              cover max(seq_lens).
+ *   heads_per_cta 0 = auto, else 1/2/4/8 KV heads handled by one CTA.
+ *   tickets    int32 [svb200_workspace_bytes/4] zeroed scratch.
+ */
+int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_cache,
+                              const void* v_cache, int64_t num_slots,
+                              const int32_t* slot_table, int64_t slot_table_stride,
+                              const int32_t* req_rows, const int32_t* seq_lens,
+                              float* mid_o, float* mid_lse, void* out,
+                              int64_t out_stride_b, float* attn_score,
+                              int64_t score_stride, int32_t batch, int32_t num_q_heads,
+                              int32_t num_kv_heads, int32_t split_tokens,
+                              int32_t num_splits, int32_t heads_per_cta,
+                              int32_t* tickets, float sm_scale, void* stream);
+
+/*
+ * H2O layer-end normalisation (+ optional fused accumulation).
+ *   score [batch][score_stride] fp32, in place: score = softmax(score * scale) over
+ *   the first `width` columns (engine/sparse_controller.py:761-767).
+ *   If cumulative != NULL: for row b with kv_len = kv_lens[b]:
+ *     cumulative[b][i] += score[b][i] for i < kv_len-1; cumulative[b][kv_len-1] = score
+ *   (H2OCacheManager.update_decode_attention_scores_all_layers, h2o.py:958-1038,
+ *    without the stack/clone of per-row tensors).
+ */
+int svb200_h2o_normalize_accumulate(float* score, int64_t score_stride, int32_t batch,
+                                    int32_t width, float scale, float* cumulative,
+                                    int64_t cum_stride, const int32_t* kv_lens,
+                                    void* stream);
+
+/*
+ * H2O burst eviction for `num_rows` (layer,row) pairs of identical length kv_len:
+ * heavy hitters = the (budget - recent) largest cumulative scores among
+ * [0, kv_len - recent) (stable: lower index wins ties), plus the `recent` suffix,
+ * in ascending order (H2OCacheManager.select_h2o_indices_batch, h2o.py:519-563);
+ * then index-only compaction of the slot rows, scores and the per-layer free
+ * stack (SnapKVCacheManager.free_part_slots_batch_layers, snapkv.py:1681-1803).
+ *   cum_rows   int64 [num_rows] element offsets of each row in `cumulative`
+ *   slot_rows  int64 [num_rows] element offsets of each row in `slot_tables`
+ *   free_rows  int64 [num_rows] element offset in `free_stack` where this row's
+ *              dropped slots start (kv_len - budget entries each), or NULL
+ *   keep_out   int32 [num_rows][budget] ascending kept indices (may be NULL)
+ */
+int svb200_h2o_select_compact(float* cumulative, const int64_t* cum_rows,
+                              int32_t* slot_tables, const int64_t* slot_rows,
+                              int32_t* free_stack, const int64_t* free_rows,
+                              int32_t* keep_out, int32_t num_rows, int32_t kv_len,
+                              int32_t budget, int32_t recent, void* stream);
+
+/*
+ * Store the new K/V rows of one layer and (quest_bounds_layer != NULL) refresh the
+ * bounds of any page the stored token completes.
+ * Replaces store_kvcache (kernels/triton/store_kvcache.py:10-71) and, for decode,
+ * the deferred refresh of quest.py:1719-1771.
+ *   key, value [n_tokens][Hkv][128] bf16 with token strides k_stride/v_stride (elements)
+ *   slot_mapping [n_tokens] int32, -1 = skip
+ */
+int svb200_store_kv_minmax(const void* key, int64_t k_stride, const void* value,
+                           int64_t v_stride, void* k_cache, void* v_cache,
+                           const int32_t* slot_mapping, int32_t n_tokens,
+                           int32_t num_kv_heads, int64_t num_slots,
+                           void* quest_bounds_layer, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVB200_H_ */

@@ -1,0 +1,290 @@
+// extern "C" entry points of libsvb200.so (see include/svb200.h): argument
+// validation, error reporting, dispatch to the kernel launchers.  No torch types.
+#include <stdarg.h>
+#include <stdio.h>
+
+#include "../../include/svb200.h"
+#include "launch.h"
+
+namespace svb200 {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+int cuda_error(const char* what, cudaError_t e) {
+  set_error("%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+  return 1000 + (int)e;
+}
+int check_launch(const char* what) {
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_error(what, e);
+  return 0;
+}
+int sm_count() {
+  static int cached = 0;
+  if (cached == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+      cached = n;
+    else
+      cached = 148;
+  }
+  return cached;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+#define SV_REQUIRE(cond, ...)    \
+  do {                           \
+    if (!(cond)) {               \
+      set_error(__VA_ARGS__);    \
+      return SVB200_EINVAL;      \
+    }                            \
+  } while (0)
+#define SV_SUPPORTED(cond, ...)  \
+  do {                           \
+    if (!(cond)) {               \
+      set_error(__VA_ARGS__);    \
+      return SVB200_EUNSUPPORTED;\
+    }                            \
+  } while (0)
+
+static int check_heads(const char* who, int hq, int hkv) {
+  SV_REQUIRE(hq > 0 && hkv > 0 && hq % hkv == 0, "%s: num_q_heads=%d must be a positive multiple of num_kv_heads=%d", who, hq, hkv);
+  SV_SUPPORTED(hq / hkv <= 16, "%s: GQA group size %d > 16 is not supported", who, hq / hkv);
+  return 0;
+}
+
+}  // namespace svb200
+
+using namespace svb200;
+
+extern "C" {
+
+int svb200_abi_version(void) { return SVB200_ABI_VERSION; }
+const char* svb200_last_error(void) { return g_err; }
+int svb200_sm_count(void) { return sm_count(); }
+
+int64_t svb200_workspace_bytes(int32_t batch, int32_t num_kv_heads) {
+  if (batch < 0 || num_kv_heads < 0) return -1;
+  return (int64_t)batch * num_kv_heads * (int64_t)sizeof(int32_t);
+}
+
+int svb200_quest_page_minmax(const void* k_cache, void* bounds_layer, const int32_t* slot_mapping,
+                             int32_t n_tokens, int32_t num_kv_heads, int64_t num_slots,
+                             void* stream) {
+  SV_REQUIRE(n_tokens >= 0, "quest_page_minmax: n_tokens=%d < 0", n_tokens);
+  if (n_tokens == 0) return 0;
+  SV_REQUIRE(k_cache && bounds_layer && slot_mapping, "quest_page_minmax: null pointer");
+  SV_REQUIRE(aligned16(k_cache) && aligned16(bounds_layer), "quest_page_minmax: buffers must be 16-byte aligned");
+  SV_REQUIRE(num_kv_heads > 0 && num_slots > 0 && num_slots % SVB200_PAGE == 0,
+             "quest_page_minmax: num_kv_heads=%d num_slots=%lld (must be a positive multiple of 16)",
+             num_kv_heads, (long long)num_slots);
+  return launch_quest_page_minmax(k_cache, bounds_layer, slot_mapping, n_tokens, num_kv_heads,
+                                  num_slots, (cudaStream_t)stream);
+}
+
+int svb200_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
+                                      const int32_t* page_table, int64_t page_table_stride,
+                                      const int32_t* req_rows, const int32_t* seq_lens,
+                                      int32_t batch, int32_t num_layers, int32_t num_kv_heads,
+                                      int64_t num_slots, int64_t num_pages, void* stream) {
+  SV_REQUIRE(batch >= 0 && num_layers >= 0, "quest_decode_page_complete: negative batch/layers");
+  if (batch == 0 || num_layers == 0) return 0;
+  SV_REQUIRE(k_cache_all && bounds_all && page_table && req_rows && seq_lens,
+             "quest_decode_page_complete: null pointer");
+  SV_REQUIRE(aligned16(k_cache_all) && aligned16(bounds_all), "quest_decode_page_complete: buffers must be 16-byte aligned");
+  SV_REQUIRE(num_kv_heads > 0 && num_slots == num_pages * SVB200_PAGE && page_table_stride > 0,
+             "quest_decode_page_complete: num_slots=%lld must equal 16*num_pages=%lld",
+             (long long)num_slots, (long long)num_pages);
+  SV_REQUIRE(num_layers <= 65535, "quest_decode_page_complete: num_layers=%d > 65535", num_layers);
+  return launch_quest_decode_page_complete(k_cache_all, bounds_all, page_table, page_table_stride,
+                                           req_rows, seq_lens, batch, num_layers, num_kv_heads,
+                                           num_slots, num_pages, (cudaStream_t)stream);
+}
+
+static int check_score_args(const char* who, const void* q, int64_t q_stride_b, const void* bounds,
+                            const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
+                            const int32_t* ctx, const void* scores, int64_t score_stride,
+                            int batch, int hq, int hkv, int n_cols) {
+  SV_REQUIRE(q && bounds && page_table && req_rows && ctx && scores, "%s: null pointer", who);
+  SV_REQUIRE(aligned16(q) && aligned16(bounds) && aligned16(scores), "%s: q/bounds/scores must be 16-byte aligned", who);
+  if (int rc = check_heads(who, hq, hkv)) return rc;
+  SV_REQUIRE(q_stride_b >= (int64_t)hq * SVB200_HEAD_DIM && q_stride_b % 8 == 0,
+             "%s: q_stride_b=%lld too small or not a multiple of 8", who, (long long)q_stride_b);
+  SV_REQUIRE(n_cols > 0 && pt_stride >= n_cols + 1, "%s: page table stride %lld must cover n_cols+1=%d pages",
+             who, (long long)pt_stride, n_cols + 1);
+  SV_REQUIRE(score_stride >= ((n_cols + 7) / 8) * 8 && score_stride % 8 == 0,
+             "%s: score_stride=%lld must be a multiple of 8 covering n_cols=%d", who,
+             (long long)score_stride, n_cols);
+  SV_REQUIRE(batch <= 65535, "%s: batch=%d > 65535", who, batch);
+  return 0;
+}
+
+int svb200_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds_layer,
+                            const int32_t* page_table, int64_t page_table_stride,
+                            const int32_t* req_rows, const int32_t* context_lens, void* scores,
+                            int64_t score_stride, int32_t batch, int32_t num_q_heads,
+                            int32_t num_kv_heads, int32_t n_cols, void* stream) {
+  SV_REQUIRE(batch >= 0, "quest_page_score: batch=%d < 0", batch);
+  if (batch == 0) return 0;
+  if (int rc = check_score_args("quest_page_score", q, q_stride_b, bounds_layer, page_table,
+                                page_table_stride, req_rows, context_lens, scores, score_stride,
+                                batch, num_q_heads, num_kv_heads, n_cols))
+    return rc;
+  return launch_quest_page_score(q, q_stride_b, bounds_layer, page_table, page_table_stride,
+                                 req_rows, context_lens, scores, score_stride, batch, num_q_heads,
+                                 num_kv_heads, n_cols, (cudaStream_t)stream);
+}
+
+static int check_select_args(const char* who, int n_cols, int prev_budget, const int32_t* packed,
+                             int64_t out_stride, const int32_t* lens) {
+  SV_REQUIRE(packed && lens, "%s: null output pointer", who);
+  SV_REQUIRE(aligned16(packed) && out_stride % 4 == 0, "%s: packed_slots must be 16-byte aligned with a stride multiple of 4", who);
+  SV_REQUIRE(prev_budget >= 1 && prev_budget <= n_cols, "%s: prev_budget=%d must be in [1, n_cols=%d]", who, prev_budget, n_cols);
+  SV_SUPPORTED(prev_budget <= 2047, "%s: prev_budget=%d > 2047 pages is not supported", who, prev_budget);
+  SV_REQUIRE(out_stride >= (int64_t)(prev_budget + 1) * SVB200_PAGE, "%s: out_stride=%lld < (prev_budget+1)*16", who, (long long)out_stride);
+  return 0;
+}
+
+int svb200_quest_select_pack(const void* scores, int64_t score_stride, int32_t n_cols,
+                             const int32_t* page_table, int64_t page_table_stride,
+                             const int32_t* req_rows, const int32_t* context_lens, int32_t batch,
+                             int32_t prev_budget, int32_t* packed_slots, int64_t out_stride,
+                             int32_t* sparse_lens, int32_t* selected_pages,
+                             const int32_t* dense_token_table, int64_t dense_table_stride,
+                             int32_t token_budget, int32_t page_budget_base, int32_t out_width,
+                             void* stream) {
+  SV_REQUIRE(batch >= 0, "quest_select_pack: batch=%d < 0", batch);
+  if (batch == 0) return 0;
+  SV_REQUIRE(scores && page_table && req_rows && context_lens, "quest_select_pack: null pointer");
+  SV_REQUIRE(aligned16(scores) && score_stride % 8 == 0 && score_stride >= ((n_cols + 7) / 8) * 8,
+             "quest_select_pack: scores must be 16-byte aligned with stride multiple of 8 covering n_cols");
+  SV_REQUIRE(n_cols > 0 && page_table_stride >= n_cols + 1, "quest_select_pack: page table stride must cover n_cols+1 pages");
+  if (int rc = check_select_args("quest_select_pack", n_cols, prev_budget, packed_slots, out_stride, sparse_lens)) return rc;
+  if (dense_token_table != nullptr) {
+    SV_REQUIRE(out_width >= (prev_budget + 1) * SVB200_PAGE && out_stride >= out_width && dense_table_stride >= out_width,
+               "quest_select_pack: out_width=%d must be >= (prev_budget+1)*16 and fit both strides", out_width);
+  }
+  return launch_quest_select_pack(scores, score_stride, n_cols, page_table, page_table_stride,
+                                  req_rows, context_lens, batch, prev_budget, packed_slots,
+                                  out_stride, sparse_lens, selected_pages, dense_token_table,
+                                  dense_table_stride, token_budget, page_budget_base, out_width,
+                                  (cudaStream_t)stream);
+}
+
+int svb200_quest_score_select_pack(const void* q, int64_t q_stride_b, const void* bounds_layer,
+                                   const int32_t* page_table, int64_t page_table_stride,
+                                   const int32_t* req_rows, const int32_t* context_lens,
+                                   void* scores, int64_t score_stride, int32_t batch,
+                                   int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols,
+                                   int32_t prev_budget, int32_t* packed_slots, int64_t out_stride,
+                                   int32_t* sparse_lens, int32_t* selected_pages, int32_t* tickets,
+                                   void* stream) {
+  SV_REQUIRE(batch >= 0, "quest_score_select_pack: batch=%d < 0", batch);
+  if (batch == 0) return 0;
+  if (int rc = check_score_args("quest_score_select_pack", q, q_stride_b, bounds_layer, page_table,
+                                page_table_stride, req_rows, context_lens, scores, score_stride,
+                                batch, num_q_heads, num_kv_heads, n_cols))
+    return rc;
+  if (int rc = check_select_args("quest_score_select_pack", n_cols, prev_budget, packed_slots, out_stride, sparse_lens)) return rc;
+  SV_REQUIRE(tickets != nullptr, "quest_score_select_pack: tickets scratch is null");
+  return launch_quest_score_select_pack(q, q_stride_b, bounds_layer, page_table, page_table_stride,
+                                        req_rows, context_lens, scores, score_stride, batch,
+                                        num_q_heads, num_kv_heads, n_cols, prev_budget,
+                                        packed_slots, out_stride, sparse_lens, selected_pages,
+                                        tickets, (cudaStream_t)stream);
+}
+
+int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_cache,
+                              const void* v_cache, int64_t num_slots, const int32_t* slot_table,
+                              int64_t slot_table_stride, const int32_t* req_rows,
+                              const int32_t* seq_lens, float* mid_o, float* mid_lse, void* out,
+                              int64_t out_stride_b, float* attn_score, int64_t score_stride,
+                              int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
+                              int32_t split_tokens, int32_t num_splits, int32_t heads_per_cta,
+                              int32_t* tickets, float sm_scale, void* stream) {
+  const char* who = "sparse_decode_attn";
+  SV_REQUIRE(batch >= 0, "%s: batch=%d < 0", who, batch);
+  if (batch == 0) return 0;
+  SV_REQUIRE(q && k_cache && v_cache && slot_table && req_rows && seq_lens && out, "%s: null pointer", who);
+  SV_REQUIRE(aligned16(q) && aligned16(k_cache) && aligned16(v_cache) && aligned16(out), "%s: q/k/v/out must be 16-byte aligned", who);
+  if (int rc = check_heads(who, num_q_heads, num_kv_heads)) return rc;
+  SV_REQUIRE(q_stride_b >= (int64_t)num_q_heads * SVB200_HEAD_DIM && q_stride_b % 8 == 0, "%s: bad q stride %lld", who, (long long)q_stride_b);
+  SV_REQUIRE(out_stride_b >= (int64_t)num_q_heads * SVB200_HEAD_DIM && out_stride_b % 8 == 0, "%s: bad out stride %lld", who, (long long)out_stride_b);
+  SV_REQUIRE(num_slots > 0 && slot_table_stride > 0, "%s: num_slots/slot_table_stride must be positive", who);
+  SV_REQUIRE(split_tokens > 0 && split_tokens % SVB200_PAGE == 0 && num_splits >= 1,
+             "%s: split_tokens=%d must be a positive multiple of 16, num_splits=%d >= 1", who, split_tokens, num_splits);
+  if (num_splits > 1) {
+    SV_REQUIRE(mid_o && mid_lse && tickets, "%s: split-K needs mid_o, mid_lse and tickets", who);
+    SV_REQUIRE(aligned16(mid_o), "%s: mid_o must be 16-byte aligned", who);
+  }
+  if (attn_score != nullptr)
+    SV_REQUIRE(score_stride > 0, "%s: score_stride must be positive when attn_score is given", who);
+  SV_REQUIRE(heads_per_cta == 0 || heads_per_cta == 1 || heads_per_cta == 2 || heads_per_cta == 4 || heads_per_cta == 8,
+             "%s: heads_per_cta=%d must be 0 (auto), 1, 2, 4 or 8", who, heads_per_cta);
+  AttnParams p;
+  p.q = q; p.q_stride_b = q_stride_b; p.k_cache = k_cache; p.v_cache = v_cache;
+  p.num_slots = num_slots; p.slot_table = slot_table; p.slot_table_stride = slot_table_stride;
+  p.req_rows = req_rows; p.seq_lens = seq_lens; p.mid_o = mid_o; p.mid_lse = mid_lse; p.out = out;
+  p.out_stride_b = out_stride_b; p.attn_score = attn_score; p.score_stride = score_stride;
+  p.batch = batch; p.hq = num_q_heads; p.hkv = num_kv_heads; p.split_tokens = split_tokens;
+  p.num_splits = num_splits; p.tickets = tickets; p.sm_scale = sm_scale;
+  return launch_sparse_decode_attn(p, heads_per_cta, (cudaStream_t)stream);
+}
+
+int svb200_h2o_normalize_accumulate(float* score, int64_t score_stride, int32_t batch,
+                                    int32_t width, float scale, float* cumulative,
+                                    int64_t cum_stride, const int32_t* kv_lens, void* stream) {
+  SV_REQUIRE(batch >= 0 && width >= 0, "h2o_normalize_accumulate: negative batch/width");
+  if (batch == 0 || width == 0) return 0;
+  SV_REQUIRE(score != nullptr && score_stride >= width, "h2o_normalize_accumulate: score null or stride %lld < width %d", (long long)score_stride, width);
+  if (cumulative != nullptr)
+    SV_REQUIRE(kv_lens != nullptr && cum_stride >= 1, "h2o_normalize_accumulate: cumulative needs kv_lens and a positive stride");
+  return launch_h2o_normalize_accumulate(score, score_stride, batch, width, scale, cumulative,
+                                         cum_stride, kv_lens, (cudaStream_t)stream);
+}
+
+int svb200_h2o_select_compact(float* cumulative, const int64_t* cum_rows, int32_t* slot_tables,
+                              const int64_t* slot_rows, int32_t* free_stack,
+                              const int64_t* free_rows, int32_t* keep_out, int32_t num_rows,
+                              int32_t kv_len, int32_t budget, int32_t recent, void* stream) {
+  SV_REQUIRE(num_rows >= 0, "h2o_select_compact: num_rows=%d < 0", num_rows);
+  if (num_rows == 0) return 0;
+  SV_REQUIRE(cumulative && cum_rows && slot_tables && slot_rows, "h2o_select_compact: null pointer");
+  SV_REQUIRE(budget > 0 && kv_len > budget, "h2o_select_compact: need kv_len=%d > budget=%d > 0", kv_len, budget);
+  SV_REQUIRE(recent >= 1 && recent <= budget, "h2o_select_compact: recent=%d must be in [1, budget=%d]", recent, budget);
+  SV_REQUIRE((free_stack == nullptr) == (free_rows == nullptr), "h2o_select_compact: free_stack and free_rows go together");
+  SV_SUPPORTED((int64_t)kv_len * 12 <= 200 * 1024, "h2o_select_compact: kv_len=%d too long for the shared-memory row cache", kv_len);
+  return launch_h2o_select_compact(cumulative, cum_rows, slot_tables, slot_rows, free_stack,
+                                   free_rows, keep_out, num_rows, kv_len, budget, recent,
+                                   (cudaStream_t)stream);
+}
+
+int svb200_store_kv_minmax(const void* key, int64_t k_stride, const void* value, int64_t v_stride,
+                           void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                           int32_t n_tokens, int32_t num_kv_heads, int64_t num_slots,
+                           void* quest_bounds_layer, void* stream) {
+  SV_REQUIRE(n_tokens >= 0, "store_kv_minmax: n_tokens=%d < 0", n_tokens);
+  if (n_tokens == 0) return 0;
+  SV_REQUIRE(key && value && k_cache && v_cache && slot_mapping, "store_kv_minmax: null pointer");
+  SV_REQUIRE(aligned16(key) && aligned16(value) && aligned16(k_cache) && aligned16(v_cache),
+             "store_kv_minmax: buffers must be 16-byte aligned");
+  SV_REQUIRE(num_kv_heads > 0 && k_stride >= (int64_t)num_kv_heads * SVB200_HEAD_DIM && k_stride % 8 == 0 &&
+                 v_stride >= (int64_t)num_kv_heads * SVB200_HEAD_DIM && v_stride % 8 == 0,
+             "store_kv_minmax: bad key/value token strides %lld/%lld", (long long)k_stride, (long long)v_stride);
+  SV_REQUIRE(num_slots > 0, "store_kv_minmax: num_slots must be positive");
+  if (quest_bounds_layer != nullptr)
+    SV_REQUIRE(aligned16(quest_bounds_layer) && num_slots % SVB200_PAGE == 0, "store_kv_minmax: bounds need 16-byte alignment and paged slots");
+  return launch_store_kv_minmax(key, k_stride, value, v_stride, k_cache, v_cache, slot_mapping,
+                                n_tokens, num_kv_heads, num_slots, quest_bounds_layer,
+                                (cudaStream_t)stream);
+}
+
+}  // extern "C"
