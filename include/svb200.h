@@ -162,6 +162,11 @@ int svb200_quest_score_select_pack(
  *              treated as masked tokens
  *   req_rows   [batch] int32, seq_lens [batch] int32 (tokens visible per row)
  *   mid_o      [batch][Hq][num_splits][128] fp32, mid_lse [batch][Hq][num_splits] fp32
+ *              (the reference hands in sliced views of a cached workspace,
+ *              layers/attention.py:15-51, so element strides are explicit:
+ *              mid_o_strides_host = {batch, head, split} (last dim contiguous, multiples
+ *              of 4), mid_lse_strides_host = {batch, head} (split contiguous); both are
+ *              HOST arrays read during the call; NULL = densely packed)
  *   out        [batch][Hq][128] bf16 (row stride out_stride_b elements)
  *   attn_score NULL (Quest) or fp32 [batch][score_stride] pre-filled by the caller
  *              (reference: -1e20); entry n is max-updated with the raw, unscaled
@@ -175,7 +180,8 @@ int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_c
                               const void* v_cache, int64_t num_slots,
                               const int32_t* slot_table, int64_t slot_table_stride,
                               const int32_t* req_rows, const int32_t* seq_lens,
-                              float* mid_o, float* mid_lse, void* out,
+                              float* mid_o, const int64_t* mid_o_strides_host,
+                              float* mid_lse, const int64_t* mid_lse_strides_host, void* out,
                               int64_t out_stride_b, float* attn_score,
                               int64_t score_stride, int32_t batch, int32_t num_q_heads,
                               int32_t num_kv_heads, int32_t split_tokens,

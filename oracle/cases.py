@@ -1,0 +1,152 @@
+"""Seeded synthetic inputs shared by oracle/gen_golden.py and tests/ (test infrastructure).
+
+Inputs are regenerated from the seed with numpy's PCG64 *integer* stream only (bit-stable
+across platforms), turned into approximately normal bf16 values with exact integer / IEEE
+fp32 arithmetic (Irwin-Hall sum of 4 bytes), so the GPU box rebuilds exactly the tensors the
+golden outputs were generated from; every golden file also stores a sha256 of the regenerated
+tensors so a drift fails loudly instead of comparing against the wrong vectors.
+Large tensors (K/V caches) therefore never need to be committed.
+"""
+from __future__ import annotations
+
+import hashlib
+
+import numpy as np
+import torch
+
+PAGE = 16
+
+QUEST_CASES = {
+    # long-text, ragged last pages incl. an exactly completed page (ctx % 16 == 0)
+    "quest_small_long": dict(seed=11, bsz=3, hq=8, hkv=4, ctx_lens=[512, 500, 389],
+                             max_context_len=512, token_budget=128, is_long_text=True),
+    # Qwen2.5-7B head geometry (28q/4kv, group 7), context bucket larger than one row
+    "quest_g7_bucket": dict(seed=12, bsz=2, hq=28, hkv=4, ctx_lens=[769, 1024],
+                            max_context_len=1024, token_budget=256, is_long_text=True),
+    # Llama geometry (32q/8kv), mixed short/long rows (dense_mask merge, not long-text)
+    "quest_mixed_dense": dict(seed=13, bsz=3, hq=32, hkv=8, ctx_lens=[200, 600, 260],
+                              max_context_len=1024, token_budget=256, is_long_text=False),
+    # group 8 with one KV head (Qwen3-32B at TP=8)
+    "quest_tp8_shard": dict(seed=14, bsz=2, hq=8, hkv=1, ctx_lens=[2000, 1999],
+                            max_context_len=2048, token_budget=1024, is_long_text=True),
+}
+
+ATTN_CASES = {
+    "attn_g7_ragged": dict(seed=21, bsz=3, hq=28, hkv=4, lens=[700, 513, 1], width=768,
+                           num_slots=2048, with_score=False),
+    "attn_g4_score": dict(seed=22, bsz=2, hq=32, hkv=8, lens=[320, 257], width=320,
+                          num_slots=1024, with_score=True),
+    "attn_g8_empty_row": dict(seed=23, bsz=3, hq=8, hkv=1, lens=[64, 0, 300], width=512,
+                              num_slots=1024, with_score=True),
+}
+
+H2O_CASES = {
+    "h2o_select_random": dict(seed=31, rows=6, kv_len=272, budget=256, ratio=0.5, ties=False),
+    "h2o_select_ties": dict(seed=32, rows=5, kv_len=200, budget=96, ratio=0.25, ties=True),
+}
+
+
+def _rng(seed: int) -> np.random.Generator:
+    return np.random.Generator(np.random.PCG64(int(seed)))
+
+
+def randn_bf16(rng: np.random.Generator, *shape: int, scale: float = 1.0) -> torch.Tensor:
+    """~N(0, scale^2) bf16 tensor from integer draws: (sum of 4 bytes - 510) / 147.8 (exact in fp32)."""
+    u = rng.integers(0, 256, size=(*shape, 4), dtype=np.int64).sum(axis=-1)
+    x = (u - 510).astype(np.float32) * np.float32(scale) / np.float32(147.8)
+    return torch.from_numpy(x).to(torch.bfloat16)
+
+
+def randperm(rng: np.random.Generator, n: int) -> torch.Tensor:
+    """Fisher-Yates from integer draws (does not rely on numpy's permutation algorithm)."""
+    a = np.arange(n, dtype=np.int64)
+    for i in range(n - 1, 0, -1):
+        j = int(rng.integers(0, i + 1))
+        a[i], a[j] = a[j], a[i]
+    return torch.from_numpy(a)
+
+
+def bf16_bits(t: torch.Tensor) -> np.ndarray:
+    """bf16 tensor -> uint16 bit-pattern array."""
+    assert t.dtype == torch.bfloat16
+    return t.contiguous().view(torch.int16).numpy().view(np.uint16).copy()
+
+
+def bf16_from_bits(a: np.ndarray) -> torch.Tensor:
+    return torch.from_numpy(a.astype(np.uint16).view(np.int16).copy()).view(torch.bfloat16)
+
+
+def digest(*tensors: torch.Tensor) -> str:
+    h = hashlib.sha256()
+    for t in tensors:
+        t = t.contiguous()
+        if t.dtype == torch.bfloat16:
+            t = t.view(torch.int16)
+        h.update(t.numpy().tobytes())
+    return h.hexdigest()
+
+
+def make_quest_inputs(*, seed, bsz, hq, hkv, ctx_lens, max_context_len, d=128, **_):
+    """Page tables with a shuffled physical page assignment, per-row K/V, q.
+
+    Row 0 of the tables is left unused so that req_indices != arange is exercised.
+    """
+    gen = _rng(seed)
+    rows = bsz + 1
+    max_pages_per_row = (max_context_len + PAGE - 1) // PAGE
+    used = sum((n + PAGE - 1) // PAGE for n in ctx_lens)
+    num_pages = used + 3
+    perm = randperm(gen, num_pages).to(torch.int32)
+    page_table = torch.full((rows, max_pages_per_row), -1, dtype=torch.int32)
+    token_table = torch.zeros((rows, max_context_len), dtype=torch.int32)
+    req_indices = torch.arange(1, bsz + 1, dtype=torch.int32)
+    ks, vs, slot_rows = [], [], []
+    cursor = 0
+    for b in range(bsz):
+        n = int(ctx_lens[b])
+        npg = (n + PAGE - 1) // PAGE
+        pg = perm[cursor:cursor + npg]
+        cursor += npg
+        row = int(req_indices[b])
+        page_table[row, :npg] = pg
+        slots = (pg[:, None] * PAGE + torch.arange(PAGE, dtype=torch.int32)[None, :]).reshape(-1)[:n]
+        token_table[row, :n] = slots
+        ks.append(randn_bf16(gen, n, hkv, d))
+        vs.append(randn_bf16(gen, n, hkv, d))
+        slot_rows.append(slots)
+    q = randn_bf16(gen, bsz, hq, d)
+    return dict(num_pages=num_pages, max_pages_per_row=max_pages_per_row, page_table=page_table,
+                token_table=token_table, req_indices=req_indices, k_rows=ks, v_rows=vs,
+                slot_rows=slot_rows, q=q, context_lens=torch.tensor(ctx_lens, dtype=torch.int32))
+
+
+def quest_fill_cache(inp, hkv, d=128):
+    """K/V caches [num_pages*16, Hkv, D] with every row's tokens written at its slots."""
+    k_cache = torch.zeros(inp["num_pages"] * PAGE, hkv, d, dtype=torch.bfloat16)
+    v_cache = torch.zeros_like(k_cache)
+    for k, v, slots in zip(inp["k_rows"], inp["v_rows"], inp["slot_rows"]):
+        k_cache.index_copy_(0, slots.long(), k)
+        v_cache.index_copy_(0, slots.long(), v)
+    return k_cache, v_cache
+
+
+def make_attn_inputs(*, seed, bsz, hq, hkv, lens, width, num_slots, d=128, **_):
+    gen = _rng(seed)
+    q = randn_bf16(gen, bsz, hq, d)
+    k_cache = randn_bf16(gen, num_slots, hkv, d)
+    v_cache = randn_bf16(gen, num_slots, hkv, d)
+    rows = bsz + 1
+    table = torch.zeros((rows, width), dtype=torch.int32)
+    for r in range(rows):
+        table[r] = randperm(gen, num_slots)[:width].to(torch.int32)
+    req = torch.arange(bsz, 0, -1, dtype=torch.int32)  # reversed rows
+    return dict(q=q, k_cache=k_cache, v_cache=v_cache, slot_table=table, req_indices=req,
+                seq_lens=torch.tensor(lens, dtype=torch.int32))
+
+
+def make_h2o_scores(*, seed, rows, kv_len, ties, **_):
+    gen = _rng(seed)
+    scores = torch.from_numpy(gen.integers(0, 1 << 24, size=(rows, kv_len)).astype(np.float32) / np.float32(1 << 24))
+    if ties:
+        scores = (scores * 8).floor() / 8  # massive ties: the stable order must decide
+    return scores

@@ -205,8 +205,9 @@ int svb200_quest_score_select_pack(const void* q, int64_t q_stride_b, const void
 int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_cache,
                               const void* v_cache, int64_t num_slots, const int32_t* slot_table,
                               int64_t slot_table_stride, const int32_t* req_rows,
-                              const int32_t* seq_lens, float* mid_o, float* mid_lse, void* out,
-                              int64_t out_stride_b, float* attn_score, int64_t score_stride,
+                              const int32_t* seq_lens, float* mid_o,
+                              const int64_t* mid_o_strides_host, float* mid_lse,
+                              const int64_t* mid_lse_strides_host, void* out, int64_t out_stride_b, float* attn_score, int64_t score_stride,
                               int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
                               int32_t split_tokens, int32_t num_splits, int32_t heads_per_cta,
                               int32_t* tickets, float sm_scale, void* stream) {
@@ -236,6 +237,20 @@ int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_c
   p.out_stride_b = out_stride_b; p.attn_score = attn_score; p.score_stride = score_stride;
   p.batch = batch; p.hq = num_q_heads; p.hkv = num_kv_heads; p.split_tokens = split_tokens;
   p.num_splits = num_splits; p.tickets = tickets; p.sm_scale = sm_scale;
+  if (mid_o_strides_host != nullptr) {
+    p.mo_sb = mid_o_strides_host[0]; p.mo_sh = mid_o_strides_host[1]; p.mo_ss = mid_o_strides_host[2];
+  } else {
+    p.mo_ss = SVB200_HEAD_DIM; p.mo_sh = p.mo_ss * num_splits; p.mo_sb = p.mo_sh * num_q_heads;
+  }
+  if (mid_lse_strides_host != nullptr) {
+    p.ml_sb = mid_lse_strides_host[0]; p.ml_sh = mid_lse_strides_host[1];
+  } else {
+    p.ml_sh = num_splits; p.ml_sb = p.ml_sh * num_q_heads;
+  }
+  if (num_splits > 1)
+    SV_REQUIRE(p.mo_ss >= SVB200_HEAD_DIM && p.mo_ss % 4 == 0 && p.mo_sh % 4 == 0 && p.mo_sb % 4 == 0 &&
+                   p.ml_sh >= num_splits,
+               "%s: mid_o strides must be multiples of 4 with split stride >= 128, mid_lse head stride >= num_splits", who);
   return launch_sparse_decode_attn(p, heads_per_cta, (cudaStream_t)stream);
 }
 

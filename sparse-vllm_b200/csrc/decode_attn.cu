@@ -118,7 +118,6 @@ template <int HPC, int NT, bool WITH_SCORE>
 __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(AttnParams p) {
   using G = AttnGeom<HPC>;
   constexpr int TL = G::TL;
-  constexpr int NREG = NT * 36;  // merge record: m[2] l[2] o[32] per n-tile
 
   extern __shared__ __align__(128) unsigned char smem[];
   unsigned char* sK = smem;                                   // [stages][TILE_BYTES]
@@ -411,15 +410,16 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
                 orow[dt * 16 + g + 8] = __float2bfloat16_rn(o_acc[nt][dt][2 + j] * inv);
               }
             } else {
-              const int64_t pidx = ((int64_t)b * p.hq + head) * p.num_splits + split;
-              float* orow = p.mid_o + pidx * kHeadDim;
+              float* orow = p.mid_o + (int64_t)b * p.mo_sb + (int64_t)head * p.mo_sh +
+                            (int64_t)split * p.mo_ss;
 #pragma unroll
               for (int dt = 0; dt < 8; ++dt) {
                 orow[dt * 16 + g] = o_acc[nt][dt][j] * inv;
                 orow[dt * 16 + g + 8] = o_acc[nt][dt][2 + j] * inv;
               }
               if (g == 0)
-                p.mid_lse[pidx] = l > 0.f ? m_run[nt][j] * kLn2 + __logf(l) : -INFINITY;
+                p.mid_lse[(int64_t)b * p.ml_sb + (int64_t)head * p.ml_sh + split] =
+                    l > 0.f ? m_run[nt][j] * kLn2 + __logf(l) : -INFINITY;
             }
           }
         }
@@ -440,18 +440,19 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
         const int nheads = HPC * gsz;
         for (int w = tid; w < nheads * 32; w += kAttnThreads) {
           const int head = hg * nheads + (w >> 5), d4 = w & 31;
-          const int64_t base = ((int64_t)b * p.hq + head) * p.num_splits;
+          const float* lse_row = p.mid_lse + (int64_t)b * p.ml_sb + (int64_t)head * p.ml_sh;
+          const float* o_row = p.mid_o + (int64_t)b * p.mo_sb + (int64_t)head * p.mo_sh;
           float mx = -INFINITY;
           for (int sidx = 0; sidx < p.num_splits; ++sidx)
-            mx = fmaxf(mx, __ldcg(p.mid_lse + base + sidx));
+            mx = fmaxf(mx, __ldcg(lse_row + sidx));
           float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
           float wsum = 0.f;
           for (int sidx = 0; sidx < p.num_splits; ++sidx) {
-            const float lse = __ldcg(p.mid_lse + base + sidx);
+            const float lse = __ldcg(lse_row + sidx);
             if (lse == -INFINITY) continue;
             const float wgt = __expf(lse - mx);
             const float4 v =
-                __ldcg(reinterpret_cast<const float4*>(p.mid_o + (base + sidx) * kHeadDim) + d4);
+                __ldcg(reinterpret_cast<const float4*>(o_row + (int64_t)sidx * p.mo_ss) + d4);
             acc.x += wgt * v.x, acc.y += wgt * v.y, acc.z += wgt * v.z, acc.w += wgt * v.w;
             wsum += wgt;
           }

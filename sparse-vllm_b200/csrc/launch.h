@@ -51,6 +51,8 @@ struct AttnParams {
   const int32_t* seq_lens;
   float* mid_o;
   float* mid_lse;
+  int64_t mo_sb, mo_sh, mo_ss;  // mid_o element strides (batch, head, split)
+  int64_t ml_sb, ml_sh;         // mid_lse element strides (batch, head)
   void* out;
   int64_t out_stride_b;
   float* attn_score;

@@ -1,0 +1,295 @@
+"""Torch-tensor front end of the C ABI (include/svb200.h).
+
+Each function validates devices / dtypes / contiguity the way the reference's Triton wrappers
+do (fail fast, kernels/triton/gqa_flash_decoding_stage1.py:298-352), passes raw device pointers
+to libsvb200.so on the CURRENT torch stream and converts non-zero return codes into
+RuntimeError.  No function here computes anything on the host and none has a fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+
+import torch
+
+from . import _native
+from ._native import check, current_stream_ptr, ptr, require_cuda
+
+HEAD_DIM = 128
+PAGE = 16
+
+
+def _i32(t: torch.Tensor, name: str) -> None:
+    require_cuda(t, name, torch.int32)
+    if t.dim() >= 1 and t.stride(-1) != 1:
+        raise ValueError(f"{name} must be contiguous in its last dimension, got strides {t.stride()}.")
+
+
+def _rows_stride(t: torch.Tensor, name: str) -> int:
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError(f"{name} must be 2-D with a contiguous last dimension, got {tuple(t.shape)}/{t.stride()}.")
+    return int(t.stride(0))
+
+
+def _kv_layer(t: torch.Tensor, name: str) -> tuple[int, int]:
+    """[slots, Hkv, 128] bf16 contiguous -> (num_slots, Hkv)."""
+    require_cuda(t, name, torch.bfloat16)
+    if t.dim() != 3 or t.shape[2] != HEAD_DIM or not t.is_contiguous():
+        raise ValueError(f"{name} must be a contiguous [slots, Hkv, {HEAD_DIM}] tensor, got {tuple(t.shape)}/{t.stride()}.")
+    return int(t.shape[0]), int(t.shape[1])
+
+
+def _q(t: torch.Tensor, name: str) -> tuple[int, int, int]:
+    """[B, Hq, 128] bf16 with contiguous (head, dim) -> (B, Hq, batch stride)."""
+    require_cuda(t, name, torch.bfloat16)
+    if t.dim() != 3 or t.shape[2] != HEAD_DIM or t.stride(2) != 1 or t.stride(1) != HEAD_DIM:
+        raise ValueError(f"{name} must be [B, H, {HEAD_DIM}] with contiguous heads, got {tuple(t.shape)}/{t.stride()}.")
+    return int(t.shape[0]), int(t.shape[1]), int(t.stride(0))
+
+
+def _bounds_layer(t: torch.Tensor, hkv: int, name: str = "bounds_layer") -> int:
+    """[pages, 2, Hkv, 128] bf16 contiguous -> num_pages."""
+    require_cuda(t, name, torch.bfloat16)
+    if t.dim() != 4 or tuple(t.shape[1:]) != (2, hkv, HEAD_DIM) or not t.is_contiguous():
+        raise ValueError(f"{name} must be a contiguous [pages, 2, {hkv}, {HEAD_DIM}] tensor, got {tuple(t.shape)}.")
+    return int(t.shape[0])
+
+
+def sm_count() -> int:
+    return _native.sm_count()
+
+
+# ----------------------------------------------------------------------------- Quest bounds
+def quest_page_minmax(k_cache: torch.Tensor, bounds_layer: torch.Tensor, slot_mapping: torch.Tensor) -> None:
+    """Rebuild the bounds of every page completed by ``slot_mapping`` (svb200_quest_page_minmax)."""
+    num_slots, hkv = _kv_layer(k_cache, "k_cache")
+    _bounds_layer(bounds_layer, hkv)
+    _i32(slot_mapping, "slot_mapping")
+    lib = _native.load()
+    check(lib.svb200_quest_page_minmax(ptr(k_cache), ptr(bounds_layer), ptr(slot_mapping),
+                                       int(slot_mapping.numel()), hkv, num_slots,
+                                       current_stream_ptr(k_cache.device)), "svb200_quest_page_minmax")
+
+
+def quest_decode_page_complete(k_cache_all: torch.Tensor, bounds_all: torch.Tensor, page_table: torch.Tensor,
+                               req_rows: torch.Tensor, seq_lens: torch.Tensor) -> None:
+    """All-layer refresh of pages completed by this decode step (svb200_quest_decode_page_complete).
+
+    k_cache_all [L, slots, Hkv, 128], bounds_all [L, pages, 2, Hkv, 128]."""
+    require_cuda(k_cache_all, "k_cache_all", torch.bfloat16)
+    require_cuda(bounds_all, "bounds_all", torch.bfloat16)
+    if k_cache_all.dim() != 4 or not k_cache_all.is_contiguous() or k_cache_all.shape[3] != HEAD_DIM:
+        raise ValueError(f"k_cache_all must be contiguous [L, slots, Hkv, {HEAD_DIM}], got {tuple(k_cache_all.shape)}.")
+    layers, num_slots, hkv, _ = (int(x) for x in k_cache_all.shape)
+    if bounds_all.dim() != 5 or not bounds_all.is_contiguous() or tuple(bounds_all.shape[2:]) != (2, hkv, HEAD_DIM) \
+            or int(bounds_all.shape[0]) != layers:
+        raise ValueError(f"bounds_all must be contiguous [L, pages, 2, Hkv, {HEAD_DIM}], got {tuple(bounds_all.shape)}.")
+    num_pages = int(bounds_all.shape[1])
+    _i32(page_table, "page_table"); _i32(req_rows, "req_rows"); _i32(seq_lens, "seq_lens")
+    lib = _native.load()
+    check(lib.svb200_quest_decode_page_complete(
+        ptr(k_cache_all), ptr(bounds_all), ptr(page_table), _rows_stride(page_table, "page_table"),
+        ptr(req_rows), ptr(seq_lens), int(req_rows.numel()), layers, hkv, num_slots, num_pages,
+        current_stream_ptr(k_cache_all.device)), "svb200_quest_decode_page_complete")
+
+
+# ----------------------------------------------------------------------------- Quest select
+def score_row_stride(n_cols: int) -> int:
+    return (int(n_cols) + 7) // 8 * 8
+
+
+def quest_page_score(q: torch.Tensor, bounds_layer: torch.Tensor, page_table: torch.Tensor,
+                     req_rows: torch.Tensor, context_lens: torch.Tensor, n_cols: int,
+                     num_kv_heads: int, scores: torch.Tensor | None = None) -> torch.Tensor:
+    """bf16 page scores [B, stride>=n_cols] (svb200_quest_page_score)."""
+    bsz, hq, qs = _q(q, "q")
+    _bounds_layer(bounds_layer, num_kv_heads)
+    _i32(page_table, "page_table"); _i32(req_rows, "req_rows"); _i32(context_lens, "context_lens")
+    if scores is None:
+        scores = torch.empty((bsz, score_row_stride(n_cols)), dtype=torch.bfloat16, device=q.device)
+    require_cuda(scores, "scores", torch.bfloat16)
+    lib = _native.load()
+    check(lib.svb200_quest_page_score(
+        ptr(q), qs, ptr(bounds_layer), ptr(page_table), _rows_stride(page_table, "page_table"),
+        ptr(req_rows), ptr(context_lens), ptr(scores), _rows_stride(scores, "scores"), bsz, hq,
+        int(num_kv_heads), int(n_cols), current_stream_ptr(q.device)), "svb200_quest_page_score")
+    return scores
+
+
+def quest_select_pack(scores: torch.Tensor, n_cols: int, page_table: torch.Tensor, req_rows: torch.Tensor,
+                      context_lens: torch.Tensor, prev_budget: int, packed_slots: torch.Tensor,
+                      sparse_lens: torch.Tensor, selected_pages: torch.Tensor | None = None,
+                      dense_token_table: torch.Tensor | None = None, token_budget: int = 0,
+                      page_budget_base: int = 0, out_width: int = 0) -> None:
+    """Top-k + last page + slot packing (svb200_quest_select_pack)."""
+    require_cuda(scores, "scores", torch.bfloat16)
+    _i32(page_table, "page_table"); _i32(req_rows, "req_rows"); _i32(context_lens, "context_lens")
+    _i32(packed_slots, "packed_slots"); _i32(sparse_lens, "sparse_lens")
+    bsz = int(req_rows.numel())
+    if selected_pages is not None:
+        _i32(selected_pages, "selected_pages")
+        if tuple(selected_pages.shape) != (bsz, prev_budget + 1) or not selected_pages.is_contiguous():
+            raise ValueError("selected_pages must be a contiguous [B, prev_budget+1] int32 tensor.")
+    dense_stride = 0
+    if dense_token_table is not None:
+        _i32(dense_token_table, "dense_token_table")
+        dense_stride = _rows_stride(dense_token_table, "dense_token_table")
+    lib = _native.load()
+    check(lib.svb200_quest_select_pack(
+        ptr(scores), _rows_stride(scores, "scores"), int(n_cols), ptr(page_table),
+        _rows_stride(page_table, "page_table"), ptr(req_rows), ptr(context_lens), bsz, int(prev_budget),
+        ptr(packed_slots), _rows_stride(packed_slots, "packed_slots"), ptr(sparse_lens), ptr(selected_pages),
+        ptr(dense_token_table), dense_stride, int(token_budget), int(page_budget_base), int(out_width),
+        current_stream_ptr(scores.device)), "svb200_quest_select_pack")
+
+
+def quest_score_select_pack(q: torch.Tensor, bounds_layer: torch.Tensor, page_table: torch.Tensor,
+                            req_rows: torch.Tensor, context_lens: torch.Tensor, n_cols: int, num_kv_heads: int,
+                            prev_budget: int, scores: torch.Tensor, packed_slots: torch.Tensor,
+                            sparse_lens: torch.Tensor, tickets: torch.Tensor,
+                            selected_pages: torch.Tensor | None = None) -> None:
+    """One-launch score + select + pack for long-text batches (svb200_quest_score_select_pack)."""
+    bsz, hq, qs = _q(q, "q")
+    _bounds_layer(bounds_layer, num_kv_heads)
+    require_cuda(scores, "scores", torch.bfloat16)
+    for t, n in ((page_table, "page_table"), (req_rows, "req_rows"), (context_lens, "context_lens"),
+                 (packed_slots, "packed_slots"), (sparse_lens, "sparse_lens"), (tickets, "tickets")):
+        _i32(t, n)
+    if tickets.numel() < bsz:
+        raise ValueError(f"tickets needs >= {bsz} int32 entries, got {tickets.numel()}.")
+    if selected_pages is not None:
+        _i32(selected_pages, "selected_pages")
+    lib = _native.load()
+    check(lib.svb200_quest_score_select_pack(
+        ptr(q), qs, ptr(bounds_layer), ptr(page_table), _rows_stride(page_table, "page_table"),
+        ptr(req_rows), ptr(context_lens), ptr(scores), _rows_stride(scores, "scores"), bsz, hq,
+        int(num_kv_heads), int(n_cols), int(prev_budget), ptr(packed_slots),
+        _rows_stride(packed_slots, "packed_slots"), ptr(sparse_lens), ptr(selected_pages), ptr(tickets),
+        current_stream_ptr(q.device)), "svb200_quest_score_select_pack")
+
+
+# ----------------------------------------------------------------------------- attention
+def attn_workspace_tickets(batch: int, num_kv_heads: int, device) -> torch.Tensor:
+    """Zeroed int32 arrival tickets (svb200_workspace_bytes); kernels leave them zeroed."""
+    nbytes = int(_native.load().svb200_workspace_bytes(int(batch), int(num_kv_heads)))
+    return torch.zeros((max(nbytes // 4, 1),), dtype=torch.int32, device=device)
+
+
+def sparse_decode_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, slot_table: torch.Tensor,
+                       req_rows: torch.Tensor, seq_lens: torch.Tensor, *, out: torch.Tensor,
+                       mid_o: torch.Tensor | None, mid_lse: torch.Tensor | None, tickets: torch.Tensor | None,
+                       split_tokens: int, num_splits: int, attn_score: torch.Tensor | None = None,
+                       heads_per_cta: int = 0, sm_scale: float | None = None) -> torch.Tensor:
+    """Split-K sparse paged GQA decode attention with fused combine (svb200_sparse_decode_attn)."""
+    bsz, hq, qs = _q(q, "q")
+    num_slots, hkv = _kv_layer(k_cache, "k_cache")
+    if _kv_layer(v_cache, "v_cache") != (num_slots, hkv):
+        raise ValueError("k_cache and v_cache must have identical shapes.")
+    ob, oh, os_ = _q(out, "out")
+    if (ob, oh) != (bsz, hq):
+        raise ValueError(f"out must be [B, Hq, {HEAD_DIM}] like q, got {tuple(out.shape)}.")
+    _i32(slot_table, "slot_table"); _i32(req_rows, "req_rows"); _i32(seq_lens, "seq_lens")
+    if int(req_rows.numel()) != bsz or int(seq_lens.numel()) != bsz:
+        raise ValueError("req_rows / seq_lens must have one entry per q row.")
+    mo_strides = ml_strides = None
+    if num_splits > 1:
+        if mid_o is None or mid_lse is None or tickets is None:
+            raise ValueError("split-K (num_splits > 1) needs mid_o, mid_lse and tickets.")
+        require_cuda(mid_o, "mid_o", torch.float32); require_cuda(mid_lse, "mid_lse", torch.float32)
+        _i32(tickets, "tickets")
+        if mid_o.dim() != 4 or mid_o.shape[0] < bsz or mid_o.shape[1] < hq or mid_o.shape[2] < num_splits \
+                or mid_o.shape[3] != HEAD_DIM or mid_o.stride(3) != 1:
+            raise ValueError(f"mid_o must be [>=B, >=Hq, >=num_splits, {HEAD_DIM}] fp32, got {tuple(mid_o.shape)}.")
+        if mid_lse.dim() != 3 or mid_lse.shape[0] < bsz or mid_lse.shape[1] < hq or mid_lse.shape[2] < num_splits \
+                or mid_lse.stride(2) != 1:
+            raise ValueError(f"mid_lse must be [>=B, >=Hq, >=num_splits] fp32, got {tuple(mid_lse.shape)}.")
+        if tickets.numel() * 4 < int(_native.load().svb200_workspace_bytes(bsz, hkv)):
+            raise ValueError("tickets scratch is smaller than svb200_workspace_bytes(batch, num_kv_heads).")
+        mo_strides = (ctypes.c_int64 * 3)(mid_o.stride(0), mid_o.stride(1), mid_o.stride(2))
+        ml_strides = (ctypes.c_int64 * 2)(mid_lse.stride(0), mid_lse.stride(1))
+    score_stride = 0
+    if attn_score is not None:
+        require_cuda(attn_score, "attn_score", torch.float32)
+        if attn_score.dim() != 2 or attn_score.shape[0] < bsz or attn_score.stride(1) != 1:
+            raise ValueError(f"attn_score must be fp32 [B, W] with contiguous W, got {tuple(attn_score.shape)}.")
+        score_stride = int(attn_score.stride(0))
+    if sm_scale is None:
+        sm_scale = 1.0 / math.sqrt(HEAD_DIM)
+    lib = _native.load()
+    check(lib.svb200_sparse_decode_attn(
+        ptr(q), qs, ptr(k_cache), ptr(v_cache), num_slots, ptr(slot_table), _rows_stride(slot_table, "slot_table"),
+        ptr(req_rows), ptr(seq_lens), ptr(mid_o), mo_strides, ptr(mid_lse), ml_strides, ptr(out), os_,
+        ptr(attn_score), score_stride, bsz, hq, hkv, int(split_tokens), int(num_splits), int(heads_per_cta),
+        ptr(tickets), float(sm_scale), current_stream_ptr(q.device)), "svb200_sparse_decode_attn")
+    return out
+
+
+# ----------------------------------------------------------------------------- H2O
+def h2o_normalize_accumulate(score: torch.Tensor, scale: float, cumulative: torch.Tensor | None = None,
+                             kv_lens: torch.Tensor | None = None, width: int | None = None) -> torch.Tensor:
+    """In-place ``softmax(score * scale)`` per row (+ fused cumulative update) (svb200_h2o_normalize_accumulate)."""
+    require_cuda(score, "score", torch.float32)
+    if score.dim() != 2 or score.stride(1) != 1:
+        raise ValueError(f"score must be fp32 [B, W] with contiguous W, got {tuple(score.shape)}/{score.stride()}.")
+    bsz = int(score.shape[0])
+    width = int(score.shape[1]) if width is None else int(width)
+    cum_stride = 0
+    if cumulative is not None:
+        require_cuda(cumulative, "cumulative", torch.float32)
+        if cumulative.dim() != 2 or cumulative.shape[0] < bsz or cumulative.stride(1) != 1 or kv_lens is None:
+            raise ValueError("cumulative must be fp32 [B, >=kv_len] and needs kv_lens.")
+        _i32(kv_lens, "kv_lens")
+        cum_stride = int(cumulative.stride(0))
+    lib = _native.load()
+    check(lib.svb200_h2o_normalize_accumulate(
+        ptr(score), int(score.stride(0)), bsz, width, float(scale), ptr(cumulative), cum_stride, ptr(kv_lens),
+        current_stream_ptr(score.device)), "svb200_h2o_normalize_accumulate")
+    return score
+
+
+def h2o_select_compact(cumulative: torch.Tensor, cum_rows: torch.Tensor, slot_tables: torch.Tensor,
+                       slot_rows: torch.Tensor, *, kv_len: int, budget: int, recent: int,
+                       free_stack: torch.Tensor | None = None, free_rows: torch.Tensor | None = None,
+                       keep_out: torch.Tensor | None = None) -> None:
+    """Burst eviction: heavy hitters + recent suffix, index-only compaction (svb200_h2o_select_compact).
+
+    ``cum_rows`` / ``slot_rows`` / ``free_rows`` are int64 ELEMENT offsets of each (layer,row) entry
+    inside ``cumulative`` / ``slot_tables`` / ``free_stack``."""
+    require_cuda(cumulative, "cumulative", torch.float32)
+    _i32(slot_tables, "slot_tables")
+    for t, n in ((cum_rows, "cum_rows"), (slot_rows, "slot_rows")):
+        require_cuda(t, n, torch.int64)
+    n_rows = int(cum_rows.numel())
+    if int(slot_rows.numel()) != n_rows:
+        raise ValueError("cum_rows and slot_rows must have the same number of entries.")
+    if free_stack is not None:
+        _i32(free_stack, "free_stack"); require_cuda(free_rows, "free_rows", torch.int64)
+    if keep_out is not None:
+        _i32(keep_out, "keep_out")
+        if tuple(keep_out.shape) != (n_rows, budget) or not keep_out.is_contiguous():
+            raise ValueError("keep_out must be a contiguous [num_rows, budget] int32 tensor.")
+    lib = _native.load()
+    check(lib.svb200_h2o_select_compact(
+        ptr(cumulative), ptr(cum_rows), ptr(slot_tables), ptr(slot_rows), ptr(free_stack), ptr(free_rows),
+        ptr(keep_out), n_rows, int(kv_len), int(budget), int(recent),
+        current_stream_ptr(cumulative.device)), "svb200_h2o_select_compact")
+
+
+# ----------------------------------------------------------------------------- KV store
+def store_kv_minmax(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                    slot_mapping: torch.Tensor, quest_bounds_layer: torch.Tensor | None = None) -> None:
+    """Scatter new K/V rows (+ fused bounds refresh of completed pages) (svb200_store_kv_minmax)."""
+    num_slots, hkv = _kv_layer(k_cache, "k_cache")
+    _kv_layer(v_cache, "v_cache")
+    for t, n in ((key, "key"), (value, "value")):
+        require_cuda(t, n, torch.bfloat16)
+        if t.dim() != 3 or tuple(t.shape[1:]) != (hkv, HEAD_DIM) or t.stride(2) != 1 or t.stride(1) != HEAD_DIM:
+            raise ValueError(f"{n} must be [T, {hkv}, {HEAD_DIM}] with contiguous heads, got {tuple(t.shape)}/{t.stride()}.")
+    _i32(slot_mapping, "slot_mapping")
+    if quest_bounds_layer is not None:
+        _bounds_layer(quest_bounds_layer, hkv, "quest_bounds_layer")
+    lib = _native.load()
+    check(lib.svb200_store_kv_minmax(
+        ptr(key), int(key.stride(0)), ptr(value), int(value.stride(0)), ptr(k_cache), ptr(v_cache),
+        ptr(slot_mapping), int(slot_mapping.numel()), hkv, num_slots, ptr(quest_bounds_layer),
+        current_stream_ptr(key.device)), "svb200_store_kv_minmax")

@@ -1,0 +1,297 @@
+"""GPU parity: Quest bounds, page scoring, top-k selection and slot packing — CUDA path (through the
+C ABI) vs the oracle and the committed reference outputs.  Integer/index results are bit-exact except
+on exactly tied scores (north_star); bf16 scores are classified exact / 1-ulp (accumulation order)."""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import cases, quest as oquest
+
+pytestmark = pytest.mark.gpu
+PAGE = 16
+DEV = "cuda:0"
+
+
+def _setup(name, golden):
+    cfg = cases.QUEST_CASES[name]
+    inp = cases.make_quest_inputs(**cfg)
+    k_cache, v_cache = cases.quest_fill_cache(inp, cfg["hkv"])
+    g = golden(name)
+    assert str(g["digest"]) == cases.digest(inp["q"], k_cache, v_cache, inp["page_table"], inp["token_table"])
+    return cfg, inp, k_cache, v_cache, g
+
+
+def _complete_pages(inp, cfg):
+    pages = []
+    for b, n in enumerate(cfg["ctx_lens"]):
+        pages += inp["page_table"][int(inp["req_indices"][b]), : n // PAGE].tolist()
+    return torch.tensor(sorted(pages), dtype=torch.long)
+
+
+def _device_bounds(g):
+    mx = cases.bf16_from_bits(g["bounds_max"])
+    mn = cases.bf16_from_bits(g["bounds_min"])
+    return torch.stack((mx, mn), dim=1).contiguous().to(DEV)  # [P, 2, Hkv, D]
+
+
+@pytest.mark.parametrize("name", list(cases.QUEST_CASES))
+def test_page_minmax_prefill_chunks(name, golden):
+    """on_kv_stored semantics: bounds appear when a page completes, also across chunk boundaries."""
+    from sparse_vllm_b200 import ops
+    cfg, inp, k_cache, v_cache, g = _setup(name, golden)
+    hkv = cfg["hkv"]
+    kc = torch.zeros_like(k_cache, device=DEV)
+    vc = torch.zeros_like(v_cache, device=DEV)
+    bounds = torch.zeros(inp["num_pages"], 2, hkv, 128, dtype=torch.bfloat16, device=DEV)
+    for b, n in enumerate(cfg["ctx_lens"]):
+        k, v, slots = inp["k_rows"][b].to(DEV), inp["v_rows"][b].to(DEV), inp["slot_rows"][b].to(DEV)
+        cut = max(1, (n // 2) | 5) if n > 2 else n
+        for lo, hi in ((0, min(cut, n)), (min(cut, n), n)):
+            if hi <= lo:
+                continue
+            ops.store_kv_minmax(k[lo:hi], v[lo:hi], kc, vc, slots[lo:hi])          # plain store
+            ops.quest_page_minmax(kc, bounds, slots[lo:hi])                          # then bounds
+    torch.cuda.synchronize()
+    assert torch.equal(kc.cpu(), k_cache) and torch.equal(vc.cpu(), v_cache)
+    pages = _complete_pages(inp, cfg)
+    ref = _device_bounds(g).cpu()
+    got = bounds.cpu()
+    assert torch.equal(got[pages], ref[pages])
+    rest = torch.ones(got.shape[0], dtype=torch.bool)
+    rest[pages] = False
+    assert not got[rest].any(), "bounds written for a page that was never completed"
+
+
+@pytest.mark.parametrize("name", ["quest_small_long", "quest_tp8_shard"])
+def test_decode_store_fused_minmax_and_page_complete(name, golden):
+    """Decode: the token that completes a page refreshes its bounds (fused store path and the
+    all-layer on_forward_end replacement give the same result)."""
+    from sparse_vllm_b200 import ops
+    cfg, inp, k_cache, v_cache, g = _setup(name, golden)
+    hkv, bsz = cfg["hkv"], cfg["bsz"]
+    layers = 3
+    ref = _device_bounds(g)
+    pages = _complete_pages(inp, cfg).to(DEV)
+    # state before the decode step: last token of each row missing, pages it would complete unset
+    kc_all = k_cache.to(DEV)[None].repeat(layers, 1, 1, 1).contiguous()
+    vc_all = v_cache.to(DEV)[None].repeat(layers, 1, 1, 1).contiguous()
+    last_slots = torch.tensor([int(inp["slot_rows"][b][-1]) for b in range(bsz)], dtype=torch.int32, device=DEV)
+    new_k = kc_all[0][last_slots.long()].clone()
+    new_v = vc_all[0][last_slots.long()].clone()
+    kc_all[:, last_slots.long()] = 0
+    bounds_fused = torch.zeros(layers, inp["num_pages"], 2, hkv, 128, dtype=torch.bfloat16, device=DEV)
+    bounds_fused[:, pages] = ref[pages]
+    completing = [b for b, n in enumerate(cfg["ctx_lens"]) if n % PAGE == 0]
+    for b in completing:
+        bounds_fused[:, int(last_slots[b]) // PAGE] = 0
+    bounds_late = bounds_fused.clone()
+    # padded batch entry (slot -1) must be skipped
+    slot_mapping = torch.cat((last_slots, torch.tensor([-1], dtype=torch.int32, device=DEV)))
+    new_k = torch.cat((new_k, new_k[:1]))
+    new_v = torch.cat((new_v, new_v[:1]))
+    kc_late = kc_all.clone()
+    for layer in range(layers):
+        ops.store_kv_minmax(new_k, new_v, kc_all[layer], vc_all[layer], slot_mapping, bounds_fused[layer])
+        ops.store_kv_minmax(new_k, new_v, kc_late[layer], vc_all[layer], slot_mapping)
+    ops.quest_decode_page_complete(kc_late, bounds_late, inp["page_table"].to(DEV), inp["req_indices"].to(DEV),
+                                   inp["context_lens"].to(DEV))
+    torch.cuda.synchronize()
+    for layer in range(layers):
+        assert torch.equal(kc_all[layer].cpu(), k_cache)
+        assert torch.equal(bounds_fused[layer][pages].cpu(), ref[pages].cpu())
+        assert torch.equal(bounds_late[layer][pages].cpu(), ref[pages].cpu())
+
+
+def _score_stats(got_bits, ref_bits, n_valid):
+    exact = ulp1 = bad = 0
+    for b in range(got_bits.shape[0]):
+        nv = int(n_valid[b])
+        d = oquest.bf16_ulp_distance(got_bits[b, :nv], ref_bits[b, :nv])
+        exact += int((d == 0).sum()); ulp1 += int((d == 1).sum()); bad += int((d > 1).sum())
+    return exact, ulp1, bad
+
+
+@pytest.mark.parametrize("name", list(cases.QUEST_CASES))
+def test_page_scores(name, golden):
+    from sparse_vllm_b200 import ops
+    cfg, inp, _, _, g = _setup(name, golden)
+    bounds = _device_bounds(g)
+    max_pages = min(inp["max_pages_per_row"], (cfg["max_context_len"] + PAGE - 1) // PAGE)
+    n_cols = max_pages - 1
+    scores = ops.quest_page_score(inp["q"].to(DEV), bounds, inp["page_table"].to(DEV), inp["req_indices"].to(DEV),
+                                  inp["context_lens"].to(DEV), n_cols, cfg["hkv"])
+    torch.cuda.synchronize()
+    got = scores.cpu()[:, :n_cols]
+    ref = cases.bf16_from_bits(g["scores_raw"])
+    n_valid = (inp["context_lens"] + PAGE - 1) // PAGE - 1
+    exact, ulp1, bad = _score_stats(got, ref, n_valid)
+    total = exact + ulp1 + bad
+    print(f"{name}: scores exact {exact}/{total}, 1-ulp {ulp1}, worse {bad}")
+    assert bad == 0, "page score differs from the reference by more than one bf16 ulp"
+    assert ulp1 <= 0.02 * total, "too many 1-ulp deviations: rounding structure is not the reference's"
+    for b in range(got.shape[0]):
+        assert bool(torch.isneginf(got[b, int(n_valid[b]):].float()).all())
+
+
+def _check_selection(name, cfg, inp, g, packed, lens, selected, scores_ref, ulp_slack=0):
+    prev = selected.shape[1] - 1
+    ref_packed, ref_lens = g["packed_slots"], g["lens"]
+    assert np.array_equal(lens, ref_lens)
+    n_valid = ((inp["context_lens"] + PAGE - 1) // PAGE - 1).tolist()
+    stats = {"exact": 0, "tie": 0, "bad": 0}
+    for b in range(packed.shape[0]):
+        row = int(inp["req_indices"][b])
+        pt = inp["page_table"][row]
+        if selected[b, 0] < 0:  # dense row: identical to the reference, element-wise
+            assert np.array_equal(packed[b], ref_packed[b])
+            continue
+        sel = selected[b].tolist()
+        assert sel[-1] == n_valid[b], "last page must be appended last"
+        assert sel[:-1] == sorted(set(sel[:-1])), "selected pages must be unique and ascending"
+        # packed slots = page slot * 16 + offset for the selected pages, in order
+        exp = (pt[torch.tensor(sel)].to(torch.int32)[:, None] * PAGE + torch.arange(PAGE, dtype=torch.int32)).reshape(-1)
+        assert np.array_equal(packed[b, : (prev + 1) * PAGE], exp.numpy())
+        # reference's page set recovered from its packed slots
+        slot_to_page = {int(pt[p]): p for p in range(len(pt)) if int(pt[p]) >= 0}
+        ref_pages = [slot_to_page[int(s) // PAGE] for s in ref_packed[b, : prev * PAGE : PAGE]]
+        c = oquest.classify_selection(scores_ref[b], ref_pages, sel[:-1], n_valid[b])
+        if c["bad"] and ulp_slack:
+            # the kernel selected on its OWN scores, which may sit one bf16 ulp from the reference's at
+            # an accumulation-order rounding boundary: pages swapped must be within that of the k-th score
+            ref_set, got_set = set(ref_pages), set(sel[:-1])
+            kth = min(scores_ref[b][list(ref_set)].float()).to(torch.bfloat16)
+            swapped = torch.tensor(sorted(ref_set ^ got_set))
+            d = oquest.bf16_ulp_distance(scores_ref[b][swapped], kth.expand(len(swapped)).contiguous())
+            if int(d.max()) <= ulp_slack:
+                c = {"exact": 0, "tie": 1, "bad": 0, "detail": c["detail"]}
+        for k in stats:
+            stats[k] += c[k]
+        assert c["bad"] == 0, f"{name} row {b}: selection differs beyond exact ties: {c['detail']}"
+    print(f"{name}: selection {stats}")
+
+
+@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("name", list(cases.QUEST_CASES))
+def test_select_pack_matches_reference(name, fused, golden):
+    from sparse_vllm_b200 import configs, ops
+    cfg, inp, _, _, g = _setup(name, golden)
+    if fused and not cfg["is_long_text"]:
+        pytest.skip("the fused launch serves long-text batches; mixed batches use the two-launch path")
+    bounds = _device_bounds(g)
+    bsz = cfg["bsz"]
+    max_pages = min(inp["max_pages_per_row"], (cfg["max_context_len"] + PAGE - 1) // PAGE)
+    n_cols = max_pages - 1
+    base, prev = configs.quest_page_budget(cfg["token_budget"], PAGE, max_pages)
+    max_keep = max(cfg["token_budget"], base * PAGE, PAGE)
+    width = (prev + 1) * PAGE if cfg["is_long_text"] else max_keep
+    packed = torch.full((bsz, width), -7, dtype=torch.int32, device=DEV)
+    lens = torch.zeros(bsz, dtype=torch.int32, device=DEV)
+    selected = torch.full((bsz, prev + 1), -9, dtype=torch.int32, device=DEV)
+    q, pt = inp["q"].to(DEV), inp["page_table"].to(DEV)
+    req, ctx = inp["req_indices"].to(DEV), inp["context_lens"].to(DEV)
+    # feed the REFERENCE scores (masked like quest.py:1883-1885) to the standalone selection so the
+    # comparison isolates top-k + packing; the fused launch uses its own scores
+    ref_scores = cases.bf16_from_bits(g["scores_raw"]).clone()
+    n_valid = (inp["context_lens"] + PAGE - 1) // PAGE - 1
+    for b in range(bsz):
+        ref_scores[b, int(n_valid[b]):] = -float("inf")
+    if fused:
+        scores = torch.empty(bsz, ops.score_row_stride(n_cols), dtype=torch.bfloat16, device=DEV)
+        tickets = torch.zeros(bsz, dtype=torch.int32, device=DEV)
+        for _ in range(2):  # twice: the tickets must be left zeroed
+            ops.quest_score_select_pack(q, bounds, pt, req, ctx, n_cols, cfg["hkv"], prev, scores, packed, lens,
+                                        tickets, selected)
+        torch.cuda.synchronize()
+        assert int(tickets.abs().sum()) == 0
+        own = scores.cpu()[:, :n_cols]
+        # selection must be exact w.r.t. the scores the kernel itself produced
+        for b in range(bsz):
+            exp = oquest.topk_numpy_lowest_index(own[b].float().numpy(), prev)
+            assert np.array_equal(np.sort(selected[b, :prev].cpu().numpy()), exp)
+        scores_for_class = own
+    else:
+        sc = torch.full((bsz, ops.score_row_stride(n_cols)), -float("inf"), dtype=torch.bfloat16)
+        sc[:, :n_cols] = ref_scores
+        dense = None if cfg["is_long_text"] else inp["token_table"].to(DEV)
+        ops.quest_select_pack(sc.to(DEV), n_cols, pt, req, ctx, prev, packed, lens, selected, dense,
+                              token_budget=cfg["token_budget"], page_budget_base=base, out_width=width)
+        torch.cuda.synchronize()
+        scores_for_class = ref_scores
+    _check_selection(name, cfg, inp, g, packed.cpu().numpy(), lens.cpu().numpy(), selected.cpu().numpy(),
+                     ref_scores, ulp_slack=1 if fused else 0)
+
+
+def test_selection_ties_take_lowest_page_first():
+    """Massive exact ties: deterministic rule = higher score first, then lower page index."""
+    from sparse_vllm_b200 import ops
+    bsz, n_cols, prev = 2, 1000, 37
+    gen = np.random.Generator(np.random.PCG64(5))
+    vals = torch.from_numpy(gen.integers(-3, 4, size=(bsz, n_cols)).astype(np.float32)).to(torch.bfloat16)
+    sc = torch.full((bsz, ops.score_row_stride(n_cols)), -float("inf"), dtype=torch.bfloat16)
+    sc[:, :n_cols] = vals
+    pt = torch.arange(bsz * (n_cols + 1), dtype=torch.int32).view(bsz, n_cols + 1).to(DEV)
+    ctx = torch.tensor([(n_cols + 1) * PAGE, (n_cols + 1) * PAGE - 5], dtype=torch.int32, device=DEV)
+    req = torch.arange(bsz, dtype=torch.int32, device=DEV)
+    packed = torch.zeros(bsz, (prev + 1) * PAGE, dtype=torch.int32, device=DEV)
+    lens = torch.zeros(bsz, dtype=torch.int32, device=DEV)
+    sel = torch.zeros(bsz, prev + 1, dtype=torch.int32, device=DEV)
+    ops.quest_select_pack(sc.to(DEV), n_cols, pt, req, ctx, prev, packed, lens, sel)
+    torch.cuda.synchronize()
+    for b in range(bsz):
+        exp = oquest.topk_numpy_lowest_index(vals[b].float().numpy(), prev)
+        assert np.array_equal(sel[b, :prev].cpu().numpy(), exp)
+        assert int(sel[b, prev]) == n_cols
+    assert lens.tolist() == [prev * PAGE + PAGE, prev * PAGE + PAGE - 5]
+
+
+@pytest.mark.parametrize("bsz,hq,hkv,ctx,budget", [(4, 28, 4, 131072, 4096), (1, 32, 8, 32768, 2048)])
+def test_full_size_properties(bsz, hq, hkv, ctx, budget):
+    """BASELINE sizes (cfg 3 at a reduced batch, cfg 2): size-independent properties of the fused launch.
+    -inf beyond the valid pages, exact top-k w.r.t. its own scores, packing = page table lookup, and the
+    scores themselves against a torch fp32 evaluation with the reference's three bf16 roundings."""
+    from sparse_vllm_b200 import configs, ops
+    gen = torch.Generator(device=DEV).manual_seed(1234)
+    max_pages = ctx // PAGE
+    n_cols = max_pages - 1
+    base, prev = configs.quest_page_budget(budget, PAGE, max_pages)
+    num_pages = bsz * max_pages
+    bounds_max = torch.randn(num_pages, hkv, 128, device=DEV, generator=gen).to(torch.bfloat16)
+    bounds_min = bounds_max - torch.rand(num_pages, hkv, 128, device=DEV, generator=gen).to(torch.bfloat16)
+    bounds = torch.stack((bounds_max, bounds_min), dim=1).contiguous()
+    pt = torch.randperm(num_pages, device=DEV, generator=gen).to(torch.int32).view(bsz, max_pages)
+    q = torch.randn(bsz, hq, 128, device=DEV, generator=gen).to(torch.bfloat16)
+    ctx_lens = torch.tensor([ctx - 3 * b for b in range(bsz)], dtype=torch.int32, device=DEV)
+    req = torch.arange(bsz, dtype=torch.int32, device=DEV)
+    scores = torch.empty(bsz, ops.score_row_stride(n_cols), dtype=torch.bfloat16, device=DEV)
+    packed = torch.zeros(bsz, (prev + 1) * PAGE, dtype=torch.int32, device=DEV)
+    lens = torch.zeros(bsz, dtype=torch.int32, device=DEV)
+    sel = torch.zeros(bsz, prev + 1, dtype=torch.int32, device=DEV)
+    tickets = torch.zeros(bsz, dtype=torch.int32, device=DEV)
+    ops.quest_score_select_pack(q, bounds, pt, req, ctx_lens, n_cols, hkv, prev, scores, packed, lens, tickets, sel)
+    torch.cuda.synchronize()
+    num_pg = (ctx_lens + PAGE - 1) // PAGE
+    for b in range(bsz):
+        nv = int(num_pg[b]) - 1
+        row = scores[b, :n_cols].float()
+        assert bool(torch.isneginf(row[nv:]).all()) and bool(torch.isfinite(row[:nv]).all())
+        s = sel[b, :prev].long()
+        assert int(sel[b, prev]) == nv
+        kth = row[s].min()
+        mask = torch.ones(n_cols, dtype=torch.bool, device=DEV)
+        mask[s] = False
+        assert float(row[mask].max()) <= float(kth)
+        exp = (pt[b][sel[b].long()][:, None] * PAGE + torch.arange(PAGE, dtype=torch.int32, device=DEV)).reshape(-1)
+        assert torch.equal(packed[b], exp)
+        assert int(lens[b]) == prev * PAGE + int(ctx_lens[b]) - nv * PAGE
+        # scores vs a torch evaluation (fp32 matmul, bf16 roundings as in quest.py:1796-1802)
+        g = hq // hkv
+        qg = q[b].view(hkv, g, 128).float()
+        pm = bounds_max[pt[b, :nv].long()].float().permute(1, 2, 0)  # [hkv, 128, nv]
+        pn = bounds_min[pt[b, :nv].long()].float().permute(1, 2, 0)
+        sp = torch.bmm(qg.clamp_min(0), pm).to(torch.bfloat16)
+        sn = torch.bmm(qg.clamp_max(0), pn).to(torch.bfloat16)
+        ref = (sp + sn).amax(dim=1).amax(dim=0)
+        d = oquest.bf16_ulp_distance(scores[b, :nv].cpu(), ref.cpu())
+        assert int(d.max()) <= 1 and float((d == 1).float().mean()) < 0.02
