@@ -1,0 +1,275 @@
+"""Quest cache manager of the B200 provider.
+
+Same role and hooks as the reference's ``QuestCacheManager`` (engine/cache_manager/quest.py): paged
+KV ``[2, L, slots, Hkv, D]``, a page table per request row, per-page key bounds kept ON THE GPU, and
+the decode-time view builder that scores pages against the query, keeps the top pages plus the newest
+one and hands attention a packed token-slot table.  What differs is the layout and the execution:
+
+* bounds live as ``[L, pages, 2(max,min), Hkv, D]`` (one contiguous record per page and layer) instead
+  of two planes ``[2, L, pages, Hkv, D]`` (quest.py:96-105), so the scoring scan reads each page once,
+  through the page table, with no gathered copy (quest.py:1870-1881 materialises two);
+* score + mask + top-k + last page + slot packing is ONE launch for long-text batches
+  (quest.py:1773-1802, 1883-1913 are ~20 torch launches); mixed batches use two launches;
+* a decode token that completes a page refreshes its bounds inside the KV store launch (or, in
+  ``decode_bounds_refresh="forward_end"`` mode, one all-layer launch in ``on_forward_end``) instead of
+  the per-layer Python loop of quest.py:1719-1771.
+
+Host-side page allocation stays in numpy like the reference (quest.py:1280-1360).
+"""
+from __future__ import annotations
+
+from types import SimpleNamespace
+
+import numpy as np
+import torch
+
+from .. import ops
+from ..configs import quest_page_budget
+from ..operators.decode_attention import (B200SparseDecodeProvider, SparseDecodeAttentionSpec,
+                                          prepare_sparse_decode_attention_op)
+from ..utils_context import get_context
+from .base import CacheManager, SparseSelection
+
+PAGE = 16
+
+
+class QuestCacheManager(CacheManager):
+    sparse_method = "quest"
+
+    def __init__(self, config, *, num_layers: int, num_kv_heads: int, head_dim: int = 128, num_pages: int,
+                 max_rows: int, max_model_len: int, device, dtype: torch.dtype = torch.bfloat16,
+                 decode_bounds_refresh: str = "fused", provider: B200SparseDecodeProvider | None = None) -> None:
+        self.config = config
+        self.page_size = int(getattr(config, "quest_chunk_size", PAGE))
+        if self.page_size != PAGE:
+            raise ValueError(f"the B200 provider supports quest_chunk_size={PAGE} only, got {self.page_size}.")
+        if decode_bounds_refresh not in ("fused", "forward_end"):
+            raise ValueError("decode_bounds_refresh must be 'fused' or 'forward_end'.")
+        self.num_pages = int(num_pages)
+        super().__init__(num_layers=num_layers, num_kv_heads=num_kv_heads, head_dim=head_dim,
+                         num_slots=self.num_pages * PAGE, device=device, dtype=dtype)
+        self.decode_bounds_refresh = decode_bounds_refresh
+        self.max_model_len = int(max_model_len)
+        self.max_pages_per_row = (self.max_model_len + PAGE - 1) // PAGE
+        self.max_rows = int(max_rows)
+        # page bounds, resident on the GPU: [L, pages, 2, Hkv, D]
+        self.bounds = torch.zeros((self.num_layers, self.num_pages, 2, self.num_kv_heads, self.head_dim),
+                                  dtype=dtype, device=self.device)
+        self.buffer_req_to_page_slots = torch.full((self.max_rows, self.max_pages_per_row), -1, dtype=torch.int32,
+                                                   device=self.device)
+        self.buffer_req_to_page_slots_cpu = np.full((self.max_rows, self.max_pages_per_row), -1, dtype=np.int32)
+        self.buffer_req_to_token_slots = torch.zeros((self.max_rows, self.max_model_len), dtype=torch.int32,
+                                                     device=self.device)
+        self.row_seq_lens = np.zeros((self.max_rows,), dtype=np.int32)
+        self.seq_id_to_row: dict[int, int] = {}
+        self._free_rows = list(range(self.max_rows - 1, -1, -1))
+        self.free_pages_cpu_stack = np.arange(self.num_pages, dtype=np.int32)
+        self._num_free_pages = self.num_pages
+        self._decode_static_max_context_len: int | None = None
+        self._scratch: dict[int, SimpleNamespace] = {}
+        self._provider = provider
+
+    # ------------------------------------------------------------------ provider / scratch
+    def _get_provider(self, num_heads: int) -> B200SparseDecodeProvider:
+        if self._provider is None:
+            spec = SparseDecodeAttentionSpec(int(num_heads), self.num_kv_heads, self.head_dim, torch.bfloat16,
+                                             page_size=PAGE, sparse_method="quest")
+            self._provider = prepare_sparse_decode_attention_op(spec, device_index=self.device.index).provider
+        return self._provider
+
+    def _get_scratch(self, batch: int, n_cols: int, width: int) -> SimpleNamespace:
+        key = int(batch)
+        s = self._scratch.get(key)
+        stride = ops.score_row_stride(n_cols)
+        if s is None or s.scores.shape[1] < stride or s.packed.shape[1] < width:
+            s = SimpleNamespace(
+                scores=torch.empty((batch, stride), dtype=torch.bfloat16, device=self.device),
+                packed=torch.zeros((batch, width), dtype=torch.int32, device=self.device),
+                lens=torch.zeros((batch,), dtype=torch.int32, device=self.device),
+                tickets=torch.zeros((batch,), dtype=torch.int32, device=self.device),
+                arange=torch.arange(batch, dtype=torch.int32, device=self.device))
+            self._scratch[key] = s
+        return s
+
+    # ------------------------------------------------------------------ allocation (host)
+    @property
+    def num_free_slots(self) -> int:
+        return self._num_free_pages * PAGE
+
+    def _get_free_row(self, seq_id: int) -> int:
+        row = self.seq_id_to_row.get(seq_id)
+        if row is None:
+            if not self._free_rows:
+                raise RuntimeError("Out of QuEST request rows.")
+            row = self._free_rows.pop()
+            self.seq_id_to_row[seq_id] = row
+            self.row_seq_lens[row] = 0
+        return row
+
+    def _pop_pages(self, n: int) -> np.ndarray:
+        if self._num_free_pages < n:
+            raise RuntimeError(f"Out of QuEST KV pages: need_pages={n}, free_pages={self._num_free_pages}.")
+        ptr = self._num_free_pages
+        pages = self.free_pages_cpu_stack[ptr - n: ptr][::-1].copy()
+        self._num_free_pages -= n
+        return pages
+
+    def allocate_prefill(self, seq_id: int, num_tokens: int) -> torch.Tensor:
+        """Slots for the next ``num_tokens`` tokens of a sequence (chunked prefill, quest.py:1426-1493)."""
+        row = self._get_free_row(seq_id)
+        cur = int(self.row_seq_lens[row])
+        new_len = cur + int(num_tokens)
+        if new_len > self.max_model_len:
+            raise RuntimeError(f"KV row length exceeds max_model_len: {new_len} > {self.max_model_len}")
+        have = (cur + PAGE - 1) // PAGE
+        need = (new_len + PAGE - 1) // PAGE
+        if need > have:
+            pages = self._pop_pages(need - have)
+            self.buffer_req_to_page_slots_cpu[row, have:need] = pages
+            self.buffer_req_to_page_slots[row, have:need] = torch.from_numpy(pages).to(self.device)
+        pos = np.arange(cur, new_len, dtype=np.int64)
+        slots = self.buffer_req_to_page_slots_cpu[row, pos // PAGE].astype(np.int64) * PAGE + pos % PAGE
+        slots_t = torch.from_numpy(slots.astype(np.int32)).to(self.device)
+        self.buffer_req_to_token_slots[row, cur:new_len] = slots_t
+        self.row_seq_lens[row] = new_len
+        self.layer_batch_state.slot_mapping = slots_t
+        return slots_t
+
+    def free_seq(self, seq_id: int) -> None:
+        row = self.seq_id_to_row.pop(seq_id, None)
+        if row is None:
+            return
+        n_pages = (int(self.row_seq_lens[row]) + PAGE - 1) // PAGE
+        pages = self.buffer_req_to_page_slots_cpu[row, :n_pages]
+        ptr = self._num_free_pages
+        self.free_pages_cpu_stack[ptr: ptr + n_pages] = pages
+        self._num_free_pages += n_pages
+        self.buffer_req_to_page_slots_cpu[row, :] = -1
+        self.buffer_req_to_page_slots[row, :] = -1
+        self.row_seq_lens[row] = 0
+        self._free_rows.append(row)
+
+    def _allocate_batch(self, seq_ids: list[int]) -> tuple[np.ndarray, np.ndarray]:
+        """One slot per sequence (decode); a new page is popped when len % 16 == 0 (quest.py:1280-1360)."""
+        rows = np.asarray([self._get_free_row(s) for s in seq_ids], dtype=np.int64)
+        cur = self.row_seq_lens[rows].astype(np.int64)
+        if cur.size and int(cur.max()) + 1 > self.max_model_len:
+            raise RuntimeError(f"KV row length exceeds max_model_len in QuEST _allocate_batch: max_cur_len={int(cur.max())}")
+        page_idx, page_off = cur // PAGE, cur % PAGE
+        new_pos = np.nonzero(page_off == 0)[0]
+        if new_pos.size:
+            pages = self._pop_pages(int(new_pos.size))
+            self.buffer_req_to_page_slots_cpu[rows[new_pos], page_idx[new_pos]] = pages
+            self.buffer_req_to_page_slots[torch.from_numpy(rows[new_pos]).to(self.device),
+                                          torch.from_numpy(page_idx[new_pos]).to(self.device)] = \
+                torch.from_numpy(pages).to(self.device)
+        slots = self.buffer_req_to_page_slots_cpu[rows, page_idx].astype(np.int64) * PAGE + page_off
+        slots32 = slots.astype(np.int32)
+        self.buffer_req_to_token_slots[torch.from_numpy(rows).to(self.device),
+                                       torch.from_numpy(cur).to(self.device)] = torch.from_numpy(slots32).to(self.device)
+        self.row_seq_lens[rows] += 1
+        return rows, slots32
+
+    def set_decode_static_max_context_len(self, cap: int | None) -> None:
+        """Pin the context bucket of the static / graph decode runner (decode_cuda_graph.py:16-26,282-300)."""
+        self._decode_static_max_context_len = None if cap is None else int(cap)
+
+    def prepare_decode_static(self, seqs, input_ids, positions, slot_mapping, context_lens, req_indices):
+        """Fill caller-owned static buffers for one decode step (quest.py:1543-1605).  Padding entries
+        replicate row 0 with slot -1."""
+        real = len(seqs)
+        graph_bs = int(input_ids.numel())
+        if real <= 0:
+            raise ValueError("Static decode requires a non-empty real decode batch.")
+        if any(int(t.numel()) != graph_bs for t in (positions, slot_mapping, context_lens, req_indices)):
+            raise ValueError("Static decode metadata buffers must have the same graph batch size.")
+        if real > graph_bs:
+            raise ValueError(f"Static decode graph batch is smaller than the real decode batch: graph={graph_bs}, real={real}.")
+        seq_ids = [s.seq_id for s in seqs]
+        rows, slots = self._allocate_batch(seq_ids)
+        lens = self.row_seq_lens[rows].astype(np.int32)
+        host = np.empty((3, graph_bs), dtype=np.int32)
+        host[0, :real], host[1, :real], host[2, :real] = slots, lens, rows
+        host[0, real:], host[1, real:], host[2, real:] = -1, lens[0], rows[0]
+        packed = torch.from_numpy(host)
+        slot_mapping.copy_(packed[0], non_blocking=True)
+        context_lens.copy_(packed[1], non_blocking=True)
+        req_indices.copy_(packed[2], non_blocking=True)
+        ids = [int(s.decode_input_token) for s in seqs] + [int(seqs[0].decode_input_token)] * (graph_bs - real)
+        pos = [int(s.decode_input_position) for s in seqs] + [int(seqs[0].decode_input_position)] * (graph_bs - real)
+        input_ids.copy_(torch.tensor(ids, dtype=input_ids.dtype))
+        positions.copy_(torch.tensor(pos, dtype=positions.dtype))
+        st = self.layer_batch_state
+        st.slot_mapping, st.context_lens, st.req_indices = slot_mapping, context_lens, req_indices
+        st.max_context_len = int(lens.max())
+        if self._decode_static_max_context_len is not None:
+            st.max_context_len = max(st.max_context_len, self._decode_static_max_context_len)
+        return input_ids, positions, None
+
+    # ------------------------------------------------------------------ bounds maintenance
+    def _fused_store_bounds(self, layer_idx: int):
+        if get_context().is_prefill or self.decode_bounds_refresh != "fused":
+            return None
+        return self.bounds[self.kv_layer_index(layer_idx)]
+
+    def on_kv_stored(self, layer_idx: int, k: torch.Tensor, slot_mapping: torch.Tensor) -> None:
+        """Prefill: bounds of every page completed by this chunk (quest.py:1608-1716).  Decode: nothing here
+        (the store launch or on_forward_end refreshes a completed page)."""
+        if slot_mapping is None or slot_mapping.numel() == 0 or not get_context().is_prefill:
+            return
+        kv_idx = self.kv_layer_index(layer_idx)
+        ops.quest_page_minmax(self.kv_cache[0, kv_idx], self.bounds[kv_idx], slot_mapping)
+
+    def on_forward_end(self, seqs, is_prefill: bool) -> None:
+        """quest.py:1719-1771: after a decode step, rebuild the bounds of pages it completed (all layers)."""
+        if is_prefill or self.decode_bounds_refresh != "forward_end":
+            return
+        st = self.layer_batch_state
+        ops.quest_decode_page_complete(self.kv_cache[0], self.bounds, self.buffer_req_to_page_slots,
+                                       st.req_indices, st.context_lens)
+
+    # ------------------------------------------------------------------ decode view
+    def _default_active_slots_for_selection(self, layer_idx: int, selection: SparseSelection) -> torch.Tensor:
+        return self.buffer_req_to_token_slots
+
+    def build_decode_view(self, layer_idx, q, active_slots, req_indices, context_lens, *, num_heads, num_kv_heads):
+        """quest.py:1805-1830."""
+        if layer_idx < int(self.config.quest_skip_layers):
+            return active_slots, req_indices, context_lens
+        token_budget = int(self.config.quest_token_budget)
+        if token_budget <= 0:
+            return active_slots, req_indices, context_lens
+        return self._build_decode_view_static(layer_idx, q, active_slots, req_indices, context_lens,
+                                              token_budget=token_budget, num_heads=num_heads,
+                                              num_kv_heads=num_kv_heads)
+
+    @torch.no_grad()
+    def _build_decode_view_static(self, layer_idx, q, active_slots, req_indices, context_lens, *, token_budget,
+                                  num_heads, num_kv_heads):
+        """quest.py:1833-1913 in one (long-text) or two (mixed) launches."""
+        page_budget_base = max(3, int(token_budget) // PAGE)
+        max_keep = max(int(token_budget), page_budget_base * PAGE, PAGE)
+        max_context_len = self.layer_batch_state.max_context_len
+        if max_context_len is None:
+            raise RuntimeError("QuEST decode CUDA graph requires max_context_len to be pinned.")
+        max_context_len = int(max_context_len)
+        if max_context_len <= max_keep:
+            return active_slots, req_indices, context_lens
+        batch = int(q.shape[0])
+        max_pages = min(self.max_pages_per_row, (max_context_len + PAGE - 1) // PAGE)
+        _, prev_budget = quest_page_budget(token_budget, PAGE, max_pages)
+        if prev_budget <= 0:
+            return active_slots, req_indices, context_lens
+        if int(num_kv_heads) != self.num_kv_heads:
+            raise ValueError(f"num_kv_heads={num_kv_heads} does not match the cache ({self.num_kv_heads}).")
+        n_cols = max_pages - 1
+        long_text = bool(get_context().is_long_text)
+        width = (prev_budget + 1) * PAGE if long_text else max_keep
+        s = self._get_scratch(batch, n_cols, width)
+        self._get_provider(num_heads).quest_select(
+            q, self.bounds[self.kv_layer_index(layer_idx)], self.buffer_req_to_page_slots, req_indices, context_lens, n_cols=n_cols,
+            num_kv_heads=self.num_kv_heads, prev_budget=prev_budget, scores=s.scores, packed_slots=s.packed,
+            sparse_lens=s.lens, tickets=s.tickets,
+            dense_token_table=None if long_text else self.buffer_req_to_token_slots,
+            token_budget=int(token_budget), page_budget_base=page_budget_base, out_width=width)
+        return s.packed[:, :width], s.arange, s.lens
