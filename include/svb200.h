@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SVB200_ABI_VERSION 1
+#define SVB200_ABI_VERSION 2
 
 enum {
   SVB200_OK = 0,
@@ -40,14 +40,23 @@ int svb200_abi_version(void);
 const char* svb200_last_error(void);
 /* Number of SMs of the current device (cached); used by hosts to size split-K. */
 int svb200_sm_count(void);
+/*
+ * Cap the grid of the persistent kernels (score/select and attention) at n CTAs;
+ * n <= 0 restores one CTA per SM.  Returns the previous cap (0 = none).  Process-wide
+ * tuning / test knob: fewer CTAs means more page tiles per CTA and rows cut at
+ * different places; results do not depend on it.
+ */
+int svb200_set_max_ctas(int32_t n);
 
 /*
- * Bytes of scratch the attention entry point needs besides mid_o / mid_lse:
- * one int32 arrival ticket per (batch row, kv-head group).  The buffer must be
- * zero-initialised once; kernels leave it zeroed.
- * Replaces nothing in the reference (its stage2 is a separate launch).
+ * Bytes of scratch svb200_sparse_decode_attn needs: one int32 arrival ticket per
+ * (batch row, KV head) followed by two fp32 partial records (output + lse) per SM.
+ * The buffer must be zero-initialised once; kernels leave the tickets zeroed.
+ * Takes the place of the reference's mid_o / mid_o_logexpsum split-K workspace
+ * (layers/attention.py:15-51), whose size grows with batch * context / 256; this one
+ * depends on the SM count only.
  */
-int64_t svb200_workspace_bytes(int32_t batch, int32_t num_kv_heads);
+int64_t svb200_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads);
 
 /* ------------------------------------------------------------------------- *
  * Quest page bounds ("metadata").  Layout owned by this provider:
@@ -100,13 +109,16 @@ int svb200_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
  * p >= ceil(ctx/16) - 1 are -inf (quest.py:1883-1885).  The gather of
  * quest.py:1870-1881 is fused: bounds are read through the page table.
  *   q            [batch][Hq][128] bf16, row stride q_stride_b elements
+ *   bounds_layer [num_pages][2][Hkv][128] bf16; page-table entries outside
+ *                [0, num_pages) score -inf
  *   page_table   [rows][page_table_stride] int32 (-1 empty)
  *   req_rows     [batch] int32 row of each batch entry in page_table
  *   context_lens [batch] int32
  *   scores       [batch][score_stride] bf16 out, score_stride >= n_cols
  */
 int svb200_quest_page_score(const void* q, int64_t q_stride_b,
-                            const void* bounds_layer, const int32_t* page_table,
+                            const void* bounds_layer, int64_t num_pages,
+                            const int32_t* page_table,
                             int64_t page_table_stride, const int32_t* req_rows,
                             const int32_t* context_lens, void* scores,
                             int64_t score_stride, int32_t batch, int32_t num_q_heads,
@@ -139,11 +151,11 @@ int svb200_quest_select_pack(const void* scores, int64_t score_stride,
 
 /*
  * Fused score + select + pack: same results as the two calls above with one
- * launch (the last CTA of each row performs the selection).
+ * launch (the last CTA to finish a row's page tiles performs its selection).
  *   tickets [batch] int32 zero-initialised scratch (left zeroed).
  */
 int svb200_quest_score_select_pack(
-    const void* q, int64_t q_stride_b, const void* bounds_layer,
+    const void* q, int64_t q_stride_b, const void* bounds_layer, int64_t num_pages,
     const int32_t* page_table, int64_t page_table_stride, const int32_t* req_rows,
     const int32_t* context_lens, void* scores, int64_t score_stride, int32_t batch,
     int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols, int32_t prev_budget,
@@ -151,42 +163,36 @@ int svb200_quest_score_select_pack(
     int32_t* selected_pages, int32_t* tickets, void* stream);
 
 /*
- * Sparse paged GQA decode attention with split-K and fused combine.
+ * Sparse paged GQA decode attention: stream-K over 16-token pages with a fused
+ * combine (one launch).
  * Replaces gqa_flash_decode_stage1(+_with_score 2D) and flash_decode_stage2
  * (kernels/triton/gqa_flash_decoding_stage1.py:6-121,211-295,
  *  kernels/triton/flash_decoding_stage2.py:8-46) behind
  * TritonAttentionBackend.run_decode (layers/attention_backend.py:217-349).
  *   q          [batch][Hq][128] bf16 (row stride q_stride_b elements)
  *   k_cache, v_cache [num_slots][Hkv][128] bf16, identical layout
- *   slot_table [rows][slot_table_stride] int32 token slots; entries < 0 are
- *              treated as masked tokens
+ *   slot_table [rows][slot_table_stride] int32 token slots; entries outside
+ *              [0, num_slots) are treated as masked tokens
+ *   max_len    upper bound of seq_lens (<= slot_table_stride); longer rows are clipped
  *   req_rows   [batch] int32, seq_lens [batch] int32 (tokens visible per row)
- *   mid_o      [batch][Hq][num_splits][128] fp32, mid_lse [batch][Hq][num_splits] fp32
- *              (the reference hands in sliced views of a cached workspace,
- *              layers/attention.py:15-51, so element strides are explicit:
- *              mid_o_strides_host = {batch, head, split} (last dim contiguous, multiples
- *              of 4), mid_lse_strides_host = {batch, head} (split contiguous); both are
- *              HOST arrays read during the call; NULL = densely packed)
- *   out        [batch][Hq][128] bf16 (row stride out_stride_b elements)
+ *   out        [batch][Hq][128] bf16 (row stride out_stride_b elements); rows with
+ *              seq_len <= 0 are zero-filled
  *   attn_score NULL (Quest) or fp32 [batch][score_stride] pre-filled by the caller
  *              (reference: -1e20); entry n is max-updated with the raw, unscaled
  *              max over local q heads of q.k[n]  (H2O / SnapKV 2D score).
- *   split_tokens tokens per split (multiple of 16); num_splits*split_tokens must
- *              cover max(seq_lens).
- *   heads_per_cta 0 = auto, else 1/2/4/8 KV heads handled by one CTA.
- *   tickets    int32 [svb200_workspace_bytes/4] zeroed scratch.
+ *   heads_per_cta 0 = auto, else 1/2/4/8 KV heads staged together by one CTA.
+ *   workspace  zero-initialised scratch of svb200_workspace_bytes() bytes (a smaller
+ *              buffer limits the number of CTAs).
  */
 int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_cache,
                               const void* v_cache, int64_t num_slots,
                               const int32_t* slot_table, int64_t slot_table_stride,
-                              const int32_t* req_rows, const int32_t* seq_lens,
-                              float* mid_o, const int64_t* mid_o_strides_host,
-                              float* mid_lse, const int64_t* mid_lse_strides_host, void* out,
-                              int64_t out_stride_b, float* attn_score,
-                              int64_t score_stride, int32_t batch, int32_t num_q_heads,
-                              int32_t num_kv_heads, int32_t split_tokens,
-                              int32_t num_splits, int32_t heads_per_cta,
-                              int32_t* tickets, float sm_scale, void* stream);
+                              int32_t max_len, const int32_t* req_rows,
+                              const int32_t* seq_lens, void* out, int64_t out_stride_b,
+                              float* attn_score, int64_t score_stride, int32_t batch,
+                              int32_t num_q_heads, int32_t num_kv_heads,
+                              int32_t heads_per_cta, void* workspace,
+                              int64_t workspace_bytes, float sm_scale, void* stream);
 
 /*
  * H2O layer-end normalisation (+ optional fused accumulation).

@@ -16,27 +16,20 @@ from .operators.decode_attention import (B200SparseDecodeProvider, SparseDecodeA
 from .utils_context import get_context
 
 
-def get_decode_workspace(context, batch_size: int, num_heads: int, num_blocks: int, head_dim: int,
-                         device: torch.device, num_kv_heads: int | None = None):
-    """Cached fp32 split-K workspace, handed out as sliced views (layers/attention.py:15-51), plus the
-    zero-initialised arrival tickets of the fused combine."""
-    mid_o = context.decode_mid_o
-    if (mid_o is None or mid_o.device != device or mid_o.shape[0] < batch_size or mid_o.shape[1] < num_heads
-            or mid_o.shape[2] < num_blocks or mid_o.shape[3] < head_dim):
-        mid_o = torch.empty((batch_size, num_heads, num_blocks, head_dim), dtype=torch.float32, device=device)
-        context.decode_mid_o = mid_o
-    mid_lse = context.decode_mid_o_logexpsum
-    if (mid_lse is None or mid_lse.device != device or mid_lse.shape[0] < batch_size
-            or mid_lse.shape[1] < num_heads or mid_lse.shape[2] < num_blocks):
-        mid_lse = torch.empty((batch_size, num_heads, num_blocks), dtype=torch.float32, device=device)
-        context.decode_mid_o_logexpsum = mid_lse
-    need = batch_size * (num_kv_heads if num_kv_heads is not None else num_heads)
-    tickets = context.decode_tickets
-    if tickets is None or tickets.device != device or tickets.numel() < need:
-        tickets = torch.zeros((need,), dtype=torch.int32, device=device)
-        context.decode_tickets = tickets
-    return (mid_o[:batch_size, :num_heads, :num_blocks, :head_dim], mid_lse[:batch_size, :num_heads, :num_blocks],
-            tickets)
+def get_decode_workspace(context, batch_size: int, num_heads: int, num_kv_heads: int,
+                         device: torch.device) -> torch.Tensor:
+    """Cached scratch of the decode launch (role of layers/attention.py:15-51 ``get_decode_workspace``).
+
+    The reference caches fp32 ``mid_o [B, Hq, ceil(len/256), D]`` + ``mid_o_logexpsum``; the stream-K kernel
+    needs arrival tickets plus two partial records per SM instead, sized by svb200_workspace_bytes.  The
+    buffer is allocated (zeroed) once per shape, outside graph capture, and stays valid for replays."""
+    key = (int(batch_size), int(num_heads), int(num_kv_heads), str(device))
+    ws = context.decode_workspace
+    if ws is None or context.decode_workspace_key != key:
+        ws = ops.attn_workspace(batch_size, num_heads, num_kv_heads, device)
+        context.decode_workspace = ws
+        context.decode_workspace_key = key
+    return ws
 
 
 class B200AttentionBackend:
@@ -49,11 +42,13 @@ class B200AttentionBackend:
             self.provider = prepare_sparse_decode_attention_op(spec, device_index=q.device.index).provider
         return self.provider
 
-    def run_decode(self, q: torch.Tensor, view: DecodeComputeView, *, mid_o: torch.Tensor,
-                   mid_o_logexpsum: torch.Tensor, max_len_in_batch: int, block_seq: int, num_heads: int,
-                   num_kv_heads: int, gqa_block_n: int = 16, gqa_num_warps: int = 2,
-                   tickets: torch.Tensor | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
-        del gqa_block_n, gqa_num_warps  # Triton launch knobs of the reference; meaningless here
+    def run_decode(self, q: torch.Tensor, view: DecodeComputeView, *, mid_o: torch.Tensor | None = None,
+                   mid_o_logexpsum: torch.Tensor | None = None, max_len_in_batch: int, block_seq: int = 256,
+                   num_heads: int, num_kv_heads: int, gqa_block_n: int = 16, gqa_num_warps: int = 2,
+                   workspace: torch.Tensor | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+        # mid_o / mid_o_logexpsum / block_seq / gqa_* are the reference's split-K workspace and Triton launch
+        # knobs; they are accepted for signature compatibility and unused (stream-K has its own scratch).
+        del mid_o, mid_o_logexpsum, block_seq, gqa_block_n, gqa_num_warps
         payload = view.payload
         if not isinstance(payload, ExplicitKVPayload):
             raise TypeError(f"B200 decode requires ExplicitKVPayload, got {type(payload).__name__}.")
@@ -62,17 +57,12 @@ class B200AttentionBackend:
         meta = view.meta
         if int(num_heads) != int(q.shape[1]) or int(num_kv_heads) != int(payload.k_cache.shape[1]):
             raise ValueError("num_heads / num_kv_heads do not match q / k_cache.")
-        if tickets is None:
-            ctx = get_context()
-            need = int(q.shape[0]) * int(num_kv_heads)
-            if ctx.decode_tickets is None or ctx.decode_tickets.device != q.device or ctx.decode_tickets.numel() < need:
-                ctx.decode_tickets = torch.zeros((need,), dtype=torch.int32, device=q.device)
-            tickets = ctx.decode_tickets
+        if workspace is None:
+            workspace = get_decode_workspace(get_context(), q.shape[0], num_heads, num_kv_heads, q.device)
         o = torch.empty_like(q) if out is None else out
         return self._provider(q, num_heads, num_kv_heads).decode(
             q, payload.k_cache, payload.v_cache, meta.active_slots, meta.req_indices, meta.context_lens, out=o,
-            mid_o=mid_o, mid_lse=mid_o_logexpsum, tickets=tickets, max_len=int(max_len_in_batch),
-            block_seq=int(block_seq), attn_score=meta.attn_score)
+            workspace=workspace, max_len=int(max_len_in_batch), attn_score=meta.attn_score)
 
 
 def decode_attention_layer(cache_manager, backend: B200AttentionBackend, layer_idx: int, q: torch.Tensor,
@@ -94,12 +84,8 @@ def decode_attention_layer(cache_manager, backend: B200AttentionBackend, layer_i
         max_len_in_batch = min(max_len_in_batch, int(meta.active_slots.shape[1]))
     if max_len_in_batch <= 0:
         raise RuntimeError(f"decode requires a positive context length, got {max_len_in_batch} at layer={layer_idx}")
-    block_seq = cache_manager.get_decode_block_seq(layer_idx, 256)
-    num_blocks = (max_len_in_batch + block_seq - 1) // block_seq
-    mid_o, mid_lse, tickets = get_decode_workspace(context, q.shape[0], num_heads, num_blocks, q.shape[-1], q.device,
-                                                   num_kv_heads)
-    o = backend.run_decode(q, view, mid_o=mid_o, mid_o_logexpsum=mid_lse, max_len_in_batch=max_len_in_batch,
-                           block_seq=block_seq, num_heads=num_heads, num_kv_heads=num_kv_heads, tickets=tickets,
-                           out=out)
+    workspace = get_decode_workspace(context, q.shape[0], num_heads, num_kv_heads, q.device)
+    o = backend.run_decode(q, view, max_len_in_batch=max_len_in_batch, num_heads=num_heads,
+                           num_kv_heads=num_kv_heads, workspace=workspace, out=out)
     cache_manager.on_layer_attention_end(layer_idx)
     return o

@@ -38,6 +38,12 @@ int sm_count() {
   return cached;
 }
 
+static int g_max_ctas = 0;
+int max_ctas() {
+  const int n = sm_count();
+  return (g_max_ctas > 0 && g_max_ctas < n) ? g_max_ctas : n;
+}
+
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 #define SV_REQUIRE(cond, ...)    \
@@ -70,10 +76,20 @@ extern "C" {
 int svb200_abi_version(void) { return SVB200_ABI_VERSION; }
 const char* svb200_last_error(void) { return g_err; }
 int svb200_sm_count(void) { return sm_count(); }
+int svb200_set_max_ctas(int32_t n) {
+  const int prev = g_max_ctas;
+  g_max_ctas = n > 0 ? n : 0;
+  return prev;
+}
 
-int64_t svb200_workspace_bytes(int32_t batch, int32_t num_kv_heads) {
-  if (batch < 0 || num_kv_heads < 0) return -1;
-  return (int64_t)batch * num_kv_heads * (int64_t)sizeof(int32_t);
+static int64_t ws_ticket_bytes(int64_t batch, int64_t hkv) {
+  return ((batch * hkv * (int64_t)sizeof(int32_t) + 255) / 256) * 256;
+}
+static int64_t ws_cta_bytes(int64_t hq) { return 2 * hq * (SVB200_HEAD_DIM + 4) * (int64_t)sizeof(float); }
+
+int64_t svb200_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads) {
+  if (batch < 0 || num_q_heads <= 0 || num_kv_heads <= 0) return -1;
+  return ws_ticket_bytes(batch, num_kv_heads) + (int64_t)sm_count() * ws_cta_bytes(num_q_heads);
 }
 
 int svb200_quest_page_minmax(const void* k_cache, void* bounds_layer, const int32_t* slot_mapping,
@@ -110,7 +126,7 @@ int svb200_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
 }
 
 static int check_score_args(const char* who, const void* q, int64_t q_stride_b, const void* bounds,
-                            const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
+                            int64_t num_pages, const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
                             const int32_t* ctx, const void* scores, int64_t score_stride,
                             int batch, int hq, int hkv, int n_cols) {
   SV_REQUIRE(q && bounds && page_table && req_rows && ctx && scores, "%s: null pointer", who);
@@ -123,22 +139,23 @@ static int check_score_args(const char* who, const void* q, int64_t q_stride_b, 
   SV_REQUIRE(score_stride >= ((n_cols + 7) / 8) * 8 && score_stride % 8 == 0,
              "%s: score_stride=%lld must be a multiple of 8 covering n_cols=%d", who,
              (long long)score_stride, n_cols);
-  SV_REQUIRE(batch <= 65535, "%s: batch=%d > 65535", who, batch);
+  SV_REQUIRE(num_pages > 0, "%s: num_pages=%lld must be positive", who, (long long)num_pages);
+  SV_REQUIRE(batch <= 8192, "%s: batch=%d > 8192", who, batch);
   return 0;
 }
 
 int svb200_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds_layer,
-                            const int32_t* page_table, int64_t page_table_stride,
+                            int64_t num_pages, const int32_t* page_table, int64_t page_table_stride,
                             const int32_t* req_rows, const int32_t* context_lens, void* scores,
                             int64_t score_stride, int32_t batch, int32_t num_q_heads,
                             int32_t num_kv_heads, int32_t n_cols, void* stream) {
   SV_REQUIRE(batch >= 0, "quest_page_score: batch=%d < 0", batch);
   if (batch == 0) return 0;
-  if (int rc = check_score_args("quest_page_score", q, q_stride_b, bounds_layer, page_table,
+  if (int rc = check_score_args("quest_page_score", q, q_stride_b, bounds_layer, num_pages, page_table,
                                 page_table_stride, req_rows, context_lens, scores, score_stride,
                                 batch, num_q_heads, num_kv_heads, n_cols))
     return rc;
-  return launch_quest_page_score(q, q_stride_b, bounds_layer, page_table, page_table_stride,
+  return launch_quest_page_score(q, q_stride_b, bounds_layer, num_pages, page_table, page_table_stride,
                                  req_rows, context_lens, scores, score_stride, batch, num_q_heads,
                                  num_kv_heads, n_cols, (cudaStream_t)stream);
 }
@@ -180,7 +197,7 @@ int svb200_quest_select_pack(const void* scores, int64_t score_stride, int32_t n
 }
 
 int svb200_quest_score_select_pack(const void* q, int64_t q_stride_b, const void* bounds_layer,
-                                   const int32_t* page_table, int64_t page_table_stride,
+                                   int64_t num_pages, const int32_t* page_table, int64_t page_table_stride,
                                    const int32_t* req_rows, const int32_t* context_lens,
                                    void* scores, int64_t score_stride, int32_t batch,
                                    int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols,
@@ -189,13 +206,13 @@ int svb200_quest_score_select_pack(const void* q, int64_t q_stride_b, const void
                                    void* stream) {
   SV_REQUIRE(batch >= 0, "quest_score_select_pack: batch=%d < 0", batch);
   if (batch == 0) return 0;
-  if (int rc = check_score_args("quest_score_select_pack", q, q_stride_b, bounds_layer, page_table,
+  if (int rc = check_score_args("quest_score_select_pack", q, q_stride_b, bounds_layer, num_pages, page_table,
                                 page_table_stride, req_rows, context_lens, scores, score_stride,
                                 batch, num_q_heads, num_kv_heads, n_cols))
     return rc;
   if (int rc = check_select_args("quest_score_select_pack", n_cols, prev_budget, packed_slots, out_stride, sparse_lens)) return rc;
   SV_REQUIRE(tickets != nullptr, "quest_score_select_pack: tickets scratch is null");
-  return launch_quest_score_select_pack(q, q_stride_b, bounds_layer, page_table, page_table_stride,
+  return launch_quest_score_select_pack(q, q_stride_b, bounds_layer, num_pages, page_table, page_table_stride,
                                         req_rows, context_lens, scores, score_stride, batch,
                                         num_q_heads, num_kv_heads, n_cols, prev_budget,
                                         packed_slots, out_stride, sparse_lens, selected_pages,
@@ -204,13 +221,12 @@ int svb200_quest_score_select_pack(const void* q, int64_t q_stride_b, const void
 
 int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_cache,
                               const void* v_cache, int64_t num_slots, const int32_t* slot_table,
-                              int64_t slot_table_stride, const int32_t* req_rows,
-                              const int32_t* seq_lens, float* mid_o,
-                              const int64_t* mid_o_strides_host, float* mid_lse,
-                              const int64_t* mid_lse_strides_host, void* out, int64_t out_stride_b, float* attn_score, int64_t score_stride,
-                              int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
-                              int32_t split_tokens, int32_t num_splits, int32_t heads_per_cta,
-                              int32_t* tickets, float sm_scale, void* stream) {
+                              int64_t slot_table_stride, int32_t max_len, const int32_t* req_rows,
+                              const int32_t* seq_lens, void* out, int64_t out_stride_b,
+                              float* attn_score, int64_t score_stride, int32_t batch,
+                              int32_t num_q_heads, int32_t num_kv_heads, int32_t heads_per_cta,
+                              void* workspace, int64_t workspace_bytes, float sm_scale,
+                              void* stream) {
   const char* who = "sparse_decode_attn";
   SV_REQUIRE(batch >= 0, "%s: batch=%d < 0", who, batch);
   if (batch == 0) return 0;
@@ -220,37 +236,28 @@ int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_c
   SV_REQUIRE(q_stride_b >= (int64_t)num_q_heads * SVB200_HEAD_DIM && q_stride_b % 8 == 0, "%s: bad q stride %lld", who, (long long)q_stride_b);
   SV_REQUIRE(out_stride_b >= (int64_t)num_q_heads * SVB200_HEAD_DIM && out_stride_b % 8 == 0, "%s: bad out stride %lld", who, (long long)out_stride_b);
   SV_REQUIRE(num_slots > 0 && slot_table_stride > 0, "%s: num_slots/slot_table_stride must be positive", who);
-  SV_REQUIRE(split_tokens > 0 && split_tokens % SVB200_PAGE == 0 && num_splits >= 1,
-             "%s: split_tokens=%d must be a positive multiple of 16, num_splits=%d >= 1", who, split_tokens, num_splits);
-  if (num_splits > 1) {
-    SV_REQUIRE(mid_o && mid_lse && tickets, "%s: split-K needs mid_o, mid_lse and tickets", who);
-    SV_REQUIRE(aligned16(mid_o), "%s: mid_o must be 16-byte aligned", who);
-  }
+  SV_REQUIRE(max_len >= 0 && max_len <= slot_table_stride, "%s: max_len=%d must be in [0, slot_table_stride=%lld]", who, max_len, (long long)slot_table_stride);
   if (attn_score != nullptr)
-    SV_REQUIRE(score_stride > 0, "%s: score_stride must be positive when attn_score is given", who);
+    SV_REQUIRE(score_stride >= max_len, "%s: score_stride=%lld must cover max_len=%d when attn_score is given", who, (long long)score_stride, max_len);
   SV_REQUIRE(heads_per_cta == 0 || heads_per_cta == 1 || heads_per_cta == 2 || heads_per_cta == 4 || heads_per_cta == 8,
              "%s: heads_per_cta=%d must be 0 (auto), 1, 2, 4 or 8", who, heads_per_cta);
+  const int64_t tk = ws_ticket_bytes(batch, num_kv_heads), per_cta = ws_cta_bytes(num_q_heads);
+  SV_REQUIRE(workspace && aligned16(workspace) && workspace_bytes >= tk + per_cta,
+             "%s: workspace must be 16-byte aligned and hold at least %lld bytes (svb200_workspace_bytes gives the full size)",
+             who, (long long)(tk + per_cta));
+  int64_t ctas = (workspace_bytes - tk) / per_cta;
+  if (ctas > sm_count()) ctas = sm_count();
   AttnParams p;
   p.q = q; p.q_stride_b = q_stride_b; p.k_cache = k_cache; p.v_cache = v_cache;
   p.num_slots = num_slots; p.slot_table = slot_table; p.slot_table_stride = slot_table_stride;
-  p.req_rows = req_rows; p.seq_lens = seq_lens; p.mid_o = mid_o; p.mid_lse = mid_lse; p.out = out;
+  p.req_rows = req_rows; p.seq_lens = seq_lens; p.out = out;
   p.out_stride_b = out_stride_b; p.attn_score = attn_score; p.score_stride = score_stride;
-  p.batch = batch; p.hq = num_q_heads; p.hkv = num_kv_heads; p.split_tokens = split_tokens;
-  p.num_splits = num_splits; p.tickets = tickets; p.sm_scale = sm_scale;
-  if (mid_o_strides_host != nullptr) {
-    p.mo_sb = mid_o_strides_host[0]; p.mo_sh = mid_o_strides_host[1]; p.mo_ss = mid_o_strides_host[2];
-  } else {
-    p.mo_ss = SVB200_HEAD_DIM; p.mo_sh = p.mo_ss * num_splits; p.mo_sb = p.mo_sh * num_q_heads;
-  }
-  if (mid_lse_strides_host != nullptr) {
-    p.ml_sb = mid_lse_strides_host[0]; p.ml_sh = mid_lse_strides_host[1];
-  } else {
-    p.ml_sh = num_splits; p.ml_sb = p.ml_sh * num_q_heads;
-  }
-  if (num_splits > 1)
-    SV_REQUIRE(p.mo_ss >= SVB200_HEAD_DIM && p.mo_ss % 4 == 0 && p.mo_sh % 4 == 0 && p.mo_sb % 4 == 0 &&
-                   p.ml_sh >= num_splits,
-               "%s: mid_o strides must be multiples of 4 with split stride >= 128, mid_lse head stride >= num_splits", who);
+  p.batch = batch; p.hq = num_q_heads; p.hkv = num_kv_heads; p.max_len = max_len;
+  p.sm_scale = sm_scale; p.max_ctas = (int)ctas; p.stages = 0;
+  char* w = static_cast<char*>(workspace);
+  p.tickets = reinterpret_cast<int32_t*>(w);
+  p.ws_lse = reinterpret_cast<float*>(w + tk);
+  p.ws_o = reinterpret_cast<float*>(w + tk + ctas * 2 * num_q_heads * 4 * (int64_t)sizeof(float));
   return launch_sparse_decode_attn(p, heads_per_cta, (cudaStream_t)stream);
 }
 

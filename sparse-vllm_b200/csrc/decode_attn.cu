@@ -1,117 +1,81 @@
-// Sparse paged GQA decode attention for sm_100a: split-K over the visible token
-// slots of each row, slot-table-indirect K/V staging, tensor-core QK^T / PV tile
-// contractions, fp32 online softmax, optional H2O head-max raw-score epilogue and a
-// fused split-K combine (the last CTA of a row merges the partials).
+// Sparse paged GQA decode attention for sm_100a.
 //
 // Reference behaviour (CURRENTF/Sparse-vLLM, src/sparsevllm/kernels/triton/):
 //   gqa_flash_decoding_stage1.py:6-121 (stage 1), 211-295 (2D head-max score),
 //   flash_decoding_stage2.py:8-46 (combine).  Conventions kept: logits scaled by
-//   head_dim^-0.5, softmax numerators cast to bf16 before PV, per-split partials
-//   normalised by their own sum, lse = max + log(sum), empty split -> (0, -inf).
+//   head_dim^-0.5, softmax numerators cast to bf16 before PV, per-partial
+//   normalisation by the partial's own sum, lse = max + log(sum), empty row -> 0.
 //
-// Work decomposition: an item is (batch row b, split s, head group hg of HPC KV
-// heads).  A persistent CTA (8 warps) walks items round-robin; the K/V tiles of
-// consecutive items form one stream so the next tile is always in flight while the
-// current one is consumed.  Inside a tile each warp owns one KV head and one
-// 16-token slice: S^T(16 tok x 8 heads) = K Q^T, then O^T(128 x 8) += V^T P^T.
+// Decomposition (stream-K over token pages instead of the reference's fixed
+// BLOCK_SEQ grid): a "row" is (batch entry b, head group hg of HPC KV heads); a
+// "unit" is one 16-token page of a row.  All units of the launch form one
+// sequence that is cut into gridDim.x equal contiguous ranges, one per persistent
+// CTA, so every SM moves the same number of bytes whatever the batch and the
+// per-row lengths are.  A CTA whose range covers a whole row writes bf16 output
+// directly; otherwise it publishes one fp32 partial (at most two per CTA) and
+// the last contributor of the row (arrival ticket) merges them.
+//
+// Inside a CTA: warps 8-9 are producers.  A producer reads 16 token slots and copies
+// each token's HPC*256 contiguous bytes of K and of V with 16-byte LDGSTS (a whole
+// warp per 512 B, masked tokens zero-filled) into a ring of S stages whose mbarriers
+// complete when the copies land (S * stage bytes ~ 160-190 KB in flight per SM).
+// (A first version issued one UBLKCP bulk copy per token row: the per-lane operands
+// serialise through uniform registers at ~110 cycles per copy and capped the kernel at
+// 2.5 TB/s, profiles/r1_b_*.)  Warps 0-7 are consumers: warp (h, tl) owns KV head h
+// and every TL-th unit: S^T(16 tok x 8 heads) = K Q^T on tensor cores, fp32 online
+// softmax with warp shuffles, O^T(128 x 8) += V^T P^T.
 #include "common.cuh"
 #include "launch.h"
 
 namespace svb200 {
 
-constexpr int kAttnWarps = 8;
-constexpr int kAttnThreads = kAttnWarps * 32;
-constexpr int kAttnStages = 2;
+constexpr int kConsumerWarps = 8;
+constexpr int kConsumerThreads = kConsumerWarps * 32;
+constexpr int kProducerWarps = 2;
+constexpr int kAttnThreads = kConsumerThreads + kProducerWarps * 32;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
+constexpr int kMaxSmem = 227 * 1024;
 
 template <int HPC>
 struct AttnGeom {
-  static constexpr int TL = kAttnWarps / HPC;       // warps (token lanes) per KV head
-  static constexpr int TILE_TOK = 16 * TL;          // tokens per staged tile
-  static constexpr int TOK_BYTES = HPC * kRowBytes;  // bytes of one token's head-group row
-  static constexpr int TOK_STRIDE = TOK_BYTES + 16;  // padded: consecutive tokens shift 4 banks
-  static constexpr int TILE_BYTES = TILE_TOK * TOK_STRIDE;
-  static constexpr int CHUNKS_PER_TOK = HPC * 16;   // 16-byte chunks per token row
-  static constexpr int CHUNKS = TILE_TOK * CHUNKS_PER_TOK;  // = 2048
-  static_assert(CHUNKS % kAttnThreads == 0, "tile must divide over the CTA");
+  static constexpr int TL = kConsumerWarps / HPC;    // consumer warps per KV head
+  static constexpr int TOK_BYTES = HPC * kRowBytes;   // one token's head-group row
+  static constexpr int TOK_STRIDE = TOK_BYTES + 16;   // +16: ldmatrix rows hit distinct banks
+  static constexpr int KV_BYTES = kPage * TOK_STRIDE;  // one tensor of one stage
+  static constexpr int STAGE_BYTES = 2 * KV_BYTES;    // K then V
 };
 
-// Position of a tile in this CTA's stream.
-struct TileCursor {
-  int item;    // global item id; >= n_items means end of stream
-  int tile;    // tile inside the item
-  int ntiles;  // tiles of the item
-  int b, hg, split;
-  int t0, t1;  // token range of the item
-  int64_t row;
+// consumer-only barrier (the producer warp never joins)
+__device__ __forceinline__ void consumer_sync() {
+  asm volatile("bar.sync 1, %0;" ::"n"(kConsumerThreads) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// CTA that owns unit u when U units are cut into G ranges [U*c/G, U*(c+1)/G).
+__device__ __forceinline__ int unit_owner(int64_t u, int64_t U, int64_t G) {
+  return (int)(((u + 1) * G + U - 1) / U - 1);
+}
+
+struct AttnSmemLayout {
+  int ring_off, valid_off, bar_off, q_off, merge_off, prefix_off, total;
 };
 
-struct AttnDims {
-  int n_items, head_groups, num_splits, split_tokens;
-};
-
-template <int HPC>
-__device__ __forceinline__ void cursor_load_item(TileCursor& c, const AttnDims& d,
-                                                 const int32_t* __restrict__ req_rows,
-                                                 const int32_t* __restrict__ seq_lens) {
-  // item = (b * num_splits + split) * head_groups + hg
-  c.hg = c.item % d.head_groups;
-  const int bs = c.item / d.head_groups;
-  c.split = bs % d.num_splits;
-  c.b = bs / d.num_splits;
-  const int len = seq_lens[c.b];
-  c.row = req_rows[c.b];
-  c.t0 = c.split * d.split_tokens;
-  c.t1 = min(len, c.t0 + d.split_tokens);
-  const int n = c.t1 - c.t0;
-  c.ntiles = n > 0 ? (n + AttnGeom<HPC>::TILE_TOK - 1) / AttnGeom<HPC>::TILE_TOK : 0;
-  c.tile = 0;
-}
-
-// Advance to the next tile of the stream (skipping items without tiles).
-template <int HPC>
-__device__ __forceinline__ void cursor_next(TileCursor& c, const AttnDims& d,
-                                            const int32_t* __restrict__ req_rows,
-                                            const int32_t* __restrict__ seq_lens) {
-  if (c.item >= d.n_items) return;
-  if (++c.tile < c.ntiles) return;
-  for (;;) {
-    c.item += gridDim.x;
-    if (c.item >= d.n_items) {
-      c.ntiles = 0;
-      c.tile = 0;
-      return;
-    }
-    cursor_load_item<HPC>(c, d, req_rows, seq_lens);
-    if (c.ntiles > 0) return;
-  }
-}
-
-template <int HPC>
-__device__ __forceinline__ void cursor_first(TileCursor& c, const AttnDims& d,
-                                             const int32_t* __restrict__ req_rows,
-                                             const int32_t* __restrict__ seq_lens) {
-  c.item = blockIdx.x;
-  c.tile = 0;
-  c.ntiles = 0;
-  while (c.item < d.n_items) {
-    cursor_load_item<HPC>(c, d, req_rows, seq_lens);
-    if (c.ntiles > 0) return;
-    c.item += gridDim.x;
-  }
-}
-
-// Slot of token `tok` of the cursor's tile, or -1 when outside the item / invalid.
-template <int HPC>
-__device__ __forceinline__ int cursor_slot(const TileCursor& c, int n_items, int tok,
-                                           const int32_t* __restrict__ slot_table,
-                                           int64_t slot_stride, int64_t num_slots) {
-  if (c.item >= n_items) return -1;
-  const int t = c.t0 + c.tile * AttnGeom<HPC>::TILE_TOK + tok;
-  if (t >= c.t1) return -1;
-  const int s = slot_table[c.row * slot_stride + t];
-  return (s >= 0 && s < num_slots) ? s : -1;
+template <int HPC, int NT>
+__host__ __device__ inline AttnSmemLayout attn_smem_layout(int stages, int gsz, int rows) {
+  using G = AttnGeom<HPC>;
+  AttnSmemLayout L;
+  int off = 0;
+  L.ring_off = off;   off += stages * G::STAGE_BYTES;
+  L.q_off = off;      off += HPC * gsz * kRowBytes;
+  L.merge_off = off;  off += (G::TL > 1) ? (kConsumerWarps - HPC) * 32 * NT * 36 * 4 : 0;
+  L.bar_off = off;    off += 2 * stages * 8;
+  L.valid_off = off;  off += ((stages * 4 + 15) / 16) * 16;
+  L.prefix_off = off; off += ((rows + 1) * 4 + 15) / 16 * 16;
+  L.total = off;
+  return L;
 }
 
 template <int HPC, int NT, bool WITH_SCORE>
@@ -120,90 +84,165 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
   constexpr int TL = G::TL;
 
   extern __shared__ __align__(128) unsigned char smem[];
-  unsigned char* sK = smem;                                   // [stages][TILE_BYTES]
-  unsigned char* sV = sK + kAttnStages * G::TILE_BYTES;        // [stages][TILE_BYTES]
-  int* sSlot = reinterpret_cast<int*>(sV + kAttnStages * G::TILE_BYTES);  // [3][TILE_TOK]
-  __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(sSlot + 3 * G::TILE_TOK);  // [HPC*gsz][128]
   const int gsz = p.hq / p.hkv;
-  float* sMerge = reinterpret_cast<float*>(sQ + HPC * gsz * kHeadDim);  // [NREG][256] (TL > 1)
+  const int HG = p.hkv / HPC;
+  const int R = p.batch * HG;
+  const int S = p.stages;
+  const AttnSmemLayout L = attn_smem_layout<HPC, NT>(S, gsz, R);
+  unsigned char* ring = smem + L.ring_off;
+  __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(smem + L.q_off);
+  float* sMerge = reinterpret_cast<float*>(smem + L.merge_off);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.bar_off);
+  uint64_t* empty_bar = full_bar + S;
+  uint32_t* sValid = reinterpret_cast<uint32_t*>(smem + L.valid_off);
+  int* sPrefix = reinterpret_cast<int*>(smem + L.prefix_off);
   __shared__ int s_flag;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int g = lane >> 2, t = lane & 3;
-  const int h_local = warp % HPC, tl = warp / HPC;
-  const int tok0 = tl * 16;
 
-  AttnDims dims;
-  dims.head_groups = p.hkv / HPC;
-  dims.num_splits = p.num_splits;
-  dims.split_tokens = p.split_tokens;
-  dims.n_items = p.batch * p.num_splits * dims.head_groups;
+  // ---- setup: barriers, per-row page counts -> exclusive prefix
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(&full_bar[s], 33);  // 32 async copy arrivals + the producer's release
+      mbar_init(&empty_bar[s], HPC);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 0) {
+    int carry = 0;
+    for (int base = 0; base < R; base += 32) {
+      const int r = base + lane;
+      int n = 0;
+      if (r < R) {
+        const int len = min(p.seq_lens[r / HG], p.max_len);
+        n = len > 0 ? (len + kPage - 1) / kPage : 0;
+      }
+      int inc = n;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+      }
+      if (r < R) sPrefix[r] = carry + inc - n;
+      carry += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) sPrefix[R] = carry;
+  }
+  // rows without tokens produce zeros (reference: empty split -> 0 / -inf)
+  for (int b = blockIdx.x; b < p.batch; b += gridDim.x) {
+    if (p.seq_lens[b] <= 0 || p.max_len <= 0) {
+      uint4* o4 = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) +
+                                           (int64_t)b * p.out_stride_b);
+      for (int i = tid; i < p.hq * 16; i += kAttnThreads) o4[i] = make_uint4(0, 0, 0, 0);
+    }
+  }
+  __syncthreads();
+
+  const int64_t U = sPrefix[R];
+  // never more ranges than units: every range is non-empty, so the contributors of a
+  // row are exactly the CTAs unit_owner(first unit) .. unit_owner(last unit)
+  const int64_t Gn = U < (int64_t)gridDim.x ? U : (int64_t)gridDim.x;
+  if ((int64_t)blockIdx.x >= Gn) return;
+  const int u0 = (int)(U * blockIdx.x / Gn), u1 = (int)(U * (blockIdx.x + 1) / Gn);
+  // first row of the range: largest r with prefix[r] <= u0 and a non-empty row
+  int r_first;
+  {
+    int lo = 0, hi = R;  // invariant: prefix[lo] <= u0 < prefix[hi]
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (sPrefix[mid] <= u0) lo = mid; else hi = mid;
+    }
+    r_first = lo;
+  }
 
   const __nv_bfloat16* kc = reinterpret_cast<const __nv_bfloat16*>(p.k_cache);
   const __nv_bfloat16* vc = reinterpret_cast<const __nv_bfloat16*>(p.v_cache);
   const int64_t slot_elems = (int64_t)p.hkv * kHeadDim;
-  const float scale_log2 = p.sm_scale * kLog2e;
 
-  // Issue the cp.async copies of one tile (slots already staged in sSlot[ring]).
-  auto issue_tile = [&](const TileCursor& c, int stage, int ring) {
-    if (c.item < dims.n_items) {
-      const uint32_t kdst = smem_u32(sK + stage * G::TILE_BYTES);
-      const uint32_t vdst = smem_u32(sV + stage * G::TILE_BYTES);
-      const int64_t head_off = (int64_t)c.hg * HPC * kHeadDim;
+  if (warp >= kConsumerWarps) {
+    // ============================================================== producers
+    // Producer warp pw feeds every kProducerWarps-th unit.  Lane t < 16 holds the slot of
+    // token t (fetched two units ahead so the table's DRAM latency hides behind the wait
+    // for a free stage); each token row (HPC*256 contiguous bytes of K, same of V) is
+    // copied by the whole warp with 16-byte LDGSTS (512 B per instruction), masked tokens
+    // zero-filled.  Every lane's copies arrive on the stage's mbarrier when they land.
+    const int n_units = u1 - u0;
+    const int pw = warp - kConsumerWarps;
+    const int tok_lane = lane & 15;
+    int r_pf = r_first, r_is = r_first;
+    auto fetch = [&](int i) -> int {  // raw slot of token tok_lane in local unit i
+      if (i >= n_units) return -1;
+      const int u = u0 + i;
+      while (sPrefix[r_pf + 1] <= u) ++r_pf;
+      const int b = r_pf / HG;
+      const int len = min(p.seq_lens[b], p.max_len);
+      const int t = (u - sPrefix[r_pf]) * kPage + tok_lane;
+      if (t >= len) return -1;
+      return __ldg(p.slot_table + (int64_t)p.req_rows[b] * p.slot_table_stride + t);
+    };
+    constexpr int LPR = G::TOK_BYTES >= 512 ? 32 : G::TOK_BYTES / 16;  // lanes per token row
+    constexpr int TPI = 32 / LPR;                                     // tokens per instruction
+    constexpr int CPR = G::TOK_BYTES / (LPR * 16);                    // instructions per row
+    const int sub = lane / LPR, chunk = lane % LPR;
+    int slot_a = fetch(pw), slot_b = fetch(pw + kProducerWarps);
+    for (int i = pw; i < n_units; i += kProducerWarps) {
+      const int slot_c = fetch(i + 2 * kProducerWarps);
+      const int my = (slot_a >= 0 && slot_a < p.num_slots) ? slot_a : -1;
+      const uint32_t mask = __ballot_sync(0xffffffffu, my >= 0) & 0xffffu;
+      const int s = i % S;
+      mbar_wait(&empty_bar[s], ((i / S) & 1) ^ 1);
+      while (sPrefix[r_is + 1] <= u0 + i) ++r_is;
+      const int hg = r_is % HG;
+      const __nv_bfloat16* ksrc = kc + (int64_t)hg * HPC * kHeadDim + chunk * 8;
+      const __nv_bfloat16* vsrc = vc + (int64_t)hg * HPC * kHeadDim + chunk * 8;
+      const uint32_t dst0 = smem_u32(ring + s * G::STAGE_BYTES) + chunk * 16;
 #pragma unroll
-      for (int i = 0; i < G::CHUNKS / kAttnThreads; ++i) {
-        const int ch = i * kAttnThreads + tid;
-        const int tok = ch / G::CHUNKS_PER_TOK, off = ch % G::CHUNKS_PER_TOK;
-        const int slot = sSlot[ring * G::TILE_TOK + tok];
-        const int64_t src = (int64_t)max(slot, 0) * slot_elems + head_off + off * 8;
-        const uint32_t d = tok * G::TOK_STRIDE + off * 16;
-        const int nbytes = slot >= 0 ? 16 : 0;  // invalid token -> zero fill
-        cp_async_16(kdst + d, kc + src, nbytes);
-        cp_async_16(vdst + d, vc + src, nbytes);
+      for (int t0 = 0; t0 < kPage; t0 += TPI) {
+        const int tok = t0 + sub;
+        const int slot = __shfl_sync(0xffffffffu, my, tok);
+        const int nbytes = slot >= 0 ? 16 : 0;
+        const int64_t off = (int64_t)max(slot, 0) * slot_elems;
+        const uint32_t dst = dst0 + tok * G::TOK_STRIDE;
+#pragma unroll
+        for (int c = 0; c < CPR; ++c) {
+          cp_async_16(dst + c * 512, ksrc + off + c * 256, nbytes);
+          cp_async_16(dst + G::KV_BYTES + c * 512, vsrc + off + c * 256, nbytes);
+        }
       }
+      if (lane == 0) sValid[s] = mask;
+      cp_async_mbar_arrive(&full_bar[s]);
+      if (lane == 0) mbar_arrive(&full_bar[s]);  // release: publishes sValid
+      slot_a = slot_b;
+      slot_b = slot_c;
     }
-    cp_async_commit();
-  };
-
-  TileCursor c0, c1, c2;
-  cursor_first<HPC>(c0, dims, p.req_rows, p.seq_lens);
-  c1 = c0;
-  cursor_next<HPC>(c1, dims, p.req_rows, p.seq_lens);
-  c2 = c1;
-  cursor_next<HPC>(c2, dims, p.req_rows, p.seq_lens);
-
-  // ---- stream prologue: slots of tiles 0 and 1, data of tile 0
-  if (tid < G::TILE_TOK) {
-    sSlot[0 * G::TILE_TOK + tid] =
-        cursor_slot<HPC>(c0, dims.n_items, tid, p.slot_table, p.slot_table_stride, p.num_slots);
-    sSlot[1 * G::TILE_TOK + tid] =
-        cursor_slot<HPC>(c1, dims.n_items, tid, p.slot_table, p.slot_table_stride, p.num_slots);
+    return;
   }
-  __syncthreads();
-  issue_tile(c0, 0, 0);
 
-  int gtile = 0;  // index of the current tile in this CTA's stream
+  // ================================================================ consumers
+  const int g = lane >> 2, t = lane & 3;
+  const int h_local = warp % HPC, tl = warp / HPC;
+  const float scale_log2 = p.sm_scale * kLog2e;
+  const int heads_row = HPC * gsz;
 
-  // ---- item loop (items without tiles still publish an empty partial)
-  for (int item = blockIdx.x; item < dims.n_items; item += gridDim.x) {
-    const int hg = item % dims.head_groups;
-    const int bs = item / dims.head_groups;
-    const int split = bs % dims.num_splits;
-    const int b = bs / dims.num_splits;
-    const int len = p.seq_lens[b];
-    const int it0 = split * dims.split_tokens;
-    const int it1 = min(len, it0 + dims.split_tokens);
-    const int ntiles = it1 > it0 ? (it1 - it0 + G::TILE_TOK - 1) / G::TILE_TOK : 0;
+  int r = r_first;
+  int i = 0;  // index of the next unit inside this CTA's range
+  while (u0 + i < u1) {
+    while (sPrefix[r + 1] <= u0 + i) ++r;
+    const int row_begin = sPrefix[r], row_end = sPrefix[r + 1];
+    const int seg_begin = u0 + i, seg_end = min(u1, row_end);
+    const int n = seg_end - seg_begin;
+    const bool complete = seg_begin == row_begin && seg_end == row_end;
+    const int b = r / HG, hg = r - b * HG;
 
-    // q rows of this head group -> smem -> B fragments
+    // q rows of this head group -> smem -> B fragments (k = head dim, n = q head)
     uint32_t qb[NT][8][2];
-    if (ntiles > 0) {
+    {
       const uint4* qsrc = reinterpret_cast<const uint4*>(
           reinterpret_cast<const __nv_bfloat16*>(p.q) + (int64_t)b * p.q_stride_b +
-          (int64_t)hg * HPC * gsz * kHeadDim);
+          (int64_t)hg * heads_row * kHeadDim);
       uint4* qdst = reinterpret_cast<uint4*>(sQ);
-      for (int i = tid; i < HPC * gsz * 16; i += kAttnThreads) qdst[i] = qsrc[i];
-      __syncthreads();
+      for (int c = tid; c < heads_row * 16; c += kConsumerThreads) qdst[c] = qsrc[c];
+      consumer_sync();
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) {
         const int hi = nt * 8 + g;
@@ -225,57 +264,47 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
 #pragma unroll
       for (int dt = 0; dt < 8; ++dt)
 #pragma unroll
-        for (int i = 0; i < 4; ++i) o_acc[nt][dt][i] = 0.f;
+        for (int e = 0; e < 4; ++e) o_acc[nt][dt][e] = 0.f;
     }
 
-    for (int tile = 0; tile < ntiles; ++tile, ++gtile) {
-      const int stage = gtile & 1, ring = gtile % 3;
-      // slots of the tile after next (consumed at the end of this iteration)
-      int pre_slot = -1;
-      if (tid < G::TILE_TOK)
-        pre_slot =
-            cursor_slot<HPC>(c2, dims.n_items, tid, p.slot_table, p.slot_table_stride, p.num_slots);
-      // next tile's data into the other stage
-      issue_tile(c1, stage ^ 1, (gtile + 1) % 3);
-      cp_async_wait<1>();
-      __syncthreads();
-
-      // ------------------------------------------------ compute on `stage`
-      const int sl0 = sSlot[ring * G::TILE_TOK + tok0 + g];
-      const int sl1 = sSlot[ring * G::TILE_TOK + tok0 + g + 8];
-      const bool tv0 = sl0 >= 0, tv1 = sl1 >= 0;
-      if (__any_sync(0xffffffffu, tv0 || tv1)) {
-        const uint32_t kbase = smem_u32(sK + stage * G::TILE_BYTES) + h_local * kRowBytes;
-        const uint32_t vbase = smem_u32(sV + stage * G::TILE_BYTES) + h_local * kRowBytes;
-        float s[NT][4];
+    for (int j = i + ((tl - i % TL + TL) % TL); j < i + n; j += TL) {
+      const int s = j % S;
+      mbar_wait(&full_bar[s], (j / S) & 1);
+      const uint32_t mask = sValid[s];
+      const bool tv0 = (mask >> g) & 1u, tv1 = (mask >> (g + 8)) & 1u;
+      if (mask != 0u) {
+        const uint32_t kbase = smem_u32(ring + s * G::STAGE_BYTES) + h_local * kRowBytes;
+        const uint32_t vbase = kbase + G::KV_BYTES;
+        float sc[NT][4];
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        for (int nt = 0; nt < NT; ++nt) sc[nt][0] = sc[nt][1] = sc[nt][2] = sc[nt][3] = 0.f;
         {
           const uint32_t kaddr =
-              kbase + (tok0 + (lane & 7) + ((lane >> 3) & 1) * 8) * G::TOK_STRIDE + (lane >> 4) * 16;
+              kbase + ((lane & 7) + ((lane >> 3) & 1) * 8) * G::TOK_STRIDE + (lane >> 4) * 16;
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk) {
             uint32_t a[4];
             ldmatrix_x4(a, kaddr + kk * 32);
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt) mma_16816(s[nt], a, qb[nt][kk][0], qb[nt][kk][1]);
+            for (int nt = 0; nt < NT; ++nt) mma_16816(sc[nt], a, qb[nt][kk][0], qb[nt][kk][1]);
           }
         }
         if constexpr (WITH_SCORE) {
-          // raw (unscaled) max over the heads of this KV head, then over KV heads via atomics
+          // raw (unscaled) max over this KV head's q heads; KV heads meet in fp32 atomics
           float r0 = -INFINITY, r1 = -INFINITY;
 #pragma unroll
           for (int nt = 0; nt < NT; ++nt) {
             const int col = nt * 8 + 2 * t;
-            if (col < gsz) r0 = fmaxf(r0, s[nt][0]), r1 = fmaxf(r1, s[nt][2]);
-            if (col + 1 < gsz) r0 = fmaxf(r0, s[nt][1]), r1 = fmaxf(r1, s[nt][3]);
+            if (col < gsz) r0 = fmaxf(r0, sc[nt][0]), r1 = fmaxf(r1, sc[nt][2]);
+            if (col + 1 < gsz) r0 = fmaxf(r0, sc[nt][1]), r1 = fmaxf(r1, sc[nt][3]);
           }
           r0 = fmaxf(r0, __shfl_xor_sync(0xffffffffu, r0, 1));
           r0 = fmaxf(r0, __shfl_xor_sync(0xffffffffu, r0, 2));
           r1 = fmaxf(r1, __shfl_xor_sync(0xffffffffu, r1, 1));
           r1 = fmaxf(r1, __shfl_xor_sync(0xffffffffu, r1, 2));
           if (t == 0) {
-            float* srow = p.attn_score + (int64_t)b * p.score_stride + it0 + tile * G::TILE_TOK + tok0;
+            const int t0 = (seg_begin + (j - i) - row_begin) * kPage;
+            float* srow = p.attn_score + (int64_t)b * p.score_stride + t0;
             if (tv0) atomic_max_f32(srow + g, r0);
             if (tv1) atomic_max_f32(srow + g + 8, r1);
           }
@@ -284,24 +313,24 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
           float x[4];
-          x[0] = tv0 ? s[nt][0] * scale_log2 : -INFINITY;
-          x[1] = tv0 ? s[nt][1] * scale_log2 : -INFINITY;
-          x[2] = tv1 ? s[nt][2] * scale_log2 : -INFINITY;
-          x[3] = tv1 ? s[nt][3] * scale_log2 : -INFINITY;
+          x[0] = tv0 ? sc[nt][0] * scale_log2 : -INFINITY;
+          x[1] = tv0 ? sc[nt][1] * scale_log2 : -INFINITY;
+          x[2] = tv1 ? sc[nt][2] * scale_log2 : -INFINITY;
+          x[3] = tv1 ? sc[nt][3] * scale_log2 : -INFINITY;
           float alpha[2];
 #pragma unroll
-          for (int j = 0; j < 2; ++j) {
-            float mloc = fmaxf(x[j], x[j + 2]);
+          for (int e = 0; e < 2; ++e) {
+            float mloc = fmaxf(x[e], x[e + 2]);
             mloc = fmaxf(mloc, __shfl_xor_sync(0xffffffffu, mloc, 4));
             mloc = fmaxf(mloc, __shfl_xor_sync(0xffffffffu, mloc, 8));
             mloc = fmaxf(mloc, __shfl_xor_sync(0xffffffffu, mloc, 16));
-            const float mnew = fmaxf(m_run[nt][j], mloc);
+            const float mnew = fmaxf(m_run[nt][e], mloc);
             const float msafe = mnew == -INFINITY ? 0.f : mnew;
-            alpha[j] = fast_exp2(m_run[nt][j] - msafe);
-            x[j] = fast_exp2(x[j] - msafe);
-            x[j + 2] = fast_exp2(x[j + 2] - msafe);
-            l_run[nt][j] = l_run[nt][j] * alpha[j] + x[j] + x[j + 2];
-            m_run[nt][j] = mnew;
+            alpha[e] = fast_exp2(m_run[nt][e] - msafe);
+            x[e] = fast_exp2(x[e] - msafe);
+            x[e + 2] = fast_exp2(x[e + 2] - msafe);
+            l_run[nt][e] = l_run[nt][e] * alpha[e] + x[e] + x[e + 2];
+            m_run[nt][e] = mnew;
           }
 #pragma unroll
           for (int dt = 0; dt < 8; ++dt) {
@@ -310,13 +339,13 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
             o_acc[nt][dt][2] *= alpha[0];
             o_acc[nt][dt][3] *= alpha[1];
           }
-          // P (tok x head) -> bf16 -> transpose -> B fragment (tok as k, head as n)
+          // P (tok x head) -> bf16 -> transpose -> B fragment (k = token, n = head)
           pb[nt][0] = movmatrix_trans(pack_bf16x2(x[0], x[1]));
           pb[nt][1] = movmatrix_trans(pack_bf16x2(x[2], x[3]));
         }
         {
           const uint32_t vaddr =
-              vbase + (tok0 + (lane & 7) + (lane >> 4) * 8) * G::TOK_STRIDE + ((lane >> 3) & 1) * 16;
+              vbase + ((lane & 7) + (lane >> 4) * 8) * G::TOK_STRIDE + ((lane >> 3) & 1) * 16;
 #pragma unroll
           for (int dt = 0; dt < 8; ++dt) {
             uint32_t a[4];
@@ -326,133 +355,132 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
           }
         }
       }
-      // ------------------------------------------------ rotate the stream
-      if (tid < G::TILE_TOK) sSlot[((gtile + 2) % 3) * G::TILE_TOK + tid] = pre_slot;
-      c1 = c2;
-      cursor_next<HPC>(c2, dims, p.req_rows, p.seq_lens);
-      __syncthreads();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_bar[s]);
     }
 
-    // ------------------------------------------------------ item epilogue
+    // ---------------------------------------------------- segment epilogue
     // per-head sums live as per-lane partials: reduce over the 8 token lanes
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        float l = l_run[nt][j];
+      for (int e = 0; e < 2; ++e) {
+        float l = l_run[nt][e];
         l += __shfl_xor_sync(0xffffffffu, l, 4);
         l += __shfl_xor_sync(0xffffffffu, l, 8);
         l += __shfl_xor_sync(0xffffffffu, l, 16);
-        l_run[nt][j] = l;
+        l_run[nt][e] = l;
       }
     if constexpr (TL > 1) {
-      if (ntiles > 0) {
-        if (tl > 0) {
+      // warps tl > 0 hand their state to the tl == 0 warp of the same KV head
+      if (tl > 0) {
+        const int widx = (tl - 1) * HPC + h_local;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+          float* rec = sMerge + ((widx * NT + nt) * 36) * 32 + lane;
+          rec[0 * 32] = m_run[nt][0];
+          rec[1 * 32] = m_run[nt][1];
+          rec[2 * 32] = l_run[nt][0];
+          rec[3 * 32] = l_run[nt][1];
+#pragma unroll
+          for (int dt = 0; dt < 8; ++dt)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) rec[(4 + dt * 4 + e) * 32] = o_acc[nt][dt][e];
+        }
+      }
+      consumer_sync();
+      if (tl == 0) {
+        for (int o = 1; o < TL; ++o) {
+          const int widx = (o - 1) * HPC + h_local;
 #pragma unroll
           for (int nt = 0; nt < NT; ++nt) {
-            float* rec = sMerge + (nt * 36) * kAttnThreads + tid;
-            rec[0 * kAttnThreads] = m_run[nt][0];
-            rec[1 * kAttnThreads] = m_run[nt][1];
-            rec[2 * kAttnThreads] = l_run[nt][0];
-            rec[3 * kAttnThreads] = l_run[nt][1];
+            const float* rec = sMerge + ((widx * NT + nt) * 36) * 32 + lane;
+            float sa[2], sb[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const float mo = rec[e * 32], lo = rec[(2 + e) * 32];
+              const float mnew = fmaxf(m_run[nt][e], mo);
+              const float msafe = mnew == -INFINITY ? 0.f : mnew;
+              sa[e] = fast_exp2(m_run[nt][e] - msafe);
+              sb[e] = fast_exp2(mo - msafe);
+              l_run[nt][e] = l_run[nt][e] * sa[e] + lo * sb[e];
+              m_run[nt][e] = mnew;
+            }
 #pragma unroll
             for (int dt = 0; dt < 8; ++dt)
 #pragma unroll
-              for (int i = 0; i < 4; ++i) rec[(4 + dt * 4 + i) * kAttnThreads] = o_acc[nt][dt][i];
-          }
-        }
-        __syncthreads();
-        if (tl == 0) {
-          for (int o = 1; o < TL; ++o) {
-            const int ptid = (o * HPC + h_local) * 32 + lane;
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt) {
-              const float* rec = sMerge + (nt * 36) * kAttnThreads + ptid;
-              float sa[2], sb[2];
-#pragma unroll
-              for (int j = 0; j < 2; ++j) {
-                const float mo = rec[j * kAttnThreads], lo = rec[(2 + j) * kAttnThreads];
-                const float mnew = fmaxf(m_run[nt][j], mo);
-                const float msafe = mnew == -INFINITY ? 0.f : mnew;
-                sa[j] = fast_exp2(m_run[nt][j] - msafe);
-                sb[j] = fast_exp2(mo - msafe);
-                l_run[nt][j] = l_run[nt][j] * sa[j] + lo * sb[j];
-                m_run[nt][j] = mnew;
-              }
-#pragma unroll
-              for (int dt = 0; dt < 8; ++dt)
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                  o_acc[nt][dt][i] = o_acc[nt][dt][i] * sa[i & 1] +
-                                     rec[(4 + dt * 4 + i) * kAttnThreads] * sb[i & 1];
-            }
+              for (int e = 0; e < 4; ++e)
+                o_acc[nt][dt][e] =
+                    o_acc[nt][dt][e] * sa[e & 1] + rec[(4 + dt * 4 + e) * 32] * sb[e & 1];
           }
         }
       }
     }
-    // publish the partial of this (b, split, head group): normalised o, natural-log lse
+    // publish: bf16 output when this CTA saw the whole row, else an fp32 partial
+    const int pslot = 2 * blockIdx.x + (seg_begin == u0 ? 0 : 1);
     if (tl == 0) {
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          const int hi = nt * 8 + 2 * t + j;
+        for (int e = 0; e < 2; ++e) {
+          const int hi = nt * 8 + 2 * t + e;
           if (hi < gsz) {
-            const int head = (hg * HPC + h_local) * gsz + hi;
-            const float l = l_run[nt][j];
+            const int head_local = h_local * gsz + hi;
+            const float l = l_run[nt][e];
             const float inv = l > 0.f ? 1.f / l : 0.f;
-            if (p.num_splits == 1) {
+            if (complete) {
               __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
-                                    (int64_t)b * p.out_stride_b + (int64_t)head * kHeadDim;
+                                    (int64_t)b * p.out_stride_b +
+                                    (int64_t)(hg * heads_row + head_local) * kHeadDim;
 #pragma unroll
               for (int dt = 0; dt < 8; ++dt) {
-                orow[dt * 16 + g] = __float2bfloat16_rn(o_acc[nt][dt][j] * inv);
-                orow[dt * 16 + g + 8] = __float2bfloat16_rn(o_acc[nt][dt][2 + j] * inv);
+                orow[dt * 16 + g] = __float2bfloat16_rn(o_acc[nt][dt][e] * inv);
+                orow[dt * 16 + g + 8] = __float2bfloat16_rn(o_acc[nt][dt][2 + e] * inv);
               }
             } else {
-              float* orow = p.mid_o + (int64_t)b * p.mo_sb + (int64_t)head * p.mo_sh +
-                            (int64_t)split * p.mo_ss;
+              float* orow = p.ws_o + ((int64_t)pslot * heads_row + head_local) * kHeadDim;
 #pragma unroll
               for (int dt = 0; dt < 8; ++dt) {
-                orow[dt * 16 + g] = o_acc[nt][dt][j] * inv;
-                orow[dt * 16 + g + 8] = o_acc[nt][dt][2 + j] * inv;
+                orow[dt * 16 + g] = o_acc[nt][dt][e] * inv;
+                orow[dt * 16 + g + 8] = o_acc[nt][dt][2 + e] * inv;
               }
               if (g == 0)
-                p.mid_lse[(int64_t)b * p.ml_sb + (int64_t)head * p.ml_sh + split] =
-                    l > 0.f ? m_run[nt][j] * kLn2 + __logf(l) : -INFINITY;
+                p.ws_lse[(int64_t)pslot * heads_row + head_local] =
+                    l > 0.f ? m_run[nt][e] * kLn2 + __logf(l) : -INFINITY;
             }
           }
         }
     }
-    if (p.num_splits > 1) {
-      // arrival ticket; the last split of (b, hg) merges all partials
+    if (!complete) {
+      // arrival ticket: the last contributor of the row merges every partial
+      const int c_first = unit_owner(row_begin, U, Gn), c_last = unit_owner(row_end - 1, U, Gn);
       __threadfence();
-      __syncthreads();
+      consumer_sync();
       if (tid == 0) {
-        int* tk = p.tickets + b * dims.head_groups + hg;
-        const int ticket = atomicAdd(tk, 1);
-        s_flag = (ticket == p.num_splits - 1);
-        if (s_flag) *tk = 0;
+        const int ticket = atomicAdd(&p.tickets[r], 1);
+        s_flag = (ticket == c_last - c_first);
+        if (s_flag) p.tickets[r] = 0;  // scratch stays zeroed for the next launch / replay
       }
-      __syncthreads();
+      consumer_sync();
       if (s_flag) {
         __threadfence();
-        const int nheads = HPC * gsz;
-        for (int w = tid; w < nheads * 32; w += kAttnThreads) {
-          const int head = hg * nheads + (w >> 5), d4 = w & 31;
-          const float* lse_row = p.mid_lse + (int64_t)b * p.ml_sb + (int64_t)head * p.ml_sh;
-          const float* o_row = p.mid_o + (int64_t)b * p.mo_sb + (int64_t)head * p.mo_sh;
+        for (int w = tid; w < heads_row * 32; w += kConsumerThreads) {
+          const int head_local = w >> 5, d4 = w & 31;
           float mx = -INFINITY;
-          for (int sidx = 0; sidx < p.num_splits; ++sidx)
-            mx = fmaxf(mx, __ldcg(lse_row + sidx));
+          for (int c = c_first; c <= c_last; ++c) {
+            const int ps = 2 * c + ((int)(U * c / Gn) >= row_begin ? 0 : 1);
+            mx = fmaxf(mx, __ldcg(p.ws_lse + (int64_t)ps * heads_row + head_local));
+          }
           float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
           float wsum = 0.f;
-          for (int sidx = 0; sidx < p.num_splits; ++sidx) {
-            const float lse = __ldcg(lse_row + sidx);
+          for (int c = c_first; c <= c_last; ++c) {
+            const int ps = 2 * c + ((int)(U * c / Gn) >= row_begin ? 0 : 1);
+            const float lse = __ldcg(p.ws_lse + (int64_t)ps * heads_row + head_local);
             if (lse == -INFINITY) continue;
             const float wgt = __expf(lse - mx);
-            const float4 v =
-                __ldcg(reinterpret_cast<const float4*>(o_row + (int64_t)sidx * p.mo_ss) + d4);
+            const float4 v = __ldcg(reinterpret_cast<const float4*>(
+                                        p.ws_o + ((int64_t)ps * heads_row + head_local) * kHeadDim) +
+                                    d4);
             acc.x += wgt * v.x, acc.y += wgt * v.y, acc.z += wgt * v.z, acc.w += wgt * v.w;
             wsum += wgt;
           }
@@ -461,29 +489,44 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
           o2.x = pack_bf16x2(acc.x * inv, acc.y * inv);
           o2.y = pack_bf16x2(acc.z * inv, acc.w * inv);
           __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
-                                (int64_t)b * p.out_stride_b + (int64_t)head * kHeadDim;
+                                (int64_t)b * p.out_stride_b +
+                                (int64_t)(hg * heads_row + head_local) * kHeadDim;
           *reinterpret_cast<uint2*>(orow + d4 * 4) = o2;
         }
       }
     }
-    __syncthreads();  // sQ / sMerge / s_flag are reused by the next item
+    consumer_sync();  // sQ / sMerge / s_flag are reused by the next segment
+    i += n;
   }
-  cp_async_wait<0>();
 }
 
 template <int HPC, int NT, bool WITH_SCORE>
-static int launch_variant(const AttnParams& p, cudaStream_t stream) {
+static int launch_variant(const AttnParams& p_in, cudaStream_t stream) {
   using G = AttnGeom<HPC>;
+  AttnParams p = p_in;
   const int gsz = p.hq / p.hkv;
-  size_t smem = (size_t)2 * kAttnStages * G::TILE_BYTES + 3 * G::TILE_TOK * sizeof(int) +
-                (size_t)HPC * gsz * kRowBytes;
-  if (G::TL > 1) smem += (size_t)NT * 36 * kAttnThreads * sizeof(float);
+  const int rows = p.batch * (p.hkv / HPC);
+  const int fixed = attn_smem_layout<HPC, NT>(0, gsz, rows).total + 256;  // + static smem
+  int stages = (kMaxSmem - fixed) / (G::STAGE_BYTES + 20);
+  if (stages > 24) stages = 24;
+  // Unit j is consumed by the warps tl = j % TL; with TL | stages a stage is always drained by the
+  // same warps, so the phase a warp waits for is never more than one ahead of the barrier (parity
+  // waits cannot tell a phase from the one two before it).
+  stages -= stages % G::TL;
+  if (stages < 2) {
+    set_error("sparse_decode_attn: batch*head_groups=%d rows leave no shared memory for the KV ring", rows);
+    return 1;
+  }
+  p.stages = stages;
+  const size_t smem = attn_smem_layout<HPC, NT>(stages, gsz, rows).total;
   auto kern = sparse_decode_attn_kernel<HPC, NT, WITH_SCORE>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return cuda_error("sparse_decode_attn smem attr", e);
-  const int n_items = p.batch * p.num_splits * (p.hkv / HPC);
-  int grid = sm_count();
-  if (grid > n_items) grid = n_items;
+  const int64_t max_units = (int64_t)rows * ((p.max_len + kPage - 1) / kPage);
+  int grid = max_ctas();
+  if (grid > p.max_ctas) grid = p.max_ctas;
+  if ((int64_t)grid > max_units) grid = (int)max_units;
+  if (grid < 1) grid = 1;
   kern<<<grid, kAttnThreads, smem, stream>>>(p);
   return check_launch("sparse_decode_attn");
 }
@@ -497,21 +540,15 @@ static int launch_hpc(const AttnParams& p, cudaStream_t stream) {
   return score ? launch_variant<HPC, 2, true>(p, stream) : launch_variant<HPC, 2, false>(p, stream);
 }
 
+int attn_auto_heads_per_cta(int hkv) {
+  for (int c = 8; c > 1; c >>= 1)
+    if (hkv % c == 0) return c;
+  return 1;
+}
+
 int launch_sparse_decode_attn(const AttnParams& p, int heads_per_cta, cudaStream_t stream) {
   if (p.batch <= 0) return 0;
-  int hpc = heads_per_cta;
-  if (hpc <= 0) {
-    // auto: whole rows of contiguous bytes per token as long as there are enough items
-    hpc = 1;
-    for (int c = 8; c >= 1; c >>= 1) {
-      if (p.hkv % c) continue;
-      const int items = p.batch * p.num_splits * (p.hkv / c);
-      if (items >= sm_count() || c == 1) {
-        hpc = c;
-        break;
-      }
-    }
-  }
+  const int hpc = heads_per_cta > 0 ? heads_per_cta : attn_auto_heads_per_cta(p.hkv);
   if (p.hkv % hpc) {
     set_error("sparse_decode_attn: heads_per_cta=%d does not divide num_kv_heads=%d", hpc, p.hkv);
     return 1;

@@ -11,6 +11,7 @@ void set_error(const char* fmt, ...);
 int cuda_error(const char* what, cudaError_t e);
 int check_launch(const char* what);
 int sm_count();
+int max_ctas();  // persistent-grid size: sm_count() unless svb200_set_max_ctas lowered it
 
 // quest.cu
 int launch_quest_page_minmax(const void* k_cache, void* bounds_layer, const int32_t* slot_mapping,
@@ -20,7 +21,7 @@ int launch_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
                                       const int32_t* req_rows, const int32_t* seq_lens, int batch,
                                       int layers, int hkv, int64_t num_slots, int64_t num_pages,
                                       cudaStream_t stream);
-int launch_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds,
+int launch_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds, int64_t num_pages,
                             const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
                             const int32_t* context_lens, void* scores, int64_t score_stride,
                             int batch, int hq, int hkv, int n_cols, cudaStream_t stream);
@@ -31,7 +32,7 @@ int launch_quest_select_pack(const void* scores, int64_t score_stride, int n_col
                              const int32_t* dense_table, int64_t dense_stride, int token_budget,
                              int page_budget_base, int out_width, cudaStream_t stream);
 int launch_quest_score_select_pack(const void* q, int64_t q_stride_b, const void* bounds,
-                                   const int32_t* page_table, int64_t pt_stride,
+                                   int64_t num_pages, const int32_t* page_table, int64_t pt_stride,
                                    const int32_t* req_rows, const int32_t* context_lens,
                                    void* scores, int64_t score_stride, int batch, int hq, int hkv,
                                    int n_cols, int k, int32_t* packed_slots, int64_t out_stride,
@@ -49,18 +50,19 @@ struct AttnParams {
   int64_t slot_table_stride;
   const int32_t* req_rows;
   const int32_t* seq_lens;
-  float* mid_o;
-  float* mid_lse;
-  int64_t mo_sb, mo_sh, mo_ss;  // mid_o element strides (batch, head, split)
-  int64_t ml_sb, ml_sh;         // mid_lse element strides (batch, head)
   void* out;
   int64_t out_stride_b;
   float* attn_score;
   int64_t score_stride;
-  int batch, hq, hkv, split_tokens, num_splits;
-  int32_t* tickets;
+  int batch, hq, hkv, max_len;
+  float* ws_o;       // [2*max_ctas][hq/head_groups][128] fp32 partial outputs
+  float* ws_lse;     // [2*max_ctas][hq/head_groups]
+  int32_t* tickets;  // [batch*head_groups] zeroed
+  int max_ctas;      // CTAs the workspace was sized for
+  int stages;        // filled by the launcher
   float sm_scale;
 };
+int attn_auto_heads_per_cta(int hkv);
 int launch_sparse_decode_attn(const AttnParams& p, int heads_per_cta, cudaStream_t stream);
 
 // h2o.cu

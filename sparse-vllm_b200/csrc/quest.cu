@@ -97,22 +97,31 @@ struct SelectSmem {
   int sel_slot[kMaxPrevBudget + 1];
 };
 
+constexpr uint32_t kNegInfKey = 0x007fu;  // order key of bf16 -inf (0xff80)
 // bf16 bit pattern -> 16-bit key that orders like the float value.
 __device__ __forceinline__ uint32_t bf16_order_key(uint32_t bits) {
   return (bits & 0x8000u) ? (~bits & 0xffffu) : (bits | 0x8000u);
 }
 
+// Barrier over the first NTHR threads of the CTA (barrier 0 = __syncthreads when NTHR is the
+// whole block; the fused scoring kernel keeps its producer warp out with barrier 1).
+template <int BAR, int NTHR>
+__device__ __forceinline__ void group_sync() {
+  asm volatile("bar.sync %0, %1;" ::"n"(BAR), "n"(NTHR) : "memory");
+}
+
+template <int BAR, int NTHR>
 __device__ __forceinline__ int block_exclusive_scan(int v, int* warp_scan) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = NTHR >> 5;
   int inc = v;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const int n = __shfl_up_sync(0xffffffffu, inc, o);
     if (lane >= o) inc += n;
   }
-  __syncthreads();  // warp_scan may still be read from a previous call
+  group_sync<BAR, NTHR>();  // warp_scan may still be read from a previous call
   if (lane == 31) warp_scan[warp] = inc;
-  __syncthreads();
+  group_sync<BAR, NTHR>();
   if (warp == 0) {
     const int w = lane < nwarps ? warp_scan[lane] : 0;
     int winc = w;
@@ -123,7 +132,7 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* warp_scan) {
     }
     warp_scan[lane] = winc - w;  // exclusive prefix of the warp totals
   }
-  __syncthreads();
+  group_sync<BAR, NTHR>();
   return warp_scan[warp] + inc - v;
 }
 
@@ -165,55 +174,57 @@ __device__ __forceinline__ void find_kth_bin(const int* hist, int k, int* bcast)
 }
 
 // scores_row: bf16 bits, 16-byte aligned, readable up to round_up(n_cols, 8).
-__device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, int n_cols, int k,
+// Columns >= n_valid count as -inf whatever the buffer holds (quest.py:1883-1885).
+template <int BAR, int NTHR>
+__device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, int n_cols, int n_valid, int k,
                                       const int32_t* __restrict__ pt_row, int ctx,
                                       int32_t* __restrict__ out_row, int32_t* __restrict__ len_out,
                                       int32_t* __restrict__ sel_pages_out, SelectSmem& sm) {
-  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int tid = threadIdx.x, nthr = NTHR;
   const int nvec = (n_cols + 7) >> 3;
   const uint4* vrow = reinterpret_cast<const uint4*>(scores_row);
 
   // ---- pass 1: histogram of the high key byte
   for (int i = tid; i < 256; i += nthr) sm.hist[i] = 0;
-  __syncthreads();
+  group_sync<BAR, NTHR>();
   for (int v = tid; v < nvec; v += nthr) {
     const uint4 x = __ldcg(vrow + v);
     const uint32_t w[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       if (v * 8 + i < n_cols) {
-        const uint32_t key = bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu);
+        const uint32_t key = v * 8 + i < n_valid ? bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu) : kNegInfKey;
         atomicAdd(&sm.hist[key >> 8], 1);
       }
     }
   }
-  __syncthreads();
+  group_sync<BAR, NTHR>();
   if (tid < 32) find_kth_bin(sm.hist, k, sm.bcast);
-  __syncthreads();
+  group_sync<BAR, NTHR>();
   const int bin1 = sm.bcast[0];
   const int k1 = k - sm.bcast[1];
-  __syncthreads();
+  group_sync<BAR, NTHR>();
 
   // ---- pass 2: histogram of the low byte inside bin1
   for (int i = tid; i < 256; i += nthr) sm.hist[i] = 0;
-  __syncthreads();
+  group_sync<BAR, NTHR>();
   for (int v = tid; v < nvec; v += nthr) {
     const uint4 x = __ldcg(vrow + v);
     const uint32_t w[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       if (v * 8 + i < n_cols) {
-        const uint32_t key = bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu);
+        const uint32_t key = v * 8 + i < n_valid ? bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu) : kNegInfKey;
         if ((int)(key >> 8) == bin1) atomicAdd(&sm.hist[key & 0xff], 1);
       }
     }
   }
-  __syncthreads();
+  group_sync<BAR, NTHR>();
   if (tid < 32) find_kth_bin(sm.hist, k1, sm.bcast);
-  __syncthreads();
+  group_sync<BAR, NTHR>();
   const uint32_t thresh = ((uint32_t)bin1 << 8) | (uint32_t)sm.bcast[0];
   const int need_eq = k1 - sm.bcast[1];  // how many keys == thresh to take (lowest index first)
-  __syncthreads();
+  group_sync<BAR, NTHR>();
 
   // ---- pass 3: ordered compaction over contiguous per-thread chunks
   const int vec_per_thr = (nvec + nthr - 1) / nthr;
@@ -225,15 +236,15 @@ __device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, i
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       if (v * 8 + i < n_cols) {
-        const uint32_t key = bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu);
+        const uint32_t key = v * 8 + i < n_valid ? bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu) : kNegInfKey;
         cnt_gt += key > thresh;
         cnt_eq += key == thresh;
       }
     }
   }
-  const int eq_before = block_exclusive_scan(cnt_eq, sm.warp_scan);
+  const int eq_before = block_exclusive_scan<BAR, NTHR>(cnt_eq, sm.warp_scan);
   const int eq_take = max(0, min(cnt_eq, need_eq - eq_before));
-  int pos = block_exclusive_scan(cnt_gt + eq_take, sm.warp_scan);
+  int pos = block_exclusive_scan<BAR, NTHR>(cnt_gt + eq_take, sm.warp_scan);
   int eq_left = eq_take;
   for (int v = v_begin; v < v_end; ++v) {
     const uint4 x = __ldcg(vrow + v);
@@ -242,7 +253,7 @@ __device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, i
     for (int i = 0; i < 8; ++i) {
       const int col = v * 8 + i;
       if (col < n_cols) {
-        const uint32_t key = bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu);
+        const uint32_t key = v * 8 + i < n_valid ? bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu) : kNegInfKey;
         bool take = key > thresh;
         if (key == thresh && eq_left > 0) {
           take = true;
@@ -255,13 +266,13 @@ __device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, i
   // last page (quest.py:1888-1889: safe_num_pages - 1)
   const int num_pages = (ctx + kPage - 1) / kPage;
   if (tid == 0) sm.sel[k] = max(num_pages, 1) - 1;
-  __syncthreads();
+  group_sync<BAR, NTHR>();
   for (int j = tid; j <= k; j += nthr) {
     const int page = sm.sel[j];
     sm.sel_slot[j] = pt_row[page];
     if (sel_pages_out) sel_pages_out[j] = page;
   }
-  __syncthreads();
+  group_sync<BAR, NTHR>();
   // packed token slots: (k+1)*16 int32 = (k+1)*4 int4
   int4* out4 = reinterpret_cast<int4*>(out_row);
   for (int idx = tid; idx < (k + 1) * 4; idx += nthr) {
@@ -269,7 +280,7 @@ __device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, i
     out4[idx] = make_int4(base, base + 1, base + 2, base + 3);
   }
   if (tid == 0) *len_out = k * kPage + (ctx - (num_pages - 1) * kPage);
-  __syncthreads();
+  group_sync<BAR, NTHR>();
 }
 
 __global__ void __launch_bounds__(256) quest_select_pack_kernel(
@@ -299,172 +310,336 @@ __global__ void __launch_bounds__(256) quest_select_pack_kernel(
     for (int i = (k + 1) * kPage + threadIdx.x; i < out_width; i += blockDim.x)
       out_row[i] = dense_row[i];
   }
-  quest_select_pack_row(scores + (int64_t)b * score_stride, n_cols, k,
-                        page_table + row * pt_stride, ctx, out_row, sparse_lens + b,
-                        selected_pages ? selected_pages + (int64_t)b * (k + 1) : nullptr, sm);
+  const int n_valid = max((ctx + kPage - 1) / kPage, 1) - 1;
+  quest_select_pack_row<0, 256>(scores + (int64_t)b * score_stride, n_cols, min(n_valid, n_cols), k,
+                                page_table + row * pt_stride, ctx, out_row, sparse_lens + b,
+                                selected_pages ? selected_pages + (int64_t)b * (k + 1) : nullptr, sm);
 }
 
 // =========================================================================
-// Page scoring.  One warp scores a tile of 16 logical pages for every local KV
-// head; A = page bounds (16 pages x 16 k), B = q+^T / q-^T (16 k x 8 heads).
-// The contraction index is permuted so each lane feeds two MMAs from ONE
-// 16-byte global load of a bounds row ("k-slot permutation").
+// Page scoring (+ fused top-k / packing).
+//
+// Stream-K over page tiles: a "unit" is 16 consecutive logical pages of one batch
+// row; only valid pages (p < ceil(ctx/16) - 1) form units.  The launch's units are
+// cut into one equal contiguous range per persistent CTA.  Warps 8-9 (producers)
+// resolve 16 page slots through the page table and copy each page's bounds record
+// ([2][Hkv][128] = Hkv*512 contiguous bytes) with 16-byte LDGSTS, a warp per 512 B,
+// into a ring of S stages (130-200 KB in flight per SM) whose mbarriers complete
+// when the copies land.  Warps 0-7
+// (consumers) take units round-robin; per unit and KV head:
+//   A = bounds rows (16 pages x 128, ldmatrix), B = q+ / q- (128 x 8 heads)
+//   score = bf16(bf16(A_max.q+) + bf16(A_min.q-)), then max over all local heads.
+// When the last contributor of a row finishes (arrival ticket), its consumer
+// warps run the top-k selection and slot packing for that row in the same launch.
 // =========================================================================
-constexpr int kScoreWarps = 4;
-constexpr int kScorePagesPerCta = kScoreWarps * 16;
+constexpr int kScoreConsumerWarps = 8;
+constexpr int kScoreConsumerThreads = kScoreConsumerWarps * 32;
+constexpr int kScoreProducerWarps = 2;
+constexpr int kScoreThreads = kScoreConsumerThreads + kScoreProducerWarps * 32;
+constexpr int kScoreMaxSmem = 227 * 1024;
 
-template <bool FUSED_SELECT>
-__global__ void __launch_bounds__(kScoreWarps * 32, 4) quest_page_score_kernel(
-    const __nv_bfloat16* __restrict__ q, int64_t q_stride_b,
-    const __nv_bfloat16* __restrict__ bounds, const int32_t* __restrict__ page_table,
-    int64_t pt_stride, const int32_t* __restrict__ req_rows,
-    const int32_t* __restrict__ context_lens, uint16_t* __restrict__ scores, int64_t score_stride,
-    int hq, int hkv, int n_cols,
-    // fused select only:
-    int k, int32_t* __restrict__ packed_slots, int64_t out_stride, int32_t* __restrict__ sparse_lens,
-    int32_t* __restrict__ selected_pages, int32_t* __restrict__ tickets) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  // sq[2][hq][128] bf16, 16-byte chunks XOR-swizzled by (head & 1) << 2
-  uint4* sq_pos = reinterpret_cast<uint4*>(smem_raw);
-  uint4* sq_neg = sq_pos + hq * 16;
+struct ScoreParams {
+  const __nv_bfloat16* q;
+  int64_t q_stride_b;
+  const __nv_bfloat16* bounds;
+  int64_t num_pages;
+  const int32_t* page_table;
+  int64_t pt_stride;
+  const int32_t* req_rows;
+  const int32_t* context_lens;
+  uint16_t* scores;
+  int64_t score_stride;
+  int batch, hq, hkv, n_cols, stages;
+  int consumers;  // consumer warps that take units; divides `stages` (see the kernel)
+  // fused select only
+  int k;
+  int32_t* packed_slots;
+  int64_t out_stride;
+  int32_t* sparse_lens;
+  int32_t* selected_pages;
+  int32_t* tickets;
+};
 
-  const int b = blockIdx.y;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int g = lane >> 2, t = lane & 3;
+struct ScoreSmemLayout {
+  int ring_off, q_off, bar_off, valid_off, prefix_off, select_off, total;
+};
+
+__host__ __device__ inline int score_rec_stride(int hkv) { return hkv * 2 * kRowBytes + 16; }
+
+__host__ __device__ inline ScoreSmemLayout score_smem_layout(int stages, int hq, int hkv, int batch,
+                                                             bool fused) {
+  ScoreSmemLayout L;
+  int off = 0;
+  L.ring_off = off;   off += stages * kPage * score_rec_stride(hkv);
+  L.q_off = off;      off += 2 * hq * kRowBytes;
+  L.bar_off = off;    off += 2 * stages * 8;
+  L.valid_off = off;  off += ((stages * 4 + 15) / 16) * 16;
+  L.prefix_off = off; off += ((batch + 1) * 4 + 15) / 16 * 16;
+  L.select_off = off; off += fused ? (int)((sizeof(SelectSmem) + 15) / 16 * 16) : 0;
+  L.total = off;
+  return L;
+}
+
+__device__ __forceinline__ void score_consumer_sync() { group_sync<1, kScoreConsumerThreads>(); }
+
+__device__ __forceinline__ int score_unit_owner(int64_t u, int64_t U, int64_t G) {
+  return (int)(((u + 1) * G + U - 1) / U - 1);
+}
+
+template <int NT, bool FUSED_SELECT>
+__global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(ScoreParams p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int S = p.stages, hq = p.hq, hkv = p.hkv, B = p.batch;
   const int gsz = hq / hkv;
-  const int ntiles = (gsz + 7) >> 3;
+  const int rec_stride = score_rec_stride(hkv);
+  const int rec_bytes = hkv * 2 * kRowBytes;
+  const int stage_bytes = kPage * rec_stride;
+  const ScoreSmemLayout L = score_smem_layout(S, hq, hkv, B, FUSED_SELECT);
+  unsigned char* ring = smem + L.ring_off;
+  // sq[sign][head][kk][t] : uint2 {b0, b1} B fragments, kk XOR-swizzled by head
+  uint32_t* sq = reinterpret_cast<uint32_t*>(smem + L.q_off);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.bar_off);
+  uint64_t* empty_bar = full_bar + S;
+  uint32_t* sValid = reinterpret_cast<uint32_t*>(smem + L.valid_off);
+  int* sPrefix = reinterpret_cast<int*>(smem + L.prefix_off);
+  __shared__ int s_flag;
 
-  // ---- stage q+ / q- (clamp_min(0) / clamp_max(0), quest.py:1796-1797)
-  {
-    const uint4* qrow = reinterpret_cast<const uint4*>(q + (int64_t)b * q_stride_b);
-    for (int c = tid; c < hq * 16; c += blockDim.x) {
-      const int head = c >> 4, chunk = c & 15;
-      const uint4 x = qrow[c];
-      uint4 p, n;
-      const uint32_t w[4] = {x.x, x.y, x.z, x.w};
-      uint32_t pw[4], nw[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const uint32_t lo = w[i] & 0xffffu, hi = w[i] >> 16;
-        const uint32_t lo_neg = (lo & 0x8000u) ? lo : 0u, lo_pos = (lo & 0x8000u) ? 0u : lo;
-        const uint32_t hi_neg = (hi & 0x8000u) ? hi : 0u, hi_pos = (hi & 0x8000u) ? 0u : hi;
-        pw[i] = lo_pos | (hi_pos << 16);
-        nw[i] = lo_neg | (hi_neg << 16);
-      }
-      p = make_uint4(pw[0], pw[1], pw[2], pw[3]);
-      n = make_uint4(nw[0], nw[1], nw[2], nw[3]);
-      const int sw = head * 16 + (chunk ^ ((head & 1) << 2));
-      sq_pos[sw] = p;
-      sq_neg[sw] = n;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  // ---- setup
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(&full_bar[s], 33);  // 32 async copy arrivals + the producer's release
+      mbar_init(&empty_bar[s], 1);
     }
+    mbar_fence_init();
+  }
+  if (warp == 0) {  // units per row -> exclusive prefix
+    int carry = 0;
+    for (int base = 0; base < B; base += 32) {
+      const int b = base + lane;
+      int n = 0;
+      if (b < B) {
+        const int ctx = p.context_lens[b];
+        const int nv = min(max((ctx + kPage - 1) / kPage, 1) - 1, p.n_cols);
+        n = (nv + 15) >> 4;
+      }
+      int inc = n;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+      }
+      if (b < B) sPrefix[b] = carry + inc - n;
+      carry += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) sPrefix[B] = carry;
+  }
+  // columns no unit covers are -inf (quest.py:1883-1885)
+  for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    const int ctx = p.context_lens[b];
+    const int nv = min(max((ctx + kPage - 1) / kPage, 1) - 1, p.n_cols);
+    uint16_t* srow = p.scores + (int64_t)b * p.score_stride;
+    for (int c = ((nv + 15) & ~15) + tid; c < p.n_cols; c += kScoreThreads) srow[c] = 0xff80u;
   }
   __syncthreads();
 
-  const int ctx = context_lens[b];
-  const int n_valid = max((ctx + kPage - 1) / kPage, 1) - 1;  // valid_prev, quest.py:1883-1884
-  const int64_t row = req_rows[b];
-  const int p0 = blockIdx.x * kScorePagesPerCta + warp * 16 + g, p1 = p0 + 8;
-  const bool v0 = p0 < n_valid && p0 < n_cols, v1 = p1 < n_valid && p1 < n_cols;
-  float best0 = -INFINITY, best1 = -INFINITY;
+  const int64_t U = sPrefix[B];
+  const int64_t Gn = U < (int64_t)gridDim.x ? U : (int64_t)gridDim.x;
+  const int u0 = Gn > 0 && (int64_t)blockIdx.x < Gn ? (int)(U * blockIdx.x / Gn) : 0;
+  const int u1 = Gn > 0 && (int64_t)blockIdx.x < Gn ? (int)(U * (blockIdx.x + 1) / Gn) : 0;
+  int r_first = 0;
+  if (u1 > u0) {
+    int lo = 0, hi = B;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (sPrefix[mid] <= u0) lo = mid; else hi = mid;
+    }
+    r_first = lo;
+  }
 
-  if (__any_sync(0xffffffffu, v0 || v1)) {
-    const int32_t* pt_row = page_table + row * pt_stride;
-    const int s0 = v0 ? max(pt_row[p0], 0) : 0;
-    const int s1 = v1 ? max(pt_row[p1], 0) : 0;
-    const int64_t page_elems = (int64_t)2 * hkv * kHeadDim;
-    const __nv_bfloat16* base0 = bounds + s0 * page_elems + t * 8;
-    const __nv_bfloat16* base1 = bounds + s1 * page_elems + t * 8;
-    const int64_t min_off = (int64_t)hkv * kHeadDim;
-    const uint4 zero4 = make_uint4(0, 0, 0, 0);
-
-    for (int h = 0; h < hkv; ++h) {
-      uint4 amax0[4], amax1[4], amin0[4], amin1[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int off = h * kHeadDim + j * 32;
-        amax0[j] = v0 ? ldg_stream_16(base0 + off) : zero4;
-        amin0[j] = v0 ? ldg_stream_16(base0 + min_off + off) : zero4;
-        amax1[j] = v1 ? ldg_stream_16(base1 + off) : zero4;
-        amin1[j] = v1 ? ldg_stream_16(base1 + min_off + off) : zero4;
+  if (warp >= kScoreConsumerWarps) {
+    // ============================================================== producers
+    const int n_units = u1 - u0;
+    const int pw = warp - kScoreConsumerWarps;
+    const int pg_lane = lane & 15;
+    int r_pf = r_first;
+    auto fetch = [&](int i) -> int {  // raw physical page of logical page pg_lane in local unit i
+      if (i >= n_units) return -1;
+      const int u = u0 + i;
+      while (sPrefix[r_pf + 1] <= u) ++r_pf;
+      const int ctx = p.context_lens[r_pf];
+      const int nv = min(max((ctx + kPage - 1) / kPage, 1) - 1, p.n_cols);
+      const int col = (u - sPrefix[r_pf]) * 16 + pg_lane;
+      if (col >= nv) return -1;
+      return __ldg(p.page_table + (int64_t)p.req_rows[r_pf] * p.pt_stride + col);
+    };
+    const int64_t rec_elems = rec_bytes / 2;
+    int pa = fetch(pw), pb = fetch(pw + kScoreProducerWarps);
+    for (int i = pw; i < n_units; i += kScoreProducerWarps) {
+      const int pc = fetch(i + 2 * kScoreProducerWarps);
+      const int my = (pa >= 0 && pa < p.num_pages) ? pa : -1;
+      const uint32_t mask = __ballot_sync(0xffffffffu, my >= 0) & 0xffffu;
+      const int s = i % S;
+      mbar_wait(&empty_bar[s], ((i / S) & 1) ^ 1);
+      const uint32_t dst0 = smem_u32(ring + s * stage_bytes) + lane * 16;
+#pragma unroll 4
+      for (int pg = 0; pg < kPage; ++pg) {
+        const int page = __shfl_sync(0xffffffffu, my, pg);
+        const int nbytes = page >= 0 ? 16 : 0;
+        const __nv_bfloat16* src = p.bounds + (int64_t)max(page, 0) * rec_elems + lane * 8;
+        const uint32_t dst = dst0 + pg * rec_stride;
+        for (int c = 0; c < hkv; ++c) cp_async_16(dst + c * 512, src + c * 256, nbytes);
       }
-      for (int nt = 0; nt < ntiles; ++nt) {
-        const int hg = nt * 8 + g;  // head (within the group) this lane feeds as B column
-        const bool hv = hg < gsz;
-        const int qh = h * gsz + (hv ? hg : 0);
-        float cp[4] = {0.f, 0.f, 0.f, 0.f}, cn[4] = {0.f, 0.f, 0.f, 0.f};
+      if (lane == 0) sValid[s] = mask;
+      cp_async_mbar_arrive(&full_bar[s]);
+      if (lane == 0) mbar_arrive(&full_bar[s]);  // release: publishes sValid
+      pa = pb;
+      pb = pc;
+    }
+    return;
+  }
+
+  // ================================================================ consumers
+  const int g = lane >> 2, t = lane & 3;
+  const uint2* sq2 = reinterpret_cast<const uint2*>(sq);
+  const int neg_off = hq * 32;  // uint2 offset of the q- fragments
+  [[maybe_unused]] SelectSmem* sel_sm = reinterpret_cast<SelectSmem*>(smem + L.select_off);
+
+  if constexpr (FUSED_SELECT) {
+    // rows without a single valid previous page never become a unit: select them here
+    for (int b = blockIdx.x; b < B; b += gridDim.x) {
+      if (sPrefix[b + 1] != sPrefix[b]) continue;
+      const int ctx = p.context_lens[b];
+      quest_select_pack_row<1, kScoreConsumerThreads>(
+          p.scores + (int64_t)b * p.score_stride, p.n_cols, 0, p.k,
+          p.page_table + (int64_t)p.req_rows[b] * p.pt_stride, ctx,
+          p.packed_slots + (int64_t)b * p.out_stride, p.sparse_lens + b,
+          p.selected_pages ? p.selected_pages + (int64_t)b * (p.k + 1) : nullptr, *sel_sm);
+    }
+  }
+
+  int r = r_first, i = 0;
+  while (u0 + i < u1) {
+    while (sPrefix[r + 1] <= u0 + i) ++r;
+    const int b = r;
+    const int row_begin = sPrefix[r], row_end = sPrefix[r + 1];
+    const int seg_begin = u0 + i, seg_end = min(u1, row_end);
+    const int n = seg_end - seg_begin;
+    const int ctx = p.context_lens[b];
+    const int nv = min(max((ctx + kPage - 1) / kPage, 1) - 1, p.n_cols);
+
+    // ---- q+ / q- (clamp_min(0) / clamp_max(0), quest.py:1796-1797) in B-fragment order
+    {
+      const uint4* qrow = reinterpret_cast<const uint4*>(p.q + (int64_t)b * p.q_stride_b);
+      for (int c = tid; c < hq * 16; c += kScoreConsumerThreads) {
+        const int head = c >> 4, chunk = c & 15;
+        const uint4 x = qrow[c];
+        const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+        const int kk = chunk >> 1, hf = chunk & 1;
+        const int base = ((head * 8 + (kk ^ (head & 7))) * 4) * 2 + hf;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int sw = qh * 16 + ((j * 4 + t) ^ ((qh & 1) << 2));
-          const uint4 bp = hv ? sq_pos[sw] : zero4;
-          const uint4 bn = hv ? sq_neg[sw] : zero4;
-          {
-            const uint32_t a[4] = {amax0[j].x, amax1[j].x, amax0[j].y, amax1[j].y};
-            mma_16816(cp, a, bp.x, bp.y);
-          }
-          {
-            const uint32_t a[4] = {amax0[j].z, amax1[j].z, amax0[j].w, amax1[j].w};
-            mma_16816(cp, a, bp.z, bp.w);
-          }
-          {
-            const uint32_t a[4] = {amin0[j].x, amin1[j].x, amin0[j].y, amin1[j].y};
-            mma_16816(cn, a, bn.x, bn.y);
-          }
-          {
-            const uint32_t a[4] = {amin0[j].z, amin1[j].z, amin0[j].w, amin1[j].w};
-            mma_16816(cn, a, bn.z, bn.w);
+        for (int tt = 0; tt < 4; ++tt) {
+          const uint32_t lo = w[tt] & 0xffffu, hi = w[tt] >> 16;
+          const uint32_t lo_neg = (lo & 0x8000u) ? lo : 0u, lo_pos = (lo & 0x8000u) ? 0u : lo;
+          const uint32_t hi_neg = (hi & 0x8000u) ? hi : 0u, hi_pos = (hi & 0x8000u) ? 0u : hi;
+          sq[base + tt * 2] = lo_pos | (hi_pos << 16);
+          sq[neg_off * 2 + base + tt * 2] = lo_neg | (hi_neg << 16);
+        }
+      }
+    }
+    score_consumer_sync();
+
+    uint16_t* srow = p.scores + (int64_t)b * p.score_stride;
+    // Unit j goes to warp j % NW, and NW divides S: a stage is always drained by the same warp, so
+    // the phase a warp waits for is never more than one ahead of the barrier (parity waits cannot
+    // tell a phase from the one two before it).
+    const int NW = p.consumers;
+    for (int j = i + ((warp - i % NW + NW) % NW); warp < NW && j < i + n; j += NW) {
+      const int s = j % S;
+      mbar_wait(&full_bar[s], (j / S) & 1);
+      const uint32_t mask = sValid[s];
+      const uint32_t abase = smem_u32(ring + s * stage_bytes) +
+                             ((lane & 7) + ((lane >> 3) & 1) * 8) * rec_stride + (lane >> 4) * 16;
+      float best0 = -INFINITY, best1 = -INFINITY;
+      for (int h = 0; h < hkv; ++h) {
+        float cp[NT][4], cn[NT][4];
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) cp[nt][e] = cn[nt][e] = 0.f;
+        const uint32_t amax_addr = abase + h * kRowBytes;
+        const uint32_t amin_addr = amax_addr + hkv * kRowBytes;
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {
+          uint32_t amax[4], amin[4];
+          ldmatrix_x4(amax, amax_addr + kk * 32);
+          ldmatrix_x4(amin, amin_addr + kk * 32);
+#pragma unroll
+          for (int nt = 0; nt < NT; ++nt) {
+            const int qh = h * gsz + min(nt * 8 + g, gsz - 1);
+            const int fi = (qh * 8 + (kk ^ (qh & 7))) * 4 + t;
+            const uint2 bp = sq2[fi], bn = sq2[neg_off + fi];
+            mma_16816(cp[nt], amax, bp.x, bp.y);
+            mma_16816(cn[nt], amin, bn.x, bn.y);
           }
         }
         // c0:(page g, head 2t) c1:(g, 2t+1) c2:(g+8, 2t) c3:(g+8, 2t+1)
-        const int col0 = nt * 8 + 2 * t;
-        float s[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) s[i] = round_bf16(round_bf16(cp[i]) + round_bf16(cn[i]));
-        if (col0 < gsz) {
-          best0 = fmaxf(best0, s[0]);
-          best1 = fmaxf(best1, s[2]);
+        for (int nt = 0; nt < NT; ++nt) {
+          float sc[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) sc[e] = round_bf16(round_bf16(cp[nt][e]) + round_bf16(cn[nt][e]));
+          const int col0 = nt * 8 + 2 * t;
+          if (col0 < gsz) best0 = fmaxf(best0, sc[0]), best1 = fmaxf(best1, sc[2]);
+          if (col0 + 1 < gsz) best0 = fmaxf(best0, sc[1]), best1 = fmaxf(best1, sc[3]);
         }
-        if (col0 + 1 < gsz) {
-          best0 = fmaxf(best0, s[1]);
-          best1 = fmaxf(best1, s[3]);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_bar[s]);
+      best0 = fmaxf(best0, __shfl_xor_sync(0xffffffffu, best0, 1));
+      best0 = fmaxf(best0, __shfl_xor_sync(0xffffffffu, best0, 2));
+      best1 = fmaxf(best1, __shfl_xor_sync(0xffffffffu, best1, 1));
+      best1 = fmaxf(best1, __shfl_xor_sync(0xffffffffu, best1, 2));
+      if (t == 0) {
+        const int p0 = (seg_begin + (j - i) - row_begin) * 16 + g, p1 = p0 + 8;
+        if (p0 < p.n_cols) {
+          __nv_bfloat16 v = __float2bfloat16_rn(best0);
+          srow[p0] = ((mask >> g) & 1u) ? *reinterpret_cast<uint16_t*>(&v) : (uint16_t)0xff80u;
+        }
+        if (p1 < p.n_cols) {
+          __nv_bfloat16 v = __float2bfloat16_rn(best1);
+          srow[p1] = ((mask >> (g + 8)) & 1u) ? *reinterpret_cast<uint16_t*>(&v) : (uint16_t)0xff80u;
         }
       }
     }
-    best0 = fmaxf(best0, __shfl_xor_sync(0xffffffffu, best0, 1));
-    best0 = fmaxf(best0, __shfl_xor_sync(0xffffffffu, best0, 2));
-    best1 = fmaxf(best1, __shfl_xor_sync(0xffffffffu, best1, 1));
-    best1 = fmaxf(best1, __shfl_xor_sync(0xffffffffu, best1, 2));
-  }
-  if (t == 0) {
-    uint16_t* srow = scores + (int64_t)b * score_stride;
-    const uint16_t ninf = 0xff80u;
-    if (p0 < n_cols) {
-      __nv_bfloat16 v = __float2bfloat16_rn(best0);
-      srow[p0] = v0 ? *reinterpret_cast<uint16_t*>(&v) : ninf;
-    }
-    if (p1 < n_cols) {
-      __nv_bfloat16 v = __float2bfloat16_rn(best1);
-      srow[p1] = v1 ? *reinterpret_cast<uint16_t*>(&v) : ninf;
-    }
-  }
 
-  if constexpr (FUSED_SELECT) {
-    __shared__ int s_last;
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) {
-      const int ticket = atomicAdd(&tickets[b], 1);
-      s_last = (ticket == (int)gridDim.x - 1);
-      if (s_last) tickets[b] = 0;  // leave the scratch zeroed for the next launch / graph replay
-    }
-    __syncthreads();
-    if (s_last) {
+    if constexpr (FUSED_SELECT) {
+      const bool complete = seg_begin == row_begin && seg_end == row_end;
       __threadfence();
-      __shared__ SelectSmem sm;
-      quest_select_pack_row(scores + (int64_t)b * score_stride, n_cols, k,
-                            page_table + row * pt_stride, ctx,
-                            packed_slots + (int64_t)b * out_stride, sparse_lens + b,
-                            selected_pages ? selected_pages + (int64_t)b * (k + 1) : nullptr, sm);
+      score_consumer_sync();
+      if (tid == 0) {
+        int last = 1;
+        if (!complete) {
+          const int c_first = score_unit_owner(row_begin, U, Gn);
+          const int c_last = score_unit_owner(row_end - 1, U, Gn);
+          const int ticket = atomicAdd(&p.tickets[b], 1);
+          last = (ticket == c_last - c_first);
+          if (last) p.tickets[b] = 0;  // scratch stays zeroed for the next launch / replay
+        }
+        s_flag = last;
+      }
+      score_consumer_sync();
+      if (s_flag) {
+        __threadfence();
+        quest_select_pack_row<1, kScoreConsumerThreads>(
+            srow, p.n_cols, nv, p.k, p.page_table + (int64_t)p.req_rows[b] * p.pt_stride, ctx,
+            p.packed_slots + (int64_t)b * p.out_stride, p.sparse_lens + b,
+            p.selected_pages ? p.selected_pages + (int64_t)b * (p.k + 1) : nullptr, *sel_sm);
+      }
     }
+    score_consumer_sync();  // sq / s_flag are reused by the next segment
+    i += n;
   }
 }
 
@@ -496,25 +671,6 @@ int launch_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
   return check_launch("quest_decode_page_complete");
 }
 
-int launch_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds,
-                            const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
-                            const int32_t* context_lens, void* scores, int64_t score_stride,
-                            int batch, int hq, int hkv, int n_cols, cudaStream_t stream) {
-  if (batch <= 0 || n_cols <= 0) return 0;
-  dim3 grid((n_cols + kScorePagesPerCta - 1) / kScorePagesPerCta, batch);
-  const size_t smem = (size_t)2 * hq * kRowBytes;
-  auto kern = quest_page_score_kernel<false>;
-  if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return cuda_error("quest_page_score smem attr", e);
-  }
-  kern<<<grid, kScoreWarps * 32, smem, stream>>>(
-      (const __nv_bfloat16*)q, q_stride_b, (const __nv_bfloat16*)bounds, page_table, pt_stride,
-      req_rows, context_lens, (uint16_t*)scores, score_stride, hq, hkv, n_cols, 0, nullptr, 0,
-      nullptr, nullptr, nullptr);
-  return check_launch("quest_page_score");
-}
-
 int launch_quest_select_pack(const void* scores, int64_t score_stride, int n_cols,
                              const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
                              const int32_t* context_lens, int batch, int k, int32_t* packed_slots,
@@ -529,26 +685,80 @@ int launch_quest_select_pack(const void* scores, int64_t score_stride, int n_col
   return check_launch("quest_select_pack");
 }
 
+template <int NT, bool FUSED>
+static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
+  const int fixed = score_smem_layout(0, p.hq, p.hkv, p.batch, FUSED).total + 256;  // + static smem
+  const int stage_bytes = kPage * score_rec_stride(p.hkv);
+  int stages = (kScoreMaxSmem - fixed) / (stage_bytes + 20);
+  if (stages > 24) stages = 24;
+  if (stages < 2) {
+    set_error("quest_page_score: %d q heads / %d kv heads / batch %d leave no shared memory for the bounds ring",
+              p.hq, p.hkv, p.batch);
+    return 1;
+  }
+  // (stages, consumer warps) with consumers | stages: prefer more consumers, then more stages
+  int best_s = stages, best_c = 1;
+  for (int s2 = stages; s2 >= 2 && s2 >= stages - 3; --s2) {
+    int c = 1;
+    for (int d = kScoreConsumerWarps; d >= 1; --d)
+      if (s2 % d == 0) { c = d; break; }
+    if (c > best_c) best_c = c, best_s = s2;
+  }
+  stages = best_s;
+  p.stages = stages;
+  p.consumers = best_c;
+  const size_t smem = score_smem_layout(stages, p.hq, p.hkv, p.batch, FUSED).total;
+  auto kern = quest_page_score_kernel<NT, FUSED>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return cuda_error("quest_page_score smem attr", e);
+  const int64_t max_units = (int64_t)p.batch * ((p.n_cols + 15) / 16);
+  int grid = max_ctas();
+  if ((int64_t)grid > max_units) grid = (int)max_units;
+  if (FUSED && grid > p.batch && max_units < p.batch) grid = p.batch;
+  if (grid < 1) grid = 1;
+  kern<<<grid, kScoreThreads, smem, stream>>>(p);
+  return check_launch(FUSED ? "quest_score_select_pack" : "quest_page_score");
+}
+
+static ScoreParams make_score_params(const void* q, int64_t q_stride_b, const void* bounds,
+                                     int64_t num_pages, const int32_t* page_table, int64_t pt_stride,
+                                     const int32_t* req_rows, const int32_t* context_lens,
+                                     void* scores, int64_t score_stride, int batch, int hq, int hkv,
+                                     int n_cols) {
+  ScoreParams p{};
+  p.q = (const __nv_bfloat16*)q; p.q_stride_b = q_stride_b;
+  p.bounds = (const __nv_bfloat16*)bounds; p.num_pages = num_pages;
+  p.page_table = page_table; p.pt_stride = pt_stride; p.req_rows = req_rows;
+  p.context_lens = context_lens; p.scores = (uint16_t*)scores; p.score_stride = score_stride;
+  p.batch = batch; p.hq = hq; p.hkv = hkv; p.n_cols = n_cols;
+  return p;
+}
+
+int launch_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds, int64_t num_pages,
+                            const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
+                            const int32_t* context_lens, void* scores, int64_t score_stride,
+                            int batch, int hq, int hkv, int n_cols, cudaStream_t stream) {
+  if (batch <= 0 || n_cols <= 0) return 0;
+  ScoreParams p = make_score_params(q, q_stride_b, bounds, num_pages, page_table, pt_stride, req_rows,
+                                    context_lens, scores, score_stride, batch, hq, hkv, n_cols);
+  return hq / hkv <= 8 ? launch_score_variant<1, false>(p, stream)
+                       : launch_score_variant<2, false>(p, stream);
+}
+
 int launch_quest_score_select_pack(const void* q, int64_t q_stride_b, const void* bounds,
-                                   const int32_t* page_table, int64_t pt_stride,
+                                   int64_t num_pages, const int32_t* page_table, int64_t pt_stride,
                                    const int32_t* req_rows, const int32_t* context_lens,
                                    void* scores, int64_t score_stride, int batch, int hq, int hkv,
                                    int n_cols, int k, int32_t* packed_slots, int64_t out_stride,
                                    int32_t* sparse_lens, int32_t* selected_pages, int32_t* tickets,
                                    cudaStream_t stream) {
   if (batch <= 0 || n_cols <= 0) return 0;
-  dim3 grid((n_cols + kScorePagesPerCta - 1) / kScorePagesPerCta, batch);
-  const size_t smem = (size_t)2 * hq * kRowBytes;
-  auto kern = quest_page_score_kernel<true>;
-  if (smem + sizeof(SelectSmem) > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return cuda_error("quest_score_select_pack smem attr", e);
-  }
-  kern<<<grid, kScoreWarps * 32, smem, stream>>>(
-      (const __nv_bfloat16*)q, q_stride_b, (const __nv_bfloat16*)bounds, page_table, pt_stride,
-      req_rows, context_lens, (uint16_t*)scores, score_stride, hq, hkv, n_cols, k, packed_slots,
-      out_stride, sparse_lens, selected_pages, tickets);
-  return check_launch("quest_score_select_pack");
+  ScoreParams p = make_score_params(q, q_stride_b, bounds, num_pages, page_table, pt_stride, req_rows,
+                                    context_lens, scores, score_stride, batch, hq, hkv, n_cols);
+  p.k = k; p.packed_slots = packed_slots; p.out_stride = out_stride; p.sparse_lens = sparse_lens;
+  p.selected_pages = selected_pages; p.tickets = tickets;
+  return hq / hkv <= 8 ? launch_score_variant<1, true>(p, stream)
+                       : launch_score_variant<2, true>(p, stream);
 }
 
 }  // namespace svb200

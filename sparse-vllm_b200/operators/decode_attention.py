@@ -74,34 +74,18 @@ class B200SparseDecodeProvider:
             self._sm_count = ops.sm_count()
         return self._sm_count
 
-    def launch_config(self, *, batch: int, num_kv_heads: int, max_len: int, block_seq: int = 256,
-                      max_splits: int | None = None) -> tuple[int, int, int]:
-        """(split_tokens, num_splits, heads_per_cta) for one launch.
+    def heads_per_cta(self, num_kv_heads: int) -> int:
+        """KV heads staged together by one CTA: as many as divide the local head count (a token's K row is
+        then HPC*256 contiguous bytes).  Load balance does not depend on it: the kernel cuts the launch's
+        16-token pages into one equal range per SM (stream-K), whatever the batch and row lengths are."""
+        for hpc in (8, 4, 2):
+            if num_kv_heads % hpc == 0:
+                return hpc
+        return 1
 
-        Work items are (row, split, head group); persistent CTAs walk them round-robin, so the policy
-        looks for >= ~4 items per SM (tail effect < 1/4 item) while keeping as many KV heads per CTA as
-        that allows (a token's K row is then HPC*256 contiguous bytes)."""
-        max_len = max(int(max_len), 1)
-        block_seq = max(PAGE, (int(block_seq) + PAGE - 1) // PAGE * PAGE)
-        cap = (max_len + block_seq - 1) // block_seq
-        if max_splits is not None:
-            cap = max(1, min(cap, int(max_splits)))
-        want = 4 * self.sm_count
-        best = None
-        for hpc in (8, 4, 2, 1):
-            if num_kv_heads % hpc:
-                continue
-            groups = num_kv_heads // hpc
-            splits = min(cap, max(1, -(-want // (batch * groups))))
-            items = batch * groups * splits
-            best = (hpc, splits)
-            if items >= want or hpc == 1:
-                break
-        hpc, splits = best
-        split_tokens = -(-max_len // splits)
-        split_tokens = (split_tokens + PAGE - 1) // PAGE * PAGE
-        splits = (max_len + split_tokens - 1) // split_tokens
-        return split_tokens, splits, hpc
+    def workspace(self, batch: int, num_q_heads: int, num_kv_heads: int, device) -> torch.Tensor:
+        """Zeroed tickets + per-SM partial records (replaces the reference's mid_o / mid_o_logexpsum)."""
+        return ops.attn_workspace(batch, num_q_heads, num_kv_heads, device)
 
     # ---- ops ------------------------------------------------------------------------------
     def _count(self, path: str, key: str = "launches") -> None:
@@ -123,15 +107,11 @@ class B200SparseDecodeProvider:
             self._count("quest_page_score")
             self._count("quest_select_pack_mixed")
 
-    def decode(self, q, k_cache, v_cache, slot_table, req_rows, seq_lens, *, out, mid_o, mid_lse, tickets,
-               max_len: int, block_seq: int = 256, attn_score=None) -> torch.Tensor:
-        max_splits = None if mid_o is None else int(mid_o.shape[2])
-        split_tokens, num_splits, hpc = self.launch_config(
-            batch=int(q.shape[0]), num_kv_heads=int(k_cache.shape[1]), max_len=max_len, block_seq=block_seq,
-            max_splits=max_splits)
-        ops.sparse_decode_attn(q, k_cache, v_cache, slot_table, req_rows, seq_lens, out=out, mid_o=mid_o,
-                               mid_lse=mid_lse, tickets=tickets, split_tokens=split_tokens, num_splits=num_splits,
-                               attn_score=attn_score, heads_per_cta=hpc)
+    def decode(self, q, k_cache, v_cache, slot_table, req_rows, seq_lens, *, out, workspace, max_len: int,
+               attn_score=None) -> torch.Tensor:
+        ops.sparse_decode_attn(q, k_cache, v_cache, slot_table, req_rows, seq_lens, out=out, workspace=workspace,
+                               max_len=max_len, attn_score=attn_score,
+                               heads_per_cta=self.heads_per_cta(int(k_cache.shape[1])))
         self._count("sparse_decode_attn_score2d" if attn_score is not None else "sparse_decode_attn")
         return out
 

@@ -110,7 +110,8 @@ def quest_page_score(q: torch.Tensor, bounds_layer: torch.Tensor, page_table: to
     require_cuda(scores, "scores", torch.bfloat16)
     lib = _native.load()
     check(lib.svb200_quest_page_score(
-        ptr(q), qs, ptr(bounds_layer), ptr(page_table), _rows_stride(page_table, "page_table"),
+        ptr(q), qs, ptr(bounds_layer), int(bounds_layer.shape[0]), ptr(page_table),
+        _rows_stride(page_table, "page_table"),
         ptr(req_rows), ptr(context_lens), ptr(scores), _rows_stride(scores, "scores"), bsz, hq,
         int(num_kv_heads), int(n_cols), current_stream_ptr(q.device)), "svb200_quest_page_score")
     return scores
@@ -161,26 +162,43 @@ def quest_score_select_pack(q: torch.Tensor, bounds_layer: torch.Tensor, page_ta
         _i32(selected_pages, "selected_pages")
     lib = _native.load()
     check(lib.svb200_quest_score_select_pack(
-        ptr(q), qs, ptr(bounds_layer), ptr(page_table), _rows_stride(page_table, "page_table"),
+        ptr(q), qs, ptr(bounds_layer), int(bounds_layer.shape[0]), ptr(page_table),
+        _rows_stride(page_table, "page_table"),
         ptr(req_rows), ptr(context_lens), ptr(scores), _rows_stride(scores, "scores"), bsz, hq,
         int(num_kv_heads), int(n_cols), int(prev_budget), ptr(packed_slots),
         _rows_stride(packed_slots, "packed_slots"), ptr(sparse_lens), ptr(selected_pages), ptr(tickets),
         current_stream_ptr(q.device)), "svb200_quest_score_select_pack")
 
 
+def set_max_ctas(n: int) -> int:
+    """Cap the persistent kernels' grids at ``n`` CTAs (<= 0: one per SM); returns the previous cap."""
+    return int(_native.load().svb200_set_max_ctas(int(n)))
+
+
 # ----------------------------------------------------------------------------- attention
-def attn_workspace_tickets(batch: int, num_kv_heads: int, device) -> torch.Tensor:
-    """Zeroed int32 arrival tickets (svb200_workspace_bytes); kernels leave them zeroed."""
-    nbytes = int(_native.load().svb200_workspace_bytes(int(batch), int(num_kv_heads)))
-    return torch.zeros((max(nbytes // 4, 1),), dtype=torch.int32, device=device)
+def attn_workspace(batch: int, num_q_heads: int, num_kv_heads: int, device, max_ctas: int | None = None) -> torch.Tensor:
+    """Zeroed scratch of svb200_workspace_bytes (arrival tickets + per-SM fp32 partials).
+
+    Allocate it once per (batch, heads) shape; kernels leave the ticket part zeroed.  ``max_ctas`` sizes it
+    for fewer CTAs than SMs (the launch then uses at most that many; tests use it to vary the decomposition)."""
+    lib = _native.load()
+    nbytes = int(lib.svb200_workspace_bytes(int(batch), int(num_q_heads), int(num_kv_heads)))
+    if nbytes <= 0:
+        raise ValueError(f"svb200_workspace_bytes({batch}, {num_q_heads}, {num_kv_heads}) = {nbytes}.")
+    if max_ctas is not None:
+        sms = int(lib.svb200_sm_count())
+        tickets = (int(batch) * int(num_kv_heads) * 4 + 255) // 256 * 256
+        per_cta = (nbytes - tickets) // sms
+        nbytes = tickets + max(1, min(int(max_ctas), sms)) * per_cta
+    return torch.zeros(((nbytes + 3) // 4,), dtype=torch.int32, device=device)
 
 
 def sparse_decode_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, slot_table: torch.Tensor,
                        req_rows: torch.Tensor, seq_lens: torch.Tensor, *, out: torch.Tensor,
-                       mid_o: torch.Tensor | None, mid_lse: torch.Tensor | None, tickets: torch.Tensor | None,
-                       split_tokens: int, num_splits: int, attn_score: torch.Tensor | None = None,
-                       heads_per_cta: int = 0, sm_scale: float | None = None) -> torch.Tensor:
-    """Split-K sparse paged GQA decode attention with fused combine (svb200_sparse_decode_attn)."""
+                       workspace: torch.Tensor, max_len: int | None = None,
+                       attn_score: torch.Tensor | None = None, heads_per_cta: int = 0,
+                       sm_scale: float | None = None) -> torch.Tensor:
+    """Stream-K sparse paged GQA decode attention with fused combine (svb200_sparse_decode_attn)."""
     bsz, hq, qs = _q(q, "q")
     num_slots, hkv = _kv_layer(k_cache, "k_cache")
     if _kv_layer(v_cache, "v_cache") != (num_slots, hkv):
@@ -191,36 +209,27 @@ def sparse_decode_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Te
     _i32(slot_table, "slot_table"); _i32(req_rows, "req_rows"); _i32(seq_lens, "seq_lens")
     if int(req_rows.numel()) != bsz or int(seq_lens.numel()) != bsz:
         raise ValueError("req_rows / seq_lens must have one entry per q row.")
-    mo_strides = ml_strides = None
-    if num_splits > 1:
-        if mid_o is None or mid_lse is None or tickets is None:
-            raise ValueError("split-K (num_splits > 1) needs mid_o, mid_lse and tickets.")
-        require_cuda(mid_o, "mid_o", torch.float32); require_cuda(mid_lse, "mid_lse", torch.float32)
-        _i32(tickets, "tickets")
-        if mid_o.dim() != 4 or mid_o.shape[0] < bsz or mid_o.shape[1] < hq or mid_o.shape[2] < num_splits \
-                or mid_o.shape[3] != HEAD_DIM or mid_o.stride(3) != 1:
-            raise ValueError(f"mid_o must be [>=B, >=Hq, >=num_splits, {HEAD_DIM}] fp32, got {tuple(mid_o.shape)}.")
-        if mid_lse.dim() != 3 or mid_lse.shape[0] < bsz or mid_lse.shape[1] < hq or mid_lse.shape[2] < num_splits \
-                or mid_lse.stride(2) != 1:
-            raise ValueError(f"mid_lse must be [>=B, >=Hq, >=num_splits] fp32, got {tuple(mid_lse.shape)}.")
-        if tickets.numel() * 4 < int(_native.load().svb200_workspace_bytes(bsz, hkv)):
-            raise ValueError("tickets scratch is smaller than svb200_workspace_bytes(batch, num_kv_heads).")
-        mo_strides = (ctypes.c_int64 * 3)(mid_o.stride(0), mid_o.stride(1), mid_o.stride(2))
-        ml_strides = (ctypes.c_int64 * 2)(mid_lse.stride(0), mid_lse.stride(1))
+    table_stride = _rows_stride(slot_table, "slot_table")
+    width = int(slot_table.shape[-1])
+    max_len = width if max_len is None else int(max_len)
+    if max_len < 0 or max_len > width:
+        raise ValueError(f"max_len={max_len} must be in [0, slot table width {width}].")
+    _i32(workspace, "workspace")
     score_stride = 0
     if attn_score is not None:
         require_cuda(attn_score, "attn_score", torch.float32)
-        if attn_score.dim() != 2 or attn_score.shape[0] < bsz or attn_score.stride(1) != 1:
-            raise ValueError(f"attn_score must be fp32 [B, W] with contiguous W, got {tuple(attn_score.shape)}.")
+        if attn_score.dim() != 2 or attn_score.shape[0] < bsz or attn_score.stride(1) != 1 \
+                or attn_score.shape[1] < max_len:
+            raise ValueError(f"attn_score must be fp32 [B, W >= max_len] with contiguous W, got {tuple(attn_score.shape)}.")
         score_stride = int(attn_score.stride(0))
     if sm_scale is None:
         sm_scale = 1.0 / math.sqrt(HEAD_DIM)
     lib = _native.load()
     check(lib.svb200_sparse_decode_attn(
-        ptr(q), qs, ptr(k_cache), ptr(v_cache), num_slots, ptr(slot_table), _rows_stride(slot_table, "slot_table"),
-        ptr(req_rows), ptr(seq_lens), ptr(mid_o), mo_strides, ptr(mid_lse), ml_strides, ptr(out), os_,
-        ptr(attn_score), score_stride, bsz, hq, hkv, int(split_tokens), int(num_splits), int(heads_per_cta),
-        ptr(tickets), float(sm_scale), current_stream_ptr(q.device)), "svb200_sparse_decode_attn")
+        ptr(q), qs, ptr(k_cache), ptr(v_cache), num_slots, ptr(slot_table), table_stride, max_len,
+        ptr(req_rows), ptr(seq_lens), ptr(out), os_, ptr(attn_score), score_stride, bsz, hq, hkv,
+        int(heads_per_cta), ptr(workspace), int(workspace.numel()) * 4, float(sm_scale),
+        current_stream_ptr(q.device)), "svb200_sparse_decode_attn")
     return out
 
 

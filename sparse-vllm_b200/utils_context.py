@@ -12,7 +12,8 @@ class Context:
     is_long_text: bool = True
     decode_mid_o: torch.Tensor | None = None
     decode_mid_o_logexpsum: torch.Tensor | None = None
-    decode_tickets: torch.Tensor | None = None
+    decode_workspace: torch.Tensor | None = None
+    decode_workspace_key: tuple | None = None
 
 
 _CONTEXT = Context()

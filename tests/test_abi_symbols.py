@@ -50,7 +50,8 @@ def test_validation_errors_need_no_gpu(native_lib):
     rc = native_lib.svb200_quest_page_minmax(None, None, None, 4, 8, 1024, None)
     assert rc == 1
     assert b"null pointer" in native_lib.svb200_last_error()
-    assert native_lib.svb200_workspace_bytes(32, 4) == 32 * 4 * 4
+    # tickets (256-byte rounded) + two (output + lse) fp32 partial records per SM (148 without a device)
+    assert native_lib.svb200_workspace_bytes(32, 28, 4) == 512 + 148 * 2 * 28 * (128 + 4) * 4
     rc = native_lib.svb200_h2o_select_compact(1, 1, 1, 1, None, None, None, 2, 100, 200, 10, None)
     assert rc == 1 and b"kv_len" in native_lib.svb200_last_error()
 

@@ -15,35 +15,34 @@ DEV = "cuda:0"
 ATOL, RTOL = 2e-2, 1e-2
 
 
-def _run_attn(inp, *, split_tokens, num_splits, hpc, with_score, width):
+def _run_attn(inp, *, max_ctas, hpc, with_score, width):
     from sparse_vllm_b200 import ops
     q = inp["q"].to(DEV)
     bsz, hq, _ = q.shape
     hkv = inp["k_cache"].shape[1]
     out = torch.full_like(q, float("nan"))
-    mid_o = torch.full((bsz, hq, num_splits, 128), float("nan"), dtype=torch.float32, device=DEV)
-    mid_lse = torch.full((bsz, hq, num_splits), float("nan"), dtype=torch.float32, device=DEV)
-    tickets = ops.attn_workspace_tickets(bsz, hkv, DEV)
+    ws = ops.attn_workspace(bsz, hq, hkv, DEV, max_ctas=max_ctas)
+    ws[(bsz * hkv * 4 + 255) // 256 * 64:] = 0x7FC00000  # partial records start out as NaN
     score = torch.full((bsz, width), -1e20, dtype=torch.float32, device=DEV) if with_score else None
     for _ in range(2):  # second run must see zeroed tickets and give the same answer
         if score is not None:
             score.fill_(-1e20)
         ops.sparse_decode_attn(q, inp["k_cache"].to(DEV), inp["v_cache"].to(DEV), inp["slot_table"].to(DEV),
-                               inp["req_indices"].to(DEV), inp["seq_lens"].to(DEV), out=out, mid_o=mid_o,
-                               mid_lse=mid_lse, tickets=tickets, split_tokens=split_tokens, num_splits=num_splits,
-                               attn_score=score, heads_per_cta=hpc)
+                               inp["req_indices"].to(DEV), inp["seq_lens"].to(DEV), out=out, workspace=ws,
+                               max_len=width, attn_score=score, heads_per_cta=hpc)
     torch.cuda.synchronize()
-    assert int(tickets.abs().sum()) == 0
+    assert int(ws[: bsz * hkv].abs().sum()) == 0
     return out.cpu(), None if score is None else score.cpu()
 
 
 def _variants(hkv, width):
+    """(heads_per_cta, CTA count): 1 CTA = every row complete, a few CTAs = rows cut mid-way, None = one per SM."""
     out = []
     for hpc in (0, 1, 2, 4, 8):
         if hpc and hkv % hpc:
             continue
-        for split_tokens in (256, 64, ((width + 15) // 16) * 16):
-            out.append((hpc, split_tokens, (width + split_tokens - 1) // split_tokens))
+        for max_ctas in (None, 1, 3, 37):
+            out.append((hpc, max_ctas))
     return out
 
 
@@ -58,10 +57,9 @@ def test_attention_matches_reference(name, golden):
     dead = [b for b, n in enumerate(cfg["lens"]) if n == 0]
     oracle_out = oattn.gqa_decode(inp["q"], inp["k_cache"], inp["v_cache"], inp["slot_table"], inp["req_indices"],
                                   inp["seq_lens"], max_len_in_batch=cfg["width"]).float()
-    for hpc, split_tokens, num_splits in _variants(cfg["hkv"], cfg["width"]):
-        out, score = _run_attn(inp, split_tokens=split_tokens, num_splits=num_splits, hpc=hpc,
-                               with_score=cfg["with_score"], width=cfg["width"])
-        tag = f"{name} hpc={hpc} split={split_tokens}x{num_splits}"
+    for hpc, max_ctas in _variants(cfg["hkv"], cfg["width"]):
+        out, score = _run_attn(inp, max_ctas=max_ctas, hpc=hpc, with_score=cfg["with_score"], width=cfg["width"])
+        tag = f"{name} hpc={hpc} ctas={max_ctas}"
         torch.testing.assert_close(out[live].float(), ref[live], atol=ATOL, rtol=RTOL, msg=lambda m: f"{tag}: {m}")
         torch.testing.assert_close(out[live].float(), oracle_out[live], atol=ATOL, rtol=RTOL, msg=lambda m: f"{tag}: {m}")
         if dead:  # an empty row yields zeros here (the reference divides 0/0); it must not be NaN
@@ -74,9 +72,8 @@ def test_attention_matches_reference(name, golden):
                 assert bool((score[b, n:] == -1e20).all()), f"{tag}: score written beyond the row length"
 
 
-def test_attention_masked_slots_and_strided_workspace():
-    """Entries < 0 in the slot table are masked tokens; mid_o/mid_lse may be sliced views of a larger
-    cached workspace (layers/attention.py:15-51) and q/out may be strided in the batch dimension."""
+def test_attention_masked_slots_and_strided_io():
+    """Entries < 0 in the slot table are masked tokens; q/out may be strided in the batch dimension."""
     from sparse_vllm_b200 import ops
     cfg = dict(seed=77, bsz=2, hq=16, hkv=2, lens=[200, 150], width=256, num_slots=512)
     inp = cases.make_attn_inputs(**cfg)
@@ -97,21 +94,19 @@ def test_attention_masked_slots_and_strided_workspace():
     q_big = torch.zeros(2, 3, 16, 128, dtype=torch.bfloat16, device=DEV)
     q_big[:, 1] = inp["q"].to(DEV)
     out_big = torch.zeros_like(q_big)
-    ws_o = torch.zeros(4, 16, 8, 128, dtype=torch.float32, device=DEV)
-    ws_l = torch.zeros(4, 16, 8, dtype=torch.float32, device=DEV)
-    tickets = ops.attn_workspace_tickets(2, 2, DEV)
-    ops.sparse_decode_attn(q_big[:, 1], inp["k_cache"].to(DEV), inp["v_cache"].to(DEV), table.to(DEV),
-                           inp["req_indices"].to(DEV), inp["seq_lens"].to(DEV), out=out_big[:, 1],
-                           mid_o=ws_o[:2, :, :4], mid_lse=ws_l[:2, :, :4], tickets=tickets,
-                           split_tokens=64, num_splits=4)
-    torch.cuda.synchronize()
-    torch.testing.assert_close(out_big[:, 1].cpu().float(), ref, atol=ATOL, rtol=RTOL)
+    for max_ctas in (None, 5):
+        out_big.zero_()
+        ops.sparse_decode_attn(q_big[:, 1], inp["k_cache"].to(DEV), inp["v_cache"].to(DEV), table.to(DEV),
+                               inp["req_indices"].to(DEV), inp["seq_lens"].to(DEV), out=out_big[:, 1],
+                               workspace=ops.attn_workspace(2, 16, 2, DEV, max_ctas=max_ctas))
+        torch.cuda.synchronize()
+        torch.testing.assert_close(out_big[:, 1].cpu().float(), ref, atol=ATOL, rtol=RTOL)
     assert not out_big[:, 0].any() and not out_big[:, 2].any()
 
 
 @pytest.mark.parametrize("hq,hkv,bsz,tokens", [(28, 4, 8, 4096), (32, 8, 4, 2176), (64, 8, 2, 4096), (8, 1, 4, 4096)])
 def test_attention_full_width_properties(hq, hkv, bsz, tokens):
-    """BASELINE selection widths: every split/head-group decomposition gives the same answer, and it
+    """BASELINE selection widths: every CTA-count/head-group decomposition gives the same answer, and it
     matches fp32 torch softmax attention over the same slots."""
     from sparse_vllm_b200 import ops
     gen = torch.Generator(device=DEV).manual_seed(99)
@@ -132,14 +127,10 @@ def test_attention_full_width_properties(hq, hkv, bsz, tokens):
         ref[b] = torch.einsum("hgn,nhd->hgd", torch.softmax(s, -1), vv).reshape(hq, 128)
     outs = []
     for hpc in (0, 1, hkv):
-        for split_tokens in (256, 1024, tokens):
-            ns = (tokens + split_tokens - 1) // split_tokens
+        for max_ctas in (None, 64, bsz):
             out = torch.empty_like(q)
-            mid_o = torch.empty(bsz, hq, ns, 128, dtype=torch.float32, device=DEV)
-            mid_lse = torch.empty(bsz, hq, ns, dtype=torch.float32, device=DEV)
-            tickets = ops.attn_workspace_tickets(bsz, hkv, DEV)
-            ops.sparse_decode_attn(q, k, v, table, req, lens, out=out, mid_o=mid_o, mid_lse=mid_lse, tickets=tickets,
-                                   split_tokens=split_tokens, num_splits=ns, heads_per_cta=hpc)
+            ws = ops.attn_workspace(bsz, hq, hkv, DEV, max_ctas=max_ctas)
+            ops.sparse_decode_attn(q, k, v, table, req, lens, out=out, workspace=ws, heads_per_cta=hpc)
             torch.cuda.synchronize()
             torch.testing.assert_close(out.float(), ref, atol=ATOL, rtol=RTOL)
             outs.append(out.float())

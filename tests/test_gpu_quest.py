@@ -246,8 +246,26 @@ def test_selection_ties_take_lowest_page_first():
     assert lens.tolist() == [prev * PAGE + PAGE, prev * PAGE + PAGE - 5]
 
 
+@pytest.mark.parametrize("max_ctas", [1, 2, 7])
+@pytest.mark.parametrize("bsz,hq,hkv,ctx,budget", [(3, 28, 4, 16384, 512), (2, 64, 8, 8192, 256), (3, 8, 1, 32768, 1024),
+                                                   (2, 32, 2, 8192, 256)])
+def test_few_ctas_many_tiles_per_cta(bsz, hq, hkv, ctx, budget, max_ctas):
+    """A capped grid makes every CTA walk many page tiles (ring wrap-around, rows cut mid-way, several
+    selections per CTA); results must not depend on the decomposition."""
+    from sparse_vllm_b200 import ops
+    prev_cap = ops.set_max_ctas(max_ctas)
+    try:
+        _check_fused_properties(bsz, hq, hkv, ctx, budget)
+    finally:
+        ops.set_max_ctas(prev_cap)
+
+
 @pytest.mark.parametrize("bsz,hq,hkv,ctx,budget", [(4, 28, 4, 131072, 4096), (1, 32, 8, 32768, 2048)])
 def test_full_size_properties(bsz, hq, hkv, ctx, budget):
+    _check_fused_properties(bsz, hq, hkv, ctx, budget)
+
+
+def _check_fused_properties(bsz, hq, hkv, ctx, budget):
     """BASELINE sizes (cfg 3 at a reduced batch, cfg 2): size-independent properties of the fused launch.
     -inf beyond the valid pages, exact top-k w.r.t. its own scores, packing = page table lookup, and the
     scores themselves against a torch fp32 evaluation with the reference's three bf16 roundings."""
