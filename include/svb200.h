@@ -47,6 +47,11 @@ int svb200_sm_count(void);
  * different places; results do not depend on it.
  */
 int svb200_set_max_ctas(int32_t n);
+/*
+ * Experiments only: when device_buffer != NULL the attention kernel writes 8 uint64 per CTA
+ * (globaltimer ns at entry, after setup, first data, consumers done, producer done, -, -, SM id).
+ */
+void svb200_debug_times(void* device_buffer);
 
 /*
  * Bytes of scratch svb200_sparse_decode_attn needs: one int32 arrival ticket per

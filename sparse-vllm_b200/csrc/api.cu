@@ -38,6 +38,8 @@ int sm_count() {
   return cached;
 }
 
+static unsigned long long* g_dbg_times = nullptr;
+unsigned long long* debug_times_buffer() { return g_dbg_times; }
 static int g_max_ctas = 0;
 int max_ctas() {
   const int n = sm_count();
@@ -76,6 +78,7 @@ extern "C" {
 int svb200_abi_version(void) { return SVB200_ABI_VERSION; }
 const char* svb200_last_error(void) { return g_err; }
 int svb200_sm_count(void) { return sm_count(); }
+void svb200_debug_times(void* device_buffer) { g_dbg_times = (unsigned long long*)device_buffer; }
 int svb200_set_max_ctas(int32_t n) {
   const int prev = g_max_ctas;
   g_max_ctas = n > 0 ? n : 0;

@@ -15,7 +15,7 @@
 // directly; otherwise it publishes one fp32 partial (at most two per CTA) and
 // the last contributor of the row (arrival ticket) merges them.
 //
-// Inside a CTA: warps 8-9 are producers.  A producer reads 16 token slots and copies
+// Inside a CTA: warps 8-11 are producers.  A producer reads 16 token slots and copies
 // each token's HPC*256 contiguous bytes of K and of V with 16-byte LDGSTS (a whole
 // warp per 512 B, masked tokens zero-filled) into a ring of S stages whose mbarriers
 // complete when the copies land (S * stage bytes ~ 160-190 KB in flight per SM).
@@ -31,7 +31,8 @@ namespace svb200 {
 
 constexpr int kConsumerWarps = 8;
 constexpr int kConsumerThreads = kConsumerWarps * 32;
-constexpr int kProducerWarps = 2;
+constexpr int kProducerWarps = 4;
+constexpr int kSlotPrefetch = 6;
 constexpr int kAttnThreads = kConsumerThreads + kProducerWarps * 32;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -99,6 +100,14 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
   __shared__ int s_flag;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  unsigned long long* dbg = p.dbg_times ? p.dbg_times + (size_t)blockIdx.x * 8 : nullptr;
+  if (dbg && tid == 0) {
+    uint32_t smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    dbg[0] = global_timer_ns();
+    dbg[7] = smid;
+    dbg[5] = dbg[6] = 0;
+  }
 
   // ---- setup: barriers, per-row page counts -> exclusive prefix
   if (tid == 0) {
@@ -138,6 +147,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
   }
   __syncthreads();
 
+  if (dbg && tid == 0) dbg[1] = global_timer_ns();
   const int64_t U = sPrefix[R];
   // never more ranges than units: every range is non-empty, so the contributors of a
   // row are exactly the CTAs unit_owner(first unit) .. unit_owner(last unit)
@@ -166,55 +176,84 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
     // for a free stage); each token row (HPC*256 contiguous bytes of K, same of V) is
     // copied by the whole warp with 16-byte LDGSTS (512 B per instruction), masked tokens
     // zero-filled.  Every lane's copies arrive on the stage's mbarrier when they land.
+    // Unit i is fed by producer i % NP with NP | S: a stage is always refilled by the same warp, so
+    // the empty-phase it waits for is never more than one ahead of the barrier (same parity
+    // argument as for the consumers).
     const int n_units = u1 - u0;
     const int pw = warp - kConsumerWarps;
+    const int NP = p.producers;
+    if (pw >= NP) return;
     const int tok_lane = lane & 15;
-    int r_pf = r_first, r_is = r_first;
+    // prefetch cursor: row / batch entry of the unit whose slots are fetched next; the row's
+    // length and table row are reloaded only when the cursor moves to another batch entry
+    int r_pf = r_first, b_pf = r_first / HG, hg_pf = r_first % HG;
+    int len_pf = min(p.seq_lens[b_pf], p.max_len);
+    const int32_t* row_pf = p.slot_table + (int64_t)p.req_rows[b_pf] * p.slot_table_stride;
     auto fetch = [&](int i) -> int {  // raw slot of token tok_lane in local unit i
       if (i >= n_units) return -1;
       const int u = u0 + i;
-      while (sPrefix[r_pf + 1] <= u) ++r_pf;
-      const int b = r_pf / HG;
-      const int len = min(p.seq_lens[b], p.max_len);
+      bool moved = false;
+      while (sPrefix[r_pf + 1] <= u) {
+        ++r_pf;
+        if (++hg_pf == HG) hg_pf = 0, ++b_pf, moved = true;
+      }
+      if (moved) {
+        len_pf = min(p.seq_lens[b_pf], p.max_len);
+        row_pf = p.slot_table + (int64_t)p.req_rows[b_pf] * p.slot_table_stride;
+      }
       const int t = (u - sPrefix[r_pf]) * kPage + tok_lane;
-      if (t >= len) return -1;
-      return __ldg(p.slot_table + (int64_t)p.req_rows[b] * p.slot_table_stride + t);
+      if (t >= len_pf) return -1;
+      return __ldg(row_pf + t);
     };
     constexpr int LPR = G::TOK_BYTES >= 512 ? 32 : G::TOK_BYTES / 16;  // lanes per token row
     constexpr int TPI = 32 / LPR;                                     // tokens per instruction
     constexpr int CPR = G::TOK_BYTES / (LPR * 16);                    // instructions per row
     const int sub = lane / LPR, chunk = lane % LPR;
-    int slot_a = fetch(pw), slot_b = fetch(pw + kProducerWarps);
-    for (int i = pw; i < n_units; i += kProducerWarps) {
-      const int slot_c = fetch(i + 2 * kProducerWarps);
+    const int64_t slot_bytes = slot_elems * 2;
+    int r_is = r_first, hg_is = r_first % HG;  // issue cursor
+    int s = pw % S;
+    uint32_t ph = (pw / S) & 1;  // phase parity of stage s at unit i
+    // slots are fetched kSlotPrefetch units of this warp ahead: the table comes from DRAM and one
+    // unit's copies are issued in far less than a DRAM round trip
+    int pf[kSlotPrefetch];
+#pragma unroll
+    for (int d = 0; d < kSlotPrefetch; ++d) pf[d] = fetch(pw + d * NP);
+    for (int i = pw; i < n_units; i += NP) {
+      const int slot_new = fetch(i + kSlotPrefetch * NP);
+      const int slot_a = pf[0];
       const int my = (slot_a >= 0 && slot_a < p.num_slots) ? slot_a : -1;
       const uint32_t mask = __ballot_sync(0xffffffffu, my >= 0) & 0xffffu;
-      const int s = i % S;
-      mbar_wait(&empty_bar[s], ((i / S) & 1) ^ 1);
-      while (sPrefix[r_is + 1] <= u0 + i) ++r_is;
-      const int hg = r_is % HG;
-      const __nv_bfloat16* ksrc = kc + (int64_t)hg * HPC * kHeadDim + chunk * 8;
-      const __nv_bfloat16* vsrc = vc + (int64_t)hg * HPC * kHeadDim + chunk * 8;
+      while (sPrefix[r_is + 1] <= u0 + i) {
+        ++r_is;
+        if (++hg_is == HG) hg_is = 0;
+      }
+      const char* kbase = reinterpret_cast<const char*>(kc) + hg_is * G::TOK_BYTES + chunk * 16;
+      const char* vbase = reinterpret_cast<const char*>(vc) + hg_is * G::TOK_BYTES + chunk * 16;
       const uint32_t dst0 = smem_u32(ring + s * G::STAGE_BYTES) + chunk * 16;
+      mbar_wait(&empty_bar[s], ph ^ 1);
 #pragma unroll
       for (int t0 = 0; t0 < kPage; t0 += TPI) {
         const int tok = t0 + sub;
         const int slot = __shfl_sync(0xffffffffu, my, tok);
         const int nbytes = slot >= 0 ? 16 : 0;
-        const int64_t off = (int64_t)max(slot, 0) * slot_elems;
+        const int64_t off = (int64_t)max(slot, 0) * slot_bytes;
         const uint32_t dst = dst0 + tok * G::TOK_STRIDE;
 #pragma unroll
         for (int c = 0; c < CPR; ++c) {
-          cp_async_16(dst + c * 512, ksrc + off + c * 256, nbytes);
-          cp_async_16(dst + G::KV_BYTES + c * 512, vsrc + off + c * 256, nbytes);
+          cp_async_16(dst + c * 512, kbase + off + c * 512, nbytes);
+          cp_async_16(dst + G::KV_BYTES + c * 512, vbase + off + c * 512, nbytes);
         }
       }
       if (lane == 0) sValid[s] = mask;
       cp_async_mbar_arrive(&full_bar[s]);
       if (lane == 0) mbar_arrive(&full_bar[s]);  // release: publishes sValid
-      slot_a = slot_b;
-      slot_b = slot_c;
+#pragma unroll
+      for (int d = 0; d + 1 < kSlotPrefetch; ++d) pf[d] = pf[d + 1];
+      pf[kSlotPrefetch - 1] = slot_new;
+      s += NP;
+      while (s >= S) s -= S, ph ^= 1;
     }
+    if (dbg && pw == 0 && lane == 0) dbg[4] = global_timer_ns();
     return;
   }
 
@@ -269,7 +308,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
 
     for (int j = i + ((tl - i % TL + TL) % TL); j < i + n; j += TL) {
       const int s = j % S;
-      mbar_wait(&full_bar[s], (j / S) & 1);
+      mbar_wait(&full_bar[s], (uint32_t)(j / S) & 1u);
+      if (dbg && tid == 0 && j == 0) dbg[2] = global_timer_ns();
       const uint32_t mask = sValid[s];
       const bool tv0 = (mask >> g) & 1u, tv1 = (mask >> (g + 8)) & 1u;
       if (mask != 0u) {
@@ -360,6 +400,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
     }
 
     // ---------------------------------------------------- segment epilogue
+    const unsigned long long t_epi = dbg ? global_timer_ns() : 0;
     // per-head sums live as per-lane partials: reduce over the 8 token lanes
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
@@ -462,42 +503,80 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
         if (s_flag) p.tickets[r] = 0;  // scratch stays zeroed for the next launch / replay
       }
       consumer_sync();
+      const unsigned long long t_cmb = dbg ? global_timer_ns() : 0;
       if (s_flag) {
+        // One warp per q head, lane = 4 output dims.  Lane c first fetches the lse of contributor
+        // c (all contributors in parallel), then the partial outputs are read with independent
+        // loads: the merge costs a couple of L2 round trips, not one per contributor.
         __threadfence();
-        for (int w = tid; w < heads_row * 32; w += kConsumerThreads) {
-          const int head_local = w >> 5, d4 = w & 31;
-          float mx = -INFINITY;
-          for (int c = c_first; c <= c_last; ++c) {
-            const int ps = 2 * c + ((int)(U * c / Gn) >= row_begin ? 0 : 1);
-            mx = fmaxf(mx, __ldcg(p.ws_lse + (int64_t)ps * heads_row + head_local));
+        const int nc = c_last - c_first + 1;
+        constexpr int HB = 4;  // heads a warp merges at once: their loads are all independent
+        for (int h0 = warp * HB; h0 < heads_row; h0 += kConsumerWarps * HB) {
+          float m[HB], wsum[HB];
+          float4 acc[HB];
+#pragma unroll
+          for (int x = 0; x < HB; ++x) m[x] = -INFINITY, wsum[x] = 0.f, acc[x] = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int c0 = 0; c0 < nc; c0 += 32) {
+            const int c = c_first + c0 + lane;
+            int ps = 0;
+            float lse[HB], wgt[HB];
+            if (c <= c_last) ps = 2 * c + ((int)(U * c / Gn) >= row_begin ? 0 : 1);
+#pragma unroll
+            for (int x = 0; x < HB; ++x)
+              lse[x] = (c <= c_last && h0 + x < heads_row)
+                           ? __ldcg(p.ws_lse + (int64_t)ps * heads_row + h0 + x)
+                           : -INFINITY;
+#pragma unroll
+            for (int x = 0; x < HB; ++x) {
+              float cm = lse[x];
+#pragma unroll
+              for (int o = 16; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+              const float mnew = fmaxf(m[x], cm);
+              const float rescale = m[x] == -INFINITY ? 0.f : __expf(m[x] - mnew);
+              acc[x].x *= rescale, acc[x].y *= rescale, acc[x].z *= rescale, acc[x].w *= rescale;
+              wsum[x] *= rescale;
+              wgt[x] = lse[x] == -INFINITY ? 0.f : __expf(lse[x] - mnew);
+              m[x] = mnew;
+            }
+            const int cnt = min(32, nc - c0);
+#pragma unroll 4
+            for (int kc2 = 0; kc2 < cnt; ++kc2) {
+              const int psk = __shfl_sync(0xffffffffu, ps, kc2);
+              const float4* src = reinterpret_cast<const float4*>(
+                                      p.ws_o + ((int64_t)psk * heads_row + h0) * kHeadDim) + lane;
+#pragma unroll
+              for (int x = 0; x < HB; ++x) {
+                const float wk = __shfl_sync(0xffffffffu, wgt[x], kc2);
+                if (wk != 0.f) {
+                  const float4 v = __ldcg(src + x * (kHeadDim / 4));
+                  acc[x].x += wk * v.x, acc[x].y += wk * v.y, acc[x].z += wk * v.z, acc[x].w += wk * v.w;
+                  wsum[x] += wk;
+                }
+              }
+            }
           }
-          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-          float wsum = 0.f;
-          for (int c = c_first; c <= c_last; ++c) {
-            const int ps = 2 * c + ((int)(U * c / Gn) >= row_begin ? 0 : 1);
-            const float lse = __ldcg(p.ws_lse + (int64_t)ps * heads_row + head_local);
-            if (lse == -INFINITY) continue;
-            const float wgt = __expf(lse - mx);
-            const float4 v = __ldcg(reinterpret_cast<const float4*>(
-                                        p.ws_o + ((int64_t)ps * heads_row + head_local) * kHeadDim) +
-                                    d4);
-            acc.x += wgt * v.x, acc.y += wgt * v.y, acc.z += wgt * v.z, acc.w += wgt * v.w;
-            wsum += wgt;
+#pragma unroll
+          for (int x = 0; x < HB; ++x) {
+            if (h0 + x < heads_row) {
+              const float inv = wsum[x] > 0.f ? 1.f / wsum[x] : 0.f;
+              uint2 o2;
+              o2.x = pack_bf16x2(acc[x].x * inv, acc[x].y * inv);
+              o2.y = pack_bf16x2(acc[x].z * inv, acc[x].w * inv);
+              __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
+                                    (int64_t)b * p.out_stride_b +
+                                    (int64_t)(hg * heads_row + h0 + x) * kHeadDim;
+              *reinterpret_cast<uint2*>(orow + lane * 4) = o2;
+            }
           }
-          const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
-          uint2 o2;
-          o2.x = pack_bf16x2(acc.x * inv, acc.y * inv);
-          o2.y = pack_bf16x2(acc.z * inv, acc.w * inv);
-          __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
-                                (int64_t)b * p.out_stride_b +
-                                (int64_t)(hg * heads_row + head_local) * kHeadDim;
-          *reinterpret_cast<uint2*>(orow + d4 * 4) = o2;
         }
+        if (dbg && tid == 0) dbg[5] += global_timer_ns() - t_cmb;
       }
     }
     consumer_sync();  // sQ / sMerge / s_flag are reused by the next segment
+    if (dbg && tid == 0) dbg[6] += global_timer_ns() - t_epi;
     i += n;
   }
+  if (dbg && tid == 0) dbg[3] = global_timer_ns();
 }
 
 template <int HPC, int NT, bool WITH_SCORE>
@@ -513,11 +592,16 @@ static int launch_variant(const AttnParams& p_in, cudaStream_t stream) {
   // same warps, so the phase a warp waits for is never more than one ahead of the barrier (parity
   // waits cannot tell a phase from the one two before it).
   stages -= stages % G::TL;
+  if (stages < G::TL) stages = 0;
   if (stages < 2) {
     set_error("sparse_decode_attn: batch*head_groups=%d rows leave no shared memory for the KV ring", rows);
     return 1;
   }
   p.stages = stages;
+  p.dbg_times = debug_times_buffer();
+  p.producers = 1;
+  for (int d = kProducerWarps; d >= 1; --d)
+    if (stages % d == 0) { p.producers = d; break; }
   const size_t smem = attn_smem_layout<HPC, NT>(stages, gsz, rows).total;
   auto kern = sparse_decode_attn_kernel<HPC, NT, WITH_SCORE>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

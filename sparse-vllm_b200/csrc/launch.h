@@ -11,6 +11,7 @@ void set_error(const char* fmt, ...);
 int cuda_error(const char* what, cudaError_t e);
 int check_launch(const char* what);
 int sm_count();
+unsigned long long* debug_times_buffer();
 int max_ctas();  // persistent-grid size: sm_count() unless svb200_set_max_ctas lowered it
 
 // quest.cu
@@ -60,6 +61,8 @@ struct AttnParams {
   int32_t* tickets;  // [batch*head_groups] zeroed
   int max_ctas;      // CTAs the workspace was sized for
   int stages;        // filled by the launcher
+  unsigned long long* dbg_times;  // experiments: per-CTA timestamps (svb200_debug_times), else null
+  int producers;     // producer warps in use (divides stages); filled by the launcher
   float sm_scale;
 };
 int attn_auto_heads_per_cta(int hkv);

@@ -175,29 +175,62 @@ __device__ __forceinline__ void find_kth_bin(const int* hist, int k, int* bcast)
 
 // scores_row: bf16 bits, 16-byte aligned, readable up to round_up(n_cols, 8).
 // Columns >= n_valid count as -inf whatever the buffer holds (quest.py:1883-1885).
-template <int BAR, int NTHR>
-__device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, int n_cols, int n_valid, int k,
-                                      const int32_t* __restrict__ pt_row, int ctx,
-                                      int32_t* __restrict__ out_row, int32_t* __restrict__ len_out,
-                                      int32_t* __restrict__ sel_pages_out, SelectSmem& sm) {
-  const int tid = threadIdx.x, nthr = NTHR;
+// Three passes over the row (high-byte histogram, low-byte histogram, ordered compaction); each
+// thread owns a contiguous chunk of 8-score vectors.  CACHED keeps the chunk in registers so the
+// row is read from L2 once (rows up to 4 * NTHR vectors = 8192 scores at 256 threads).
+constexpr int kSelectVecPerThread = 4;
+
+template <int BAR, int NTHR, bool CACHED>
+__device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, int n_cols, int n_valid,
+                                       int k, const int32_t* __restrict__ pt_row, int ctx,
+                                       int32_t* __restrict__ out_row, int32_t* __restrict__ len_out,
+                                       int32_t* __restrict__ sel_pages_out, SelectSmem& sm) {
+  constexpr int VPT = kSelectVecPerThread;
+  const int tid = threadIdx.x;
   const int nvec = (n_cols + 7) >> 3;
   const uint4* vrow = reinterpret_cast<const uint4*>(scores_row);
-
-  // ---- pass 1: histogram of the high key byte
-  for (int i = tid; i < 256; i += nthr) sm.hist[i] = 0;
-  group_sync<BAR, NTHR>();
-  for (int v = tid; v < nvec; v += nthr) {
-    const uint4 x = __ldcg(vrow + v);
-    const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+  const int vec_per_thr = CACHED ? VPT : (nvec + NTHR - 1) / NTHR;
+  const int v_begin = min(tid * vec_per_thr, nvec), v_end = min(v_begin + vec_per_thr, nvec);
+  uint4 xr[VPT];
+  if constexpr (CACHED) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      if (v * 8 + i < n_cols) {
-        const uint32_t key = v * 8 + i < n_valid ? bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu) : kNegInfKey;
-        atomicAdd(&sm.hist[key >> 8], 1);
+    for (int vv = 0; vv < VPT; ++vv)
+      xr[vv] = v_begin + vv < v_end ? __ldcg(vrow + v_begin + vv) : make_uint4(0, 0, 0, 0);
+  }
+  // body(col, key, valid) for every column slot of this thread's chunk, in ascending column order.
+  // Control flow is warp-uniform (invalid slots are passed with valid = false) so bodies may use
+  // full-mask warp primitives.
+  auto for_each_key = [&](auto&& body) {
+    auto one_vec = [&](int v, bool vec_ok, const uint4& x) {
+      const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int col = v * 8 + i;
+        body(col, col < n_valid ? bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu) : kNegInfKey,
+             vec_ok && col < n_cols);
+      }
+    };
+    if constexpr (CACHED) {
+#pragma unroll
+      for (int vv = 0; vv < VPT; ++vv) one_vec(v_begin + vv, v_begin + vv < v_end, xr[vv]);
+    } else {
+      for (int vv = 0; vv < vec_per_thr; ++vv) {
+        const bool ok = v_begin + vv < v_end;
+        one_vec(v_begin + vv, ok, ok ? __ldcg(vrow + v_begin + vv) : make_uint4(0, 0, 0, 0));
       }
     }
-  }
+  };
+  // Histogram increment aggregated over the lanes that hit the same bin: page scores crowd into a
+  // few exponent bins, and one shared-memory atomic per lane would serialise on them.
+  auto hist_add = [&](int bin, bool valid) {
+    const unsigned peers = __match_any_sync(0xffffffffu, valid ? bin : -1);
+    if (valid && (tid & 31) == __ffs(peers) - 1) atomicAdd(&sm.hist[bin], __popc(peers));
+  };
+
+  // ---- pass 1: histogram of the high key byte
+  for (int i = tid; i < 256; i += NTHR) sm.hist[i] = 0;
+  group_sync<BAR, NTHR>();
+  for_each_key([&](int, uint32_t key, bool valid) { hist_add(key >> 8, valid); });
   group_sync<BAR, NTHR>();
   if (tid < 32) find_kth_bin(sm.hist, k, sm.bcast);
   group_sync<BAR, NTHR>();
@@ -206,19 +239,11 @@ __device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, i
   group_sync<BAR, NTHR>();
 
   // ---- pass 2: histogram of the low byte inside bin1
-  for (int i = tid; i < 256; i += nthr) sm.hist[i] = 0;
+  for (int i = tid; i < 256; i += NTHR) sm.hist[i] = 0;
   group_sync<BAR, NTHR>();
-  for (int v = tid; v < nvec; v += nthr) {
-    const uint4 x = __ldcg(vrow + v);
-    const uint32_t w[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      if (v * 8 + i < n_cols) {
-        const uint32_t key = v * 8 + i < n_valid ? bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu) : kNegInfKey;
-        if ((int)(key >> 8) == bin1) atomicAdd(&sm.hist[key & 0xff], 1);
-      }
-    }
-  }
+  for_each_key([&](int, uint32_t key, bool valid) {
+    hist_add(key & 0xff, valid && (int)(key >> 8) == bin1);
+  });
   group_sync<BAR, NTHR>();
   if (tid < 32) find_kth_bin(sm.hist, k1, sm.bcast);
   group_sync<BAR, NTHR>();
@@ -226,48 +251,29 @@ __device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, i
   const int need_eq = k1 - sm.bcast[1];  // how many keys == thresh to take (lowest index first)
   group_sync<BAR, NTHR>();
 
-  // ---- pass 3: ordered compaction over contiguous per-thread chunks
-  const int vec_per_thr = (nvec + nthr - 1) / nthr;
-  const int v_begin = min(tid * vec_per_thr, nvec), v_end = min(v_begin + vec_per_thr, nvec);
+  // ---- pass 3: ordered compaction
   int cnt_gt = 0, cnt_eq = 0;
-  for (int v = v_begin; v < v_end; ++v) {
-    const uint4 x = __ldcg(vrow + v);
-    const uint32_t w[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      if (v * 8 + i < n_cols) {
-        const uint32_t key = v * 8 + i < n_valid ? bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu) : kNegInfKey;
-        cnt_gt += key > thresh;
-        cnt_eq += key == thresh;
-      }
-    }
-  }
+  for_each_key([&](int, uint32_t key, bool valid) {
+    cnt_gt += valid && key > thresh;
+    cnt_eq += valid && key == thresh;
+  });
   const int eq_before = block_exclusive_scan<BAR, NTHR>(cnt_eq, sm.warp_scan);
   const int eq_take = max(0, min(cnt_eq, need_eq - eq_before));
   int pos = block_exclusive_scan<BAR, NTHR>(cnt_gt + eq_take, sm.warp_scan);
   int eq_left = eq_take;
-  for (int v = v_begin; v < v_end; ++v) {
-    const uint4 x = __ldcg(vrow + v);
-    const uint32_t w[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int col = v * 8 + i;
-      if (col < n_cols) {
-        const uint32_t key = v * 8 + i < n_valid ? bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu) : kNegInfKey;
-        bool take = key > thresh;
-        if (key == thresh && eq_left > 0) {
-          take = true;
-          --eq_left;
-        }
-        if (take) sm.sel[pos++] = col;
-      }
+  for_each_key([&](int col, uint32_t key, bool valid) {
+    bool take = valid && key > thresh;
+    if (valid && key == thresh && eq_left > 0) {
+      take = true;
+      --eq_left;
     }
-  }
+    if (take) sm.sel[pos++] = col;
+  });
   // last page (quest.py:1888-1889: safe_num_pages - 1)
   const int num_pages = (ctx + kPage - 1) / kPage;
   if (tid == 0) sm.sel[k] = max(num_pages, 1) - 1;
   group_sync<BAR, NTHR>();
-  for (int j = tid; j <= k; j += nthr) {
+  for (int j = tid; j <= k; j += NTHR) {
     const int page = sm.sel[j];
     sm.sel_slot[j] = pt_row[page];
     if (sel_pages_out) sel_pages_out[j] = page;
@@ -275,12 +281,25 @@ __device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, i
   group_sync<BAR, NTHR>();
   // packed token slots: (k+1)*16 int32 = (k+1)*4 int4
   int4* out4 = reinterpret_cast<int4*>(out_row);
-  for (int idx = tid; idx < (k + 1) * 4; idx += nthr) {
+  for (int idx = tid; idx < (k + 1) * 4; idx += NTHR) {
     const int base = sm.sel_slot[idx >> 2] * kPage + (idx & 3) * 4;
     out4[idx] = make_int4(base, base + 1, base + 2, base + 3);
   }
   if (tid == 0) *len_out = k * kPage + (ctx - (num_pages - 1) * kPage);
   group_sync<BAR, NTHR>();
+}
+
+template <int BAR, int NTHR>
+__device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, int n_cols, int n_valid, int k,
+                                      const int32_t* __restrict__ pt_row, int ctx,
+                                      int32_t* __restrict__ out_row, int32_t* __restrict__ len_out,
+                                      int32_t* __restrict__ sel_pages_out, SelectSmem& sm) {
+  if (((n_cols + 7) >> 3) <= kSelectVecPerThread * NTHR)
+    quest_select_pack_impl<BAR, NTHR, true>(scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out,
+                                            sel_pages_out, sm);
+  else
+    quest_select_pack_impl<BAR, NTHR, false>(scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out,
+                                             sel_pages_out, sm);
 }
 
 __global__ void __launch_bounds__(256) quest_select_pack_kernel(
@@ -321,7 +340,7 @@ __global__ void __launch_bounds__(256) quest_select_pack_kernel(
 //
 // Stream-K over page tiles: a "unit" is 16 consecutive logical pages of one batch
 // row; only valid pages (p < ceil(ctx/16) - 1) form units.  The launch's units are
-// cut into one equal contiguous range per persistent CTA.  Warps 8-9 (producers)
+// cut into one equal contiguous range per persistent CTA.  Warps 8-11 (producers)
 // resolve 16 page slots through the page table and copy each page's bounds record
 // ([2][Hkv][128] = Hkv*512 contiguous bytes) with 16-byte LDGSTS, a warp per 512 B,
 // into a ring of S stages (130-200 KB in flight per SM) whose mbarriers complete
@@ -334,7 +353,8 @@ __global__ void __launch_bounds__(256) quest_select_pack_kernel(
 // =========================================================================
 constexpr int kScoreConsumerWarps = 8;
 constexpr int kScoreConsumerThreads = kScoreConsumerWarps * 32;
-constexpr int kScoreProducerWarps = 2;
+constexpr int kScoreProducerWarps = 4;
+constexpr int kPagePrefetch = 6;
 constexpr int kScoreThreads = kScoreConsumerThreads + kScoreProducerWarps * 32;
 constexpr int kScoreMaxSmem = 227 * 1024;
 
@@ -350,7 +370,9 @@ struct ScoreParams {
   uint16_t* scores;
   int64_t score_stride;
   int batch, hq, hkv, n_cols, stages;
+  unsigned long long* dbg_times;  // experiments: per-CTA timestamps (svb200_debug_times), else null
   int consumers;  // consumer warps that take units; divides `stages` (see the kernel)
+  int producers;  // producer warps that feed units; divides `stages`
   // fused select only
   int k;
   int32_t* packed_slots;
@@ -405,6 +427,14 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   __shared__ int s_flag;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  unsigned long long* dbg = p.dbg_times ? p.dbg_times + (size_t)blockIdx.x * 8 : nullptr;
+  if (dbg && tid == 0) {
+    uint32_t smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    dbg[0] = global_timer_ns();
+    dbg[7] = smid;
+    dbg[5] = 0;
+  }
 
   // ---- setup
   if (tid == 0) {
@@ -444,6 +474,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   }
   __syncthreads();
 
+  if (dbg && tid == 0) dbg[1] = global_timer_ns();
   const int64_t U = sPrefix[B];
   const int64_t Gn = U < (int64_t)gridDim.x ? U : (int64_t)gridDim.x;
   const int u0 = Gn > 0 && (int64_t)blockIdx.x < Gn ? (int)(U * blockIdx.x / Gn) : 0;
@@ -460,43 +491,63 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
 
   if (warp >= kScoreConsumerWarps) {
     // ============================================================== producers
+    // unit i is fed by producer i % NP, NP | S (a stage is always refilled by the same warp)
     const int n_units = u1 - u0;
     const int pw = warp - kScoreConsumerWarps;
+    const int NP = p.producers;
+    if (pw >= NP) return;
     const int pg_lane = lane & 15;
     int r_pf = r_first;
+    auto row_nv = [&](int r) {
+      const int ctx = p.context_lens[r];
+      return min(max((ctx + kPage - 1) / kPage, 1) - 1, p.n_cols);
+    };
+    int nv_pf = row_nv(r_pf);
+    const int32_t* row_pf = p.page_table + (int64_t)p.req_rows[r_pf] * p.pt_stride;
     auto fetch = [&](int i) -> int {  // raw physical page of logical page pg_lane in local unit i
       if (i >= n_units) return -1;
       const int u = u0 + i;
-      while (sPrefix[r_pf + 1] <= u) ++r_pf;
-      const int ctx = p.context_lens[r_pf];
-      const int nv = min(max((ctx + kPage - 1) / kPage, 1) - 1, p.n_cols);
+      if (sPrefix[r_pf + 1] <= u) {
+        while (sPrefix[r_pf + 1] <= u) ++r_pf;
+        nv_pf = row_nv(r_pf);
+        row_pf = p.page_table + (int64_t)p.req_rows[r_pf] * p.pt_stride;
+      }
       const int col = (u - sPrefix[r_pf]) * 16 + pg_lane;
-      if (col >= nv) return -1;
-      return __ldg(p.page_table + (int64_t)p.req_rows[r_pf] * p.pt_stride + col);
+      if (col >= nv_pf) return -1;
+      return __ldg(row_pf + col);
     };
-    const int64_t rec_elems = rec_bytes / 2;
-    int pa = fetch(pw), pb = fetch(pw + kScoreProducerWarps);
-    for (int i = pw; i < n_units; i += kScoreProducerWarps) {
-      const int pc = fetch(i + 2 * kScoreProducerWarps);
+    int s = pw % S;
+    uint32_t ph = (pw / S) & 1;  // phase parity of stage s at unit i
+    const char* src0 = reinterpret_cast<const char*>(p.bounds) + lane * 16;
+    // page ids are fetched kPagePrefetch units of this warp ahead (the table comes from DRAM)
+    int pf[kPagePrefetch];
+#pragma unroll
+    for (int d = 0; d < kPagePrefetch; ++d) pf[d] = fetch(pw + d * NP);
+    for (int i = pw; i < n_units; i += NP) {
+      const int page_new = fetch(i + kPagePrefetch * NP);
+      const int pa = pf[0];
       const int my = (pa >= 0 && pa < p.num_pages) ? pa : -1;
       const uint32_t mask = __ballot_sync(0xffffffffu, my >= 0) & 0xffffu;
-      const int s = i % S;
-      mbar_wait(&empty_bar[s], ((i / S) & 1) ^ 1);
       const uint32_t dst0 = smem_u32(ring + s * stage_bytes) + lane * 16;
+      mbar_wait(&empty_bar[s], ph ^ 1);
 #pragma unroll 4
       for (int pg = 0; pg < kPage; ++pg) {
         const int page = __shfl_sync(0xffffffffu, my, pg);
         const int nbytes = page >= 0 ? 16 : 0;
-        const __nv_bfloat16* src = p.bounds + (int64_t)max(page, 0) * rec_elems + lane * 8;
+        const char* src = src0 + (int64_t)max(page, 0) * rec_bytes;
         const uint32_t dst = dst0 + pg * rec_stride;
-        for (int c = 0; c < hkv; ++c) cp_async_16(dst + c * 512, src + c * 256, nbytes);
+        for (int c = 0; c < hkv; ++c) cp_async_16(dst + c * 512, src + c * 512, nbytes);
       }
       if (lane == 0) sValid[s] = mask;
       cp_async_mbar_arrive(&full_bar[s]);
       if (lane == 0) mbar_arrive(&full_bar[s]);  // release: publishes sValid
-      pa = pb;
-      pb = pc;
+#pragma unroll
+      for (int d = 0; d + 1 < kPagePrefetch; ++d) pf[d] = pf[d + 1];
+      pf[kPagePrefetch - 1] = page_new;
+      s += NP;
+      while (s >= S) s -= S, ph ^= 1;
     }
+    if (dbg && pw == 0 && lane == 0) dbg[4] = global_timer_ns();
     return;
   }
 
@@ -558,6 +609,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
     for (int j = i + ((warp - i % NW + NW) % NW); warp < NW && j < i + n; j += NW) {
       const int s = j % S;
       mbar_wait(&full_bar[s], (j / S) & 1);
+      if (dbg && tid == 0 && j == 0) dbg[2] = global_timer_ns();
       const uint32_t mask = sValid[s];
       const uint32_t abase = smem_u32(ring + s * stage_bytes) +
                              ((lane & 7) + ((lane >> 3) & 1) * 8) * rec_stride + (lane >> 4) * 16;
@@ -632,15 +684,18 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       score_consumer_sync();
       if (s_flag) {
         __threadfence();
+        const unsigned long long ts = dbg ? global_timer_ns() : 0;
         quest_select_pack_row<1, kScoreConsumerThreads>(
             srow, p.n_cols, nv, p.k, p.page_table + (int64_t)p.req_rows[b] * p.pt_stride, ctx,
             p.packed_slots + (int64_t)b * p.out_stride, p.sparse_lens + b,
             p.selected_pages ? p.selected_pages + (int64_t)b * (p.k + 1) : nullptr, *sel_sm);
+        if (dbg && tid == 0) dbg[5] += global_timer_ns() - ts;
       }
     }
     score_consumer_sync();  // sq / s_flag are reused by the next segment
     i += n;
   }
+  if (dbg && tid == 0) dbg[3] = global_timer_ns();
 }
 
 // =========================================================================
@@ -696,17 +751,21 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
               p.hq, p.hkv, p.batch);
     return 1;
   }
-  // (stages, consumer warps) with consumers | stages: prefer more consumers, then more stages
-  int best_s = stages, best_c = 1;
+  // (stages, consumer warps, producer warps) with consumers | stages and producers | stages:
+  // prefer more producers + consumers, then more stages
+  int best_s = stages, best_c = 1, best_p = 1;
   for (int s2 = stages; s2 >= 2 && s2 >= stages - 3; --s2) {
-    int c = 1;
+    int c = 1, pr = 1;
     for (int d = kScoreConsumerWarps; d >= 1; --d)
       if (s2 % d == 0) { c = d; break; }
-    if (c > best_c) best_c = c, best_s = s2;
+    for (int d = kScoreProducerWarps; d >= 1; --d)
+      if (s2 % d == 0) { pr = d; break; }
+    if (c + 2 * pr > best_c + 2 * best_p || s2 == stages) best_c = c, best_p = pr, best_s = s2;
   }
   stages = best_s;
   p.stages = stages;
   p.consumers = best_c;
+  p.producers = best_p;
   const size_t smem = score_smem_layout(stages, p.hq, p.hkv, p.batch, FUSED).total;
   auto kern = quest_page_score_kernel<NT, FUSED>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -731,6 +790,7 @@ static ScoreParams make_score_params(const void* q, int64_t q_stride_b, const vo
   p.page_table = page_table; p.pt_stride = pt_stride; p.req_rows = req_rows;
   p.context_lens = context_lens; p.scores = (uint16_t*)scores; p.score_stride = score_stride;
   p.batch = batch; p.hq = hq; p.hkv = hkv; p.n_cols = n_cols;
+  p.dbg_times = debug_times_buffer();
   return p;
 }
 
