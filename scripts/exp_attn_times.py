@@ -42,3 +42,25 @@ print("fastest CTAs (cta, sm, dur):", [(int(i), int(t[i, 7]), round(float(dur[i]
 print("slowest CTAs (cta, sm, dur):", [(int(i), int(t[i, 7]), round(float(dur[i]), 1)) for i in order[-6:]])
 hist = torch.histc(dur, bins=10, min=float(dur.min()), max=float(dur.max()))
 print("duration histogram", float(dur.min()), float(dur.max()), hist.tolist())
+# second launch with other pages: are the same SMs slow (position) or is it the data (random pages)?
+pages2 = torch.stack([torch.randperm(num_pages, device=dev)[:sel_pages] for _ in range(B)])
+table2 = (pages2[:, :, None] * 16 + torch.arange(16, device=dev)[None, None]).reshape(B, -1).to(torch.int32).contiguous()
+durs = {}
+for name, tb in (("same", table), ("other", table2), ("same2", table)):
+    flush.zero_()
+    buf.zero_()
+    lib.svb200_debug_times(buf.data_ptr())
+    ops.sparse_decode_attn(q, k, v, tb, req, lens, out=out, workspace=ws)
+    torch.cuda.synchronize()
+    lib.svb200_debug_times(None)
+    tt = buf.view(148, 8).cpu()
+    d = (tt[:, 3] - tt[:, 0]).float() / 1000.0
+    bysm = torch.zeros(148)
+    bysm[tt[:, 7].long()] = d
+    durs[name] = (d, bysm)
+print("corr by CTA  first/same:", float(torch.corrcoef(torch.stack([dur, durs['same'][0]]))[0, 1]),
+      " same/other:", float(torch.corrcoef(torch.stack([durs['same'][0], durs['other'][0]]))[0, 1]))
+print("corr by SM   same/other:", float(torch.corrcoef(torch.stack([durs['same'][1], durs['other'][1]]))[0, 1]),
+      " same/same2:", float(torch.corrcoef(torch.stack([durs['same'][1], durs['same2'][1]]))[0, 1]))
+pd = (t[:, 4] - t[:, 0]).float() / 1000.0
+print("producer0 done - by CTA index (first 148):", [round(float(x), 1) for x in pd.tolist()])
