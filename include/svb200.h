@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SVB200_ABI_VERSION 2
+#define SVB200_ABI_VERSION 3
 
 enum {
   SVB200_OK = 0,
@@ -47,6 +47,19 @@ int svb200_sm_count(void);
  * different places; results do not depend on it.
  */
 int svb200_set_max_ctas(int32_t n);
+/*
+ * Experiment knob `which` (0 = row groups of the score scheduler, 1 = row groups of the attention
+ * scheduler) := value; 0 restores the automatic choice.  Returns the previous value, -1 for an
+ * unknown knob.  Results never depend on it.
+ */
+int svb200_set_tuning(int32_t which, int32_t value);
+/*
+ * int32 entries of the scheduler scratch the persistent score kernels need for `rows` batch rows
+ * (1 + 2*rows: finished-CTA count, next chunk per row, scored units per row).  Zero-initialise it
+ * once; the last CTA of every launch leaves it zeroed.  One scratch per stream: two launches that
+ * may run concurrently must not share it.
+ */
+int64_t svb200_sched_scratch_ints(int32_t rows);
 /*
  * Experiments only: when device_buffer != NULL the attention kernel writes 8 uint64 per CTA
  * (globaltimer ns at entry, after setup, first data, consumers done, producer done, -, -, SM id).
@@ -120,6 +133,9 @@ int svb200_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
  *   req_rows     [batch] int32 row of each batch entry in page_table
  *   context_lens [batch] int32
  *   scores       [batch][score_stride] bf16 out, score_stride >= n_cols
+ *   sched_scratch svb200_sched_scratch_ints(batch) zeroed int32 (left zeroed)
+ * Work is claimed dynamically (chunks of 32 pages from per-row counters), so SMs the memory
+ * system serves faster score more pages; the result does not depend on who scored what.
  */
 int svb200_quest_page_score(const void* q, int64_t q_stride_b,
                             const void* bounds_layer, int64_t num_pages,
@@ -127,7 +143,8 @@ int svb200_quest_page_score(const void* q, int64_t q_stride_b,
                             int64_t page_table_stride, const int32_t* req_rows,
                             const int32_t* context_lens, void* scores,
                             int64_t score_stride, int32_t batch, int32_t num_q_heads,
-                            int32_t num_kv_heads, int32_t n_cols, void* stream);
+                            int32_t num_kv_heads, int32_t n_cols, int32_t* sched_scratch,
+                            void* stream);
 
 /*
  * Top-k page selection + slot packing for one layer (quest.py:1887-1913):
@@ -156,8 +173,9 @@ int svb200_quest_select_pack(const void* scores, int64_t score_stride,
 
 /*
  * Fused score + select + pack: same results as the two calls above with one
- * launch (the last CTA to finish a row's page tiles performs its selection).
- *   tickets [batch] int32 zero-initialised scratch (left zeroed).
+ * launch (the CTA that scores a row's last pages performs its selection while the
+ * others go on with the next rows).
+ *   tickets  svb200_sched_scratch_ints(batch) zero-initialised int32 scratch (left zeroed).
  */
 int svb200_quest_score_select_pack(
     const void* q, int64_t q_stride_b, const void* bounds_layer, int64_t num_pages,

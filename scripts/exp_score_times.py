@@ -19,27 +19,42 @@ req = torch.arange(bsz, dtype=torch.int32, device=dev)
 scores = torch.empty(bsz, ops.score_row_stride(n_cols), dtype=torch.bfloat16, device=dev)
 packed = torch.zeros(bsz, (prev + 1) * 16, dtype=torch.int32, device=dev)
 lens = torch.zeros(bsz, dtype=torch.int32, device=dev)
-tickets = torch.zeros(bsz, dtype=torch.int32, device=dev)
+tickets = ops.sched_scratch(bsz, dev)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-buf = torch.zeros(148 * 8, dtype=torch.int64, device=dev)
+buf = torch.zeros(148 * 16, dtype=torch.int64, device=dev)
 lib = _native.load()
-for it in range(4):
-    flush.zero_()
-    if it == 3:
-        lib.svb200_debug_times(buf.data_ptr())
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    ops.quest_score_select_pack(q, bounds, pt, req, ctx_lens, n_cols, hkv, prev, scores, packed, lens, tickets, None)
-    e1.record(); torch.cuda.synchronize()
-    print("launch", it, e0.elapsed_time(e1) * 1e3, "us")
-lib.svb200_debug_times(None)
-t = buf.view(148, 8).cpu()
-t0 = int(t[:, 0].min())
-rel = (t[:, :5] - t0).float() / 1000.0
-for name, col in (("entry", 0), ("setup", 1), ("first data", 2), ("consumers done", 3), ("producer done", 4)):
-    c = rel[:, col]
-    print(f"{name:15s} min {c.min():7.2f} med {c.median():7.2f} max {c.max():7.2f}")
-sel = t[:, 5].float() / 1000.0
-print("select time per CTA (us): n>0", int((sel > 0).sum()), "mean of those", float(sel[sel > 0].mean()), "max", float(sel.max()))
-dur = rel[:, 3] - rel[:, 0]
-print("duration histogram", float(dur.min()), float(dur.max()), torch.histc(dur, bins=10, min=float(dur.min()), max=float(dur.max())).tolist())
+import os
+for cfg in (sys.argv[1] if len(sys.argv) > 1 else "0:0:0").split(","):
+    groups, minb, sdiv = (int(x) for x in cfg.split(":"))
+    ops.set_tuning(0, groups); ops.set_tuning(2, minb); ops.set_tuning(3, sdiv)
+    buf.zero_()
+    for it in range(4):
+        flush.zero_()
+        if it == 3:
+            lib.svb200_debug_times(buf.data_ptr())
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ops.quest_score_select_pack(q, bounds, pt, req, ctx_lens, n_cols, hkv, prev, scores, packed, lens, tickets, None)
+        e1.record(); torch.cuda.synchronize()
+        if it >= 2:
+            print("groups:minbatch:sharediv", cfg, "launch", it, round(e0.elapsed_time(e1) * 1e3, 1), "us")
+    lib.svb200_debug_times(None)
+    t = buf.view(148, 16).cpu()
+    t0 = int(t[:, 0].min())
+    rel = (t[:, :5] - t0).float() / 1000.0
+    for name, col in (("first data", 2), ("consumers done", 3), ("producer done", 4)):
+        c = rel[:, col]
+        print(f"  {name:15s} min {c.min():7.2f} med {c.median():7.2f} max {c.max():7.2f}")
+    sel = t[:, 5].float() / 1000.0
+    units = t[:, 6].float()
+    w = t[:, 8:13].float().median(dim=0).values / 1000.0
+    print("  median waits us: producer0 desc", round(float(w[0]), 1), "empty", round(float(w[1]), 1), "ids", round(float(w[2]), 1),
+          "| consumer warp0 desc", round(float(w[3]), 1), "full", round(float(w[4]), 1))
+    ph = t[:, 13:16].float() / 1000.0
+    m = sel > 0
+    if m.any():
+        print("  select phases us (mean over selecting CTAs): load", round(float(ph[m, 0].mean()), 1), "search", round(float(ph[m, 1].mean()), 1), "compact+pack", round(float(ph[m, 2].mean()), 1))
+    rate = units / (rel[:, 4] - rel[:, 2]).clamp(min=1.0)
+    print("  select us: n>0", int((sel > 0).sum()), "mean", round(float(sel[sel > 0].mean()), 1), "max", round(float(sel.max()), 1),
+          "| units/CTA min", int(units.min()), "med", int(units.median()), "max", int(units.max()), "sum", int(units.sum()),
+          "| units/us while streaming: min", round(float(rate.min()), 2), "med", round(float(rate.median()), 2), "max", round(float(rate.max()), 2))

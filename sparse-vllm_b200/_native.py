@@ -14,7 +14,7 @@ from pathlib import Path
 import torch
 
 _LIB_PATH = Path(__file__).resolve().parent / "lib" / "libsvb200.so"
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 # name -> (restype, argtypes); mirrors include/svb200.h one to one.
 _P = c_void_p
@@ -23,6 +23,8 @@ _SIGNATURES = {
     "svb200_last_error": (c_char_p, []),
     "svb200_sm_count": (c_int32, []),
     "svb200_set_max_ctas": (c_int32, [c_int32]),
+    "svb200_set_tuning": (c_int32, [c_int32, c_int32]),
+    "svb200_sched_scratch_ints": (c_int64, [c_int32]),
     "svb200_debug_times": (None, [_P]),
     "svb200_workspace_bytes": (c_int64, [c_int32, c_int32, c_int32]),
     "svb200_quest_page_minmax": (c_int32, [_P, _P, _P, c_int32, c_int32, c_int64, _P]),
@@ -30,7 +32,7 @@ _SIGNATURES = {
         c_int32, [_P, _P, _P, c_int64, _P, _P, c_int32, c_int32, c_int32, c_int64, c_int64, _P]),
     "svb200_quest_page_score": (
         c_int32, [_P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32, c_int32, c_int32,
-                  _P]),
+                  _P, _P]),
     "svb200_quest_select_pack": (
         c_int32, [_P, c_int64, c_int32, _P, c_int64, _P, _P, c_int32, c_int32, _P, c_int64, _P, _P, _P,
                   c_int64, c_int32, c_int32, c_int32, _P]),

@@ -86,7 +86,7 @@ class QuestCacheManager(CacheManager):
                 scores=torch.empty((batch, stride), dtype=torch.bfloat16, device=self.device),
                 packed=torch.zeros((batch, width), dtype=torch.int32, device=self.device),
                 lens=torch.zeros((batch,), dtype=torch.int32, device=self.device),
-                tickets=torch.zeros((batch,), dtype=torch.int32, device=self.device),
+                tickets=ops.sched_scratch(batch, self.device),
                 arange=torch.arange(batch, dtype=torch.int32, device=self.device))
             self._scratch[key] = s
         return s

@@ -40,6 +40,8 @@ int sm_count() {
 
 static unsigned long long* g_dbg_times = nullptr;
 unsigned long long* debug_times_buffer() { return g_dbg_times; }
+static int g_tuning[kTuneCount] = {0};
+int tuning(int which) { return (which >= 0 && which < kTuneCount) ? g_tuning[which] : 0; }
 static int g_max_ctas = 0;
 int max_ctas() {
   const int n = sm_count();
@@ -84,6 +86,14 @@ int svb200_set_max_ctas(int32_t n) {
   g_max_ctas = n > 0 ? n : 0;
   return prev;
 }
+
+int svb200_set_tuning(int32_t which, int32_t value) {
+  if (which < 0 || which >= kTuneCount) return -1;
+  const int prev = g_tuning[which];
+  g_tuning[which] = value;
+  return prev;
+}
+int64_t svb200_sched_scratch_ints(int32_t rows) { return rows < 0 ? -1 : 1 + 2 * (int64_t)rows; }
 
 static int64_t ws_ticket_bytes(int64_t batch, int64_t hkv) {
   return ((batch * hkv * (int64_t)sizeof(int32_t) + 255) / 256) * 256;
@@ -151,16 +161,17 @@ int svb200_quest_page_score(const void* q, int64_t q_stride_b, const void* bound
                             int64_t num_pages, const int32_t* page_table, int64_t page_table_stride,
                             const int32_t* req_rows, const int32_t* context_lens, void* scores,
                             int64_t score_stride, int32_t batch, int32_t num_q_heads,
-                            int32_t num_kv_heads, int32_t n_cols, void* stream) {
+                            int32_t num_kv_heads, int32_t n_cols, int32_t* sched_scratch, void* stream) {
   SV_REQUIRE(batch >= 0, "quest_page_score: batch=%d < 0", batch);
   if (batch == 0) return 0;
+  SV_REQUIRE(sched_scratch != nullptr, "quest_page_score: sched_scratch is null");
   if (int rc = check_score_args("quest_page_score", q, q_stride_b, bounds_layer, num_pages, page_table,
                                 page_table_stride, req_rows, context_lens, scores, score_stride,
                                 batch, num_q_heads, num_kv_heads, n_cols))
     return rc;
   return launch_quest_page_score(q, q_stride_b, bounds_layer, num_pages, page_table, page_table_stride,
                                  req_rows, context_lens, scores, score_stride, batch, num_q_heads,
-                                 num_kv_heads, n_cols, (cudaStream_t)stream);
+                                 num_kv_heads, n_cols, sched_scratch, (cudaStream_t)stream);
 }
 
 static int check_select_args(const char* who, int n_cols, int prev_budget, const int32_t* packed,

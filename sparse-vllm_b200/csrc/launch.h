@@ -13,6 +13,9 @@ int check_launch(const char* what);
 int sm_count();
 unsigned long long* debug_times_buffer();
 int max_ctas();  // persistent-grid size: sm_count() unless svb200_set_max_ctas lowered it
+// experiment knobs (svb200_set_tuning); 0 = automatic
+enum { kTuneScoreGroups = 0, kTuneAttnGroups = 1, kTuneMinBatch = 2, kTuneShareDiv = 3, kTuneCount = 8 };
+int tuning(int which);
 
 // quest.cu
 int launch_quest_page_minmax(const void* k_cache, void* bounds_layer, const int32_t* slot_mapping,
@@ -25,7 +28,7 @@ int launch_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
 int launch_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds, int64_t num_pages,
                             const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
                             const int32_t* context_lens, void* scores, int64_t score_stride,
-                            int batch, int hq, int hkv, int n_cols, cudaStream_t stream);
+                            int batch, int hq, int hkv, int n_cols, int32_t* sched, cudaStream_t stream);
 int launch_quest_select_pack(const void* scores, int64_t score_stride, int n_cols,
                              const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
                              const int32_t* context_lens, int batch, int k, int32_t* packed_slots,

@@ -7,6 +7,7 @@
 //   select  : _build_decode_view_static 1833-1913
 #include "common.cuh"
 #include "launch.h"
+#include "sched.cuh"
 
 namespace svb200 {
 
@@ -90,29 +91,30 @@ __global__ void __launch_bounds__(128) quest_decode_page_complete_kernel(
 constexpr int kMaxPrevBudget = 2047;
 
 struct SelectSmem {
-  int hist[256];
-  int warp_scan[32];
-  int bcast[4];
+  int cnt[16];
+  int warp_scan[33];
   int sel[kMaxPrevBudget + 1];
   int sel_slot[kMaxPrevBudget + 1];
 };
 
 constexpr uint32_t kNegInfKey = 0x007fu;  // order key of bf16 -inf (0xff80)
-// bf16 bit pattern -> 16-bit key that orders like the float value.
+// bf16 bit pattern -> 16-bit key that orders like the float value; never 0 (0 = "no such column").
 __device__ __forceinline__ uint32_t bf16_order_key(uint32_t bits) {
-  return (bits & 0x8000u) ? (~bits & 0xffffu) : (bits | 0x8000u);
+  const uint32_t k = (bits & 0x8000u) ? (~bits & 0xffffu) : (bits | 0x8000u);
+  return k ? k : 1u;
 }
 
 // Barrier over the first NTHR threads of the CTA (barrier 0 = __syncthreads when NTHR is the
-// whole block; the fused scoring kernel keeps its producer warp out with barrier 1).
+// whole block; the fused scoring kernel keeps its producer warps out with barrier 1).
 template <int BAR, int NTHR>
 __device__ __forceinline__ void group_sync() {
   asm volatile("bar.sync %0, %1;" ::"n"(BAR), "n"(NTHR) : "memory");
 }
 
-template <int BAR, int NTHR>
-__device__ __forceinline__ int block_exclusive_scan(int v, int* warp_scan) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = NTHR >> 5;
+// Exclusive prefix of v over the group's threads; `total` receives the sum over the group.
+template <int BAR, int NTHR, int TID0>
+__device__ __forceinline__ int block_exclusive_scan(int v, int* warp_scan, int& total) {
+  const int lane = threadIdx.x & 31, warp = (threadIdx.x - TID0) >> 5, nwarps = NTHR >> 5;
   int inc = v;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -131,143 +133,126 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* warp_scan) {
       if (lane >= o) winc += n;
     }
     warp_scan[lane] = winc - w;  // exclusive prefix of the warp totals
+    if (lane == 31) warp_scan[32] = winc;
   }
   group_sync<BAR, NTHR>();
+  total = warp_scan[32];
   return warp_scan[warp] + inc - v;
-}
-
-// Finds the bin holding the k-th largest item: largest bin B with sum(hist[B..255]) >= k.
-// Returns B and the count strictly above it.  Executed by warp 0; result via bcast.
-__device__ __forceinline__ void find_kth_bin(const int* hist, int k, int* bcast) {
-  const int lane = threadIdx.x & 31;
-  // lane L owns bins [8L, 8L+8); higher lanes = higher bins.
-  int local[8];
-  int lsum = 0;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    local[i] = hist[lane * 8 + i];
-    lsum += local[i];
-  }
-  // suffix sum over lanes (inclusive)
-  int suf = lsum;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    int n = __shfl_down_sync(0xffffffffu, suf, o);
-    if (lane + o < 32) suf += n;
-  }
-  const int above_lane = suf - lsum;  // items in bins of higher lanes
-  // the owning lane: above_lane < k <= suf
-  if (above_lane < k && k <= suf) {
-    int above = above_lane;
-    int bin = lane * 8 + 7;
-#pragma unroll
-    for (int i = 7; i >= 0; --i) {
-      if (above + local[i] >= k) {
-        bin = lane * 8 + i;
-        break;
-      }
-      above += local[i];
-    }
-    bcast[0] = bin;
-    bcast[1] = above;
-  }
 }
 
 // scores_row: bf16 bits, 16-byte aligned, readable up to round_up(n_cols, 8).
 // Columns >= n_valid count as -inf whatever the buffer holds (quest.py:1883-1885).
-// Three passes over the row (high-byte histogram, low-byte histogram, ordered compaction); each
-// thread owns a contiguous chunk of 8-score vectors.  CACHED keeps the chunk in registers so the
-// row is read from L2 once (rows up to 4 * NTHR vectors = 8192 scores at 256 threads).
+// The k-th largest 16-bit order key is found by a bitwise binary search (16 counting rounds over keys
+// held in registers, one barrier each); a single ordered compaction then takes every key above it and
+// the lowest-indexed ties.  Each thread owns a contiguous chunk of 8-score vectors.  CACHED keeps the
+// chunk in registers so the row is read from L2 once (rows up to 4 * NTHR vectors = 8192 scores at
+// 256 threads); longer rows re-read it every round.
 constexpr int kSelectVecPerThread = 4;
 
-template <int BAR, int NTHR, bool CACHED>
+template <int BAR, int NTHR, bool CACHED, int TID0>
 __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, int n_cols, int n_valid,
                                        int k, const int32_t* __restrict__ pt_row, int ctx,
                                        int32_t* __restrict__ out_row, int32_t* __restrict__ len_out,
-                                       int32_t* __restrict__ sel_pages_out, SelectSmem& sm) {
+                                       int32_t* __restrict__ sel_pages_out, SelectSmem& sm,
+                                       unsigned long long* tdbg = nullptr) {
   constexpr int VPT = kSelectVecPerThread;
-  const int tid = threadIdx.x;
+  const unsigned long long tq0 = tdbg ? global_timer_ns() : 0;
+  const int tid = threadIdx.x - TID0, lane = tid & 31;  // TID0: first thread of the group (a warp boundary)
   const int nvec = (n_cols + 7) >> 3;
   const uint4* vrow = reinterpret_cast<const uint4*>(scores_row);
   const int vec_per_thr = CACHED ? VPT : (nvec + NTHR - 1) / NTHR;
   const int v_begin = min(tid * vec_per_thr, nvec), v_end = min(v_begin + vec_per_thr, nvec);
-  uint4 xr[VPT];
+  // one vector of 8 scores -> 4 words of packed order keys (low half = even column)
+  auto to_keys = [&](int v, const uint4& x, uint32_t (&out)[4]) {
+    const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c0 = v * 8 + 2 * i, c1 = c0 + 1;
+      const uint32_t lo = c0 >= n_cols ? 0u : (c0 < n_valid ? bf16_order_key(w[i] & 0xffffu) : kNegInfKey);
+      const uint32_t hi = c1 >= n_cols ? 0u : (c1 < n_valid ? bf16_order_key(w[i] >> 16) : kNegInfKey);
+      out[i] = lo | (hi << 16);
+    }
+  };
+  uint32_t kw[VPT][4];
   if constexpr (CACHED) {
 #pragma unroll
-    for (int vv = 0; vv < VPT; ++vv)
-      xr[vv] = v_begin + vv < v_end ? __ldcg(vrow + v_begin + vv) : make_uint4(0, 0, 0, 0);
-  }
-  // body(col, key, valid) for every column slot of this thread's chunk, in ascending column order.
-  // Control flow is warp-uniform (invalid slots are passed with valid = false) so bodies may use
-  // full-mask warp primitives.
-  auto for_each_key = [&](auto&& body) {
-    auto one_vec = [&](int v, bool vec_ok, const uint4& x) {
-      const uint32_t w[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int col = v * 8 + i;
-        body(col, col < n_valid ? bf16_order_key((w[i >> 1] >> ((i & 1) * 16)) & 0xffffu) : kNegInfKey,
-             vec_ok && col < n_cols);
+    for (int vv = 0; vv < VPT; ++vv) {
+      if (v_begin + vv < v_end) {
+        to_keys(v_begin + vv, __ldcg(vrow + v_begin + vv), kw[vv]);
+      } else {
+        kw[vv][0] = kw[vv][1] = kw[vv][2] = kw[vv][3] = 0u;
       }
-    };
+    }
+  }
+  // body(first column of the word, packed key word), ascending column order
+  auto for_each_word = [&](auto&& body) {
     if constexpr (CACHED) {
 #pragma unroll
-      for (int vv = 0; vv < VPT; ++vv) one_vec(v_begin + vv, v_begin + vv < v_end, xr[vv]);
+      for (int vv = 0; vv < VPT; ++vv)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) body((v_begin + vv) * 8 + 2 * i, kw[vv][i]);
     } else {
-      for (int vv = 0; vv < vec_per_thr; ++vv) {
-        const bool ok = v_begin + vv < v_end;
-        one_vec(v_begin + vv, ok, ok ? __ldcg(vrow + v_begin + vv) : make_uint4(0, 0, 0, 0));
+      for (int v = v_begin; v < v_end; ++v) {
+        uint32_t w[4];
+        to_keys(v, __ldcg(vrow + v), w);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) body(v * 8 + 2 * i, w[i]);
       }
     }
   };
-  // Histogram increment aggregated over the lanes that hit the same bin: page scores crowd into a
-  // few exponent bins, and one shared-memory atomic per lane would serialise on them.
-  auto hist_add = [&](int bin, bool valid) {
-    const unsigned peers = __match_any_sync(0xffffffffu, valid ? bin : -1);
-    if (valid && (tid & 31) == __ffs(peers) - 1) atomicAdd(&sm.hist[bin], __popc(peers));
-  };
 
-  // ---- pass 1: histogram of the high key byte
-  for (int i = tid; i < 256; i += NTHR) sm.hist[i] = 0;
+  // ---- k-th largest key: largest T with count(key >= T) >= k
+  const unsigned long long tq1 = tdbg ? global_timer_ns() : 0;
+  if (tid < 16) sm.cnt[tid] = 0;
   group_sync<BAR, NTHR>();
-  for_each_key([&](int, uint32_t key, bool valid) { hist_add(key >> 8, valid); });
-  group_sync<BAR, NTHR>();
-  if (tid < 32) find_kth_bin(sm.hist, k, sm.bcast);
-  group_sync<BAR, NTHR>();
-  const int bin1 = sm.bcast[0];
-  const int k1 = k - sm.bcast[1];
-  group_sync<BAR, NTHR>();
-
-  // ---- pass 2: histogram of the low byte inside bin1
-  for (int i = tid; i < 256; i += NTHR) sm.hist[i] = 0;
-  group_sync<BAR, NTHR>();
-  for_each_key([&](int, uint32_t key, bool valid) {
-    hist_add(key & 0xff, valid && (int)(key >> 8) == bin1);
-  });
-  group_sync<BAR, NTHR>();
-  if (tid < 32) find_kth_bin(sm.hist, k1, sm.bcast);
-  group_sync<BAR, NTHR>();
-  const uint32_t thresh = ((uint32_t)bin1 << 8) | (uint32_t)sm.bcast[0];
-  const int need_eq = k1 - sm.bcast[1];  // how many keys == thresh to take (lowest index first)
-  group_sync<BAR, NTHR>();
-
-  // ---- pass 3: ordered compaction
-  int cnt_gt = 0, cnt_eq = 0;
-  for_each_key([&](int, uint32_t key, bool valid) {
-    cnt_gt += valid && key > thresh;
-    cnt_eq += valid && key == thresh;
-  });
-  const int eq_before = block_exclusive_scan<BAR, NTHR>(cnt_eq, sm.warp_scan);
-  const int eq_take = max(0, min(cnt_eq, need_eq - eq_before));
-  int pos = block_exclusive_scan<BAR, NTHR>(cnt_gt + eq_take, sm.warp_scan);
-  int eq_left = eq_take;
-  for_each_key([&](int col, uint32_t key, bool valid) {
-    bool take = valid && key > thresh;
-    if (valid && key == thresh && eq_left > 0) {
-      take = true;
-      --eq_left;
+  uint32_t thresh = 0;
+  for (int bit = 15; bit >= 0; --bit) {
+    const uint32_t cand = thresh | (1u << bit), cand_hi = cand << 16;
+    int c = 0;
+    if constexpr (CACHED) {
+      int ca[4] = {0, 0, 0, 0};  // independent chains: the adds would otherwise serialise
+#pragma unroll
+      for (int vv = 0; vv < VPT; ++vv)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          ca[i] += (kw[vv][i] >= cand_hi) ? 1 : 0;
+          ca[(i + 2) & 3] += ((kw[vv][i] & 0xffffu) >= cand) ? 1 : 0;
+        }
+      c = (ca[0] + ca[1]) + (ca[2] + ca[3]);
+    } else {
+      for_each_word([&](int, uint32_t w) {
+        c += (w >= cand_hi) ? 1 : 0;
+        c += ((w & 0xffffu) >= cand) ? 1 : 0;
+      });
     }
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0 && c) atomicAdd(&sm.cnt[bit], c);
+    group_sync<BAR, NTHR>();
+    if (sm.cnt[bit] >= k) thresh = cand;
+  }
+
+  // ---- ordered compaction: keys above thresh, then the lowest-indexed ties
+  const unsigned long long tq2 = tdbg ? global_timer_ns() : 0;
+  int cnt_gt = 0, cnt_eq = 0;
+  for_each_word([&](int, uint32_t w) {
+    const uint32_t lo = w & 0xffffu, hi = w >> 16;
+    cnt_gt += (lo > thresh) + (hi > thresh);
+    cnt_eq += (lo == thresh && lo) + (hi == thresh && hi);
+  });
+  int total;
+  const int before = block_exclusive_scan<BAR, NTHR, TID0>(cnt_gt | (cnt_eq << 16), sm.warp_scan, total);
+  const int need_eq = k - (total & 0xffff);  // ties to take
+  const int eq_before = before >> 16;
+  int pos = (before & 0xffff) + min(eq_before, need_eq);
+  int eq_left = max(0, min(cnt_eq, need_eq - eq_before));
+  for_each_word([&](int col, uint32_t w) {
+    const uint32_t lo = w & 0xffffu, hi = w >> 16;
+    bool take = lo > thresh;
+    if (lo == thresh && lo && eq_left > 0) take = true, --eq_left;
     if (take) sm.sel[pos++] = col;
+    take = hi > thresh;
+    if (hi == thresh && hi && eq_left > 0) take = true, --eq_left;
+    if (take) sm.sel[pos++] = col + 1;
   });
   // last page (quest.py:1888-1889: safe_num_pages - 1)
   const int num_pages = (ctx + kPage - 1) / kPage;
@@ -287,19 +272,24 @@ __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, 
   }
   if (tid == 0) *len_out = k * kPage + (ctx - (num_pages - 1) * kPage);
   group_sync<BAR, NTHR>();
+  if (tdbg && tid == 0) {
+    const unsigned long long tq3 = global_timer_ns();
+    tdbg[0] += tq1 - tq0, tdbg[1] += tq2 - tq1, tdbg[2] += tq3 - tq2;
+  }
 }
 
-template <int BAR, int NTHR>
+template <int BAR, int NTHR, int TID0 = 0>
 __device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, int n_cols, int n_valid, int k,
                                       const int32_t* __restrict__ pt_row, int ctx,
                                       int32_t* __restrict__ out_row, int32_t* __restrict__ len_out,
-                                      int32_t* __restrict__ sel_pages_out, SelectSmem& sm) {
+                                      int32_t* __restrict__ sel_pages_out, SelectSmem& sm,
+                                      unsigned long long* tdbg = nullptr) {
   if (((n_cols + 7) >> 3) <= kSelectVecPerThread * NTHR)
-    quest_select_pack_impl<BAR, NTHR, true>(scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out,
-                                            sel_pages_out, sm);
+    quest_select_pack_impl<BAR, NTHR, true, TID0>(scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out,
+                                            sel_pages_out, sm, tdbg);
   else
-    quest_select_pack_impl<BAR, NTHR, false>(scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out,
-                                             sel_pages_out, sm);
+    quest_select_pack_impl<BAR, NTHR, false, TID0>(scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out,
+                                             sel_pages_out, sm, tdbg);
 }
 
 __global__ void __launch_bounds__(256) quest_select_pack_kernel(
@@ -338,25 +328,30 @@ __global__ void __launch_bounds__(256) quest_select_pack_kernel(
 // =========================================================================
 // Page scoring (+ fused top-k / packing).
 //
-// Stream-K over page tiles: a "unit" is 16 consecutive logical pages of one batch
-// row; only valid pages (p < ceil(ctx/16) - 1) form units.  The launch's units are
-// cut into one equal contiguous range per persistent CTA.  Warps 8-11 (producers)
-// resolve 16 page slots through the page table and copy each page's bounds record
-// ([2][Hkv][128] = Hkv*512 contiguous bytes) with 16-byte LDGSTS, a warp per 512 B,
-// into a ring of S stages (130-200 KB in flight per SM) whose mbarriers complete
-// when the copies land.  Warps 0-7
-// (consumers) take units round-robin; per unit and KV head:
+// A "unit" is 16 consecutive logical pages of one batch row; only valid pages
+// (p < ceil(ctx/16) - 1) form units.  Units are handed out dynamically (sched.cuh): a
+// scheduler warp claims chunks of 2 units from per-row counters; the CTAs of a group walk
+// the group's rows one after the other, so rows finish at staggered times and the top-k of
+// a finished row runs while the other CTAs keep streaming the next row.
+// Producer warps resolve the 2 x 16 page slots of a chunk through the page table (fetched
+// kIdDepth chunks ahead) and copy each page's bounds record ([2][Hkv][128] = Hkv*512
+// contiguous bytes) with 16-byte LDGSTS, a warp per 512 B, into a ring of S stages
+// (~200 KB in flight per SM) whose mbarriers complete when the copies land.  Consumer warps
+// take units round-robin; per unit and KV head:
 //   A = bounds rows (16 pages x 128, ldmatrix), B = q+ / q- (128 x 8 heads)
 //   score = bf16(bf16(A_max.q+) + bf16(A_min.q-)), then max over all local heads.
-// When the last contributor of a row finishes (arrival ticket), its consumer
-// warps run the top-k selection and slot packing for that row in the same launch.
+// A CTA leaving a row adds the units it scored to the row's counter; the CTA that completes
+// the row runs the top-k selection and slot packing for it in the same launch.
 // =========================================================================
-constexpr int kScoreConsumerWarps = 8;
+constexpr int kScoreConsumerWarps = 6;
 constexpr int kScoreConsumerThreads = kScoreConsumerWarps * 32;
-constexpr int kScoreProducerWarps = 4;
-constexpr int kPagePrefetch = 6;
-constexpr int kScoreThreads = kScoreConsumerThreads + kScoreProducerWarps * 32;
+constexpr int kScoreProducerWarps = 6;  // + 1 scheduler warp
+constexpr int kIdDepth = 3;             // chunks whose page ids are in flight ahead of the copies
+constexpr int kScoreSelectWarps = 8;     // dedicated top-k warps: the stream never waits for a selection
+constexpr int kScoreSelectThreads = kScoreSelectWarps * 32;
+constexpr int kScoreThreads = kScoreConsumerThreads + (kScoreProducerWarps + 1) * 32 + kScoreSelectThreads;
 constexpr int kScoreMaxSmem = 227 * 1024;
+static_assert(kIdDepth < kSchedQueue, "producers read kIdDepth descriptors ahead of the one they issue");
 
 struct ScoreParams {
   const __nv_bfloat16* q;
@@ -373,17 +368,19 @@ struct ScoreParams {
   unsigned long long* dbg_times;  // experiments: per-CTA timestamps (svb200_debug_times), else null
   int consumers;  // consumer warps that take units; divides `stages` (see the kernel)
   int producers;  // producer warps that feed units; divides `stages`
+  int groups;     // row groups of the scheduler
+  int min_batch, share_div;  // guided claim size = max(min_batch, left / (share_div * CTAs per group))
+  int32_t* sched;  // sched_scratch_ints(batch) zeroed ints
   // fused select only
   int k;
   int32_t* packed_slots;
   int64_t out_stride;
   int32_t* sparse_lens;
   int32_t* selected_pages;
-  int32_t* tickets;
 };
 
 struct ScoreSmemLayout {
-  int ring_off, q_off, bar_off, valid_off, prefix_off, select_off, total;
+  int ring_off, q_off, bar_off, valid_off, rows_off, sched_off, select_off, total;
 };
 
 __host__ __device__ inline int score_rec_stride(int hkv) { return hkv * 2 * kRowBytes + 16; }
@@ -396,17 +393,14 @@ __host__ __device__ inline ScoreSmemLayout score_smem_layout(int stages, int hq,
   L.q_off = off;      off += 2 * hq * kRowBytes;
   L.bar_off = off;    off += 2 * stages * 8;
   L.valid_off = off;  off += ((stages * 4 + 15) / 16) * 16;
-  L.prefix_off = off; off += ((batch + 1) * 4 + 15) / 16 * 16;
+  L.rows_off = off;   off += (2 * batch * 4 + 15) / 16 * 16;  // valid pages, page-table row of each row
+  L.sched_off = off;  off += (int)((sizeof(SchedSmem) + 15) / 16 * 16);
   L.select_off = off; off += fused ? (int)((sizeof(SelectSmem) + 15) / 16 * 16) : 0;
   L.total = off;
   return L;
 }
 
 __device__ __forceinline__ void score_consumer_sync() { group_sync<1, kScoreConsumerThreads>(); }
-
-__device__ __forceinline__ int score_unit_owner(int64_t u, int64_t U, int64_t G) {
-  return (int)(((u + 1) * G + U - 1) / U - 1);
-}
 
 template <int NT, bool FUSED_SELECT>
 __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(ScoreParams p) {
@@ -423,17 +417,19 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.bar_off);
   uint64_t* empty_bar = full_bar + S;
   uint32_t* sValid = reinterpret_cast<uint32_t*>(smem + L.valid_off);
-  int* sPrefix = reinterpret_cast<int*>(smem + L.prefix_off);
+  int* sNv = reinterpret_cast<int*>(smem + L.rows_off);  // valid previous pages of row b
+  int* sReq = sNv + B;                                   // page-table row of row b
+  SchedSmem& sched = *reinterpret_cast<SchedSmem*>(smem + L.sched_off);
   __shared__ int s_flag;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  unsigned long long* dbg = p.dbg_times ? p.dbg_times + (size_t)blockIdx.x * 8 : nullptr;
+  unsigned long long* dbg = p.dbg_times ? p.dbg_times + (size_t)blockIdx.x * 16 : nullptr;
   if (dbg && tid == 0) {
     uint32_t smid;
     asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
     dbg[0] = global_timer_ns();
     dbg[7] = smid;
-    dbg[5] = 0;
+    dbg[2] = dbg[4] = dbg[5] = dbg[6] = dbg[13] = dbg[14] = dbg[15] = 0;
   }
 
   // ---- setup
@@ -442,28 +438,14 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       mbar_init(&full_bar[s], 33);  // 32 async copy arrivals + the producer's release
       mbar_init(&empty_bar[s], 1);
     }
+    sched_init(sched, p.producers + kScoreConsumerWarps);
+    s_flag = 0;
     mbar_fence_init();
   }
-  if (warp == 0) {  // units per row -> exclusive prefix
-    int carry = 0;
-    for (int base = 0; base < B; base += 32) {
-      const int b = base + lane;
-      int n = 0;
-      if (b < B) {
-        const int ctx = p.context_lens[b];
-        const int nv = min(max((ctx + kPage - 1) / kPage, 1) - 1, p.n_cols);
-        n = (nv + 15) >> 4;
-      }
-      int inc = n;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += v;
-      }
-      if (b < B) sPrefix[b] = carry + inc - n;
-      carry += __shfl_sync(0xffffffffu, inc, 31);
-    }
-    if (lane == 0) sPrefix[B] = carry;
+  for (int b = tid; b < B; b += kScoreThreads) {
+    const int ctx = p.context_lens[b];
+    sNv[b] = min(max((ctx + kPage - 1) / kPage, 1) - 1, p.n_cols);
+    sReq[b] = p.req_rows[b];
   }
   // columns no unit covers are -inf (quest.py:1883-1885)
   for (int b = blockIdx.x; b < B; b += gridDim.x) {
@@ -473,81 +455,130 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
     for (int c = ((nv + 15) & ~15) + tid; c < p.n_cols; c += kScoreThreads) srow[c] = 0xff80u;
   }
   __syncthreads();
-
   if (dbg && tid == 0) dbg[1] = global_timer_ns();
-  const int64_t U = sPrefix[B];
-  const int64_t Gn = U < (int64_t)gridDim.x ? U : (int64_t)gridDim.x;
-  const int u0 = Gn > 0 && (int64_t)blockIdx.x < Gn ? (int)(U * blockIdx.x / Gn) : 0;
-  const int u1 = Gn > 0 && (int64_t)blockIdx.x < Gn ? (int)(U * (blockIdx.x + 1) / Gn) : 0;
-  int r_first = 0;
-  if (u1 > u0) {
-    int lo = 0, hi = B;
-    while (hi - lo > 1) {
-      const int mid = (lo + hi) >> 1;
-      if (sPrefix[mid] <= u0) lo = mid; else hi = mid;
-    }
-    r_first = lo;
+  auto units_of_row = [&](int r) { return (sNv[r] + 15) >> 4; };
+  int* next_chunk = p.sched + 1;
+  int* units_done = p.sched + 1 + B;
+
+  if (warp == kScoreConsumerWarps + kScoreProducerWarps) {
+    // ============================================================== scheduler
+    sched_run(sched, next_chunk, B, p.groups, p.min_batch, p.share_div, units_of_row);
+    return;
   }
 
-  if (warp >= kScoreConsumerWarps) {
+  if (warp >= kScoreConsumerWarps && warp < kScoreConsumerWarps + kScoreProducerWarps) {
     // ============================================================== producers
-    // unit i is fed by producer i % NP, NP | S (a stage is always refilled by the same warp)
-    const int n_units = u1 - u0;
+    // unit i (CTA-local running index) is fed by producer i % NP into stage i % S, NP | S: a stage
+    // is always refilled by the same warp.  Lane l holds the physical page of logical page
+    // unit_begin*16 + l of the chunk (2 units x 16 pages), fetched kIdDepth chunks ahead.
     const int pw = warp - kScoreConsumerWarps;
     const int NP = p.producers;
     if (pw >= NP) return;
-    const int pg_lane = lane & 15;
-    int r_pf = r_first;
-    auto row_nv = [&](int r) {
-      const int ctx = p.context_lens[r];
-      return min(max((ctx + kPage - 1) / kPage, 1) - 1, p.n_cols);
-    };
-    int nv_pf = row_nv(r_pf);
-    const int32_t* row_pf = p.page_table + (int64_t)p.req_rows[r_pf] * p.pt_stride;
-    auto fetch = [&](int i) -> int {  // raw physical page of logical page pg_lane in local unit i
-      if (i >= n_units) return -1;
-      const int u = u0 + i;
-      if (sPrefix[r_pf + 1] <= u) {
-        while (sPrefix[r_pf + 1] <= u) ++r_pf;
-        nv_pf = row_nv(r_pf);
-        row_pf = p.page_table + (int64_t)p.req_rows[r_pf] * p.pt_stride;
+    ChunkDesc dq[kIdDepth];
+    int idq[kIdDepth];
+    unsigned long long w_desc = 0, w_empty = 0, w_ids = 0;
+    int n_read = 0;
+    bool ended = false;
+    auto fetch = [&](ChunkDesc& d, int& id) {
+      id = -1;
+      if (ended) {
+        d.row = -1;
+        return;
       }
-      const int col = (u - sPrefix[r_pf]) * 16 + pg_lane;
-      if (col >= nv_pf) return -1;
-      return __ldg(row_pf + col);
+      const unsigned long long tw = dbg ? global_timer_ns() : 0;
+      d = sched_read(sched, n_read++);
+      if (dbg) w_desc += global_timer_ns() - tw;
+      if (d.row < 0) {
+        ended = true;
+        return;
+      }
+      const int col = d.unit_begin * 16 + lane;
+      if (lane < d.n_units * 16 && col < sNv[d.row])
+        id = __ldg(p.page_table + (int64_t)sReq[d.row] * p.pt_stride + col);
     };
-    int s = pw % S;
-    uint32_t ph = (pw / S) & 1;  // phase parity of stage s at unit i
+#pragma unroll
+    for (int t = 0; t < kIdDepth; ++t) fetch(dq[t], idq[t]);
     const char* src0 = reinterpret_cast<const char*>(p.bounds) + lane * 16;
-    // page ids are fetched kPagePrefetch units of this warp ahead (the table comes from DRAM)
-    int pf[kPagePrefetch];
+    // dq / idq form a circular FIFO indexed at compile time (the loop body is unrolled kIdDepth
+    // times): a register that waits for its table load is never moved, so the load's latency is
+    // only paid when the id is finally used, kIdDepth chunks later.
+    bool done = false;
+    while (!done) {
 #pragma unroll
-    for (int d = 0; d < kPagePrefetch; ++d) pf[d] = fetch(pw + d * NP);
-    for (int i = pw; i < n_units; i += NP) {
-      const int page_new = fetch(i + kPagePrefetch * NP);
-      const int pa = pf[0];
-      const int my = (pa >= 0 && pa < p.num_pages) ? pa : -1;
-      const uint32_t mask = __ballot_sync(0xffffffffu, my >= 0) & 0xffffu;
-      const uint32_t dst0 = smem_u32(ring + s * stage_bytes) + lane * 16;
-      mbar_wait(&empty_bar[s], ph ^ 1);
+      for (int u = 0; u < kIdDepth; ++u) {
+        if (done) break;
+        const ChunkDesc cur = dq[u];
+        const int pa = idq[u];
+        fetch(dq[u], idq[u]);
+        if (cur.row < 0) {
+          done = true;
+          break;
+        }
+        const unsigned long long ti = dbg ? global_timer_ns() : 0;
+        const int my = (pa >= 0 && pa < p.num_pages) ? pa : -1;
+        const uint32_t ball = __ballot_sync(0xffffffffu, my >= 0);
+        if (dbg) w_ids += global_timer_ns() - ti;
+        for (int j = 0; j < cur.n_units; ++j) {
+          const int i = cur.unit_base + j;
+          if (i % NP != pw) continue;
+          const int s = i % S;
+          const uint32_t ph = (uint32_t)(i / S) & 1u;
+          const uint32_t dst0 = smem_u32(ring + s * stage_bytes) + lane * 16;
+          const unsigned long long te = dbg ? global_timer_ns() : 0;
+          mbar_wait(&empty_bar[s], ph ^ 1u);
+          if (dbg) w_empty += global_timer_ns() - te;
 #pragma unroll 4
-      for (int pg = 0; pg < kPage; ++pg) {
-        const int page = __shfl_sync(0xffffffffu, my, pg);
-        const int nbytes = page >= 0 ? 16 : 0;
-        const char* src = src0 + (int64_t)max(page, 0) * rec_bytes;
-        const uint32_t dst = dst0 + pg * rec_stride;
-        for (int c = 0; c < hkv; ++c) cp_async_16(dst + c * 512, src + c * 512, nbytes);
+          for (int pg = 0; pg < kPage; ++pg) {
+            const int page = __shfl_sync(0xffffffffu, my, j * 16 + pg);
+            const int nbytes = page >= 0 ? 16 : 0;
+            const char* src = src0 + (int64_t)max(page, 0) * rec_bytes;
+            const uint32_t dst = dst0 + pg * rec_stride;
+            for (int c = 0; c < hkv; ++c) cp_async_16(dst + c * 512, src + c * 512, nbytes);
+          }
+          if (lane == 0) sValid[s] = (ball >> (j * 16)) & 0xffffu;
+          cp_async_mbar_arrive(&full_bar[s]);
+          if (lane == 0) mbar_arrive(&full_bar[s]);  // release: publishes sValid
+        }
       }
-      if (lane == 0) sValid[s] = mask;
-      cp_async_mbar_arrive(&full_bar[s]);
-      if (lane == 0) mbar_arrive(&full_bar[s]);  // release: publishes sValid
-#pragma unroll
-      for (int d = 0; d + 1 < kPagePrefetch; ++d) pf[d] = pf[d + 1];
-      pf[kPagePrefetch - 1] = page_new;
-      s += NP;
-      while (s >= S) s -= S, ph ^= 1;
     }
-    if (dbg && pw == 0 && lane == 0) dbg[4] = global_timer_ns();
+    if (dbg && pw == 0 && lane == 0) dbg[4] = global_timer_ns(), dbg[8] = w_desc, dbg[9] = w_empty, dbg[10] = w_ids;
+    return;
+  }
+
+  if (warp > kScoreConsumerWarps + kScoreProducerWarps) {
+    // ============================================================== select warps
+    // CTA c selects rows c, c + gridDim, ...: it waits until the row's counter shows every unit
+    // scored (the consumers of all CTAs add what they scored when they leave a row), then runs the
+    // top-k and packing.  The stream (producers / consumers) never waits for a selection.
+    if constexpr (FUSED_SELECT) {
+      SelectSmem* sel_sm = reinterpret_cast<SelectSmem*>(smem + L.select_off);
+      const int stid = tid - (kScoreThreads - kScoreSelectThreads);
+      for (int b = blockIdx.x; b < B; b += gridDim.x) {
+        const int need = units_of_row(b);
+        if (need > 0 && stid == 0) {
+          const volatile int* ctr = units_done + b;
+          if (*ctr < need) {
+            const uint64_t t0 = global_timer_ns();
+            while (*ctr < need) {
+              __nanosleep(256);
+              if (global_timer_ns() - t0 > 2000000000ull) __trap();
+            }
+          }
+        }
+        group_sync<2, kScoreSelectThreads>();
+        __threadfence();
+        const unsigned long long ts = dbg ? global_timer_ns() : 0;
+        quest_select_pack_row<2, kScoreSelectThreads, (kScoreThreads - kScoreSelectThreads)>(
+            p.scores + (int64_t)b * p.score_stride, p.n_cols, sNv[b], p.k,
+            p.page_table + (int64_t)sReq[b] * p.pt_stride, p.context_lens[b],
+            p.packed_slots + (int64_t)b * p.out_stride, p.sparse_lens + b,
+            p.selected_pages ? p.selected_pages + (int64_t)b * (p.k + 1) : nullptr, *sel_sm,
+            dbg ? dbg + 13 : nullptr);
+        if (dbg && stid == 0) dbg[5] += global_timer_ns() - ts;
+      }
+      // the CTA's scratch may be recycled once BOTH its consumers and its select warps are done
+      if (stid == 0 && atomicAdd(&s_flag, 1) == 1) sched_finish(p.sched, B);
+    }
     return;
   }
 
@@ -555,61 +586,64 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   const int g = lane >> 2, t = lane & 3;
   const uint2* sq2 = reinterpret_cast<const uint2*>(sq);
   const int neg_off = hq * 32;  // uint2 offset of the q- fragments
-  [[maybe_unused]] SelectSmem* sel_sm = reinterpret_cast<SelectSmem*>(smem + L.select_off);
-
-  if constexpr (FUSED_SELECT) {
-    // rows without a single valid previous page never become a unit: select them here
-    for (int b = blockIdx.x; b < B; b += gridDim.x) {
-      if (sPrefix[b + 1] != sPrefix[b]) continue;
-      const int ctx = p.context_lens[b];
-      quest_select_pack_row<1, kScoreConsumerThreads>(
-          p.scores + (int64_t)b * p.score_stride, p.n_cols, 0, p.k,
-          p.page_table + (int64_t)p.req_rows[b] * p.pt_stride, ctx,
-          p.packed_slots + (int64_t)b * p.out_stride, p.sparse_lens + b,
-          p.selected_pages ? p.selected_pages + (int64_t)b * (p.k + 1) : nullptr, *sel_sm);
-    }
-  }
-
-  int r = r_first, i = 0;
-  while (u0 + i < u1) {
-    while (sPrefix[r + 1] <= u0 + i) ++r;
-    const int b = r;
-    const int row_begin = sPrefix[r], row_end = sPrefix[r + 1];
-    const int seg_begin = u0 + i, seg_end = min(u1, row_end);
-    const int n = seg_end - seg_begin;
-    const int ctx = p.context_lens[b];
-    const int nv = min(max((ctx + kPage - 1) / kPage, 1) - 1, p.n_cols);
-
-    // ---- q+ / q- (clamp_min(0) / clamp_max(0), quest.py:1796-1797) in B-fragment order
-    {
-      const uint4* qrow = reinterpret_cast<const uint4*>(p.q + (int64_t)b * p.q_stride_b);
-      for (int c = tid; c < hq * 16; c += kScoreConsumerThreads) {
-        const int head = c >> 4, chunk = c & 15;
-        const uint4 x = qrow[c];
-        const uint32_t w[4] = {x.x, x.y, x.z, x.w};
-        const int kk = chunk >> 1, hf = chunk & 1;
-        const int base = ((head * 8 + (kk ^ (head & 7))) * 4) * 2 + hf;
+  // q+ / q- (clamp_min(0) / clamp_max(0), quest.py:1796-1797) of row b in B-fragment order
+  auto stage_q = [&](int b) {
+    const uint4* qrow = reinterpret_cast<const uint4*>(p.q + (int64_t)b * p.q_stride_b);
+    for (int c = tid; c < hq * 16; c += kScoreConsumerThreads) {
+      const int head = c >> 4, chunk = c & 15;
+      const uint4 x = qrow[c];
+      const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+      const int kk = chunk >> 1, hf = chunk & 1;
+      const int base = ((head * 8 + (kk ^ (head & 7))) * 4) * 2 + hf;
 #pragma unroll
-        for (int tt = 0; tt < 4; ++tt) {
-          const uint32_t lo = w[tt] & 0xffffu, hi = w[tt] >> 16;
-          const uint32_t lo_neg = (lo & 0x8000u) ? lo : 0u, lo_pos = (lo & 0x8000u) ? 0u : lo;
-          const uint32_t hi_neg = (hi & 0x8000u) ? hi : 0u, hi_pos = (hi & 0x8000u) ? 0u : hi;
-          sq[base + tt * 2] = lo_pos | (hi_pos << 16);
-          sq[neg_off * 2 + base + tt * 2] = lo_neg | (hi_neg << 16);
-        }
+      for (int tt = 0; tt < 4; ++tt) {
+        const uint32_t lo = w[tt] & 0xffffu, hi = w[tt] >> 16;
+        const uint32_t lo_neg = (lo & 0x8000u) ? lo : 0u, lo_pos = (lo & 0x8000u) ? 0u : lo;
+        const uint32_t hi_neg = (hi & 0x8000u) ? hi : 0u, hi_pos = (hi & 0x8000u) ? 0u : hi;
+        sq[base + tt * 2] = lo_pos | (hi_pos << 16);
+        sq[neg_off * 2 + base + tt * 2] = lo_neg | (hi_neg << 16);
       }
     }
-    score_consumer_sync();
+  };
 
-    uint16_t* srow = p.scores + (int64_t)b * p.score_stride;
-    // Unit j goes to warp j % NW, and NW divides S: a stage is always drained by the same warp, so
-    // the phase a warp waits for is never more than one ahead of the barrier (parity waits cannot
-    // tell a phase from the one two before it).
-    const int NW = p.consumers;
-    for (int j = i + ((warp - i % NW + NW) % NW); warp < NW && j < i + n; j += NW) {
-      const int s = j % S;
-      mbar_wait(&full_bar[s], (j / S) & 1);
-      if (dbg && tid == 0 && j == 0) dbg[2] = global_timer_ns();
+  // Unit i goes to warp i % NW, and NW divides S: a stage is always drained by the same warp, so
+  // the phase a warp waits for is never more than one ahead of the barrier (parity waits cannot
+  // tell a phase from the one two before it).
+  const int NW = p.consumers;
+  bool first_seen = false;
+  int cur_row = -2, visit_units = 0, total_units = 0;  // -2: no row yet (-1 is the end descriptor)
+  unsigned long long c_desc = 0, c_full = 0;
+  for (int n = 0;; ++n) {
+    const unsigned long long tc = dbg ? global_timer_ns() : 0;
+    const ChunkDesc d = sched_read(sched, n);
+    if (dbg) c_desc += global_timer_ns() - tc;
+    if (d.row != cur_row) {
+      // leave cur_row: add the units scored here to the row's counter (fire and forget; the row's
+      // selecting CTA polls it), stage the next row's q
+      score_consumer_sync();
+      if constexpr (FUSED_SELECT) {
+        if (tid == 0 && cur_row >= 0) {
+          __threadfence();
+          atomicAdd(units_done + cur_row, visit_units);
+        }
+      }
+      if (d.row >= 0) stage_q(d.row);
+      score_consumer_sync();
+      cur_row = d.row;
+      visit_units = 0;
+      if (d.row < 0) break;
+    }
+    visit_units += d.n_units;
+    total_units += d.n_units;
+    uint16_t* srow = p.scores + (int64_t)d.row * p.score_stride;
+    for (int j = 0; j < d.n_units; ++j) {
+      const int i = d.unit_base + j;
+      if (warp >= NW || i % NW != warp) continue;
+      const int s = i % S;
+      const unsigned long long tf = dbg ? global_timer_ns() : 0;
+      mbar_wait(&full_bar[s], (uint32_t)(i / S) & 1u);
+      if (dbg) c_full += global_timer_ns() - tf;
+      if (dbg && tid == 0 && !first_seen) dbg[2] = global_timer_ns(), first_seen = true;
       const uint32_t mask = sValid[s];
       const uint32_t abase = smem_u32(ring + s * stage_bytes) +
                              ((lane & 7) + ((lane >> 3) & 1) * 8) * rec_stride + (lane >> 4) * 16;
@@ -654,7 +688,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       best1 = fmaxf(best1, __shfl_xor_sync(0xffffffffu, best1, 1));
       best1 = fmaxf(best1, __shfl_xor_sync(0xffffffffu, best1, 2));
       if (t == 0) {
-        const int p0 = (seg_begin + (j - i) - row_begin) * 16 + g, p1 = p0 + 8;
+        const int p0 = (d.unit_begin + j) * 16 + g, p1 = p0 + 8;
         if (p0 < p.n_cols) {
           __nv_bfloat16 v = __float2bfloat16_rn(best0);
           srow[p0] = ((mask >> g) & 1u) ? *reinterpret_cast<uint16_t*>(&v) : (uint16_t)0xff80u;
@@ -665,37 +699,11 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
         }
       }
     }
-
-    if constexpr (FUSED_SELECT) {
-      const bool complete = seg_begin == row_begin && seg_end == row_end;
-      __threadfence();
-      score_consumer_sync();
-      if (tid == 0) {
-        int last = 1;
-        if (!complete) {
-          const int c_first = score_unit_owner(row_begin, U, Gn);
-          const int c_last = score_unit_owner(row_end - 1, U, Gn);
-          const int ticket = atomicAdd(&p.tickets[b], 1);
-          last = (ticket == c_last - c_first);
-          if (last) p.tickets[b] = 0;  // scratch stays zeroed for the next launch / replay
-        }
-        s_flag = last;
-      }
-      score_consumer_sync();
-      if (s_flag) {
-        __threadfence();
-        const unsigned long long ts = dbg ? global_timer_ns() : 0;
-        quest_select_pack_row<1, kScoreConsumerThreads>(
-            srow, p.n_cols, nv, p.k, p.page_table + (int64_t)p.req_rows[b] * p.pt_stride, ctx,
-            p.packed_slots + (int64_t)b * p.out_stride, p.sparse_lens + b,
-            p.selected_pages ? p.selected_pages + (int64_t)b * (p.k + 1) : nullptr, *sel_sm);
-        if (dbg && tid == 0) dbg[5] += global_timer_ns() - ts;
-      }
-    }
-    score_consumer_sync();  // sq / s_flag are reused by the next segment
-    i += n;
   }
-  if (dbg && tid == 0) dbg[3] = global_timer_ns();
+  if (tid == 0) {
+    if (dbg) dbg[3] = global_timer_ns(), dbg[6] = (unsigned long long)total_units, dbg[11] = c_desc, dbg[12] = c_full;
+    if (!FUSED_SELECT || atomicAdd(&s_flag, 1) == 1) sched_finish(p.sched, B);
+  }
 }
 
 // =========================================================================
@@ -766,14 +774,23 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
   p.stages = stages;
   p.consumers = best_c;
   p.producers = best_p;
+  // Row groups (sched.cuh): by default every row is its own group, i.e. gridDim/batch CTAs start on
+  // each row and q is staged once per CTA; fewer groups make rows end at staggered times.
+  int groups = tuning(kTuneScoreGroups);
+  if (groups <= 0) groups = p.batch;
+  if (groups > p.batch) groups = p.batch;
+  if (groups < 1) groups = 1;
+  p.groups = groups;
+  p.min_batch = tuning(kTuneMinBatch) > 0 ? tuning(kTuneMinBatch) : kMinBatch;
+  p.share_div = tuning(kTuneShareDiv) > 0 ? tuning(kTuneShareDiv) : 4;
   const size_t smem = score_smem_layout(stages, p.hq, p.hkv, p.batch, FUSED).total;
   auto kern = quest_page_score_kernel<NT, FUSED>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return cuda_error("quest_page_score smem attr", e);
-  const int64_t max_units = (int64_t)p.batch * ((p.n_cols + 15) / 16);
+  const int64_t units_row = (p.n_cols + 15) / 16;
+  const int64_t max_chunks = (int64_t)p.batch * ((units_row + kChunkUnits - 1) / kChunkUnits);
   int grid = max_ctas();
-  if ((int64_t)grid > max_units) grid = (int)max_units;
-  if (FUSED && grid > p.batch && max_units < p.batch) grid = p.batch;
+  if ((int64_t)grid > max_chunks) grid = (int)max_chunks;
   if (grid < 1) grid = 1;
   kern<<<grid, kScoreThreads, smem, stream>>>(p);
   return check_launch(FUSED ? "quest_score_select_pack" : "quest_page_score");
@@ -797,10 +814,11 @@ static ScoreParams make_score_params(const void* q, int64_t q_stride_b, const vo
 int launch_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds, int64_t num_pages,
                             const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
                             const int32_t* context_lens, void* scores, int64_t score_stride,
-                            int batch, int hq, int hkv, int n_cols, cudaStream_t stream) {
+                            int batch, int hq, int hkv, int n_cols, int32_t* sched, cudaStream_t stream) {
   if (batch <= 0 || n_cols <= 0) return 0;
   ScoreParams p = make_score_params(q, q_stride_b, bounds, num_pages, page_table, pt_stride, req_rows,
                                     context_lens, scores, score_stride, batch, hq, hkv, n_cols);
+  p.sched = sched;
   return hq / hkv <= 8 ? launch_score_variant<1, false>(p, stream)
                        : launch_score_variant<2, false>(p, stream);
 }
@@ -816,7 +834,7 @@ int launch_quest_score_select_pack(const void* q, int64_t q_stride_b, const void
   ScoreParams p = make_score_params(q, q_stride_b, bounds, num_pages, page_table, pt_stride, req_rows,
                                     context_lens, scores, score_stride, batch, hq, hkv, n_cols);
   p.k = k; p.packed_slots = packed_slots; p.out_stride = out_stride; p.sparse_lens = sparse_lens;
-  p.selected_pages = selected_pages; p.tickets = tickets;
+  p.selected_pages = selected_pages; p.sched = tickets;
   return hq / hkv <= 8 ? launch_score_variant<1, true>(p, stream)
                        : launch_score_variant<2, true>(p, stream);
 }

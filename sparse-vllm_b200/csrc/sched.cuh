@@ -1,0 +1,144 @@
+// Dynamic chunk scheduling shared by the persistent page-scoring and decode-attention kernels.
+//
+// Why: with one equal static cut per SM the same SMs are always served ~20 % slower by the memory
+// system (profiles/r1_c_ncu_summary.md) and the fast ones idle.  Here the work of a launch is
+// rows x chunks (a chunk = up to kChunkUnits consecutive units of one row) claimed with atomicAdd on
+// the row's counter.  A CTA starts on its home rows (group = blockIdx % groups; rows group,
+// group + groups, ...) and claims guided batches there: half of its fair share of what is left, so
+// batches are large while a row is far from done (the claim's round trip hides behind queued work)
+// and shrink to one chunk near the end (little is hoarded when the row runs dry).  Once its home
+// rows are exhausted it steals single chunks from the row with the most chunks left.
+//
+// One scheduler warp per CTA claims and posts descriptors into a shared-memory queue (full/empty
+// mbarrier pair per slot); every producer and consumer warp reads every descriptor in order.
+#pragma once
+
+#include "common.cuh"
+
+namespace svb200 {
+
+constexpr int kChunkUnits = 2;   // units per claimed chunk (one table lookup per lane: 2 x 16 entries)
+constexpr int kSchedQueue = 8;   // descriptor slots: ring (3 chunks) + id prefetch + 1; more would only hoard work
+constexpr int kMinBatch = 2;     // chunks per claim at least (an atomicAdd costs 3-4 us under load; one more is in flight)
+
+struct ChunkDesc {
+  int row;         // -1: end of work
+  int unit_begin;  // first unit inside the row
+  int n_units;     // 1..kChunkUnits
+  int unit_base;   // CTA-local running unit index of the chunk's first unit (ring stage = index % S)
+};
+
+struct SchedSmem {
+  ChunkDesc desc[kSchedQueue];
+  uint64_t full[kSchedQueue];
+  uint64_t empty[kSchedQueue];
+};
+
+// Global scratch of one launch family: ints [0] = finished CTAs, [1 + r] = next chunk of row r,
+// [1 + rows + r] = units of row r done.  Zero-initialised once; the last CTA to finish zeroes it again.
+__host__ __device__ inline int sched_scratch_ints(int rows) { return 1 + 2 * rows; }
+
+__device__ __forceinline__ void sched_init(SchedSmem& q, int readers) {
+  for (int s = 0; s < kSchedQueue; ++s) {
+    mbar_init(&q.full[s], 1);
+    mbar_init(&q.empty[s], readers);
+  }
+}
+
+// Reader side (whole warp): descriptor n, released as soon as it is copied to registers.
+__device__ __forceinline__ ChunkDesc sched_read(SchedSmem& q, int n) {
+  const int slot = n % kSchedQueue;
+  mbar_wait(&q.full[slot], (uint32_t)(n / kSchedQueue) & 1u);
+  const ChunkDesc d = q.desc[slot];
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mbar_arrive(&q.empty[slot]);
+  return d;
+}
+
+__device__ __forceinline__ int ld_volatile_shared(const int* p) {
+  int v;
+  asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_volatile_shared(int* p, int v) {
+  asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
+}
+
+// Scheduler warp.  units_of_row(r) -> units of row r (uniform across the launch).
+template <class UnitsOfRow>
+__device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int rows, int groups,
+                          int min_batch, int share_div, UnitsOfRow units_of_row) {
+  const int lane = threadIdx.x & 31;
+  int n = 0, ubase = 0;
+  auto post = [&](int row, int begin, int cnt) {
+    const int slot = n % kSchedQueue;
+    if (n >= kSchedQueue) mbar_wait(&q.empty[slot], (uint32_t)(n / kSchedQueue - 1) & 1u);
+    if (lane == 0) {
+      q.desc[slot] = ChunkDesc{row, begin, cnt, ubase};
+      mbar_arrive(&q.full[slot]);
+    }
+    __syncwarp();
+    ubase += cnt;
+    ++n;
+  };
+  // claims chunks of `row` until it is exhausted; the next claim is in flight while the current
+  // batch is posted
+  const int share = max(1, (int)gridDim.x / groups);  // CTAs that start on the same rows
+  auto drain = [&](int row, bool guided) {
+    const int nu = units_of_row(row);
+    const int d = (nu + kChunkUnits - 1) / kChunkUnits;
+    if (d == 0) return;
+    auto batch = [&](int left) { return guided ? max(min_batch, left / (share_div * share)) : min_batch; };
+    int m = batch(d), j = 0;
+    if (lane == 0) j = atomicAdd(next_chunk + row, m);
+    j = __shfl_sync(0xffffffffu, j, 0);
+    while (j < d) {
+      const int end = min(j + m, d), left = d - end;
+      int m2 = 0, j2 = 0;
+      if (left > 0) {
+        m2 = batch(left);
+        if (lane == 0) j2 = atomicAdd(next_chunk + row, m2);
+      }
+      for (int c = j; c < end; ++c) post(row, c * kChunkUnits, min(kChunkUnits, nu - c * kChunkUnits));
+      if (left <= 0) return;
+      j = __shfl_sync(0xffffffffu, j2, 0);
+      m = m2;
+    }
+  };
+  const int grp = (int)(blockIdx.x % (unsigned)groups);
+  for (int row = grp; row < rows; row += groups) drain(row, true);
+  // steal: the row with the most chunks left (counters only grow: a stale read can only show too much)
+  while (true) {
+    int best = 0, best_row = -1;
+    for (int base = 0; base < rows; base += 32) {
+      const int r = base + lane;
+      if (r < rows) {
+        const int rr = (r + (int)blockIdx.x) % rows;
+        const int nu = units_of_row(rr);
+        const int left = (nu + kChunkUnits - 1) / kChunkUnits - __ldcg(next_chunk + rr);
+        if (left > best) best = left, best_row = rr;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const int ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const int orow = __shfl_xor_sync(0xffffffffu, best_row, o);
+      if (ob > best || (ob == best && orow > best_row)) best = ob, best_row = orow;
+    }
+    if (best <= 0) break;
+    drain(best_row, false);
+  }
+  post(-1, 0, 0);
+}
+
+// Last CTA out zeroes the scratch for the next launch / graph replay.  Called by one thread after
+// all of the CTA's global side effects (and after its scheduler warp posted the end descriptor).
+__device__ __forceinline__ void sched_finish(int* scratch, int rows) {
+  __threadfence();
+  const int f = atomicAdd(scratch, 1);
+  if (f == (int)gridDim.x - 1) {
+    for (int i = 0; i < sched_scratch_ints(rows); ++i) scratch[i] = 0;
+  }
+}
+
+}  // namespace svb200

@@ -100,7 +100,8 @@ class B200SparseDecodeProvider:
                                         prev_budget, scores, packed_slots, sparse_lens, tickets, selected_pages)
             self._count("quest_score_select_pack_fused")
         else:
-            ops.quest_page_score(q, bounds_layer, page_table, req_rows, context_lens, n_cols, num_kv_heads, scores)
+            ops.quest_page_score(q, bounds_layer, page_table, req_rows, context_lens, n_cols, num_kv_heads, scores,
+                                 sched=tickets)
             ops.quest_select_pack(scores, n_cols, page_table, req_rows, context_lens, prev_budget, packed_slots,
                                   sparse_lens, selected_pages, dense_token_table, token_budget, page_budget_base,
                                   out_width)

@@ -100,9 +100,15 @@ def score_row_stride(n_cols: int) -> int:
 
 def quest_page_score(q: torch.Tensor, bounds_layer: torch.Tensor, page_table: torch.Tensor,
                      req_rows: torch.Tensor, context_lens: torch.Tensor, n_cols: int,
-                     num_kv_heads: int, scores: torch.Tensor | None = None) -> torch.Tensor:
-    """bf16 page scores [B, stride>=n_cols] (svb200_quest_page_score)."""
+                     num_kv_heads: int, scores: torch.Tensor | None = None,
+                     sched: torch.Tensor | None = None) -> torch.Tensor:
+    """bf16 page scores [B, stride>=n_cols] (svb200_quest_page_score).  ``sched``: sched_scratch(B)."""
     bsz, hq, qs = _q(q, "q")
+    if sched is None:
+        sched = sched_scratch(bsz, q.device)
+    _i32(sched, "sched")
+    if sched.numel() < sched_scratch_ints(bsz):
+        raise ValueError(f"sched needs >= {sched_scratch_ints(bsz)} int32 entries, got {sched.numel()}.")
     _bounds_layer(bounds_layer, num_kv_heads)
     _i32(page_table, "page_table"); _i32(req_rows, "req_rows"); _i32(context_lens, "context_lens")
     if scores is None:
@@ -113,7 +119,7 @@ def quest_page_score(q: torch.Tensor, bounds_layer: torch.Tensor, page_table: to
         ptr(q), qs, ptr(bounds_layer), int(bounds_layer.shape[0]), ptr(page_table),
         _rows_stride(page_table, "page_table"),
         ptr(req_rows), ptr(context_lens), ptr(scores), _rows_stride(scores, "scores"), bsz, hq,
-        int(num_kv_heads), int(n_cols), current_stream_ptr(q.device)), "svb200_quest_page_score")
+        int(num_kv_heads), int(n_cols), ptr(sched), current_stream_ptr(q.device)), "svb200_quest_page_score")
     return scores
 
 
@@ -156,8 +162,8 @@ def quest_score_select_pack(q: torch.Tensor, bounds_layer: torch.Tensor, page_ta
     for t, n in ((page_table, "page_table"), (req_rows, "req_rows"), (context_lens, "context_lens"),
                  (packed_slots, "packed_slots"), (sparse_lens, "sparse_lens"), (tickets, "tickets")):
         _i32(t, n)
-    if tickets.numel() < bsz:
-        raise ValueError(f"tickets needs >= {bsz} int32 entries, got {tickets.numel()}.")
+    if tickets.numel() < sched_scratch_ints(bsz):
+        raise ValueError(f"tickets needs >= {sched_scratch_ints(bsz)} int32 entries (sched_scratch), got {tickets.numel()}.")
     if selected_pages is not None:
         _i32(selected_pages, "selected_pages")
     lib = _native.load()
@@ -168,6 +174,21 @@ def quest_score_select_pack(q: torch.Tensor, bounds_layer: torch.Tensor, page_ta
         int(num_kv_heads), int(n_cols), int(prev_budget), ptr(packed_slots),
         _rows_stride(packed_slots, "packed_slots"), ptr(sparse_lens), ptr(selected_pages), ptr(tickets),
         current_stream_ptr(q.device)), "svb200_quest_score_select_pack")
+
+
+def sched_scratch_ints(rows: int) -> int:
+    """int32 entries of the scheduler scratch of the persistent score kernels for ``rows`` batch rows."""
+    return int(_native.load().svb200_sched_scratch_ints(int(rows)))
+
+
+def sched_scratch(rows: int, device) -> torch.Tensor:
+    """Zeroed scheduler scratch (allocate once per stream; launches leave it zeroed)."""
+    return torch.zeros((sched_scratch_ints(rows),), dtype=torch.int32, device=device)
+
+
+def set_tuning(which: int, value: int) -> int:
+    """Experiment knob (svb200_set_tuning); returns the previous value."""
+    return int(_native.load().svb200_set_tuning(int(which), int(value)))
 
 
 def set_max_ctas(n: int) -> int:

@@ -199,7 +199,7 @@ def test_select_pack_matches_reference(name, fused, golden):
         ref_scores[b, int(n_valid[b]):] = -float("inf")
     if fused:
         scores = torch.empty(bsz, ops.score_row_stride(n_cols), dtype=torch.bfloat16, device=DEV)
-        tickets = torch.zeros(bsz, dtype=torch.int32, device=DEV)
+        tickets = ops.sched_scratch(bsz, DEV)
         for _ in range(2):  # twice: the tickets must be left zeroed
             ops.quest_score_select_pack(q, bounds, pt, req, ctx, n_cols, cfg["hkv"], prev, scores, packed, lens,
                                         tickets, selected)
@@ -286,7 +286,7 @@ def _check_fused_properties(bsz, hq, hkv, ctx, budget):
     packed = torch.zeros(bsz, (prev + 1) * PAGE, dtype=torch.int32, device=DEV)
     lens = torch.zeros(bsz, dtype=torch.int32, device=DEV)
     sel = torch.zeros(bsz, prev + 1, dtype=torch.int32, device=DEV)
-    tickets = torch.zeros(bsz, dtype=torch.int32, device=DEV)
+    tickets = ops.sched_scratch(bsz, DEV)
     ops.quest_score_select_pack(q, bounds, pt, req, ctx_lens, n_cols, hkv, prev, scores, packed, lens, tickets, sel)
     torch.cuda.synchronize()
     num_pg = (ctx_lens + PAGE - 1) // PAGE
