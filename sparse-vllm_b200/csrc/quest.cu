@@ -462,7 +462,8 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
 
   if (warp == kScoreConsumerWarps + kScoreProducerWarps) {
     // ============================================================== scheduler
-    sched_run(sched, next_chunk, B, p.groups, p.min_batch, p.share_div, units_of_row);
+    sched_run(sched, next_chunk, B, p.groups, p.min_batch, p.share_div, min(kSchedQueue, (S + kChunkUnits - 1) / kChunkUnits + kIdDepth + 1),
+              units_of_row);
     return;
   }
 
@@ -493,7 +494,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
         return;
       }
       const int col = d.unit_begin * 16 + lane;
-      if (lane < d.n_units * 16 && col < sNv[d.row])
+      if (lane < d.units() * 16 && col < sNv[d.row])
         id = __ldg(p.page_table + (int64_t)sReq[d.row] * p.pt_stride + col);
     };
 #pragma unroll
@@ -518,7 +519,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
         const int my = (pa >= 0 && pa < p.num_pages) ? pa : -1;
         const uint32_t ball = __ballot_sync(0xffffffffu, my >= 0);
         if (dbg) w_ids += global_timer_ns() - ti;
-        for (int j = 0; j < cur.n_units; ++j) {
+        for (int j = 0; j < cur.units(); ++j) {
           const int i = cur.unit_base + j;
           if (i % NP != pw) continue;
           const int s = i % S;
@@ -633,10 +634,10 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       visit_units = 0;
       if (d.row < 0) break;
     }
-    visit_units += d.n_units;
-    total_units += d.n_units;
+    visit_units += d.units();
+    total_units += d.units();
     uint16_t* srow = p.scores + (int64_t)d.row * p.score_stride;
-    for (int j = 0; j < d.n_units; ++j) {
+    for (int j = 0; j < d.units(); ++j) {
       const int i = d.unit_base + j;
       if (warp >= NW || i % NW != warp) continue;
       const int s = i % S;

@@ -7,7 +7,8 @@
 // group + groups, ...) and claims guided batches there: half of its fair share of what is left, so
 // batches are large while a row is far from done (the claim's round trip hides behind queued work)
 // and shrink to one chunk near the end (little is hoarded when the row runs dry).  Once its home
-// rows are exhausted it steals single chunks from the row with the most chunks left.
+// rows are exhausted (or if it has none: gridDim is not a multiple of the groups) it steals a few
+// chunks at a time from the row with the most chunks left.
 //
 // One scheduler warp per CTA claims and posts descriptors into a shared-memory queue (full/empty
 // mbarrier pair per slot); every producer and consumer warp reads every descriptor in order.
@@ -18,14 +19,16 @@
 namespace svb200 {
 
 constexpr int kChunkUnits = 2;   // units per claimed chunk (one table lookup per lane: 2 x 16 entries)
-constexpr int kSchedQueue = 8;   // descriptor slots: ring (3 chunks) + id prefetch + 1; more would only hoard work
+constexpr int kSchedQueue = 16;  // descriptor slots (sched_run's `depth` <= kSchedQueue bounds what is actually posted ahead)
 constexpr int kMinBatch = 2;     // chunks per claim at least (an atomicAdd costs 3-4 us under load; one more is in flight)
 
 struct ChunkDesc {
   int row;         // -1: end of work
   int unit_begin;  // first unit inside the row
-  int n_units;     // 1..kChunkUnits
+  int n_units;     // 1..kChunkUnits, | aux << 8 (aux: what reserve(row) returned for this visit of the row)
   int unit_base;   // CTA-local running unit index of the chunk's first unit (ring stage = index % S)
+  __device__ __forceinline__ int units() const { return n_units & 0xff; }
+  __device__ __forceinline__ int aux() const { return n_units >> 8; }
 };
 
 struct SchedSmem {
@@ -65,16 +68,25 @@ __device__ __forceinline__ void st_volatile_shared(int* p, int v) {
 }
 
 // Scheduler warp.  units_of_row(r) -> units of row r (uniform across the launch).
-template <class UnitsOfRow>
+// reserve(row) is called once before a row is drained: < 0 = this CTA may not work on the row,
+// else the value travels in the row's descriptors (aux).
+struct ReserveNone {
+  __device__ __forceinline__ int operator()(int) const { return 0; }
+};
+template <class UnitsOfRow, class Reserve = ReserveNone>
 __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int rows, int groups,
-                          int min_batch, int share_div, UnitsOfRow units_of_row) {
+                          int min_batch, int share_div, int depth, UnitsOfRow units_of_row,
+                          Reserve reserve = Reserve()) {
   const int lane = threadIdx.x & 31;
-  int n = 0, ubase = 0;
+  int n = 0, ubase = 0, aux = 0;
   auto post = [&](int row, int begin, int cnt) {
     const int slot = n % kSchedQueue;
-    if (n >= kSchedQueue) mbar_wait(&q.empty[slot], (uint32_t)(n / kSchedQueue - 1) & 1u);
+    // at most `depth` (<= kSchedQueue) descriptors are posted ahead of the slowest reader: what is
+    // posted is committed to this CTA and cannot be stolen
+    if (n >= depth)
+      mbar_wait(&q.empty[(n - depth) % kSchedQueue], (uint32_t)((n - depth) / kSchedQueue) & 1u);
     if (lane == 0) {
-      q.desc[slot] = ChunkDesc{row, begin, cnt, ubase};
+      q.desc[slot] = ChunkDesc{row, begin, cnt | (aux << 8), ubase};
       mbar_arrive(&q.full[slot]);
     }
     __syncwarp();
@@ -84,29 +96,39 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
   // claims chunks of `row` until it is exhausted; the next claim is in flight while the current
   // batch is posted
   const int share = max(1, (int)gridDim.x / groups);  // CTAs that start on the same rows
-  auto drain = [&](int row, bool guided) {
+  constexpr int kStealVisit = 12;  // chunks a thief takes per visit of a row before it looks again
+  auto drain = [&](int row, bool guided) -> bool {  // false: reserve() refused the row
     const int nu = units_of_row(row);
     const int d = (nu + kChunkUnits - 1) / kChunkUnits;
-    if (d == 0) return;
+    if (d == 0) return true;
+    if (!guided && __ldcg(next_chunk + row) >= d) return true;  // thief, nothing left: do not reserve
+    aux = reserve(row);
+    if (aux < 0) return false;
     auto batch = [&](int left) { return guided ? max(min_batch, left / (share_div * share)) : min_batch; };
-    int m = batch(d), j = 0;
+    int m = batch(d), j = 0, taken = 0;
     if (lane == 0) j = atomicAdd(next_chunk + row, m);
     j = __shfl_sync(0xffffffffu, j, 0);
     while (j < d) {
-      const int end = min(j + m, d), left = d - end;
+      const int end = min(j + m, d);
+      taken += end - j;
+      const int left = (guided || taken < kStealVisit) ? d - end : 0;
       int m2 = 0, j2 = 0;
       if (left > 0) {
         m2 = batch(left);
         if (lane == 0) j2 = atomicAdd(next_chunk + row, m2);
       }
       for (int c = j; c < end; ++c) post(row, c * kChunkUnits, min(kChunkUnits, nu - c * kChunkUnits));
-      if (left <= 0) return;
+      if (left <= 0) return true;
       j = __shfl_sync(0xffffffffu, j2, 0);
       m = m2;
     }
+    return true;
   };
-  const int grp = (int)(blockIdx.x % (unsigned)groups);
-  for (int row = grp; row < rows; row += groups) drain(row, true);
+  // share * groups CTAs own home rows; the others help wherever most is left from the start
+  if ((int)blockIdx.x < share * groups) {
+    const int grp = (int)(blockIdx.x % (unsigned)groups);
+    for (int row = grp; row < rows; row += groups) drain(row, true);
+  }
   // steal: the row with the most chunks left (counters only grow: a stale read can only show too much)
   while (true) {
     int best = 0, best_row = -1;
@@ -126,18 +148,18 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
       if (ob > best || (ob == best && orow > best_row)) best = ob, best_row = orow;
     }
     if (best <= 0) break;
-    drain(best_row, false);
+    if (!drain(best_row, false)) break;  // contributor slots of that row are used up: stop stealing
   }
   post(-1, 0, 0);
 }
 
 // Last CTA out zeroes the scratch for the next launch / graph replay.  Called by one thread after
 // all of the CTA's global side effects (and after its scheduler warp posted the end descriptor).
-__device__ __forceinline__ void sched_finish(int* scratch, int rows) {
+__device__ __forceinline__ void sched_finish(int* scratch, int rows, int extra = 0) {
   __threadfence();
   const int f = atomicAdd(scratch, 1);
   if (f == (int)gridDim.x - 1) {
-    for (int i = 0; i < sched_scratch_ints(rows); ++i) scratch[i] = 0;
+    for (int i = 0; i < sched_scratch_ints(rows) + extra; ++i) scratch[i] = 0;
   }
 }
 
