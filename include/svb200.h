@@ -67,16 +67,13 @@ int64_t svb200_sched_scratch_ints(int32_t rows);
 void svb200_debug_times(void* device_buffer);
 
 /*
- * Bytes of scratch svb200_sparse_decode_attn needs: a header of int32 scheduler counters
- * (next chunk / attended units / contributors per (batch row, KV head group)) and contributor-slot
- * states, then fp32 partial records (output + lse per q head) for the contributor slots of every
- * row: 2*SMs + 26*batch rows' worth, whatever the context length.  The buffer must be
- * zero-initialised once; every launch leaves the header zeroed.  One workspace per stream.
+ * Bytes of scratch svb200_sparse_decode_attn needs: one int32 arrival ticket per
+ * (batch row, KV head) followed by two fp32 partial records (output + lse) per SM.
+ * The buffer must be zero-initialised once; kernels leave the tickets zeroed.
  * Takes the place of the reference's mid_o / mid_o_logexpsum split-K workspace
- * (layers/attention.py:15-51), whose size grows with batch * context / 256.
- * svb200_workspace_header_bytes = size of the zeroed int32 header at the front.
+ * (layers/attention.py:15-51), whose size grows with batch * context / 256; this one
+ * depends on the SM count only.
  */
-int64_t svb200_workspace_header_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads);
 int64_t svb200_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads);
 
 /* ------------------------------------------------------------------------- *
@@ -189,9 +186,8 @@ int svb200_quest_score_select_pack(
     int32_t* selected_pages, int32_t* tickets, void* stream);
 
 /*
- * Sparse paged GQA decode attention: 16-token pages claimed dynamically by persistent CTAs
- * (one running softmax state per CTA and row), fused combine by the CTA that completes a row
- * (one launch).
+ * Sparse paged GQA decode attention: stream-K over 16-token pages with a fused
+ * combine (one launch).
  * Replaces gqa_flash_decode_stage1(+_with_score 2D) and flash_decode_stage2
  * (kernels/triton/gqa_flash_decoding_stage1.py:6-121,211-295,
  *  kernels/triton/flash_decoding_stage2.py:8-46) behind

@@ -23,18 +23,14 @@ for it in range(4):
     flush.zero_()
     if it == 3:
         lib.svb200_debug_times(buf.data_ptr())
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
     ops.sparse_decode_attn(q, k, v, table, req, lens, out=out, workspace=ws)
-    e1.record()
     torch.cuda.synchronize()
-    print("launch", it, round(e0.elapsed_time(e1) * 1e3, 1), "us")
 lib.svb200_debug_times(None)
 t = buf.view(148, 8).cpu()
 t0 = int(t[:, 0].min())
 rel = (t[:, :5] - t0).float() / 1000.0
 print("cols: entry, setup done, first data, consumers done, producer0 done (us, relative to first CTA entry)")
-for name, col in (("entry", 0), ("first data", 2), ("consumers done", 3), ("producer done", 4)):
+for name, col in (("entry", 0), ("setup", 1), ("first data", 2), ("consumers done", 3), ("producer done", 4)):
     c = rel[:, col]
     print(f"{name:15s} min {c.min():7.2f} med {c.median():7.2f} max {c.max():7.2f}")
 cmb = t[:, 5].float() / 1000.0; epi = t[:, 6].float() / 1000.0
@@ -46,8 +42,25 @@ print("fastest CTAs (cta, sm, dur):", [(int(i), int(t[i, 7]), round(float(dur[i]
 print("slowest CTAs (cta, sm, dur):", [(int(i), int(t[i, 7]), round(float(dur[i]), 1)) for i in order[-6:]])
 hist = torch.histc(dur, bins=10, min=float(dur.min()), max=float(dur.max()))
 print("duration histogram", float(dur.min()), float(dur.max()), hist.tolist())
-units = (t[:, 1] & 0xffffffff).float(); visits = (t[:, 1] >> 32).float()
-rate = units / (rel[:, 4] - rel[:, 2]).clamp(min=1.0)
-print("units/CTA min", int(units.min()), "med", int(units.median()), "max", int(units.max()), "sum", int(units.sum()),
-      "| row visits/CTA med", int(visits.median()), "max", int(visits.max()),
-      "| units/us while streaming min", round(float(rate.min()), 2), "med", round(float(rate.median()), 2), "max", round(float(rate.max()), 2))
+# second launch with other pages: are the same SMs slow (position) or is it the data (random pages)?
+pages2 = torch.stack([torch.randperm(num_pages, device=dev)[:sel_pages] for _ in range(B)])
+table2 = (pages2[:, :, None] * 16 + torch.arange(16, device=dev)[None, None]).reshape(B, -1).to(torch.int32).contiguous()
+durs = {}
+for name, tb in (("same", table), ("other", table2), ("same2", table)):
+    flush.zero_()
+    buf.zero_()
+    lib.svb200_debug_times(buf.data_ptr())
+    ops.sparse_decode_attn(q, k, v, tb, req, lens, out=out, workspace=ws)
+    torch.cuda.synchronize()
+    lib.svb200_debug_times(None)
+    tt = buf.view(148, 8).cpu()
+    d = (tt[:, 3] - tt[:, 0]).float() / 1000.0
+    bysm = torch.zeros(148)
+    bysm[tt[:, 7].long()] = d
+    durs[name] = (d, bysm)
+print("corr by CTA  first/same:", float(torch.corrcoef(torch.stack([dur, durs['same'][0]]))[0, 1]),
+      " same/other:", float(torch.corrcoef(torch.stack([durs['same'][0], durs['other'][0]]))[0, 1]))
+print("corr by SM   same/other:", float(torch.corrcoef(torch.stack([durs['same'][1], durs['other'][1]]))[0, 1]),
+      " same/same2:", float(torch.corrcoef(torch.stack([durs['same'][1], durs['same2'][1]]))[0, 1]))
+pd = (t[:, 4] - t[:, 0]).float() / 1000.0
+print("producer0 done - by CTA index (first 148):", [round(float(x), 1) for x in pd.tolist()])

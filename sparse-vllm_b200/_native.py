@@ -26,7 +26,6 @@ _SIGNATURES = {
     "svb200_set_tuning": (c_int32, [c_int32, c_int32]),
     "svb200_sched_scratch_ints": (c_int64, [c_int32]),
     "svb200_debug_times": (None, [_P]),
-    "svb200_workspace_header_bytes": (c_int64, [c_int32, c_int32, c_int32]),
     "svb200_workspace_bytes": (c_int64, [c_int32, c_int32, c_int32]),
     "svb200_quest_page_minmax": (c_int32, [_P, _P, _P, c_int32, c_int32, c_int64, _P]),
     "svb200_quest_decode_page_complete": (

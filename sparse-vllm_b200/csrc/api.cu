@@ -95,26 +95,14 @@ int svb200_set_tuning(int32_t which, int32_t value) {
 }
 int64_t svb200_sched_scratch_ints(int32_t rows) { return rows < 0 ? -1 : 1 + 2 * (int64_t)rows; }
 
-// Workspace of svb200_sparse_decode_attn: [zeroed ints: 1 + 3*rows_max scheduler counters, slot_max
-// slot states][lse: rec_max fp32][o: rec_max * 128 fp32] with rows_max = batch * Hkv (heads_per_cta 1),
-// slot_max = 2*SMs + 26*rows_max contributor slots, rec_max = Hq * (2*SMs + 26*batch) head records
-// (bounds of rows * attn_row_slots(grid, rows) [* heads per row] over every head grouping).
-static int64_t ws_rows_max(int64_t batch, int64_t hkv) { return batch * hkv; }
-static int64_t ws_slot_max(int64_t batch, int64_t hkv) { return 2 * (int64_t)sm_count() + 26 * ws_rows_max(batch, hkv); }
-static int64_t ws_rec_max(int64_t batch, int64_t hq) { return hq * (2 * (int64_t)sm_count() + 26 * batch); }
-static int64_t ws_header_bytes(int64_t batch, int64_t hkv) {
-  const int64_t ints = 1 + 3 * ws_rows_max(batch, hkv) + ws_slot_max(batch, hkv);
-  return (ints * (int64_t)sizeof(int32_t) + 255) / 256 * 256;
+static int64_t ws_ticket_bytes(int64_t batch, int64_t hkv) {
+  return ((batch * hkv * (int64_t)sizeof(int32_t) + 255) / 256) * 256;
 }
+static int64_t ws_cta_bytes(int64_t hq) { return 2 * hq * (SVB200_HEAD_DIM + 4) * (int64_t)sizeof(float); }
 
-int64_t svb200_workspace_header_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads) {
-  if (batch < 0 || num_q_heads <= 0 || num_kv_heads <= 0) return -1;
-  return ws_header_bytes(batch, num_kv_heads);
-}
 int64_t svb200_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads) {
   if (batch < 0 || num_q_heads <= 0 || num_kv_heads <= 0) return -1;
-  return ws_header_bytes(batch, num_kv_heads) +
-         ws_rec_max(batch, num_q_heads) * (SVB200_HEAD_DIM + 1) * (int64_t)sizeof(float);
+  return ws_ticket_bytes(batch, num_kv_heads) + (int64_t)sm_count() * ws_cta_bytes(num_q_heads);
 }
 
 int svb200_quest_page_minmax(const void* k_cache, void* bounds_layer, const int32_t* slot_mapping,
@@ -267,26 +255,23 @@ int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_c
     SV_REQUIRE(score_stride >= max_len, "%s: score_stride=%lld must cover max_len=%d when attn_score is given", who, (long long)score_stride, max_len);
   SV_REQUIRE(heads_per_cta == 0 || heads_per_cta == 1 || heads_per_cta == 2 || heads_per_cta == 4 || heads_per_cta == 8,
              "%s: heads_per_cta=%d must be 0 (auto), 1, 2, 4 or 8", who, heads_per_cta);
-  const int64_t hdr = ws_header_bytes(batch, num_kv_heads);
-  SV_REQUIRE(workspace && aligned16(workspace) && workspace_bytes >= hdr + (int64_t)num_q_heads * (SVB200_HEAD_DIM + 1) * 4,
-             "%s: workspace must be 16-byte aligned and hold svb200_workspace_bytes() = %lld bytes",
-             who, (long long)svb200_workspace_bytes(batch, num_q_heads, num_kv_heads));
-  // head records that fit behind the header (a smaller buffer limits the number of CTAs)
-  const int64_t recs = ((workspace_bytes - hdr) / ((SVB200_HEAD_DIM + 1) * (int64_t)sizeof(float))) / 4 * 4;
+  const int64_t tk = ws_ticket_bytes(batch, num_kv_heads), per_cta = ws_cta_bytes(num_q_heads);
+  SV_REQUIRE(workspace && aligned16(workspace) && workspace_bytes >= tk + per_cta,
+             "%s: workspace must be 16-byte aligned and hold at least %lld bytes (svb200_workspace_bytes gives the full size)",
+             who, (long long)(tk + per_cta));
+  int64_t ctas = (workspace_bytes - tk) / per_cta;
+  if (ctas > sm_count()) ctas = sm_count();
   AttnParams p;
   p.q = q; p.q_stride_b = q_stride_b; p.k_cache = k_cache; p.v_cache = v_cache;
   p.num_slots = num_slots; p.slot_table = slot_table; p.slot_table_stride = slot_table_stride;
   p.req_rows = req_rows; p.seq_lens = seq_lens; p.out = out;
   p.out_stride_b = out_stride_b; p.attn_score = attn_score; p.score_stride = score_stride;
   p.batch = batch; p.hq = num_q_heads; p.hkv = num_kv_heads; p.max_len = max_len;
-  p.sm_scale = sm_scale; p.stages = 0;
+  p.sm_scale = sm_scale; p.max_ctas = (int)ctas; p.stages = 0;
   char* w = static_cast<char*>(workspace);
-  p.sched = reinterpret_cast<int32_t*>(w);
-  p.slot_state = p.sched + 1 + 3 * ws_rows_max(batch, num_kv_heads);
-  p.slot_capacity = ws_slot_max(batch, num_kv_heads);
-  p.rec_capacity = recs;
-  p.ws_lse = reinterpret_cast<float*>(w + hdr);
-  p.ws_o = p.ws_lse + recs;
+  p.tickets = reinterpret_cast<int32_t*>(w);
+  p.ws_lse = reinterpret_cast<float*>(w + tk);
+  p.ws_o = reinterpret_cast<float*>(w + tk + ctas * 2 * num_q_heads * 4 * (int64_t)sizeof(float));
   return launch_sparse_decode_attn(p, heads_per_cta, (cudaStream_t)stream);
 }
 

@@ -59,12 +59,10 @@ struct AttnParams {
   float* attn_score;
   int64_t score_stride;
   int batch, hq, hkv, max_len;
-  // workspace (svb200_workspace_bytes): zeroed ints, then fp32 partial records
-  int32_t* sched;       // [1 + 3*rows]: finished CTAs, next chunk / units done / contributors per row
-  int32_t* slot_state;  // [slot_capacity]: 1 = the contributor slot holds a partial (left zeroed)
-  float* ws_lse;        // [rec_capacity] one per (contributor slot, q head of the row)
-  float* ws_o;          // [rec_capacity][128]
-  int64_t rec_capacity, slot_capacity;
+  float* ws_o;       // [2*max_ctas][hq/head_groups][128] fp32 partial outputs
+  float* ws_lse;     // [2*max_ctas][hq/head_groups]
+  int32_t* tickets;  // [batch*head_groups] zeroed
+  int max_ctas;      // CTAs the workspace was sized for
   int stages;        // filled by the launcher
   unsigned long long* dbg_times;  // experiments: per-CTA timestamps (svb200_debug_times), else null
   int producers;     // producer warps in use (divides stages); filled by the launcher

@@ -198,22 +198,20 @@ def set_max_ctas(n: int) -> int:
 
 # ----------------------------------------------------------------------------- attention
 def attn_workspace(batch: int, num_q_heads: int, num_kv_heads: int, device, max_ctas: int | None = None) -> torch.Tensor:
-    """Zeroed scratch of svb200_workspace_bytes (scheduler counters + fp32 partial records).
+    """Zeroed scratch of svb200_workspace_bytes (arrival tickets + per-SM fp32 partials).
 
-    Allocate it once per (batch, heads) shape and stream; launches leave the header zeroed.  ``max_ctas``
-    makes launches that use this workspace run on at most that many CTAs (tests vary the decomposition)."""
+    Allocate it once per (batch, heads) shape; kernels leave the ticket part zeroed.  ``max_ctas`` sizes it
+    for fewer CTAs than SMs (the launch then uses at most that many; tests use it to vary the decomposition)."""
     lib = _native.load()
     nbytes = int(lib.svb200_workspace_bytes(int(batch), int(num_q_heads), int(num_kv_heads)))
     if nbytes <= 0:
         raise ValueError(f"svb200_workspace_bytes({batch}, {num_q_heads}, {num_kv_heads}) = {nbytes}.")
-    ws = torch.zeros(((nbytes + 3) // 4,), dtype=torch.int32, device=device)
-    ws._svb200_max_ctas = None if max_ctas is None else max(1, int(max_ctas))
-    return ws
-
-
-def attn_workspace_header_ints(batch: int, num_q_heads: int, num_kv_heads: int) -> int:
-    """int32 entries of the zeroed header at the front of attn_workspace()."""
-    return int(_native.load().svb200_workspace_header_bytes(int(batch), int(num_q_heads), int(num_kv_heads))) // 4
+    if max_ctas is not None:
+        sms = int(lib.svb200_sm_count())
+        tickets = (int(batch) * int(num_kv_heads) * 4 + 255) // 256 * 256
+        per_cta = (nbytes - tickets) // sms
+        nbytes = tickets + max(1, min(int(max_ctas), sms)) * per_cta
+    return torch.zeros(((nbytes + 3) // 4,), dtype=torch.int32, device=device)
 
 
 def sparse_decode_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, slot_table: torch.Tensor,
@@ -248,17 +246,11 @@ def sparse_decode_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Te
     if sm_scale is None:
         sm_scale = 1.0 / math.sqrt(HEAD_DIM)
     lib = _native.load()
-    cap = getattr(workspace, "_svb200_max_ctas", None)
-    prev = lib.svb200_set_max_ctas(int(cap)) if cap else None
-    try:
-        check(lib.svb200_sparse_decode_attn(
-            ptr(q), qs, ptr(k_cache), ptr(v_cache), num_slots, ptr(slot_table), table_stride, max_len,
-            ptr(req_rows), ptr(seq_lens), ptr(out), os_, ptr(attn_score), score_stride, bsz, hq, hkv,
-            int(heads_per_cta), ptr(workspace), int(workspace.numel()) * 4, float(sm_scale),
-            current_stream_ptr(q.device)), "svb200_sparse_decode_attn")
-    finally:
-        if prev is not None:
-            lib.svb200_set_max_ctas(int(prev))
+    check(lib.svb200_sparse_decode_attn(
+        ptr(q), qs, ptr(k_cache), ptr(v_cache), num_slots, ptr(slot_table), table_stride, max_len,
+        ptr(req_rows), ptr(seq_lens), ptr(out), os_, ptr(attn_score), score_stride, bsz, hq, hkv,
+        int(heads_per_cta), ptr(workspace), int(workspace.numel()) * 4, float(sm_scale),
+        current_stream_ptr(q.device)), "svb200_sparse_decode_attn")
     return out
 
 

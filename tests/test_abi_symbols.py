@@ -50,12 +50,8 @@ def test_validation_errors_need_no_gpu(native_lib):
     rc = native_lib.svb200_quest_page_minmax(None, None, None, 4, 8, 1024, None)
     assert rc == 1
     assert b"null pointer" in native_lib.svb200_last_error()
-    # zeroed int32 header (1 + 3*rows scheduler counters + 2*SMs + 26*rows slot states, 256-byte rounded)
-    # + (output + lse) fp32 records for Hq * (2*SMs + 26*batch) heads (148 SMs without a device)
-    rows, sms = 32 * 4, 148
-    hdr = ((1 + 3 * rows + 2 * sms + 26 * rows) * 4 + 255) // 256 * 256
-    assert native_lib.svb200_workspace_header_bytes(32, 28, 4) == hdr
-    assert native_lib.svb200_workspace_bytes(32, 28, 4) == hdr + 28 * (2 * sms + 26 * 32) * (128 + 1) * 4
+    # tickets (256-byte rounded) + two (output + lse) fp32 partial records per SM (148 without a device)
+    assert native_lib.svb200_workspace_bytes(32, 28, 4) == 512 + 148 * 2 * 28 * (128 + 4) * 4
     rc = native_lib.svb200_h2o_select_compact(1, 1, 1, 1, None, None, None, 2, 100, 200, 10, None)
     assert rc == 1 and b"kv_len" in native_lib.svb200_last_error()
 
