@@ -3,9 +3,10 @@
 
 A "step" is one decode step of the hot path over the whole batch: for each of the model's L layers,
 Quest page scoring + top-k page selection + slot packing, then sparse paged GQA decode attention
-(split-K, fused combine).  N=1 runs BASELINE config 3 (Qwen2.5-7B shape, bs 32, 128K ctx, budget
-4096); N>1 runs config 5 (Qwen3-32B shape, bs 16, 128K ctx) with KV heads sharded over the ranks and
-an NCCL all-gather of the attention output per layer.  See DESIGN.md "Measurement".
+(split-K, fused combine).  Every N runs BASELINE config 5 (Qwen3-32B shape, 64 q / 8 KV heads, bs 16,
+128K ctx, budget 4096): at N>1 KV heads are sharded over the ranks with an NCCL all-gather of the
+attention output per layer (strong scaling).  At N=1 config 3 (Qwen2.5-7B shape, bs 32, 128K ctx) is
+measured as well and reported under "other_workloads".  See DESIGN.md "Measurement".
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload cfg2|cfg3|cfg5]
 """
@@ -53,13 +54,17 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph replay")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--verbose", action="store_true", help="phase timestamps on stderr")
     return ap.parse_args()
 
 
 def pick_workload(args) -> dict:
     key = args.workload
     if key == "auto":
-        key = "cfg3" if args.gpus == 1 else "cfg5"
+        # One workload at every N, so that the 1/2/4/8-GPU series is a strong-scaling curve: config 5
+        # (8 KV heads, the largest configuration; it fits one B200).  Config 3 (4 KV heads, cannot be
+        # sharded 8 ways) is measured next to it at N=1 and reported under "other_workloads".
+        key = "cfg5"
     w = dict(WORKLOADS[key])
     w["key"] = key
     w["budget"] = w["sink"] + w["decode_keep"] + w["recent"]
@@ -289,6 +294,16 @@ def run_b200(args) -> dict:
     import torch
     import torch.distributed as dist
 
+    t_start = time.perf_counter()
+    if args.verbose:
+        import faulthandler
+        faulthandler.dump_traceback_later(75, exit=False, file=sys.stderr)
+
+    def note(msg):
+        if args.verbose:
+            print(f"[bench rank {os.environ.get('RANK', '0')} +{time.perf_counter() - t_start:6.1f}s] {msg}",
+                  file=sys.stderr, flush=True)
+
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -300,12 +315,14 @@ def run_b200(args) -> dict:
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    note("process group ready")
     w = pick_workload(args)
     if w["hkv"] % world:
         raise SystemExit(f"{w['key']}: {w['hkv']} KV heads cannot be sharded over {world} ranks")
 
     mgr, cfg, phys, hq, hkv = build_state(w, rank, world, args.phys_layers, args.skip_layers,
                                            headroom_steps=2 * (args.steps + max(args.warmup, 3)) + 16)
+    note(f"state built ({phys} physical layers)")
     step = DecodeStep(w, mgr, phys, hq, hkv, world, args.skip_layers)
     geo = geometry(w, hkv, hq)
     steps, warmup = args.steps, max(args.warmup, 3)
@@ -323,14 +340,17 @@ def run_b200(args) -> dict:
         for _ in range(2):
             step.layers()
         stream.synchronize()
+        note("eager steps done")
         if not args.no_graph:
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=stream):
                 step.layers()
         run = graph.replay if graph is not None else step.layers
+        note("graph captured" if graph is not None else "no graph")
         for _ in range(warmup):
             run()
         barrier()
+        note("warm-up done")
         sampler = ClockSampler(local_rank)
         sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -340,6 +360,7 @@ def run_b200(args) -> dict:
         e1.record(stream)
         barrier()
         dev_ms = e0.elapsed_time(e1)
+        note("timed region done")
 
         # ---- (2) per-kernel durations, live, eager launches with event pairs
         timers = KernelTimers(mgr._get_provider(hq))
@@ -350,6 +371,7 @@ def run_b200(args) -> dict:
         timers.enabled = False
         barrier()
         ksum = timers.summary()
+        note("per-kernel timing done")
 
         # ---- (3) end to end through the public API with HOST buffers
         def e2e_step():
@@ -369,7 +391,9 @@ def run_b200(args) -> dict:
         f1.record(stream)
         barrier()
         e2e_ms = f0.elapsed_time(f1)
+        note("e2e done")
         clocks = sampler.stop()
+        note("clock sampler stopped")
 
     times = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -398,13 +422,29 @@ def run_b200(args) -> dict:
     roof_step = {"achieved": step_bytes / (ms_per_step * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                  "bytes_per_step": step_bytes}
     roof_step["frac"] = roof_step["achieved"] / peak
+    def shutdown():
+        """Release the captured graph BEFORE the NCCL communicator it references (destroying the process
+        group under a live graph hangs), and never let clean-up keep the job alive."""
+        nonlocal graph
+        if world == 1:
+            return
+        watchdog = threading.Timer(30.0, os._exit, (0,))
+        watchdog.daemon = True
+        watchdog.start()
+        if graph is not None:
+            graph.reset()
+            graph = None
+        torch.cuda.synchronize()
+        dist.barrier()
+        dist.destroy_process_group()
+        watchdog.cancel()
+
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        shutdown()
         return {}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": w["name"], "layers": w["layers"], "q_heads": w["hq"], "kv_heads": w["hkv"],
                    "batch": w["bsz"], "ctx": w["ctx"], "page": PAGE, "token_budget": w["budget"],
@@ -418,7 +458,9 @@ def run_b200(args) -> dict:
         "clocks": clocks,
     }
     if world > 1:
-        dist.destroy_process_group()
+        print(json.dumps(line), flush=True)  # before clean-up: the line must not depend on it
+        line["_printed"] = True
+        shutdown()
     return line
 
 
@@ -500,7 +542,7 @@ def run_reference(args) -> dict:
     return {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warmup, "ms_per_step": per * 1e3, "higher_is_better": True,
-        "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": w["name"], "layers": w["layers"], "q_heads": w["hq"], "kv_heads": w["hkv"],
                    "batch": w["bsz"], "ctx": w["ctx"], "page": PAGE, "token_budget": w["budget"],
                    "quest_skip_layers": args.skip_layers, "parallelism": "host cores"},
@@ -510,15 +552,32 @@ def run_reference(args) -> dict:
     }
 
 
+def secondary_workload(key: str, args) -> dict:
+    """The same bench on another BASELINE config in a fresh process (its own KV pools), summarised."""
+    cmd = [sys.executable, str(ROOT / "bench.py"), "--workload", key, "--no-cpu-baseline", "--steps", str(args.steps),
+           "--warmup", str(args.warmup)]
+    try:
+        res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+        d = json.loads([ln for ln in res.stdout.splitlines() if ln.startswith("{")][-1])
+    except Exception as exc:  # the primary line must not depend on the secondary one
+        return {"error": f"{type(exc).__name__}: {exc}"}
+    return {"workload": d["config"]["workload"], "value": d["value"], "unit": d["unit"], "ms_per_step": d["ms_per_step"],
+            "e2e": d["e2e"]["value"], "roofline_frac": d["roofline"]["frac"],
+            "roofline_attention_frac": d["roofline_attention"]["frac"], "roofline_step_frac": d["roofline_step"]["frac"],
+            "score_launch_ms": d["roofline"]["avg_launch_ms"], "attention_launch_ms": d["roofline_attention"]["avg_launch_ms"]}
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
         line = run_reference(args)
     else:
         line = run_b200(args)
+        if line and args.gpus == 1 and args.workload == "auto":
+            line["other_workloads"] = {"cfg3": secondary_workload("cfg3", args)}
         if line and not args.no_cpu_baseline and args.gpus == 1:
             line["cpu_baseline"] = cpu_baseline(pick_workload(args), args.cpu_seconds)
-    if line:
+    if line and not line.pop("_printed", False):
         print(json.dumps(line), flush=True)
 
 

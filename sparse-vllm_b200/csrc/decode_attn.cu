@@ -625,7 +625,7 @@ static int launch_hpc(const AttnParams& p, cudaStream_t stream) {
 }
 
 int attn_auto_heads_per_cta(int hkv) {
-  for (int c = 8; c > 1; c >>= 1)
+  for (int c = 4; c > 1; c >>= 1)  // 4 heads = 1 KB token rows and six ring stages; 8 would leave three
     if (hkv % c == 0) return c;
   return 1;
 }

@@ -365,6 +365,7 @@ struct ScoreParams {
   uint16_t* scores;
   int64_t score_stride;
   int batch, hq, hkv, n_cols, stages;
+  int ppu;  // pages per unit: 16, or 8 when a page's record is 4 KB (Hkv 8) so that six stages still fit
   unsigned long long* dbg_times;  // experiments: per-CTA timestamps (svb200_debug_times), else null
   int consumers;  // consumer warps that take units; divides `stages` (see the kernel)
   int producers;  // producer warps that feed units; divides `stages`
@@ -385,11 +386,13 @@ struct ScoreSmemLayout {
 
 __host__ __device__ inline int score_rec_stride(int hkv) { return hkv * 2 * kRowBytes + 16; }
 
+__host__ __device__ inline int score_pages_per_unit(int hkv) { return hkv > 4 ? 8 : 16; }
+
 __host__ __device__ inline ScoreSmemLayout score_smem_layout(int stages, int hq, int hkv, int batch,
                                                              bool fused) {
   ScoreSmemLayout L;
   int off = 0;
-  L.ring_off = off;   off += stages * kPage * score_rec_stride(hkv);
+  L.ring_off = off;   off += stages * score_pages_per_unit(hkv) * score_rec_stride(hkv);
   L.q_off = off;      off += 2 * hq * kRowBytes;
   L.bar_off = off;    off += 2 * stages * 8;
   L.valid_off = off;  off += ((stages * 4 + 15) / 16) * 16;
@@ -409,7 +412,9 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   const int gsz = hq / hkv;
   const int rec_stride = score_rec_stride(hkv);
   const int rec_bytes = hkv * 2 * kRowBytes;
-  const int stage_bytes = kPage * rec_stride;
+  const int ppu = p.ppu;
+  const uint32_t unit_mask = (1u << ppu) - 1u;
+  const int stage_bytes = ppu * rec_stride;
   const ScoreSmemLayout L = score_smem_layout(S, hq, hkv, B, FUSED_SELECT);
   unsigned char* ring = smem + L.ring_off;
   // sq[sign][head][kk][t] : uint2 {b0, b1} B fragments, kk XOR-swizzled by head
@@ -452,11 +457,11 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
     const int ctx = p.context_lens[b];
     const int nv = min(max((ctx + kPage - 1) / kPage, 1) - 1, p.n_cols);
     uint16_t* srow = p.scores + (int64_t)b * p.score_stride;
-    for (int c = ((nv + 15) & ~15) + tid; c < p.n_cols; c += kScoreThreads) srow[c] = 0xff80u;
+    for (int c = (nv + ppu - 1) / ppu * ppu + tid; c < p.n_cols; c += kScoreThreads) srow[c] = 0xff80u;
   }
   __syncthreads();
   if (dbg && tid == 0) dbg[1] = global_timer_ns();
-  auto units_of_row = [&](int r) { return (sNv[r] + 15) >> 4; };
+  auto units_of_row = [&](int r) { return (sNv[r] + ppu - 1) / ppu; };
   int* next_chunk = p.sched + 1;
   int* units_done = p.sched + 1 + B;
 
@@ -493,8 +498,8 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
         ended = true;
         return;
       }
-      const int col = d.unit_begin * 16 + lane;
-      if (lane < d.units() * 16 && col < sNv[d.row])
+      const int col = d.unit_begin * ppu + lane;
+      if (lane < d.units() * ppu && col < sNv[d.row])
         id = __ldg(p.page_table + (int64_t)sReq[d.row] * p.pt_stride + col);
     };
 #pragma unroll
@@ -529,14 +534,14 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
           mbar_wait(&empty_bar[s], ph ^ 1u);
           if (dbg) w_empty += global_timer_ns() - te;
 #pragma unroll 4
-          for (int pg = 0; pg < kPage; ++pg) {
-            const int page = __shfl_sync(0xffffffffu, my, j * 16 + pg);
+          for (int pg = 0; pg < ppu; ++pg) {
+            const int page = __shfl_sync(0xffffffffu, my, j * ppu + pg);
             const int nbytes = page >= 0 ? 16 : 0;
             const char* src = src0 + (int64_t)max(page, 0) * rec_bytes;
             const uint32_t dst = dst0 + pg * rec_stride;
             for (int c = 0; c < hkv; ++c) cp_async_16(dst + c * 512, src + c * 512, nbytes);
           }
-          if (lane == 0) sValid[s] = (ball >> (j * 16)) & 0xffffu;
+          if (lane == 0) sValid[s] = (ball >> (j * ppu)) & unit_mask;
           cp_async_mbar_arrive(&full_bar[s]);
           if (lane == 0) mbar_arrive(&full_bar[s]);  // release: publishes sValid
         }
@@ -689,7 +694,8 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       best1 = fmaxf(best1, __shfl_xor_sync(0xffffffffu, best1, 1));
       best1 = fmaxf(best1, __shfl_xor_sync(0xffffffffu, best1, 2));
       if (t == 0) {
-        const int p0 = (d.unit_begin + j) * 16 + g, p1 = p0 + 8;
+        // rows 8-15 of the tile are not pages when ppu == 8 (stale shared memory: never written out)
+        const int p0 = (d.unit_begin + j) * ppu + g, p1 = ppu > 8 ? p0 + 8 : p.n_cols;
         if (p0 < p.n_cols) {
           __nv_bfloat16 v = __float2bfloat16_rn(best0);
           srow[p0] = ((mask >> g) & 1u) ? *reinterpret_cast<uint16_t*>(&v) : (uint16_t)0xff80u;
@@ -752,7 +758,8 @@ int launch_quest_select_pack(const void* scores, int64_t score_stride, int n_col
 template <int NT, bool FUSED>
 static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
   const int fixed = score_smem_layout(0, p.hq, p.hkv, p.batch, FUSED).total + 256;  // + static smem
-  const int stage_bytes = kPage * score_rec_stride(p.hkv);
+  p.ppu = score_pages_per_unit(p.hkv);
+  const int stage_bytes = p.ppu * score_rec_stride(p.hkv);
   int stages = (kScoreMaxSmem - fixed) / (stage_bytes + 20);
   if (stages > 24) stages = 24;
   if (stages < 2) {
@@ -788,7 +795,7 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
   auto kern = quest_page_score_kernel<NT, FUSED>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return cuda_error("quest_page_score smem attr", e);
-  const int64_t units_row = (p.n_cols + 15) / 16;
+  const int64_t units_row = (p.n_cols + p.ppu - 1) / p.ppu;
   const int64_t max_chunks = (int64_t)p.batch * ((units_row + kChunkUnits - 1) / kChunkUnits);
   int grid = max_ctas();
   if ((int64_t)grid > max_chunks) grid = (int)max_chunks;
