@@ -5,7 +5,9 @@ sys.path.insert(0, ".")
 import svb200_import  # noqa
 from sparse_vllm_b200 import ops, _native, configs
 dev = "cuda:0"
-bsz, hq, hkv, ctx, budget = 32, 28, 4, 131072, 4096
+import os
+bsz, hq, hkv = (int(x) for x in os.environ.get('SHAPE', '32,28,4').split(','))
+ctx, budget = 131072, 4096
 gen = torch.Generator(device=dev).manual_seed(1)
 max_pages = ctx // 16
 n_cols = max_pages - 1

@@ -365,6 +365,7 @@ struct ScoreParams {
   uint16_t* scores;
   int64_t score_stride;
   int batch, hq, hkv, n_cols, stages;
+  int bulk;  // 1: one UBLKCP per page record, 0: 16-byte LDGSTS
   int ppu;  // pages per unit: 16, or 8 when a page's record is 4 KB (Hkv 8) so that six stages still fit
   unsigned long long* dbg_times;  // experiments: per-CTA timestamps (svb200_debug_times), else null
   int consumers;  // consumer warps that take units; divides `stages` (see the kernel)
@@ -440,7 +441,8 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   // ---- setup
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
-      mbar_init(&full_bar[s], 33);  // 32 async copy arrivals + the producer's release
+      // LDGSTS: 32 async copy arrivals + the producer's release; bulk: the expect_tx arrival
+      mbar_init(&full_bar[s], p.bulk ? 1 : 33);
       mbar_init(&empty_bar[s], 1);
     }
     sched_init(sched, p.producers + kScoreConsumerWarps);
@@ -529,10 +531,25 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
           if (i % NP != pw) continue;
           const int s = i % S;
           const uint32_t ph = (uint32_t)(i / S) & 1u;
-          const uint32_t dst0 = smem_u32(ring + s * stage_bytes) + lane * 16;
+          const uint32_t umask = (ball >> (j * ppu)) & unit_mask;
           const unsigned long long te = dbg ? global_timer_ns() : 0;
           mbar_wait(&empty_bar[s], ph ^ 1u);
           if (dbg) w_empty += global_timer_ns() - te;
+          if (p.bulk) {
+            // one bulk async copy (UBLKCP) per page record, issued by the lane that holds the page id:
+            // no shuffles, one instruction per Hkv*512 bytes; bytes are counted on the stage's mbarrier
+            if (lane == 0) {
+              sValid[s] = umask;
+              mbar_arrive_expect_tx(&full_bar[s], (uint32_t)__popc(umask) * (uint32_t)rec_bytes);
+            }
+            const int pg = lane - j * ppu;
+            if (pg >= 0 && pg < ppu && my >= 0)
+              bulk_g2s(smem_u32(ring + s * stage_bytes) + pg * rec_stride,
+                       reinterpret_cast<const char*>(p.bounds) + (int64_t)my * rec_bytes, (uint32_t)rec_bytes,
+                       &full_bar[s]);
+            continue;
+          }
+          const uint32_t dst0 = smem_u32(ring + s * stage_bytes) + lane * 16;
 #pragma unroll 4
           for (int pg = 0; pg < ppu; ++pg) {
             const int page = __shfl_sync(0xffffffffu, my, j * ppu + pg);
@@ -541,7 +558,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
             const uint32_t dst = dst0 + pg * rec_stride;
             for (int c = 0; c < hkv; ++c) cp_async_16(dst + c * 512, src + c * 512, nbytes);
           }
-          if (lane == 0) sValid[s] = (ball >> (j * ppu)) & unit_mask;
+          if (lane == 0) sValid[s] = umask;
           cp_async_mbar_arrive(&full_bar[s]);
           if (lane == 0) mbar_arrive(&full_bar[s]);  // release: publishes sValid
         }
@@ -789,7 +806,15 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
   if (groups > p.batch) groups = p.batch;
   if (groups < 1) groups = 1;
   p.groups = groups;
-  p.min_batch = tuning(kTuneMinBatch) > 0 ? tuning(kTuneMinBatch) : kMinBatch;
+  p.bulk = tuning(kTuneScoreCopy) == 1 ? 0 : 1;
+  // a claim's round trip costs 3-4 us under load: one batch must be worth that much streaming
+  // (~128 KB per SM), or the scheduler cannot keep the ring fed when units are small (few KV heads)
+  {
+    const int chunk_bytes = kChunkUnits * stage_bytes;
+    int mb = (128 * 1024 + chunk_bytes - 1) / chunk_bytes;
+    if (mb < kMinBatch) mb = kMinBatch;
+    p.min_batch = tuning(kTuneMinBatch) > 0 ? tuning(kTuneMinBatch) : mb;
+  }
   p.share_div = tuning(kTuneShareDiv) > 0 ? tuning(kTuneShareDiv) : 4;
   const size_t smem = score_smem_layout(stages, p.hq, p.hkv, p.batch, FUSED).total;
   auto kern = quest_page_score_kernel<NT, FUSED>;
