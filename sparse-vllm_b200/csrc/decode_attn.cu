@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
   // ---- setup: barriers, per-row page counts -> exclusive prefix
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
-      mbar_init(&full_bar[s], 33);  // 32 async copy arrivals + the producer's release
+      mbar_init(&full_bar[s], 1);  // the producer's expect_tx arrival; the copies' bytes complete the phase
       mbar_init(&empty_bar[s], HPC);
     }
     mbar_fence_init();
@@ -227,26 +227,27 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
         ++r_is;
         if (++hg_is == HG) hg_is = 0;
       }
-      const char* kbase = reinterpret_cast<const char*>(kc) + hg_is * G::TOK_BYTES + chunk * 16;
-      const char* vbase = reinterpret_cast<const char*>(vc) + hg_is * G::TOK_BYTES + chunk * 16;
-      const uint32_t dst0 = smem_u32(ring + s * G::STAGE_BYTES) + chunk * 16;
+      // One bulk async copy (UBLKCP) per token row and tensor: lanes 0-15 copy the K rows of tokens
+      // 0-15, lanes 16-31 the V rows (HPC*256 contiguous bytes each), straight from the lane that holds
+      // the slot: no shuffles, one instruction per row instead of 2-4 LDGSTS; the bytes are counted on
+      // the stage's mbarrier.  V rows of masked tokens are zeroed by hand (P is 0 there, but 0 x stale
+      // NaN would poison the accumulator); K rows of masked tokens only feed logits that are masked.
+      const bool is_v = lane >= 16;
+      const char* base = reinterpret_cast<const char*>(is_v ? vc : kc) + hg_is * G::TOK_BYTES;
+      const uint32_t dst = smem_u32(ring + s * G::STAGE_BYTES) + (is_v ? G::KV_BYTES : 0) + tok_lane * G::TOK_STRIDE;
       mbar_wait(&empty_bar[s], ph ^ 1);
-#pragma unroll
-      for (int t0 = 0; t0 < kPage; t0 += TPI) {
-        const int tok = t0 + sub;
-        const int slot = __shfl_sync(0xffffffffu, my, tok);
-        const int nbytes = slot >= 0 ? 16 : 0;
-        const int64_t off = (int64_t)max(slot, 0) * slot_bytes;
-        const uint32_t dst = dst0 + tok * G::TOK_STRIDE;
-#pragma unroll
-        for (int c = 0; c < CPR; ++c) {
-          cp_async_16(dst + c * 512, kbase + off + c * 512, nbytes);
-          cp_async_16(dst + G::KV_BYTES + c * 512, vbase + off + c * 512, nbytes);
+      if (mask != 0xffffu) {
+        if (my < 0 && is_v) {
+          uint4* z = reinterpret_cast<uint4*>(ring + s * G::STAGE_BYTES + G::KV_BYTES + tok_lane * G::TOK_STRIDE);
+          for (int c = 0; c < G::TOK_BYTES / 16; ++c) z[c] = make_uint4(0, 0, 0, 0);
         }
+        __syncwarp();  // the zeroed rows are ordered before lane 0's arrival below
       }
-      if (lane == 0) sValid[s] = mask;
-      cp_async_mbar_arrive(&full_bar[s]);
-      if (lane == 0) mbar_arrive(&full_bar[s]);  // release: publishes sValid
+      if (lane == 0) {
+        sValid[s] = mask;
+        mbar_arrive_expect_tx(&full_bar[s], (uint32_t)__popc(mask) * 2u * (uint32_t)G::TOK_BYTES);
+      }
+      if (my >= 0) bulk_g2s(dst, base + (int64_t)my * slot_bytes, (uint32_t)G::TOK_BYTES, &full_bar[s]);
 #pragma unroll
       for (int d = 0; d + 1 < kSlotPrefetch; ++d) pf[d] = pf[d + 1];
       pf[kSlotPrefetch - 1] = slot_new;
