@@ -140,6 +140,14 @@ def geometry(w: dict, hkv_local: int, hq_local: int) -> dict:
                 dense_bytes=dense_bytes)
 
 
+def ncu_traffic(workload_key: str, kernel: str):
+    """DRAM bytes per launch of `kernel` from the committed ncu capture of this workload, or None."""
+    try:
+        return json.loads((ROOT / "profiles" / "r1_traffic.json").read_text())[workload_key][kernel]
+    except Exception:
+        return None
+
+
 def measured_peak_gbs() -> tuple[float, str]:
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -413,11 +421,13 @@ def run_b200(args) -> dict:
     sparse_layers = w["layers"] - args.skip_layers
     step_bytes = (sel_bytes + attn_bytes) * sparse_layers + geo["dense_bytes"] * w["bsz"] * args.skip_layers
     roof = {"bound": "hbm", "kernel": "quest_page_score_kernel<fused select+pack>", "achieved": sel_bytes / (sel_ms * 1e-3) / 1e9,
-            "peak": peak, "unit": "GB/s", "peak_source": peak_src, "traffic": None,
+            "peak": peak, "unit": "GB/s", "peak_source": peak_src,
+            "traffic": ncu_traffic(w["key"], "quest_page_score_kernel") if world == 1 else None,
             "bytes_per_launch": sel_bytes, "avg_launch_ms": sel_ms}
     roof["frac"] = roof["achieved"] / peak
     roof_attn = {"bound": "hbm", "kernel": "sparse_decode_attn_kernel", "achieved": attn_bytes / (attn_ms * 1e-3) / 1e9,
-                 "peak": peak, "unit": "GB/s", "bytes_per_launch": attn_bytes, "avg_launch_ms": attn_ms}
+                 "peak": peak, "unit": "GB/s", "bytes_per_launch": attn_bytes, "avg_launch_ms": attn_ms,
+                 "traffic": ncu_traffic(w["key"], "sparse_decode_attn_kernel") if world == 1 else None}
     roof_attn["frac"] = roof_attn["achieved"] / peak
     roof_step = {"achieved": step_bytes / (ms_per_step * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                  "bytes_per_step": step_bytes}
