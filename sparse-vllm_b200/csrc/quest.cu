@@ -671,37 +671,52 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       const uint32_t abase = smem_u32(ring + s * stage_bytes) +
                              ((lane & 7) + ((lane >> 3) & 1) * 8) * rec_stride + (lane >> 4) * 16;
       float best0 = -INFINITY, best1 = -INFINITY;
-      for (int h = 0; h < hkv; ++h) {
-        float cp[NT][4], cn[NT][4];
+      // KV heads two at a time: the two heads' ldmatrix -> mma chains are independent, so the in-order
+      // issue of one warp overlaps their latencies (one head at a time left the consumers the bottleneck
+      // at Hkv 8); an odd last head runs alone
+      for (int h = 0; h < hkv; h += 2) {
+        const bool two = h + 1 < hkv;
+        const int h1 = two ? h + 1 : h;
+        float cp[2][NT][4], cn[2][NT][4];
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt)
+        for (int x = 0; x < 2; ++x)
 #pragma unroll
-          for (int e = 0; e < 4; ++e) cp[nt][e] = cn[nt][e] = 0.f;
-        const uint32_t amax_addr = abase + h * kRowBytes;
-        const uint32_t amin_addr = amax_addr + hkv * kRowBytes;
+          for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) cp[x][nt][e] = cn[x][nt][e] = 0.f;
+        const uint32_t amax0 = abase + h * kRowBytes, amin0 = amax0 + hkv * kRowBytes;
+        const uint32_t amax1 = abase + h1 * kRowBytes, amin1 = amax1 + hkv * kRowBytes;
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
-          uint32_t amax[4], amin[4];
-          ldmatrix_x4(amax, amax_addr + kk * 32);
-          ldmatrix_x4(amin, amin_addr + kk * 32);
+          uint32_t a0x[4], a0n[4], a1x[4], a1n[4];
+          ldmatrix_x4(a0x, amax0 + kk * 32);
+          ldmatrix_x4(a0n, amin0 + kk * 32);
+          ldmatrix_x4(a1x, amax1 + kk * 32);
+          ldmatrix_x4(a1n, amin1 + kk * 32);
 #pragma unroll
           for (int nt = 0; nt < NT; ++nt) {
-            const int qh = h * gsz + min(nt * 8 + g, gsz - 1);
-            const int fi = (qh * 8 + (kk ^ (qh & 7))) * 4 + t;
-            const uint2 bp = sq2[fi], bn = sq2[neg_off + fi];
-            mma_16816(cp[nt], amax, bp.x, bp.y);
-            mma_16816(cn[nt], amin, bn.x, bn.y);
+            const int q0 = h * gsz + min(nt * 8 + g, gsz - 1), q1 = h1 * gsz + min(nt * 8 + g, gsz - 1);
+            const int f0 = (q0 * 8 + (kk ^ (q0 & 7))) * 4 + t, f1 = (q1 * 8 + (kk ^ (q1 & 7))) * 4 + t;
+            const uint2 bp0 = sq2[f0], bn0 = sq2[neg_off + f0], bp1 = sq2[f1], bn1 = sq2[neg_off + f1];
+            mma_16816(cp[0][nt], a0x, bp0.x, bp0.y);
+            mma_16816(cn[0][nt], a0n, bn0.x, bn0.y);
+            mma_16816(cp[1][nt], a1x, bp1.x, bp1.y);
+            mma_16816(cn[1][nt], a1n, bn1.x, bn1.y);
           }
         }
         // c0:(page g, head 2t) c1:(g, 2t+1) c2:(g+8, 2t) c3:(g+8, 2t+1)
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-          float sc[4];
+        for (int x = 0; x < 2; ++x) {
+          if (x == 1 && !two) break;
 #pragma unroll
-          for (int e = 0; e < 4; ++e) sc[e] = round_bf16(round_bf16(cp[nt][e]) + round_bf16(cn[nt][e]));
-          const int col0 = nt * 8 + 2 * t;
-          if (col0 < gsz) best0 = fmaxf(best0, sc[0]), best1 = fmaxf(best1, sc[2]);
-          if (col0 + 1 < gsz) best0 = fmaxf(best0, sc[1]), best1 = fmaxf(best1, sc[3]);
+          for (int nt = 0; nt < NT; ++nt) {
+            float sc[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) sc[e] = round_bf16(round_bf16(cp[x][nt][e]) + round_bf16(cn[x][nt][e]));
+            const int col0 = nt * 8 + 2 * t;
+            if (col0 < gsz) best0 = fmaxf(best0, sc[0]), best1 = fmaxf(best1, sc[2]);
+            if (col0 + 1 < gsz) best0 = fmaxf(best0, sc[1]), best1 = fmaxf(best1, sc[3]);
+          }
         }
       }
       __syncwarp();
