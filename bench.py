@@ -39,6 +39,10 @@ WORKLOADS = {
                  ctx=131072, sink=64, decode_keep=3520, recent=512),
     "cfg5": dict(name="cfg5: Qwen3-32B shape quest bs16 ctx128K budget4096 TP", layers=64, hq=64, hkv=8, bsz=16,
                  ctx=131072, sink=64, decode_keep=3520, recent=512),
+    # h2o scored decode: the prompt is compacted to the budget by the prefill side, rows then cycle
+    # budget+1 .. budget+interval tokens between two burst evictions
+    "cfg4": dict(name="cfg4: Llama-3.1-8B shape h2o bs64 ctx32K budget2048 interval128", layers=32, hq=32, hkv=8,
+                 bsz=64, ctx=32768, h2o_budget=2048, h2o_interval=128, sink=0, decode_keep=0, recent=0),
 }
 
 
@@ -474,6 +478,160 @@ def run_b200(args) -> dict:
     return line
 
 
+# --------------------------------------------------------------------------------------- h2o arm
+def run_h2o(args) -> dict:
+    """cfg4: H2O scored decode through the cache-manager hooks, steady state over whole eviction
+    intervals (every step: per-layer slot claim, KV store, scored attention, normalise + accumulate;
+    one burst eviction per interval).  A "step" is one decode step of the batch over all layers."""
+    import torch
+    from types import SimpleNamespace
+    import svb200_import  # noqa: F401
+    from sparse_vllm_b200 import configs
+    from sparse_vllm_b200.attention_backend import B200AttentionBackend, decode_attention_layer
+    from sparse_vllm_b200.cache_manager.base import CacheManager
+    from sparse_vllm_b200.utils_context import reset_context, set_context
+
+    if args.gpus != 1:
+        raise SystemExit("cfg4 is a single-GPU workload")
+    w = pick_workload(args)
+    L, hq, hkv, bsz, budget, interval = w["layers"], w["hq"], w["hkv"], w["bsz"], w["h2o_budget"], w["h2o_interval"]
+    width = budget + interval
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    reset_context()
+    set_context(False)
+    cfg = configs.make_sparse_config(sparse_method="h2o", h2o_decode_budget=budget, h2o_prefill_budget=budget,
+                                     h2o_decode_eviction_interval=interval, h2o_recent_ratio=0.5)
+    mgr = CacheManager.create(cfg, num_layers=L, num_kv_heads=hkv, num_slots=bsz * width + 64, max_rows=bsz, device=dev)
+    gen = torch.Generator(device=dev).manual_seed(11)
+    for b in range(bsz):  # what the prefill side hands over: budget tokens per layer + their cumulative scores
+        k = torch.randn(L, budget, hkv, HEAD_DIM, generator=gen, device=dev, dtype=torch.bfloat16)
+        v = torch.randn(L, budget, hkv, HEAD_DIM, generator=gen, device=dev, dtype=torch.bfloat16)
+        mgr.admit_compacted_prompt(b, k, v, torch.rand(L, budget, generator=gen, device=dev))
+    del k, v
+    backend = B200AttentionBackend(provider=mgr._get_provider(hq))
+    seqs = [SimpleNamespace(seq_id=b) for b in range(bsz)]
+    ids = torch.zeros(bsz, dtype=torch.int64, device=dev)
+    pos = torch.zeros(bsz, dtype=torch.int64, device=dev)
+    slot_mapping = torch.zeros(bsz, dtype=torch.int32, device=dev)
+    ctx = torch.zeros(bsz, dtype=torch.int32, device=dev)
+    req = torch.zeros(bsz, dtype=torch.int32, device=dev)
+    q = torch.randn(L, bsz, hq, HEAD_DIM, generator=gen, device=dev, dtype=torch.bfloat16)
+    k_new = torch.randn(L, bsz, hkv, HEAD_DIM, generator=gen, device=dev, dtype=torch.bfloat16)
+    v_new = torch.randn(L, bsz, hkv, HEAD_DIM, generator=gen, device=dev, dtype=torch.bfloat16)
+    out = torch.empty(L, bsz, hq, HEAD_DIM, device=dev, dtype=torch.bfloat16)
+    h_q, h_k, h_v = (torch.empty(t.shape, dtype=t.dtype).pin_memory().copy_(t) for t in (q, k_new, v_new))
+    h_out = torch.empty(out.shape, dtype=out.dtype).pin_memory()
+
+    def layers():
+        for layer in range(L):
+            mgr.save_rope_kv_if_needed(layer, k_new[layer], v_new[layer])
+            decode_attention_layer(mgr, backend, layer, q[layer], mgr.decode_selection(layer), num_heads=hq,
+                                   num_kv_heads=hkv, out=out[layer])
+
+    stream = torch.cuda.Stream()
+    evictions = 0
+    with torch.cuda.stream(stream):
+        mgr.prepare_decode_static(seqs, ids, pos, slot_mapping, ctx, req)
+        layers()
+        evictions += bool(mgr.evict_after_decode())
+        stream.synchronize()
+        graph = None
+        if not args.no_graph:
+            mgr.prepare_decode_static(seqs, ids, pos, slot_mapping, ctx, req)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=stream):
+                layers()
+            graph.replay()  # capture does not execute: this is the step the prepare above belongs to
+            evictions += bool(mgr.evict_after_decode())
+        run_layers = graph.replay if graph is not None else layers
+
+        def step(e2e: bool):
+            nonlocal evictions
+            mgr.prepare_decode_static(seqs, ids, pos, slot_mapping, ctx, req)
+            if e2e:
+                q.copy_(h_q, non_blocking=True)
+                k_new.copy_(h_k, non_blocking=True)
+                v_new.copy_(h_v, non_blocking=True)
+            run_layers()
+            evictions += bool(mgr.evict_after_decode())
+            if e2e:
+                h_out.copy_(out, non_blocking=True)
+
+        def steps_to_interval_start() -> int:
+            return (budget + interval - int(mgr.row_seq_lens[0])) % interval
+
+        for _ in range(steps_to_interval_start() + interval):  # warm-up: into steady state, one whole interval
+            step(False)
+        torch.cuda.synchronize()
+        sampler = ClockSampler(0)
+        sampler.start()
+        n_int = max(1, round(args.steps / interval))
+        steps = n_int * interval
+        ev0 = evictions
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            step(False)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        dev_ms = e0.elapsed_time(e1)
+        assert evictions - ev0 == n_int, (evictions, ev0, n_int)
+
+        timers = KernelTimers(mgr._get_provider(hq))
+        timers.enabled = True
+        for _ in range(3):  # eager, event pairs around the scored attention launch
+            mgr.prepare_decode_static(seqs, ids, pos, slot_mapping, ctx, req)
+            layers()
+            evictions += bool(mgr.evict_after_decode())
+        timers.enabled = False
+        torch.cuda.synchronize()
+        attn_ms = timers.summary()["sparse_decode_attn"]["avg_ms"]
+        attn_len = int(mgr.row_seq_lens[0])  # the rows' length at those launches (+-1)
+
+        for _ in range(steps_to_interval_start()):
+            step(True)
+        torch.cuda.synchronize()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(stream)
+        for _ in range(steps):
+            step(True)
+        f1.record(stream)
+        torch.cuda.synchronize()
+        e2e_ms = f0.elapsed_time(f1)
+        clocks = sampler.stop()
+
+    ms_per_step = dev_ms / steps
+    peak, peak_src = measured_peak_gbs()
+    tok_bytes = 2 * hkv * HEAD_DIM * 2  # K + V rows of one token
+    # per (row, layer): KV of the tokens held, their slot ids, the fp32 score row (fill + max-update + normalise)
+    attn_bytes = bsz * attn_len * (tok_bytes + 4 + 3 * 4)
+    mean_len = budget + (interval + 1) / 2
+    step_bytes = L * bsz * mean_len * (tok_bytes + 4 + 3 * 4)
+    roof = {"bound": "hbm", "kernel": "sparse_decode_attn_kernel<score2d>", "achieved": attn_bytes / (attn_ms * 1e-3) / 1e9,
+            "peak": peak, "unit": "GB/s", "peak_source": peak_src, "traffic": None, "bytes_per_launch": attn_bytes,
+            "avg_launch_ms": attn_ms, "tokens_per_row": attn_len}
+    roof["frac"] = roof["achieved"] / peak
+    roof_step = {"achieved": step_bytes / (ms_per_step * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "bytes_per_step": step_bytes}
+    roof_step["frac"] = roof_step["achieved"] / peak
+    launches_per_step = 3 * L + 1  # store, scored attention, normalise+accumulate per layer; score refill
+    return {
+        "metric": "h2o_scored_decode_tokens_per_s", "value": bsz / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": 1,
+        "steps": steps, "warmup": interval, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": w["name"], "layers": L, "q_heads": hq, "kv_heads": hkv, "batch": bsz,
+                   "h2o_decode_budget": budget, "h2o_decode_eviction_interval": interval, "recent_ratio": 0.5,
+                   "row_tokens": f"{budget + 1}..{width}", "evictions_timed": n_int,
+                   "l2": "inputs larger than L2 (>= 0.55 GB of KV touched per layer, 32 distinct layers)",
+                   "timed": ("cuda graph replay of the layer loop" if graph is not None else "eager")
+                   + " + per-step host prepare + burst eviction every interval"},
+        "e2e": {"value": bsz / (e2e_ms / steps * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / steps,
+                "h2d_bytes_per_step": (h_q.numel() + h_k.numel() + h_v.numel()) * 2, "d2h_bytes_per_step": h_out.numel() * 2},
+        "gpu_launches": launches_per_step * steps + 1 * n_int,
+        "roofline": roof, "roofline_step": roof_step, "clocks": clocks,
+    }
+
+
 # --------------------------------------------------------------------------------------- CPU arm
 class CpuSample:
     """Bounded sample of the same workload on the host cores with the oracle port (oracle/): `rows`
@@ -536,6 +694,8 @@ def run_reference(args) -> dict:
     if rank != 0:
         return {}
     w = pick_workload(args)
+    if "h2o_budget" in w:
+        raise SystemExit("--impl reference times the quest workloads (cfg2/cfg3/cfg5)")
     steps, warmup = args.steps, max(args.warmup, 1)
     sample = CpuSample(w, rows=2)
     # keep the whole run within a few minutes
@@ -566,15 +726,20 @@ def secondary_workload(key: str, args) -> dict:
     """The same bench on another BASELINE config in a fresh process (its own KV pools), summarised."""
     cmd = [sys.executable, str(ROOT / "bench.py"), "--workload", key, "--no-cpu-baseline", "--steps", str(args.steps),
            "--warmup", str(args.warmup)]
+    res = None
     try:
         res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
         d = json.loads([ln for ln in res.stdout.splitlines() if ln.startswith("{")][-1])
     except Exception as exc:  # the primary line must not depend on the secondary one
-        return {"error": f"{type(exc).__name__}: {exc}"}
-    return {"workload": d["config"]["workload"], "value": d["value"], "unit": d["unit"], "ms_per_step": d["ms_per_step"],
-            "e2e": d["e2e"]["value"], "roofline_frac": d["roofline"]["frac"],
-            "roofline_attention_frac": d["roofline_attention"]["frac"], "roofline_step_frac": d["roofline_step"]["frac"],
-            "score_launch_ms": d["roofline"]["avg_launch_ms"], "attention_launch_ms": d["roofline_attention"]["avg_launch_ms"]}
+        return {"error": f"{type(exc).__name__}: {exc}", "stderr_tail": res.stderr[-400:] if res is not None else None}
+    out = {"workload": d["config"]["workload"], "metric": d["metric"], "value": d["value"], "unit": d["unit"],
+           "ms_per_step": d["ms_per_step"], "steps": d["steps"], "e2e": d["e2e"]["value"],
+           "roofline_kernel": d["roofline"]["kernel"], "roofline_frac": d["roofline"]["frac"],
+           "roofline_launch_ms": d["roofline"]["avg_launch_ms"], "roofline_step_frac": d["roofline_step"]["frac"]}
+    if "roofline_attention" in d:
+        out["roofline_attention_frac"] = d["roofline_attention"]["frac"]
+        out["attention_launch_ms"] = d["roofline_attention"]["avg_launch_ms"]
+    return out
 
 
 def main():
@@ -582,10 +747,11 @@ def main():
     if args.impl == "reference":
         line = run_reference(args)
     else:
-        line = run_b200(args)
+        h2o = args.workload == "cfg4"
+        line = run_h2o(args) if h2o else run_b200(args)
         if line and args.gpus == 1 and args.workload == "auto":
-            line["other_workloads"] = {"cfg3": secondary_workload("cfg3", args)}
-        if line and not args.no_cpu_baseline and args.gpus == 1:
+            line["other_workloads"] = {"cfg3": secondary_workload("cfg3", args), "cfg4": secondary_workload("cfg4", args)}
+        if line and not args.no_cpu_baseline and args.gpus == 1 and not h2o:
             line["cpu_baseline"] = cpu_baseline(pick_workload(args), args.cpu_seconds)
     if line and not line.pop("_printed", False):
         print(json.dumps(line), flush=True)

@@ -55,7 +55,9 @@ class H2OCacheManager(CacheManager):
         self.row_seq_lens = np.zeros((R,), dtype=np.int32)
         self.seq_id_to_row: dict[int, int] = {}
         self._free_rows = list(range(R - 1, -1, -1))
-        self._layer_slot_mapping: torch.Tensor | None = None  # [L, B] slots of the current decode token
+        # [L, rows] slots of the current decode token; a static buffer so that a captured layer loop replays
+        self._layer_slot_mapping = torch.zeros((L, R), dtype=torch.int32, device=self.device)
+        self._batch = 0
         self._kv_lens_dev = torch.zeros((R,), dtype=torch.int32, device=self.device)
         self._rows_dev: torch.Tensor | None = None
         self._batch_rows: list[int] = []
@@ -133,7 +135,8 @@ class H2OCacheManager(CacheManager):
         rows_dev = torch.as_tensor(rows, dtype=torch.int64, device=self.device)
         lens_dev = torch.as_tensor(lens.astype(np.int64), device=self.device)
         self.slot_tables[:, rows_dev, lens_dev] = new
-        self._layer_slot_mapping = new.contiguous()
+        self._layer_slot_mapping[:, :bsz] = new
+        self._batch = bsz
         self.row_seq_lens[rows] = lens + 1
         ctx = torch.as_tensor((lens + 1).astype(np.int32), device=self.device)
         context_lens[:bsz] = ctx
@@ -149,7 +152,7 @@ class H2OCacheManager(CacheManager):
         self.step_scores[:, :bsz].fill_(SCORE_FILL)  # sparse_controller.py:545-594
 
     def layer_slot_mapping(self, layer_idx: int) -> torch.Tensor:
-        return self._layer_slot_mapping[self.kv_layer_index(layer_idx)]
+        return self._layer_slot_mapping[self.kv_layer_index(layer_idx), : self._batch]
 
     def save_rope_kv_if_needed(self, layer_idx, k, v, slot_mapping=None) -> None:
         k_cache, v_cache = self.get_layer_kv_cache(layer_idx)
