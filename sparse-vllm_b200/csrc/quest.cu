@@ -366,7 +366,8 @@ struct ScoreParams {
   int64_t score_stride;
   int batch, hq, hkv, n_cols, stages;
   int bulk;  // 1: one UBLKCP per page record, 0: 16-byte LDGSTS
-  int ppu;  // pages per unit: 16, or 8 when a page's record is 4 KB (Hkv 8) so that six stages still fit
+  int ppu;     // pages per unit: 16 (8 only for an odd head count > 4 that cannot be split)
+  int hsplit;  // ring stages per unit: 1, or 2 = a stage holds half of the KV heads of the unit's pages
   unsigned long long* dbg_times;  // experiments: per-CTA timestamps (svb200_debug_times), else null
   int consumers;  // consumer warps that take units; divides `stages` (see the kernel)
   int producers;  // producer warps that feed units; divides `stages`
@@ -385,16 +386,21 @@ struct ScoreSmemLayout {
   int ring_off, q_off, bar_off, valid_off, rows_off, sched_off, select_off, total;
 };
 
-__host__ __device__ inline int score_rec_stride(int hkv) { return hkv * 2 * kRowBytes + 16; }
+// shared-memory stride of one page inside a stage holding `heads` KV heads (max rows, then min rows)
+__host__ __device__ inline int score_rec_stride(int heads) { return heads * 2 * kRowBytes + 16; }
 
-__host__ __device__ inline int score_pages_per_unit(int hkv) { return hkv > 4 ? 8 : 16; }
+// A 16-page unit of Hkv 8 is 64 KB: as one stage only three would fit.  Such a unit is streamed as two
+// stages of four heads each (two 1 KB copies per page and stage) and the consumer warp keeps the
+// running maximum over both; the mma tile stays 16 pages tall (8-page units wasted half of it).
+__host__ __device__ inline int score_head_split(int hkv) { return (hkv > 4 && hkv % 2 == 0) ? 2 : 1; }
+__host__ __device__ inline int score_pages_per_unit(int hkv, int hsplit) { return (hkv > 4 && hsplit == 1) ? 8 : 16; }
 
-__host__ __device__ inline ScoreSmemLayout score_smem_layout(int stages, int hq, int hkv, int batch,
+__host__ __device__ inline ScoreSmemLayout score_smem_layout(int stages, int hq, int hkv, int hsplit, int batch,
                                                              bool fused) {
   ScoreSmemLayout L;
   int off = 0;
-  L.ring_off = off;   off += stages * score_pages_per_unit(hkv) * score_rec_stride(hkv);
-  L.q_off = off;      off += 2 * hq * kRowBytes;
+  L.ring_off = off;   off += stages * score_pages_per_unit(hkv, hsplit) * score_rec_stride(hkv / hsplit);
+  L.q_off = off;      off += hq * kRowBytes;
   L.bar_off = off;    off += 2 * stages * 8;
   L.valid_off = off;  off += ((stages * 4 + 15) / 16) * 16;
   L.rows_off = off;   off += (2 * batch * 4 + 15) / 16 * 16;  // valid pages, page-table row of each row
@@ -404,6 +410,11 @@ __host__ __device__ inline ScoreSmemLayout score_smem_layout(int stages, int hq,
   return L;
 }
 
+// bf16x2 clamp_min(0) / clamp_max(0) by sign bit (NaN keeps its sign's side, like the reference's clamp)
+__device__ __forceinline__ uint32_t q_neg_mask(uint32_t x) { return ((x >> 15) & 0x00010001u) * 0xffffu; }
+__device__ __forceinline__ uint32_t q_pos(uint32_t x) { return x & ~q_neg_mask(x); }
+__device__ __forceinline__ uint32_t q_neg(uint32_t x) { return x & q_neg_mask(x); }
+
 __device__ __forceinline__ void score_consumer_sync() { group_sync<1, kScoreConsumerThreads>(); }
 
 template <int NT, bool FUSED_SELECT>
@@ -411,14 +422,17 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   extern __shared__ __align__(128) unsigned char smem[];
   const int S = p.stages, hq = p.hq, hkv = p.hkv, B = p.batch;
   const int gsz = hq / hkv;
-  const int rec_stride = score_rec_stride(hkv);
-  const int rec_bytes = hkv * 2 * kRowBytes;
+  const int hs = p.hsplit, hh = hkv / hs;  // stages per unit, KV heads per stage
+  const int rec_stride = score_rec_stride(hh);
+  const int rec_bytes = hkv * 2 * kRowBytes;  // a page's record in HBM: max rows of all heads, then min rows
+  const int part_bytes = hh * kRowBytes;      // max (or min) rows of one stage's heads
   const int ppu = p.ppu;
   const uint32_t unit_mask = (1u << ppu) - 1u;
   const int stage_bytes = ppu * rec_stride;
-  const ScoreSmemLayout L = score_smem_layout(S, hq, hkv, B, FUSED_SELECT);
+  const ScoreSmemLayout L = score_smem_layout(S, hq, hkv, hs, B, FUSED_SELECT);
   unsigned char* ring = smem + L.ring_off;
-  // sq[sign][head][kk][t] : uint2 {b0, b1} B fragments, kk XOR-swizzled by head
+  // sq[head][kk][t] : uint2 {b0, b1} B fragments of q, kk XOR-swizzled by head; q+ / q- are taken from
+  // them with one bf16x2 max / min each when a fragment is used (two copies cost a ring stage at 64 heads)
   uint32_t* sq = reinterpret_cast<uint32_t*>(smem + L.q_off);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.bar_off);
   uint64_t* empty_bar = full_bar + S;
@@ -469,15 +483,15 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
 
   if (warp == kScoreConsumerWarps + kScoreProducerWarps) {
     // ============================================================== scheduler
-    sched_run(sched, next_chunk, B, p.groups, p.min_batch, p.share_div, min(kSchedQueue, (S + kChunkUnits - 1) / kChunkUnits + kIdDepth + 1),
+    sched_run(sched, next_chunk, B, p.groups, p.min_batch, p.share_div, min(kSchedQueue, (S / hs + kChunkUnits - 1) / kChunkUnits + kIdDepth + 1),
               units_of_row);
     return;
   }
 
   if (warp >= kScoreConsumerWarps && warp < kScoreConsumerWarps + kScoreProducerWarps) {
     // ============================================================== producers
-    // unit i (CTA-local running index) is fed by producer i % NP into stage i % S, NP | S: a stage
-    // is always refilled by the same warp.  Lane l holds the physical page of logical page
+    // stage-load ii = i * hs + part (i: CTA-local running unit index) is fed by producer ii % NP into
+    // stage ii % S, NP | S: a stage is always refilled by the same warp.  Lane l holds the physical page of logical page
     // unit_begin*16 + l of the chunk (2 units x 16 pages), fetched kIdDepth chunks ahead.
     const int pw = warp - kScoreConsumerWarps;
     const int NP = p.producers;
@@ -526,27 +540,36 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
         const int my = (pa >= 0 && pa < p.num_pages) ? pa : -1;
         const uint32_t ball = __ballot_sync(0xffffffffu, my >= 0);
         if (dbg) w_ids += global_timer_ns() - ti;
-        for (int j = 0; j < cur.units(); ++j) {
-          const int i = cur.unit_base + j;
-          if (i % NP != pw) continue;
-          const int s = i % S;
-          const uint32_t ph = (uint32_t)(i / S) & 1u;
-          const uint32_t umask = (ball >> (j * ppu)) & unit_mask;
+        for (int jj = 0; jj < cur.units() * hs; ++jj) {
+          const int j = jj / hs, part = jj - j * hs;
+          const int ii = cur.unit_base * hs + jj;
+          if (ii % NP != pw) continue;
+          const int s = ii % S;
+          const uint32_t round = (uint32_t)(ii / S), ph = round & 1u;
+          // valid pages of the unit | the stage's fill count (the consumer checks it: see there)
+          const uint32_t umask = (ball >> (j * ppu)) & unit_mask, tagged = umask | (round << 16);
           const unsigned long long te = dbg ? global_timer_ns() : 0;
           mbar_wait(&empty_bar[s], ph ^ 1u);
           if (dbg) w_empty += global_timer_ns() - te;
           if (p.bulk) {
-            // one bulk async copy (UBLKCP) per page record, issued by the lane that holds the page id:
-            // no shuffles, one instruction per Hkv*512 bytes; bytes are counted on the stage's mbarrier
+            // bulk async copies (UBLKCP) issued by the lane that holds the page id: no shuffles, one
+            // instruction per record (or two per half record: its max rows, its min rows); bytes are
+            // counted on the stage's mbarrier
             if (lane == 0) {
-              sValid[s] = umask;
-              mbar_arrive_expect_tx(&full_bar[s], (uint32_t)__popc(umask) * (uint32_t)rec_bytes);
+              sValid[s] = tagged;
+              mbar_arrive_expect_tx(&full_bar[s], (uint32_t)__popc(umask) * 2u * (uint32_t)part_bytes);
             }
             const int pg = lane - j * ppu;
-            if (pg >= 0 && pg < ppu && my >= 0)
-              bulk_g2s(smem_u32(ring + s * stage_bytes) + pg * rec_stride,
-                       reinterpret_cast<const char*>(p.bounds) + (int64_t)my * rec_bytes, (uint32_t)rec_bytes,
-                       &full_bar[s]);
+            if (pg >= 0 && pg < ppu && my >= 0) {
+              const uint32_t dst = smem_u32(ring + s * stage_bytes) + pg * rec_stride;
+              const char* src = reinterpret_cast<const char*>(p.bounds) + (int64_t)my * rec_bytes + part * part_bytes;
+              if (hs == 1) {
+                bulk_g2s(dst, src, (uint32_t)rec_bytes, &full_bar[s]);
+              } else {
+                bulk_g2s(dst, src, (uint32_t)part_bytes, &full_bar[s]);
+                bulk_g2s(dst + part_bytes, src + hkv * kRowBytes, (uint32_t)part_bytes, &full_bar[s]);
+              }
+            }
             continue;
           }
           const uint32_t dst0 = smem_u32(ring + s * stage_bytes) + lane * 16;
@@ -558,7 +581,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
             const uint32_t dst = dst0 + pg * rec_stride;
             for (int c = 0; c < hkv; ++c) cp_async_16(dst + c * 512, src + c * 512, nbytes);
           }
-          if (lane == 0) sValid[s] = umask;
+          if (lane == 0) sValid[s] = tagged;
           cp_async_mbar_arrive(&full_bar[s]);
           if (lane == 0) mbar_arrive(&full_bar[s]);  // release: publishes sValid
         }
@@ -608,8 +631,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   // ================================================================ consumers
   const int g = lane >> 2, t = lane & 3;
   const uint2* sq2 = reinterpret_cast<const uint2*>(sq);
-  const int neg_off = hq * 32;  // uint2 offset of the q- fragments
-  // q+ / q- (clamp_min(0) / clamp_max(0), quest.py:1796-1797) of row b in B-fragment order
+  // q of row b in B-fragment order (q+ / q- = clamp_min(0) / clamp_max(0), quest.py:1796-1797, see q_pos / q_neg)
   auto stage_q = [&](int b) {
     const uint4* qrow = reinterpret_cast<const uint4*>(p.q + (int64_t)b * p.q_stride_b);
     for (int c = tid; c < hq * 16; c += kScoreConsumerThreads) {
@@ -619,19 +641,14 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       const int kk = chunk >> 1, hf = chunk & 1;
       const int base = ((head * 8 + (kk ^ (head & 7))) * 4) * 2 + hf;
 #pragma unroll
-      for (int tt = 0; tt < 4; ++tt) {
-        const uint32_t lo = w[tt] & 0xffffu, hi = w[tt] >> 16;
-        const uint32_t lo_neg = (lo & 0x8000u) ? lo : 0u, lo_pos = (lo & 0x8000u) ? 0u : lo;
-        const uint32_t hi_neg = (hi & 0x8000u) ? hi : 0u, hi_pos = (hi & 0x8000u) ? 0u : hi;
-        sq[base + tt * 2] = lo_pos | (hi_pos << 16);
-        sq[neg_off * 2 + base + tt * 2] = lo_neg | (hi_neg << 16);
-      }
+      for (int tt = 0; tt < 4; ++tt) sq[base + tt * 2] = w[tt];
     }
   };
 
-  // Unit i goes to warp i % NW, and NW divides S: a stage is always drained by the same warp, so
-  // the phase a warp waits for is never more than one ahead of the barrier (parity waits cannot
-  // tell a phase from the one two before it).
+  // Unit i goes to warp i % NW, which drains all of its hs stage-loads.  A parity wait cannot tell a
+  // phase from the one two before it, and a stage may be drained by different warps in consecutive
+  // rounds (NW need not divide S / hs): the producer therefore tags the stage's valid mask with its
+  // fill count, and a warp only trusts the barrier once the tag shows the fill it is waiting for.
   const int NW = p.consumers;
   bool first_seen = false;
   int cur_row = -2, visit_units = 0, total_units = 0;  // -2: no row yet (-1 is the end descriptor)
@@ -662,20 +679,32 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
     for (int j = 0; j < d.units(); ++j) {
       const int i = d.unit_base + j;
       if (warp >= NW || i % NW != warp) continue;
-      const int s = i % S;
+      float best0 = -INFINITY, best1 = -INFINITY;
+      uint32_t mask = 0;
+      for (int part = 0; part < hs; ++part) {
+      const int ii = i * hs + part;
+      const int s = ii % S;
+      const uint32_t round = (uint32_t)(ii / S);
       const unsigned long long tf = dbg ? global_timer_ns() : 0;
-      mbar_wait(&full_bar[s], (uint32_t)(i / S) & 1u);
+      while (true) {
+        mbar_wait(&full_bar[s], round & 1u);
+        mask = (uint32_t)ld_volatile_shared(reinterpret_cast<const int*>(sValid + s));
+        if ((mask >> 16) == (round & 0xffffu)) {
+          mbar_wait(&full_bar[s], round & 1u);  // the tag is written before the copies land: wait for them
+          break;
+        }
+        __nanosleep(64);
+      }
       if (dbg) c_full += global_timer_ns() - tf;
       if (dbg && tid == 0 && !first_seen) dbg[2] = global_timer_ns(), first_seen = true;
-      const uint32_t mask = sValid[s];
       const uint32_t abase = smem_u32(ring + s * stage_bytes) +
                              ((lane & 7) + ((lane >> 3) & 1) * 8) * rec_stride + (lane >> 4) * 16;
-      float best0 = -INFINITY, best1 = -INFINITY;
       // KV heads two at a time: the two heads' ldmatrix -> mma chains are independent, so the in-order
       // issue of one warp overlaps their latencies (one head at a time left the consumers the bottleneck
       // at Hkv 8); an odd last head runs alone
-      for (int h = 0; h < hkv; h += 2) {
-        const bool two = h + 1 < hkv;
+      const int hbase = part * hh;  // first KV head of this stage
+      for (int h = 0; h < hh; h += 2) {
+        const bool two = h + 1 < hh;
         const int h1 = two ? h + 1 : h;
         float cp[2][NT][4], cn[2][NT][4];
 #pragma unroll
@@ -684,8 +713,8 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
           for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
             for (int e = 0; e < 4; ++e) cp[x][nt][e] = cn[x][nt][e] = 0.f;
-        const uint32_t amax0 = abase + h * kRowBytes, amin0 = amax0 + hkv * kRowBytes;
-        const uint32_t amax1 = abase + h1 * kRowBytes, amin1 = amax1 + hkv * kRowBytes;
+        const uint32_t amax0 = abase + h * kRowBytes, amin0 = amax0 + hh * kRowBytes;
+        const uint32_t amax1 = abase + h1 * kRowBytes, amin1 = amax1 + hh * kRowBytes;
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           uint32_t a0x[4], a0n[4], a1x[4], a1n[4];
@@ -695,13 +724,13 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
           ldmatrix_x4(a1n, amin1 + kk * 32);
 #pragma unroll
           for (int nt = 0; nt < NT; ++nt) {
-            const int q0 = h * gsz + min(nt * 8 + g, gsz - 1), q1 = h1 * gsz + min(nt * 8 + g, gsz - 1);
+            const int q0 = (hbase + h) * gsz + min(nt * 8 + g, gsz - 1), q1 = (hbase + h1) * gsz + min(nt * 8 + g, gsz - 1);
             const int f0 = (q0 * 8 + (kk ^ (q0 & 7))) * 4 + t, f1 = (q1 * 8 + (kk ^ (q1 & 7))) * 4 + t;
-            const uint2 bp0 = sq2[f0], bn0 = sq2[neg_off + f0], bp1 = sq2[f1], bn1 = sq2[neg_off + f1];
-            mma_16816(cp[0][nt], a0x, bp0.x, bp0.y);
-            mma_16816(cn[0][nt], a0n, bn0.x, bn0.y);
-            mma_16816(cp[1][nt], a1x, bp1.x, bp1.y);
-            mma_16816(cn[1][nt], a1n, bn1.x, bn1.y);
+            const uint2 b0 = sq2[f0], b1 = sq2[f1];
+            mma_16816(cp[0][nt], a0x, q_pos(b0.x), q_pos(b0.y));
+            mma_16816(cn[0][nt], a0n, q_neg(b0.x), q_neg(b0.y));
+            mma_16816(cp[1][nt], a1x, q_pos(b1.x), q_pos(b1.y));
+            mma_16816(cn[1][nt], a1n, q_neg(b1.x), q_neg(b1.y));
           }
         }
         // c0:(page g, head 2t) c1:(g, 2t+1) c2:(g+8, 2t) c3:(g+8, 2t+1)
@@ -721,6 +750,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty_bar[s]);
+      }  // part
       best0 = fmaxf(best0, __shfl_xor_sync(0xffffffffu, best0, 1));
       best0 = fmaxf(best0, __shfl_xor_sync(0xffffffffu, best0, 2));
       best1 = fmaxf(best1, __shfl_xor_sync(0xffffffffu, best1, 1));
@@ -789,9 +819,11 @@ int launch_quest_select_pack(const void* scores, int64_t score_stride, int n_col
 
 template <int NT, bool FUSED>
 static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
-  const int fixed = score_smem_layout(0, p.hq, p.hkv, p.batch, FUSED).total + 256;  // + static smem
-  p.ppu = score_pages_per_unit(p.hkv);
-  const int stage_bytes = p.ppu * score_rec_stride(p.hkv);
+  p.hsplit = score_head_split(p.hkv);
+  if (const int t = tuning(kTuneScoreSplit); t > 0 && p.hkv % t == 0) p.hsplit = t;  // experiments
+  p.ppu = score_pages_per_unit(p.hkv, p.hsplit);
+  const int fixed = score_smem_layout(0, p.hq, p.hkv, p.hsplit, p.batch, FUSED).total + 256;  // + static smem
+  const int stage_bytes = p.ppu * score_rec_stride(p.hkv / p.hsplit);
   int stages = (kScoreMaxSmem - fixed) / (stage_bytes + 20);
   if (stages > 24) stages = 24;
   if (stages < 2) {
@@ -805,7 +837,7 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
   for (int s2 = stages; s2 >= 2 && s2 >= stages - 3; --s2) {
     int c = 1, pr = 1;
     for (int d = kScoreConsumerWarps; d >= 1; --d)
-      if (s2 % d == 0) { c = d; break; }
+      if (s2 % d == 0 || p.hsplit > 1) { c = d; break; }
     for (int d = kScoreProducerWarps; d >= 1; --d)
       if (s2 % d == 0) { pr = d; break; }
     if (c + 2 * pr > best_c + 2 * best_p || s2 == stages) best_c = c, best_p = pr, best_s = s2;
@@ -821,17 +853,17 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
   if (groups > p.batch) groups = p.batch;
   if (groups < 1) groups = 1;
   p.groups = groups;
-  p.bulk = tuning(kTuneScoreCopy) == 1 ? 0 : 1;
+  p.bulk = (tuning(kTuneScoreCopy) == 1 && p.hsplit == 1) ? 0 : 1;
   // a claim's round trip costs 3-4 us under load: one batch must be worth that much streaming
   // (~128 KB per SM), or the scheduler cannot keep the ring fed when units are small (few KV heads)
   {
-    const int chunk_bytes = kChunkUnits * stage_bytes;
+    const int chunk_bytes = kChunkUnits * stage_bytes * p.hsplit;
     int mb = (128 * 1024 + chunk_bytes - 1) / chunk_bytes;
     if (mb < kMinBatch) mb = kMinBatch;
     p.min_batch = tuning(kTuneMinBatch) > 0 ? tuning(kTuneMinBatch) : mb;
   }
   p.share_div = tuning(kTuneShareDiv) > 0 ? tuning(kTuneShareDiv) : 4;
-  const size_t smem = score_smem_layout(stages, p.hq, p.hkv, p.batch, FUSED).total;
+  const size_t smem = score_smem_layout(stages, p.hq, p.hkv, p.hsplit, p.batch, FUSED).total;
   auto kern = quest_page_score_kernel<NT, FUSED>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return cuda_error("quest_page_score smem attr", e);
