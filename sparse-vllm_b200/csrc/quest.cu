@@ -396,11 +396,11 @@ __host__ __device__ inline int score_head_split(int hkv) { return (hkv > 4 && hk
 __host__ __device__ inline int score_pages_per_unit(int hkv, int hsplit) { return (hkv > 4 && hsplit == 1) ? 8 : 16; }
 
 __host__ __device__ inline ScoreSmemLayout score_smem_layout(int stages, int hq, int hkv, int hsplit, int batch,
-                                                             bool fused) {
+                                                             bool fused, int q_copies) {
   ScoreSmemLayout L;
   int off = 0;
   L.ring_off = off;   off += stages * score_pages_per_unit(hkv, hsplit) * score_rec_stride(hkv / hsplit);
-  L.q_off = off;      off += hq * kRowBytes;
+  L.q_off = off;      off += q_copies * hq * kRowBytes;
   L.bar_off = off;    off += 2 * stages * 8;
   L.valid_off = off;  off += ((stages * 4 + 15) / 16) * 16;
   L.rows_off = off;   off += (2 * batch * 4 + 15) / 16 * 16;  // valid pages, page-table row of each row
@@ -417,7 +417,9 @@ __device__ __forceinline__ uint32_t q_neg(uint32_t x) { return x & q_neg_mask(x)
 
 __device__ __forceinline__ void score_consumer_sync() { group_sync<1, kScoreConsumerThreads>(); }
 
-template <int NT, bool FUSED_SELECT>
+// QSPLIT: q+ and q- are both staged (when that does not cost a ring stage); else q is staged once and
+// split by sign when a fragment is used.
+template <int NT, bool FUSED_SELECT, bool QSPLIT>
 __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(ScoreParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int S = p.stages, hq = p.hq, hkv = p.hkv, B = p.batch;
@@ -429,10 +431,10 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   const int ppu = p.ppu;
   const uint32_t unit_mask = (1u << ppu) - 1u;
   const int stage_bytes = ppu * rec_stride;
-  const ScoreSmemLayout L = score_smem_layout(S, hq, hkv, hs, B, FUSED_SELECT);
+  const ScoreSmemLayout L = score_smem_layout(S, hq, hkv, hs, B, FUSED_SELECT, QSPLIT ? 2 : 1);
   unsigned char* ring = smem + L.ring_off;
-  // sq[head][kk][t] : uint2 {b0, b1} B fragments of q, kk XOR-swizzled by head; q+ / q- are taken from
-  // them with one bf16x2 max / min each when a fragment is used (two copies cost a ring stage at 64 heads)
+  // sq[sign][head][kk][t] : uint2 {b0, b1} B fragments of q+ / q-, kk XOR-swizzled by head (QSPLIT), or
+  // sq[head][kk][t] of q itself, split by sign when a fragment is used (two copies cost a ring stage at 64 heads)
   uint32_t* sq = reinterpret_cast<uint32_t*>(smem + L.q_off);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.bar_off);
   uint64_t* empty_bar = full_bar + S;
@@ -631,6 +633,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   // ================================================================ consumers
   const int g = lane >> 2, t = lane & 3;
   const uint2* sq2 = reinterpret_cast<const uint2*>(sq);
+  const int neg_off = hq * 32;  // uint2 offset of the q- fragments (QSPLIT)
   // q of row b in B-fragment order (q+ / q- = clamp_min(0) / clamp_max(0), quest.py:1796-1797, see q_pos / q_neg)
   auto stage_q = [&](int b) {
     const uint4* qrow = reinterpret_cast<const uint4*>(p.q + (int64_t)b * p.q_stride_b);
@@ -641,7 +644,14 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       const int kk = chunk >> 1, hf = chunk & 1;
       const int base = ((head * 8 + (kk ^ (head & 7))) * 4) * 2 + hf;
 #pragma unroll
-      for (int tt = 0; tt < 4; ++tt) sq[base + tt * 2] = w[tt];
+      for (int tt = 0; tt < 4; ++tt) {
+        if constexpr (QSPLIT) {
+          sq[base + tt * 2] = q_pos(w[tt]);
+          sq[neg_off * 2 + base + tt * 2] = q_neg(w[tt]);
+        } else {
+          sq[base + tt * 2] = w[tt];
+        }
+      }
     }
   };
 
@@ -726,11 +736,17 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
           for (int nt = 0; nt < NT; ++nt) {
             const int q0 = (hbase + h) * gsz + min(nt * 8 + g, gsz - 1), q1 = (hbase + h1) * gsz + min(nt * 8 + g, gsz - 1);
             const int f0 = (q0 * 8 + (kk ^ (q0 & 7))) * 4 + t, f1 = (q1 * 8 + (kk ^ (q1 & 7))) * 4 + t;
-            const uint2 b0 = sq2[f0], b1 = sq2[f1];
-            mma_16816(cp[0][nt], a0x, q_pos(b0.x), q_pos(b0.y));
-            mma_16816(cn[0][nt], a0n, q_neg(b0.x), q_neg(b0.y));
-            mma_16816(cp[1][nt], a1x, q_pos(b1.x), q_pos(b1.y));
-            mma_16816(cn[1][nt], a1n, q_neg(b1.x), q_neg(b1.y));
+            uint2 bp0 = sq2[f0], bp1 = sq2[f1], bn0, bn1;
+            if constexpr (QSPLIT) {
+              bn0 = sq2[neg_off + f0], bn1 = sq2[neg_off + f1];
+            } else {
+              bn0 = make_uint2(q_neg(bp0.x), q_neg(bp0.y)), bn1 = make_uint2(q_neg(bp1.x), q_neg(bp1.y));
+              bp0 = make_uint2(q_pos(bp0.x), q_pos(bp0.y)), bp1 = make_uint2(q_pos(bp1.x), q_pos(bp1.y));
+            }
+            mma_16816(cp[0][nt], a0x, bp0.x, bp0.y);
+            mma_16816(cn[0][nt], a0n, bn0.x, bn0.y);
+            mma_16816(cp[1][nt], a1x, bp1.x, bp1.y);
+            mma_16816(cn[1][nt], a1n, bn1.x, bn1.y);
           }
         }
         // c0:(page g, head 2t) c1:(g, 2t+1) c2:(g+8, 2t) c3:(g+8, 2t+1)
@@ -817,35 +833,61 @@ int launch_quest_select_pack(const void* scores, int64_t score_stride, int n_col
   return check_launch("quest_select_pack");
 }
 
-template <int NT, bool FUSED>
-static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
-  p.hsplit = score_head_split(p.hkv);
-  if (const int t = tuning(kTuneScoreSplit); t > 0 && p.hkv % t == 0) p.hsplit = t;  // experiments
-  p.ppu = score_pages_per_unit(p.hkv, p.hsplit);
-  const int fixed = score_smem_layout(0, p.hq, p.hkv, p.hsplit, p.batch, FUSED).total + 256;  // + static smem
+struct ScorePlan {
+  int stages, consumers, producers;
+};
+
+// (stages, consumer warps, producer warps) for a ring next to `q_copies` staged copies of q; stages == 0:
+// no room.  producers | stages always; consumers | stages unless the fills are tagged per head split
+// (see the kernel).  Prefer more producers + consumers, then more stages.
+static ScorePlan score_plan(const ScoreParams& p, bool fused, int q_copies) {
+  const int fixed = score_smem_layout(0, p.hq, p.hkv, p.hsplit, p.batch, fused, q_copies).total + 256;  // + static smem
   const int stage_bytes = p.ppu * score_rec_stride(p.hkv / p.hsplit);
   int stages = (kScoreMaxSmem - fixed) / (stage_bytes + 20);
   if (stages > 24) stages = 24;
-  if (stages < 2) {
-    set_error("quest_page_score: %d q heads / %d kv heads / batch %d leave no shared memory for the bounds ring",
-              p.hq, p.hkv, p.batch);
-    return 1;
-  }
-  // (stages, consumer warps, producer warps) with consumers | stages and producers | stages:
-  // prefer more producers + consumers, then more stages
-  int best_s = stages, best_c = 1, best_p = 1;
+  if (stages < 2) return ScorePlan{0, 0, 0};
+  ScorePlan best{stages, 1, 1};
   for (int s2 = stages; s2 >= 2 && s2 >= stages - 3; --s2) {
     int c = 1, pr = 1;
     for (int d = kScoreConsumerWarps; d >= 1; --d)
       if (s2 % d == 0 || p.hsplit > 1) { c = d; break; }
     for (int d = kScoreProducerWarps; d >= 1; --d)
       if (s2 % d == 0) { pr = d; break; }
-    if (c + 2 * pr > best_c + 2 * best_p || s2 == stages) best_c = c, best_p = pr, best_s = s2;
+    if (c + 2 * pr > best.consumers + 2 * best.producers || s2 == stages) best = ScorePlan{s2, c, pr};
   }
-  stages = best_s;
+  return best;
+}
+
+template <int NT, bool FUSED, bool QSPLIT>
+static cudaError_t launch_score_kernel(const ScoreParams& p, int grid, size_t smem, cudaStream_t stream) {
+  auto kern = quest_page_score_kernel<NT, FUSED, QSPLIT>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  kern<<<grid, kScoreThreads, smem, stream>>>(p);
+  return cudaSuccess;
+}
+
+template <int NT, bool FUSED>
+static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
+  p.hsplit = score_head_split(p.hkv);
+  if (const int t = tuning(kTuneScoreSplit); t > 0 && p.hkv % t == 0) p.hsplit = t;  // experiments
+  p.ppu = score_pages_per_unit(p.hkv, p.hsplit);
+  const int stage_bytes = p.ppu * score_rec_stride(p.hkv / p.hsplit);
+  const ScorePlan one = score_plan(p, FUSED, 1), two = score_plan(p, FUSED, 2);
+  if (one.stages == 0) {
+    set_error("quest_page_score: %d q heads / %d kv heads / batch %d leave no shared memory for the bounds ring",
+              p.hq, p.hkv, p.batch);
+    return 1;
+  }
+  // q+ and q- are both staged only if that costs nothing of the ring
+  bool qsplit = two.stages == one.stages && two.producers == one.producers && two.consumers == one.consumers;
+  if (tuning(kTuneScoreQ) == 1) qsplit = false;
+  if (tuning(kTuneScoreQ) == 2 && two.stages > 0) qsplit = true;
+  const ScorePlan plan = qsplit ? two : one;
+  const int stages = plan.stages;
   p.stages = stages;
-  p.consumers = best_c;
-  p.producers = best_p;
+  p.consumers = plan.consumers;
+  p.producers = plan.producers;
   // Row groups (sched.cuh): by default every row is its own group, i.e. gridDim/batch CTAs start on
   // each row and q is staged once per CTA; fewer groups make rows end at staggered times.
   int groups = tuning(kTuneScoreGroups);
@@ -863,16 +905,15 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
     p.min_batch = tuning(kTuneMinBatch) > 0 ? tuning(kTuneMinBatch) : mb;
   }
   p.share_div = tuning(kTuneShareDiv) > 0 ? tuning(kTuneShareDiv) : 4;
-  const size_t smem = score_smem_layout(stages, p.hq, p.hkv, p.hsplit, p.batch, FUSED).total;
-  auto kern = quest_page_score_kernel<NT, FUSED>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return cuda_error("quest_page_score smem attr", e);
+  const size_t smem = score_smem_layout(stages, p.hq, p.hkv, p.hsplit, p.batch, FUSED, qsplit ? 2 : 1).total;
   const int64_t units_row = (p.n_cols + p.ppu - 1) / p.ppu;
   const int64_t max_chunks = (int64_t)p.batch * ((units_row + kChunkUnits - 1) / kChunkUnits);
   int grid = max_ctas();
   if ((int64_t)grid > max_chunks) grid = (int)max_chunks;
   if (grid < 1) grid = 1;
-  kern<<<grid, kScoreThreads, smem, stream>>>(p);
+  const cudaError_t e = qsplit ? launch_score_kernel<NT, FUSED, true>(p, grid, smem, stream)
+                               : launch_score_kernel<NT, FUSED, false>(p, grid, smem, stream);
+  if (e != cudaSuccess) return cuda_error("quest_page_score smem attr", e);
   return check_launch(FUSED ? "quest_score_select_pack" : "quest_page_score");
 }
 
