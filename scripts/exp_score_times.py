@@ -28,7 +28,7 @@ lib = _native.load()
 import os
 for cfg in (sys.argv[1] if len(sys.argv) > 1 else "0:0:0").split(","):
     groups, minb, sdiv = (int(x) for x in cfg.split(":"))
-    ops.set_tuning(0, groups); ops.set_tuning(2, minb); ops.set_tuning(3, sdiv); ops.set_tuning(5, int(os.environ.get('SPLIT', '0'))); ops.set_tuning(6, int(os.environ.get('QCOPY', '0')))
+    ops.set_tuning(0, groups); ops.set_tuning(2, minb); ops.set_tuning(3, sdiv); ops.set_tuning(5, int(os.environ.get('SPLIT', '0'))); ops.set_tuning(6, int(os.environ.get('QCOPY', '0'))); ops.set_tuning(7, int(os.environ.get('IDD', '0')))
     buf.zero_()
     for it in range(4):
         flush.zero_()
@@ -47,6 +47,15 @@ for cfg in (sys.argv[1] if len(sys.argv) > 1 else "0:0:0").split(","):
     for name, col in (("first data", 2), ("consumers done", 3), ("producer done", 4)):
         c = rel[:, col]
         print(f"  {name:15s} min {c.min():7.2f} med {c.median():7.2f} max {c.max():7.2f}")
+    if os.environ.get('CLAIMS'):
+        lc = (t[bsz:, 15] - t0).float() / 1000.0
+        dn = rel[bsz:, 3]
+        drain = dn - lc
+        order = dn.argsort()
+        print("  last successful claim us: min", round(float(lc.min()), 1), "med", round(float(lc.median()), 1), "max", round(float(lc.max()), 1),
+              "| done - last claim: min", round(float(drain.min()), 1), "med", round(float(drain.median()), 1), "max", round(float(drain.max()), 1))
+        for i in list(order[:4]) + list(order[-6:]):
+            print(f"    cta {int(i) + bsz:3d} sm {int(t[int(i) + bsz, 7]):3d} last claim {float(lc[i]):6.1f} done {float(dn[i]):6.1f} units {int(t[int(i) + bsz, 6])}")
     sel = t[:, 5].float() / 1000.0
     units = t[:, 6].float()
     w = t[:, 8:13].float().median(dim=0).values / 1000.0

@@ -486,7 +486,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   if (warp == kScoreConsumerWarps + kScoreProducerWarps) {
     // ============================================================== scheduler
     sched_run(sched, next_chunk, B, p.groups, p.min_batch, p.share_div, min(kSchedQueue, (S / hs + kChunkUnits - 1) / kChunkUnits + kIdDepth + 1),
-              units_of_row);
+              units_of_row, ReserveNone(), (dbg && blockIdx.x >= (unsigned)B) ? dbg + 15 : nullptr);
     return;
   }
 

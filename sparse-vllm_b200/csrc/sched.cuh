@@ -76,7 +76,7 @@ struct ReserveNone {
 template <class UnitsOfRow, class Reserve = ReserveNone>
 __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int rows, int groups,
                           int min_batch, int share_div, int depth, UnitsOfRow units_of_row,
-                          Reserve reserve = Reserve()) {
+                          Reserve reserve = Reserve(), unsigned long long* t_last_claim = nullptr) {
   const int lane = threadIdx.x & 31;
   int n = 0, ubase = 0, aux = 0;
   auto post = [&](int row, int begin, int cnt) {
@@ -109,6 +109,7 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
     if (lane == 0) j = atomicAdd(next_chunk + row, m);
     j = __shfl_sync(0xffffffffu, j, 0);
     while (j < d) {
+      if (t_last_claim && lane == 0) *t_last_claim = global_timer_ns();
       const int end = min(j + m, d);
       taken += end - j;
       const int left = (guided || taken < kStealVisit) ? d - end : 0;
