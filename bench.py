@@ -248,8 +248,9 @@ class DecodeStep:
                                        self.context_lens, self.req_indices)
 
     def layers(self):
-        """Device side: per layer store the new K/V row (bounds refresh fused), build the Quest view,
-        run decode attention; under TP all-gather the head shards."""
+        """Device side: per layer hand the new K/V row to the cache manager (stored, bounds refresh included,
+        by the layer's scoring launch), build the Quest view, run decode attention; under TP all-gather the
+        head shards."""
         from sparse_vllm_b200.attention_backend import decode_attention_layer
         from sparse_vllm_b200.cache_manager.base import SparseSelection
         torch, mgr = self.torch, self.mgr
@@ -261,7 +262,8 @@ class DecodeStep:
                                   max_context_len=st.max_context_len)
             decode_attention_layer(mgr, self.backend, layer, self.q[layer], sel, num_heads=self.hq,
                                    num_kv_heads=self.hkv, out=self.out[layer])
-            n += 2 if layer < self.skip else 3
+            # dense layer: store + attention; sparse layer: (store fused into) score/select/pack + attention
+            n += 2 if (layer < self.skip or getattr(mgr, "fuse_decode_store", False)) else 3
             if self.world > 1:
                 import torch.distributed as dist
                 dist.all_gather_into_tensor(self.gathered.view(self.world, -1),

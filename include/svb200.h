@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SVB200_ABI_VERSION 3
+#define SVB200_ABI_VERSION 4
 
 enum {
   SVB200_OK = 0,
@@ -179,6 +179,29 @@ int svb200_quest_select_pack(const void* scores, int64_t score_stride,
  */
 int svb200_quest_score_select_pack(
     const void* q, int64_t q_stride_b, const void* bounds_layer, int64_t num_pages,
+    const int32_t* page_table, int64_t page_table_stride, const int32_t* req_rows,
+    const int32_t* context_lens, void* scores, int64_t score_stride, int32_t batch,
+    int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols, int32_t prev_budget,
+    int32_t* packed_slots, int64_t out_stride, int32_t* sparse_lens,
+    int32_t* selected_pages, int32_t* tickets, void* stream);
+
+/*
+ * svb200_quest_score_select_pack that also performs the decode step's KV store
+ * (svb200_store_kv_minmax for batch tokens, token b = batch row b) inside the same
+ * launch: warps that wait for the first row to be scored write the rows.  Legal because
+ * a decode token always lands in its row's LAST page, which the launch never scores
+ * (columns [0, pages-1)), and the attention launch that reads the rows comes after.
+ * Replaces store_kvcache (kernels/triton/store_kvcache.py:10-71) + the decode part
+ * of on_forward_end (quest.py:1719-1771) + build_decode_view (quest.py:1805-1913) for
+ * one layer.
+ *   refresh_bounds  != 0: rebuild the bounds record of a page the token completes
+ *                   (requires num_slots == num_pages * 16); bounds_layer is written.
+ */
+int svb200_quest_store_score_select_pack(
+    const void* key, int64_t k_stride, const void* value, int64_t v_stride,
+    void* k_cache, void* v_cache, const int32_t* slot_mapping, int64_t num_slots,
+    int32_t refresh_bounds,
+    const void* q, int64_t q_stride_b, void* bounds_layer, int64_t num_pages,
     const int32_t* page_table, int64_t page_table_stride, const int32_t* req_rows,
     const int32_t* context_lens, void* scores, int64_t score_stride, int32_t batch,
     int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols, int32_t prev_budget,

@@ -14,7 +14,7 @@ from pathlib import Path
 import torch
 
 _LIB_PATH = Path(__file__).resolve().parent / "lib" / "libsvb200.so"
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 # name -> (restype, argtypes); mirrors include/svb200.h one to one.
 _P = c_void_p
@@ -38,6 +38,10 @@ _SIGNATURES = {
                   c_int64, c_int32, c_int32, c_int32, _P]),
     "svb200_quest_score_select_pack": (
         c_int32, [_P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32, c_int32, c_int32,
+                  c_int32, _P, c_int64, _P, _P, _P, _P]),
+    "svb200_quest_store_score_select_pack": (
+        c_int32, [_P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32,
+                  _P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32, c_int32, c_int32,
                   c_int32, _P, c_int64, _P, _P, _P, _P]),
     "svb200_sparse_decode_attn": (
         c_int32, [_P, c_int64, _P, _P, c_int64, _P, c_int64, c_int32, _P, _P, _P, c_int64, _P, c_int64,

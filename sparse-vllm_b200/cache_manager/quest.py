@@ -38,7 +38,8 @@ class QuestCacheManager(CacheManager):
 
     def __init__(self, config, *, num_layers: int, num_kv_heads: int, head_dim: int = 128, num_pages: int,
                  max_rows: int, max_model_len: int, device, dtype: torch.dtype = torch.bfloat16,
-                 decode_bounds_refresh: str = "fused", provider: B200SparseDecodeProvider | None = None) -> None:
+                 decode_bounds_refresh: str = "fused", provider: B200SparseDecodeProvider | None = None,
+                 fuse_decode_store: bool = True) -> None:
         self.config = config
         self.page_size = int(getattr(config, "quest_chunk_size", PAGE))
         if self.page_size != PAGE:
@@ -68,6 +69,9 @@ class QuestCacheManager(CacheManager):
         self._decode_static_max_context_len: int | None = None
         self._scratch: dict[int, SimpleNamespace] = {}
         self._provider = provider
+        # decode: the layer's new K/V rows wait here for the layer's scoring launch, which stores them itself
+        self.fuse_decode_store = bool(fuse_decode_store)
+        self._pending_store: tuple[int, ops.DecodeStore] | None = None
 
     # ------------------------------------------------------------------ provider / scratch
     def _get_provider(self, num_heads: int) -> B200SparseDecodeProvider:
@@ -206,6 +210,47 @@ class QuestCacheManager(CacheManager):
             st.max_context_len = max(st.max_context_len, self._decode_static_max_context_len)
         return input_ids, positions, None
 
+    # ------------------------------------------------------------------ KV store
+    def save_rope_kv_if_needed(self, layer_idx: int, k: torch.Tensor, v: torch.Tensor,
+                               slot_mapping: torch.Tensor | None = None) -> None:
+        """Decode step of a sparse layer with a long-text batch: the rows are handed to the layer's scoring
+        launch (``build_decode_view`` follows in the same layer; a decode token lands in its row's last page,
+        which that launch never scores) instead of a launch of their own.  Anything that looks at the cache
+        before (``get_layer_kv_cache``, the next store, ``on_forward_end``) stores them first."""
+        self.flush_pending_store()
+        if slot_mapping is None:
+            slot_mapping = self.layer_batch_state.slot_mapping
+        ctx = get_context()
+        if (self.fuse_decode_store and not ctx.is_prefill and bool(ctx.is_long_text)
+                and layer_idx >= int(self.config.quest_skip_layers) and int(self.config.quest_token_budget) > 0
+                and slot_mapping is not None and int(k.shape[0]) == int(slot_mapping.numel())):
+            k_cache, v_cache = CacheManager.get_layer_kv_cache(self, layer_idx)
+            self._pending_store = (layer_idx, ops.DecodeStore(k, v, k_cache, v_cache, slot_mapping,
+                                                              self.decode_bounds_refresh == "fused"))
+            return
+        super().save_rope_kv_if_needed(layer_idx, k, v, slot_mapping)
+
+    def flush_pending_store(self) -> None:
+        pend, self._pending_store = self._pending_store, None
+        if pend is not None:
+            layer_idx, st = pend
+            ops.store_kv_minmax(st.key, st.value, st.k_cache, st.v_cache, st.slot_mapping,
+                                self.bounds[self.kv_layer_index(layer_idx)] if st.refresh_bounds else None)
+
+    def _take_pending_store(self, layer_idx: int) -> ops.DecodeStore | None:
+        if self._pending_store is None:
+            return None
+        if self._pending_store[0] != layer_idx:
+            self.flush_pending_store()
+            return None
+        st = self._pending_store[1]
+        self._pending_store = None
+        return st
+
+    def get_layer_kv_cache(self, layer_idx: int) -> tuple[torch.Tensor, torch.Tensor]:
+        self.flush_pending_store()
+        return super().get_layer_kv_cache(layer_idx)
+
     # ------------------------------------------------------------------ bounds maintenance
     def _fused_store_bounds(self, layer_idx: int):
         if get_context().is_prefill or self.decode_bounds_refresh != "fused":
@@ -222,6 +267,7 @@ class QuestCacheManager(CacheManager):
 
     def on_forward_end(self, seqs, is_prefill: bool) -> None:
         """quest.py:1719-1771: after a decode step, rebuild the bounds of pages it completed (all layers)."""
+        self.flush_pending_store()
         if is_prefill or self.decode_bounds_refresh != "forward_end":
             return
         st = self.layer_batch_state
@@ -271,5 +317,6 @@ class QuestCacheManager(CacheManager):
             num_kv_heads=self.num_kv_heads, prev_budget=prev_budget, scores=s.scores, packed_slots=s.packed,
             sparse_lens=s.lens, tickets=s.tickets,
             dense_token_table=None if long_text else self.buffer_req_to_token_slots,
-            token_budget=int(token_budget), page_budget_base=page_budget_base, out_width=width)
+            token_budget=int(token_budget), page_budget_base=page_budget_base, out_width=width,
+            store=self._take_pending_store(layer_idx))
         return s.packed[:, :width], s.arange, s.lens

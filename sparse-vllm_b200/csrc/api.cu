@@ -230,7 +230,43 @@ int svb200_quest_score_select_pack(const void* q, int64_t q_stride_b, const void
                                         req_rows, context_lens, scores, score_stride, batch,
                                         num_q_heads, num_kv_heads, n_cols, prev_budget,
                                         packed_slots, out_stride, sparse_lens, selected_pages,
-                                        tickets, (cudaStream_t)stream);
+                                        tickets, nullptr, (cudaStream_t)stream);
+}
+
+int svb200_quest_store_score_select_pack(const void* key, int64_t k_stride, const void* value, int64_t v_stride,
+                                         void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                                         int64_t num_slots, int32_t refresh_bounds,
+                                         const void* q, int64_t q_stride_b, void* bounds_layer,
+                                         int64_t num_pages, const int32_t* page_table, int64_t page_table_stride,
+                                         const int32_t* req_rows, const int32_t* context_lens,
+                                         void* scores, int64_t score_stride, int32_t batch,
+                                         int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols,
+                                         int32_t prev_budget, int32_t* packed_slots, int64_t out_stride,
+                                         int32_t* sparse_lens, int32_t* selected_pages, int32_t* tickets,
+                                         void* stream) {
+  const char* who = "quest_store_score_select_pack";
+  SV_REQUIRE(batch >= 0, "%s: batch=%d < 0", who, batch);
+  if (batch == 0) return 0;
+  if (int rc = check_score_args(who, q, q_stride_b, bounds_layer, num_pages, page_table,
+                                page_table_stride, req_rows, context_lens, scores, score_stride,
+                                batch, num_q_heads, num_kv_heads, n_cols))
+    return rc;
+  if (int rc = check_select_args(who, n_cols, prev_budget, packed_slots, out_stride, sparse_lens)) return rc;
+  SV_REQUIRE(tickets != nullptr, "%s: tickets scratch is null", who);
+  SV_REQUIRE(key && value && k_cache && v_cache && slot_mapping, "%s: null store pointer", who);
+  SV_REQUIRE(aligned16(key) && aligned16(value) && aligned16(k_cache) && aligned16(v_cache),
+             "%s: key/value/caches must be 16-byte aligned", who);
+  SV_REQUIRE(k_stride >= (int64_t)num_kv_heads * SVB200_HEAD_DIM && k_stride % 8 == 0 &&
+                 v_stride >= (int64_t)num_kv_heads * SVB200_HEAD_DIM && v_stride % 8 == 0,
+             "%s: bad key/value token strides %lld/%lld", who, (long long)k_stride, (long long)v_stride);
+  SV_REQUIRE(num_slots > 0 && (!refresh_bounds || num_slots == num_pages * SVB200_PAGE),
+             "%s: num_slots=%lld must be positive (and num_pages*%d with refresh_bounds)", who, (long long)num_slots, SVB200_PAGE);
+  const FusedStore st{key, k_stride, value, v_stride, k_cache, v_cache, slot_mapping, num_slots, refresh_bounds};
+  return launch_quest_score_select_pack(q, q_stride_b, bounds_layer, num_pages, page_table, page_table_stride,
+                                        req_rows, context_lens, scores, score_stride, batch,
+                                        num_q_heads, num_kv_heads, n_cols, prev_budget,
+                                        packed_slots, out_stride, sparse_lens, selected_pages,
+                                        tickets, &st, (cudaStream_t)stream);
 }
 
 int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_cache,

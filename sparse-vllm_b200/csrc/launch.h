@@ -35,13 +35,26 @@ int launch_quest_select_pack(const void* scores, int64_t score_stride, int n_col
                              int64_t out_stride, int32_t* sparse_lens, int32_t* selected_pages,
                              const int32_t* dense_table, int64_t dense_stride, int token_budget,
                              int page_budget_base, int out_width, cudaStream_t stream);
+// New K/V rows of the step (one token per batch row) stored by the scoring launch itself.
+struct FusedStore {
+  const void* key;
+  int64_t k_stride;
+  const void* value;
+  int64_t v_stride;
+  void* k_cache;
+  void* v_cache;
+  const int32_t* slot_mapping;
+  int64_t num_slots;
+  int refresh_bounds;  // rebuild the bounds record of a page the token completes
+};
+
 int launch_quest_score_select_pack(const void* q, int64_t q_stride_b, const void* bounds,
                                    int64_t num_pages, const int32_t* page_table, int64_t pt_stride,
                                    const int32_t* req_rows, const int32_t* context_lens,
                                    void* scores, int64_t score_stride, int batch, int hq, int hkv,
                                    int n_cols, int k, int32_t* packed_slots, int64_t out_stride,
                                    int32_t* sparse_lens, int32_t* selected_pages, int32_t* tickets,
-                                   cudaStream_t stream);
+                                   const FusedStore* store, cudaStream_t stream);
 
 // decode_attn.cu
 struct AttnParams {

@@ -8,6 +8,7 @@
 #include "common.cuh"
 #include "launch.h"
 #include "sched.cuh"
+#include "store_kv.cuh"
 
 namespace svb200 {
 
@@ -380,6 +381,9 @@ struct ScoreParams {
   int64_t out_stride;
   int32_t* sparse_lens;
   int32_t* selected_pages;
+  // fused store of the step's new K/V rows (store.key == null: none), one token per batch row
+  StoreArgs store;
+  int store_tokens;
 };
 
 struct ScoreSmemLayout {
@@ -601,6 +605,12 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
     if constexpr (FUSED_SELECT) {
       SelectSmem* sel_sm = reinterpret_cast<SelectSmem*>(smem + L.select_off);
       const int stid = tid - (kScoreThreads - kScoreSelectThreads);
+      // The step's new K/V rows (and the bounds of a page they complete) are written here, by warps
+      // that have nothing else to do until the first row is scored.  The token's page is the row's
+      // last one, which this launch never scores (n_valid = pages - 1); attention runs after the launch.
+      if (p.store.key != nullptr)
+        for (int tok = blockIdx.x; tok < p.store_tokens; tok += gridDim.x)
+          store_kv_token(p.store, tok, hkv, stid, kScoreSelectThreads);
       for (int b = blockIdx.x; b < B; b += gridDim.x) {
         const int need = units_of_row(b);
         if (need > 0 && stid == 0) {
@@ -950,12 +960,19 @@ int launch_quest_score_select_pack(const void* q, int64_t q_stride_b, const void
                                    void* scores, int64_t score_stride, int batch, int hq, int hkv,
                                    int n_cols, int k, int32_t* packed_slots, int64_t out_stride,
                                    int32_t* sparse_lens, int32_t* selected_pages, int32_t* tickets,
-                                   cudaStream_t stream) {
+                                   const FusedStore* store, cudaStream_t stream) {
   if (batch <= 0 || n_cols <= 0) return 0;
   ScoreParams p = make_score_params(q, q_stride_b, bounds, num_pages, page_table, pt_stride, req_rows,
                                     context_lens, scores, score_stride, batch, hq, hkv, n_cols);
   p.k = k; p.packed_slots = packed_slots; p.out_stride = out_stride; p.sparse_lens = sparse_lens;
   p.selected_pages = selected_pages; p.sched = tickets;
+  if (store != nullptr) {
+    p.store = StoreArgs{(const __nv_bfloat16*)store->key, store->k_stride, (const __nv_bfloat16*)store->value,
+                        store->v_stride, (__nv_bfloat16*)store->k_cache, (__nv_bfloat16*)store->v_cache,
+                        store->slot_mapping, store->num_slots,
+                        store->refresh_bounds ? (__nv_bfloat16*)const_cast<void*>(bounds) : nullptr};
+    p.store_tokens = batch;
+  }
   return hq / hkv <= 8 ? launch_score_variant<1, true>(p, stream)
                        : launch_score_variant<2, true>(p, stream);
 }

@@ -95,12 +95,20 @@ class B200SparseDecodeProvider:
 
     def quest_select(self, q, bounds_layer, page_table, req_rows, context_lens, *, n_cols, num_kv_heads,
                      prev_budget, scores, packed_slots, sparse_lens, tickets, selected_pages=None,
-                     dense_token_table=None, token_budget=0, page_budget_base=0, out_width=0) -> None:
+                     dense_token_table=None, token_budget=0, page_budget_base=0, out_width=0,
+                     store: ops.DecodeStore | None = None) -> None:
+        """``store``: the step's new K/V rows, not yet in the cache.  The long-text launch writes them itself;
+        the two-launch (mixed) path stores them first with the stand-alone kernel."""
         if dense_token_table is None:
             ops.quest_score_select_pack(q, bounds_layer, page_table, req_rows, context_lens, n_cols, num_kv_heads,
-                                        prev_budget, scores, packed_slots, sparse_lens, tickets, selected_pages)
-            self._count("quest_score_select_pack_fused")
+                                        prev_budget, scores, packed_slots, sparse_lens, tickets, selected_pages,
+                                        store=store)
+            self._count("quest_store_score_select_pack_fused" if store is not None else "quest_score_select_pack_fused")
         else:
+            if store is not None:
+                ops.store_kv_minmax(store.key, store.value, store.k_cache, store.v_cache, store.slot_mapping,
+                                    bounds_layer if store.refresh_bounds else None)
+                self._count("store_kv_minmax")
             ops.quest_page_score(q, bounds_layer, page_table, req_rows, context_lens, n_cols, num_kv_heads, scores,
                                  sched=tickets)
             ops.quest_select_pack(scores, n_cols, page_table, req_rows, context_lens, prev_budget, packed_slots,

@@ -150,12 +150,23 @@ def quest_select_pack(scores: torch.Tensor, n_cols: int, page_table: torch.Tenso
         current_stream_ptr(scores.device)), "svb200_quest_select_pack")
 
 
+class DecodeStore:
+    """New K/V rows of a decode step (token b = batch row b) for the scoring launch to store itself."""
+
+    __slots__ = ("key", "value", "k_cache", "v_cache", "slot_mapping", "refresh_bounds")
+
+    def __init__(self, key, value, k_cache, v_cache, slot_mapping, refresh_bounds: bool):
+        self.key, self.value, self.k_cache, self.v_cache = key, value, k_cache, v_cache
+        self.slot_mapping, self.refresh_bounds = slot_mapping, bool(refresh_bounds)
+
+
 def quest_score_select_pack(q: torch.Tensor, bounds_layer: torch.Tensor, page_table: torch.Tensor,
                             req_rows: torch.Tensor, context_lens: torch.Tensor, n_cols: int, num_kv_heads: int,
                             prev_budget: int, scores: torch.Tensor, packed_slots: torch.Tensor,
                             sparse_lens: torch.Tensor, tickets: torch.Tensor,
-                            selected_pages: torch.Tensor | None = None) -> None:
-    """One-launch score + select + pack for long-text batches (svb200_quest_score_select_pack)."""
+                            selected_pages: torch.Tensor | None = None, store: DecodeStore | None = None) -> None:
+    """One-launch score + select + pack for long-text batches (svb200_quest_score_select_pack); with
+    ``store`` the launch also writes the step's K/V rows (svb200_quest_store_score_select_pack)."""
     bsz, hq, qs = _q(q, "q")
     _bounds_layer(bounds_layer, num_kv_heads)
     require_cuda(scores, "scores", torch.bfloat16)
@@ -167,13 +178,30 @@ def quest_score_select_pack(q: torch.Tensor, bounds_layer: torch.Tensor, page_ta
     if selected_pages is not None:
         _i32(selected_pages, "selected_pages")
     lib = _native.load()
-    check(lib.svb200_quest_score_select_pack(
-        ptr(q), qs, ptr(bounds_layer), int(bounds_layer.shape[0]), ptr(page_table),
-        _rows_stride(page_table, "page_table"),
-        ptr(req_rows), ptr(context_lens), ptr(scores), _rows_stride(scores, "scores"), bsz, hq,
-        int(num_kv_heads), int(n_cols), int(prev_budget), ptr(packed_slots),
-        _rows_stride(packed_slots, "packed_slots"), ptr(sparse_lens), ptr(selected_pages), ptr(tickets),
-        current_stream_ptr(q.device)), "svb200_quest_score_select_pack")
+    score_args = (ptr(q), qs, ptr(bounds_layer), int(bounds_layer.shape[0]), ptr(page_table),
+                  _rows_stride(page_table, "page_table"),
+                  ptr(req_rows), ptr(context_lens), ptr(scores), _rows_stride(scores, "scores"), bsz, hq,
+                  int(num_kv_heads), int(n_cols), int(prev_budget), ptr(packed_slots),
+                  _rows_stride(packed_slots, "packed_slots"), ptr(sparse_lens), ptr(selected_pages), ptr(tickets),
+                  current_stream_ptr(q.device))
+    if store is None:
+        check(lib.svb200_quest_score_select_pack(*score_args), "svb200_quest_score_select_pack")
+        return
+    num_slots, hkv = _kv_layer(store.k_cache, "k_cache")
+    _kv_layer(store.v_cache, "v_cache")
+    if hkv != int(num_kv_heads):
+        raise ValueError(f"store caches hold {hkv} KV heads, scoring uses {num_kv_heads}.")
+    for t, n in ((store.key, "key"), (store.value, "value")):
+        require_cuda(t, n, torch.bfloat16)
+        if t.dim() != 3 or tuple(t.shape) != (bsz, hkv, HEAD_DIM) or t.stride(2) != 1 or t.stride(1) != HEAD_DIM:
+            raise ValueError(f"{n} must be [{bsz}, {hkv}, {HEAD_DIM}] with contiguous heads, got {tuple(t.shape)}/{t.stride()}.")
+    _i32(store.slot_mapping, "slot_mapping")
+    if int(store.slot_mapping.numel()) != bsz:
+        raise ValueError(f"slot_mapping must hold one slot per batch row ({bsz}), got {store.slot_mapping.numel()}.")
+    check(lib.svb200_quest_store_score_select_pack(
+        ptr(store.key), int(store.key.stride(0)), ptr(store.value), int(store.value.stride(0)), ptr(store.k_cache),
+        ptr(store.v_cache), ptr(store.slot_mapping), num_slots, int(store.refresh_bounds), *score_args),
+        "svb200_quest_store_score_select_pack")
 
 
 def sched_scratch_ints(rows: int) -> int:

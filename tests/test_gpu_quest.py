@@ -313,3 +313,64 @@ def _check_fused_properties(bsz, hq, hkv, ctx, budget):
         ref = (sp + sn).amax(dim=1).amax(dim=0)
         d = oquest.bf16_ulp_distance(scores[b, :nv].cpu(), ref.cpu())
         assert int(d.max()) <= 1 and float((d == 1).float().mean()) < 0.02
+
+
+@pytest.mark.parametrize("max_ctas", [0, 2])
+@pytest.mark.parametrize("bsz,hq,hkv,ctx,budget", [(5, 28, 4, 16384, 512), (3, 64, 8, 8192, 256), (4, 8, 1, 8192, 256)])
+def test_store_fused_into_scoring_launch(bsz, hq, hkv, ctx, budget, max_ctas):
+    """svb200_quest_store_score_select_pack == svb200_store_kv_minmax followed by
+    svb200_quest_score_select_pack, bit for bit: K/V rows, the bounds of a page a token completes,
+    scores, selection, packed slots.  Rows end at every offset of their last page (one completes it),
+    one token carries slot -1 (skipped)."""
+    from sparse_vllm_b200 import configs, ops
+    gen = torch.Generator(device=DEV).manual_seed(77)
+    max_pages = ctx // PAGE
+    n_cols = max_pages - 1
+    _, prev = configs.quest_page_budget(budget, PAGE, max_pages)
+    num_pages = bsz * max_pages
+    num_slots = num_pages * PAGE
+    k_cache = torch.randn(num_slots, hkv, 128, device=DEV, generator=gen).to(torch.bfloat16)
+    v_cache = torch.randn(num_slots, hkv, 128, device=DEV, generator=gen).to(torch.bfloat16)
+    bounds = torch.zeros(num_pages, 2, hkv, 128, device=DEV, dtype=torch.bfloat16)
+    ops.quest_page_minmax(k_cache, bounds, torch.arange(num_slots, dtype=torch.int32, device=DEV))
+    pt = torch.randperm(num_pages, device=DEV, generator=gen).to(torch.int32).view(bsz, max_pages)
+    q = torch.randn(bsz, hq, 128, device=DEV, generator=gen).to(torch.bfloat16)
+    # row b holds ctx - 16*b - b tokens after this step; row 0 completes its last page
+    ctx_lens = torch.tensor([ctx - 17 * b for b in range(bsz)], dtype=torch.int32, device=DEV)
+    last = (ctx_lens - 1)
+    slots = (pt[torch.arange(bsz, device=DEV), (last // PAGE).long()] * PAGE + last % PAGE).to(torch.int32)
+    slots[bsz - 1] = -1
+    k_new = torch.randn(bsz, hkv, 128, device=DEV, generator=gen).to(torch.bfloat16) * 3
+    v_new = torch.randn(bsz, hkv, 128, device=DEV, generator=gen).to(torch.bfloat16)
+    req = torch.arange(bsz, dtype=torch.int32, device=DEV)
+
+    def run(fused: bool):
+        kc, vc, bd = k_cache.clone(), v_cache.clone(), bounds.clone()
+        scores = torch.empty(bsz, ops.score_row_stride(n_cols), dtype=torch.bfloat16, device=DEV)
+        packed = torch.zeros(bsz, (prev + 1) * PAGE, dtype=torch.int32, device=DEV)
+        lens = torch.zeros(bsz, dtype=torch.int32, device=DEV)
+        sel = torch.zeros(bsz, prev + 1, dtype=torch.int32, device=DEV)
+        tickets = ops.sched_scratch(bsz, DEV)
+        store = None
+        if fused:
+            store = ops.DecodeStore(k_new, v_new, kc, vc, slots, True)
+        else:
+            ops.store_kv_minmax(k_new, v_new, kc, vc, slots, bd)
+        for _ in range(2):  # the launch is idempotent and leaves its scratch ready for the next one
+            ops.quest_score_select_pack(q, bd, pt, req, ctx_lens, n_cols, hkv, prev, scores, packed, lens, tickets,
+                                        sel, store=store)
+        torch.cuda.synchronize()
+        assert int(tickets.abs().sum()) == 0
+        return kc, vc, bd, scores[:, :n_cols].view(torch.int16), packed, lens, sel
+
+    prev_cap = ops.set_max_ctas(max_ctas)
+    try:
+        ref, got = run(False), run(True)
+    finally:
+        ops.set_max_ctas(prev_cap)
+    for name, a, b in zip(("k_cache", "v_cache", "bounds", "scores", "packed", "lens", "selected"), ref, got):
+        assert torch.equal(a.view(torch.int16) if a.dtype == torch.bfloat16 else a,
+                           b.view(torch.int16) if b.dtype == torch.bfloat16 else b), name
+    # the store really happened: row 0's token is in the cache and its page's bounds changed
+    assert torch.equal(got[0][int(slots[0])], k_new[0]) and torch.equal(got[1][int(slots[0])], v_new[0])
+    assert int(slots[0]) % PAGE == PAGE - 1 and not torch.equal(got[2][int(slots[0]) // PAGE], bounds[int(slots[0]) // PAGE])
