@@ -48,9 +48,11 @@ int svb200_sm_count(void);
  */
 int svb200_set_max_ctas(int32_t n);
 /*
- * Experiment knob `which` (0 = row groups of the score scheduler, 1 = row groups of the attention
- * scheduler) := value; 0 restores the automatic choice.  Returns the previous value, -1 for an
- * unknown knob.  Results never depend on it.
+ * Experiment knob `which` := value; 0 restores the automatic choice.  Returns the previous value,
+ * -1 for an unknown knob.  Results never depend on it.  Score kernel: 0 = row groups of the
+ * scheduler, 2 = chunks per claim at least, 3 = divisor of the guided claim size, 4 = 1: 16-byte
+ * LDGSTS copies instead of bulk copies, 5 = ring stages per 16-page unit (1, 2, 4), 6 = 1: stage q
+ * once / 2: stage q+ and q-.  1 = reserved (attention scheduler).
  */
 int svb200_set_tuning(int32_t which, int32_t value);
 /*

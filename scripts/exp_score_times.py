@@ -28,7 +28,7 @@ lib = _native.load()
 import os
 for cfg in (sys.argv[1] if len(sys.argv) > 1 else "0:0:0").split(","):
     groups, minb, sdiv = (int(x) for x in cfg.split(":"))
-    ops.set_tuning(0, groups); ops.set_tuning(2, minb); ops.set_tuning(3, sdiv); ops.set_tuning(5, int(os.environ.get('SPLIT', '0'))); ops.set_tuning(6, int(os.environ.get('QCOPY', '0'))); ops.set_tuning(7, int(os.environ.get('IDD', '0')))
+    ops.set_tuning(0, groups); ops.set_tuning(2, minb); ops.set_tuning(3, sdiv); ops.set_tuning(5, int(os.environ.get('SPLIT', '0'))); ops.set_tuning(6, int(os.environ.get('QCOPY', '0')))
     buf.zero_()
     for it in range(4):
         flush.zero_()
