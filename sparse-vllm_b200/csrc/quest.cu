@@ -464,6 +464,9 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       // LDGSTS: 32 async copy arrivals + the producer's release; bulk: the expect_tx arrival
       mbar_init(&full_bar[s], p.bulk ? 1 : 33);
       mbar_init(&empty_bar[s], 1);
+      // no fill yet: a consumer whose first unit is a later round of the stage passes the fresh barrier's
+      // parity test and must not find a tag a previous launch left in shared memory (rounds stay < 0xffff)
+      sValid[s] = 0xffffffffu;
     }
     sched_init(sched, p.producers + kScoreConsumerWarps);
     s_flag = 0;

@@ -265,6 +265,14 @@ def test_full_size_properties(bsz, hq, hkv, ctx, budget):
     _check_fused_properties(bsz, hq, hkv, ctx, budget)
 
 
+@pytest.mark.parametrize("bsz,hq,hkv", [(2, 32, 8), (3, 64, 8), (1, 32, 8), (2, 16, 2)])
+def test_few_units_per_cta_back_to_back(bsz, hq, hkv):
+    """Every CTA gets a handful of units, so a consumer warp's FIRST unit is a later fill of its ring
+    stage, and launches follow each other on shared memory the previous one left behind (stage tags)."""
+    for _ in range(4):
+        _check_fused_properties(bsz, hq, hkv, 32768, 2048)
+
+
 def _check_fused_properties(bsz, hq, hkv, ctx, budget):
     """BASELINE sizes (cfg 3 at a reduced batch, cfg 2): size-independent properties of the fused launch.
     -inf beyond the valid pages, exact top-k w.r.t. its own scores, packing = page table lookup, and the
