@@ -792,7 +792,7 @@ def main():
         h2o = args.workload == "cfg4"
         line = run_h2o(args) if h2o else run_b200(args)
         if line and args.gpus == 1 and args.workload == "auto":
-            line["other_workloads"] = {"cfg3": secondary_workload("cfg3", args), "cfg4": secondary_workload("cfg4", args)}
+            line["other_workloads"] = {k: secondary_workload(k, args) for k in ("cfg2", "cfg3", "cfg4")}
         if line and not args.no_cpu_baseline and args.gpus == 1 and not h2o:
             line["cpu_baseline"] = cpu_baseline(pick_workload(args), args.cpu_seconds)
     if line and not line.pop("_printed", False):

@@ -52,7 +52,8 @@ int svb200_set_max_ctas(int32_t n);
  * -1 for an unknown knob.  Results never depend on it.  Score kernel: 0 = row groups of the
  * scheduler, 2 = chunks per claim at least, 3 = divisor of the guided claim size, 4 = 1: 16-byte
  * LDGSTS copies instead of bulk copies, 5 = ring stages per 16-page unit (1, 2, 4), 6 = 1: stage q
- * once / 2: stage q+ and q-.  1 = reserved (attention scheduler).
+ * once / 2: stage q+ and q-.  Attention kernel: 1 = KB of K/V a CTA should stream at least
+ * (grid sizing of small launches; default 256).
  */
 int svb200_set_tuning(int32_t which, int32_t value);
 /*

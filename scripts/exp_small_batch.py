@@ -62,3 +62,8 @@ for cap in [int(x) for x in (sys.argv[1] if len(sys.argv) > 1 else "0,16,32,64,9
     if which in ('both', 'attn'):
         print(f"cap {cap:4d}: attention    {timed(attn):6.1f} us", flush=True)
 ops.set_max_ctas(0)
+if os.environ.get('MINKB'):
+    for kb in [int(x) for x in os.environ['MINKB'].split(',')]:
+        ops.set_tuning(1, kb)
+        print(f"min KB per CTA {kb:4d}: attention {timed(attn):6.1f} us", flush=True)
+    ops.set_tuning(1, 0)

@@ -611,6 +611,16 @@ static int launch_variant(const AttnParams& p_in, cudaStream_t stream) {
   int grid = max_ctas();
   if (grid > p.max_ctas) grid = p.max_ctas;
   if ((int64_t)grid > max_units) grid = (int)max_units;
+  // Small launches (one short row: cfg2) are latency-bound: every CTA pays the same start-up and the
+  // last contributor of a row merges one partial per CTA, so a CTA should stream >= ~256 KB of K/V
+  // (bs 1, 2064 tokens, 8 KV heads: 148 CTAs 36 us, 32 CTAs 17 us).  max_len bounds the work from above.
+  {
+    int kb = tuning(kTuneAttnMinKB) > 0 ? tuning(kTuneAttnMinKB) : 256;
+    const int64_t unit_kb = (int64_t)HPC * 2 * kPage * kHeadDim * 2 / 1024;  // K + V rows of HPC heads, 16 tokens
+    const int64_t min_units = (kb + unit_kb - 1) / unit_kb;
+    const int64_t want = (max_units + min_units - 1) / min_units;
+    if ((int64_t)grid > want) grid = (int)want;
+  }
   if (grid < 1) grid = 1;
   kern<<<grid, kAttnThreads, smem, stream>>>(p);
   return check_launch("sparse_decode_attn");

@@ -14,7 +14,7 @@ int sm_count();
 unsigned long long* debug_times_buffer();
 int max_ctas();  // persistent-grid size: sm_count() unless svb200_set_max_ctas lowered it
 // experiment knobs (svb200_set_tuning); 0 = automatic
-enum { kTuneScoreGroups = 0, kTuneAttnGroups = 1, kTuneMinBatch = 2, kTuneShareDiv = 3, kTuneScoreCopy = 4, kTuneScoreSplit = 5, kTuneScoreQ = 6, kTuneCount = 8 };
+enum { kTuneScoreGroups = 0, kTuneAttnMinKB = 1, kTuneMinBatch = 2, kTuneShareDiv = 3, kTuneScoreCopy = 4, kTuneScoreSplit = 5, kTuneScoreQ = 6, kTuneCount = 8 };
 int tuning(int which);
 
 // quest.cu
