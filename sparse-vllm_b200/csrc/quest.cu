@@ -465,7 +465,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       mbar_init(&full_bar[s], p.bulk ? 1 : 33);
       mbar_init(&empty_bar[s], 1);
       // no fill yet: a consumer whose first unit is a later round of the stage passes the fresh barrier's
-      // parity test and must not find a tag a previous launch left in shared memory (rounds stay < 0xffff)
+      // parity test and must not find a tag a previous launch left in shared memory (tags are 15 bits)
       sValid[s] = 0xffffffffu;
     }
     sched_init(sched, p.producers + kScoreConsumerWarps);
@@ -556,7 +556,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
           const int s = ii % S;
           const uint32_t round = (uint32_t)(ii / S), ph = round & 1u;
           // valid pages of the unit | the stage's fill count (the consumer checks it: see there)
-          const uint32_t umask = (ball >> (j * ppu)) & unit_mask, tagged = umask | (round << 16);
+          const uint32_t umask = (ball >> (j * ppu)) & unit_mask, tagged = umask | ((round & 0x7fffu) << 16);
           const unsigned long long te = dbg ? global_timer_ns() : 0;
           mbar_wait(&empty_bar[s], ph ^ 1u);
           if (dbg) w_empty += global_timer_ns() - te;
@@ -712,7 +712,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       while (true) {
         mbar_wait(&full_bar[s], round & 1u);
         mask = (uint32_t)ld_volatile_shared(reinterpret_cast<const int*>(sValid + s));
-        if ((mask >> 16) == (round & 0xffffu)) {
+        if ((mask >> 16) == (round & 0x7fffu)) {
           mbar_wait(&full_bar[s], round & 1u);  // the tag is written before the copies land: wait for them
           break;
         }
