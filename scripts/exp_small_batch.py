@@ -27,6 +27,7 @@ tickets = ops.sched_scratch(bsz, dev)
 out = torch.empty_like(q)
 ws = ops.attn_workspace(bsz, hq, hkv, dev)
 hpc = int(os.environ.get('HPC', 4))
+ops.set_tuning(4, int(os.environ.get('COPY', '0')))  # 1: LDGSTS instead of bulk copies in the score kernel
 
 
 def timed(fn, reps=5):
