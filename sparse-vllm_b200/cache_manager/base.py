@@ -65,12 +65,16 @@ class CacheManager:
 
     sparse_method = ""
 
+    # Tests of the host-side bookkeeping set this to build a manager on CPU tensors with the launches
+    # replaced by recorders; every op still refuses non-CUDA tensors (ops.require_cuda).
+    _allow_host_tensors = False
+
     def __init__(self, *, num_layers: int, num_kv_heads: int, head_dim: int, num_slots: int,
                  device: torch.device | str, dtype: torch.dtype = torch.bfloat16) -> None:
         if head_dim != ops.HEAD_DIM or dtype != torch.bfloat16:
             raise ValueError(f"the B200 provider serves bf16 KV with head_dim={ops.HEAD_DIM} only.")
         self.device = torch.device(device)
-        if self.device.type != "cuda":
+        if self.device.type != "cuda" and not self._allow_host_tensors:
             raise RuntimeError("the B200 provider has no CPU path: cache managers live on a CUDA device.")
         self.num_layers = int(num_layers)
         self.num_kv_heads = int(num_kv_heads)
