@@ -1,3 +1,5 @@
+"""Repro / experiment: back-to-back fused score launches (eager, per-launch sync, or graph replays) at small
+batches (SHAPE=bsz,hq,hkv CTX= BUDGET=); found the stale ring-stage tag bug (tests: test_few_units_per_cta_back_to_back)."""
 import os, sys
 import torch
 sys.path.insert(0, ".")
@@ -6,7 +8,7 @@ from sparse_vllm_b200 import ops, configs
 dev = "cuda:0"
 mode = sys.argv[1]
 bsz, hq, hkv = (int(x) for x in os.environ.get('SHAPE', '1,32,8').split(','))
-ctx, budget = 32768, 2048
+ctx, budget = int(os.environ.get('CTX', 32768)), int(os.environ.get('BUDGET', 2048))
 gen = torch.Generator(device=dev).manual_seed(1)
 max_pages = ctx // 16
 n_cols = max_pages - 1
