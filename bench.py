@@ -28,6 +28,7 @@ if str(ROOT) not in sys.path:
 
 PAGE = 16
 HEAD_DIM = 128
+NOMINAL_GBS = 8000.0  # north_star: "B200's ~8 TB/s"
 METRIC = "sparse_decode_attn_tokens_per_s_128k"
 UNIT = "tok/s"
 
@@ -56,6 +57,11 @@ def parse_args():
     ap.add_argument("--phys-layers", type=int, default=0, help="distinct KV/bounds pools cycled by the layers (0 = auto)")
     ap.add_argument("--skip-layers", type=int, default=0, help="quest_skip_layers (dense layers at the bottom)")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph replay")
+    ap.add_argument("--collective", default="push", choices=["push", "nccl"],
+                    help="N>1: gather of the attention head shards: 'push' = peer stores in the attention epilogue "
+                         "(svb200_sparse_decode_attn_tp), 'nccl' = all_gather_into_tensor after every layer")
+    ap.add_argument("--pdl", type=int, default=-1, help="programmatic dependent launch: 1 on, 0 off, -1 library default")
+    ap.add_argument("--tune", default="", help="experiment knobs 'which=value,...' (svb200_set_tuning)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--verbose", action="store_true", help="phase timestamps on stderr")
@@ -188,6 +194,8 @@ def build_state(w: dict, rank: int, world: int, phys_layers: int, skip_layers: i
     # physical pages in a seeded random order (non-contiguous page tables, like kernel_bench/test_decode.py)
     g = torch.Generator().manual_seed(20260609 + rank)
     mgr.free_pages_cpu_stack[:] = torch.randperm(num_pages, generator=g).numpy().astype("int32")
+    # ... and bounds chunks in a shuffled order too (rows do not get consecutive chunks)
+    mgr.free_chunks_cpu_stack[:] = torch.randperm(mgr.num_chunks, generator=g).numpy().astype("int32")
     headroom = max(256, (headroom_steps + 15) // 16 * 16)  # tokens the bench may append per row
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
     set_context(True)
@@ -212,7 +220,7 @@ def build_state(w: dict, rank: int, world: int, phys_layers: int, skip_layers: i
 class DecodeStep:
     """One decode step over all layers through the provider's public API (cache-manager hooks + backend)."""
 
-    def __init__(self, w, mgr, phys_layers, hq, hkv, world, skip_layers):
+    def __init__(self, w, mgr, phys_layers, hq, hkv, world, skip_layers, collective="push"):
         import torch
         from sparse_vllm_b200.attention_backend import B200AttentionBackend
         self.torch = torch
@@ -225,7 +233,17 @@ class DecodeStep:
         self.k_new = torch.randn(L, B, hkv, HEAD_DIM, device=dev, dtype=torch.bfloat16, generator=gen)
         self.v_new = torch.randn(L, B, hkv, HEAD_DIM, device=dev, dtype=torch.bfloat16, generator=gen)
         self.out = torch.zeros(L, B, hq, HEAD_DIM, device=dev, dtype=torch.bfloat16)
-        self.gathered = torch.zeros(B, hq * world * HEAD_DIM, device=dev, dtype=torch.bfloat16) if world > 1 else None
+        self.collective = collective if world > 1 else "none"
+        self.comm = None
+        self.gathered = None
+        if world > 1:
+            if self.collective == "push":
+                from sparse_vllm_b200.parallel import PeerComm
+                nb = B * hq * world * HEAD_DIM * 2
+                self.comm = PeerComm(2 * nb)  # two gathered buffers: a peer may be one layer ahead
+                self.gathered = [self.comm.view(i * nb, (B, hq * world, HEAD_DIM), torch.bfloat16) for i in range(2)]
+            else:
+                self.gathered = [torch.zeros(world, B, hq, HEAD_DIM, device=dev, dtype=torch.bfloat16) for _ in range(2)]
         self.backend = B200AttentionBackend(provider=mgr._get_provider(hq))
         self.input_ids = torch.zeros(B, dtype=torch.int64, device=dev)
         self.positions = torch.zeros(B, dtype=torch.int64, device=dev)
@@ -261,16 +279,76 @@ class DecodeStep:
             mgr.save_rope_kv_if_needed(layer, self.k_new[layer], self.v_new[layer], st.slot_mapping)
             sel = SparseSelection(kind="full", req_indices=st.req_indices, context_lens=st.context_lens,
                                   max_context_len=st.max_context_len)
+            push = self.collective == "push"
             decode_attention_layer(mgr, self.backend, layer, self.q[layer], sel, num_heads=self.hq,
-                                   num_kv_heads=self.hkv, out=self.out[layer])
+                                   num_kv_heads=self.hkv, out=self.out[layer], tp_comm=self.comm if push else None,
+                                   tp_gathered=self.gathered[layer & 1] if push else None)
             # dense layer: store + attention; sparse layer: (store fused into) score/select/pack + attention
             n += 2 if (layer < self.skip or getattr(mgr, "fuse_decode_store", False)) else 3
-            if self.world > 1:
+            if self.collective == "nccl":
                 import torch.distributed as dist
-                dist.all_gather_into_tensor(self.gathered.view(self.world, -1),
-                                            self.out[layer].reshape(1, -1).contiguous().view(-1))
+                dist.all_gather_into_tensor(self.gathered[layer & 1].view(-1), self.out[layer].view(-1))
         if lo == 0 and hi == self.w["layers"]:
             self.launches_per_step = n
+
+
+def verify_gather(step) -> None:
+    """N>1, before anything is timed: after one eager step the gathered attention output of the last layer must
+    hold every rank's head shard at its place — checked against an NCCL all-gather of the ranks' local outputs
+    (bit for bit), on every rank."""
+    import torch
+    import torch.distributed as dist
+    L, world = step.w["layers"], step.world
+    layer = L - 1
+    local = step.out[layer].contiguous()
+    ref = torch.empty(world, *local.shape, dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(ref.view(-1), local.view(-1))
+    got = step.gathered[layer & 1]
+    if step.collective == "push":  # [B, world*Hq, D] with rank r's heads at r*Hq
+        want = ref.permute(1, 0, 2, 3).reshape(got.shape)
+    else:
+        want = ref
+    if not torch.equal(got, want):
+        bad = (got != want).nonzero()[:4].tolist()
+        raise SystemExit(f"rank {dist.get_rank()}: gathered attention output differs from the ranks' shards at {bad}")
+    # every rank also holds the same gathered tensor (cross-check through a MAX/MIN all-reduce of a checksum)
+    chk = got.view(torch.int16).to(torch.int64).sum().reshape(1)
+    lo, hi = chk.clone(), chk.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    if int(lo) != int(hi):
+        raise SystemExit("ranks disagree on the gathered attention output")
+
+
+def graph_kernel_times(step, stream, lo: int, hi: int, reps: int = 5) -> dict:
+    """Average duration of the score+select launch and of the attention launch of layers [lo, hi): each is
+    captured ALONE in a CUDA graph (the other one replaced by a no-op) and replayed, so the figure is the
+    kernel's own time back to back with itself — no Python launch cadence in it (the eager event pairs of
+    round 1 measured the host at small per-rank work)."""
+    import torch
+    prov = step.mgr._get_provider(step.hq)
+    real_select, real_decode = prov.quest_select, prov.decode
+    out = {}
+    try:
+        for key in ("quest_score_select_pack", "sparse_decode_attn"):
+            prov.quest_select = real_select if key == "quest_score_select_pack" else (lambda *a, **k: None)
+            prov.decode = real_decode if key == "sparse_decode_attn" else (lambda q, *a, out=None, **k: out)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=stream):
+                step.layers(lo, hi)
+            g.replay()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(reps):
+                g.replay()
+            e1.record(stream)
+            stream.synchronize()
+            n = reps * (hi - lo)
+            out[key] = {"launches": n, "avg_ms": e0.elapsed_time(e1) / n, "how": "graph replay of this launch alone"}
+            g.reset()
+    finally:
+        prov.quest_select, prov.decode = real_select, real_decode
+    return out
 
 
 class KernelTimers:
@@ -339,7 +417,13 @@ def run_b200(args) -> dict:
     mgr, cfg, phys, hq, hkv = build_state(w, rank, world, args.phys_layers, args.skip_layers,
                                            headroom_steps=2 * (args.steps + max(args.warmup, 3)) + 16)
     note(f"state built ({phys} physical layers)")
-    step = DecodeStep(w, mgr, phys, hq, hkv, world, args.skip_layers)
+    from sparse_vllm_b200 import ops as _ops
+    if args.pdl >= 0:
+        _ops.set_tuning(7, 1 if args.pdl else 2)
+    for item in filter(None, args.tune.split(",")):
+        which, value = item.split("=")
+        _ops.set_tuning(int(which), int(value))
+    step = DecodeStep(w, mgr, phys, hq, hkv, world, args.skip_layers, collective=args.collective)
     geo = geometry(w, hkv, hq)
     steps, warmup = args.steps, max(args.warmup, 3)
 
@@ -356,6 +440,8 @@ def run_b200(args) -> dict:
         for _ in range(2):
             step.layers()
         stream.synchronize()
+        if world > 1:
+            verify_gather(step)
         note("eager steps done")
         if not args.no_graph:
             graph = torch.cuda.CUDAGraph()
@@ -378,15 +464,22 @@ def run_b200(args) -> dict:
         dev_ms = e0.elapsed_time(e1)
         note("timed region done")
 
-        # ---- (2) per-kernel durations, live, eager launches with event pairs
-        timers = KernelTimers(mgr._get_provider(hq))
-        step.layers()
-        timers.enabled = True
-        for _ in range(min(steps, 5)):
+        # ---- (2) per-kernel durations, live: each hot launch alone in a graph (eager event pairs with --no-graph)
+        skip = args.skip_layers
+        kdense = None
+        if graph is not None:
+            ksum = graph_kernel_times(step, stream, skip, w["layers"])
+            if skip > 0:
+                kdense = graph_kernel_times(step, stream, 0, skip)["sparse_decode_attn"]
+        else:
+            timers = KernelTimers(mgr._get_provider(hq))
             step.layers()
-        timers.enabled = False
+            timers.enabled = True
+            for _ in range(min(steps, 5)):
+                step.layers(skip)
+            timers.enabled = False
+            ksum = timers.summary()
         barrier()
-        ksum = timers.summary()
         note("per-kernel timing done")
 
         # ---- (3) end to end through the public API with HOST buffers: every step copies its q / new K,V
@@ -466,6 +559,7 @@ def run_b200(args) -> dict:
             "traffic": ncu_traffic(w["key"], "quest_page_score_kernel") if world == 1 else None,
             "bytes_per_launch": sel_bytes, "avg_launch_ms": sel_ms}
     roof["frac"] = roof["achieved"] / peak
+    roof["how"] = ksum["quest_score_select_pack"].get("how", "eager launches, CUDA event pairs")
     roof_attn = {"bound": "hbm", "kernel": "sparse_decode_attn_kernel", "achieved": attn_bytes / (attn_ms * 1e-3) / 1e9,
                  "peak": peak, "unit": "GB/s", "bytes_per_launch": attn_bytes, "avg_launch_ms": attn_ms,
                  "traffic": ncu_traffic(w["key"], "sparse_decode_attn_kernel") if world == 1 else None}
@@ -473,6 +567,16 @@ def run_b200(args) -> dict:
     roof_step = {"achieved": step_bytes / (ms_per_step * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                  "bytes_per_step": step_bytes}
     roof_step["frac"] = roof_step["achieved"] / peak
+    for r_ in (roof, roof_attn, roof_step):  # north_star quotes ~8 TB/s nominal: report against that too
+        r_["frac_of_nominal_8tbs"] = r_["achieved"] / NOMINAL_GBS
+    roof_dense = None
+    if kdense is not None:
+        dense_bytes = geo["dense_bytes"] * w["bsz"]
+        roof_dense = {"bound": "hbm", "kernel": "sparse_decode_attn_kernel (dense skip layer, identity slot table)",
+                      "achieved": dense_bytes / (kdense["avg_ms"] * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                      "bytes_per_launch": dense_bytes, "avg_launch_ms": kdense["avg_ms"]}
+        roof_dense["frac"] = roof_dense["achieved"] / peak
+        roof_dense["frac_of_nominal_8tbs"] = roof_dense["achieved"] / NOMINAL_GBS
     def shutdown():
         """Release the captured graph BEFORE the NCCL communicator it references (destroying the process
         group under a live graph hangs), and never let clean-up keep the job alive."""
@@ -490,6 +594,8 @@ def run_b200(args) -> dict:
         chunk_graphs.clear()
         torch.cuda.synchronize()
         dist.barrier()
+        if step.comm is not None:
+            step.comm.close()
         dist.destroy_process_group()
         watchdog.cancel()
 
@@ -502,9 +608,14 @@ def run_b200(args) -> dict:
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": w["name"], "layers": w["layers"], "q_heads": w["hq"], "kv_heads": w["hkv"],
                    "batch": w["bsz"], "ctx": w["ctx"], "page": PAGE, "token_budget": w["budget"],
-                   "quest_skip_layers": args.skip_layers, "parallelism": f"tp{world} (KV heads sharded)",
+                   "quest_skip_layers": args.skip_layers,
+                   "parallelism": f"tp{world} (KV heads sharded"
+                   + (f"; head shards gathered by {'peer stores in the attention epilogue (NVLink)' if args.collective == 'push' else 'NCCL all_gather_into_tensor'})" if world > 1 else ")"),
+                   "pdl": {1: "on", 0: "off"}.get(args.pdl, "library default"),
                    "physical_kv_pools": phys, "l2": "inputs larger than L2 (>= 0.8 GB touched per layer; layers cycle "
-                   f"{phys} distinct KV+bounds pools)", "timed": "cuda graph replay" if graph is not None else "eager"},
+                   f"{phys} distinct KV+bounds pools)",
+                   "timed": ("cuda graph replay of one decode step (slots and lengths frozen at the step prepared before "
+                             "capture; only the e2e arm advances the context)") if graph is not None else "eager"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / steps,
                 "how": f"{n_chunks} chunks of {per} layers; a chunk's H2D copy and the previous chunk's D2H read-back "
@@ -513,6 +624,8 @@ def run_b200(args) -> dict:
         "roofline": roof, "roofline_attention": roof_attn, "roofline_step": roof_step,
         "clocks": clocks,
     }
+    if roof_dense is not None:
+        line["roofline_dense_layer"] = roof_dense
     if world > 1:
         print(json.dumps(line), flush=True)  # before clean-up: the line must not depend on it
         line["_printed"] = True

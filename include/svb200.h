@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SVB200_ABI_VERSION 4
+#define SVB200_ABI_VERSION 5
 
 enum {
   SVB200_OK = 0,
@@ -49,11 +49,14 @@ int svb200_sm_count(void);
 int svb200_set_max_ctas(int32_t n);
 /*
  * Experiment knob `which` := value; 0 restores the automatic choice.  Returns the previous value,
- * -1 for an unknown knob.  Results never depend on it.  Score kernel: 0 = row groups of the
- * scheduler, 2 = chunks per claim at least, 3 = divisor of the guided claim size, 4 = 1: 16-byte
- * LDGSTS copies instead of bulk copies, 5 = ring stages per 16-page unit (1, 2, 4), 6 = 1: stage q
- * once / 2: stage q+ and q-.  Attention kernel: 1 = KB of K/V a CTA should stream at least
- * (grid sizing of small launches; default 256).
+ * -1 for an unknown knob.  Results never depend on it (except 5, which is an experiment that skips the math).
+ * Score kernel: 0 = row groups of the scheduler, 2 = chunks per claim at least, 3 = divisor of the guided
+ * claim size, 4 = units per claimed chunk, 6 = 1: stage q once / 2: stage q+ and q-.
+ * Attention kernel: 1 = KB of K/V a CTA should stream at least (grid sizing of small launches; default 256),
+ * 8 = 2: one bulk copy per token row even where a granule of rows is contiguous.
+ * Both: 5 = 1 (score) / 2 (attention): stream the bytes but skip the tensor-core contractions (results
+ * are garbage; measures what the copy pipeline alone sustains), 7 = programmatic dependent launch
+ * (1 = on, 2 = off): a launch may start while its predecessor in the stream drains.
  */
 int svb200_set_tuning(int32_t which, int32_t value);
 /*
@@ -80,11 +83,16 @@ void svb200_debug_times(void* device_buffer);
 int64_t svb200_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads);
 
 /* ------------------------------------------------------------------------- *
- * Quest page bounds ("metadata").  Layout owned by this provider:
- *   bounds[L][num_pages][2][Hkv][128] bf16, [..][0] = max, [..][1] = min
- * (the reference keeps two separate planes metadata_cache[2][L][P][Hkv][D],
- *  engine/cache_manager/quest.py:96-105; interleaving per page makes one page's
- *  bounds a single contiguous 512*Hkv-byte record for the scoring scan).
+ * Quest page bounds ("metadata").  Layout owned by this provider (csrc/bounds_layout.cuh):
+ * a *bounds chunk* holds the bounds of 16 consecutive LOGICAL pages of one request row,
+ *   bounds_layer[num_chunks][hs][16][2 (max,min)][Hkv/hs][128] bf16
+ * (hs = smallest divisor of Hkv leaving <= 4 heads; 16-byte segments of every 256-byte row are
+ *  XOR-swizzled by page & 7), so the scoring scan reads one contiguous 8-32 KB piece per ring stage
+ * with no page-table indirection.  The reference keeps two planes metadata_cache[2][L][P][Hkv][D]
+ * indexed by PHYSICAL page and gathers them per row (engine/cache_manager/quest.py:96-105,
+ * 1870-1881).  Two int32 maps, maintained by the cache manager when it allocates pages:
+ *   unit_table[rows][stride]: bounds chunk of (row, logical page / 16), -1 = none
+ *   page_rec[num_pages]     : physical page -> chunk * 16 + (logical page % 16), -1 = unassigned
  * ------------------------------------------------------------------------- */
 
 /*
@@ -94,12 +102,12 @@ int64_t svb200_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_k
  * (engine/cache_manager/quest.py:1608-1716): K rows were already stored, so
  * full pages and pages completed across chunks are the same scan.
  *   k_cache      [num_slots][Hkv][128] bf16 (one layer)
- *   bounds_layer [num_pages][2][Hkv][128] bf16 (one layer)
+ *   bounds_layer num_chunks bounds chunks (one layer); page_rec [num_slots/16] int32
  *   slot_mapping [n_tokens] int32 (-1 = padding)
  */
-int svb200_quest_page_minmax(const void* k_cache, void* bounds_layer,
-                             const int32_t* slot_mapping, int32_t n_tokens,
-                             int32_t num_kv_heads, int64_t num_slots,
+int svb200_quest_page_minmax(const void* k_cache, void* bounds_layer, int64_t num_chunks,
+                             const int32_t* page_rec, const int32_t* slot_mapping,
+                             int32_t n_tokens, int32_t num_kv_heads, int64_t num_slots,
                              void* stream);
 
 /*
@@ -108,11 +116,12 @@ int svb200_quest_page_minmax(const void* k_cache, void* bounds_layer,
  * of page (len/16 - 1) in each layer.
  * Replaces QuestCacheManager.on_forward_end (quest.py:1719-1771, a Python loop
  * over layers with three launches each).
- *   k_cache_all  [L][num_slots][Hkv][128] bf16, bounds_all [L][num_pages][2][Hkv][128]
+ *   k_cache_all  [L][num_slots][Hkv][128] bf16, bounds_all [L][num_chunks] bounds chunks
  *   page_table   [rows][page_table_stride] int32, req_rows [batch] int32,
  *   seq_lens     [batch] int32 (length INCLUDING the token just stored)
  */
-int svb200_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
+int svb200_quest_decode_page_complete(const void* k_cache_all, void* bounds_all, int64_t num_chunks,
+                                      const int32_t* page_rec,
                                       const int32_t* page_table,
                                       int64_t page_table_stride,
                                       const int32_t* req_rows,
@@ -128,22 +137,22 @@ int svb200_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
  * (fp32 accumulation, three bf16 roundings — exactly the rounding structure of
  *  QuestCacheManager._score_pages_batched, quest.py:1773-1802), columns
  * p >= ceil(ctx/16) - 1 are -inf (quest.py:1883-1885).  The gather of
- * quest.py:1870-1881 is fused: bounds are read through the page table.
+ * quest.py:1870-1881 does not exist: a row's bounds are contiguous chunks.
  *   q            [batch][Hq][128] bf16, row stride q_stride_b elements
- *   bounds_layer [num_pages][2][Hkv][128] bf16; page-table entries outside
- *                [0, num_pages) score -inf
- *   page_table   [rows][page_table_stride] int32 (-1 empty)
- *   req_rows     [batch] int32 row of each batch entry in page_table
+ *   bounds_layer num_chunks bounds chunks; units whose unit_table entry is outside
+ *                [0, num_chunks) score -inf
+ *   unit_table   [rows][unit_table_stride] int32
+ *   req_rows     [batch] int32 row of each batch entry in unit_table / page_table
  *   context_lens [batch] int32
  *   scores       [batch][score_stride] bf16 out, score_stride >= n_cols
  *   sched_scratch svb200_sched_scratch_ints(batch) zeroed int32 (left zeroed)
- * Work is claimed dynamically (chunks of 32 pages from per-row counters), so SMs the memory
+ * Work is claimed dynamically (~64 KB chunks from per-row counters), so SMs the memory
  * system serves faster score more pages; the result does not depend on who scored what.
  */
 int svb200_quest_page_score(const void* q, int64_t q_stride_b,
-                            const void* bounds_layer, int64_t num_pages,
-                            const int32_t* page_table,
-                            int64_t page_table_stride, const int32_t* req_rows,
+                            const void* bounds_layer, int64_t num_chunks,
+                            const int32_t* unit_table,
+                            int64_t unit_table_stride, const int32_t* req_rows,
                             const int32_t* context_lens, void* scores,
                             int64_t score_stride, int32_t batch, int32_t num_q_heads,
                             int32_t num_kv_heads, int32_t n_cols, int32_t* sched_scratch,
@@ -181,7 +190,8 @@ int svb200_quest_select_pack(const void* scores, int64_t score_stride,
  *   tickets  svb200_sched_scratch_ints(batch) zero-initialised int32 scratch (left zeroed).
  */
 int svb200_quest_score_select_pack(
-    const void* q, int64_t q_stride_b, const void* bounds_layer, int64_t num_pages,
+    const void* q, int64_t q_stride_b, const void* bounds_layer, int64_t num_chunks,
+    const int32_t* unit_table, int64_t unit_table_stride,
     const int32_t* page_table, int64_t page_table_stride, const int32_t* req_rows,
     const int32_t* context_lens, void* scores, int64_t score_stride, int32_t batch,
     int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols, int32_t prev_budget,
@@ -198,13 +208,15 @@ int svb200_quest_score_select_pack(
  * of on_forward_end (quest.py:1719-1771) + build_decode_view (quest.py:1805-1913) for
  * one layer.
  *   refresh_bounds  != 0: rebuild the bounds record of a page the token completes
- *                   (requires num_slots == num_pages * 16); bounds_layer is written.
+ *                   (through page_rec); bounds_layer is written.
+ * With n_cols <= 0 nothing is scored but the rows are still stored.
  */
 int svb200_quest_store_score_select_pack(
     const void* key, int64_t k_stride, const void* value, int64_t v_stride,
     void* k_cache, void* v_cache, const int32_t* slot_mapping, int64_t num_slots,
-    int32_t refresh_bounds,
-    const void* q, int64_t q_stride_b, void* bounds_layer, int64_t num_pages,
+    int32_t refresh_bounds, const int32_t* page_rec,
+    const void* q, int64_t q_stride_b, void* bounds_layer, int64_t num_chunks,
+    const int32_t* unit_table, int64_t unit_table_stride,
     const int32_t* page_table, int64_t page_table_stride, const int32_t* req_rows,
     const int32_t* context_lens, void* scores, int64_t score_stride, int32_t batch,
     int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols, int32_t prev_budget,
@@ -288,7 +300,62 @@ int svb200_store_kv_minmax(const void* key, int64_t k_stride, const void* value,
                            int64_t v_stride, void* k_cache, void* v_cache,
                            const int32_t* slot_mapping, int32_t n_tokens,
                            int32_t num_kv_heads, int64_t num_slots,
-                           void* quest_bounds_layer, void* stream);
+                           void* quest_bounds_layer, const int32_t* page_rec,
+                           int64_t num_chunks, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * Tensor parallelism over NVLink peer memory (one process per GPU).
+ * A communicator is plain data: every rank maps every rank's data buffer and sync block
+ * (svb200_symm_alloc / svb200_ipc_open below, or any other peer-mapped memory).
+ *   peer_buf[r]   data buffer of rank r (same size on every rank), 16-byte aligned
+ *   peer_sync[r]  sync block of rank r: int32[16], zero-initialised; [q] = arrival flag written by
+ *                 rank q, [8] = epoch, [9] = finished CTAs (owner only)
+ * Every rank must issue the same sequence of collective launches on a communicator.  A rank can run at
+ * most one collective ahead of its peers, so callers alternate two regions of peer_buf.
+ * ------------------------------------------------------------------------- */
+#define SVB200_MAX_PEERS 8
+typedef struct {
+  int32_t world, rank;
+  void* peer_buf[SVB200_MAX_PEERS];
+  int32_t* peer_sync[SVB200_MAX_PEERS];
+} svb200_comm_t;
+
+/*
+ * svb200_sparse_decode_attn whose epilogue also gathers the head shards: every final bf16 row
+ * [b][h_local] is stored to rank r's peer_buf[r] + gather_offset_bytes at
+ * [b][rank*Hq + h_local][128] (row stride gather_stride_b elements >= world*Hq*128) for every r, and the
+ * launch completes only after all ranks' rows have arrived here — the [B][Hq_total][128] tensor o_proj reads.
+ * Replaces the per-layer NCCL collective after attention (the reference all-reduces after a row-parallel
+ * o_proj, layers/linear.py:581-589; its fused providers, operators/all_reduce.py:115-409, are H100-only).
+ */
+int svb200_sparse_decode_attn_tp(const void* q, int64_t q_stride_b, const void* k_cache,
+                                 const void* v_cache, int64_t num_slots,
+                                 const int32_t* slot_table, int64_t slot_table_stride,
+                                 int32_t max_len, const int32_t* req_rows,
+                                 const int32_t* seq_lens, void* out, int64_t out_stride_b,
+                                 float* attn_score, int64_t score_stride, int32_t batch,
+                                 int32_t num_q_heads, int32_t num_kv_heads,
+                                 int32_t heads_per_cta, void* workspace,
+                                 int64_t workspace_bytes, float sm_scale,
+                                 const svb200_comm_t* comm, int64_t gather_offset_bytes,
+                                 int64_t gather_stride_b, void* stream);
+
+/*
+ * One-shot SUM all-reduce of n_elems bf16 (a multiple of 8): rank r's input is
+ * peer_buf[r] + in_offset_bytes; every rank reads all inputs over NVLink, accumulates in fp32 in rank
+ * order (bit-identical results on all ranks) and writes bf16 to its local `out`.
+ * Role of ParallelContext.tp_all_reduce after RowParallelLinear (distributed/parallel_context.py:87-116,
+ * layers/linear.py:581-589; provider family operators/all_reduce.py).
+ */
+int svb200_allreduce_sum_bf16(const svb200_comm_t* comm, int64_t in_offset_bytes, int64_t n_elems,
+                              void* out, void* stream);
+
+/* cudaMalloc'ed, zeroed device memory + its 64-byte CUDA IPC handle (host buffers). */
+int svb200_symm_alloc(int64_t bytes, void** ptr_host, void* handle64_host);
+int svb200_symm_free(void* ptr);
+/* Map a peer's allocation from its IPC handle (enables peer access lazily); unmap it. */
+int svb200_ipc_open(const void* handle64_host, void** ptr_host);
+int svb200_ipc_close(void* ptr);
 
 #ifdef __cplusplus
 }

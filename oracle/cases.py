@@ -130,6 +130,29 @@ def quest_fill_cache(inp, hkv, d=128):
     return k_cache, v_cache
 
 
+def chunk_maps(page_table: torch.Tensor, num_pages: int, seed: int = 0, spare: int = 3):
+    """Bounds-chunk assignment for a page table whose rows hold a prefix of valid pages (-1 after it):
+    every (row, logical page // 16) gets a chunk id from a SHUFFLED pool (so the unit-table indirection is
+    exercised), ``page_rec[physical page] = chunk * 16 + logical page % 16`` (csrc/bounds_layout.cuh).
+    Returns (unit_table [rows, units] int32, page_rec [num_pages] int32, num_chunks)."""
+    pt = page_table.cpu().numpy()
+    rows, max_pages = pt.shape
+    max_units = (max_pages + PAGE - 1) // PAGE
+    num_chunks = rows * max_units + spare
+    perm = np.random.Generator(np.random.PCG64(seed)).permutation(num_chunks).astype(np.int32)
+    unit_table = np.full((rows, max_units), -1, dtype=np.int32)
+    page_rec = np.full((num_pages,), -1, dtype=np.int32)
+    k = 0
+    for r in range(rows):
+        npg = int((pt[r] >= 0).sum())
+        nu = (npg + PAGE - 1) // PAGE
+        unit_table[r, :nu] = perm[k: k + nu]
+        k += nu
+        j = np.arange(npg)
+        page_rec[pt[r, :npg]] = unit_table[r, j // PAGE] * PAGE + j % PAGE
+    return torch.from_numpy(unit_table), torch.from_numpy(page_rec), num_chunks
+
+
 def make_attn_inputs(*, seed, bsz, hq, hkv, lens, width, num_slots, d=128, **_):
     gen = _rng(seed)
     q = randn_bf16(gen, bsz, hq, d)

@@ -173,6 +173,27 @@ def classify_selection(scores_ref: torch.Tensor, sel_ref, sel_got, n_valid: int)
     return {"exact": 0, "tie": int(ok), "bad": int(not ok), "detail": detail}
 
 
+def classify_selection_ulp(scores_ref: torch.Tensor, sel_ref, sel_got, n_valid: int, ulp_slack: int = 1) -> dict:
+    """``classify_selection`` plus the third class of SURVEY.md §7: ``near`` = the two page sets differ only
+    in pages whose REFERENCE score sits within ``ulp_slack`` bf16 ulps of the reference's k-th score (a kernel
+    that selects on its own scores may see those one rounding step away: cuBLAS / oneDNN / this kernel
+    accumulate fp32 in different orders).  Anything else is ``bad`` — in particular a wrong selection made on
+    correct scores.  Returns counts exact / tie / near / bad (exactly one is 1)."""
+    c = classify_selection(scores_ref, sel_ref, sel_got, n_valid)
+    out = {"exact": c["exact"], "tie": c["tie"], "near": 0, "bad": c["bad"], "detail": c["detail"]}
+    if not c["bad"] or ulp_slack <= 0:
+        return out
+    ref, got = set(int(x) for x in sel_ref), set(int(x) for x in sel_got)
+    if any(not 0 <= i < max(n_valid, 1) for i in got):
+        return out
+    kth = scores_ref[sorted(ref)].float().min().to(scores_ref.dtype)
+    swapped = torch.tensor(sorted(ref ^ got), dtype=torch.long)
+    d = bf16_ulp_distance(scores_ref[swapped], kth.expand(len(swapped)).contiguous())
+    if int(d.max()) <= ulp_slack:
+        out.update(near=1, bad=0)
+    return out
+
+
 def topk_numpy_lowest_index(scores_row: np.ndarray, k: int) -> np.ndarray:
     """Deterministic top-k used for size-independent checks: ties -> lowest index."""
     order = np.lexsort((np.arange(scores_row.size), -scores_row.astype(np.float64)))

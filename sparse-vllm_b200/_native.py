@@ -8,16 +8,27 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_char_p, c_float, c_int32, c_int64, c_void_p
+from ctypes import POINTER, c_char_p, c_float, c_int32, c_int64, c_void_p
 from pathlib import Path
 
 import torch
 
 _LIB_PATH = Path(__file__).resolve().parent / "lib" / "libsvb200.so"
-ABI_VERSION = 4
+ABI_VERSION = 5
+
+MAX_PEERS = 8
+
+
+class Comm(ctypes.Structure):
+    """svb200_comm_t: peer-mapped data buffers and sync blocks of every rank."""
+    _fields_ = [("world", c_int32), ("rank", c_int32), ("peer_buf", c_void_p * MAX_PEERS),
+                ("peer_sync", c_void_p * MAX_PEERS)]
+
 
 # name -> (restype, argtypes); mirrors include/svb200.h one to one.
 _P = c_void_p
+_ATTN_ARGS = [_P, c_int64, _P, _P, c_int64, _P, c_int64, c_int32, _P, _P, _P, c_int64, _P, c_int64,
+              c_int32, c_int32, c_int32, c_int32, _P, c_int64, c_float]
 _SIGNATURES = {
     "svb200_abi_version": (c_int32, []),
     "svb200_last_error": (c_char_p, []),
@@ -27,9 +38,9 @@ _SIGNATURES = {
     "svb200_sched_scratch_ints": (c_int64, [c_int32]),
     "svb200_debug_times": (None, [_P]),
     "svb200_workspace_bytes": (c_int64, [c_int32, c_int32, c_int32]),
-    "svb200_quest_page_minmax": (c_int32, [_P, _P, _P, c_int32, c_int32, c_int64, _P]),
+    "svb200_quest_page_minmax": (c_int32, [_P, _P, c_int64, _P, _P, c_int32, c_int32, c_int64, _P]),
     "svb200_quest_decode_page_complete": (
-        c_int32, [_P, _P, _P, c_int64, _P, _P, c_int32, c_int32, c_int32, c_int64, c_int64, _P]),
+        c_int32, [_P, _P, c_int64, _P, _P, c_int64, _P, _P, c_int32, c_int32, c_int32, c_int64, c_int64, _P]),
     "svb200_quest_page_score": (
         c_int32, [_P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32, c_int32, c_int32,
                   _P, _P]),
@@ -37,21 +48,25 @@ _SIGNATURES = {
         c_int32, [_P, c_int64, c_int32, _P, c_int64, _P, _P, c_int32, c_int32, _P, c_int64, _P, _P, _P,
                   c_int64, c_int32, c_int32, c_int32, _P]),
     "svb200_quest_score_select_pack": (
-        c_int32, [_P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32, c_int32, c_int32,
-                  c_int32, _P, c_int64, _P, _P, _P, _P]),
+        c_int32, [_P, c_int64, _P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32,
+                  c_int32, c_int32, c_int32, _P, c_int64, _P, _P, _P, _P]),
     "svb200_quest_store_score_select_pack": (
-        c_int32, [_P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32,
-                  _P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32, c_int32, c_int32,
-                  c_int32, _P, c_int64, _P, _P, _P, _P]),
-    "svb200_sparse_decode_attn": (
-        c_int32, [_P, c_int64, _P, _P, c_int64, _P, c_int64, c_int32, _P, _P, _P, c_int64, _P, c_int64,
-                  c_int32, c_int32, c_int32, c_int32, _P, c_int64, c_float, _P]),
+        c_int32, [_P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, _P,
+                  _P, c_int64, _P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32,
+                  c_int32, c_int32, c_int32, _P, c_int64, _P, _P, _P, _P]),
+    "svb200_sparse_decode_attn": (c_int32, [*_ATTN_ARGS, _P]),
+    "svb200_sparse_decode_attn_tp": (c_int32, [*_ATTN_ARGS, POINTER(Comm), c_int64, c_int64, _P]),
+    "svb200_allreduce_sum_bf16": (c_int32, [POINTER(Comm), c_int64, c_int64, _P, _P]),
+    "svb200_symm_alloc": (c_int32, [c_int64, POINTER(c_void_p), _P]),
+    "svb200_symm_free": (c_int32, [_P]),
+    "svb200_ipc_open": (c_int32, [_P, POINTER(c_void_p)]),
+    "svb200_ipc_close": (c_int32, [_P]),
     "svb200_h2o_normalize_accumulate": (
         c_int32, [_P, c_int64, c_int32, c_int32, c_float, _P, c_int64, _P, _P]),
     "svb200_h2o_select_compact": (
         c_int32, [_P, _P, _P, _P, _P, _P, _P, c_int32, c_int32, c_int32, c_int32, _P]),
     "svb200_store_kv_minmax": (
-        c_int32, [_P, c_int64, _P, c_int64, _P, _P, _P, c_int32, c_int32, c_int64, _P, _P]),
+        c_int32, [_P, c_int64, _P, c_int64, _P, _P, _P, c_int32, c_int32, c_int64, _P, _P, c_int64, _P]),
 }
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)
 
@@ -105,6 +120,11 @@ def ptr(t: torch.Tensor | None) -> int | None:
 
 
 def current_stream_ptr(device: torch.device | None = None) -> int:
+    """Stream of ``device`` the launch goes to.  The library launches on the thread's CURRENT device, so a
+    tensor living on another device is refused instead of launching on the wrong GPU (fail fast)."""
+    if device is not None and device.index is not None and device.index != torch.cuda.current_device():
+        raise RuntimeError(f"tensors live on {device} but the current CUDA device is {torch.cuda.current_device()}: "
+                           "call torch.cuda.set_device(...) (one process per GPU) before using the provider.")
     return torch.cuda.current_stream(device).cuda_stream
 
 

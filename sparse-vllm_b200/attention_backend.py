@@ -45,9 +45,12 @@ class B200AttentionBackend:
     def run_decode(self, q: torch.Tensor, view: DecodeComputeView, *, mid_o: torch.Tensor | None = None,
                    mid_o_logexpsum: torch.Tensor | None = None, max_len_in_batch: int, block_seq: int = 256,
                    num_heads: int, num_kv_heads: int, gqa_block_n: int = 16, gqa_num_warps: int = 2,
-                   workspace: torch.Tensor | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+                   workspace: torch.Tensor | None = None, out: torch.Tensor | None = None,
+                   tp_comm=None, tp_gathered: torch.Tensor | None = None) -> torch.Tensor:
         # mid_o / mid_o_logexpsum / block_seq / gqa_* are the reference's split-K workspace and Triton launch
         # knobs; they are accepted for signature compatibility and unused (stream-K has its own scratch).
+        # tp_comm / tp_gathered (extension): the launch's epilogue also gathers the head shards of all TP ranks
+        # into ``tp_gathered [B, world*Hq, D]`` (parallel.PeerComm), in place of a collective after the layer.
         del mid_o, mid_o_logexpsum, block_seq, gqa_block_n, gqa_num_warps
         payload = view.payload
         if not isinstance(payload, ExplicitKVPayload):
@@ -62,12 +65,14 @@ class B200AttentionBackend:
         o = torch.empty_like(q) if out is None else out
         return self._provider(q, num_heads, num_kv_heads).decode(
             q, payload.k_cache, payload.v_cache, meta.active_slots, meta.req_indices, meta.context_lens, out=o,
-            workspace=workspace, max_len=int(max_len_in_batch), attn_score=meta.attn_score)
+            workspace=workspace, max_len=int(max_len_in_batch), attn_score=meta.attn_score,
+            comm=tp_comm, gathered=tp_gathered)
 
 
 def decode_attention_layer(cache_manager, backend: B200AttentionBackend, layer_idx: int, q: torch.Tensor,
                            selection: SparseSelection, *, num_heads: int, num_kv_heads: int,
-                           out: torch.Tensor | None = None) -> torch.Tensor:
+                           out: torch.Tensor | None = None, tp_comm=None,
+                           tp_gathered: torch.Tensor | None = None) -> torch.Tensor:
     """Decode branch of the generic ``Attention.forward`` (layers/attention.py:162-250)."""
     context = get_context()
     view = cache_manager.build_decode_compute_view(layer_idx, q, selection, num_heads=num_heads,
@@ -86,6 +91,7 @@ def decode_attention_layer(cache_manager, backend: B200AttentionBackend, layer_i
         raise RuntimeError(f"decode requires a positive context length, got {max_len_in_batch} at layer={layer_idx}")
     workspace = get_decode_workspace(context, q.shape[0], num_heads, num_kv_heads, q.device)
     o = backend.run_decode(q, view, max_len_in_batch=max_len_in_batch, num_heads=num_heads,
-                           num_kv_heads=num_kv_heads, workspace=workspace, out=out)
+                           num_kv_heads=num_kv_heads, workspace=workspace, out=out, tp_comm=tp_comm,
+                           tp_gathered=tp_gathered)
     cache_manager.on_layer_attention_end(layer_idx)
     return o

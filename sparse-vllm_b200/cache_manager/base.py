@@ -113,7 +113,8 @@ class CacheManager:
         if slot_mapping is None:
             slot_mapping = self.layer_batch_state.slot_mapping
         k_cache, v_cache = self.get_layer_kv_cache(layer_idx)
-        ops.store_kv_minmax(k, v, k_cache, v_cache, slot_mapping, self._fused_store_bounds(layer_idx))
+        ops.store_kv_minmax(k, v, k_cache, v_cache, slot_mapping, self._fused_store_bounds(layer_idx),
+                            getattr(self, "page_rec", None))
         self.on_kv_stored(layer_idx, k, slot_mapping)
 
     def _fused_store_bounds(self, layer_idx: int) -> torch.Tensor | None:

@@ -5,9 +5,11 @@ KV ``[2, L, slots, Hkv, D]``, a page table per request row, per-page key bounds 
 the decode-time view builder that scores pages against the query, keeps the top pages plus the newest
 one and hands attention a packed token-slot table.  What differs is the layout and the execution:
 
-* bounds live as ``[L, pages, 2(max,min), Hkv, D]`` (one contiguous record per page and layer) instead
-  of two planes ``[2, L, pages, Hkv, D]`` (quest.py:96-105), so the scoring scan reads each page once,
-  through the page table, with no gathered copy (quest.py:1870-1881 materialises two);
+* bounds live in *chunks* of 16 consecutive LOGICAL pages of one row (``ops.bounds_shape``,
+  csrc/bounds_layout.cuh) instead of two planes ``[2, L, P, Hkv, D]`` indexed by physical page
+  (quest.py:96-105): the scoring scan of a row is a stream of contiguous 8-64 KB reads with no page-table
+  indirection and no gathered copy (quest.py:1870-1881 materialises two).  The manager assigns a chunk to
+  (row, logical page // 16) when it allocates the page and keeps ``unit_table`` / ``page_rec`` on the device;
 * score + mask + top-k + last page + slot packing is ONE launch for long-text batches
   (quest.py:1773-1802, 1883-1913 are ~20 torch launches); mixed batches use two launches;
 * a decode token that completes a page refreshes its bounds inside the KV store launch (or, in
@@ -53,9 +55,15 @@ class QuestCacheManager(CacheManager):
         self.max_model_len = int(max_model_len)
         self.max_pages_per_row = (self.max_model_len + PAGE - 1) // PAGE
         self.max_rows = int(max_rows)
-        # page bounds, resident on the GPU: [L, pages, 2, Hkv, D]
-        self.bounds = torch.zeros((self.num_layers, self.num_pages, 2, self.num_kv_heads, self.head_dim),
-                                  dtype=dtype, device=self.device)
+        # page bounds, resident on the GPU, in chunks of 16 logical pages of one row (a row wastes < 1 chunk)
+        self.max_units_per_row = (self.max_pages_per_row + PAGE - 1) // PAGE
+        self.num_chunks = (self.num_pages + PAGE - 1) // PAGE + self.max_rows
+        self.bounds = self._alloc_bounds()
+        self.unit_table = torch.full((self.max_rows, self.max_units_per_row), -1, dtype=torch.int32, device=self.device)
+        self.unit_table_cpu = np.full((self.max_rows, self.max_units_per_row), -1, dtype=np.int32)
+        self.page_rec = torch.full((self.num_pages,), -1, dtype=torch.int32, device=self.device)
+        self.free_chunks_cpu_stack = np.arange(self.num_chunks - 1, -1, -1, dtype=np.int32)
+        self._num_free_chunks = self.num_chunks
         self.buffer_req_to_page_slots = torch.full((self.max_rows, self.max_pages_per_row), -1, dtype=torch.int32,
                                                    device=self.device)
         self.buffer_req_to_page_slots_cpu = np.full((self.max_rows, self.max_pages_per_row), -1, dtype=np.int32)
@@ -72,6 +80,16 @@ class QuestCacheManager(CacheManager):
         # decode: the layer's new K/V rows wait here for the layer's scoring launch, which stores them itself
         self.fuse_decode_store = bool(fuse_decode_store)
         self._pending_store: tuple[int, ops.DecodeStore] | None = None
+
+    def _alloc_bounds(self) -> torch.Tensor:
+        if self.device.type != "cuda":  # host-logic tests (_allow_host_tensors): same shape, no kernel touches it
+            return torch.zeros((self.num_layers, *ops.bounds_shape(self.num_chunks, self.num_kv_heads)), dtype=torch.bfloat16)
+        return ops.alloc_bounds(self.num_chunks, self.num_kv_heads, self.device, layers=self.num_layers)
+
+    def bounds_by_page(self, layer_idx: int) -> torch.Tensor:
+        """``[num_pages, 2 (max, min), Hkv, D]`` indexed by physical page — the reference's ``metadata_cache``
+        order (quest.py:96-105) — rebuilt from the chunk layout (debugging / tests, not the hot path)."""
+        return ops.unpack_bounds(self.bounds[self.kv_layer_index(layer_idx)], self.page_rec)
 
     # ------------------------------------------------------------------ provider / scratch
     def _get_provider(self, num_heads: int) -> B200SparseDecodeProvider:
@@ -118,6 +136,27 @@ class QuestCacheManager(CacheManager):
         self._num_free_pages -= n
         return pages
 
+    def _assign_bounds_records(self, rows: np.ndarray, page_idx: np.ndarray, pages: np.ndarray) -> None:
+        """Give the freshly allocated ``pages`` (logical page ``page_idx`` of table row ``rows``) their bounds
+        records: a new chunk per (row, page_idx // 16) when page_idx % 16 == 0.  Host numpy + three small
+        H2D index updates, like the page-table update next to it."""
+        rows = np.asarray(rows, dtype=np.int64)
+        page_idx = np.asarray(page_idx, dtype=np.int64)
+        units = page_idx // PAGE
+        new_unit = np.nonzero(page_idx % PAGE == 0)[0]
+        if new_unit.size:
+            if self._num_free_chunks < new_unit.size:
+                raise RuntimeError(f"Out of QuEST bounds chunks: need={new_unit.size}, free={self._num_free_chunks}.")
+            ptr = self._num_free_chunks
+            chunks = self.free_chunks_cpu_stack[ptr - new_unit.size: ptr][::-1].copy()
+            self._num_free_chunks -= int(new_unit.size)
+            self.unit_table_cpu[rows[new_unit], units[new_unit]] = chunks
+            self.unit_table[torch.from_numpy(rows[new_unit]).to(self.device),
+                            torch.from_numpy(units[new_unit]).to(self.device)] = torch.from_numpy(chunks).to(self.device)
+        recs = self.unit_table_cpu[rows, units].astype(np.int64) * PAGE + page_idx % PAGE
+        self.page_rec[torch.from_numpy(np.asarray(pages, dtype=np.int64)).to(self.device)] = \
+            torch.from_numpy(recs.astype(np.int32)).to(self.device)
+
     def allocate_prefill(self, seq_id: int, num_tokens: int) -> torch.Tensor:
         """Slots for the next ``num_tokens`` tokens of a sequence (chunked prefill, quest.py:1426-1493)."""
         row = self._get_free_row(seq_id)
@@ -131,6 +170,7 @@ class QuestCacheManager(CacheManager):
             pages = self._pop_pages(need - have)
             self.buffer_req_to_page_slots_cpu[row, have:need] = pages
             self.buffer_req_to_page_slots[row, have:need] = torch.from_numpy(pages).to(self.device)
+            self._assign_bounds_records(np.full(need - have, row), np.arange(have, need), pages)
         pos = np.arange(cur, new_len, dtype=np.int64)
         slots = self.buffer_req_to_page_slots_cpu[row, pos // PAGE].astype(np.int64) * PAGE + pos % PAGE
         slots_t = torch.from_numpy(slots.astype(np.int32)).to(self.device)
@@ -148,6 +188,13 @@ class QuestCacheManager(CacheManager):
         ptr = self._num_free_pages
         self.free_pages_cpu_stack[ptr: ptr + n_pages] = pages
         self._num_free_pages += n_pages
+        self.page_rec[torch.from_numpy(pages.astype(np.int64)).to(self.device)] = -1
+        n_units = (n_pages + PAGE - 1) // PAGE
+        ptr = self._num_free_chunks
+        self.free_chunks_cpu_stack[ptr: ptr + n_units] = self.unit_table_cpu[row, :n_units]
+        self._num_free_chunks += n_units
+        self.unit_table_cpu[row, :] = -1
+        self.unit_table[row, :] = -1
         self.buffer_req_to_page_slots_cpu[row, :] = -1
         self.buffer_req_to_page_slots[row, :] = -1
         self.row_seq_lens[row] = 0
@@ -167,6 +214,7 @@ class QuestCacheManager(CacheManager):
             self.buffer_req_to_page_slots[torch.from_numpy(rows[new_pos]).to(self.device),
                                           torch.from_numpy(page_idx[new_pos]).to(self.device)] = \
                 torch.from_numpy(pages).to(self.device)
+            self._assign_bounds_records(rows[new_pos], page_idx[new_pos], pages)
         slots = self.buffer_req_to_page_slots_cpu[rows, page_idx].astype(np.int64) * PAGE + page_off
         slots32 = slots.astype(np.int32)
         self.buffer_req_to_token_slots[torch.from_numpy(rows).to(self.device),
@@ -226,7 +274,7 @@ class QuestCacheManager(CacheManager):
                 and slot_mapping is not None and int(k.shape[0]) == int(slot_mapping.numel())):
             k_cache, v_cache = CacheManager.get_layer_kv_cache(self, layer_idx)
             self._pending_store = (layer_idx, ops.DecodeStore(k, v, k_cache, v_cache, slot_mapping,
-                                                              self.decode_bounds_refresh == "fused"))
+                                                              self.decode_bounds_refresh == "fused", self.page_rec))
             return
         super().save_rope_kv_if_needed(layer_idx, k, v, slot_mapping)
 
@@ -235,7 +283,7 @@ class QuestCacheManager(CacheManager):
         if pend is not None:
             layer_idx, st = pend
             ops.store_kv_minmax(st.key, st.value, st.k_cache, st.v_cache, st.slot_mapping,
-                                self.bounds[self.kv_layer_index(layer_idx)] if st.refresh_bounds else None)
+                                self.bounds[self.kv_layer_index(layer_idx)] if st.refresh_bounds else None, self.page_rec)
 
     def _take_pending_store(self, layer_idx: int) -> ops.DecodeStore | None:
         if self._pending_store is None:
@@ -263,7 +311,7 @@ class QuestCacheManager(CacheManager):
         if slot_mapping is None or slot_mapping.numel() == 0 or not get_context().is_prefill:
             return
         kv_idx = self.kv_layer_index(layer_idx)
-        ops.quest_page_minmax(self.kv_cache[0, kv_idx], self.bounds[kv_idx], slot_mapping)
+        ops.quest_page_minmax(self.kv_cache[0, kv_idx], self.bounds[kv_idx], self.page_rec, slot_mapping)
 
     def on_forward_end(self, seqs, is_prefill: bool) -> None:
         """quest.py:1719-1771: after a decode step, rebuild the bounds of pages it completed (all layers)."""
@@ -271,7 +319,7 @@ class QuestCacheManager(CacheManager):
         if is_prefill or self.decode_bounds_refresh != "forward_end":
             return
         st = self.layer_batch_state
-        ops.quest_decode_page_complete(self.kv_cache[0], self.bounds, self.buffer_req_to_page_slots,
+        ops.quest_decode_page_complete(self.kv_cache[0], self.bounds, self.page_rec, self.buffer_req_to_page_slots,
                                        st.req_indices, st.context_lens)
 
     # ------------------------------------------------------------------ decode view
@@ -313,7 +361,8 @@ class QuestCacheManager(CacheManager):
         width = (prev_budget + 1) * PAGE if long_text else max_keep
         s = self._get_scratch(batch, n_cols, width)
         self._get_provider(num_heads).quest_select(
-            q, self.bounds[self.kv_layer_index(layer_idx)], self.buffer_req_to_page_slots, req_indices, context_lens, n_cols=n_cols,
+            q, self.bounds[self.kv_layer_index(layer_idx)], self.unit_table, self.buffer_req_to_page_slots, req_indices,
+            context_lens, n_cols=n_cols,
             num_kv_heads=self.num_kv_heads, prev_budget=prev_budget, scores=s.scores, packed_slots=s.packed,
             sparse_lens=s.lens, tickets=s.tickets,
             dense_token_table=None if long_text else self.buffer_req_to_token_slots,

@@ -2,6 +2,7 @@
 // validation, error reporting, dispatch to the kernel launchers.  No torch types.
 #include <stdarg.h>
 #include <stdio.h>
+#include <string.h>
 
 #include "../../include/svb200.h"
 #include "launch.h"
@@ -38,10 +39,15 @@ int sm_count() {
   return cached;
 }
 
+#ifndef SVB200_PDL_DEFAULT
+#define SVB200_PDL_DEFAULT 0
+#endif
 static unsigned long long* g_dbg_times = nullptr;
 unsigned long long* debug_times_buffer() { return g_dbg_times; }
 static int g_tuning[kTuneCount] = {0};
 int tuning(int which) { return (which >= 0 && which < kTuneCount) ? g_tuning[which] : 0; }
+// programmatic dependent launch (knob 7: 1 = on, 2 = off, 0 = the build's default)
+bool pdl_enabled() { return g_tuning[kTunePdl] != 2 && (g_tuning[kTunePdl] == 1 || SVB200_PDL_DEFAULT); }
 static int g_max_ctas = 0;
 int max_ctas() {
   const int n = sm_count();
@@ -105,71 +111,77 @@ int64_t svb200_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_k
   return ws_ticket_bytes(batch, num_kv_heads) + (int64_t)sm_count() * ws_cta_bytes(num_q_heads);
 }
 
-int svb200_quest_page_minmax(const void* k_cache, void* bounds_layer, const int32_t* slot_mapping,
+int svb200_quest_page_minmax(const void* k_cache, void* bounds_layer, int64_t num_chunks,
+                             const int32_t* page_rec, const int32_t* slot_mapping,
                              int32_t n_tokens, int32_t num_kv_heads, int64_t num_slots,
                              void* stream) {
   SV_REQUIRE(n_tokens >= 0, "quest_page_minmax: n_tokens=%d < 0", n_tokens);
   if (n_tokens == 0) return 0;
-  SV_REQUIRE(k_cache && bounds_layer && slot_mapping, "quest_page_minmax: null pointer");
+  SV_REQUIRE(k_cache && bounds_layer && slot_mapping && page_rec, "quest_page_minmax: null pointer");
+  SV_REQUIRE(num_chunks > 0 && num_chunks <= (INT32_MAX >> 4), "quest_page_minmax: num_chunks=%lld out of range", (long long)num_chunks);
   SV_REQUIRE(aligned16(k_cache) && aligned16(bounds_layer), "quest_page_minmax: buffers must be 16-byte aligned");
   SV_REQUIRE(num_kv_heads > 0 && num_slots > 0 && num_slots % SVB200_PAGE == 0,
              "quest_page_minmax: num_kv_heads=%d num_slots=%lld (must be a positive multiple of 16)",
              num_kv_heads, (long long)num_slots);
-  return launch_quest_page_minmax(k_cache, bounds_layer, slot_mapping, n_tokens, num_kv_heads,
-                                  num_slots, (cudaStream_t)stream);
+  return launch_quest_page_minmax(k_cache, bounds_layer, page_rec, slot_mapping, n_tokens, num_kv_heads,
+                                  num_slots, num_chunks, (cudaStream_t)stream);
 }
 
-int svb200_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
+int svb200_quest_decode_page_complete(const void* k_cache_all, void* bounds_all, int64_t num_chunks,
+                                      const int32_t* page_rec,
                                       const int32_t* page_table, int64_t page_table_stride,
                                       const int32_t* req_rows, const int32_t* seq_lens,
                                       int32_t batch, int32_t num_layers, int32_t num_kv_heads,
                                       int64_t num_slots, int64_t num_pages, void* stream) {
   SV_REQUIRE(batch >= 0 && num_layers >= 0, "quest_decode_page_complete: negative batch/layers");
   if (batch == 0 || num_layers == 0) return 0;
-  SV_REQUIRE(k_cache_all && bounds_all && page_table && req_rows && seq_lens,
+  SV_REQUIRE(k_cache_all && bounds_all && page_table && req_rows && seq_lens && page_rec,
              "quest_decode_page_complete: null pointer");
+  SV_REQUIRE(num_chunks > 0 && num_chunks <= (INT32_MAX >> 4), "quest_decode_page_complete: num_chunks=%lld out of range", (long long)num_chunks);
   SV_REQUIRE(aligned16(k_cache_all) && aligned16(bounds_all), "quest_decode_page_complete: buffers must be 16-byte aligned");
   SV_REQUIRE(num_kv_heads > 0 && num_slots == num_pages * SVB200_PAGE && page_table_stride > 0,
              "quest_decode_page_complete: num_slots=%lld must equal 16*num_pages=%lld",
              (long long)num_slots, (long long)num_pages);
   SV_REQUIRE(num_layers <= 65535, "quest_decode_page_complete: num_layers=%d > 65535", num_layers);
-  return launch_quest_decode_page_complete(k_cache_all, bounds_all, page_table, page_table_stride,
+  return launch_quest_decode_page_complete(k_cache_all, bounds_all, page_rec, page_table, page_table_stride,
                                            req_rows, seq_lens, batch, num_layers, num_kv_heads,
-                                           num_slots, num_pages, (cudaStream_t)stream);
+                                           num_slots, num_pages, num_chunks, (cudaStream_t)stream);
 }
 
 static int check_score_args(const char* who, const void* q, int64_t q_stride_b, const void* bounds,
-                            int64_t num_pages, const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
+                            int64_t num_chunks, const int32_t* unit_table, int64_t ut_stride, const int32_t* req_rows,
                             const int32_t* ctx, const void* scores, int64_t score_stride,
                             int batch, int hq, int hkv, int n_cols) {
-  SV_REQUIRE(q && bounds && page_table && req_rows && ctx && scores, "%s: null pointer", who);
+  SV_REQUIRE(q && bounds && unit_table && req_rows && ctx && scores, "%s: null pointer", who);
   SV_REQUIRE(aligned16(q) && aligned16(bounds) && aligned16(scores), "%s: q/bounds/scores must be 16-byte aligned", who);
   if (int rc = check_heads(who, hq, hkv)) return rc;
   SV_REQUIRE(q_stride_b >= (int64_t)hq * SVB200_HEAD_DIM && q_stride_b % 8 == 0,
              "%s: q_stride_b=%lld too small or not a multiple of 8", who, (long long)q_stride_b);
-  SV_REQUIRE(n_cols > 0 && pt_stride >= n_cols + 1, "%s: page table stride %lld must cover n_cols+1=%d pages",
-             who, (long long)pt_stride, n_cols + 1);
+  SV_REQUIRE(n_cols > 0 && ut_stride * SVB200_PAGE >= n_cols, "%s: unit table stride %lld must cover n_cols=%d pages",
+             who, (long long)ut_stride, n_cols);
+  // the selection scans tie counts in 16-bit lanes of one word
+  SV_SUPPORTED(n_cols < 32768, "%s: n_cols=%d >= 32768 pages (contexts of 512K tokens and more) is not supported", who, n_cols);
   SV_REQUIRE(score_stride >= ((n_cols + 7) / 8) * 8 && score_stride % 8 == 0,
              "%s: score_stride=%lld must be a multiple of 8 covering n_cols=%d", who,
              (long long)score_stride, n_cols);
-  SV_REQUIRE(num_pages > 0, "%s: num_pages=%lld must be positive", who, (long long)num_pages);
+  SV_REQUIRE(num_chunks > 0, "%s: num_chunks=%lld must be positive", who, (long long)num_chunks);
   SV_REQUIRE(batch <= 8192, "%s: batch=%d > 8192", who, batch);
   return 0;
 }
 
 int svb200_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds_layer,
-                            int64_t num_pages, const int32_t* page_table, int64_t page_table_stride,
+                            int64_t num_chunks, const int32_t* unit_table, int64_t unit_table_stride,
                             const int32_t* req_rows, const int32_t* context_lens, void* scores,
                             int64_t score_stride, int32_t batch, int32_t num_q_heads,
                             int32_t num_kv_heads, int32_t n_cols, int32_t* sched_scratch, void* stream) {
   SV_REQUIRE(batch >= 0, "quest_page_score: batch=%d < 0", batch);
   if (batch == 0) return 0;
   SV_REQUIRE(sched_scratch != nullptr, "quest_page_score: sched_scratch is null");
-  if (int rc = check_score_args("quest_page_score", q, q_stride_b, bounds_layer, num_pages, page_table,
-                                page_table_stride, req_rows, context_lens, scores, score_stride,
+  if (int rc = check_score_args("quest_page_score", q, q_stride_b, bounds_layer, num_chunks, unit_table,
+                                unit_table_stride, req_rows, context_lens, scores, score_stride,
                                 batch, num_q_heads, num_kv_heads, n_cols))
     return rc;
-  return launch_quest_page_score(q, q_stride_b, bounds_layer, num_pages, page_table, page_table_stride,
+  return launch_quest_page_score(q, q_stride_b, bounds_layer, num_chunks, unit_table, unit_table_stride,
                                  req_rows, context_lens, scores, score_stride, batch, num_q_heads,
                                  num_kv_heads, n_cols, sched_scratch, (cudaStream_t)stream);
 }
@@ -198,6 +210,7 @@ int svb200_quest_select_pack(const void* scores, int64_t score_stride, int32_t n
   SV_REQUIRE(aligned16(scores) && score_stride % 8 == 0 && score_stride >= ((n_cols + 7) / 8) * 8,
              "quest_select_pack: scores must be 16-byte aligned with stride multiple of 8 covering n_cols");
   SV_REQUIRE(n_cols > 0 && page_table_stride >= n_cols + 1, "quest_select_pack: page table stride must cover n_cols+1 pages");
+  SV_SUPPORTED(n_cols < 32768, "quest_select_pack: n_cols=%d >= 32768 pages is not supported", n_cols);
   if (int rc = check_select_args("quest_select_pack", n_cols, prev_budget, packed_slots, out_stride, sparse_lens)) return rc;
   if (dense_token_table != nullptr) {
     SV_REQUIRE(out_width >= (prev_budget + 1) * SVB200_PAGE && out_stride >= out_width && dense_table_stride >= out_width,
@@ -211,7 +224,8 @@ int svb200_quest_select_pack(const void* scores, int64_t score_stride, int32_t n
 }
 
 int svb200_quest_score_select_pack(const void* q, int64_t q_stride_b, const void* bounds_layer,
-                                   int64_t num_pages, const int32_t* page_table, int64_t page_table_stride,
+                                   int64_t num_chunks, const int32_t* unit_table, int64_t unit_table_stride,
+                                   const int32_t* page_table, int64_t page_table_stride,
                                    const int32_t* req_rows, const int32_t* context_lens,
                                    void* scores, int64_t score_stride, int32_t batch,
                                    int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols,
@@ -220,13 +234,16 @@ int svb200_quest_score_select_pack(const void* q, int64_t q_stride_b, const void
                                    void* stream) {
   SV_REQUIRE(batch >= 0, "quest_score_select_pack: batch=%d < 0", batch);
   if (batch == 0) return 0;
-  if (int rc = check_score_args("quest_score_select_pack", q, q_stride_b, bounds_layer, num_pages, page_table,
-                                page_table_stride, req_rows, context_lens, scores, score_stride,
+  if (int rc = check_score_args("quest_score_select_pack", q, q_stride_b, bounds_layer, num_chunks, unit_table,
+                                unit_table_stride, req_rows, context_lens, scores, score_stride,
                                 batch, num_q_heads, num_kv_heads, n_cols))
     return rc;
   if (int rc = check_select_args("quest_score_select_pack", n_cols, prev_budget, packed_slots, out_stride, sparse_lens)) return rc;
   SV_REQUIRE(tickets != nullptr, "quest_score_select_pack: tickets scratch is null");
-  return launch_quest_score_select_pack(q, q_stride_b, bounds_layer, num_pages, page_table, page_table_stride,
+  SV_REQUIRE(page_table && page_table_stride >= n_cols + 1, "quest_score_select_pack: page table (stride %lld) must cover n_cols+1=%d pages",
+             (long long)page_table_stride, n_cols + 1);
+  return launch_quest_score_select_pack(q, q_stride_b, bounds_layer, num_chunks, unit_table, unit_table_stride,
+                                        page_table, page_table_stride,
                                         req_rows, context_lens, scores, score_stride, batch,
                                         num_q_heads, num_kv_heads, n_cols, prev_budget,
                                         packed_slots, out_stride, sparse_lens, selected_pages,
@@ -235,9 +252,10 @@ int svb200_quest_score_select_pack(const void* q, int64_t q_stride_b, const void
 
 int svb200_quest_store_score_select_pack(const void* key, int64_t k_stride, const void* value, int64_t v_stride,
                                          void* k_cache, void* v_cache, const int32_t* slot_mapping,
-                                         int64_t num_slots, int32_t refresh_bounds,
+                                         int64_t num_slots, int32_t refresh_bounds, const int32_t* page_rec,
                                          const void* q, int64_t q_stride_b, void* bounds_layer,
-                                         int64_t num_pages, const int32_t* page_table, int64_t page_table_stride,
+                                         int64_t num_chunks, const int32_t* unit_table, int64_t unit_table_stride,
+                                         const int32_t* page_table, int64_t page_table_stride,
                                          const int32_t* req_rows, const int32_t* context_lens,
                                          void* scores, int64_t score_stride, int32_t batch,
                                          int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols,
@@ -247,39 +265,53 @@ int svb200_quest_store_score_select_pack(const void* key, int64_t k_stride, cons
   const char* who = "quest_store_score_select_pack";
   SV_REQUIRE(batch >= 0, "%s: batch=%d < 0", who, batch);
   if (batch == 0) return 0;
-  if (int rc = check_score_args(who, q, q_stride_b, bounds_layer, num_pages, page_table,
-                                page_table_stride, req_rows, context_lens, scores, score_stride,
+  if (int rc = check_score_args(who, q, q_stride_b, bounds_layer, num_chunks, unit_table,
+                                unit_table_stride, req_rows, context_lens, scores, score_stride,
                                 batch, num_q_heads, num_kv_heads, n_cols))
     return rc;
   if (int rc = check_select_args(who, n_cols, prev_budget, packed_slots, out_stride, sparse_lens)) return rc;
   SV_REQUIRE(tickets != nullptr, "%s: tickets scratch is null", who);
+  SV_REQUIRE(page_table && page_table_stride >= n_cols + 1, "%s: page table (stride %lld) must cover n_cols+1=%d pages", who,
+             (long long)page_table_stride, n_cols + 1);
+  SV_REQUIRE(!refresh_bounds || page_rec, "%s: refresh_bounds needs page_rec", who);
   SV_REQUIRE(key && value && k_cache && v_cache && slot_mapping, "%s: null store pointer", who);
   SV_REQUIRE(aligned16(key) && aligned16(value) && aligned16(k_cache) && aligned16(v_cache),
              "%s: key/value/caches must be 16-byte aligned", who);
   SV_REQUIRE(k_stride >= (int64_t)num_kv_heads * SVB200_HEAD_DIM && k_stride % 8 == 0 &&
                  v_stride >= (int64_t)num_kv_heads * SVB200_HEAD_DIM && v_stride % 8 == 0,
              "%s: bad key/value token strides %lld/%lld", who, (long long)k_stride, (long long)v_stride);
-  SV_REQUIRE(num_slots > 0 && (!refresh_bounds || num_slots == num_pages * SVB200_PAGE),
-             "%s: num_slots=%lld must be positive (and num_pages*%d with refresh_bounds)", who, (long long)num_slots, SVB200_PAGE);
-  const FusedStore st{key, k_stride, value, v_stride, k_cache, v_cache, slot_mapping, num_slots, refresh_bounds};
-  return launch_quest_score_select_pack(q, q_stride_b, bounds_layer, num_pages, page_table, page_table_stride,
+  SV_REQUIRE(num_slots > 0 && (!refresh_bounds || num_slots % SVB200_PAGE == 0),
+             "%s: num_slots=%lld must be positive (and a multiple of %d with refresh_bounds)", who, (long long)num_slots, SVB200_PAGE);
+  const FusedStore st{key, k_stride, value, v_stride, k_cache, v_cache, slot_mapping, num_slots, refresh_bounds, page_rec};
+  return launch_quest_score_select_pack(q, q_stride_b, bounds_layer, num_chunks, unit_table, unit_table_stride,
+                                        page_table, page_table_stride,
                                         req_rows, context_lens, scores, score_stride, batch,
                                         num_q_heads, num_kv_heads, n_cols, prev_budget,
                                         packed_slots, out_stride, sparse_lens, selected_pages,
                                         tickets, &st, (cudaStream_t)stream);
 }
 
-int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_cache,
-                              const void* v_cache, int64_t num_slots, const int32_t* slot_table,
-                              int64_t slot_table_stride, int32_t max_len, const int32_t* req_rows,
-                              const int32_t* seq_lens, void* out, int64_t out_stride_b,
-                              float* attn_score, int64_t score_stride, int32_t batch,
-                              int32_t num_q_heads, int32_t num_kv_heads, int32_t heads_per_cta,
-                              void* workspace, int64_t workspace_bytes, float sm_scale,
-                              void* stream) {
-  const char* who = "sparse_decode_attn";
+static int check_comm(const char* who, const svb200_comm_t* comm) {
+  SV_REQUIRE(comm->world >= 1 && comm->world <= SVB200_MAX_PEERS && comm->rank >= 0 && comm->rank < comm->world,
+             "%s: comm world=%d rank=%d (world must be 1..%d)", who, comm->world, comm->rank, SVB200_MAX_PEERS);
+  for (int r = 0; r < comm->world; ++r)
+    SV_REQUIRE(comm->peer_buf[r] && comm->peer_sync[r] && aligned16(comm->peer_buf[r]),
+               "%s: comm peer %d has a null / unaligned buffer", who, r);
+  return 0;
+}
+
+static int decode_attn_impl(const char* who, const void* q, int64_t q_stride_b, const void* k_cache,
+                            const void* v_cache, int64_t num_slots, const int32_t* slot_table,
+                            int64_t slot_table_stride, int32_t max_len, const int32_t* req_rows,
+                            const int32_t* seq_lens, void* out, int64_t out_stride_b,
+                            float* attn_score, int64_t score_stride, int32_t batch,
+                            int32_t num_q_heads, int32_t num_kv_heads, int32_t heads_per_cta,
+                            void* workspace, int64_t workspace_bytes, float sm_scale,
+                            const svb200_comm_t* comm, int64_t gather_offset_bytes, int64_t gather_stride_b,
+                            void* stream) {
   SV_REQUIRE(batch >= 0, "%s: batch=%d < 0", who, batch);
-  if (batch == 0) return 0;
+  if (batch == 0 && (comm == nullptr || comm->world <= 1)) return 0;
+  SV_REQUIRE(batch > 0, "%s: an empty batch cannot take part in the tensor-parallel push", who);
   SV_REQUIRE(q && k_cache && v_cache && slot_table && req_rows && seq_lens && out, "%s: null pointer", who);
   SV_REQUIRE(aligned16(q) && aligned16(k_cache) && aligned16(v_cache) && aligned16(out), "%s: q/k/v/out must be 16-byte aligned", who);
   if (int rc = check_heads(who, num_q_heads, num_kv_heads)) return rc;
@@ -308,7 +340,111 @@ int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_c
   p.tickets = reinterpret_cast<int32_t*>(w);
   p.ws_lse = reinterpret_cast<float*>(w + tk);
   p.ws_o = reinterpret_cast<float*>(w + tk + ctas * 2 * num_q_heads * 4 * (int64_t)sizeof(float));
+  p.no_math = 0;
+  p.granule = 1;
+  p.push = PushArgs{};
+  if (comm != nullptr && comm->world > 1) {
+    if (int rc = check_comm(who, comm)) return rc;
+    SV_REQUIRE(gather_offset_bytes >= 0 && gather_offset_bytes % 16 == 0 &&
+                   gather_stride_b >= (int64_t)comm->world * num_q_heads * SVB200_HEAD_DIM && gather_stride_b % 8 == 0,
+               "%s: gathered buffer offset %lld / row stride %lld (needs 16-byte alignment and >= world*Hq*128 elements per row)",
+               who, (long long)gather_offset_bytes, (long long)gather_stride_b);
+    p.push.world = comm->world;
+    p.push.rank = comm->rank;
+    p.push.stride_b = gather_stride_b;
+    for (int r = 0; r < comm->world; ++r) {
+      p.push.out[r] = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(comm->peer_buf[r]) + gather_offset_bytes);
+      p.push.sync[r] = comm->peer_sync[r];
+    }
+  }
   return launch_sparse_decode_attn(p, heads_per_cta, (cudaStream_t)stream);
+}
+
+int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_cache,
+                              const void* v_cache, int64_t num_slots, const int32_t* slot_table,
+                              int64_t slot_table_stride, int32_t max_len, const int32_t* req_rows,
+                              const int32_t* seq_lens, void* out, int64_t out_stride_b,
+                              float* attn_score, int64_t score_stride, int32_t batch,
+                              int32_t num_q_heads, int32_t num_kv_heads, int32_t heads_per_cta,
+                              void* workspace, int64_t workspace_bytes, float sm_scale,
+                              void* stream) {
+  return decode_attn_impl("sparse_decode_attn", q, q_stride_b, k_cache, v_cache, num_slots, slot_table,
+                          slot_table_stride, max_len, req_rows, seq_lens, out, out_stride_b, attn_score,
+                          score_stride, batch, num_q_heads, num_kv_heads, heads_per_cta, workspace,
+                          workspace_bytes, sm_scale, nullptr, 0, 0, stream);
+}
+
+int svb200_sparse_decode_attn_tp(const void* q, int64_t q_stride_b, const void* k_cache,
+                                 const void* v_cache, int64_t num_slots, const int32_t* slot_table,
+                                 int64_t slot_table_stride, int32_t max_len, const int32_t* req_rows,
+                                 const int32_t* seq_lens, void* out, int64_t out_stride_b,
+                                 float* attn_score, int64_t score_stride, int32_t batch,
+                                 int32_t num_q_heads, int32_t num_kv_heads, int32_t heads_per_cta,
+                                 void* workspace, int64_t workspace_bytes, float sm_scale,
+                                 const svb200_comm_t* comm, int64_t gather_offset_bytes,
+                                 int64_t gather_stride_b, void* stream) {
+  const char* who = "sparse_decode_attn_tp";
+  SV_REQUIRE(comm != nullptr, "%s: comm is null", who);
+  return decode_attn_impl(who, q, q_stride_b, k_cache, v_cache, num_slots, slot_table,
+                          slot_table_stride, max_len, req_rows, seq_lens, out, out_stride_b, attn_score,
+                          score_stride, batch, num_q_heads, num_kv_heads, heads_per_cta, workspace,
+                          workspace_bytes, sm_scale, comm, gather_offset_bytes, gather_stride_b, stream);
+}
+
+int svb200_allreduce_sum_bf16(const svb200_comm_t* comm, int64_t in_offset_bytes, int64_t n_elems,
+                              void* out, void* stream) {
+  const char* who = "allreduce_sum_bf16";
+  SV_REQUIRE(comm != nullptr && out != nullptr, "%s: null pointer", who);
+  if (int rc = check_comm(who, comm)) return rc;
+  SV_REQUIRE(n_elems >= 0 && n_elems % 8 == 0 && in_offset_bytes >= 0 && in_offset_bytes % 16 == 0 && aligned16(out),
+             "%s: n_elems=%lld must be a multiple of 8, offsets / out 16-byte aligned", who, (long long)n_elems);
+  if (n_elems == 0) return 0;
+  AllReduceArgs a{};
+  a.world = comm->world;
+  a.rank = comm->rank;
+  for (int r = 0; r < comm->world; ++r) {
+    a.in[r] = reinterpret_cast<const __nv_bfloat16*>(static_cast<const char*>(comm->peer_buf[r]) + in_offset_bytes);
+    a.sync[r] = comm->peer_sync[r];
+  }
+  a.out = static_cast<__nv_bfloat16*>(out);
+  a.n = n_elems;
+  return launch_allreduce_sum_bf16(a, (cudaStream_t)stream);
+}
+
+/* ---- peer-mapped ("symmetric") memory: plain cudaMalloc + CUDA IPC handles ---- */
+int svb200_symm_alloc(int64_t bytes, void** ptr_host, void* handle64_host) {
+  SV_REQUIRE(bytes > 0 && ptr_host && handle64_host, "symm_alloc: bad arguments");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, (size_t)bytes);
+  if (e != cudaSuccess) return cuda_error("symm_alloc cudaMalloc", e);
+  e = cudaMemset(p, 0, (size_t)bytes);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(static_cast<cudaIpcMemHandle_t*>(handle64_host), p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return cuda_error("symm_alloc", e);
+  }
+  *ptr_host = p;
+  return 0;
+}
+int svb200_symm_free(void* ptr) {
+  const cudaError_t e = cudaFree(ptr);
+  return e == cudaSuccess ? 0 : cuda_error("symm_free", e);
+}
+int svb200_ipc_open(const void* handle64_host, void** ptr_host) {
+  SV_REQUIRE(handle64_host && ptr_host, "ipc_open: null pointer");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64_host, sizeof(h));
+  void* p = nullptr;
+  const cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) return cuda_error("ipc_open", e);
+  *ptr_host = p;
+  return 0;
+}
+int svb200_ipc_close(void* ptr) {
+  const cudaError_t e = cudaIpcCloseMemHandle(ptr);
+  return e == cudaSuccess ? 0 : cuda_error("ipc_close", e);
 }
 
 int svb200_h2o_normalize_accumulate(float* score, int64_t score_stride, int32_t batch,
@@ -342,7 +478,8 @@ int svb200_h2o_select_compact(float* cumulative, const int64_t* cum_rows, int32_
 int svb200_store_kv_minmax(const void* key, int64_t k_stride, const void* value, int64_t v_stride,
                            void* k_cache, void* v_cache, const int32_t* slot_mapping,
                            int32_t n_tokens, int32_t num_kv_heads, int64_t num_slots,
-                           void* quest_bounds_layer, void* stream) {
+                           void* quest_bounds_layer, const int32_t* page_rec, int64_t num_chunks,
+                           void* stream) {
   SV_REQUIRE(n_tokens >= 0, "store_kv_minmax: n_tokens=%d < 0", n_tokens);
   if (n_tokens == 0) return 0;
   SV_REQUIRE(key && value && k_cache && v_cache && slot_mapping, "store_kv_minmax: null pointer");
@@ -353,9 +490,10 @@ int svb200_store_kv_minmax(const void* key, int64_t k_stride, const void* value,
              "store_kv_minmax: bad key/value token strides %lld/%lld", (long long)k_stride, (long long)v_stride);
   SV_REQUIRE(num_slots > 0, "store_kv_minmax: num_slots must be positive");
   if (quest_bounds_layer != nullptr)
-    SV_REQUIRE(aligned16(quest_bounds_layer) && num_slots % SVB200_PAGE == 0, "store_kv_minmax: bounds need 16-byte alignment and paged slots");
+    SV_REQUIRE(aligned16(quest_bounds_layer) && num_slots % SVB200_PAGE == 0 && page_rec && num_chunks > 0,
+               "store_kv_minmax: bounds need 16-byte alignment, paged slots, page_rec and num_chunks");
   return launch_store_kv_minmax(key, k_stride, value, v_stride, k_cache, v_cache, slot_mapping,
-                                n_tokens, num_kv_heads, num_slots, quest_bounds_layer,
+                                n_tokens, num_kv_heads, num_slots, quest_bounds_layer, page_rec, num_chunks,
                                 (cudaStream_t)stream);
 }
 

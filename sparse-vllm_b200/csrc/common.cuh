@@ -83,18 +83,21 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug traps after ~2 s instead of hanging the GPU.
+// Bounded wait: a protocol bug traps instead of hanging the GPU.  The bound counts failed polls (each
+// try_wait suspends the thread for a hardware time slice), not wall time: %globaltimer keeps running while
+// a context is preempted, time-sliced or stopped under a debugger / profiler replay, and a correct launch
+// must survive that.
 __device__ __forceinline__ uint64_t global_timer_ns() {
   uint64_t t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
+constexpr uint32_t kSpinLimit = 1u << 26;
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
-  const uint64_t t0 = global_timer_ns();
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > 2000000000ull) __trap();
+    if (++spins > kSpinLimit) __trap();
   }
 }
 // 1-D bulk async copy global -> shared::cta, completion counted on an mbarrier.
@@ -137,6 +140,26 @@ __device__ __forceinline__ uint32_t movmatrix_trans(uint32_t x) {
   uint32_t y;
   asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(y) : "r"(x));
   return y;
+}
+
+// ------------------------------------------------- programmatic dependent launch ----
+// A kernel launched with the programmatic-stream-serialization attribute may start while its
+// predecessor in the stream is still running; pdl_wait() blocks until the predecessor has completed and
+// its writes are visible (a no-op for a normal launch).  Every CTA calls it before it touches global
+// memory, so completion stays transitive along a chain of such launches.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+// ------------------------------------------------------- system-scope flags ----
+__device__ __forceinline__ void st_release_sys(int32_t* p, int32_t v) {
+  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
+  int32_t v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
 }
 
 // ------------------------------------------------------------- misc ----

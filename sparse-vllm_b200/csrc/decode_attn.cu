@@ -15,15 +15,24 @@
 // directly; otherwise it publishes one fp32 partial (at most two per CTA) and
 // the last contributor of the row (arrival ticket) merges them.
 //
-// Inside a CTA: warps 8-11 are producers.  A producer reads 16 token slots and copies
-// each token's HPC*256 contiguous bytes of K and of V with 16-byte LDGSTS (a whole
-// warp per 512 B, masked tokens zero-filled) into a ring of S stages whose mbarriers
-// complete when the copies land (S * stage bytes ~ 160-190 KB in flight per SM).
-// (A first version issued one UBLKCP bulk copy per token row: the per-lane operands
-// serialise through uniform registers at ~110 cycles per copy and capped the kernel at
-// 2.5 TB/s, profiles/r1_b_*.)  Warps 0-7 are consumers: warp (h, tl) owns KV head h
-// and every TL-th unit: S^T(16 tok x 8 heads) = K Q^T on tensor cores, fp32 online
-// softmax with warp shuffles, O^T(128 x 8) += V^T P^T.
+// Inside a CTA: warps 8-11 are producers.  A producer reads 16 token slots (prefetched kSlotPrefetch
+// units ahead) and issues bulk async copies (cp.async.bulk, SASS UBLKCP) into a ring of S stages whose
+// mbarriers count the bytes (S * stage bytes ~ 160-190 KB in flight per SM): lanes 0-15 copy K, lanes
+// 16-31 V.  A copy moves a *granule* of GRAN consecutive token rows when their slots are consecutive
+// (a Quest page is 16 consecutive slots) and the CTA stages every local KV head (HPC == Hkv: token rows
+// are then contiguous in the cache), else one token row (HPC*256 bytes).  GRAN is chosen so that a copy
+// is >= 1 KB: the copy engine issues one bulk copy per ~30-45 cycles per SM whatever its size, so 256-byte
+// copies (one KV head per rank under TP 8) capped the launch at 1.6 TB/s.  Granules sit 16 bytes apart
+// modulo 128 in shared memory and the mma tile's rows are a fixed permutation of the unit's tokens
+// (row_tok) so that ldmatrix still hits distinct banks (two-way conflicts at GRAN 4).
+// Warps 0-7 are consumers: warp (h, tl) owns KV head h and every TL-th unit: S^T(16 tok x 8 heads) =
+// K Q^T on tensor cores (mma.sync m16n8k16 bf16, fp32 accumulate), fp32 online softmax with warp
+// shuffles, O^T(128 x 8) += V^T P^T.
+//
+// Tensor parallelism (push epilogue): with a svb200_comm_t the final bf16 rows are also written into
+// every rank's gathered [B][world*Hq][128] buffer over NVLink (peer stores), and the last CTA of the
+// launch signals the peers and waits for theirs: when the launch completes, the all-gather of the head
+// shards has completed as well (no NCCL launch per layer).
 #include "common.cuh"
 #include "launch.h"
 
@@ -42,9 +51,16 @@ template <int HPC>
 struct AttnGeom {
   static constexpr int TL = kConsumerWarps / HPC;    // consumer warps per KV head
   static constexpr int TOK_BYTES = HPC * kRowBytes;   // one token's head-group row
-  static constexpr int TOK_STRIDE = TOK_BYTES + 16;   // +16: ldmatrix rows hit distinct banks
-  static constexpr int KV_BYTES = kPage * TOK_STRIDE;  // one tensor of one stage
+  static constexpr int GRAN = HPC == 1 ? 4 : (HPC == 2 ? 2 : 1);  // token rows per copy granule (>= 1 KB)
+  static constexpr int GSTRIDE = GRAN * TOK_BYTES + 16;  // +16: granules (ldmatrix rows) hit distinct banks
+  static constexpr int KV_BYTES = (kPage / GRAN) * GSTRIDE;  // one tensor of one stage
   static constexpr int STAGE_BYTES = 2 * KV_BYTES;    // K then V
+  // byte offset of token `tok` (0..15) inside a stage's K (or V) part
+  __device__ static __forceinline__ int tok_off(int tok) { return (tok / GRAN) * GSTRIDE + (tok % GRAN) * TOK_BYTES; }
+  // token held by row r of the 16-row mma tile: rows 0-7 (one ldmatrix phase) come from distinct granules
+  __device__ static __forceinline__ int row_tok(int r) {
+    return GRAN == 1 ? r : (GRAN == 2 ? 2 * (r & 7) + (r >> 3) : 4 * (r & 3) + (r >> 2));
+  }
 };
 
 // consumer-only barrier (the producer warp never joins)
@@ -58,6 +74,31 @@ __device__ __forceinline__ void fence_proxy_async() {
 // CTA that owns unit u when U units are cut into G ranges [U*c/G, U*(c+1)/G).
 __device__ __forceinline__ int unit_owner(int64_t u, int64_t U, int64_t G) {
   return (int)(((u + 1) * G + U - 1) / U - 1);
+}
+
+// ---- tensor-parallel push epilogue (see the file header)
+// Called by ONE thread per CTA (every CTA of the grid, exactly once) after the CTA's peer stores were
+// fenced (__threadfence_system by the writers) and a CTA barrier.  The last CTA to arrive bumps the epoch,
+// raises this rank's flag on every peer and waits for the peers' flags: the launch does not complete
+// before every rank's rows have landed here.  Flags only grow, peers can be at most one launch ahead.
+__device__ void push_finish(const PushArgs& ps) {
+  int32_t* local = ps.sync[ps.rank];
+  __threadfence_system();
+  if (atomicAdd(local + kSyncDone, 1) != (int)gridDim.x - 1) return;
+  local[kSyncDone] = 0;
+  __threadfence_system();
+  const int32_t e = local[kSyncEpoch] + 1;
+  local[kSyncEpoch] = e;
+  for (int r = 0; r < ps.world; ++r)
+    if (r != ps.rank) st_release_sys(ps.sync[r] + ps.rank, e);
+  for (int r = 0; r < ps.world; ++r) {
+    if (r == ps.rank) continue;
+    uint32_t spins = 0;
+    while (ld_acquire_sys(local + r) - e < 0) {
+      __nanosleep(32);
+      if (++spins > kSpinLimit) __trap();
+    }
+  }
 }
 
 struct AttnSmemLayout {
@@ -117,6 +158,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
     }
     mbar_fence_init();
   }
+  pdl_wait();
+  const bool push = p.push.world > 1;
   if (warp == 0) {
     int carry = 0;
     for (int base = 0; base < R; base += 32) {
@@ -143,16 +186,28 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
       uint4* o4 = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) +
                                            (int64_t)b * p.out_stride_b);
       for (int i = tid; i < p.hq * 16; i += kAttnThreads) o4[i] = make_uint4(0, 0, 0, 0);
+      if (push) {
+        for (int r = 0; r < p.push.world; ++r) {
+          uint4* g4 = reinterpret_cast<uint4*>(p.push.out[r] + (int64_t)b * p.push.stride_b +
+                                               (int64_t)p.push.rank * p.hq * kHeadDim);
+          for (int i = tid; i < p.hq * 16; i += kAttnThreads) g4[i] = make_uint4(0, 0, 0, 0);
+        }
+        __threadfence_system();
+      }
     }
   }
   __syncthreads();
+  pdl_launch_dependents();
 
   if (dbg && tid == 0) dbg[1] = global_timer_ns();
   const int64_t U = sPrefix[R];
   // never more ranges than units: every range is non-empty, so the contributors of a
   // row are exactly the CTAs unit_owner(first unit) .. unit_owner(last unit)
   const int64_t Gn = U < (int64_t)gridDim.x ? U : (int64_t)gridDim.x;
-  if ((int64_t)blockIdx.x >= Gn) return;
+  if ((int64_t)blockIdx.x >= Gn) {
+    if (push && tid == 0) push_finish(p.push);
+    return;
+  }
   const int u0 = (int)(U * blockIdx.x / Gn), u1 = (int)(U * (blockIdx.x + 1) / Gn);
   // first row of the range: largest r with prefix[r] <= u0 and a non-empty row
   int r_first;
@@ -171,11 +226,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
 
   if (warp >= kConsumerWarps) {
     // ============================================================== producers
-    // Producer warp pw feeds every kProducerWarps-th unit.  Lane t < 16 holds the slot of
-    // token t (fetched two units ahead so the table's DRAM latency hides behind the wait
-    // for a free stage); each token row (HPC*256 contiguous bytes of K, same of V) is
-    // copied by the whole warp with 16-byte LDGSTS (512 B per instruction), masked tokens
-    // zero-filled.  Every lane's copies arrive on the stage's mbarrier when they land.
+    // Producer warp pw feeds every NP-th unit.  Lane t (and t + 16) holds the slot of token t, fetched
+    // kSlotPrefetch units of this warp ahead so the table's DRAM latency hides behind queued copies.
     // Unit i is fed by producer i % NP with NP | S: a stage is always refilled by the same warp, so
     // the empty-phase it waits for is never more than one ahead of the barrier (same parity
     // argument as for the consumers).
@@ -205,11 +257,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
       if (t >= len_pf) return -1;
       return __ldg(row_pf + t);
     };
-    constexpr int LPR = G::TOK_BYTES >= 512 ? 32 : G::TOK_BYTES / 16;  // lanes per token row
-    constexpr int TPI = 32 / LPR;                                     // tokens per instruction
-    constexpr int CPR = G::TOK_BYTES / (LPR * 16);                    // instructions per row
-    const int sub = lane / LPR, chunk = lane % LPR;
     const int64_t slot_bytes = slot_elems * 2;
+    // granule copies need the GRAN token rows contiguous in the cache: every local KV head staged together
+    const bool gran_ok = G::GRAN > 1 && p.hkv == HPC && p.granule;
     int r_is = r_first, hg_is = r_first % HG;  // issue cursor
     int s = pw % S;
     uint32_t ph = (pw / S) & 1;  // phase parity of stage s at unit i
@@ -227,19 +277,30 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
         ++r_is;
         if (++hg_is == HG) hg_is = 0;
       }
-      // One bulk async copy (UBLKCP) per token row and tensor: lanes 0-15 copy the K rows of tokens
-      // 0-15, lanes 16-31 the V rows (HPC*256 contiguous bytes each), straight from the lane that holds
-      // the slot: no shuffles, one instruction per row instead of 2-4 LDGSTS; the bytes are counted on
-      // the stage's mbarrier.  V rows of masked tokens are zeroed by hand (P is 0 there, but 0 x stale
-      // NaN would poison the accumulator); K rows of masked tokens only feed logits that are masked.
+      // Bulk async copies (UBLKCP): lanes 0-15 copy K rows of tokens 0-15, lanes 16-31 the V rows, straight
+      // from the lane that holds the slot (no shuffles of addresses); the bytes are counted on the stage's
+      // mbarrier.  The first lane of a granule copies all GRAN rows when their slots are consecutive.
+      // V rows of masked tokens are zeroed by hand (P is 0 there, but 0 x stale NaN would poison the
+      // accumulator); K rows of masked tokens only feed logits that are masked.
       const bool is_v = lane >= 16;
+      bool lead_bulk = false, covered = false;
+      if constexpr (G::GRAN > 1) {
+        bool contig = gran_ok && my >= 0;
+#pragma unroll
+        for (int x = 1; x < G::GRAN; ++x) contig = contig && (__shfl_down_sync(0xffffffffu, my, x) == my + x);
+        const bool leader = (tok_lane % G::GRAN) == 0;
+        const uint32_t gm = __ballot_sync(0xffffffffu, leader && contig);
+        lead_bulk = leader && contig;
+        covered = (gm >> (lane - tok_lane % G::GRAN)) & 1u;
+      }
       const char* base = reinterpret_cast<const char*>(is_v ? vc : kc) + hg_is * G::TOK_BYTES;
-      const uint32_t dst = smem_u32(ring + s * G::STAGE_BYTES) + (is_v ? G::KV_BYTES : 0) + tok_lane * G::TOK_STRIDE;
+      const uint32_t dst = smem_u32(ring + s * G::STAGE_BYTES) + (is_v ? G::KV_BYTES : 0) + G::tok_off(tok_lane);
       mbar_wait(&empty_bar[s], ph ^ 1);
       if (mask != 0xffffu) {
         if (my < 0 && is_v) {
-          uint4* z = reinterpret_cast<uint4*>(ring + s * G::STAGE_BYTES + G::KV_BYTES + tok_lane * G::TOK_STRIDE);
+          uint4* z = reinterpret_cast<uint4*>(ring + s * G::STAGE_BYTES + G::KV_BYTES + G::tok_off(tok_lane));
           for (int c = 0; c < G::TOK_BYTES / 16; ++c) z[c] = make_uint4(0, 0, 0, 0);
+          fence_proxy_async();  // generic-proxy stores to a stage the async proxy (bulk copies) rewrites later
         }
         __syncwarp();  // the zeroed rows are ordered before lane 0's arrival below
       }
@@ -247,7 +308,10 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
         sValid[s] = mask;
         mbar_arrive_expect_tx(&full_bar[s], (uint32_t)__popc(mask) * 2u * (uint32_t)G::TOK_BYTES);
       }
-      if (my >= 0) bulk_g2s(dst, base + (int64_t)my * slot_bytes, (uint32_t)G::TOK_BYTES, &full_bar[s]);
+      if (lead_bulk)
+        bulk_g2s(dst, base + (int64_t)my * slot_bytes, (uint32_t)(G::GRAN * G::TOK_BYTES), &full_bar[s]);
+      else if (my >= 0 && !covered)
+        bulk_g2s(dst, base + (int64_t)my * slot_bytes, (uint32_t)G::TOK_BYTES, &full_bar[s]);
 #pragma unroll
       for (int d = 0; d + 1 < kSlotPrefetch; ++d) pf[d] = pf[d + 1];
       pf[kSlotPrefetch - 1] = slot_new;
@@ -312,8 +376,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
       mbar_wait(&full_bar[s], (uint32_t)(j / S) & 1u);
       if (dbg && tid == 0 && j == 0) dbg[2] = global_timer_ns();
       const uint32_t mask = sValid[s];
-      const bool tv0 = (mask >> g) & 1u, tv1 = (mask >> (g + 8)) & 1u;
-      if (mask != 0u) {
+      const bool tv0 = (mask >> G::row_tok(g)) & 1u, tv1 = (mask >> G::row_tok(g + 8)) & 1u;
+      if (mask != 0u && !p.no_math) {
         const uint32_t kbase = smem_u32(ring + s * G::STAGE_BYTES) + h_local * kRowBytes;
         const uint32_t vbase = kbase + G::KV_BYTES;
         float sc[NT][4];
@@ -321,7 +385,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
         for (int nt = 0; nt < NT; ++nt) sc[nt][0] = sc[nt][1] = sc[nt][2] = sc[nt][3] = 0.f;
         {
           const uint32_t kaddr =
-              kbase + ((lane & 7) + ((lane >> 3) & 1) * 8) * G::TOK_STRIDE + (lane >> 4) * 16;
+              kbase + G::tok_off(G::row_tok((lane & 7) + ((lane >> 3) & 1) * 8)) + (lane >> 4) * 16;
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk) {
             uint32_t a[4];
@@ -346,8 +410,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
           if (t == 0) {
             const int t0 = (seg_begin + (j - i) - row_begin) * kPage;
             float* srow = p.attn_score + (int64_t)b * p.score_stride + t0;
-            if (tv0) atomic_max_f32(srow + g, r0);
-            if (tv1) atomic_max_f32(srow + g + 8, r1);
+            if (tv0) atomic_max_f32(srow + G::row_tok(g), r0);
+            if (tv1) atomic_max_f32(srow + G::row_tok(g + 8), r1);
           }
         }
         uint32_t pb[NT][2];
@@ -386,7 +450,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
         }
         {
           const uint32_t vaddr =
-              vbase + ((lane & 7) + (lane >> 4) * 8) * G::TOK_STRIDE + ((lane >> 3) & 1) * 16;
+              vbase + G::tok_off(G::row_tok((lane & 7) + (lane >> 4) * 8)) + ((lane >> 3) & 1) * 16;
 #pragma unroll
           for (int dt = 0; dt < 8; ++dt) {
             uint32_t a[4];
@@ -460,6 +524,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
     }
     // publish: bf16 output when this CTA saw the whole row, else an fp32 partial
     const int pslot = 2 * blockIdx.x + (seg_begin == u0 ? 0 : 1);
+    // a whole row: the bf16 rows are staged in sQ (every warp has its q fragments in registers by now: the
+    // barrier makes sure of it) and leave as 16-byte vectors, to this rank and, under TP, to every peer
+    if (complete) consumer_sync();
     if (tl == 0) {
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt)
@@ -471,9 +538,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
             const float l = l_run[nt][e];
             const float inv = l > 0.f ? 1.f / l : 0.f;
             if (complete) {
-              __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
-                                    (int64_t)b * p.out_stride_b +
-                                    (int64_t)(hg * heads_row + head_local) * kHeadDim;
+              __nv_bfloat16* orow = sQ + head_local * kHeadDim;
 #pragma unroll
               for (int dt = 0; dt < 8; ++dt) {
                 orow[dt * 16 + g] = __float2bfloat16_rn(o_acc[nt][dt][e] * inv);
@@ -492,6 +557,21 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
             }
           }
         }
+    }
+    if (complete) {
+      consumer_sync();
+      const uint4* src = reinterpret_cast<const uint4*>(sQ);
+      const int64_t head0 = (int64_t)hg * heads_row * kHeadDim;
+      uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (int64_t)b * p.out_stride_b + head0);
+      for (int c = tid; c < heads_row * 16; c += kConsumerThreads) dst[c] = src[c];
+      if (push) {
+        for (int r = 0; r < p.push.world; ++r) {
+          uint4* g4 = reinterpret_cast<uint4*>(p.push.out[r] + (int64_t)b * p.push.stride_b +
+                                               (int64_t)p.push.rank * p.hq * kHeadDim + head0);
+          for (int c = tid; c < heads_row * 16; c += kConsumerThreads) g4[c] = src[c];
+        }
+        __threadfence_system();
+      }
     }
     if (!complete) {
       // arrival ticket: the last contributor of the row merges every partial
@@ -567,9 +647,15 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
                                     (int64_t)b * p.out_stride_b +
                                     (int64_t)(hg * heads_row + h0 + x) * kHeadDim;
               *reinterpret_cast<uint2*>(orow + lane * 4) = o2;
+              if (push) {
+                const int64_t off = (int64_t)b * p.push.stride_b +
+                                    ((int64_t)p.push.rank * p.hq + hg * heads_row + h0 + x) * kHeadDim + lane * 4;
+                for (int r = 0; r < p.push.world; ++r) *reinterpret_cast<uint2*>(p.push.out[r] + off) = o2;
+              }
             }
           }
         }
+        if (push) __threadfence_system();
         if (dbg && tid == 0) dbg[5] += global_timer_ns() - t_cmb;
       }
     }
@@ -578,6 +664,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
     i += n;
   }
   if (dbg && tid == 0) dbg[3] = global_timer_ns();
+  if (push && tid == 0) push_finish(p.push);  // the loop's last consumer_sync ordered the CTA's peer stores before this
 }
 
 template <int HPC, int NT, bool WITH_SCORE>
@@ -622,7 +709,10 @@ static int launch_variant(const AttnParams& p_in, cudaStream_t stream) {
     if ((int64_t)grid > want) grid = (int)want;
   }
   if (grid < 1) grid = 1;
-  kern<<<grid, kAttnThreads, smem, stream>>>(p);
+  p.no_math = tuning(kTuneNoMath) == 2;
+  p.granule = tuning(kTuneAttnGranule) != 2;
+  e = launch_kernel(kern, dim3(grid), dim3(kAttnThreads), smem, stream, p);
+  if (e != cudaSuccess) return cuda_error("sparse_decode_attn launch", e);
   return check_launch("sparse_decode_attn");
 }
 

@@ -1,6 +1,7 @@
 // Host-side declarations shared between the kernel translation units and api.cu.
 #pragma once
 
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -14,19 +15,47 @@ int sm_count();
 unsigned long long* debug_times_buffer();
 int max_ctas();  // persistent-grid size: sm_count() unless svb200_set_max_ctas lowered it
 // experiment knobs (svb200_set_tuning); 0 = automatic
-enum { kTuneScoreGroups = 0, kTuneAttnMinKB = 1, kTuneMinBatch = 2, kTuneShareDiv = 3, kTuneScoreCopy = 4, kTuneScoreSplit = 5, kTuneScoreQ = 6, kTuneCount = 8 };
+enum {
+  kTuneScoreGroups = 0, kTuneAttnMinKB = 1, kTuneMinBatch = 2, kTuneShareDiv = 3, kTuneChunkUnits = 4,
+  kTuneNoMath = 5, kTuneScoreQ = 6, kTunePdl = 7, kTuneAttnGranule = 8, kTuneCount = 16
+};
 int tuning(int which);
+bool pdl_enabled();  // launches carry the programmatic-stream-serialization attribute
+
+// Every kernel of the library is launched through this: with PDL enabled the launch may begin while its
+// predecessor in the stream drains (the kernels call pdl_wait() before they touch global memory).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                 Args&&... args) {
+  static_assert(sizeof...(KArgs) == sizeof...(Args), "argument count");
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  unsigned n = 0;
+  if (pdl_enabled()) {
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    n = 1;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
 
 // quest.cu
-int launch_quest_page_minmax(const void* k_cache, void* bounds_layer, const int32_t* slot_mapping,
-                             int n_tokens, int hkv, int64_t num_slots, cudaStream_t stream);
-int launch_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
+int launch_quest_page_minmax(const void* k_cache, void* bounds_layer, const int32_t* page_rec,
+                             const int32_t* slot_mapping, int n_tokens, int hkv, int64_t num_slots,
+                             int64_t num_chunks, cudaStream_t stream);
+int launch_quest_decode_page_complete(const void* k_cache_all, void* bounds_all, const int32_t* page_rec,
                                       const int32_t* page_table, int64_t pt_stride,
                                       const int32_t* req_rows, const int32_t* seq_lens, int batch,
                                       int layers, int hkv, int64_t num_slots, int64_t num_pages,
-                                      cudaStream_t stream);
-int launch_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds, int64_t num_pages,
-                            const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
+                                      int64_t num_chunks, cudaStream_t stream);
+int launch_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds, int64_t num_chunks,
+                            const int32_t* unit_table, int64_t ut_stride, const int32_t* req_rows,
                             const int32_t* context_lens, void* scores, int64_t score_stride,
                             int batch, int hq, int hkv, int n_cols, int32_t* sched, cudaStream_t stream);
 int launch_quest_select_pack(const void* scores, int64_t score_stride, int n_cols,
@@ -46,15 +75,27 @@ struct FusedStore {
   const int32_t* slot_mapping;
   int64_t num_slots;
   int refresh_bounds;  // rebuild the bounds record of a page the token completes
+  const int32_t* page_rec;  // physical page -> bounds record (needed with refresh_bounds)
 };
 
 int launch_quest_score_select_pack(const void* q, int64_t q_stride_b, const void* bounds,
-                                   int64_t num_pages, const int32_t* page_table, int64_t pt_stride,
+                                   int64_t num_chunks, const int32_t* unit_table, int64_t ut_stride,
+                                   const int32_t* page_table, int64_t pt_stride,
                                    const int32_t* req_rows, const int32_t* context_lens,
                                    void* scores, int64_t score_stride, int batch, int hq, int hkv,
                                    int n_cols, int k, int32_t* packed_slots, int64_t out_stride,
                                    int32_t* sparse_lens, int32_t* selected_pages, int32_t* tickets,
                                    const FusedStore* store, cudaStream_t stream);
+
+// Peer access for the tensor-parallel epilogues (collective.cu, decode_attn.cu); mirrors svb200_comm_t.
+constexpr int kMaxPeers = 8;
+constexpr int kSyncEpoch = 8, kSyncDone = 9, kSyncInts = 16;  // int32 layout of a rank's sync block
+struct PushArgs {
+  int world, rank;             // world <= 1: no push
+  __nv_bfloat16* out[kMaxPeers];  // gathered [B][world*Hq][128] bf16 buffer of every rank (own included)
+  int64_t stride_b;            // elements between batch rows of the gathered buffers
+  int32_t* sync[kMaxPeers];    // sync block of every rank: [r] = arrival flag written by rank r, [8] epoch, [9] finished CTAs
+};
 
 // decode_attn.cu
 struct AttnParams {
@@ -80,6 +121,9 @@ struct AttnParams {
   unsigned long long* dbg_times;  // experiments: per-CTA timestamps (svb200_debug_times), else null
   int producers;     // producer warps in use (divides stages); filled by the launcher
   float sm_scale;
+  int no_math;       // experiments: consumers release the stages without the contractions
+  int granule;       // copy granules of several token rows where the slots allow it
+  PushArgs push;     // tensor-parallel push epilogue (world <= 1: none)
 };
 int attn_auto_heads_per_cta(int hkv);
 int launch_sparse_decode_attn(const AttnParams& p, int heads_per_cta, cudaStream_t stream);
@@ -93,9 +137,20 @@ int launch_h2o_select_compact(float* cumulative, const int64_t* cum_rows, int32_
                               const int64_t* free_rows, int32_t* keep_out, int num_rows, int kv_len,
                               int budget, int recent, cudaStream_t stream);
 
+// collective.cu
+struct AllReduceArgs {
+  int world, rank;
+  const __nv_bfloat16* in[kMaxPeers];  // this call's input of every rank (own included), n elements each
+  int32_t* sync[kMaxPeers];
+  __nv_bfloat16* out;                  // local result
+  int64_t n;                           // elements, a multiple of 8
+};
+int launch_allreduce_sum_bf16(const AllReduceArgs& a, cudaStream_t stream);
+
 // store_kv.cu
 int launch_store_kv_minmax(const void* key, int64_t k_stride, const void* value, int64_t v_stride,
                            void* k_cache, void* v_cache, const int32_t* slot_mapping, int n_tokens,
-                           int hkv, int64_t num_slots, void* bounds_layer, cudaStream_t stream);
+                           int hkv, int64_t num_slots, void* bounds_layer, const int32_t* page_rec,
+                           int64_t num_chunks, cudaStream_t stream);
 
 }  // namespace svb200

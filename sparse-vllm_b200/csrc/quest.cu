@@ -2,9 +2,10 @@
 // radix top-k page selection + slot packing.
 //
 // Reference behaviour (CURRENTF/Sparse-vLLM, src/sparsevllm/engine/cache_manager/quest.py):
-//   bounds  : on_kv_stored 1608-1716, on_forward_end 1719-1771
+//   bounds  : on_kv_stored 1608-1716, on_forward_end 1719-1771 (HBM layout: bounds_layout.cuh)
 //   scoring : _score_pages_batched 1773-1802 (three bf16 roundings per head score)
 //   select  : _build_decode_view_static 1833-1913
+#include "bounds_layout.cuh"
 #include "common.cuh"
 #include "launch.h"
 #include "sched.cuh"
@@ -13,7 +14,7 @@
 namespace svb200 {
 
 // =========================================================================
-// Page bounds.  bounds[page][2][Hkv][128]; plane 0 = max, plane 1 = min.
+// Page bounds (layout: bounds_layout.cuh).  plane 0 = max, plane 1 = min.
 // =========================================================================
 __device__ __forceinline__ void page_minmax_vec(const __nv_bfloat16* page_base, int64_t row_elems,
                                                 uint4& mx, uint4& mn) {
@@ -39,23 +40,27 @@ __device__ __forceinline__ void page_minmax_vec(const __nv_bfloat16* page_base, 
 // One warp per token that completes a page (slot % 16 == 15).
 __global__ void __launch_bounds__(256) quest_page_minmax_kernel(
     const __nv_bfloat16* __restrict__ k_cache, __nv_bfloat16* __restrict__ bounds,
-    const int32_t* __restrict__ slot_mapping, int n_tokens, int hkv, int64_t num_slots) {
+    const int32_t* __restrict__ page_rec, const int32_t* __restrict__ slot_mapping, int n_tokens, int hkv,
+    int64_t num_slots, int64_t num_recs) {
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int warps_per_block = blockDim.x >> 5;
   const int64_t row_elems = (int64_t)hkv * kHeadDim;
   const int vecs = hkv * (kHeadDim / 8);
+  const int hs = bounds_head_split(hkv);
   for (int tok = blockIdx.x * warps_per_block + (threadIdx.x >> 5); tok < n_tokens;
        tok += gridDim.x * warps_per_block) {
     const int slot = slot_mapping[tok];
     if (slot < 0 || (slot & (kPage - 1)) != kPage - 1 || slot >= num_slots) continue;
     const int64_t page = slot >> 4;
+    const int rec = page_rec[page];
+    if (rec < 0 || rec >= num_recs) continue;
     const __nv_bfloat16* page_base = k_cache + page * kPage * row_elems;
-    __nv_bfloat16* out = bounds + page * 2 * row_elems;
     for (int v = lane; v < vecs; v += 32) {
       uint4 mx, mn;
       page_minmax_vec(page_base + v * 8, row_elems, mx, mn);
-      *reinterpret_cast<uint4*>(out + v * 8) = mx;
-      *reinterpret_cast<uint4*>(out + row_elems + v * 8) = mn;
+      *reinterpret_cast<uint4*>(bounds + bounds_seg_offset(rec, 0, v >> 4, v & 15, hkv, hs)) = mx;
+      *reinterpret_cast<uint4*>(bounds + bounds_seg_offset(rec, 1, v >> 4, v & 15, hkv, hs)) = mn;
     }
   }
 }
@@ -63,25 +68,29 @@ __global__ void __launch_bounds__(256) quest_page_minmax_kernel(
 // grid (batch, layers): rebuild the bounds of the page a decode token just completed.
 __global__ void __launch_bounds__(128) quest_decode_page_complete_kernel(
     const __nv_bfloat16* __restrict__ k_cache_all, __nv_bfloat16* __restrict__ bounds_all,
-    const int32_t* __restrict__ page_table, int64_t pt_stride,
+    const int32_t* __restrict__ page_rec, const int32_t* __restrict__ page_table, int64_t pt_stride,
     const int32_t* __restrict__ req_rows, const int32_t* __restrict__ seq_lens, int hkv,
-    int64_t num_slots, int64_t num_pages) {
+    int64_t num_slots, int64_t num_pages, int64_t num_recs) {
+  pdl_wait();
   const int b = blockIdx.x, layer = blockIdx.y;
   const int len = seq_lens[b];
   if (len <= 0 || (len & (kPage - 1)) != 0) return;
   const int64_t row = req_rows[b];
   const int slot_page = page_table[row * pt_stride + (len / kPage - 1)];
   if (slot_page < 0 || slot_page >= num_pages) return;
+  const int rec = page_rec[slot_page];
+  if (rec < 0 || rec >= num_recs) return;
   const int64_t row_elems = (int64_t)hkv * kHeadDim;
+  const int hs = bounds_head_split(hkv);
   const __nv_bfloat16* page_base =
       k_cache_all + ((int64_t)layer * num_slots + (int64_t)slot_page * kPage) * row_elems;
-  __nv_bfloat16* out = bounds_all + ((int64_t)layer * num_pages + slot_page) * 2 * row_elems;
+  __nv_bfloat16* out = bounds_all + (int64_t)layer * num_recs * 2 * row_elems;
   const int vecs = hkv * (kHeadDim / 8);
   for (int v = threadIdx.x; v < vecs; v += blockDim.x) {
     uint4 mx, mn;
     page_minmax_vec(page_base + v * 8, row_elems, mx, mn);
-    *reinterpret_cast<uint4*>(out + v * 8) = mx;
-    *reinterpret_cast<uint4*>(out + row_elems + v * 8) = mn;
+    *reinterpret_cast<uint4*>(out + bounds_seg_offset(rec, 0, v >> 4, v & 15, hkv, hs)) = mx;
+    *reinterpret_cast<uint4*>(out + bounds_seg_offset(rec, 1, v >> 4, v & 15, hkv, hs)) = mn;
   }
 }
 
@@ -301,6 +310,7 @@ __global__ void __launch_bounds__(256) quest_select_pack_kernel(
     const int32_t* __restrict__ dense_table, int64_t dense_stride, int token_budget,
     int page_budget_base, int out_width) {
   __shared__ SelectSmem sm;
+  pdl_wait();
   const int b = blockIdx.x;
   const int ctx = context_lens[b];
   const int64_t row = req_rows[b];
@@ -330,50 +340,49 @@ __global__ void __launch_bounds__(256) quest_select_pack_kernel(
 // Page scoring (+ fused top-k / packing).
 //
 // A "unit" is 16 consecutive logical pages of one batch row; only valid pages
-// (p < ceil(ctx/16) - 1) form units.  Units are handed out dynamically (sched.cuh): a
-// scheduler warp claims chunks of 2 units from per-row counters; the CTAs of a group walk
-// the group's rows one after the other, so rows finish at staggered times and the top-k of
-// a finished row runs while the other CTAs keep streaming the next row.
-// Producer warps resolve the 2 x 16 page slots of a chunk through the page table (fetched
-// kIdDepth chunks ahead) and copy each page's bounds record ([2][Hkv][128] = Hkv*512
-// contiguous bytes) with 16-byte LDGSTS, a warp per 512 B, into a ring of S stages
-// (~200 KB in flight per SM) whose mbarriers complete when the copies land.  Consumer warps
-// take units round-robin; per unit and KV head:
-//   A = bounds rows (16 pages x 128, ldmatrix), B = q+ / q- (128 x 8 heads)
+// (p < ceil(ctx/16) - 1) form units.  The bounds of a unit are one contiguous bounds chunk
+// (bounds_layout.cuh), streamed as hs ring stages of hh = Hkv/hs heads each.  Units are handed out
+// dynamically (sched.cuh): a scheduler warp claims chunks of ~64 KB from per-row counters and posts
+// descriptors; ONE loader warp resolves each unit's chunk id through the unit table (fetched
+// kIdDepth descriptors ahead) and issues one bulk async copy (cp.async.bulk, SASS UBLKCP) per ring
+// stage, 8-32 KB each, counted on the stage's mbarrier.  Consumer warps take units round-robin;
+// per unit and KV head:
+//   A = bounds rows (16 pages x 128, ldmatrix from the swizzled stage), B = q+ / q- (128 x 8 heads)
 //   score = bf16(bf16(A_max.q+) + bf16(A_min.q-)), then max over all local heads.
-// A CTA leaving a row adds the units it scored to the row's counter; the CTA that completes
-// the row runs the top-k selection and slot packing for it in the same launch.
+// A CTA leaving a row adds the units it scored to the row's counter; the row's designated CTA runs
+// the top-k selection and slot packing for it in the same launch (8 dedicated select warps).
 // =========================================================================
 constexpr int kScoreConsumerWarps = 6;
 constexpr int kScoreConsumerThreads = kScoreConsumerWarps * 32;
-constexpr int kScoreProducerWarps = 6;  // + 1 scheduler warp
-constexpr int kIdDepth = 3;             // chunks whose page ids are in flight ahead of the copies
-constexpr int kScoreSelectWarps = 8;     // dedicated top-k warps: the stream never waits for a selection
+constexpr int kScoreLoaderWarp = kScoreConsumerWarps;      // one loader warp ...
+constexpr int kScoreSchedWarp = kScoreConsumerWarps + 1;   // ... and one scheduler warp
+constexpr int kIdDepth = 2;             // descriptors whose chunk ids are in flight ahead of the copies
+constexpr int kScoreSelectWarps = 8;    // dedicated top-k warps: the stream never waits for a selection
 constexpr int kScoreSelectThreads = kScoreSelectWarps * 32;
-constexpr int kScoreThreads = kScoreConsumerThreads + (kScoreProducerWarps + 1) * 32 + kScoreSelectThreads;
+constexpr int kScoreThreads = kScoreConsumerThreads + 2 * 32 + kScoreSelectThreads;
 constexpr int kScoreMaxSmem = 227 * 1024;
-static_assert(kIdDepth < kSchedQueue, "producers read kIdDepth descriptors ahead of the one they issue");
+static_assert(kIdDepth < kSchedQueue, "the loader reads kIdDepth descriptors ahead of the one it issues");
 
 struct ScoreParams {
   const __nv_bfloat16* q;
   int64_t q_stride_b;
-  const __nv_bfloat16* bounds;
-  int64_t num_pages;
-  const int32_t* page_table;
+  const __nv_bfloat16* bounds;  // bounds chunks of this layer
+  int64_t num_chunks;
+  const int32_t* unit_table;  // [rows][ut_stride]: bounds chunk of (row, logical page / 16)
+  int64_t ut_stride;
+  const int32_t* page_table;  // fused select only: logical page -> physical page (slot packing)
   int64_t pt_stride;
   const int32_t* req_rows;
   const int32_t* context_lens;
   uint16_t* scores;
   int64_t score_stride;
   int batch, hq, hkv, n_cols, stages;
-  int bulk;  // 1: one UBLKCP per page record, 0: 16-byte LDGSTS
-  int ppu;     // pages per unit: 16 (8 only for an odd head count > 4 that cannot be split)
-  int hsplit;  // ring stages per unit: 1, or 2 = a stage holds half of the KV heads of the unit's pages
+  int hsplit;  // ring stages per unit (bounds_head_split)
   unsigned long long* dbg_times;  // experiments: per-CTA timestamps (svb200_debug_times), else null
-  int consumers;  // consumer warps that take units; divides `stages` (see the kernel)
-  int producers;  // producer warps that feed units; divides `stages`
-  int groups;     // row groups of the scheduler
-  int min_batch, share_div;  // guided claim size = max(min_batch, left / (share_div * CTAs per group))
+  int groups;                     // row groups of the scheduler
+  int chunk_units;                // units per claimed chunk
+  int min_batch, share_div;       // guided claim size = max(min_batch, left / (share_div * CTAs per group))
+  int no_math;                    // experiments: consumers release the stages without the contractions
   int32_t* sched;  // sched_scratch_ints(batch) zeroed ints
   // fused select only
   int k;
@@ -390,24 +399,17 @@ struct ScoreSmemLayout {
   int ring_off, q_off, bar_off, valid_off, rows_off, sched_off, select_off, total;
 };
 
-// shared-memory stride of one page inside a stage holding `heads` KV heads (max rows, then min rows)
-__host__ __device__ inline int score_rec_stride(int heads) { return heads * 2 * kRowBytes + 16; }
-
-// A 16-page unit of Hkv 8 is 64 KB: as one stage only three would fit.  Such a unit is streamed as two
-// stages of four heads each (two 1 KB copies per page and stage) and the consumer warp keeps the
-// running maximum over both; the mma tile stays 16 pages tall (8-page units wasted half of it).
-__host__ __device__ inline int score_head_split(int hkv) { return (hkv > 4 && hkv % 2 == 0) ? 2 : 1; }
-__host__ __device__ inline int score_pages_per_unit(int hkv, int hsplit) { return (hkv > 4 && hsplit == 1) ? 8 : 16; }
+__host__ __device__ inline int score_stage_bytes(int hkv, int hsplit) { return (int)bounds_part_bytes(hkv, hsplit); }
 
 __host__ __device__ inline ScoreSmemLayout score_smem_layout(int stages, int hq, int hkv, int hsplit, int batch,
                                                              bool fused, int q_copies) {
   ScoreSmemLayout L;
   int off = 0;
-  L.ring_off = off;   off += stages * score_pages_per_unit(hkv, hsplit) * score_rec_stride(hkv / hsplit);
+  L.ring_off = off;   off += stages * score_stage_bytes(hkv, hsplit);
   L.q_off = off;      off += q_copies * hq * kRowBytes;
   L.bar_off = off;    off += 2 * stages * 8;
   L.valid_off = off;  off += ((stages * 4 + 15) / 16) * 16;
-  L.rows_off = off;   off += (2 * batch * 4 + 15) / 16 * 16;  // valid pages, page-table row of each row
+  L.rows_off = off;   off += (2 * batch * 4 + 15) / 16 * 16;  // valid pages, table row of each batch row
   L.sched_off = off;  off += (int)((sizeof(SchedSmem) + 15) / 16 * 16);
   L.select_off = off; off += fused ? (int)((sizeof(SelectSmem) + 15) / 16 * 16) : 0;
   L.total = off;
@@ -428,13 +430,9 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   extern __shared__ __align__(128) unsigned char smem[];
   const int S = p.stages, hq = p.hq, hkv = p.hkv, B = p.batch;
   const int gsz = hq / hkv;
-  const int hs = p.hsplit, hh = hkv / hs;  // stages per unit, KV heads per stage
-  const int rec_stride = score_rec_stride(hh);
-  const int rec_bytes = hkv * 2 * kRowBytes;  // a page's record in HBM: max rows of all heads, then min rows
-  const int part_bytes = hh * kRowBytes;      // max (or min) rows of one stage's heads
-  const int ppu = p.ppu;
-  const uint32_t unit_mask = (1u << ppu) - 1u;
-  const int stage_bytes = ppu * rec_stride;
+  const int hs = p.hsplit, hh = hkv / hs;     // stages per unit, KV heads per stage
+  const int rec_stride = hh * 2 * kRowBytes;  // one page inside a stage: max rows of the stage's heads, then min rows
+  const int stage_bytes = kPage * rec_stride;
   const ScoreSmemLayout L = score_smem_layout(S, hq, hkv, hs, B, FUSED_SELECT, QSPLIT ? 2 : 1);
   unsigned char* ring = smem + L.ring_off;
   // sq[sign][head][kk][t] : uint2 {b0, b1} B fragments of q+ / q-, kk XOR-swizzled by head (QSPLIT), or
@@ -444,33 +442,33 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   uint64_t* empty_bar = full_bar + S;
   uint32_t* sValid = reinterpret_cast<uint32_t*>(smem + L.valid_off);
   int* sNv = reinterpret_cast<int*>(smem + L.rows_off);  // valid previous pages of row b
-  int* sReq = sNv + B;                                   // page-table row of row b
+  int* sReq = sNv + B;                                   // table row of batch row b
   SchedSmem& sched = *reinterpret_cast<SchedSmem*>(smem + L.sched_off);
   __shared__ int s_flag;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   unsigned long long* dbg = p.dbg_times ? p.dbg_times + (size_t)blockIdx.x * 16 : nullptr;
+
+  // ---- setup that touches no global memory (runs while a programmatic predecessor drains)
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(&full_bar[s], 1);  // the loader's expect_tx arrival; the copy's bytes complete the phase
+      mbar_init(&empty_bar[s], 1);
+      // no fill yet: a consumer whose first unit is a later round of the stage passes the fresh barrier's
+      // parity test and must not find a tag a previous launch left in shared memory (tags are 15 bits)
+      sValid[s] = 0xffffffffu;
+    }
+    sched_init(sched, 1 + kScoreConsumerWarps);
+    s_flag = 0;
+    mbar_fence_init();
+  }
+  pdl_wait();
   if (dbg && tid == 0) {
     uint32_t smid;
     asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
     dbg[0] = global_timer_ns();
     dbg[7] = smid;
     dbg[2] = dbg[4] = dbg[5] = dbg[6] = dbg[13] = dbg[14] = dbg[15] = 0;
-  }
-
-  // ---- setup
-  if (tid == 0) {
-    for (int s = 0; s < S; ++s) {
-      // LDGSTS: 32 async copy arrivals + the producer's release; bulk: the expect_tx arrival
-      mbar_init(&full_bar[s], p.bulk ? 1 : 33);
-      mbar_init(&empty_bar[s], 1);
-      // no fill yet: a consumer whose first unit is a later round of the stage passes the fresh barrier's
-      // parity test and must not find a tag a previous launch left in shared memory (tags are 15 bits)
-      sValid[s] = 0xffffffffu;
-    }
-    sched_init(sched, p.producers + kScoreConsumerWarps);
-    s_flag = 0;
-    mbar_fence_init();
   }
   for (int b = tid; b < B; b += kScoreThreads) {
     const int ctx = p.context_lens[b];
@@ -482,32 +480,33 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
     const int ctx = p.context_lens[b];
     const int nv = min(max((ctx + kPage - 1) / kPage, 1) - 1, p.n_cols);
     uint16_t* srow = p.scores + (int64_t)b * p.score_stride;
-    for (int c = (nv + ppu - 1) / ppu * ppu + tid; c < p.n_cols; c += kScoreThreads) srow[c] = 0xff80u;
+    for (int c = (nv + kPage - 1) / kPage * kPage + tid; c < p.n_cols; c += kScoreThreads) srow[c] = 0xff80u;
   }
   __syncthreads();
+  pdl_launch_dependents();
   if (dbg && tid == 0) dbg[1] = global_timer_ns();
-  auto units_of_row = [&](int r) { return (sNv[r] + ppu - 1) / ppu; };
+  auto units_of_row = [&](int r) { return (sNv[r] + kPage - 1) / kPage; };
   int* next_chunk = p.sched + 1;
   int* units_done = p.sched + 1 + B;
 
-  if (warp == kScoreConsumerWarps + kScoreProducerWarps) {
+  if (warp == kScoreSchedWarp) {
     // ============================================================== scheduler
-    sched_run(sched, next_chunk, B, p.groups, p.min_batch, p.share_div, min(kSchedQueue, (S / hs + kChunkUnits - 1) / kChunkUnits + kIdDepth + 1),
-              units_of_row, ReserveNone(), (dbg && blockIdx.x >= (unsigned)B) ? dbg + 15 : nullptr);
+    const int depth = min(kSchedQueue, (S / hs + p.chunk_units - 1) / p.chunk_units + kIdDepth + 1);
+    sched_run(sched, next_chunk, B, p.groups, p.chunk_units, p.min_batch, p.share_div, depth, units_of_row,
+              ReserveNone(), (dbg && blockIdx.x >= (unsigned)B) ? dbg + 15 : nullptr);
     return;
   }
 
-  if (warp >= kScoreConsumerWarps && warp < kScoreConsumerWarps + kScoreProducerWarps) {
-    // ============================================================== producers
-    // stage-load ii = i * hs + part (i: CTA-local running unit index) is fed by producer ii % NP into
-    // stage ii % S, NP | S: a stage is always refilled by the same warp.  Lane l holds the physical page of logical page
-    // unit_begin*16 + l of the chunk (2 units x 16 pages), fetched kIdDepth chunks ahead.
-    const int pw = warp - kScoreConsumerWarps;
-    const int NP = p.producers;
-    if (pw >= NP) return;
+  if (warp == kScoreLoaderWarp) {
+    // ============================================================== loader
+    // Stage-load ii = i * hs + part (i: CTA-local running unit index) goes into stage ii % S.  Lane l holds
+    // the bounds chunk of unit unit_begin + l of a descriptor, fetched kIdDepth descriptors ahead; lane 0
+    // issues ONE bulk async copy per stage-load.  A partly valid last unit is copied whole (the chunk
+    // exists; rows of pages that do not count are masked when the scores are written).
+    const uint32_t part_bytes = (uint32_t)stage_bytes;
     ChunkDesc dq[kIdDepth];
     int idq[kIdDepth];
-    unsigned long long w_desc = 0, w_empty = 0, w_ids = 0;
+    unsigned long long w_desc = 0, w_empty = 0;
     int n_read = 0;
     bool ended = false;
     auto fetch = [&](ChunkDesc& d, int& id) {
@@ -523,88 +522,63 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
         ended = true;
         return;
       }
-      const int col = d.unit_begin * ppu + lane;
-      if (lane < d.units() * ppu && col < sNv[d.row])
-        id = __ldg(p.page_table + (int64_t)sReq[d.row] * p.pt_stride + col);
+      if (lane < d.units()) id = __ldg(p.unit_table + (int64_t)sReq[d.row] * p.ut_stride + d.unit_begin + lane);
     };
 #pragma unroll
     for (int t = 0; t < kIdDepth; ++t) fetch(dq[t], idq[t]);
-    const char* src0 = reinterpret_cast<const char*>(p.bounds) + lane * 16;
+    const char* bounds_bytes = reinterpret_cast<const char*>(p.bounds);
     // dq / idq form a circular FIFO indexed at compile time (the loop body is unrolled kIdDepth
     // times): a register that waits for its table load is never moved, so the load's latency is
-    // only paid when the id is finally used, kIdDepth chunks later.
+    // only paid when the id is finally used, kIdDepth descriptors later.
     bool done = false;
     while (!done) {
 #pragma unroll
       for (int u = 0; u < kIdDepth; ++u) {
         if (done) break;
         const ChunkDesc cur = dq[u];
-        const int pa = idq[u];
+        const int ids = idq[u];
         fetch(dq[u], idq[u]);
         if (cur.row < 0) {
           done = true;
           break;
         }
-        const unsigned long long ti = dbg ? global_timer_ns() : 0;
-        const int my = (pa >= 0 && pa < p.num_pages) ? pa : -1;
-        const uint32_t ball = __ballot_sync(0xffffffffu, my >= 0);
-        if (dbg) w_ids += global_timer_ns() - ti;
-        for (int jj = 0; jj < cur.units() * hs; ++jj) {
-          const int j = jj / hs, part = jj - j * hs;
-          const int ii = cur.unit_base * hs + jj;
-          if (ii % NP != pw) continue;
-          const int s = ii % S;
-          const uint32_t round = (uint32_t)(ii / S), ph = round & 1u;
-          // valid pages of the unit | the stage's fill count (the consumer checks it: see there)
-          const uint32_t umask = (ball >> (j * ppu)) & unit_mask, tagged = umask | ((round & 0x7fffu) << 16);
-          const unsigned long long te = dbg ? global_timer_ns() : 0;
-          mbar_wait(&empty_bar[s], ph ^ 1u);
-          if (dbg) w_empty += global_timer_ns() - te;
-          if (p.bulk) {
-            // bulk async copies (UBLKCP) issued by the lane that holds the page id: no shuffles, one
-            // instruction per record (or two per half record: its max rows, its min rows); bytes are
-            // counted on the stage's mbarrier
+        const int nv = sNv[cur.row];
+        for (int j = 0; j < cur.units(); ++j) {
+          const int c = __shfl_sync(0xffffffffu, ids, j);
+          const bool have = c >= 0 && c < p.num_chunks;
+          const int cnt = nv - (cur.unit_begin + j) * kPage;  // valid pages of the unit (> 0)
+          const uint32_t umask = have ? (cnt >= kPage ? 0xffffu : ((1u << max(cnt, 0)) - 1u)) : 0u;
+          for (int part = 0; part < hs; ++part) {
+            const int ii = (cur.unit_base + j) * hs + part;
+            const int s = ii % S;
+            const uint32_t round = (uint32_t)(ii / S);
+            const unsigned long long te = dbg ? global_timer_ns() : 0;
+            mbar_wait(&empty_bar[s], (round & 1u) ^ 1u);
+            if (dbg) w_empty += global_timer_ns() - te;
             if (lane == 0) {
-              sValid[s] = tagged;
-              mbar_arrive_expect_tx(&full_bar[s], (uint32_t)__popc(umask) * 2u * (uint32_t)part_bytes);
-            }
-            const int pg = lane - j * ppu;
-            if (pg >= 0 && pg < ppu && my >= 0) {
-              const uint32_t dst = smem_u32(ring + s * stage_bytes) + pg * rec_stride;
-              const char* src = reinterpret_cast<const char*>(p.bounds) + (int64_t)my * rec_bytes + part * part_bytes;
-              if (hs == 1) {
-                bulk_g2s(dst, src, (uint32_t)rec_bytes, &full_bar[s]);
+              // valid pages of the unit | the stage's fill count (the consumer checks it: see there)
+              sValid[s] = umask | ((round & 0x7fffu) << 16);
+              if (have) {
+                mbar_arrive_expect_tx(&full_bar[s], part_bytes);
+                bulk_g2s(smem_u32(ring + s * stage_bytes),
+                         bounds_bytes + ((int64_t)c * hs + part) * (int64_t)part_bytes, part_bytes, &full_bar[s]);
               } else {
-                bulk_g2s(dst, src, (uint32_t)part_bytes, &full_bar[s]);
-                bulk_g2s(dst + part_bytes, src + hkv * kRowBytes, (uint32_t)part_bytes, &full_bar[s]);
+                mbar_arrive(&full_bar[s]);
               }
             }
-            continue;
           }
-          const uint32_t dst0 = smem_u32(ring + s * stage_bytes) + lane * 16;
-#pragma unroll 4
-          for (int pg = 0; pg < ppu; ++pg) {
-            const int page = __shfl_sync(0xffffffffu, my, j * ppu + pg);
-            const int nbytes = page >= 0 ? 16 : 0;
-            const char* src = src0 + (int64_t)max(page, 0) * rec_bytes;
-            const uint32_t dst = dst0 + pg * rec_stride;
-            for (int c = 0; c < hkv; ++c) cp_async_16(dst + c * 512, src + c * 512, nbytes);
-          }
-          if (lane == 0) sValid[s] = tagged;
-          cp_async_mbar_arrive(&full_bar[s]);
-          if (lane == 0) mbar_arrive(&full_bar[s]);  // release: publishes sValid
         }
       }
     }
-    if (dbg && pw == 0 && lane == 0) dbg[4] = global_timer_ns(), dbg[8] = w_desc, dbg[9] = w_empty, dbg[10] = w_ids;
+    if (dbg && lane == 0) dbg[4] = global_timer_ns(), dbg[8] = w_desc, dbg[9] = w_empty;
     return;
   }
 
-  if (warp > kScoreConsumerWarps + kScoreProducerWarps) {
+  if (warp > kScoreSchedWarp) {
     // ============================================================== select warps
     // CTA c selects rows c, c + gridDim, ...: it waits until the row's counter shows every unit
     // scored (the consumers of all CTAs add what they scored when they leave a row), then runs the
-    // top-k and packing.  The stream (producers / consumers) never waits for a selection.
+    // top-k and packing.  The stream (loader / consumers) never waits for a selection.
     if constexpr (FUSED_SELECT) {
       SelectSmem* sel_sm = reinterpret_cast<SelectSmem*>(smem + L.select_off);
       const int stid = tid - (kScoreThreads - kScoreSelectThreads);
@@ -618,12 +592,10 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
         const int need = units_of_row(b);
         if (need > 0 && stid == 0) {
           const volatile int* ctr = units_done + b;
-          if (*ctr < need) {
-            const uint64_t t0 = global_timer_ns();
-            while (*ctr < need) {
-              __nanosleep(256);
-              if (global_timer_ns() - t0 > 2000000000ull) __trap();
-            }
+          uint32_t spins = 0;
+          while (*ctr < need) {
+            __nanosleep(64);
+            if (++spins > kSpinLimit) __trap();
           }
         }
         group_sync<2, kScoreSelectThreads>();
@@ -669,10 +641,13 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   };
 
   // Unit i goes to warp i % NW, which drains all of its hs stage-loads.  A parity wait cannot tell a
-  // phase from the one two before it, and a stage may be drained by different warps in consecutive
-  // rounds (NW need not divide S / hs): the producer therefore tags the stage's valid mask with its
+  // phase from the one two before it, and a stage is drained by different warps in consecutive
+  // rounds (NW need not divide S / hs): the loader therefore tags the stage's valid mask with its
   // fill count, and a warp only trusts the barrier once the tag shows the fill it is waiting for.
-  const int NW = p.consumers;
+  constexpr int NW = kScoreConsumerWarps;
+  // ldmatrix lane -> (page row, 16-byte column half); the stage is swizzled by (page & 7) (bounds_layout.cuh)
+  const uint32_t lm_row = (uint32_t)((lane & 7) + ((lane >> 3) & 1) * 8) * (uint32_t)rec_stride;
+  const uint32_t lm_hi = (uint32_t)(lane >> 4) << 4, lm_xor = (uint32_t)(lane & 7) << 4;
   bool first_seen = false;
   int cur_row = -2, visit_units = 0, total_units = 0;  // -2: no row yet (-1 is the end descriptor)
   unsigned long long c_desc = 0, c_full = 0;
@@ -701,92 +676,91 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
     uint16_t* srow = p.scores + (int64_t)d.row * p.score_stride;
     for (int j = 0; j < d.units(); ++j) {
       const int i = d.unit_base + j;
-      if (warp >= NW || i % NW != warp) continue;
+      if (i % NW != warp) continue;
       float best0 = -INFINITY, best1 = -INFINITY;
       uint32_t mask = 0;
       for (int part = 0; part < hs; ++part) {
-      const int ii = i * hs + part;
-      const int s = ii % S;
-      const uint32_t round = (uint32_t)(ii / S);
-      const unsigned long long tf = dbg ? global_timer_ns() : 0;
-      while (true) {
-        mbar_wait(&full_bar[s], round & 1u);
-        mask = (uint32_t)ld_volatile_shared(reinterpret_cast<const int*>(sValid + s));
-        if ((mask >> 16) == (round & 0x7fffu)) {
-          mbar_wait(&full_bar[s], round & 1u);  // the tag is written before the copies land: wait for them
-          break;
+        const int ii = i * hs + part;
+        const int s = ii % S;
+        const uint32_t round = (uint32_t)(ii / S);
+        const unsigned long long tf = dbg ? global_timer_ns() : 0;
+        while (true) {
+          mbar_wait(&full_bar[s], round & 1u);
+          mask = (uint32_t)ld_volatile_shared(reinterpret_cast<const int*>(sValid + s));
+          if ((mask >> 16) == (round & 0x7fffu)) {
+            mbar_wait(&full_bar[s], round & 1u);  // the tag is written before the copy lands: wait for it
+            break;
+          }
+          __nanosleep(64);
         }
-        __nanosleep(64);
-      }
-      if (dbg) c_full += global_timer_ns() - tf;
-      if (dbg && tid == 0 && !first_seen) dbg[2] = global_timer_ns(), first_seen = true;
-      const uint32_t abase = smem_u32(ring + s * stage_bytes) +
-                             ((lane & 7) + ((lane >> 3) & 1) * 8) * rec_stride + (lane >> 4) * 16;
-      // KV heads two at a time: the two heads' ldmatrix -> mma chains are independent, so the in-order
-      // issue of one warp overlaps their latencies (one head at a time left the consumers the bottleneck
-      // at Hkv 8); an odd last head runs alone
-      const int hbase = part * hh;  // first KV head of this stage
-      for (int h = 0; h < hh; h += 2) {
-        const bool two = h + 1 < hh;
-        const int h1 = two ? h + 1 : h;
-        float cp[2][NT][4], cn[2][NT][4];
+        if (dbg) c_full += global_timer_ns() - tf;
+        if (dbg && tid == 0 && !first_seen) dbg[2] = global_timer_ns(), first_seen = true;
+        const uint32_t abase = smem_u32(ring + s * stage_bytes) + lm_row;
+        // KV heads two at a time: the two heads' ldmatrix -> mma chains are independent, so the in-order
+        // issue of one warp overlaps their latencies (one head at a time left the consumers the bottleneck
+        // at Hkv 8); an odd last head runs alone
+        const int hbase = part * hh;  // first KV head of this stage
+        for (int h = 0; h < hh && !p.no_math; h += 2) {
+          const bool two = h + 1 < hh;
+          const int h1 = two ? h + 1 : h;
+          float cp[2][NT][4], cn[2][NT][4];
 #pragma unroll
-        for (int x = 0; x < 2; ++x)
+          for (int x = 0; x < 2; ++x)
 #pragma unroll
-          for (int nt = 0; nt < NT; ++nt)
+            for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
-            for (int e = 0; e < 4; ++e) cp[x][nt][e] = cn[x][nt][e] = 0.f;
-        const uint32_t amax0 = abase + h * kRowBytes, amin0 = amax0 + hh * kRowBytes;
-        const uint32_t amax1 = abase + h1 * kRowBytes, amin1 = amax1 + hh * kRowBytes;
+              for (int e = 0; e < 4; ++e) cp[x][nt][e] = cn[x][nt][e] = 0.f;
+          const uint32_t amax0 = abase + h * kRowBytes, amin0 = amax0 + hh * kRowBytes;
+          const uint32_t amax1 = abase + h1 * kRowBytes, amin1 = amax1 + hh * kRowBytes;
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          uint32_t a0x[4], a0n[4], a1x[4], a1n[4];
-          ldmatrix_x4(a0x, amax0 + kk * 32);
-          ldmatrix_x4(a0n, amin0 + kk * 32);
-          ldmatrix_x4(a1x, amax1 + kk * 32);
-          ldmatrix_x4(a1n, amin1 + kk * 32);
+          for (int kk = 0; kk < 8; ++kk) {
+            const uint32_t koff = ((uint32_t)(kk * 32) | lm_hi) ^ lm_xor;
+            uint32_t a0x[4], a0n[4], a1x[4], a1n[4];
+            ldmatrix_x4(a0x, amax0 + koff);
+            ldmatrix_x4(a0n, amin0 + koff);
+            ldmatrix_x4(a1x, amax1 + koff);
+            ldmatrix_x4(a1n, amin1 + koff);
 #pragma unroll
-          for (int nt = 0; nt < NT; ++nt) {
-            const int q0 = (hbase + h) * gsz + min(nt * 8 + g, gsz - 1), q1 = (hbase + h1) * gsz + min(nt * 8 + g, gsz - 1);
-            const int f0 = (q0 * 8 + (kk ^ (q0 & 7))) * 4 + t, f1 = (q1 * 8 + (kk ^ (q1 & 7))) * 4 + t;
-            uint2 bp0 = sq2[f0], bp1 = sq2[f1], bn0, bn1;
-            if constexpr (QSPLIT) {
-              bn0 = sq2[neg_off + f0], bn1 = sq2[neg_off + f1];
-            } else {
-              bn0 = make_uint2(q_neg(bp0.x), q_neg(bp0.y)), bn1 = make_uint2(q_neg(bp1.x), q_neg(bp1.y));
-              bp0 = make_uint2(q_pos(bp0.x), q_pos(bp0.y)), bp1 = make_uint2(q_pos(bp1.x), q_pos(bp1.y));
+            for (int nt = 0; nt < NT; ++nt) {
+              const int q0 = (hbase + h) * gsz + min(nt * 8 + g, gsz - 1), q1 = (hbase + h1) * gsz + min(nt * 8 + g, gsz - 1);
+              const int f0 = (q0 * 8 + (kk ^ (q0 & 7))) * 4 + t, f1 = (q1 * 8 + (kk ^ (q1 & 7))) * 4 + t;
+              uint2 bp0 = sq2[f0], bp1 = sq2[f1], bn0, bn1;
+              if constexpr (QSPLIT) {
+                bn0 = sq2[neg_off + f0], bn1 = sq2[neg_off + f1];
+              } else {
+                bn0 = make_uint2(q_neg(bp0.x), q_neg(bp0.y)), bn1 = make_uint2(q_neg(bp1.x), q_neg(bp1.y));
+                bp0 = make_uint2(q_pos(bp0.x), q_pos(bp0.y)), bp1 = make_uint2(q_pos(bp1.x), q_pos(bp1.y));
+              }
+              mma_16816(cp[0][nt], a0x, bp0.x, bp0.y);
+              mma_16816(cn[0][nt], a0n, bn0.x, bn0.y);
+              mma_16816(cp[1][nt], a1x, bp1.x, bp1.y);
+              mma_16816(cn[1][nt], a1n, bn1.x, bn1.y);
             }
-            mma_16816(cp[0][nt], a0x, bp0.x, bp0.y);
-            mma_16816(cn[0][nt], a0n, bn0.x, bn0.y);
-            mma_16816(cp[1][nt], a1x, bp1.x, bp1.y);
-            mma_16816(cn[1][nt], a1n, bn1.x, bn1.y);
+          }
+          // c0:(page g, head 2t) c1:(g, 2t+1) c2:(g+8, 2t) c3:(g+8, 2t+1)
+#pragma unroll
+          for (int x = 0; x < 2; ++x) {
+            if (x == 1 && !two) break;
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+              float sc[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) sc[e] = round_bf16(round_bf16(cp[x][nt][e]) + round_bf16(cn[x][nt][e]));
+              const int col0 = nt * 8 + 2 * t;
+              if (col0 < gsz) best0 = fmaxf(best0, sc[0]), best1 = fmaxf(best1, sc[2]);
+              if (col0 + 1 < gsz) best0 = fmaxf(best0, sc[1]), best1 = fmaxf(best1, sc[3]);
+            }
           }
         }
-        // c0:(page g, head 2t) c1:(g, 2t+1) c2:(g+8, 2t) c3:(g+8, 2t+1)
-#pragma unroll
-        for (int x = 0; x < 2; ++x) {
-          if (x == 1 && !two) break;
-#pragma unroll
-          for (int nt = 0; nt < NT; ++nt) {
-            float sc[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) sc[e] = round_bf16(round_bf16(cp[x][nt][e]) + round_bf16(cn[x][nt][e]));
-            const int col0 = nt * 8 + 2 * t;
-            if (col0 < gsz) best0 = fmaxf(best0, sc[0]), best1 = fmaxf(best1, sc[2]);
-            if (col0 + 1 < gsz) best0 = fmaxf(best0, sc[1]), best1 = fmaxf(best1, sc[3]);
-          }
-        }
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&empty_bar[s]);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[s]);
       }  // part
       best0 = fmaxf(best0, __shfl_xor_sync(0xffffffffu, best0, 1));
       best0 = fmaxf(best0, __shfl_xor_sync(0xffffffffu, best0, 2));
       best1 = fmaxf(best1, __shfl_xor_sync(0xffffffffu, best1, 1));
       best1 = fmaxf(best1, __shfl_xor_sync(0xffffffffu, best1, 2));
       if (t == 0) {
-        // rows 8-15 of the tile are not pages when ppu == 8 (stale shared memory: never written out)
-        const int p0 = (d.unit_begin + j) * ppu + g, p1 = ppu > 8 ? p0 + 8 : p.n_cols;
+        const int p0 = (d.unit_begin + j) * kPage + g, p1 = p0 + 8;
         if (p0 < p.n_cols) {
           __nv_bfloat16 v = __float2bfloat16_rn(best0);
           srow[p0] = ((mask >> g) & 1u) ? *reinterpret_cast<uint16_t*>(&v) : (uint16_t)0xff80u;
@@ -807,29 +781,30 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
 // =========================================================================
 // Host launchers
 // =========================================================================
-int launch_quest_page_minmax(const void* k_cache, void* bounds_layer, const int32_t* slot_mapping,
-                             int n_tokens, int hkv, int64_t num_slots, cudaStream_t stream) {
+int launch_quest_page_minmax(const void* k_cache, void* bounds_layer, const int32_t* page_rec,
+                             const int32_t* slot_mapping, int n_tokens, int hkv, int64_t num_slots,
+                             int64_t num_chunks, cudaStream_t stream) {
   if (n_tokens <= 0) return 0;
   const int warps_per_block = 8;
   int blocks = (n_tokens + warps_per_block - 1) / warps_per_block;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  quest_page_minmax_kernel<<<blocks, warps_per_block * 32, 0, stream>>>(
-      (const __nv_bfloat16*)k_cache, (__nv_bfloat16*)bounds_layer, slot_mapping, n_tokens, hkv,
-      num_slots);
-  return check_launch("quest_page_minmax");
+  const cudaError_t e = launch_kernel(quest_page_minmax_kernel, dim3(blocks), dim3(warps_per_block * 32), 0, stream,
+                                      (const __nv_bfloat16*)k_cache, (__nv_bfloat16*)bounds_layer, page_rec,
+                                      slot_mapping, n_tokens, hkv, num_slots, num_chunks * kPage);
+  return e != cudaSuccess ? cuda_error("quest_page_minmax", e) : check_launch("quest_page_minmax");
 }
 
-int launch_quest_decode_page_complete(const void* k_cache_all, void* bounds_all,
+int launch_quest_decode_page_complete(const void* k_cache_all, void* bounds_all, const int32_t* page_rec,
                                       const int32_t* page_table, int64_t pt_stride,
                                       const int32_t* req_rows, const int32_t* seq_lens, int batch,
                                       int layers, int hkv, int64_t num_slots, int64_t num_pages,
-                                      cudaStream_t stream) {
+                                      int64_t num_chunks, cudaStream_t stream) {
   if (batch <= 0 || layers <= 0) return 0;
-  dim3 grid(batch, layers);
-  quest_decode_page_complete_kernel<<<grid, 128, 0, stream>>>(
-      (const __nv_bfloat16*)k_cache_all, (__nv_bfloat16*)bounds_all, page_table, pt_stride,
-      req_rows, seq_lens, hkv, num_slots, num_pages);
-  return check_launch("quest_decode_page_complete");
+  const cudaError_t e = launch_kernel(quest_decode_page_complete_kernel, dim3(batch, layers), dim3(128), 0, stream,
+                                      (const __nv_bfloat16*)k_cache_all, (__nv_bfloat16*)bounds_all, page_rec,
+                                      page_table, pt_stride, req_rows, seq_lens, hkv, num_slots, num_pages,
+                                      num_chunks * kPage);
+  return e != cudaSuccess ? cuda_error("quest_decode_page_complete", e) : check_launch("quest_decode_page_complete");
 }
 
 int launch_quest_select_pack(const void* scores, int64_t score_stride, int n_cols,
@@ -839,36 +814,19 @@ int launch_quest_select_pack(const void* scores, int64_t score_stride, int n_col
                              const int32_t* dense_table, int64_t dense_stride, int token_budget,
                              int page_budget_base, int out_width, cudaStream_t stream) {
   if (batch <= 0) return 0;
-  quest_select_pack_kernel<<<batch, 256, 0, stream>>>(
-      (const uint16_t*)scores, score_stride, n_cols, page_table, pt_stride, req_rows, context_lens,
-      k, packed_slots, out_stride, sparse_lens, selected_pages, dense_table, dense_stride,
-      token_budget, page_budget_base, out_width);
-  return check_launch("quest_select_pack");
+  const cudaError_t e = launch_kernel(quest_select_pack_kernel, dim3(batch), dim3(256), 0, stream,
+                                      (const uint16_t*)scores, score_stride, n_cols, page_table, pt_stride, req_rows,
+                                      context_lens, k, packed_slots, out_stride, sparse_lens, selected_pages,
+                                      dense_table, dense_stride, token_budget, page_budget_base, out_width);
+  return e != cudaSuccess ? cuda_error("quest_select_pack", e) : check_launch("quest_select_pack");
 }
 
-struct ScorePlan {
-  int stages, consumers, producers;
-};
-
-// (stages, consumer warps, producer warps) for a ring next to `q_copies` staged copies of q; stages == 0:
-// no room.  producers | stages always; consumers | stages unless the fills are tagged per head split
-// (see the kernel).  Prefer more producers + consumers, then more stages.
-static ScorePlan score_plan(const ScoreParams& p, bool fused, int q_copies) {
+// Ring stages next to `q_copies` staged copies of q (0: no room).
+static int score_stages(const ScoreParams& p, bool fused, int q_copies) {
   const int fixed = score_smem_layout(0, p.hq, p.hkv, p.hsplit, p.batch, fused, q_copies).total + 256;  // + static smem
-  const int stage_bytes = p.ppu * score_rec_stride(p.hkv / p.hsplit);
-  int stages = (kScoreMaxSmem - fixed) / (stage_bytes + 20);
+  int stages = (kScoreMaxSmem - fixed) / (score_stage_bytes(p.hkv, p.hsplit) + 20);
   if (stages > 24) stages = 24;
-  if (stages < 2) return ScorePlan{0, 0, 0};
-  ScorePlan best{stages, 1, 1};
-  for (int s2 = stages; s2 >= 2 && s2 >= stages - 3; --s2) {
-    int c = 1, pr = 1;
-    for (int d = kScoreConsumerWarps; d >= 1; --d)
-      if (s2 % d == 0 || p.hsplit > 1) { c = d; break; }
-    for (int d = kScoreProducerWarps; d >= 1; --d)
-      if (s2 % d == 0) { pr = d; break; }
-    if (c + 2 * pr > best.consumers + 2 * best.producers || s2 == stages) best = ScorePlan{s2, c, pr};
-  }
-  return best;
+  return stages < 2 ? 0 : stages;
 }
 
 template <int NT, bool FUSED, bool QSPLIT>
@@ -876,31 +834,24 @@ static cudaError_t launch_score_kernel(const ScoreParams& p, int grid, size_t sm
   auto kern = quest_page_score_kernel<NT, FUSED, QSPLIT>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  kern<<<grid, kScoreThreads, smem, stream>>>(p);
-  return cudaSuccess;
+  return launch_kernel(kern, dim3(grid), dim3(kScoreThreads), smem, stream, p);
 }
 
 template <int NT, bool FUSED>
 static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
-  p.hsplit = score_head_split(p.hkv);
-  if (const int t = tuning(kTuneScoreSplit); t > 0 && p.hkv % t == 0) p.hsplit = t;  // experiments
-  p.ppu = score_pages_per_unit(p.hkv, p.hsplit);
-  const int stage_bytes = p.ppu * score_rec_stride(p.hkv / p.hsplit);
-  const ScorePlan one = score_plan(p, FUSED, 1), two = score_plan(p, FUSED, 2);
-  if (one.stages == 0) {
+  p.hsplit = bounds_head_split(p.hkv);
+  const int stage_bytes = score_stage_bytes(p.hkv, p.hsplit);
+  const int one = score_stages(p, FUSED, 1), two = score_stages(p, FUSED, 2);
+  if (one == 0) {
     set_error("quest_page_score: %d q heads / %d kv heads / batch %d leave no shared memory for the bounds ring",
               p.hq, p.hkv, p.batch);
     return 1;
   }
   // q+ and q- are both staged only if that costs nothing of the ring
-  bool qsplit = two.stages == one.stages && two.producers == one.producers && two.consumers == one.consumers;
+  bool qsplit = two == one;
   if (tuning(kTuneScoreQ) == 1) qsplit = false;
-  if (tuning(kTuneScoreQ) == 2 && two.stages > 0) qsplit = true;
-  const ScorePlan plan = qsplit ? two : one;
-  const int stages = plan.stages;
-  p.stages = stages;
-  p.consumers = plan.consumers;
-  p.producers = plan.producers;
+  if (tuning(kTuneScoreQ) == 2 && two > 0) qsplit = true;
+  p.stages = qsplit ? two : one;
   // Row groups (sched.cuh): by default every row is its own group, i.e. gridDim/batch CTAs start on
   // each row and q is staged once per CTA; fewer groups make rows end at staggered times.
   int groups = tuning(kTuneScoreGroups);
@@ -908,49 +859,53 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
   if (groups > p.batch) groups = p.batch;
   if (groups < 1) groups = 1;
   p.groups = groups;
-  p.bulk = (tuning(kTuneScoreCopy) == 1 && p.hsplit == 1) ? 0 : 1;
-  // a claim's round trip costs 3-4 us under load: one batch must be worth that much streaming
-  // (~128 KB per SM), or the scheduler cannot keep the ring fed when units are small (few KV heads)
+  // A claimed chunk is ~64 KB of bounds (what is claimed cannot be stolen: big chunks make the launch's tail
+  // ragged); a claim's round trip costs 3-4 us under load, so one batch of chunks is worth >= ~128 KB of
+  // streaming, or the scheduler cannot keep the ring fed.
   {
-    const int chunk_bytes = kChunkUnits * stage_bytes * p.hsplit;
+    const int unit_bytes = stage_bytes * p.hsplit;
+    int cu = tuning(kTuneChunkUnits) > 0 ? tuning(kTuneChunkUnits) : (64 * 1024) / unit_bytes;
+    p.chunk_units = cu < 1 ? 1 : (cu > kMaxChunkUnits ? kMaxChunkUnits : cu);
+    const int chunk_bytes = p.chunk_units * unit_bytes;
     int mb = (128 * 1024 + chunk_bytes - 1) / chunk_bytes;
     if (mb < kMinBatch) mb = kMinBatch;
     p.min_batch = tuning(kTuneMinBatch) > 0 ? tuning(kTuneMinBatch) : mb;
   }
   p.share_div = tuning(kTuneShareDiv) > 0 ? tuning(kTuneShareDiv) : 4;
-  const size_t smem = score_smem_layout(stages, p.hq, p.hkv, p.hsplit, p.batch, FUSED, qsplit ? 2 : 1).total;
-  const int64_t units_row = (p.n_cols + p.ppu - 1) / p.ppu;
-  const int64_t max_chunks = (int64_t)p.batch * ((units_row + kChunkUnits - 1) / kChunkUnits);
+  p.no_math = tuning(kTuneNoMath) == 1;
+  const size_t smem = score_smem_layout(p.stages, p.hq, p.hkv, p.hsplit, p.batch, FUSED, qsplit ? 2 : 1).total;
+  const int64_t units_row = (p.n_cols + kPage - 1) / kPage;
+  const int64_t max_chunks = (int64_t)p.batch * ((units_row + p.chunk_units - 1) / p.chunk_units);
   int grid = max_ctas();
   if ((int64_t)grid > max_chunks) grid = (int)max_chunks;
   if (grid < 1) grid = 1;
   const cudaError_t e = qsplit ? launch_score_kernel<NT, FUSED, true>(p, grid, smem, stream)
                                : launch_score_kernel<NT, FUSED, false>(p, grid, smem, stream);
-  if (e != cudaSuccess) return cuda_error("quest_page_score smem attr", e);
+  if (e != cudaSuccess) return cuda_error("quest_page_score launch", e);
   return check_launch(FUSED ? "quest_score_select_pack" : "quest_page_score");
 }
 
 static ScoreParams make_score_params(const void* q, int64_t q_stride_b, const void* bounds,
-                                     int64_t num_pages, const int32_t* page_table, int64_t pt_stride,
+                                     int64_t num_chunks, const int32_t* unit_table, int64_t ut_stride,
                                      const int32_t* req_rows, const int32_t* context_lens,
                                      void* scores, int64_t score_stride, int batch, int hq, int hkv,
                                      int n_cols) {
   ScoreParams p{};
   p.q = (const __nv_bfloat16*)q; p.q_stride_b = q_stride_b;
-  p.bounds = (const __nv_bfloat16*)bounds; p.num_pages = num_pages;
-  p.page_table = page_table; p.pt_stride = pt_stride; p.req_rows = req_rows;
+  p.bounds = (const __nv_bfloat16*)bounds; p.num_chunks = num_chunks;
+  p.unit_table = unit_table; p.ut_stride = ut_stride; p.req_rows = req_rows;
   p.context_lens = context_lens; p.scores = (uint16_t*)scores; p.score_stride = score_stride;
   p.batch = batch; p.hq = hq; p.hkv = hkv; p.n_cols = n_cols;
   p.dbg_times = debug_times_buffer();
   return p;
 }
 
-int launch_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds, int64_t num_pages,
-                            const int32_t* page_table, int64_t pt_stride, const int32_t* req_rows,
+int launch_quest_page_score(const void* q, int64_t q_stride_b, const void* bounds, int64_t num_chunks,
+                            const int32_t* unit_table, int64_t ut_stride, const int32_t* req_rows,
                             const int32_t* context_lens, void* scores, int64_t score_stride,
                             int batch, int hq, int hkv, int n_cols, int32_t* sched, cudaStream_t stream) {
   if (batch <= 0 || n_cols <= 0) return 0;
-  ScoreParams p = make_score_params(q, q_stride_b, bounds, num_pages, page_table, pt_stride, req_rows,
+  ScoreParams p = make_score_params(q, q_stride_b, bounds, num_chunks, unit_table, ut_stride, req_rows,
                                     context_lens, scores, score_stride, batch, hq, hkv, n_cols);
   p.sched = sched;
   return hq / hkv <= 8 ? launch_score_variant<1, false>(p, stream)
@@ -958,22 +913,33 @@ int launch_quest_page_score(const void* q, int64_t q_stride_b, const void* bound
 }
 
 int launch_quest_score_select_pack(const void* q, int64_t q_stride_b, const void* bounds,
-                                   int64_t num_pages, const int32_t* page_table, int64_t pt_stride,
+                                   int64_t num_chunks, const int32_t* unit_table, int64_t ut_stride,
+                                   const int32_t* page_table, int64_t pt_stride,
                                    const int32_t* req_rows, const int32_t* context_lens,
                                    void* scores, int64_t score_stride, int batch, int hq, int hkv,
                                    int n_cols, int k, int32_t* packed_slots, int64_t out_stride,
                                    int32_t* sparse_lens, int32_t* selected_pages, int32_t* tickets,
                                    const FusedStore* store, cudaStream_t stream) {
-  if (batch <= 0 || n_cols <= 0) return 0;
-  ScoreParams p = make_score_params(q, q_stride_b, bounds, num_pages, page_table, pt_stride, req_rows,
+  if (batch <= 0) return 0;
+  if (n_cols <= 0) {
+    // nothing to score: the step's rows must still reach the cache
+    if (store == nullptr) return 0;
+    return launch_store_kv_minmax(store->key, store->k_stride, store->value, store->v_stride, store->k_cache,
+                                  store->v_cache, store->slot_mapping, batch, hkv, store->num_slots,
+                                  store->refresh_bounds ? const_cast<void*>(bounds) : nullptr, store->page_rec,
+                                  num_chunks, stream);
+  }
+  ScoreParams p = make_score_params(q, q_stride_b, bounds, num_chunks, unit_table, ut_stride, req_rows,
                                     context_lens, scores, score_stride, batch, hq, hkv, n_cols);
+  p.page_table = page_table; p.pt_stride = pt_stride;
   p.k = k; p.packed_slots = packed_slots; p.out_stride = out_stride; p.sparse_lens = sparse_lens;
   p.selected_pages = selected_pages; p.sched = tickets;
   if (store != nullptr) {
     p.store = StoreArgs{(const __nv_bfloat16*)store->key, store->k_stride, (const __nv_bfloat16*)store->value,
                         store->v_stride, (__nv_bfloat16*)store->k_cache, (__nv_bfloat16*)store->v_cache,
                         store->slot_mapping, store->num_slots,
-                        store->refresh_bounds ? (__nv_bfloat16*)const_cast<void*>(bounds) : nullptr};
+                        store->refresh_bounds ? (__nv_bfloat16*)const_cast<void*>(bounds) : nullptr,
+                        store->page_rec, num_chunks * kPage};
     p.store_tokens = batch;
   }
   return hq / hkv <= 8 ? launch_score_variant<1, true>(p, stream)

@@ -1,14 +1,16 @@
-// Dynamic chunk scheduling shared by the persistent page-scoring and decode-attention kernels.
+// Dynamic chunk scheduling of the persistent page-scoring kernel.
 //
 // Why: with one equal static cut per SM the same SMs are always served ~20 % slower by the memory
 // system (profiles/r1_c_ncu_summary.md) and the fast ones idle.  Here the work of a launch is
-// rows x chunks (a chunk = up to kChunkUnits consecutive units of one row) claimed with atomicAdd on
-// the row's counter.  A CTA starts on its home rows (group = blockIdx % groups; rows group,
-// group + groups, ...) and claims guided batches there: half of its fair share of what is left, so
+// rows x chunks (a chunk = up to `cu` consecutive units of one row, sized to ~64 KB by the launcher)
+// claimed with atomicAdd on the row's counter.  A CTA starts on its home rows (group = blockIdx %
+// groups; rows group, group + groups, ...).  Its FIRST batch on its first home row is static (the
+// l-th home CTA of the row owns chunks [l*m0, (l+1)*m0): no atomic round trip before the first byte
+// moves); after that it claims guided batches: a fraction of its fair share of what is left, so
 // batches are large while a row is far from done (the claim's round trip hides behind queued work)
-// and shrink to one chunk near the end (little is hoarded when the row runs dry).  Once its home
-// rows are exhausted (or if it has none: gridDim is not a multiple of the groups) it steals a few
-// chunks at a time from the row with the most chunks left.
+// and shrink near the end (little is hoarded when the row runs dry).  Once its home rows are
+// exhausted (or if it has none: gridDim is not a multiple of the groups) it steals a few chunks at a
+// time from the row with the most chunks left.
 //
 // One scheduler warp per CTA claims and posts descriptors into a shared-memory queue (full/empty
 // mbarrier pair per slot); every producer and consumer warp reads every descriptor in order.
@@ -18,14 +20,14 @@
 
 namespace svb200 {
 
-constexpr int kChunkUnits = 2;   // units per claimed chunk (one table lookup per lane: 2 x 16 entries)
+constexpr int kMaxChunkUnits = 8;  // units per claimed chunk at most (a producer lane looks up one unit's chunk id)
 constexpr int kSchedQueue = 16;  // descriptor slots (sched_run's `depth` <= kSchedQueue bounds what is actually posted ahead)
 constexpr int kMinBatch = 2;     // chunks per claim at least (an atomicAdd costs 3-4 us under load; one more is in flight)
 
 struct ChunkDesc {
   int row;         // -1: end of work
   int unit_begin;  // first unit inside the row
-  int n_units;     // 1..kChunkUnits, | aux << 8 (aux: what reserve(row) returned for this visit of the row)
+  int n_units;     // 1..kMaxChunkUnits, | aux << 8 (aux: what reserve(row) returned for this visit of the row)
   int unit_base;   // CTA-local running unit index of the chunk's first unit (ring stage = index % S)
   __device__ __forceinline__ int units() const { return n_units & 0xff; }
   __device__ __forceinline__ int aux() const { return n_units >> 8; }
@@ -74,7 +76,7 @@ struct ReserveNone {
   __device__ __forceinline__ int operator()(int) const { return 0; }
 };
 template <class UnitsOfRow, class Reserve = ReserveNone>
-__device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int rows, int groups,
+__device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int rows, int groups, int cu,
                           int min_batch, int share_div, int depth, UnitsOfRow units_of_row,
                           Reserve reserve = Reserve(), unsigned long long* t_last_claim = nullptr) {
   const int lane = threadIdx.x & 31;
@@ -97,28 +99,47 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
   // batch is posted
   const int share = max(1, (int)gridDim.x / groups);  // CTAs that start on the same rows
   constexpr int kStealVisit = 12;  // chunks a thief takes per visit of a row before it looks again
-  auto drain = [&](int row, bool guided) -> bool {  // false: reserve() refused the row
+  auto chunks_of = [&](int row) { return (units_of_row(row) + cu - 1) / cu; };
+  auto guided_batch = [&](int left) { return max(min_batch, left / (share_div * share)); };
+  // chunks of `row` that are handed out statically (first batch of the CTAs whose first home row it is);
+  // the row's counter counts the chunks claimed BEYOND them.  Every CTA computes the same value.
+  auto static_chunks = [&](int row) {
+    if (row >= groups || share * groups > (int)gridDim.x) return 0;
+    const int d = chunks_of(row);
+    return min(d, share * guided_batch(d));
+  };
+  auto drain = [&](int row, bool guided, bool first_home) -> bool {  // false: reserve() refused the row
     const int nu = units_of_row(row);
-    const int d = (nu + kChunkUnits - 1) / kChunkUnits;
+    const int d = (nu + cu - 1) / cu;
     if (d == 0) return true;
-    if (!guided && __ldcg(next_chunk + row) >= d) return true;  // thief, nothing left: do not reserve
+    const int base = static_chunks(row);
+    if (!guided && base + __ldcg(next_chunk + row) >= d) return true;  // thief, nothing left: do not reserve
     aux = reserve(row);
     if (aux < 0) return false;
-    auto batch = [&](int left) { return guided ? max(min_batch, left / (share_div * share)) : min_batch; };
+    auto batch = [&](int left) { return guided ? guided_batch(left) : min_batch; };
     int m = batch(d), j = 0, taken = 0;
-    if (lane == 0) j = atomicAdd(next_chunk + row, m);
-    j = __shfl_sync(0xffffffffu, j, 0);
+    if (first_home) {
+      j = (int)(blockIdx.x / (unsigned)groups) * m;  // static: no round trip before the first copy
+      if (j >= base) first_home = false;             // (the row is shorter than the static pieces)
+    }
+    if (!first_home) {
+      if (lane == 0) j = base + atomicAdd(next_chunk + row, m);
+      j = __shfl_sync(0xffffffffu, j, 0);
+    }
     while (j < d) {
       if (t_last_claim && lane == 0) *t_last_claim = global_timer_ns();
-      const int end = min(j + m, d);
+      // a static piece ends where the static region does; what is left for claims starts behind that region
+      const int end = min(j + m, first_home ? base : d);
+      const int claimed_to = first_home ? base : end;
+      first_home = false;
       taken += end - j;
-      const int left = (guided || taken < kStealVisit) ? d - end : 0;
+      const int left = (guided || taken < kStealVisit) ? d - claimed_to : 0;
       int m2 = 0, j2 = 0;
       if (left > 0) {
         m2 = batch(left);
-        if (lane == 0) j2 = atomicAdd(next_chunk + row, m2);
+        if (lane == 0) j2 = base + atomicAdd(next_chunk + row, m2);
       }
-      for (int c = j; c < end; ++c) post(row, c * kChunkUnits, min(kChunkUnits, nu - c * kChunkUnits));
+      for (int c = j; c < end; ++c) post(row, c * cu, min(cu, nu - c * cu));
       if (left <= 0) return true;
       j = __shfl_sync(0xffffffffu, j2, 0);
       m = m2;
@@ -128,7 +149,7 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
   // share * groups CTAs own home rows; the others help wherever most is left from the start
   if ((int)blockIdx.x < share * groups) {
     const int grp = (int)(blockIdx.x % (unsigned)groups);
-    for (int row = grp; row < rows; row += groups) drain(row, true);
+    for (int row = grp; row < rows; row += groups) drain(row, true, row == grp);
   }
   // steal: the row with the most chunks left (counters only grow: a stale read can only show too much)
   while (true) {
@@ -138,7 +159,7 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
       if (r < rows) {
         const int rr = (r + (int)blockIdx.x) % rows;
         const int nu = units_of_row(rr);
-        const int left = (nu + kChunkUnits - 1) / kChunkUnits - __ldcg(next_chunk + rr);
+        const int left = (nu + cu - 1) / cu - static_chunks(rr) - __ldcg(next_chunk + rr);
         if (left > best) best = left, best_row = rr;
       }
     }
@@ -149,7 +170,7 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
       if (ob > best || (ob == best && orow > best_row)) best = ob, best_row = orow;
     }
     if (best <= 0) break;
-    if (!drain(best_row, false)) break;  // contributor slots of that row are used up: stop stealing
+    if (!drain(best_row, false, false)) break;  // contributor slots of that row are used up: stop stealing
   }
   post(-1, 0, 0);
 }

@@ -17,11 +17,12 @@ __global__ void __launch_bounds__(128) store_kv_minmax_kernel(StoreArgs a, int h
 
 int launch_store_kv_minmax(const void* key, int64_t k_stride, const void* value, int64_t v_stride,
                            void* k_cache, void* v_cache, const int32_t* slot_mapping, int n_tokens,
-                           int hkv, int64_t num_slots, void* bounds_layer, cudaStream_t stream) {
+                           int hkv, int64_t num_slots, void* bounds_layer, const int32_t* page_rec,
+                           int64_t num_chunks, cudaStream_t stream) {
   if (n_tokens <= 0) return 0;
   const StoreArgs a{(const __nv_bfloat16*)key, k_stride, (const __nv_bfloat16*)value, v_stride,
                     (__nv_bfloat16*)k_cache, (__nv_bfloat16*)v_cache, slot_mapping, num_slots,
-                    (__nv_bfloat16*)bounds_layer};
+                    (__nv_bfloat16*)bounds_layer, page_rec, num_chunks * kPage};
   store_kv_minmax_kernel<<<n_tokens, 128, 0, stream>>>(a, hkv);
   return check_launch("store_kv_minmax");
 }

@@ -6,6 +6,7 @@
 // decode token completes it).
 #pragma once
 
+#include "bounds_layout.cuh"
 #include "common.cuh"
 
 namespace svb200 {
@@ -19,7 +20,9 @@ struct StoreArgs {
   __nv_bfloat16* v_cache;
   const int32_t* slot_mapping;  // [tokens]
   int64_t num_slots;
-  __nv_bfloat16* bounds;  // page records of this layer, or null: no refresh
+  __nv_bfloat16* bounds;  // bounds chunks of this layer (bounds_layout.cuh), or null: no refresh
+  const int32_t* page_rec;  // physical page -> bounds record (-1: the page belongs to no row), with bounds
+  int64_t num_recs;         // 16 * number of bounds chunks
 };
 
 // Thread `t` of `nthr` moves every nthr-th 16-byte vector of token `tok`.  Bounds refresh: valid when no
@@ -57,9 +60,12 @@ __device__ __forceinline__ void store_kv_token(const StoreArgs& a, int tok, int 
           }
         }
       }
-      __nv_bfloat16* out = a.bounds + page * 2 * row_elems;
-      *reinterpret_cast<uint4*>(out + v * 8) = mx;
-      *reinterpret_cast<uint4*>(out + row_elems + v * 8) = mn;
+      const int rec = a.page_rec[page];
+      if (rec >= 0 && rec < a.num_recs) {
+        const int hs = bounds_head_split(hkv);
+        *reinterpret_cast<uint4*>(a.bounds + bounds_seg_offset(rec, 0, v >> 4, v & 15, hkv, hs)) = mx;
+        *reinterpret_cast<uint4*>(a.bounds + bounds_seg_offset(rec, 1, v >> 4, v & 15, hkv, hs)) = mn;
+      }
     }
   }
 }

@@ -93,23 +93,23 @@ class B200SparseDecodeProvider:
         d = self._stats.setdefault(path, {})
         d[key] = d.get(key, 0) + 1
 
-    def quest_select(self, q, bounds_layer, page_table, req_rows, context_lens, *, n_cols, num_kv_heads,
+    def quest_select(self, q, bounds_layer, unit_table, page_table, req_rows, context_lens, *, n_cols, num_kv_heads,
                      prev_budget, scores, packed_slots, sparse_lens, tickets, selected_pages=None,
                      dense_token_table=None, token_budget=0, page_budget_base=0, out_width=0,
                      store: ops.DecodeStore | None = None) -> None:
         """``store``: the step's new K/V rows, not yet in the cache.  The long-text launch writes them itself;
         the two-launch (mixed) path stores them first with the stand-alone kernel."""
         if dense_token_table is None:
-            ops.quest_score_select_pack(q, bounds_layer, page_table, req_rows, context_lens, n_cols, num_kv_heads,
+            ops.quest_score_select_pack(q, bounds_layer, unit_table, page_table, req_rows, context_lens, n_cols, num_kv_heads,
                                         prev_budget, scores, packed_slots, sparse_lens, tickets, selected_pages,
                                         store=store)
             self._count("quest_store_score_select_pack_fused" if store is not None else "quest_score_select_pack_fused")
         else:
             if store is not None:
                 ops.store_kv_minmax(store.key, store.value, store.k_cache, store.v_cache, store.slot_mapping,
-                                    bounds_layer if store.refresh_bounds else None)
+                                    bounds_layer if store.refresh_bounds else None, store.page_rec)
                 self._count("store_kv_minmax")
-            ops.quest_page_score(q, bounds_layer, page_table, req_rows, context_lens, n_cols, num_kv_heads, scores,
+            ops.quest_page_score(q, bounds_layer, unit_table, req_rows, context_lens, n_cols, num_kv_heads, scores,
                                  sched=tickets)
             ops.quest_select_pack(scores, n_cols, page_table, req_rows, context_lens, prev_budget, packed_slots,
                                   sparse_lens, selected_pages, dense_token_table, token_budget, page_budget_base,
@@ -118,11 +118,13 @@ class B200SparseDecodeProvider:
             self._count("quest_select_pack_mixed")
 
     def decode(self, q, k_cache, v_cache, slot_table, req_rows, seq_lens, *, out, workspace, max_len: int,
-               attn_score=None) -> torch.Tensor:
+               attn_score=None, comm=None, gathered=None) -> torch.Tensor:
+        """``comm`` / ``gathered``: tensor-parallel push epilogue (ops.sparse_decode_attn)."""
         ops.sparse_decode_attn(q, k_cache, v_cache, slot_table, req_rows, seq_lens, out=out, workspace=workspace,
                                max_len=max_len, attn_score=attn_score,
-                               heads_per_cta=self.heads_per_cta(int(k_cache.shape[1])))
-        self._count("sparse_decode_attn_score2d" if attn_score is not None else "sparse_decode_attn")
+                               heads_per_cta=self.heads_per_cta(int(k_cache.shape[1])), comm=comm, gathered=gathered)
+        self._count(("sparse_decode_attn_score2d" if attn_score is not None else "sparse_decode_attn")
+                    + ("_tp_push" if comm is not None and comm.world > 1 else ""))
         return out
 
     def runtime_kernel_stats(self) -> dict[str, object]:

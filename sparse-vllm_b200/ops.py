@@ -47,12 +47,73 @@ def _q(t: torch.Tensor, name: str) -> tuple[int, int, int]:
     return int(t.shape[0]), int(t.shape[1]), int(t.stride(0))
 
 
+def bounds_head_split(hkv: int) -> int:
+    """Ring stages per 16-page unit: the smallest divisor of Hkv leaving <= 4 heads (csrc/bounds_layout.cuh)."""
+    hkv = int(hkv)
+    for d in range(1, hkv):
+        if hkv % d == 0 and hkv // d <= 4:
+            return d
+    return 1 if hkv <= 4 else hkv
+
+
+def bounds_shape(num_chunks: int, hkv: int) -> tuple[int, ...]:
+    """One layer of Quest bounds: ``[chunks, hs, 16 pages, 2 (max, min), Hkv/hs, 128]`` (bounds_layout.cuh)."""
+    hs = bounds_head_split(hkv)
+    return (int(num_chunks), hs, PAGE, 2, int(hkv) // hs, HEAD_DIM)
+
+
+def alloc_bounds(num_chunks: int, hkv: int, device, layers: int | None = None) -> torch.Tensor:
+    shape = bounds_shape(num_chunks, hkv)
+    return torch.zeros(shape if layers is None else (int(layers), *shape), dtype=torch.bfloat16, device=device)
+
+
 def _bounds_layer(t: torch.Tensor, hkv: int, name: str = "bounds_layer") -> int:
-    """[pages, 2, Hkv, 128] bf16 contiguous -> num_pages."""
+    """Validates one layer of bounds chunks -> num_chunks."""
     require_cuda(t, name, torch.bfloat16)
-    if t.dim() != 4 or tuple(t.shape[1:]) != (2, hkv, HEAD_DIM) or not t.is_contiguous():
-        raise ValueError(f"{name} must be a contiguous [pages, 2, {hkv}, {HEAD_DIM}] tensor, got {tuple(t.shape)}.")
+    if t.dim() != 6 or tuple(t.shape[1:]) != bounds_shape(0, hkv)[1:] or not t.is_contiguous():
+        raise ValueError(f"{name} must be a contiguous [chunks, {', '.join(map(str, bounds_shape(0, hkv)[1:]))}] tensor "
+                         f"(ops.alloc_bounds), got {tuple(t.shape)}.")
     return int(t.shape[0])
+
+
+def _swizzle_index(page_in_chunk: torch.Tensor) -> torch.Tensor:
+    """[P] -> [P, 16]: position of 16-byte segment s of a row of page p is s ^ (p & 7)."""
+    seg = torch.arange(16, device=page_in_chunk.device)
+    return seg[None, :] ^ (page_in_chunk[:, None] & 7)
+
+
+def pack_bounds(page_major: torch.Tensor, page_rec: torch.Tensor, bounds_layer: torch.Tensor) -> torch.Tensor:
+    """Import page-major bounds ``[P, 2, Hkv, 128]`` (the reference's ``metadata_cache`` order, indexed by
+    physical page) into this provider's chunk layout; pages with ``page_rec < 0`` are skipped.  Host-side
+    indexing utility (tests, migration of an existing cache), not a kernel of the hot path."""
+    p_total, _, hkv, _ = page_major.shape
+    hs = bounds_head_split(hkv)
+    hh = hkv // hs
+    rec = page_rec.to(torch.long)
+    pages = torch.nonzero(rec >= 0, as_tuple=False).flatten()
+    rec = rec[pages]
+    chunk, pg = rec >> 4, rec & 15
+    x = page_major[pages].reshape(len(pages), 2, hs, hh, 16, 8)
+    idx = _swizzle_index(pg)[:, None, None, None, :, None].expand(len(pages), 2, hs, hh, 16, 8)
+    x = x.gather(4, idx)  # out[.., s, :] = in[.., s ^ (p & 7), :]
+    bounds_layer[chunk, :, pg] = x.permute(0, 2, 1, 3, 4, 5).reshape(len(pages), hs, 2, hh, HEAD_DIM)
+    return bounds_layer
+
+
+def unpack_bounds(bounds_layer: torch.Tensor, page_rec: torch.Tensor) -> torch.Tensor:
+    """Inverse of ``pack_bounds``: ``[P, 2, Hkv, 128]`` indexed by physical page (zeros where unassigned)."""
+    _, hs, _, _, hh, _ = bounds_layer.shape
+    hkv = hs * hh
+    out = torch.zeros((int(page_rec.numel()), 2, hkv, HEAD_DIM), dtype=bounds_layer.dtype, device=bounds_layer.device)
+    rec = page_rec.to(torch.long)
+    pages = torch.nonzero(rec >= 0, as_tuple=False).flatten()
+    rec = rec[pages]
+    chunk, pg = rec >> 4, rec & 15
+    x = bounds_layer[chunk, :, pg].reshape(len(pages), hs, 2, hh, 16, 8)
+    idx = _swizzle_index(pg)[:, None, None, None, :, None].expand(len(pages), hs, 2, hh, 16, 8)
+    x = x.gather(4, idx)
+    out[pages] = x.permute(0, 2, 1, 3, 4, 5).reshape(len(pages), 2, hkv, HEAD_DIM)
+    return out
 
 
 def sm_count() -> int:
@@ -60,37 +121,46 @@ def sm_count() -> int:
 
 
 # ----------------------------------------------------------------------------- Quest bounds
-def quest_page_minmax(k_cache: torch.Tensor, bounds_layer: torch.Tensor, slot_mapping: torch.Tensor) -> None:
+def quest_page_minmax(k_cache: torch.Tensor, bounds_layer: torch.Tensor, page_rec: torch.Tensor,
+                      slot_mapping: torch.Tensor) -> None:
     """Rebuild the bounds of every page completed by ``slot_mapping`` (svb200_quest_page_minmax)."""
     num_slots, hkv = _kv_layer(k_cache, "k_cache")
-    _bounds_layer(bounds_layer, hkv)
-    _i32(slot_mapping, "slot_mapping")
+    num_chunks = _bounds_layer(bounds_layer, hkv)
+    _i32(slot_mapping, "slot_mapping"); _page_rec(page_rec, num_slots)
     lib = _native.load()
-    check(lib.svb200_quest_page_minmax(ptr(k_cache), ptr(bounds_layer), ptr(slot_mapping),
+    check(lib.svb200_quest_page_minmax(ptr(k_cache), ptr(bounds_layer), num_chunks, ptr(page_rec), ptr(slot_mapping),
                                        int(slot_mapping.numel()), hkv, num_slots,
                                        current_stream_ptr(k_cache.device)), "svb200_quest_page_minmax")
 
 
-def quest_decode_page_complete(k_cache_all: torch.Tensor, bounds_all: torch.Tensor, page_table: torch.Tensor,
-                               req_rows: torch.Tensor, seq_lens: torch.Tensor) -> None:
+def _page_rec(page_rec: torch.Tensor, num_slots: int) -> None:
+    _i32(page_rec, "page_rec")
+    if page_rec.dim() != 1 or int(page_rec.numel()) * PAGE < num_slots:
+        raise ValueError(f"page_rec must be a 1-D int32 tensor with one entry per physical page "
+                         f"(>= {num_slots // PAGE}), got {tuple(page_rec.shape)}.")
+
+
+def quest_decode_page_complete(k_cache_all: torch.Tensor, bounds_all: torch.Tensor, page_rec: torch.Tensor,
+                               page_table: torch.Tensor, req_rows: torch.Tensor, seq_lens: torch.Tensor) -> None:
     """All-layer refresh of pages completed by this decode step (svb200_quest_decode_page_complete).
 
-    k_cache_all [L, slots, Hkv, 128], bounds_all [L, pages, 2, Hkv, 128]."""
+    k_cache_all [L, slots, Hkv, 128], bounds_all [L, chunks, ...] (ops.alloc_bounds(layers=L))."""
     require_cuda(k_cache_all, "k_cache_all", torch.bfloat16)
     require_cuda(bounds_all, "bounds_all", torch.bfloat16)
     if k_cache_all.dim() != 4 or not k_cache_all.is_contiguous() or k_cache_all.shape[3] != HEAD_DIM:
         raise ValueError(f"k_cache_all must be contiguous [L, slots, Hkv, {HEAD_DIM}], got {tuple(k_cache_all.shape)}.")
     layers, num_slots, hkv, _ = (int(x) for x in k_cache_all.shape)
-    if bounds_all.dim() != 5 or not bounds_all.is_contiguous() or tuple(bounds_all.shape[2:]) != (2, hkv, HEAD_DIM) \
-            or int(bounds_all.shape[0]) != layers:
-        raise ValueError(f"bounds_all must be contiguous [L, pages, 2, Hkv, {HEAD_DIM}], got {tuple(bounds_all.shape)}.")
-    num_pages = int(bounds_all.shape[1])
-    _i32(page_table, "page_table"); _i32(req_rows, "req_rows"); _i32(seq_lens, "seq_lens")
+    if bounds_all.dim() != 7 or int(bounds_all.shape[0]) != layers:
+        raise ValueError(f"bounds_all must be [L={layers}, chunks, ...] (ops.alloc_bounds), got {tuple(bounds_all.shape)}.")
+    num_chunks = _bounds_layer(bounds_all[0], hkv, "bounds_all[0]")
+    if not bounds_all.is_contiguous():
+        raise ValueError("bounds_all must be contiguous.")
+    _i32(page_table, "page_table"); _i32(req_rows, "req_rows"); _i32(seq_lens, "seq_lens"); _page_rec(page_rec, num_slots)
     lib = _native.load()
     check(lib.svb200_quest_decode_page_complete(
-        ptr(k_cache_all), ptr(bounds_all), ptr(page_table), _rows_stride(page_table, "page_table"),
-        ptr(req_rows), ptr(seq_lens), int(req_rows.numel()), layers, hkv, num_slots, num_pages,
-        current_stream_ptr(k_cache_all.device)), "svb200_quest_decode_page_complete")
+        ptr(k_cache_all), ptr(bounds_all), num_chunks, ptr(page_rec), ptr(page_table),
+        _rows_stride(page_table, "page_table"), ptr(req_rows), ptr(seq_lens), int(req_rows.numel()), layers, hkv,
+        num_slots, num_slots // PAGE, current_stream_ptr(k_cache_all.device)), "svb200_quest_decode_page_complete")
 
 
 # ----------------------------------------------------------------------------- Quest select
@@ -98,7 +168,7 @@ def score_row_stride(n_cols: int) -> int:
     return (int(n_cols) + 7) // 8 * 8
 
 
-def quest_page_score(q: torch.Tensor, bounds_layer: torch.Tensor, page_table: torch.Tensor,
+def quest_page_score(q: torch.Tensor, bounds_layer: torch.Tensor, unit_table: torch.Tensor,
                      req_rows: torch.Tensor, context_lens: torch.Tensor, n_cols: int,
                      num_kv_heads: int, scores: torch.Tensor | None = None,
                      sched: torch.Tensor | None = None) -> torch.Tensor:
@@ -109,15 +179,14 @@ def quest_page_score(q: torch.Tensor, bounds_layer: torch.Tensor, page_table: to
     _i32(sched, "sched")
     if sched.numel() < sched_scratch_ints(bsz):
         raise ValueError(f"sched needs >= {sched_scratch_ints(bsz)} int32 entries, got {sched.numel()}.")
-    _bounds_layer(bounds_layer, num_kv_heads)
-    _i32(page_table, "page_table"); _i32(req_rows, "req_rows"); _i32(context_lens, "context_lens")
+    num_chunks = _bounds_layer(bounds_layer, num_kv_heads)
+    _i32(unit_table, "unit_table"); _i32(req_rows, "req_rows"); _i32(context_lens, "context_lens")
     if scores is None:
         scores = torch.empty((bsz, score_row_stride(n_cols)), dtype=torch.bfloat16, device=q.device)
     require_cuda(scores, "scores", torch.bfloat16)
     lib = _native.load()
     check(lib.svb200_quest_page_score(
-        ptr(q), qs, ptr(bounds_layer), int(bounds_layer.shape[0]), ptr(page_table),
-        _rows_stride(page_table, "page_table"),
+        ptr(q), qs, ptr(bounds_layer), num_chunks, ptr(unit_table), _rows_stride(unit_table, "unit_table"),
         ptr(req_rows), ptr(context_lens), ptr(scores), _rows_stride(scores, "scores"), bsz, hq,
         int(num_kv_heads), int(n_cols), ptr(sched), current_stream_ptr(q.device)), "svb200_quest_page_score")
     return scores
@@ -153,33 +222,35 @@ def quest_select_pack(scores: torch.Tensor, n_cols: int, page_table: torch.Tenso
 class DecodeStore:
     """New K/V rows of a decode step (token b = batch row b) for the scoring launch to store itself."""
 
-    __slots__ = ("key", "value", "k_cache", "v_cache", "slot_mapping", "refresh_bounds")
+    __slots__ = ("key", "value", "k_cache", "v_cache", "slot_mapping", "refresh_bounds", "page_rec")
 
-    def __init__(self, key, value, k_cache, v_cache, slot_mapping, refresh_bounds: bool):
+    def __init__(self, key, value, k_cache, v_cache, slot_mapping, refresh_bounds: bool, page_rec=None):
         self.key, self.value, self.k_cache, self.v_cache = key, value, k_cache, v_cache
-        self.slot_mapping, self.refresh_bounds = slot_mapping, bool(refresh_bounds)
+        self.slot_mapping, self.refresh_bounds, self.page_rec = slot_mapping, bool(refresh_bounds), page_rec
 
 
-def quest_score_select_pack(q: torch.Tensor, bounds_layer: torch.Tensor, page_table: torch.Tensor,
-                            req_rows: torch.Tensor, context_lens: torch.Tensor, n_cols: int, num_kv_heads: int,
+def quest_score_select_pack(q: torch.Tensor, bounds_layer: torch.Tensor, unit_table: torch.Tensor,
+                            page_table: torch.Tensor, req_rows: torch.Tensor, context_lens: torch.Tensor,
+                            n_cols: int, num_kv_heads: int,
                             prev_budget: int, scores: torch.Tensor, packed_slots: torch.Tensor,
                             sparse_lens: torch.Tensor, tickets: torch.Tensor,
                             selected_pages: torch.Tensor | None = None, store: DecodeStore | None = None) -> None:
     """One-launch score + select + pack for long-text batches (svb200_quest_score_select_pack); with
     ``store`` the launch also writes the step's K/V rows (svb200_quest_store_score_select_pack)."""
     bsz, hq, qs = _q(q, "q")
-    _bounds_layer(bounds_layer, num_kv_heads)
+    num_chunks = _bounds_layer(bounds_layer, num_kv_heads)
     require_cuda(scores, "scores", torch.bfloat16)
-    for t, n in ((page_table, "page_table"), (req_rows, "req_rows"), (context_lens, "context_lens"),
-                 (packed_slots, "packed_slots"), (sparse_lens, "sparse_lens"), (tickets, "tickets")):
+    for t, n in ((unit_table, "unit_table"), (page_table, "page_table"), (req_rows, "req_rows"),
+                 (context_lens, "context_lens"), (packed_slots, "packed_slots"), (sparse_lens, "sparse_lens"),
+                 (tickets, "tickets")):
         _i32(t, n)
     if tickets.numel() < sched_scratch_ints(bsz):
         raise ValueError(f"tickets needs >= {sched_scratch_ints(bsz)} int32 entries (sched_scratch), got {tickets.numel()}.")
     if selected_pages is not None:
         _i32(selected_pages, "selected_pages")
     lib = _native.load()
-    score_args = (ptr(q), qs, ptr(bounds_layer), int(bounds_layer.shape[0]), ptr(page_table),
-                  _rows_stride(page_table, "page_table"),
+    score_args = (ptr(q), qs, ptr(bounds_layer), num_chunks, ptr(unit_table), _rows_stride(unit_table, "unit_table"),
+                  ptr(page_table), _rows_stride(page_table, "page_table"),
                   ptr(req_rows), ptr(context_lens), ptr(scores), _rows_stride(scores, "scores"), bsz, hq,
                   int(num_kv_heads), int(n_cols), int(prev_budget), ptr(packed_slots),
                   _rows_stride(packed_slots, "packed_slots"), ptr(sparse_lens), ptr(selected_pages), ptr(tickets),
@@ -198,10 +269,14 @@ def quest_score_select_pack(q: torch.Tensor, bounds_layer: torch.Tensor, page_ta
     _i32(store.slot_mapping, "slot_mapping")
     if int(store.slot_mapping.numel()) != bsz:
         raise ValueError(f"slot_mapping must hold one slot per batch row ({bsz}), got {store.slot_mapping.numel()}.")
+    if store.refresh_bounds:
+        if store.page_rec is None:
+            raise ValueError("a store that refreshes bounds needs page_rec.")
+        _page_rec(store.page_rec, num_slots)
     check(lib.svb200_quest_store_score_select_pack(
         ptr(store.key), int(store.key.stride(0)), ptr(store.value), int(store.value.stride(0)), ptr(store.k_cache),
-        ptr(store.v_cache), ptr(store.slot_mapping), num_slots, int(store.refresh_bounds), *score_args),
-        "svb200_quest_store_score_select_pack")
+        ptr(store.v_cache), ptr(store.slot_mapping), num_slots, int(store.refresh_bounds), ptr(store.page_rec),
+        *score_args), "svb200_quest_store_score_select_pack")
 
 
 def sched_scratch_ints(rows: int) -> int:
@@ -246,8 +321,12 @@ def sparse_decode_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Te
                        req_rows: torch.Tensor, seq_lens: torch.Tensor, *, out: torch.Tensor,
                        workspace: torch.Tensor, max_len: int | None = None,
                        attn_score: torch.Tensor | None = None, heads_per_cta: int = 0,
-                       sm_scale: float | None = None) -> torch.Tensor:
-    """Stream-K sparse paged GQA decode attention with fused combine (svb200_sparse_decode_attn)."""
+                       sm_scale: float | None = None, comm=None, gathered: torch.Tensor | None = None) -> torch.Tensor:
+    """Stream-K sparse paged GQA decode attention with fused combine (svb200_sparse_decode_attn).
+
+    ``comm`` (a ``parallel.PeerComm``) + ``gathered`` (a ``[B, world*Hq, 128]`` view INSIDE ``comm``'s local data
+    buffer): the epilogue also stores this rank's rows into every rank's gathered buffer and the launch completes
+    when all ranks' rows have arrived (svb200_sparse_decode_attn_tp)."""
     bsz, hq, qs = _q(q, "q")
     num_slots, hkv = _kv_layer(k_cache, "k_cache")
     if _kv_layer(v_cache, "v_cache") != (num_slots, hkv):
@@ -274,11 +353,33 @@ def sparse_decode_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Te
     if sm_scale is None:
         sm_scale = 1.0 / math.sqrt(HEAD_DIM)
     lib = _native.load()
-    check(lib.svb200_sparse_decode_attn(
-        ptr(q), qs, ptr(k_cache), ptr(v_cache), num_slots, ptr(slot_table), table_stride, max_len,
-        ptr(req_rows), ptr(seq_lens), ptr(out), os_, ptr(attn_score), score_stride, bsz, hq, hkv,
-        int(heads_per_cta), ptr(workspace), int(workspace.numel()) * 4, float(sm_scale),
-        current_stream_ptr(q.device)), "svb200_sparse_decode_attn")
+    args = (ptr(q), qs, ptr(k_cache), ptr(v_cache), num_slots, ptr(slot_table), table_stride, max_len,
+            ptr(req_rows), ptr(seq_lens), ptr(out), os_, ptr(attn_score), score_stride, bsz, hq, hkv,
+            int(heads_per_cta), ptr(workspace), int(workspace.numel()) * 4, float(sm_scale))
+    if comm is None or comm.world <= 1:
+        check(lib.svb200_sparse_decode_attn(*args, current_stream_ptr(q.device)), "svb200_sparse_decode_attn")
+        return out
+    if gathered is None:
+        raise ValueError("the tensor-parallel epilogue needs the gathered output view.")
+    require_cuda(gathered, "gathered", torch.bfloat16)
+    gb, gh, gs = _q(gathered, "gathered")
+    if (gb, gh) != (bsz, comm.world * hq):
+        raise ValueError(f"gathered must be [B={bsz}, world*Hq={comm.world * hq}, {HEAD_DIM}], got {tuple(gathered.shape)}.")
+    check(lib.svb200_sparse_decode_attn_tp(*args, comm.struct_ptr(), comm.offset_of(gathered), gs,
+                                           current_stream_ptr(q.device)), "svb200_sparse_decode_attn_tp")
+    return out
+
+
+def allreduce_sum_bf16(comm, inp: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """One-shot NVLink SUM all-reduce (svb200_allreduce_sum_bf16): ``inp`` is a contiguous bf16 view INSIDE
+    ``comm``'s local data buffer (every rank passes the view at the same offset), ``out`` a local bf16 tensor."""
+    require_cuda(inp, "inp", torch.bfloat16)
+    require_cuda(out, "out", torch.bfloat16)
+    if not inp.is_contiguous() or not out.is_contiguous() or inp.numel() != out.numel() or inp.numel() % 8:
+        raise ValueError("inp / out must be contiguous bf16 tensors of the same size, a multiple of 8 elements.")
+    lib = _native.load()
+    check(lib.svb200_allreduce_sum_bf16(comm.struct_ptr(), comm.offset_of(inp), int(inp.numel()), ptr(out),
+                                        current_stream_ptr(inp.device)), "svb200_allreduce_sum_bf16")
     return out
 
 
@@ -335,7 +436,8 @@ def h2o_select_compact(cumulative: torch.Tensor, cum_rows: torch.Tensor, slot_ta
 
 # ----------------------------------------------------------------------------- KV store
 def store_kv_minmax(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
-                    slot_mapping: torch.Tensor, quest_bounds_layer: torch.Tensor | None = None) -> None:
+                    slot_mapping: torch.Tensor, quest_bounds_layer: torch.Tensor | None = None,
+                    page_rec: torch.Tensor | None = None) -> None:
     """Scatter new K/V rows (+ fused bounds refresh of completed pages) (svb200_store_kv_minmax)."""
     num_slots, hkv = _kv_layer(k_cache, "k_cache")
     _kv_layer(v_cache, "v_cache")
@@ -344,10 +446,15 @@ def store_kv_minmax(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tenso
         if t.dim() != 3 or tuple(t.shape[1:]) != (hkv, HEAD_DIM) or t.stride(2) != 1 or t.stride(1) != HEAD_DIM:
             raise ValueError(f"{n} must be [T, {hkv}, {HEAD_DIM}] with contiguous heads, got {tuple(t.shape)}/{t.stride()}.")
     _i32(slot_mapping, "slot_mapping")
+    num_chunks = 0
     if quest_bounds_layer is not None:
-        _bounds_layer(quest_bounds_layer, hkv, "quest_bounds_layer")
+        num_chunks = _bounds_layer(quest_bounds_layer, hkv, "quest_bounds_layer")
+        if page_rec is None:
+            raise ValueError("quest_bounds_layer needs page_rec (physical page -> bounds record).")
+        _page_rec(page_rec, num_slots)
     lib = _native.load()
     check(lib.svb200_store_kv_minmax(
         ptr(key), int(key.stride(0)), ptr(value), int(value.stride(0)), ptr(k_cache), ptr(v_cache),
         ptr(slot_mapping), int(slot_mapping.numel()), hkv, num_slots, ptr(quest_bounds_layer),
+        ptr(page_rec) if quest_bounds_layer is not None else None, num_chunks,
         current_stream_ptr(key.device)), "svb200_store_kv_minmax")

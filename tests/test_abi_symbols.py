@@ -17,7 +17,7 @@ def test_header_declares_the_minimum_set():
     names = _header_functions()
     for required in ("svb200_quest_page_minmax", "svb200_quest_score_select_pack", "svb200_sparse_decode_attn",
                      "svb200_h2o_normalize_accumulate", "svb200_h2o_select_compact", "svb200_store_kv_minmax",
-                     "svb200_workspace_bytes"):
+                     "svb200_workspace_bytes", "svb200_sparse_decode_attn_tp", "svb200_allreduce_sum_bf16"):
         assert required in names
 
 
@@ -47,7 +47,7 @@ def test_binding_arity_matches_header():
 
 def test_validation_errors_need_no_gpu(native_lib):
     """Argument validation happens before any CUDA call: bad arguments return EINVAL with a message."""
-    rc = native_lib.svb200_quest_page_minmax(None, None, None, 4, 8, 1024, None)
+    rc = native_lib.svb200_quest_page_minmax(None, None, 8, None, None, 4, 8, 1024, None)
     assert rc == 1
     assert b"null pointer" in native_lib.svb200_last_error()
     # tickets (256-byte rounded) + two (output + lse) fp32 partial records per SM (148 without a device)
@@ -68,4 +68,5 @@ def test_product_package_has_no_oracle_or_cpu_fallback():
         assert "import triton" not in src, path
     k = torch.zeros(32, 1, 128, dtype=torch.bfloat16)
     with pytest.raises(RuntimeError, match="no CPU path"):
-        ops.quest_page_minmax(k, torch.zeros(2, 2, 1, 128, dtype=torch.bfloat16), torch.zeros(1, dtype=torch.int32))
+        ops.quest_page_minmax(k, torch.zeros(ops.bounds_shape(2, 1), dtype=torch.bfloat16), torch.zeros(2, dtype=torch.int32),
+                              torch.zeros(1, dtype=torch.int32))

@@ -97,10 +97,11 @@ def test_quest_decode_steps_through_manager(hq, hkv):
             assert torch.equal(k_cache[slots], k_new[layer]) and torch.equal(v_cache[slots], v_new[layer])
             mx, mn = oquest.build_bounds_from_cache(k_cache)
             page_table = fused.buffer_req_to_page_slots.cpu()
+            by_page = fused.bounds_by_page(layer).cpu()
             for b in range(bsz):  # bounds of every completed page, incl. the one this step may have completed
                 done = page_table[b, : int(ctx[b]) // PAGE].long()
-                assert torch.equal(fused.bounds[layer].cpu()[done, 0], mx[done])
-                assert torch.equal(fused.bounds[layer].cpu()[done, 1], mn[done])
+                assert torch.equal(by_page[done, 0], mx[done])
+                assert torch.equal(by_page[done, 1], mn[done])
             view = oquest.build_decode_view_static(
                 q[layer], mx, mn, page_table, fused.buffer_req_to_token_slots.cpu(), bufs[0].req.cpu(), ctx,
                 token_budget=int(cfg.quest_token_budget), num_kv_heads=hkv, max_context_len=max_len,
@@ -113,10 +114,12 @@ def test_quest_decode_steps_through_manager(hq, hkv):
                 inv = {int(p): i for i, p in enumerate(page_table[b].tolist()) if p >= 0}
                 got = [inv[int(p)] for p in got_pages[b, :prev]]
                 n_valid = (int(ctx[b]) + PAGE - 1) // PAGE - 1
-                c = oquest.classify_selection(view["scores"][b], view["selected_pages"][b, :prev].tolist(), got, n_valid)
-                if c["bad"]:  # a one-ulp score difference may swap pages around the k-th score
-                    d = oquest.bf16_ulp_distance(sf.scores[b, :n_valid].cpu(), view["scores"][b, :n_valid])
-                    assert int(d.max()) <= 1, (step, layer, b, c["detail"])
+                # a one-ulp score difference may swap pages, but only pages within one ulp of the k-th score
+                c = oquest.classify_selection_ulp(view["scores"][b], view["selected_pages"][b, :prev].tolist(), got,
+                                                  n_valid, ulp_slack=1)
+                assert c["bad"] == 0, (step, layer, b, c["detail"])
+                d = oquest.bf16_ulp_distance(sf.scores[b, :n_valid].cpu(), view["scores"][b, :n_valid])
+                assert int(d.max()) <= 1, (step, layer, b)
                 assert inv[int(got_pages[b, prev])] == n_valid  # the last page rides along
             ref = oattn.gqa_decode(q[layer], k_cache, v_cache, sf.packed.cpu()[:, :width], torch.arange(bsz, dtype=torch.int32),
                                    sf.lens.cpu(), max_len_in_batch=width)

@@ -29,7 +29,7 @@ class _FakeProvider:
     def __init__(self):
         self.select_calls = []
 
-    def quest_select(self, q, bounds_layer, page_table, req_rows, context_lens, **kw):
+    def quest_select(self, q, bounds_layer, unit_table, page_table, req_rows, context_lens, **kw):
         self.select_calls.append(kw)
 
 
@@ -146,3 +146,32 @@ def test_store_is_not_deferred_when_it_cannot_be_fused(rig):
     set_context(False, is_long_text=False)  # mixed batch: two launches, the store goes first
     mgr2.save_rope_kv_if_needed(1, k, k)
     assert rig.rec.names() == ["store_kv_minmax"] and mgr2._pending_store is None
+
+
+def test_bounds_chunks_follow_page_allocation(rig):
+    """Every (row, logical page // 16) owns one bounds chunk; page_rec maps a physical page to its record;
+    a decode token that opens logical page 16 opens a new chunk; freeing a sequence returns its chunks."""
+    from sparse_vllm_b200 import configs
+    from sparse_vllm_b200.cache_manager.quest import QuestCacheManager
+    cfg = configs.make_sparse_config(sparse_method="quest", sink_keep_tokens=16, decode_keep_tokens=96, recent_keep_tokens=16)
+    mgr = QuestCacheManager(cfg, num_layers=1, num_kv_heads=2, num_pages=64, max_rows=2, max_model_len=512,
+                            device=torch.device("cpu"), provider=_FakeProvider())
+    assert mgr.num_chunks == 64 // PAGE + 2 and mgr._num_free_chunks == mgr.num_chunks
+    assert tuple(mgr.bounds.shape) == (1, mgr.num_chunks, 1, PAGE, 2, 2, 128)
+    mgr.allocate_prefill(0, 256)  # exactly 16 pages: one chunk
+    mgr.allocate_prefill(1, 300)  # 19 pages: two chunks
+    ut, rec, pt = mgr.unit_table_cpu, mgr.page_rec.numpy(), mgr.buffer_req_to_page_slots_cpu
+    assert (ut[0] >= 0).sum() == 1 and (ut[1] >= 0).sum() == 2 and mgr._num_free_chunks == mgr.num_chunks - 3
+    assert np.array_equal(mgr.unit_table.numpy(), ut)
+    for row, n_pages in ((0, 16), (1, 19)):
+        j = np.arange(n_pages)
+        assert np.array_equal(rec[pt[row, :n_pages]], ut[row, j // PAGE] * PAGE + j % PAGE)
+    assert len(set(ut[ut >= 0].tolist())) == 3 and (rec >= 0).sum() == 35
+    # the next decode token of row 0 opens logical page 16 -> a second chunk for row 0
+    seqs = [SimpleNamespace(seq_id=0, decode_input_token=1, decode_input_position=0)]
+    mgr.prepare_decode_static(seqs, *_step_buffers(1))
+    assert (ut[0] >= 0).sum() == 2 and int(rec[pt[0, 16]]) == int(ut[0, 1]) * PAGE
+    assert np.array_equal(mgr.unit_table.numpy(), ut)
+    mgr.free_seq(1)
+    assert mgr._num_free_chunks == mgr.num_chunks - 2 and (mgr.unit_table_cpu[1] == -1).all()
+    assert (mgr.page_rec.numpy() >= 0).sum() == 17
