@@ -31,6 +31,18 @@ QUEST_CASES = {
                             max_context_len=2048, token_budget=1024, is_long_text=True),
 }
 
+# BASELINE.json shapes at full size (one layer): inputs are regenerated from the seed with byte-wide draws
+# (`compact`), only digests / scores / packed slots / attention outputs are committed.
+QUEST_BASELINE_CASES = {
+    # cfg1: tiny random-init Llama-style model (configs/debug/qwen3_tiny_random.json: 8 q / 4 kv heads), bs 1,
+    # 4K context, budget 512 (sink 64 + decode 384 + recent 64), quest_skip_layers 0
+    "quest_cfg1": dict(seed=41, bsz=1, hq=8, hkv=4, ctx_lens=[4091], max_context_len=4096, token_budget=512,
+                       is_long_text=True, compact=True),
+    # cfg2: Llama-3.1-8B shape (32 q / 8 kv), bs 1, 32K context, budget 2048
+    "quest_cfg2": dict(seed=42, bsz=1, hq=32, hkv=8, ctx_lens=[32765], max_context_len=32768, token_budget=2048,
+                       is_long_text=True, compact=True),
+}
+
 ATTN_CASES = {
     "attn_g7_ragged": dict(seed=21, bsz=3, hq=28, hkv=4, lens=[700, 513, 1], width=768,
                            num_slots=2048, with_score=False),
@@ -50,9 +62,10 @@ def _rng(seed: int) -> np.random.Generator:
     return np.random.Generator(np.random.PCG64(int(seed)))
 
 
-def randn_bf16(rng: np.random.Generator, *shape: int, scale: float = 1.0) -> torch.Tensor:
-    """~N(0, scale^2) bf16 tensor from integer draws: (sum of 4 bytes - 510) / 147.8 (exact in fp32)."""
-    u = rng.integers(0, 256, size=(*shape, 4), dtype=np.int64).sum(axis=-1)
+def randn_bf16(rng: np.random.Generator, *shape: int, scale: float = 1.0, compact: bool = False) -> torch.Tensor:
+    """~N(0, scale^2) bf16 tensor from integer draws: (sum of 4 bytes - 510) / 147.8 (exact in fp32).
+    ``compact`` draws bytes (a different, equally bit-stable stream; 8x less memory for the large cases)."""
+    u = rng.integers(0, 256, size=(*shape, 4), dtype=np.uint8 if compact else np.int64).sum(axis=-1, dtype=np.int64)
     x = (u - 510).astype(np.float32) * np.float32(scale) / np.float32(147.8)
     return torch.from_numpy(x).to(torch.bfloat16)
 
@@ -86,7 +99,7 @@ def digest(*tensors: torch.Tensor) -> str:
     return h.hexdigest()
 
 
-def make_quest_inputs(*, seed, bsz, hq, hkv, ctx_lens, max_context_len, d=128, **_):
+def make_quest_inputs(*, seed, bsz, hq, hkv, ctx_lens, max_context_len, d=128, compact=False, **_):
     """Page tables with a shuffled physical page assignment, per-row K/V, q.
 
     Row 0 of the tables is left unused so that req_indices != arange is exercised.
@@ -111,10 +124,10 @@ def make_quest_inputs(*, seed, bsz, hq, hkv, ctx_lens, max_context_len, d=128, *
         page_table[row, :npg] = pg
         slots = (pg[:, None] * PAGE + torch.arange(PAGE, dtype=torch.int32)[None, :]).reshape(-1)[:n]
         token_table[row, :n] = slots
-        ks.append(randn_bf16(gen, n, hkv, d))
-        vs.append(randn_bf16(gen, n, hkv, d))
+        ks.append(randn_bf16(gen, n, hkv, d, compact=compact))
+        vs.append(randn_bf16(gen, n, hkv, d, compact=compact))
         slot_rows.append(slots)
-    q = randn_bf16(gen, bsz, hq, d)
+    q = randn_bf16(gen, bsz, hq, d, compact=compact)
     return dict(num_pages=num_pages, max_pages_per_row=max_pages_per_row, page_table=page_table,
                 token_table=token_table, req_indices=req_indices, k_rows=ks, v_rows=vs,
                 slot_rows=slot_rows, q=q, context_lens=torch.tensor(ctx_lens, dtype=torch.int32))

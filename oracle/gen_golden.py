@@ -72,14 +72,15 @@ def make_quest_manager(*, layers, hkv, d, num_pages, rows, max_model_len, token_
     return m
 
 
-def quest_case(name, *, seed, bsz, hq, hkv, ctx_lens, max_context_len, token_budget, is_long_text=True, d=128):
+def quest_case(name, *, seed, bsz, hq, hkv, ctx_lens, max_context_len, token_budget, is_long_text=True, d=128,
+               compact=False):
     """One layer of Quest on the inputs of oracle/cases.py: prefill bounds via on_kv_stored (two
     chunks that split a page), decode-page completion via on_forward_end, then build_decode_view."""
     from sparsevllm.utils.context import set_context
     from sparsevllm.engine.cache_manager import quest as quest_mod
 
     inp = cases.make_quest_inputs(seed=seed, bsz=bsz, hq=hq, hkv=hkv, ctx_lens=ctx_lens,
-                                  max_context_len=max_context_len, d=d)
+                                  max_context_len=max_context_len, d=d, compact=compact)
     rows = bsz + 1
     m = make_quest_manager(layers=1, hkv=hkv, d=d, num_pages=inp["num_pages"], rows=rows,
                            max_model_len=max_context_len, token_budget=token_budget)
@@ -147,11 +148,29 @@ def quest_case(name, *, seed, bsz, hq, hkv, ctx_lens, max_context_len, token_bud
         quest_mod.QuestCacheManager._score_pages_batched = staticmethod(orig_score)
     out = {
         "digest": np.array(cases.digest(q, k_cache, v_cache, inp["page_table"], inp["token_table"])),
-        "bounds_max": bits(m.metadata_cache[0, 0]), "bounds_min": bits(m.metadata_cache[1, 0]),
         "scores_raw": bits(captured["scores_raw"]),
         "packed_slots": packed.numpy().astype(np.int32), "req_out": req_out.numpy().astype(np.int32),
         "lens": lens.numpy().astype(np.int32),
     }
+    if compact:
+        # BASELINE-size case: the bounds are committed as a digest (max plane, min plane, physical page order;
+        # never-completed pages are zero), and the reference's Triton decode kernels (interpreter, fp32-upcast
+        # inputs) run on the reference's own packed slots so the attention launch is pinned at this size too
+        out["bounds_digest"] = np.array(cases.digest(m.metadata_cache[0, 0], m.metadata_cache[1, 0]))
+        from sparsevllm.kernels.triton.flash_decoding_stage2 import flash_decode_stage2
+        from sparsevllm.kernels.triton.gqa_flash_decoding_stage1 import flash_decode_stage1
+        block_seq, width = 256, int(packed.shape[1])
+        nblk = (width + block_seq - 1) // block_seq
+        mid_o = torch.zeros(bsz, hq, nblk, d, dtype=torch.float32)
+        mid_lse = torch.zeros(bsz, hq, nblk, dtype=torch.float32)
+        qf = q.float()
+        flash_decode_stage1(qf, k_cache.float(), v_cache.float(), packed, req_out, lens, width, mid_o, mid_lse, block_seq)
+        o = torch.empty_like(qf)
+        flash_decode_stage2(mid_o, mid_lse, lens, o, block_seq)
+        out["attn_out_f32"] = o.numpy()
+    else:
+        out["bounds_max"] = bits(m.metadata_cache[0, 0])
+        out["bounds_min"] = bits(m.metadata_cache[1, 0])
     GOLDEN.mkdir(parents=True, exist_ok=True)
     np.savez_compressed(GOLDEN / f"{name}.npz", **out)
     print(f"[quest] {name}: packed {tuple(packed.shape)} lens {lens.tolist()[:4]}")
@@ -212,7 +231,7 @@ def h2o_case(name, *, seed, rows, kv_len, budget, ratio, ties):
 
 def main():
     torch.set_num_threads(max(1, os.cpu_count() or 1))
-    for name, cfg in cases.QUEST_CASES.items():
+    for name, cfg in {**cases.QUEST_CASES, **cases.QUEST_BASELINE_CASES}.items():
         quest_case(name, **cfg)
     for name, cfg in cases.ATTN_CASES.items():
         attention_case(name, **cfg)

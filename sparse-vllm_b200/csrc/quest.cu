@@ -859,24 +859,27 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
   if (groups > p.batch) groups = p.batch;
   if (groups < 1) groups = 1;
   p.groups = groups;
-  // A claimed chunk is ~64 KB of bounds (what is claimed cannot be stolen: big chunks make the launch's tail
-  // ragged); a claim's round trip costs 3-4 us under load, so one batch of chunks is worth >= ~128 KB of
-  // streaming, or the scheduler cannot keep the ring fed.
+  const int64_t units_row = (p.n_cols + kPage - 1) / kPage;
+  int grid = max_ctas();
+  // What is claimed cannot be stolen, so claims bound the raggedness of the launch's tail; but a claim's round
+  // trip costs 3-4 us under load and must hide behind queued streaming.  A claim is worth 1/8 of a CTA's share
+  // of the launch, between 32 KB (small launches: TP shards, one-row batches) and 128 KB, made of two chunks.
   {
-    const int unit_bytes = stage_bytes * p.hsplit;
-    int cu = tuning(kTuneChunkUnits) > 0 ? tuning(kTuneChunkUnits) : (64 * 1024) / unit_bytes;
+    const int64_t unit_bytes = (int64_t)stage_bytes * p.hsplit;
+    const int64_t per_cta = (int64_t)p.batch * units_row * unit_bytes / grid;
+    int64_t claim = per_cta / 8;
+    claim = claim < 32 * 1024 ? 32 * 1024 : (claim > 128 * 1024 ? 128 * 1024 : claim);
+    int cu = tuning(kTuneChunkUnits) > 0 ? tuning(kTuneChunkUnits) : (int)(claim / 2 / unit_bytes);
     p.chunk_units = cu < 1 ? 1 : (cu > kMaxChunkUnits ? kMaxChunkUnits : cu);
-    const int chunk_bytes = p.chunk_units * unit_bytes;
-    int mb = (128 * 1024 + chunk_bytes - 1) / chunk_bytes;
+    const int64_t chunk_bytes = p.chunk_units * unit_bytes;
+    int mb = (int)((claim + chunk_bytes - 1) / chunk_bytes);
     if (mb < kMinBatch) mb = kMinBatch;
     p.min_batch = tuning(kTuneMinBatch) > 0 ? tuning(kTuneMinBatch) : mb;
   }
   p.share_div = tuning(kTuneShareDiv) > 0 ? tuning(kTuneShareDiv) : 4;
   p.no_math = tuning(kTuneNoMath) == 1;
   const size_t smem = score_smem_layout(p.stages, p.hq, p.hkv, p.hsplit, p.batch, FUSED, qsplit ? 2 : 1).total;
-  const int64_t units_row = (p.n_cols + kPage - 1) / kPage;
   const int64_t max_chunks = (int64_t)p.batch * ((units_row + p.chunk_units - 1) / p.chunk_units);
-  int grid = max_ctas();
   if ((int64_t)grid > max_chunks) grid = (int)max_chunks;
   if (grid < 1) grid = 1;
   const cudaError_t e = qsplit ? launch_score_kernel<NT, FUSED, true>(p, grid, smem, stream)

@@ -103,10 +103,13 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
   auto guided_batch = [&](int left) { return max(min_batch, left / (share_div * share)); };
   // chunks of `row` that are handed out statically (first batch of the CTAs whose first home row it is);
   // the row's counter counts the chunks claimed BEYOND them.  Every CTA computes the same value.
+  // (a static piece costs no claim round trip, so it may be a single chunk: small launches then spread over
+  // every CTA instead of min_batch chunks going to each of a few)
+  auto static_piece = [&](int d) { return max(1, d / (share_div * share)); };
   auto static_chunks = [&](int row) {
     if (row >= groups || share * groups > (int)gridDim.x) return 0;
     const int d = chunks_of(row);
-    return min(d, share * guided_batch(d));
+    return min(d, share * static_piece(d));
   };
   auto drain = [&](int row, bool guided, bool first_home) -> bool {  // false: reserve() refused the row
     const int nu = units_of_row(row);
@@ -117,10 +120,10 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
     aux = reserve(row);
     if (aux < 0) return false;
     auto batch = [&](int left) { return guided ? guided_batch(left) : min_batch; };
-    int m = batch(d), j = 0, taken = 0;
+    int m = first_home ? static_piece(d) : batch(d), j = 0, taken = 0;
     if (first_home) {
       j = (int)(blockIdx.x / (unsigned)groups) * m;  // static: no round trip before the first copy
-      if (j >= base) first_home = false;             // (the row is shorter than the static pieces)
+      if (j >= base) first_home = false, m = batch(d);  // (the row is shorter than the static pieces)
     }
     if (!first_home) {
       if (lane == 0) j = base + atomicAdd(next_chunk + row, m);
