@@ -34,6 +34,9 @@ UNIT = "tok/s"
 
 # BASELINE.json configs (shapes only; weights/data are synthetic).  budget = sink + decode_keep + recent.
 WORKLOADS = {
+    # tiny random-init Llama-style model (reference configs/debug/qwen3_tiny_random.json): CPU arms only
+    "cfg1": dict(name="cfg1: tiny Llama-style model quest bs1 ctx4K budget512 (CPU reference path)", layers=2, hq=8, hkv=4,
+                 bsz=1, ctx=4096, sink=64, decode_keep=384, recent=64),
     "cfg2": dict(name="cfg2: Llama-3.1-8B shape quest bs1 ctx32K budget2048", layers=32, hq=32, hkv=8, bsz=1,
                  ctx=32768, sink=64, decode_keep=1472, recent=512),
     "cfg3": dict(name="cfg3: Qwen2.5-7B shape quest bs32 ctx128K budget4096", layers=28, hq=28, hkv=4, bsz=32,
@@ -52,7 +55,9 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "incumbent"],
+                    help="reference = the reference's CPU torch path on the host cores; incumbent = the reference's "
+                         "own torch + Triton GPU path on this GPU (both from oracle/_ref, unmodified)")
     ap.add_argument("--workload", default="auto", choices=["auto", *WORKLOADS])
     ap.add_argument("--phys-layers", type=int, default=0, help="distinct KV/bounds pools cycled by the layers (0 = auto)")
     ap.add_argument("--skip-layers", type=int, default=0, help="quest_skip_layers (dense layers at the bottom)")
@@ -830,29 +835,58 @@ class CpuSample:
                 f"budget {self.w['budget']}): page scoring + top-k + packing + sparse attention, scaled by rows/(t*layers)")
 
 
+def make_cpu_sample(w: dict, rows: int):
+    """The reference itself (oracle/_ref, kind "reference") when the vendored copy is there, else the oracle port."""
+    from oracle import ref_arms
+    why = ref_arms.reference_available()
+    if why is None:
+        try:
+            return ref_arms.RefCpuSample(w, rows), "reference", None
+        except Exception as exc:  # e.g. a dependency of the reference package is missing on this box
+            why = f"importing the vendored reference failed: {type(exc).__name__}: {exc}"
+    return CpuSample(w, rows), "port", why
+
+
 def cpu_baseline(w: dict, budget_s: float) -> dict:
-    sample = CpuSample(w, rows=2)
+    sample, kind, why = make_cpu_sample(w, rows=2)
     sample.run_once()  # warm-up
     times, t_start = [], time.perf_counter()
     while len(times) < 3 or (time.perf_counter() - t_start < budget_s and len(times) < 50):
         times.append(sample.run_once())
     times.sort()
     med = times[len(times) // 2]
-    return {"value": sample.tokens_per_s(med), "unit": UNIT, "cores": sample.cores, "kind": "port",
-            "sample": sample.describe() + f"; median of {len(times)} runs"}
+    out = {"value": sample.tokens_per_s(med), "unit": UNIT, "cores": sample.cores, "kind": kind,
+           "sample": sample.describe() + f"; median of {len(times)} runs", "sample_ms": med * 1e3}
+    if why:
+        out["port_because"] = why
+    # BASELINE config 1 runs natively on the host (no scaling): a whole decode step of the tiny model's Quest path
+    try:
+        w1 = dict(WORKLOADS["cfg1"], key="cfg1")
+        w1["budget"] = w1["sink"] + w1["decode_keep"] + w1["recent"]
+        s1, kind1, _ = make_cpu_sample(w1, rows=1)
+        s1.run_once()
+        t1 = sorted(s1.run_once() for _ in range(9))[4] * w1["layers"]
+        out["cfg1_native"] = {"workload": w1["name"], "value": 1.0 / t1, "unit": UNIT, "ms_per_step": t1 * 1e3,
+                              "kind": kind1, "cores": s1.cores}
+    except Exception as exc:
+        out["cfg1_native"] = {"error": f"{type(exc).__name__}: {exc}"}
+    return out
 
 
 def run_reference(args) -> dict:
-    """`--impl reference`: the reference's algorithm on the host cores (oracle port: the reference is a
-    Python package that is not present on the GPU box), same metric/config, every step a bounded sample."""
+    """`--impl reference`: the reference's CPU torch path for this hot path on the host cores (the unmodified
+    package vendored under oracle/_ref; the oracle port only if that copy is unusable), same metric/config, every
+    step a bounded sample.  `ms_per_step` is the full decode step the sample's rate implies (all rows, all layers);
+    the measured sample time is `sample_ms`."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return {}
     w = pick_workload(args)
     if "h2o_budget" in w:
-        raise SystemExit("--impl reference times the quest workloads (cfg2/cfg3/cfg5)")
+        raise SystemExit("--impl reference times the quest workloads (cfg1/cfg2/cfg3/cfg5)")
     steps, warmup = args.steps, max(args.warmup, 1)
-    sample = CpuSample(w, rows=2)
+    rows = min(2, w["bsz"])
+    sample, kind, why = make_cpu_sample(w, rows=rows)
     # keep the whole run within a few minutes
     t_probe = sample.run_once()
     budget = 150.0
@@ -864,23 +898,57 @@ def run_reference(args) -> dict:
         sample.run_once()
     per = (time.perf_counter() - t0) / steps
     value = sample.tokens_per_s(per)
+    step_ms = per * 1e3 * w["layers"] * w["bsz"] / rows
+    base = {"value": value, "unit": UNIT, "cores": sample.cores, "kind": kind, "sample": sample.describe()}
+    if why:
+        base["port_because"] = why
     return {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-        "warmup": warmup, "ms_per_step": per * 1e3, "higher_is_better": True,
+        "warmup": warmup, "ms_per_step": step_ms, "sample_ms": per * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": w["name"], "layers": w["layers"], "q_heads": w["hq"], "kv_heads": w["hkv"],
                    "batch": w["bsz"], "ctx": w["ctx"], "page": PAGE, "token_budget": w["budget"],
-                   "quest_skip_layers": args.skip_layers, "parallelism": "host cores"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": sample.cores, "kind": "port", "sample": sample.describe()},
+                   "quest_skip_layers": args.skip_layers, "parallelism": "host cores",
+                   "timed": f"each step = {rows} sequence(s) x 1 layer of the workload; ms_per_step = sample_ms x layers x batch / {rows}"},
+        "cpu_baseline": base,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
 
 
-def secondary_workload(key: str, args) -> dict:
+def run_incumbent(args) -> dict:
+    """`--impl incumbent`: the reference's own GPU path (torch selection + Triton decode kernels, oracle/_ref,
+    unmodified) on this B200 — the like-for-like number the provider replaces."""
+    import torch
+    from oracle import ref_arms
+    why = ref_arms.reference_available()
+    if why is not None:
+        return {"impl": "incumbent", "unavailable": why}
+    if args.gpus != 1:
+        return {"impl": "incumbent", "unavailable": "single-GPU arm"}
+    torch.cuda.set_device(0)
+    w = pick_workload(args)
+    try:
+        return ref_arms.run_incumbent(w, steps=max(1, min(args.steps, 5)), warmup=args.warmup)
+    except Exception as exc:
+        return {"impl": "incumbent", "unavailable": f"{type(exc).__name__}: {exc}"[:400]}
+
+
+def incumbent_subprocess(key: str, args) -> dict:
+    cmd = [sys.executable, str(ROOT / "bench.py"), "--impl", "incumbent", "--workload", key, "--steps", "3", "--warmup", "3"]
+    res = None
+    try:
+        res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+        return json.loads([ln for ln in res.stdout.splitlines() if ln.startswith("{")][-1])
+    except Exception as exc:
+        return {"impl": "incumbent", "unavailable": f"{type(exc).__name__}: {exc}",
+                "stderr_tail": res.stderr[-400:] if res is not None else None}
+
+
+def secondary_workload(key: str, args, extra=()) -> dict:
     """The same bench on another BASELINE config in a fresh process (its own KV pools), summarised."""
     cmd = [sys.executable, str(ROOT / "bench.py"), "--workload", key, "--no-cpu-baseline", "--steps", str(args.steps),
-           "--warmup", str(args.warmup)]
+           "--warmup", str(args.warmup), *extra]
     res = None
     try:
         res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
@@ -894,6 +962,10 @@ def secondary_workload(key: str, args) -> dict:
     if "roofline_attention" in d:
         out["roofline_attention_frac"] = d["roofline_attention"]["frac"]
         out["attention_launch_ms"] = d["roofline_attention"]["avg_launch_ms"]
+    if "roofline_dense_layer" in d:
+        out["quest_skip_layers"] = d["config"]["quest_skip_layers"]
+        out["dense_layer_launch_ms"] = d["roofline_dense_layer"]["avg_launch_ms"]
+        out["dense_layer_frac"] = d["roofline_dense_layer"]["frac"]
     return out
 
 
@@ -901,11 +973,18 @@ def main():
     args = parse_args()
     if args.impl == "reference":
         line = run_reference(args)
+    elif args.impl == "incumbent":
+        line = run_incumbent(args)
     else:
         h2o = args.workload == "cfg4"
         line = run_h2o(args) if h2o else run_b200(args)
         if line and args.gpus == 1 and args.workload == "auto":
             line["other_workloads"] = {k: secondary_workload(k, args) for k in ("cfg2", "cfg3", "cfg4")}
+            line["other_workloads"]["cfg5_skip2"] = secondary_workload("cfg5", args, extra=["--skip-layers", "2"])
+            # the reference's own GPU path on the same box, same workload (reported, never part of `value`)
+            line["incumbent"] = incumbent_subprocess("cfg5", args)
+            if "value" in line["incumbent"]:
+                line["incumbent"]["speedup_of_value"] = line["value"] / line["incumbent"]["value"]
         if line and not args.no_cpu_baseline and args.gpus == 1 and not h2o:
             line["cpu_baseline"] = cpu_baseline(pick_workload(args), args.cpu_seconds)
     if line and not line.pop("_printed", False):
