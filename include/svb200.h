@@ -259,18 +259,49 @@ int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_c
  * H2O layer-end normalisation (+ optional fused accumulation).
  *   score [batch][score_stride] fp32, in place: score = softmax(score * scale) over
  *   the first `width` columns (engine/sparse_controller.py:761-767).
- *   If cumulative != NULL: for row b with kv_len = kv_lens[b]:
- *     cumulative[b][i] += score[b][i] for i < kv_len-1; cumulative[b][kv_len-1] = score
+ *   If cumulative != NULL: for batch entry b with kv_len = kv_lens[b] and row c = cum_rows[b] (b when
+ *   cum_rows is NULL: consecutive rows):
+ *     cumulative[c][i] += score[b][i] for i < kv_len-1; cumulative[c][kv_len-1] = score
  *   (H2OCacheManager.update_decode_attention_scores_all_layers, h2o.py:958-1038,
  *    without the stack/clone of per-row tensors).
+ *   refill != 0 (with cumulative): the score row is left holding `refill` (the reference's -1e20) instead of
+ *   the normalised values, i.e. ready for the next step's max-updates; the reference refills the whole
+ *   [L,B,W] buffer with a launch of its own every step (sparse_controller.py:545-594).
  */
 int svb200_h2o_normalize_accumulate(float* score, int64_t score_stride, int32_t batch,
                                     int32_t width, float scale, float* cumulative,
-                                    int64_t cum_stride, const int32_t* kv_lens,
-                                    void* stream);
+                                    int64_t cum_stride, const int32_t* cum_rows,
+                                    const int32_t* kv_lens, float refill, void* stream);
 
 /*
- * H2O burst eviction for `num_rows` (layer,row) pairs of identical length kv_len:
+ * Prefill window scoring (H2O; the SnapKV-style candidate range is supported too): for batch row b the
+ * queries at physical positions [score_starts[b], score_ends[b]) — the last <= 128 tokens of the prefill
+ * chunk — attend causally to the row's kv positions [candidate_start, max(candidate_start, ctx - num_recent));
+ *   score[b][kv] = max over q heads of (sum over those queries of softmax_kv(q.k * sm_scale)[q][kv]) / n_queries
+ * Replaces prefill_score_fwd in probability mode (kernels/triton/prefill_score.py:70-428: partial-stats,
+ * reduce and final kernels) as driven by H2OCacheManager.collect_prefill_attention_score (h2o.py:778-894).
+ *   q [T][Hq][128] bf16 chunk tokens of all rows (token stride q_stride), start_loc[b] = first token of row b
+ *   k_cache [num_slots][Hkv][128] bf16 (the chunk's K rows are already stored), slot_table [rows][stride]
+ *   context_lens / prompt_cache_lens [B]: physical row length with / without the chunk
+ *   score [B][score_stride] fp32: overwritten (zero outside the candidate range)
+ * If cumulative != NULL the step scores are accumulated like H2OCacheManager._accumulate_score (h2o.py:611-626):
+ *   cumulative[cum_rows[b]][i] = (i < prompt_cache_len ? cumulative[..][i] : 0) + n_queries * score[b][i], i < ctx
+ */
+int svb200_h2o_prefill_score(const void* q, int64_t q_stride, const void* k_cache, int64_t num_slots,
+                             const int32_t* slot_table, int64_t slot_table_stride,
+                             const int32_t* req_rows, const int32_t* start_loc,
+                             const int32_t* context_lens, const int32_t* prompt_cache_lens,
+                             const int32_t* score_starts, const int32_t* score_ends, float* score,
+                             int64_t score_stride, float* cumulative, int64_t cum_stride,
+                             const int32_t* cum_rows, int32_t batch, int32_t num_q_heads,
+                             int32_t num_kv_heads, int32_t max_query_len, int32_t max_context_len,
+                             int32_t candidate_start, int32_t num_recent_tokens, float sm_scale,
+                             void* stream);
+
+/*
+ * H2O burst eviction for `num_rows` (layer,row) pairs of length kv_lens[i] (all kv_len when kv_lens is
+ * NULL; kv_len is then also the longest row: it sizes the shared-memory row cache; entries no longer than
+ * `budget` are left alone):
  * heavy hitters = the (budget - recent) largest cumulative scores among
  * [0, kv_len - recent) (stable: lower index wins ties), plus the `recent` suffix,
  * in ascending order (H2OCacheManager.select_h2o_indices_batch, h2o.py:519-563);
@@ -279,14 +310,14 @@ int svb200_h2o_normalize_accumulate(float* score, int64_t score_stride, int32_t 
  *   cum_rows   int64 [num_rows] element offsets of each row in `cumulative`
  *   slot_rows  int64 [num_rows] element offsets of each row in `slot_tables`
  *   free_rows  int64 [num_rows] element offset in `free_stack` where this row's
- *              dropped slots start (kv_len - budget entries each), or NULL
+ *              dropped slots start (its kv_len - budget entries), or NULL
  *   keep_out   int32 [num_rows][budget] ascending kept indices (may be NULL)
  */
 int svb200_h2o_select_compact(float* cumulative, const int64_t* cum_rows,
                               int32_t* slot_tables, const int64_t* slot_rows,
                               int32_t* free_stack, const int64_t* free_rows,
-                              int32_t* keep_out, int32_t num_rows, int32_t kv_len,
-                              int32_t budget, int32_t recent, void* stream);
+                              int32_t* keep_out, int32_t num_rows, const int32_t* kv_lens,
+                              int32_t kv_len, int32_t budget, int32_t recent, void* stream);
 
 /*
  * Store the new K/V rows of one layer and (quest_bounds_layer != NULL) refresh the

@@ -58,6 +58,15 @@ H2O_CASES = {
 }
 
 
+# H2O prefill window scoring: rows = (physical prefix length before the chunk, chunk length); `window` = queries
+# scored at the end of every chunk (h2o_prefill_score_window)
+H2O_PREFILL_CASES = {
+    "h2o_prefill_g4_w32": dict(seed=51, hq=8, hkv=2, rows=[(0, 200), (150, 100), (64, 20)], window=32, num_slots=1024),
+    "h2o_prefill_g7_w32": dict(seed=52, hq=28, hkv=4, rows=[(96, 129), (0, 33)], window=32, num_slots=512),
+    "h2o_prefill_g8_w128": dict(seed=53, hq=16, hkv=2, rows=[(300, 256), (0, 128)], window=128, num_slots=1024),
+}
+
+
 def _rng(seed: int) -> np.random.Generator:
     return np.random.Generator(np.random.PCG64(int(seed)))
 
@@ -186,3 +195,33 @@ def make_h2o_scores(*, seed, rows, kv_len, ties, **_):
     if ties:
         scores = (scores * 8).floor() / 8  # massive ties: the stable order must decide
     return scores
+
+
+def make_h2o_prefill_inputs(*, seed, hq, hkv, rows, window, num_slots, d=128, **_):
+    """A prefill chunk per row on top of a compressed physical prefix: q of the chunk tokens (all rows
+    concatenated), K cache, shuffled slot tables, and the score ranges of prefill_score_ranges (h2o.py:749-776)."""
+    gen = _rng(seed)
+    bsz = len(rows)
+    k_cache = randn_bf16(gen, num_slots, hkv, d)
+    ctx = [c + n for c, n in rows]
+    width = max(ctx)
+    table = torch.zeros((bsz + 1, width), dtype=torch.int32)
+    perm = randperm(gen, num_slots).to(torch.int32)
+    cursor = 0
+    req = torch.arange(bsz, 0, -1, dtype=torch.int32)  # reversed table rows
+    for b in range(bsz):
+        table[int(req[b]), : ctx[b]] = perm[cursor: cursor + ctx[b]]
+        cursor += ctx[b]
+    total = sum(n for _, n in rows)
+    q = randn_bf16(gen, total, hq, d)
+    start_loc, off = [], 0
+    for _, n in rows:
+        start_loc.append(off)
+        off += n
+    cache_lens = [c for c, _ in rows]
+    starts = [max(c, c + n - window) if window > 0 else c for c, n in rows]
+    return dict(q=q, k_cache=k_cache, slot_table=table, req_indices=req,
+                start_loc=torch.tensor(start_loc, dtype=torch.int32), context_lens=torch.tensor(ctx, dtype=torch.int32),
+                prompt_cache_lens=torch.tensor(cache_lens, dtype=torch.int32),
+                score_starts=torch.tensor(starts, dtype=torch.int32), score_ends=torch.tensor(ctx, dtype=torch.int32),
+                max_query_len=max(e - s_ for s_, e in zip(starts, ctx)), max_context_len=width)

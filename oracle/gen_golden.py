@@ -229,6 +229,23 @@ def h2o_case(name, *, seed, rows, kv_len, budget, ratio, ties):
     print(f"[h2o] {name}: keep {tuple(keep_b.shape)}")
 
 
+def h2o_prefill_case(name, **cfg):
+    """Reference Triton prefill scoring (three kernels, probability mode) under the interpreter, fp32-upcast
+    inputs, with the arguments H2OCacheManager.collect_prefill_attention_score passes (h2o.py:849-865)."""
+    from sparsevllm.kernels.triton.prefill_score import prefill_score_fwd
+
+    inp = cases.make_h2o_prefill_inputs(**cfg)
+    bsz = len(cfg["rows"])
+    score = torch.empty(bsz, inp["max_context_len"], dtype=torch.float32)
+    prefill_score_fwd(inp["q"].float(), inp["k_cache"].float(), score, inp["req_indices"], inp["start_loc"],
+                      inp["context_lens"], inp["prompt_cache_lens"], inp["max_query_len"], inp["slot_table"],
+                      inp["score_starts"], inp["score_ends"], candidate_start=0, num_recent_tokens=0,
+                      score_mode="probability")
+    np.savez_compressed(GOLDEN / f"{name}.npz", digest=np.array(cases.digest(inp["q"], inp["k_cache"], inp["slot_table"])),
+                        score=score.numpy())
+    print(f"[h2o prefill] {name}: score {tuple(score.shape)} sums {score.sum(dim=1).tolist()}")
+
+
 def main():
     torch.set_num_threads(max(1, os.cpu_count() or 1))
     for name, cfg in {**cases.QUEST_CASES, **cases.QUEST_BASELINE_CASES}.items():
@@ -237,6 +254,8 @@ def main():
         attention_case(name, **cfg)
     for name, cfg in cases.H2O_CASES.items():
         h2o_case(name, **cfg)
+    for name, cfg in cases.H2O_PREFILL_CASES.items():
+        h2o_prefill_case(name, **cfg)
 
 
 if __name__ == "__main__":

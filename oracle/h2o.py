@@ -75,3 +75,58 @@ def compact_rows(slot_rows: torch.Tensor, scores: torch.Tensor, keep: torch.Tens
     out = torch.zeros_like(slot_rows)
     out[:, :budget] = new_slots
     return out, scores.gather(1, keep), dropped
+
+
+def prefill_window_score(q, k_cache, slot_table, req_indices, start_loc, context_lens, prompt_cache_lens, score_starts,
+                         score_ends, *, candidate_start: int = 0, num_recent_tokens: int = 0):
+    """Token scores of a prefill chunk: ``prefill_score_fwd`` in probability mode
+    (kernels/triton/prefill_score.py:70-428; wrapper 430-680) as H2O drives it (h2o.py:778-894).
+
+    For row b the queries at physical positions [score_starts[b], score_ends[b]) attend causally to kv positions
+    in [candidate_start, max(candidate_start, ctx - num_recent)); logits are q.k * D^-0.5, masked entries -1e20,
+    every (query, head) row is softmax-normalised over the candidates (a row with no candidate contributes 0);
+    score[b][kv] = max over q heads of sum over queries of the probabilities / max(score_end - score_start, 1).
+    Returns fp32 [B, max(context_lens)] (zeros outside the candidate range)."""
+    bsz = int(req_indices.numel())
+    hq, d = int(q.shape[1]), int(q.shape[2])
+    hkv = int(k_cache.shape[1])
+    g = hq // hkv
+    out = torch.zeros((bsz, int(context_lens.max())), dtype=torch.float32)
+    scale = float(d) ** -0.5
+    for b in range(bsz):
+        ctx, cache_len = int(context_lens[b]), int(prompt_cache_lens[b])
+        chunk_len = ctx - cache_len
+        qs, qe = int(score_starts[b]), int(score_ends[b])
+        ce = max(candidate_start, ctx - num_recent_tokens)
+        if ce <= candidate_start:
+            continue
+        q_abs = torch.arange(qs, qe)
+        q_rel = q_abs - cache_len
+        ok = (q_rel >= 0) & (q_rel < chunk_len)
+        q_abs, q_rel = q_abs[ok], q_rel[ok]
+        if q_abs.numel() == 0:
+            continue
+        kv_pos = torch.arange(candidate_start, ce)
+        slots = slot_table[int(req_indices[b]), candidate_start:ce].long()
+        k = k_cache[slots].float()                                  # [n, Hkv, D]
+        qv = q[int(start_loc[b]) + q_rel].float()                   # [nq, Hq, D]
+        kk = k.repeat_interleave(g, dim=1)                          # [n, Hq, D]
+        logits = torch.einsum("qhd,nhd->hqn", qv, kk) * scale
+        causal = q_abs[:, None] >= kv_pos[None, :]
+        logits = torch.where(causal[None], logits, torch.full_like(logits, -1.0e20))
+        m = logits.max(dim=-1, keepdim=True).values
+        p = torch.where(causal[None], torch.exp(logits - m), torch.zeros_like(logits))
+        l = p.sum(dim=-1, keepdim=True)
+        p = p / torch.where(l > 0, l, torch.ones_like(l))
+        head_score = p.sum(dim=1) / float(max(qe - qs, 1))          # [Hq, n]
+        out[b, candidate_start:ce] = head_score.max(dim=0).values
+    return out
+
+
+def accumulate_prefill(previous, step_score, new_len: int, weight: float):
+    """``H2OCacheManager._accumulate_score`` (h2o.py:611-626): zero-extend the previous cumulative vector to
+    ``new_len`` and add ``weight * step_score[:new_len]``."""
+    cum = torch.zeros(new_len, dtype=torch.float32)
+    if previous is not None:
+        cum[: previous.numel()] = previous.float()
+    return cum + float(weight) * step_score[:new_len].float()

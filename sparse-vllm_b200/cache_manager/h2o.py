@@ -34,7 +34,8 @@ class H2OCacheManager(CacheManager):
     sparse_method = "h2o"
 
     def __init__(self, config, *, num_layers: int, num_kv_heads: int, num_slots: int, max_rows: int,
-                 device, head_dim: int = ops.HEAD_DIM, provider: B200SparseDecodeProvider | None = None) -> None:
+                 device, head_dim: int = ops.HEAD_DIM, provider: B200SparseDecodeProvider | None = None,
+                 max_prefill_chunk: int = 0) -> None:
         super().__init__(num_layers=num_layers, num_kv_heads=num_kv_heads, head_dim=head_dim,
                          num_slots=num_slots, device=device)
         self.config = config
@@ -44,12 +45,18 @@ class H2OCacheManager(CacheManager):
         if self.budget <= 0 or self.interval <= 0:
             raise ValueError("h2o_decode_budget and h2o_eviction_interval must be positive.")
         self.max_rows = int(max_rows)
-        # a row never holds more than budget + interval tokens between two evictions
-        self.width = self.budget + self.interval
+        self.prefill_budget = int(getattr(config, "h2o_prefill_budget", self.budget))
+        self.score_window = int(getattr(config, "h2o_prefill_score_window", 128))
+        # a row never holds more than budget + interval tokens between two decode evictions, and during chunked
+        # prefill at most the prefill budget plus one chunk (h2o.py:665-748)
+        self.max_prefill_chunk = int(max_prefill_chunk)
+        self.decode_width = self.budget + self.interval
+        self.width = max(self.decode_width,
+                         self.prefill_budget + self.max_prefill_chunk if self.max_prefill_chunk > 0 else 0)
         L, R, W = self.num_layers, self.max_rows, self.width
         self.slot_tables = torch.zeros((L, R, W), dtype=torch.int32, device=self.device)
         self.cumulative = torch.zeros((L * R, W), dtype=torch.float32, device=self.device)
-        self.step_scores = torch.full((L, R, W), SCORE_FILL, dtype=torch.float32, device=self.device)
+        self.step_scores = torch.full((L, R, self.decode_width), SCORE_FILL, dtype=torch.float32, device=self.device)
         self.free_stack = torch.arange(self.num_slots, dtype=torch.int32, device=self.device).repeat(L, 1).contiguous()
         self.num_free = self.num_slots
         self.row_seq_lens = np.zeros((R,), dtype=np.int32)
@@ -60,7 +67,13 @@ class H2OCacheManager(CacheManager):
         self._batch = 0
         self._kv_lens_dev = torch.zeros((R,), dtype=torch.int32, device=self.device)
         self._rows_dev: torch.Tensor | None = None
+        self._rows_dev_i32 = torch.zeros((R,), dtype=torch.int32, device=self.device)
         self._batch_rows: list[int] = []
+        # rows that decoded since they were admitted (h2o.py:1498-1516 `_h2o_active_decode_seq_ids`): under slot
+        # pressure every such row that is over budget is reclaimable, scheduled in this step or not
+        self._active_decode_rows: set[int] = set()
+        # the layer-end kernel hands the step-score rows back pre-filled with SCORE_FILL (no refill launch per step)
+        self.refill_in_kernel = True
         self._provider = provider
 
     # ------------------------------------------------------------------ provider
@@ -120,7 +133,91 @@ class H2OCacheManager(CacheManager):
             self.free_stack[:, self.num_free: self.num_free + n] = self.slot_tables[:, row, :n]
             self.num_free += n
         self.row_seq_lens[row] = 0
+        self._active_decode_rows.discard(row)
         self._free_rows.append(row)
+
+    # ------------------------------------------------------------------ prefill side
+    def allocate_prefill_chunk(self, seq_id: int, num_tokens: int) -> torch.Tensor:
+        """Append a chunk of ``num_tokens`` prompt tokens to the sequence's compressed physical row in EVERY
+        layer (``_prepare_prefill``, h2o.py:665-748): returns the ``[L, num_tokens]`` slots to store the chunk's
+        K/V rows at (``save_rope_kv_if_needed(layer, k, v, slots[layer])``)."""
+        row = self._get_free_row(seq_id)
+        cur = int(self.row_seq_lens[row])
+        n = int(num_tokens)
+        if cur + n > self.width:
+            raise RuntimeError(f"H2O prefill chunk does not fit the row: have={cur} chunk={n} width={self.width} "
+                               "(construct the manager with max_prefill_chunk >= the chunk size).")
+        slots = self._pop_slots(n)
+        self.slot_tables[:, row, cur: cur + n] = slots
+        self.row_seq_lens[row] = cur + n
+        return slots
+
+    def collect_prefill_attention_score(self, layer_idx: int, q: torch.Tensor, seq_ids: list[int],
+                                        chunk_lens: list[int], b_start_loc: torch.Tensor | None = None) -> torch.Tensor:
+        """Score the layer's chunk (h2o.py:778-894): the last ``h2o_prefill_score_window`` queries of every
+        row's chunk attend causally to the whole physical row; the max-over-heads token probabilities are added,
+        weighted by the number of scoring queries, to the row's cumulative scores (new positions start at 0).
+        ``q [sum(chunk_lens), Hq, D]`` holds the chunk tokens of all rows; the chunk's K rows are already stored
+        (``allocate_prefill_chunk`` + ``save_rope_kv_if_needed``).  Returns the step scores ``[B, max ctx]``."""
+        kv_idx = self.kv_layer_index(layer_idx)
+        rows = [self.seq_id_to_row[int(sid)] for sid in seq_ids]
+        ctx = [int(self.row_seq_lens[r]) for r in rows]
+        cache = [c - int(n) for c, n in zip(ctx, chunk_lens)]
+        if min(cache) < 0:
+            raise RuntimeError(f"H2O current chunk exceeds its physical row: context={ctx} chunk={list(chunk_lens)}.")
+        starts = [max(c, e - self.score_window) for c, e in zip(cache, ctx)]  # prefill_score_ranges, h2o.py:749-776
+        host = np.empty((6, len(rows)), dtype=np.int32)
+        host[0], host[1], host[2], host[3], host[4] = rows, ctx, cache, starts, ctx
+        host[5] = np.concatenate(([0], np.cumsum(chunk_lens)[:-1]))
+        meta = torch.from_numpy(host).to(self.device)
+        start_loc = meta[5] if b_start_loc is None else b_start_loc
+        max_ctx = max(ctx)
+        key = (len(rows), max_ctx)
+        if getattr(self, "_prefill_score_buf", None) is None or self._prefill_score_key != key:
+            self._prefill_score_buf = torch.empty((len(rows), (max_ctx + 63) // 64 * 64), dtype=torch.float32, device=self.device)
+            self._prefill_score_key = key
+        k_cache, _ = self.get_layer_kv_cache(layer_idx)
+        cum = self.cumulative.view(self.num_layers, self.max_rows, self.width)[kv_idx]
+        ops.h2o_prefill_score(q, k_cache, self.slot_tables[kv_idx], meta[0], start_loc, meta[1], meta[2], meta[3], meta[4],
+                              self._prefill_score_buf, max_query_len=max(e - s for s, e in zip(starts, ctx)),
+                              max_context_len=max_ctx, cumulative=cum, cum_rows=meta[0])
+        return self._prefill_score_buf[:, :max_ctx]
+
+    def evict_after_prefill(self, seq_ids: list[int], final: bool, keep_out: torch.Tensor | None = None) -> bool:
+        """After a chunk's forward (h2o.py:1352-1496): rows longer than the prefill budget (``final``: the decode
+        budget) keep their heavy hitters plus the recent suffix in every layer.  Index-only compaction of slot rows
+        and cumulative scores, dropped slots back to the free stacks.  (The reference additionally MOVES the kept
+        K/V rows of a final chunk into the row's lowest slots, h2o.py:1181-1350; here attention always reads
+        through the slot table, so the bytes stay where they are.)"""
+        budget = self.budget if final else self.prefill_budget
+        rows = [self.seq_id_to_row[int(sid)] for sid in seq_ids]
+        evict = [r for r in rows if int(self.row_seq_lens[r]) > budget]
+        self.last_evicted_rows = evict
+        if not evict:
+            return False
+        self._compact_rows(evict, budget, keep_out)
+        return True
+
+    def _compact_rows(self, evict: list[int], budget: int, keep_out: torch.Tensor | None) -> None:
+        L, R, W = self.num_layers, self.max_rows, self.width
+        lens = self.row_seq_lens[evict].astype(np.int64)
+        drops = lens - budget
+        if self.num_free + int(drops.sum()) > self.num_slots:
+            raise RuntimeError(f"H2O eviction would overflow the free-slot stack: end={self.num_free + int(drops.sum())} "
+                               f"capacity={self.num_slots}.")
+        rows_t = torch.as_tensor(evict, dtype=torch.int64, device=self.device)
+        layer_t = torch.arange(L, device=self.device, dtype=torch.int64)[:, None]
+        offs = ((layer_t * R + rows_t[None, :]) * W).reshape(-1)
+        within = torch.as_tensor(np.concatenate(([0], np.cumsum(drops)[:-1])), dtype=torch.int64, device=self.device)
+        free_rows = (layer_t * self.num_slots + self.num_free + within[None, :]).reshape(-1)
+        kv_lens = torch.as_tensor(lens.astype(np.int32), device=self.device).repeat(L)
+        max_len = int(lens.max())
+        recent = min(max(1, int(budget * self.recent_ratio)), budget)  # h2o.py:498-499
+        ops.h2o_select_compact(self.cumulative, offs, self.slot_tables, offs, kv_len=max_len, budget=budget,
+                               recent=recent, free_stack=self.free_stack, free_rows=free_rows,
+                               keep_out=keep_out, kv_lens=kv_lens)
+        self.num_free += int(drops.sum())
+        self.row_seq_lens[evict] = budget
 
     # ------------------------------------------------------------------ decode step (host)
     def prepare_decode_static(self, seqs, input_ids, positions, slot_mapping, context_lens, req_indices) -> None:
@@ -129,7 +226,7 @@ class H2OCacheManager(CacheManager):
         bsz = len(seqs)
         rows = [self.seq_id_to_row[int(s.seq_id)] for s in seqs]
         lens = self.row_seq_lens[rows]
-        if int(lens.max()) + 1 > self.width:
+        if int(lens.max()) + 1 > self.decode_width:
             raise RuntimeError("row longer than budget + interval: evict_after_decode() was not called.")
         new = self._pop_slots(bsz)  # [L, B]
         rows_dev = torch.as_tensor(rows, dtype=torch.int64, device=self.device)
@@ -144,12 +241,14 @@ class H2OCacheManager(CacheManager):
         slot_mapping[:bsz] = new[0]
         self._kv_lens_dev[:bsz] = ctx
         self._rows_dev = rows_dev
+        self._rows_dev_i32[:bsz] = rows_dev.to(torch.int32)
         self._batch_rows = rows
         self.layer_batch_state.slot_mapping = slot_mapping[:bsz]
         self.layer_batch_state.context_lens = context_lens[:bsz]
         self.layer_batch_state.req_indices = req_indices[:bsz]
-        self.layer_batch_state.max_context_len = self.width
-        self.step_scores[:, :bsz].fill_(SCORE_FILL)  # sparse_controller.py:545-594
+        self.layer_batch_state.max_context_len = self.decode_width
+        if not self.refill_in_kernel:
+            self.step_scores[:, :bsz].fill_(SCORE_FILL)  # sparse_controller.py:545-594
 
     def layer_slot_mapping(self, layer_idx: int) -> torch.Tensor:
         return self._layer_slot_mapping[self.kv_layer_index(layer_idx), : self._batch]
@@ -166,7 +265,7 @@ class H2OCacheManager(CacheManager):
         bsz = int(st.context_lens.numel())
         kv_idx = self.kv_layer_index(layer_idx)
         return SparseSelection(kind="h2o", req_indices=st.req_indices, context_lens=st.context_lens,
-                               max_context_len=self.width, attn_score=self.step_scores[kv_idx, :bsz],
+                               max_context_len=self.decode_width, attn_score=self.step_scores[kv_idx, :bsz],
                                active_slots=self.slot_tables[kv_idx])
 
     def _default_active_slots_for_selection(self, layer_idx, selection):
@@ -174,45 +273,38 @@ class H2OCacheManager(CacheManager):
 
     def on_layer_attention_end(self, layer_idx: int) -> None:
         """softmax(score * D^-0.5) in place (sparse_controller.py:761-767) fused with the cumulative update
-        (h2o.py:958-1038): cum[:kv_len-1] += step, cum[kv_len-1] = step."""
+        (h2o.py:958-1038): cum[:kv_len-1] += step, cum[kv_len-1] = step.  Batch entry b updates the cumulative
+        row of ITS request row (any row set, in any order)."""
         kv_idx = self.kv_layer_index(layer_idx)
         bsz = len(self._batch_rows)
-        rows = self._batch_rows
         cum = self.cumulative.view(self.num_layers, self.max_rows, self.width)[kv_idx]
-        if rows != list(range(rows[0], rows[0] + bsz)):
-            raise NotImplementedError("decode batches must use consecutive rows (the fused update indexes them by stride).")
         ops.h2o_normalize_accumulate(self.step_scores[kv_idx, :bsz], 1.0 / math.sqrt(self.head_dim),
-                                     cumulative=cum[rows[0]: rows[0] + bsz], kv_lens=self._kv_lens_dev[:bsz],
-                                     width=self.width)
+                                     cumulative=cum, kv_lens=self._kv_lens_dev[:bsz], width=self.decode_width,
+                                     cum_rows=self._rows_dev_i32[:bsz],
+                                     refill=SCORE_FILL if self.refill_in_kernel else 0.0)
 
     # ------------------------------------------------------------------ eviction
     def recent_count(self, kv_len: int) -> int:
         return min(max(1, int(self.budget * self.recent_ratio)), self.budget, kv_len)  # h2o.py:498-499
 
     def evict_after_decode(self, keep_out: torch.Tensor | None = None) -> bool:
-        """Burst eviction (h2o.py:1498-1625): when the batch rows reached budget + interval tokens (or
-        the free stack is empty and they exceed the budget) every (layer, row) keeps the heavy hitters
-        plus the recent suffix; slot rows and cumulative scores are compacted in place, dropped slots go
-        back to the layer's free stack.  Returns True if an eviction ran."""
-        rows = self._batch_rows
+        """Burst eviction (h2o.py:1498-1625): every row of the decode batch that reached budget + interval
+        tokens — or, when the step consumed the last free slot, every ACTIVE decode row over budget, scheduled
+        or not (1510-1522) — keeps its heavy hitters plus the recent suffix in every layer; slot rows and
+        cumulative scores are compacted in place, dropped slots go back to the layer's free stack.  Rows may
+        differ in length (the reference groups them by length; here one launch takes per-entry lengths).
+        ``keep_out`` [L * evicted rows, budget] receives the kept indices (row order = ``last_evicted_rows``).
+        Returns True if an eviction ran."""
+        rows = list(self._batch_rows)
         if not rows:
             return False
-        lens = self.row_seq_lens[rows]
-        kv_len = int(lens[0])
-        if not (lens == kv_len).all():
-            raise NotImplementedError("rows of one decode batch evict on a common length.")
-        if not (kv_len >= self.budget + self.interval or (self.num_free < len(rows) and kv_len >= self.budget + 1)):
+        self._active_decode_rows.update(rows)
+        under_pressure = self.num_free <= 0
+        trigger = self.budget + 1 if under_pressure else self.budget + self.interval
+        candidates = rows + (sorted(self._active_decode_rows.difference(rows)) if under_pressure else [])
+        evict = [r for r in candidates if int(self.row_seq_lens[r]) >= trigger]
+        self.last_evicted_rows = evict
+        if not evict:
             return False
-        L, R, W = self.num_layers, self.max_rows, self.width
-        drop = kv_len - self.budget
-        lr = (torch.arange(L, device=self.device, dtype=torch.int64)[:, None] * R + self._rows_dev[None, :]).reshape(-1)
-        offs = lr * W
-        within = torch.arange(len(rows), device=self.device, dtype=torch.int64) * drop
-        free_rows = (torch.arange(L, device=self.device, dtype=torch.int64)[:, None] * self.num_slots
-                     + self.num_free + within[None, :]).reshape(-1)
-        ops.h2o_select_compact(self.cumulative, offs, self.slot_tables, offs, kv_len=kv_len, budget=self.budget,
-                               recent=self.recent_count(kv_len), free_stack=self.free_stack, free_rows=free_rows,
-                               keep_out=keep_out)
-        self.num_free += len(rows) * drop
-        self.row_seq_lens[rows] = self.budget
+        self._compact_rows(evict, self.budget, keep_out)
         return True

@@ -64,6 +64,7 @@ class SparseMethodConfig:
     h2o_decode_eviction_interval: int = 128
     h2o_prefill_budget: int = 8192
     h2o_recent_ratio: float = 0.5
+    h2o_prefill_score_window: int = 128
 
     def __post_init__(self):
         self.vllm_sparse_method = normalize_sparse_method(self.vllm_sparse_method)
@@ -100,6 +101,9 @@ class SparseMethodConfig:
         self.h2o_recent_ratio = float(self.h2o_recent_ratio)
         if not 0.0 < self.h2o_recent_ratio < 1.0:
             raise ValueError(f"h2o_recent_ratio must be in (0, 1), got {self.h2o_recent_ratio}.")
+        if not 1 <= int(self.h2o_prefill_score_window) <= 128:  # configs/sparse.py:94-98 (probability mode)
+            raise ValueError("h2o_prefill_score_window must be in [1, 128] because the prefill score kernel supports at "
+                             f"most 128 query tokens, got {self.h2o_prefill_score_window}.")
 
     @property
     def h2o_decode_capacity(self) -> int:

@@ -449,20 +449,52 @@ int svb200_ipc_close(void* ptr) {
 
 int svb200_h2o_normalize_accumulate(float* score, int64_t score_stride, int32_t batch,
                                     int32_t width, float scale, float* cumulative,
-                                    int64_t cum_stride, const int32_t* kv_lens, void* stream) {
+                                    int64_t cum_stride, const int32_t* cum_rows, const int32_t* kv_lens,
+                                    float refill, void* stream) {
   SV_REQUIRE(batch >= 0 && width >= 0, "h2o_normalize_accumulate: negative batch/width");
   if (batch == 0 || width == 0) return 0;
   SV_REQUIRE(score != nullptr && score_stride >= width, "h2o_normalize_accumulate: score null or stride %lld < width %d", (long long)score_stride, width);
   if (cumulative != nullptr)
     SV_REQUIRE(kv_lens != nullptr && cum_stride >= 1, "h2o_normalize_accumulate: cumulative needs kv_lens and a positive stride");
   return launch_h2o_normalize_accumulate(score, score_stride, batch, width, scale, cumulative,
-                                         cum_stride, kv_lens, (cudaStream_t)stream);
+                                         cum_stride, cum_rows, kv_lens, refill, (cudaStream_t)stream);
+}
+
+int svb200_h2o_prefill_score(const void* q, int64_t q_stride, const void* k_cache, int64_t num_slots,
+                             const int32_t* slot_table, int64_t slot_table_stride, const int32_t* req_rows,
+                             const int32_t* start_loc, const int32_t* context_lens,
+                             const int32_t* prompt_cache_lens, const int32_t* score_starts,
+                             const int32_t* score_ends, float* score, int64_t score_stride,
+                             float* cumulative, int64_t cum_stride, const int32_t* cum_rows, int32_t batch,
+                             int32_t num_q_heads, int32_t num_kv_heads, int32_t max_query_len,
+                             int32_t max_context_len, int32_t candidate_start, int32_t num_recent_tokens,
+                             float sm_scale, void* stream) {
+  const char* who = "h2o_prefill_score";
+  SV_REQUIRE(batch >= 0 && max_query_len >= 0 && max_context_len >= 0, "%s: negative sizes", who);
+  if (batch == 0 || max_query_len == 0 || max_context_len == 0) return 0;
+  SV_REQUIRE(q && k_cache && slot_table && req_rows && start_loc && context_lens && prompt_cache_lens && score_starts &&
+                 score_ends && score, "%s: null pointer", who);
+  SV_REQUIRE(aligned16(q) && aligned16(k_cache), "%s: q / k_cache must be 16-byte aligned", who);
+  if (int rc = check_heads(who, num_q_heads, num_kv_heads)) return rc;
+  SV_REQUIRE(q_stride >= (int64_t)num_q_heads * SVB200_HEAD_DIM && q_stride % 8 == 0, "%s: bad q token stride %lld", who, (long long)q_stride);
+  SV_SUPPORTED(max_query_len <= 128, "%s: probability scoring serves windows of <= 128 queries, got %d (prefill_score.py:505-509)", who, max_query_len);
+  SV_REQUIRE(score_stride >= max_context_len && slot_table_stride >= max_context_len && num_slots > 0,
+             "%s: score_stride=%lld / slot_table_stride=%lld must cover max_context_len=%d", who, (long long)score_stride,
+             (long long)slot_table_stride, max_context_len);
+  SV_REQUIRE(candidate_start >= 0 && num_recent_tokens >= 0, "%s: negative candidate range", who);
+  if (cumulative != nullptr) SV_REQUIRE(cum_rows != nullptr && cum_stride >= max_context_len, "%s: cumulative needs cum_rows and a stride covering max_context_len", who);
+  PrefillScoreHostArgs h{q, q_stride, k_cache, num_slots, slot_table, slot_table_stride, req_rows, start_loc, context_lens,
+                         prompt_cache_lens, score_starts, score_ends, score, score_stride, cumulative, cum_stride, cum_rows,
+                         batch, num_q_heads, num_kv_heads, max_query_len, max_context_len, candidate_start, num_recent_tokens,
+                         sm_scale};
+  return launch_h2o_prefill_score(h, (cudaStream_t)stream);
 }
 
 int svb200_h2o_select_compact(float* cumulative, const int64_t* cum_rows, int32_t* slot_tables,
                               const int64_t* slot_rows, int32_t* free_stack,
                               const int64_t* free_rows, int32_t* keep_out, int32_t num_rows,
-                              int32_t kv_len, int32_t budget, int32_t recent, void* stream) {
+                              const int32_t* kv_lens, int32_t kv_len, int32_t budget, int32_t recent,
+                              void* stream) {
   SV_REQUIRE(num_rows >= 0, "h2o_select_compact: num_rows=%d < 0", num_rows);
   if (num_rows == 0) return 0;
   SV_REQUIRE(cumulative && cum_rows && slot_tables && slot_rows, "h2o_select_compact: null pointer");
@@ -471,7 +503,7 @@ int svb200_h2o_select_compact(float* cumulative, const int64_t* cum_rows, int32_
   SV_REQUIRE((free_stack == nullptr) == (free_rows == nullptr), "h2o_select_compact: free_stack and free_rows go together");
   SV_SUPPORTED((int64_t)kv_len * 12 <= 200 * 1024, "h2o_select_compact: kv_len=%d too long for the shared-memory row cache", kv_len);
   return launch_h2o_select_compact(cumulative, cum_rows, slot_tables, slot_rows, free_stack,
-                                   free_rows, keep_out, num_rows, kv_len, budget, recent,
+                                   free_rows, keep_out, num_rows, kv_lens, kv_len, budget, recent,
                                    (cudaStream_t)stream);
 }
 

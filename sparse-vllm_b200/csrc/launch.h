@@ -131,11 +131,25 @@ int launch_sparse_decode_attn(const AttnParams& p, int heads_per_cta, cudaStream
 // h2o.cu
 int launch_h2o_normalize_accumulate(float* score, int64_t score_stride, int batch, int width,
                                     float scale, float* cumulative, int64_t cum_stride,
-                                    const int32_t* kv_lens, cudaStream_t stream);
+                                    const int32_t* cum_rows, const int32_t* kv_lens, float refill,
+                                    cudaStream_t stream);
 int launch_h2o_select_compact(float* cumulative, const int64_t* cum_rows, int32_t* slot_tables,
                               const int64_t* slot_rows, int32_t* free_stack,
-                              const int64_t* free_rows, int32_t* keep_out, int num_rows, int kv_len,
-                              int budget, int recent, cudaStream_t stream);
+                              const int64_t* free_rows, int32_t* keep_out, int num_rows,
+                              const int32_t* kv_lens, int kv_len, int budget, int recent, cudaStream_t stream);
+
+struct PrefillScoreHostArgs {
+  const void* q; int64_t q_stride;
+  const void* k_cache; int64_t num_slots;
+  const int32_t* slot_table; int64_t table_stride;
+  const int32_t* req_rows; const int32_t* start_loc; const int32_t* context_lens;
+  const int32_t* prompt_cache_lens; const int32_t* score_starts; const int32_t* score_ends;
+  float* score; int64_t score_stride;
+  float* cumulative; int64_t cum_stride; const int32_t* cum_rows;
+  int batch, hq, hkv, max_query_len, max_context_len, candidate_start, num_recent;
+  float sm_scale;
+};
+int launch_h2o_prefill_score(const PrefillScoreHostArgs& h, cudaStream_t stream);
 
 // collective.cu
 struct AllReduceArgs {

@@ -385,8 +385,11 @@ def allreduce_sum_bf16(comm, inp: torch.Tensor, out: torch.Tensor) -> torch.Tens
 
 # ----------------------------------------------------------------------------- H2O
 def h2o_normalize_accumulate(score: torch.Tensor, scale: float, cumulative: torch.Tensor | None = None,
-                             kv_lens: torch.Tensor | None = None, width: int | None = None) -> torch.Tensor:
-    """In-place ``softmax(score * scale)`` per row (+ fused cumulative update) (svb200_h2o_normalize_accumulate)."""
+                             kv_lens: torch.Tensor | None = None, width: int | None = None,
+                             cum_rows: torch.Tensor | None = None, refill: float = 0.0) -> torch.Tensor:
+    """In-place ``softmax(score * scale)`` per row (+ fused cumulative update) (svb200_h2o_normalize_accumulate).
+    ``cum_rows`` [B] int32: row of each batch entry inside ``cumulative`` (default: entry b -> row b);
+    ``refill`` != 0: leave the score rows holding ``refill`` instead of the normalised values."""
     require_cuda(score, "score", torch.float32)
     if score.dim() != 2 or score.stride(1) != 1:
         raise ValueError(f"score must be fp32 [B, W] with contiguous W, got {tuple(score.shape)}/{score.stride()}.")
@@ -395,25 +398,68 @@ def h2o_normalize_accumulate(score: torch.Tensor, scale: float, cumulative: torc
     cum_stride = 0
     if cumulative is not None:
         require_cuda(cumulative, "cumulative", torch.float32)
-        if cumulative.dim() != 2 or cumulative.shape[0] < bsz or cumulative.stride(1) != 1 or kv_lens is None:
-            raise ValueError("cumulative must be fp32 [B, >=kv_len] and needs kv_lens.")
+        if cumulative.dim() != 2 or cumulative.stride(1) != 1 or kv_lens is None or \
+                (cum_rows is None and cumulative.shape[0] < bsz):
+            raise ValueError("cumulative must be fp32 [rows, >=kv_len] and needs kv_lens.")
         _i32(kv_lens, "kv_lens")
+        if cum_rows is not None:
+            _i32(cum_rows, "cum_rows")
+            if int(cum_rows.numel()) != bsz:
+                raise ValueError("cum_rows must hold one row index per batch entry.")
         cum_stride = int(cumulative.stride(0))
     lib = _native.load()
     check(lib.svb200_h2o_normalize_accumulate(
-        ptr(score), int(score.stride(0)), bsz, width, float(scale), ptr(cumulative), cum_stride, ptr(kv_lens),
+        ptr(score), int(score.stride(0)), bsz, width, float(scale), ptr(cumulative), cum_stride,
+        ptr(cum_rows) if cumulative is not None else None, ptr(kv_lens), float(refill),
         current_stream_ptr(score.device)), "svb200_h2o_normalize_accumulate")
+    return score
+
+
+def h2o_prefill_score(q: torch.Tensor, k_cache: torch.Tensor, slot_table: torch.Tensor, req_rows: torch.Tensor,
+                      start_loc: torch.Tensor, context_lens: torch.Tensor, prompt_cache_lens: torch.Tensor,
+                      score_starts: torch.Tensor, score_ends: torch.Tensor, score: torch.Tensor, *, max_query_len: int,
+                      max_context_len: int, cumulative: torch.Tensor | None = None, cum_rows: torch.Tensor | None = None,
+                      candidate_start: int = 0, num_recent_tokens: int = 0, sm_scale: float | None = None) -> torch.Tensor:
+    """Prefill window token scores (+ fused cumulative update) (svb200_h2o_prefill_score)."""
+    require_cuda(q, "q", torch.bfloat16)
+    if q.dim() != 3 or q.shape[2] != HEAD_DIM or q.stride(2) != 1 or q.stride(1) != HEAD_DIM:
+        raise ValueError(f"q must be [T, Hq, {HEAD_DIM}] with contiguous heads, got {tuple(q.shape)}/{q.stride()}.")
+    num_slots, hkv = _kv_layer(k_cache, "k_cache")
+    for t, n in ((slot_table, "slot_table"), (req_rows, "req_rows"), (start_loc, "start_loc"), (context_lens, "context_lens"),
+                 (prompt_cache_lens, "prompt_cache_lens"), (score_starts, "score_starts"), (score_ends, "score_ends")):
+        _i32(t, n)
+    bsz = int(req_rows.numel())
+    require_cuda(score, "score", torch.float32)
+    if score.dim() != 2 or score.shape[0] < bsz or score.stride(1) != 1 or score.shape[1] < max_context_len:
+        raise ValueError(f"score must be fp32 [B, >= max_context_len] with contiguous columns, got {tuple(score.shape)}.")
+    cum_stride = 0
+    if cumulative is not None:
+        require_cuda(cumulative, "cumulative", torch.float32)
+        if cumulative.dim() != 2 or cumulative.stride(1) != 1 or cum_rows is None:
+            raise ValueError("cumulative must be fp32 [rows, >= max_context_len] and needs cum_rows.")
+        _i32(cum_rows, "cum_rows")
+        cum_stride = int(cumulative.stride(0))
+    if sm_scale is None:
+        sm_scale = 1.0 / math.sqrt(HEAD_DIM)
+    lib = _native.load()
+    check(lib.svb200_h2o_prefill_score(
+        ptr(q), int(q.stride(0)), ptr(k_cache), num_slots, ptr(slot_table), _rows_stride(slot_table, "slot_table"),
+        ptr(req_rows), ptr(start_loc), ptr(context_lens), ptr(prompt_cache_lens), ptr(score_starts), ptr(score_ends),
+        ptr(score), int(score.stride(0)), ptr(cumulative), cum_stride, ptr(cum_rows) if cumulative is not None else None,
+        bsz, int(q.shape[1]), hkv, int(max_query_len), int(max_context_len), int(candidate_start),
+        int(num_recent_tokens), float(sm_scale), current_stream_ptr(q.device)), "svb200_h2o_prefill_score")
     return score
 
 
 def h2o_select_compact(cumulative: torch.Tensor, cum_rows: torch.Tensor, slot_tables: torch.Tensor,
                        slot_rows: torch.Tensor, *, kv_len: int, budget: int, recent: int,
                        free_stack: torch.Tensor | None = None, free_rows: torch.Tensor | None = None,
-                       keep_out: torch.Tensor | None = None) -> None:
+                       keep_out: torch.Tensor | None = None, kv_lens: torch.Tensor | None = None) -> None:
     """Burst eviction: heavy hitters + recent suffix, index-only compaction (svb200_h2o_select_compact).
 
     ``cum_rows`` / ``slot_rows`` / ``free_rows`` are int64 ELEMENT offsets of each (layer,row) entry
-    inside ``cumulative`` / ``slot_tables`` / ``free_stack``."""
+    inside ``cumulative`` / ``slot_tables`` / ``free_stack``.  ``kv_lens`` [num_rows] int32: per-entry lengths
+    (then ``kv_len`` is the longest); entries not longer than ``budget`` are left alone."""
     require_cuda(cumulative, "cumulative", torch.float32)
     _i32(slot_tables, "slot_tables")
     for t, n in ((cum_rows, "cum_rows"), (slot_rows, "slot_rows")):
@@ -423,14 +469,19 @@ def h2o_select_compact(cumulative: torch.Tensor, cum_rows: torch.Tensor, slot_ta
         raise ValueError("cum_rows and slot_rows must have the same number of entries.")
     if free_stack is not None:
         _i32(free_stack, "free_stack"); require_cuda(free_rows, "free_rows", torch.int64)
+    if kv_lens is not None:
+        _i32(kv_lens, "kv_lens")
+        if int(kv_lens.numel()) != n_rows:
+            raise ValueError("kv_lens must hold one length per (layer, row) entry.")
     if keep_out is not None:
         _i32(keep_out, "keep_out")
-        if tuple(keep_out.shape) != (n_rows, budget) or not keep_out.is_contiguous():
-            raise ValueError("keep_out must be a contiguous [num_rows, budget] int32 tensor.")
+        if keep_out.dim() != 2 or int(keep_out.shape[0]) < n_rows or int(keep_out.shape[1]) != budget \
+                or not keep_out.is_contiguous():
+            raise ValueError("keep_out must be a contiguous [>= num_rows, budget] int32 tensor.")
     lib = _native.load()
     check(lib.svb200_h2o_select_compact(
         ptr(cumulative), ptr(cum_rows), ptr(slot_tables), ptr(slot_rows), ptr(free_stack), ptr(free_rows),
-        ptr(keep_out), n_rows, int(kv_len), int(budget), int(recent),
+        ptr(keep_out), n_rows, ptr(kv_lens), int(kv_len), int(budget), int(recent),
         current_stream_ptr(cumulative.device)), "svb200_h2o_select_compact")
 
 

@@ -52,7 +52,7 @@ def test_validation_errors_need_no_gpu(native_lib):
     assert b"null pointer" in native_lib.svb200_last_error()
     # tickets (256-byte rounded) + two (output + lse) fp32 partial records per SM (148 without a device)
     assert native_lib.svb200_workspace_bytes(32, 28, 4) == 512 + 148 * 2 * 28 * (128 + 4) * 4
-    rc = native_lib.svb200_h2o_select_compact(1, 1, 1, 1, None, None, None, 2, 100, 200, 10, None)
+    rc = native_lib.svb200_h2o_select_compact(1, 1, 1, 1, None, None, None, 2, None, 100, 200, 10, None)
     assert rc == 1 and b"kv_len" in native_lib.svb200_last_error()
 
 

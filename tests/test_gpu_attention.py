@@ -223,3 +223,41 @@ def test_h2o_select_compact_full_size():
     exp_slots, exp_scores, exp_drop = oh2o.compact_rows(slots, scores, ref_keep)
     assert torch.equal(tab, exp_slots) and torch.equal(cum[:, :budget], exp_scores)
     assert torch.equal(free[2: 2 + rows * (kv_len - budget)].view(rows, -1), exp_drop)
+
+
+@pytest.mark.parametrize("name", list(cases.H2O_PREFILL_CASES))
+def test_h2o_prefill_score_matches_reference(name, golden):
+    """svb200_h2o_prefill_score against the reference's Triton prefill scoring (golden: interpreter, fp32-upcast
+    inputs) and the oracle, plus the fused cumulative update (expand with zeros, weight = scoring queries)."""
+    from sparse_vllm_b200 import ops
+    cfg = cases.H2O_PREFILL_CASES[name]
+    inp = cases.make_h2o_prefill_inputs(**cfg)
+    g = golden(name)
+    assert str(g["digest"]) == cases.digest(inp["q"], inp["k_cache"], inp["slot_table"])
+    bsz, width = len(cfg["rows"]), inp["max_context_len"]
+    dev = {k: v.to(DEV) for k, v in inp.items() if isinstance(v, torch.Tensor)}
+    score = torch.full((bsz, width + 3), float("nan"), dtype=torch.float32, device=DEV)
+    gen = torch.Generator().manual_seed(1)
+    prev = torch.rand(bsz + 1, width + 5, generator=gen)  # cumulative rows (table rows), garbage beyond the prefix
+    cum = prev.clone().to(DEV)
+    for _ in range(2):  # idempotent w.r.t. the score buffer (the launcher zero-fills it)
+        ops.h2o_prefill_score(dev["q"], dev["k_cache"], dev["slot_table"], dev["req_indices"], dev["start_loc"],
+                              dev["context_lens"], dev["prompt_cache_lens"], dev["score_starts"], dev["score_ends"], score,
+                              max_query_len=inp["max_query_len"], max_context_len=width)
+    ops.h2o_prefill_score(dev["q"], dev["k_cache"], dev["slot_table"], dev["req_indices"], dev["start_loc"],
+                          dev["context_lens"], dev["prompt_cache_lens"], dev["score_starts"], dev["score_ends"], score,
+                          max_query_len=inp["max_query_len"], max_context_len=width, cumulative=cum, cum_rows=dev["req_indices"])
+    torch.cuda.synchronize()
+    ref = torch.from_numpy(g["score"])
+    orc = oh2o.prefill_window_score(inp["q"], inp["k_cache"], inp["slot_table"], inp["req_indices"], inp["start_loc"],
+                                    inp["context_lens"], inp["prompt_cache_lens"], inp["score_starts"], inp["score_ends"])
+    got = score.cpu()
+    for b, n in enumerate(inp["context_lens"].tolist()):
+        torch.testing.assert_close(got[b, :n], ref[b, :n], atol=2e-5, rtol=2e-3)
+        torch.testing.assert_close(got[b, :n], orc[b, :n], atol=2e-5, rtol=2e-3)
+        row = int(inp["req_indices"][b])
+        cache_len = int(inp["prompt_cache_lens"][b])
+        weight = float(inp["score_ends"][b] - inp["score_starts"][b])
+        want = oh2o.accumulate_prefill(prev[row, :cache_len] if cache_len else None, got[b], new_len=n, weight=weight)
+        torch.testing.assert_close(cum[row, :n].cpu(), want, atol=1e-5, rtol=1e-5)
+        assert torch.equal(cum[row, n:].cpu(), prev[row, n:]), "cumulative written beyond the row"
