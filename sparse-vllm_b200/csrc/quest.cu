@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(128) quest_decode_page_complete_kernel(
 constexpr int kMaxPrevBudget = 2047;
 
 struct SelectSmem {
-  int cnt[16];
+  int wcnt[16][8];  // per search round: one count per warp of the group (<= 8 warps), summed by every thread
   int warp_scan[33];
   int sel[kMaxPrevBudget + 1];
   int sel_slot[kMaxPrevBudget + 1];
@@ -213,8 +213,9 @@ __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, 
 
   // ---- k-th largest key: largest T with count(key >= T) >= k
   const unsigned long long tq1 = tdbg ? global_timer_ns() : 0;
-  if (tid < 16) sm.cnt[tid] = 0;
-  group_sync<BAR, NTHR>();
+  static_assert(NTHR <= 256, "SelectSmem::wcnt holds one count per warp of at most 8 warps");
+  constexpr int NWARP = NTHR / 32;
+  group_sync<BAR, NTHR>();  // sm.wcnt may still be read by a previous call
   uint32_t thresh = 0;
   for (int bit = 15; bit >= 0; --bit) {
     const uint32_t cand = thresh | (1u << bit), cand_hi = cand << 16;
@@ -235,10 +236,14 @@ __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, 
         c += ((w & 0xffffu) >= cand) ? 1 : 0;
       });
     }
+    // one slot per (round, warp): no atomics, no reset; every thread sums the warps' counts after the barrier
     c = __reduce_add_sync(0xffffffffu, c);
-    if (lane == 0 && c) atomicAdd(&sm.cnt[bit], c);
+    if (lane == 0) sm.wcnt[bit][tid >> 5] = c;
     group_sync<BAR, NTHR>();
-    if (sm.cnt[bit] >= k) thresh = cand;
+    int total_c = 0;
+#pragma unroll
+    for (int w = 0; w < NWARP; ++w) total_c += sm.wcnt[bit][w];
+    if (total_c >= k) thresh = cand;
   }
 
   // ---- ordered compaction: keys above thresh, then the lowest-indexed ties
