@@ -274,6 +274,21 @@ int svb200_h2o_normalize_accumulate(float* score, int64_t score_stride, int32_t 
                                     const int32_t* kv_lens, float refill, void* stream);
 
 /*
+ * Dense causal prefill attention of a chunk over its paged row (cached prefix + the chunk, whose K/V rows are
+ * already stored): query m of row b sits at physical position m + prompt_cache_lens[b] and attends to kv
+ * positions <= its own through the slot table; logits q.k * sm_scale, fp32 online softmax, P cast to bf16
+ * before PV.  Replaces context_attention_fwd (kernels/triton/context_flashattention_nopad.py:11-79, 242-302).
+ *   q, out [T][Hq][128] bf16 (token strides q_stride / out_stride), start_loc[b] = first chunk token of row b
+ *   max_chunk_len = longest chunk of the batch (sizes the grid)
+ */
+int svb200_prefill_attn(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
+                        int64_t num_slots, const int32_t* slot_table, int64_t slot_table_stride,
+                        const int32_t* req_rows, const int32_t* start_loc, const int32_t* context_lens,
+                        const int32_t* prompt_cache_lens, void* out, int64_t out_stride, int32_t batch,
+                        int32_t num_q_heads, int32_t num_kv_heads, int32_t max_chunk_len, float sm_scale,
+                        void* stream);
+
+/*
  * Prefill window scoring (H2O; the SnapKV-style candidate range is supported too): for batch row b the
  * queries at physical positions [score_starts[b], score_ends[b]) — the last <= 128 tokens of the prefill
  * chunk — attend causally to the row's kv positions [candidate_start, max(candidate_start, ctx - num_recent));

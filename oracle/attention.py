@@ -140,3 +140,34 @@ def dense_softmax_attention_f64(q, k_cache, v_cache, slot_table, req_indices, se
         p = torch.softmax(s, dim=-1)
         out[b] = torch.einsum("hgn,nhd->hgd", p, v).reshape(hq, d)
     return out
+
+
+def prefill_attention(q, k_cache, v_cache, slot_table, req_indices, start_loc, context_lens, prompt_cache_lens):
+    """Dense causal prefill attention of a chunk over its paged row: ``context_attention_fwd``
+    (kernels/triton/context_flashattention_nopad.py:11-79, 242-302).  Query m of row b sits at physical position
+    m + prompt_cache_len and attends to kv positions <= its own through the slot table; logits q.k * D^-0.5,
+    softmax in fp32, numerators cast to V's dtype before PV (line 70), output in q's dtype.  q [T, Hq, D]."""
+    hq, d = int(q.shape[1]), int(q.shape[2])
+    hkv = int(k_cache.shape[1])
+    g = hq // hkv
+    out = torch.zeros_like(q)
+    scale = float(d) ** -0.5
+    for b in range(int(req_indices.numel())):
+        ctx, cache_len = int(context_lens[b]), int(prompt_cache_lens[b])
+        n = ctx - cache_len
+        if n <= 0:
+            continue
+        slots = slot_table[int(req_indices[b]), :ctx].long()
+        k = k_cache[slots].float().repeat_interleave(g, dim=1)      # [ctx, Hq, D]
+        v = v_cache[slots].repeat_interleave(g, dim=1)
+        s0 = int(start_loc[b])
+        qv = q[s0: s0 + n].float()
+        logits = torch.einsum("mhd,nhd->hmn", qv, k) * scale
+        causal = (torch.arange(n)[:, None] + cache_len) >= torch.arange(ctx)[None, :]
+        logits = logits.masked_fill(~causal[None], float("-inf"))
+        m = logits.max(dim=-1, keepdim=True).values
+        p = torch.exp(logits - m)
+        l = p.sum(dim=-1, keepdim=True)
+        o = torch.einsum("hmn,nhd->mhd", p.to(v.dtype).float(), v.float()) / l.permute(1, 0, 2)
+        out[s0: s0 + n] = o.to(q.dtype)
+    return out

@@ -220,8 +220,20 @@ def make_h2o_prefill_inputs(*, seed, hq, hkv, rows, window, num_slots, d=128, **
         off += n
     cache_lens = [c for c, _ in rows]
     starts = [max(c, c + n - window) if window > 0 else c for c, n in rows]
-    return dict(q=q, k_cache=k_cache, slot_table=table, req_indices=req,
+    v_cache = randn_bf16(gen, num_slots, hkv, d)  # drawn last: the scoring cases' digests do not depend on it
+    return dict(q=q, k_cache=k_cache, v_cache=v_cache, slot_table=table, req_indices=req,
                 start_loc=torch.tensor(start_loc, dtype=torch.int32), context_lens=torch.tensor(ctx, dtype=torch.int32),
                 prompt_cache_lens=torch.tensor(cache_lens, dtype=torch.int32),
                 score_starts=torch.tensor(starts, dtype=torch.int32), score_ends=torch.tensor(ctx, dtype=torch.int32),
                 max_query_len=max(e - s_ for s_, e in zip(starts, ctx)), max_context_len=width)
+
+
+def prefill_golden_tokens(inp) -> torch.Tensor:
+    """Chunk tokens (indices into q) whose attention output the prefill goldens keep: the first 4 and the last 12
+    of every row's chunk (both ends of the causal range), to keep the fixtures small."""
+    keep = []
+    chunk = (inp["context_lens"] - inp["prompt_cache_lens"]).tolist()
+    for s0, n in zip(inp["start_loc"].tolist(), chunk):
+        idx = sorted(set(list(range(min(4, n))) + list(range(max(0, n - 12), n))))
+        keep += [s0 + i for i in idx]
+    return torch.tensor(keep, dtype=torch.long)

@@ -241,9 +241,17 @@ def h2o_prefill_case(name, **cfg):
                       inp["context_lens"], inp["prompt_cache_lens"], inp["max_query_len"], inp["slot_table"],
                       inp["score_starts"], inp["score_ends"], candidate_start=0, num_recent_tokens=0,
                       score_mode="probability")
+    # the dense prefill attention of the same chunk (context_attention_fwd, fp32-upcast inputs under the interpreter)
+    from sparsevllm.kernels.triton.context_flashattention_nopad import context_attention_fwd
+    qf = inp["q"].float()
+    o = torch.zeros_like(qf)
+    chunk_lens = inp["context_lens"] - inp["prompt_cache_lens"]
+    context_attention_fwd(qf, inp["k_cache"].float(), inp["v_cache"].float(), o, inp["req_indices"], inp["start_loc"],
+                          inp["context_lens"], inp["prompt_cache_lens"], int(chunk_lens.max()), inp["slot_table"])
     np.savez_compressed(GOLDEN / f"{name}.npz", digest=np.array(cases.digest(inp["q"], inp["k_cache"], inp["slot_table"])),
-                        score=score.numpy())
-    print(f"[h2o prefill] {name}: score {tuple(score.shape)} sums {score.sum(dim=1).tolist()}")
+                        score=score.numpy(), v_digest=np.array(cases.digest(inp["v_cache"])),
+                        attn_out_f16=o[cases.prefill_golden_tokens(inp)].numpy().astype(np.float16))
+    print(f"[h2o prefill] {name}: score {tuple(score.shape)} sums {score.sum(dim=1).tolist()} attn {tuple(o.shape)}")
 
 
 def main():

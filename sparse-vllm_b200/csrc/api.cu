@@ -460,6 +460,31 @@ int svb200_h2o_normalize_accumulate(float* score, int64_t score_stride, int32_t 
                                          cum_stride, cum_rows, kv_lens, refill, (cudaStream_t)stream);
 }
 
+int svb200_prefill_attn(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache, int64_t num_slots,
+                        const int32_t* slot_table, int64_t slot_table_stride, const int32_t* req_rows,
+                        const int32_t* start_loc, const int32_t* context_lens, const int32_t* prompt_cache_lens,
+                        void* out, int64_t out_stride, int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
+                        int32_t max_chunk_len, float sm_scale, void* stream) {
+  const char* who = "prefill_attn";
+  SV_REQUIRE(batch >= 0 && max_chunk_len >= 0, "%s: negative sizes", who);
+  if (batch == 0 || max_chunk_len == 0) return 0;
+  SV_REQUIRE(q && k_cache && v_cache && slot_table && req_rows && start_loc && context_lens && prompt_cache_lens && out,
+             "%s: null pointer", who);
+  SV_REQUIRE(aligned16(q) && aligned16(k_cache) && aligned16(v_cache) && aligned16(out), "%s: q/k/v/out must be 16-byte aligned", who);
+  if (int rc = check_heads(who, num_q_heads, num_kv_heads)) return rc;
+  SV_SUPPORTED(num_q_heads / num_kv_heads <= 8, "%s: GQA group size %d > 8 is not supported", who, num_q_heads / num_kv_heads);
+  SV_REQUIRE(q_stride >= (int64_t)num_q_heads * SVB200_HEAD_DIM && q_stride % 8 == 0 &&
+                 out_stride >= (int64_t)num_q_heads * SVB200_HEAD_DIM && out_stride % 2 == 0,
+             "%s: bad q / out token strides %lld / %lld", who, (long long)q_stride, (long long)out_stride);
+  SV_REQUIRE(num_slots > 0 && slot_table_stride > 0, "%s: num_slots / slot_table_stride must be positive", who);
+  SV_REQUIRE(batch * (int64_t)num_kv_heads <= 65535, "%s: batch * kv heads = %lld exceeds the grid's y extent", who,
+             (long long)batch * num_kv_heads);
+  PrefillAttnHostArgs h{q, q_stride, k_cache, v_cache, num_slots, slot_table, slot_table_stride, req_rows, start_loc,
+                        context_lens, prompt_cache_lens, out, out_stride, batch, num_q_heads, num_kv_heads, max_chunk_len,
+                        sm_scale};
+  return launch_prefill_attn(h, (cudaStream_t)stream);
+}
+
 int svb200_h2o_prefill_score(const void* q, int64_t q_stride, const void* k_cache, int64_t num_slots,
                              const int32_t* slot_table, int64_t slot_table_stride, const int32_t* req_rows,
                              const int32_t* start_loc, const int32_t* context_lens,

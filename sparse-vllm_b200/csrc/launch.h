@@ -151,6 +151,18 @@ struct PrefillScoreHostArgs {
 };
 int launch_h2o_prefill_score(const PrefillScoreHostArgs& h, cudaStream_t stream);
 
+// prefill_attn.cu
+struct PrefillAttnHostArgs {
+  const void* q; int64_t q_stride;
+  const void* k_cache; const void* v_cache; int64_t num_slots;
+  const int32_t* slot_table; int64_t table_stride;
+  const int32_t* req_rows; const int32_t* start_loc; const int32_t* context_lens; const int32_t* prompt_cache_lens;
+  void* out; int64_t out_stride;
+  int batch, hq, hkv, max_chunk_len;
+  float sm_scale;
+};
+int launch_prefill_attn(const PrefillAttnHostArgs& h, cudaStream_t stream);
+
 // collective.cu
 struct AllReduceArgs {
   int world, rank;

@@ -415,6 +415,36 @@ def h2o_normalize_accumulate(score: torch.Tensor, scale: float, cumulative: torc
     return score
 
 
+def prefill_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, slot_table: torch.Tensor,
+                 req_rows: torch.Tensor, start_loc: torch.Tensor, context_lens: torch.Tensor,
+                 prompt_cache_lens: torch.Tensor, *, max_chunk_len: int, out: torch.Tensor | None = None,
+                 sm_scale: float | None = None) -> torch.Tensor:
+    """Dense causal prefill attention of a chunk over its paged row (svb200_prefill_attn)."""
+    require_cuda(q, "q", torch.bfloat16)
+    if q.dim() != 3 or q.shape[2] != HEAD_DIM or q.stride(2) != 1 or q.stride(1) != HEAD_DIM:
+        raise ValueError(f"q must be [T, Hq, {HEAD_DIM}] with contiguous heads, got {tuple(q.shape)}/{q.stride()}.")
+    num_slots, hkv = _kv_layer(k_cache, "k_cache")
+    if _kv_layer(v_cache, "v_cache") != (num_slots, hkv):
+        raise ValueError("k_cache and v_cache must have identical shapes.")
+    for t, n in ((slot_table, "slot_table"), (req_rows, "req_rows"), (start_loc, "start_loc"),
+                 (context_lens, "context_lens"), (prompt_cache_lens, "prompt_cache_lens")):
+        _i32(t, n)
+    if out is None:
+        out = torch.empty_like(q)
+    require_cuda(out, "out", torch.bfloat16)
+    if out.shape != q.shape or out.stride(2) != 1 or out.stride(1) != HEAD_DIM:
+        raise ValueError("out must have q's shape with contiguous heads.")
+    if sm_scale is None:
+        sm_scale = 1.0 / math.sqrt(HEAD_DIM)
+    lib = _native.load()
+    check(lib.svb200_prefill_attn(
+        ptr(q), int(q.stride(0)), ptr(k_cache), ptr(v_cache), num_slots, ptr(slot_table), _rows_stride(slot_table, "slot_table"),
+        ptr(req_rows), ptr(start_loc), ptr(context_lens), ptr(prompt_cache_lens), ptr(out), int(out.stride(0)),
+        int(req_rows.numel()), int(q.shape[1]), hkv, int(max_chunk_len), float(sm_scale),
+        current_stream_ptr(q.device)), "svb200_prefill_attn")
+    return out
+
+
 def h2o_prefill_score(q: torch.Tensor, k_cache: torch.Tensor, slot_table: torch.Tensor, req_rows: torch.Tensor,
                       start_loc: torch.Tensor, context_lens: torch.Tensor, prompt_cache_lens: torch.Tensor,
                       score_starts: torch.Tensor, score_ends: torch.Tensor, score: torch.Tensor, *, max_query_len: int,

@@ -261,3 +261,24 @@ def test_h2o_prefill_score_matches_reference(name, golden):
         want = oh2o.accumulate_prefill(prev[row, :cache_len] if cache_len else None, got[b], new_len=n, weight=weight)
         torch.testing.assert_close(cum[row, :n].cpu(), want, atol=1e-5, rtol=1e-5)
         assert torch.equal(cum[row, n:].cpu(), prev[row, n:]), "cumulative written beyond the row"
+
+
+@pytest.mark.parametrize("name", list(cases.H2O_PREFILL_CASES))
+def test_prefill_attention_matches_reference(name, golden):
+    """svb200_prefill_attn (dense causal chunk attention over the paged row) against the reference's Triton
+    context_attention_fwd (golden) and the oracle on every token."""
+    from sparse_vllm_b200 import ops
+    inp = cases.make_h2o_prefill_inputs(**cases.H2O_PREFILL_CASES[name])
+    g = golden(name)
+    assert str(g["v_digest"]) == cases.digest(inp["v_cache"])
+    dev = {k: v.to(DEV) for k, v in inp.items() if isinstance(v, torch.Tensor)}
+    chunk = inp["context_lens"] - inp["prompt_cache_lens"]
+    out = torch.full_like(dev["q"], float("nan"))
+    ops.prefill_attn(dev["q"], dev["k_cache"], dev["v_cache"], dev["slot_table"], dev["req_indices"], dev["start_loc"],
+                     dev["context_lens"], dev["prompt_cache_lens"], max_chunk_len=int(chunk.max()), out=out)
+    torch.cuda.synchronize()
+    ref = oattn.prefill_attention(inp["q"], inp["k_cache"], inp["v_cache"], inp["slot_table"], inp["req_indices"],
+                                  inp["start_loc"], inp["context_lens"], inp["prompt_cache_lens"])
+    torch.testing.assert_close(out.cpu().float(), ref.float(), atol=ATOL, rtol=RTOL)
+    tok = cases.prefill_golden_tokens(inp)
+    torch.testing.assert_close(out.cpu()[tok].float(), torch.from_numpy(g["attn_out_f16"]).float(), atol=ATOL, rtol=RTOL)
