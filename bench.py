@@ -660,15 +660,36 @@ def run_h2o(args) -> dict:
     torch.cuda.set_device(dev)
     reset_context()
     set_context(False)
+    chunk, window = 4096, 128
     cfg = configs.make_sparse_config(sparse_method="h2o", h2o_decode_budget=budget, h2o_prefill_budget=budget,
-                                     h2o_decode_eviction_interval=interval, h2o_recent_ratio=0.5)
-    mgr = CacheManager.create(cfg, num_layers=L, num_kv_heads=hkv, num_slots=bsz * width + 64, max_rows=bsz, device=dev)
+                                     h2o_decode_eviction_interval=interval, h2o_recent_ratio=0.5,
+                                     h2o_prefill_score_window=window)
+    mgr = CacheManager.create(cfg, num_layers=L, num_kv_heads=hkv, num_slots=bsz * (budget + chunk) + 64, max_rows=bsz,
+                              device=dev, max_prefill_chunk=chunk)
     gen = torch.Generator(device=dev).manual_seed(11)
-    for b in range(bsz):  # what the prefill side hands over: budget tokens per layer + their cumulative scores
-        k = torch.randn(L, budget, hkv, HEAD_DIM, generator=gen, device=dev, dtype=torch.bfloat16)
-        v = torch.randn(L, budget, hkv, HEAD_DIM, generator=gen, device=dev, dtype=torch.bfloat16)
-        mgr.admit_compacted_prompt(b, k, v, torch.rand(L, budget, generator=gen, device=dev))
-    del k, v
+    # ---- the 32K prompt of every row goes through the provider's prefill side (h2o.py:665-894, 1352-1496): chunks of
+    # 4096 tokens are appended to the compressed row of every layer (KV store), the last 128 queries of the chunk score
+    # the row (svb200_h2o_prefill_score, cumulative scores accumulate), rows over the budget are compacted after every
+    # chunk (svb200_h2o_select_compact).  Activations are synthetic per layer, so the dense prefill attention
+    # (svb200_prefill_attn) has no consumer here and is not run.
+    set_context(True)
+    ids_all = list(range(bsz))
+    n_chunks = w["ctx"] // chunk
+    k_src = torch.randn(bsz * chunk, hkv, HEAD_DIM, generator=gen, device=dev, dtype=torch.bfloat16)
+    v_src = torch.randn(bsz * chunk, hkv, HEAD_DIM, generator=gen, device=dev, dtype=torch.bfloat16)
+    q_src = torch.randn(bsz * chunk, hq, HEAD_DIM, generator=gen, device=dev, dtype=torch.bfloat16)
+    t_pre0 = time.perf_counter()
+    for c in range(n_chunks):
+        slots = torch.stack([mgr.allocate_prefill_chunk(b, chunk) for b in ids_all], dim=1).reshape(L, bsz * chunk).contiguous()
+        for layer in range(L):
+            mgr.save_rope_kv_if_needed(layer, k_src, v_src, slots[layer])
+            mgr.collect_prefill_attention_score(layer, q_src, ids_all, [chunk] * bsz)
+        mgr.evict_after_prefill(ids_all, final=c == n_chunks - 1)
+        k_src.mul_(-1.0)  # cheap variation between chunks
+    torch.cuda.synchronize()
+    prefill_s = time.perf_counter() - t_pre0
+    del k_src, v_src, q_src, slots
+    set_context(False)
     backend = B200AttentionBackend(provider=mgr._get_provider(hq))
     seqs = [SimpleNamespace(seq_id=b) for b in range(bsz)]
     ids = torch.zeros(bsz, dtype=torch.int64, device=dev)
@@ -782,6 +803,9 @@ def run_h2o(args) -> dict:
         "config": {"workload": w["name"], "layers": L, "q_heads": hq, "kv_heads": hkv, "batch": bsz,
                    "h2o_decode_budget": budget, "h2o_decode_eviction_interval": interval, "recent_ratio": 0.5,
                    "row_tokens": f"{budget + 1}..{width}", "evictions_timed": n_int,
+                   "prompt": f"{w['ctx']}-token prompt per row admitted through the provider's prefill side: {n_chunks} chunks of "
+                             f"{chunk} tokens x {L} layers (KV store, window scoring of the last {window} queries, compaction "
+                             f"to the budget after every chunk), {prefill_s:.1f} s of setup, not timed",
                    "l2": "inputs larger than L2 (>= 0.55 GB of KV touched per layer, 32 distinct layers)",
                    "timed": ("cuda graph replay of the layer loop" if graph is not None else "eager")
                    + " + per-step host prepare + burst eviction every interval"},

@@ -34,27 +34,10 @@ __device__ __forceinline__ uint4 ldg_stream_16(const void* p) {
   return r;
 }
 
-// ------------------------------------------------------------ cp.async ----
+// ------------------------------------------------------------ shared memory ----
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
-// 16-byte async copy global->shared; src_bytes = 0 zero-fills the destination.
-__device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src, int src_bytes) {
-  asm volatile("cp.async.cg.shared.global.L2::128B [%0], [%1], 16, %2;" ::"r"(dst),
-               "l"(src), "r"(src_bytes)
-               : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() {
-  asm volatile("cp.async.commit_group;" ::: "memory");
-}
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-
-// Arrive on `bar` once every cp.async this thread issued so far has landed (the arrival
-// is part of the barrier's expected count: .noinc).
-__device__ __forceinline__ void cp_async_mbar_arrive(uint64_t* bar);
 
 // ------------------------------------------------ mbarrier + bulk copy ----
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -109,10 +92,6 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
           "r"(dst),
       "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
-}
-
-__device__ __forceinline__ void cp_async_mbar_arrive(uint64_t* bar) {
-  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
 // ------------------------------------------------------- tensor cores ----
