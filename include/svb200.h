@@ -274,6 +274,19 @@ int svb200_h2o_normalize_accumulate(float* score, int64_t score_stride, int32_t 
                                     const int32_t* kv_lens, float refill, void* stream);
 
 /*
+ * Device side of H2OCacheManager.prepare_decode_static (h2o.py:257-476) in one launch: meta = int32
+ * [rows[B], new_lens[B], free_top] (host-packed, one pinned copy).  For every (layer l, batch entry b) the slot
+ * free_stack[l][free_top - B + b] is appended to the layer's slot row (slot_tables[l][row][new_len - 1]) and
+ * written to layer_slot_mapping[l][b]; layer 0 also fills the static step buffers context_lens / req_indices /
+ * slot_mapping / kv_lens / rows_out [B].
+ */
+int svb200_h2o_prepare_decode(const int32_t* meta, const int32_t* free_stack, int64_t free_stride,
+                              int32_t* slot_tables, int64_t layer_stride, int64_t row_stride,
+                              int32_t* layer_slot_mapping, int64_t lsm_stride, int32_t* context_lens,
+                              int32_t* req_indices, int32_t* slot_mapping, int32_t* kv_lens,
+                              int32_t* rows_out, int32_t batch, int32_t num_layers, void* stream);
+
+/*
  * Dense causal prefill attention of a chunk over its paged row (cached prefix + the chunk, whose K/V rows are
  * already stored): query m of row b sits at physical position m + prompt_cache_lens[b] and attends to kv
  * positions <= its own through the slot table; logits q.k * sm_scale, fp32 online softmax, P cast to bf16

@@ -63,6 +63,8 @@ _SIGNATURES = {
     "svb200_ipc_close": (c_int32, [_P]),
     "svb200_h2o_normalize_accumulate": (
         c_int32, [_P, c_int64, c_int32, c_int32, c_float, _P, c_int64, _P, _P, c_float, _P]),
+    "svb200_h2o_prepare_decode": (
+        c_int32, [_P, _P, c_int64, _P, c_int64, c_int64, _P, c_int64, _P, _P, _P, _P, _P, c_int32, c_int32, _P]),
     "svb200_prefill_attn": (
         c_int32, [_P, c_int64, _P, _P, c_int64, _P, c_int64, _P, _P, _P, _P, _P, c_int64, c_int32, c_int32, c_int32,
                   c_int32, c_float, _P]),

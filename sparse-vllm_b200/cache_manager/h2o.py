@@ -66,7 +66,8 @@ class H2OCacheManager(CacheManager):
         self._layer_slot_mapping = torch.zeros((L, R), dtype=torch.int32, device=self.device)
         self._batch = 0
         self._kv_lens_dev = torch.zeros((R,), dtype=torch.int32, device=self.device)
-        self._rows_dev: torch.Tensor | None = None
+        self._prep_host: list[torch.Tensor] | None = None
+        self._prep_dev: torch.Tensor | None = None
         self._rows_dev_i32 = torch.zeros((R,), dtype=torch.int32, device=self.device)
         self._batch_rows: list[int] = []
         # rows that decoded since they were admitted (h2o.py:1498-1516 `_h2o_active_decode_seq_ids`): under slot
@@ -228,20 +229,34 @@ class H2OCacheManager(CacheManager):
         lens = self.row_seq_lens[rows]
         if int(lens.max()) + 1 > self.decode_width:
             raise RuntimeError("row longer than budget + interval: evict_after_decode() was not called.")
-        new = self._pop_slots(bsz)  # [L, B]
-        rows_dev = torch.as_tensor(rows, dtype=torch.int64, device=self.device)
-        lens_dev = torch.as_tensor(lens.astype(np.int64), device=self.device)
-        self.slot_tables[:, rows_dev, lens_dev] = new
-        self._layer_slot_mapping[:, :bsz] = new
+        if self.num_free < bsz:
+            raise RuntimeError(f"Out of H2O KV slots: need={bsz}, free={self.num_free}.")
+        # host -> device: one pinned copy of [rows, new lens, free top], one launch that pops the slots of every
+        # layer, appends them to the slot rows and fills the static step buffers (the reference issues ~10 indexing
+        # ops and copies here, h2o.py:257-476)
+        if self._prep_host is None:  # two pinned staging buffers: a buffer is rewritten only after its copy completed
+            on_gpu = self.device.type == "cuda"
+            mk = lambda: torch.empty(2 * self.max_rows + 1, dtype=torch.int32)
+            self._prep_host = [mk().pin_memory() if on_gpu else mk() for _ in range(2)]
+            self._prep_done = [torch.cuda.Event() if on_gpu else None for _ in range(2)]
+            self._prep_dev = torch.empty(2 * self.max_rows + 1, dtype=torch.int32, device=self.device)
+            self._prep_turn = 0
+        turn = self._prep_turn
+        self._prep_turn ^= 1
+        if self._prep_done[turn] is not None:
+            self._prep_done[turn].synchronize()
+        host = self._prep_host[turn].numpy()
+        host[:bsz] = rows
+        host[bsz: 2 * bsz] = lens + 1
+        host[2 * bsz] = self.num_free
+        self._prep_dev[: 2 * bsz + 1].copy_(self._prep_host[turn][: 2 * bsz + 1], non_blocking=True)
+        if self._prep_done[turn] is not None:
+            self._prep_done[turn].record()
+        ops.h2o_prepare_decode(self._prep_dev, self.free_stack, self.slot_tables, self._layer_slot_mapping,
+                               context_lens, req_indices, slot_mapping, self._kv_lens_dev, self._rows_dev_i32, bsz)
+        self.num_free -= bsz
         self._batch = bsz
         self.row_seq_lens[rows] = lens + 1
-        ctx = torch.as_tensor((lens + 1).astype(np.int32), device=self.device)
-        context_lens[:bsz] = ctx
-        req_indices[:bsz] = rows_dev.to(torch.int32)
-        slot_mapping[:bsz] = new[0]
-        self._kv_lens_dev[:bsz] = ctx
-        self._rows_dev = rows_dev
-        self._rows_dev_i32[:bsz] = rows_dev.to(torch.int32)
         self._batch_rows = rows
         self.layer_batch_state.slot_mapping = slot_mapping[:bsz]
         self.layer_batch_state.context_lens = context_lens[:bsz]

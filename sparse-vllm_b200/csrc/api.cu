@@ -460,6 +460,21 @@ int svb200_h2o_normalize_accumulate(float* score, int64_t score_stride, int32_t 
                                          cum_stride, cum_rows, kv_lens, refill, (cudaStream_t)stream);
 }
 
+int svb200_h2o_prepare_decode(const int32_t* meta, const int32_t* free_stack, int64_t free_stride,
+                              int32_t* slot_tables, int64_t layer_stride, int64_t row_stride,
+                              int32_t* layer_slot_mapping, int64_t lsm_stride, int32_t* context_lens,
+                              int32_t* req_indices, int32_t* slot_mapping, int32_t* kv_lens, int32_t* rows_out,
+                              int32_t batch, int32_t num_layers, void* stream) {
+  SV_REQUIRE(batch >= 0 && num_layers >= 0, "h2o_prepare_decode: negative batch / layers");
+  if (batch == 0 || num_layers == 0) return 0;
+  SV_REQUIRE(meta && free_stack && slot_tables && layer_slot_mapping && context_lens && req_indices && slot_mapping &&
+                 kv_lens && rows_out, "h2o_prepare_decode: null pointer");
+  SV_REQUIRE(free_stride > 0 && layer_stride > 0 && row_stride > 0 && lsm_stride >= batch, "h2o_prepare_decode: bad strides");
+  return launch_h2o_prepare_decode(meta, free_stack, free_stride, slot_tables, layer_stride, row_stride, layer_slot_mapping,
+                                   lsm_stride, context_lens, req_indices, slot_mapping, kv_lens, rows_out, batch, num_layers,
+                                   (cudaStream_t)stream);
+}
+
 int svb200_prefill_attn(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache, int64_t num_slots,
                         const int32_t* slot_table, int64_t slot_table_stride, const int32_t* req_rows,
                         const int32_t* start_loc, const int32_t* context_lens, const int32_t* prompt_cache_lens,

@@ -468,6 +468,47 @@ int launch_h2o_prefill_score(const PrefillScoreHostArgs& h, cudaStream_t stream)
   return check_launch("h2o_prefill_score");
 }
 
+// =========================================================================
+// Host -> device hand-over of one H2O decode step (H2OCacheManager.prepare_decode_static, h2o.py:257-476):
+// meta = [rows[B], new_lens[B], free_top] packed by the host (one pinned copy); thread (l, b) pops the b-th of
+// the B topmost free slots of layer l, appends it to the layer's slot row and fills the static step buffers.
+// =========================================================================
+__global__ void __launch_bounds__(256) h2o_prepare_decode_kernel(
+    const int32_t* __restrict__ meta, const int32_t* __restrict__ free_stack, int64_t free_stride,
+    int32_t* __restrict__ slot_tables, int64_t layer_stride, int64_t row_stride,
+    int32_t* __restrict__ layer_slot_mapping, int64_t lsm_stride, int32_t* __restrict__ context_lens,
+    int32_t* __restrict__ req_indices, int32_t* __restrict__ slot_mapping, int32_t* __restrict__ kv_lens,
+    int32_t* __restrict__ rows_out, int batch, int layers) {
+  pdl_wait();
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= batch * layers) return;
+  const int l = idx / batch, b = idx - l * batch;
+  const int row = meta[b], len = meta[batch + b], free_top = meta[2 * batch];
+  const int32_t slot = free_stack[(int64_t)l * free_stride + free_top - batch + b];
+  slot_tables[(int64_t)l * layer_stride + (int64_t)row * row_stride + (len - 1)] = slot;
+  layer_slot_mapping[(int64_t)l * lsm_stride + b] = slot;
+  if (l == 0) {
+    context_lens[b] = len;
+    req_indices[b] = row;
+    slot_mapping[b] = slot;
+    kv_lens[b] = len;
+    rows_out[b] = row;
+  }
+}
+
+int launch_h2o_prepare_decode(const int32_t* meta, const int32_t* free_stack, int64_t free_stride, int32_t* slot_tables,
+                              int64_t layer_stride, int64_t row_stride, int32_t* layer_slot_mapping, int64_t lsm_stride,
+                              int32_t* context_lens, int32_t* req_indices, int32_t* slot_mapping, int32_t* kv_lens,
+                              int32_t* rows_out, int batch, int layers, cudaStream_t stream) {
+  if (batch <= 0 || layers <= 0) return 0;
+  const int n = batch * layers;
+  const cudaError_t e = launch_kernel(h2o_prepare_decode_kernel, dim3((n + 255) / 256), dim3(256), 0, stream, meta,
+                                      free_stack, free_stride, slot_tables, layer_stride, row_stride, layer_slot_mapping,
+                                      lsm_stride, context_lens, req_indices, slot_mapping, kv_lens, rows_out, batch, layers);
+  if (e != cudaSuccess) return cuda_error("h2o_prepare_decode launch", e);
+  return check_launch("h2o_prepare_decode");
+}
+
 int launch_h2o_normalize_accumulate(float* score, int64_t score_stride, int batch, int width,
                                     float scale, float* cumulative, int64_t cum_stride,
                                     const int32_t* cum_rows, const int32_t* kv_lens, float refill,

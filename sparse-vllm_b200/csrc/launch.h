@@ -138,6 +138,10 @@ int launch_h2o_select_compact(float* cumulative, const int64_t* cum_rows, int32_
                               const int64_t* free_rows, int32_t* keep_out, int num_rows,
                               const int32_t* kv_lens, int kv_len, int budget, int recent, cudaStream_t stream);
 
+int launch_h2o_prepare_decode(const int32_t* meta, const int32_t* free_stack, int64_t free_stride, int32_t* slot_tables,
+                              int64_t layer_stride, int64_t row_stride, int32_t* layer_slot_mapping, int64_t lsm_stride,
+                              int32_t* context_lens, int32_t* req_indices, int32_t* slot_mapping, int32_t* kv_lens,
+                              int32_t* rows_out, int batch, int layers, cudaStream_t stream);
 struct PrefillScoreHostArgs {
   const void* q; int64_t q_stride;
   const void* k_cache; int64_t num_slots;

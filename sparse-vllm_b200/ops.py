@@ -415,6 +415,26 @@ def h2o_normalize_accumulate(score: torch.Tensor, scale: float, cumulative: torc
     return score
 
 
+def h2o_prepare_decode(meta: torch.Tensor, free_stack: torch.Tensor, slot_tables: torch.Tensor,
+                       layer_slot_mapping: torch.Tensor, context_lens: torch.Tensor, req_indices: torch.Tensor,
+                       slot_mapping: torch.Tensor, kv_lens: torch.Tensor, rows_out: torch.Tensor, batch: int) -> None:
+    """One launch for the device side of an H2O decode step's preparation (svb200_h2o_prepare_decode)."""
+    for t, n in ((meta, "meta"), (free_stack, "free_stack"), (slot_tables, "slot_tables"),
+                 (layer_slot_mapping, "layer_slot_mapping"), (context_lens, "context_lens"), (req_indices, "req_indices"),
+                 (slot_mapping, "slot_mapping"), (kv_lens, "kv_lens"), (rows_out, "rows_out")):
+        _i32(t, n)
+    if slot_tables.dim() != 3 or free_stack.dim() != 2 or layer_slot_mapping.dim() != 2 or meta.numel() < 2 * batch + 1:
+        raise ValueError("h2o_prepare_decode: slot_tables [L, rows, W], free_stack [L, slots], layer_slot_mapping [L, rows], "
+                         "meta [2B+1] expected.")
+    layers = int(slot_tables.shape[0])
+    lib = _native.load()
+    check(lib.svb200_h2o_prepare_decode(
+        ptr(meta), ptr(free_stack), int(free_stack.stride(0)), ptr(slot_tables), int(slot_tables.stride(0)),
+        int(slot_tables.stride(1)), ptr(layer_slot_mapping), int(layer_slot_mapping.stride(0)), ptr(context_lens),
+        ptr(req_indices), ptr(slot_mapping), ptr(kv_lens), ptr(rows_out), int(batch), layers,
+        current_stream_ptr(slot_tables.device)), "svb200_h2o_prepare_decode")
+
+
 def prefill_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, slot_table: torch.Tensor,
                  req_rows: torch.Tensor, start_loc: torch.Tensor, context_lens: torch.Tensor,
                  prompt_cache_lens: torch.Tensor, *, max_chunk_len: int, out: torch.Tensor | None = None,
