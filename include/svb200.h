@@ -53,7 +53,8 @@ int svb200_set_max_ctas(int32_t n);
  * Score kernel: 0 = row groups of the scheduler, 2 = chunks per claim at least, 3 = divisor of the guided
  * claim size, 4 = units per claimed chunk, 6 = 1: stage q once / 2: stage q+ and q-.
  * Attention kernel: 1 = KB of K/V a CTA should stream at least (grid sizing of small launches; default 256),
- * 8 = 2: one bulk copy per token row even where a granule of rows is contiguous.
+ * 8 = 2: one bulk copy per token row even where a granule of rows is contiguous, 9 = KV heads staged together by
+ * a CTA when the caller passes heads_per_cta = 0 (1, 2, 4, 8; default: the largest of 4, 2, 1 that divides Hkv).
  * Both: 5 = 1 (score) / 2 (attention): stream the bytes but skip the tensor-core contractions (results
  * are garbage; measures what the copy pipeline alone sustains), 7 = programmatic dependent launch
  * (1 = on, 2 = off): a launch may start while its predecessor in the stream drains.

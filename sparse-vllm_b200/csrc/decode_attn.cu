@@ -51,7 +51,7 @@ template <int HPC>
 struct AttnGeom {
   static constexpr int TL = kConsumerWarps / HPC;    // consumer warps per KV head
   static constexpr int TOK_BYTES = HPC * kRowBytes;   // one token's head-group row
-  static constexpr int GRAN = HPC == 1 ? 4 : (HPC == 2 ? 2 : 1);  // token rows per copy granule (>= 1 KB)
+  static constexpr int GRAN = HPC == 1 ? 4 : 2;  // token rows per copy granule (1 KB at one or two heads, 2-4 KB above)
   static constexpr int GSTRIDE = GRAN * TOK_BYTES + 16;  // +16: granules (ldmatrix rows) hit distinct banks
   static constexpr int KV_BYTES = (kPage / GRAN) * GSTRIDE;  // one tensor of one stage
   static constexpr int STAGE_BYTES = 2 * KV_BYTES;    // K then V
@@ -726,7 +726,10 @@ static int launch_hpc(const AttnParams& p, cudaStream_t stream) {
 }
 
 int attn_auto_heads_per_cta(int hkv) {
-  for (int c = 4; c > 1; c >>= 1)  // 4 heads = 1 KB token rows and six ring stages; 8 would leave three
+  // 4 heads = 1 KB token rows and six ring stages.  8 heads (knob 9 = 1): three stages of 64 KB, but with all of a
+  // rank's heads staged together the rows of a page are contiguous and a copy moves a granule of them.
+  if (tuning(kTuneAttnHpc) > 0 && hkv % tuning(kTuneAttnHpc) == 0) return tuning(kTuneAttnHpc);
+  for (int c = 4; c > 1; c >>= 1)
     if (hkv % c == 0) return c;
   return 1;
 }

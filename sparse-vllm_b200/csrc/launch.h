@@ -17,7 +17,7 @@ int max_ctas();  // persistent-grid size: sm_count() unless svb200_set_max_ctas 
 // experiment knobs (svb200_set_tuning); 0 = automatic
 enum {
   kTuneScoreGroups = 0, kTuneAttnMinKB = 1, kTuneMinBatch = 2, kTuneShareDiv = 3, kTuneChunkUnits = 4,
-  kTuneNoMath = 5, kTuneScoreQ = 6, kTunePdl = 7, kTuneAttnGranule = 8, kTuneCount = 16
+  kTuneNoMath = 5, kTuneScoreQ = 6, kTunePdl = 7, kTuneAttnGranule = 8, kTuneAttnHpc = 9, kTuneCount = 16
 };
 int tuning(int which);
 bool pdl_enabled();  // launches carry the programmatic-stream-serialization attribute

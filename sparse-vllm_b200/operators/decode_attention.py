@@ -75,14 +75,12 @@ class B200SparseDecodeProvider:
         return self._sm_count
 
     def heads_per_cta(self, num_kv_heads: int) -> int:
-        """KV heads staged together by one CTA: up to 4 that divide the local head count (a token's K row is
-        then HPC*256 contiguous bytes, 1 KB at 4; 8 heads would leave only three ring stages).  Load balance
-        does not depend on it: the kernel cuts the launch's 16-token pages into one equal range per SM
-        (stream-K), whatever the batch and row lengths are."""
-        for hpc in (4, 2):
-            if num_kv_heads % hpc == 0:
-                return hpc
-        return 1
+        """KV heads staged together by one CTA: 0 = the library's choice (up to 4 that divide the local head count: a
+        token's K row is then HPC*256 contiguous bytes; experiment knob 9 overrides it).  Load balance does not depend
+        on it: the kernel cuts the launch's 16-token pages into one equal range per SM (stream-K), whatever the batch
+        and row lengths are."""
+        del num_kv_heads
+        return 0
 
     def workspace(self, batch: int, num_q_heads: int, num_kv_heads: int, device) -> torch.Tensor:
         """Zeroed tickets + per-SM partial records (replaces the reference's mid_o / mid_o_logexpsum)."""

@@ -463,11 +463,23 @@ def test_baseline_shapes_against_reference(name, golden):
                              ref_scores, ulp_slack=1)
     _record_parity(name, int(n_valid.sum()), exact, ulp1, worse, stats)
     # attention at this size on the reference's own selection
-    out = torch.empty_like(q)
-    ops.sparse_decode_attn(q, kc, vc, torch.from_numpy(g["packed_slots"]).to(DEV), torch.from_numpy(g["req_out"]).to(DEV),
-                           torch.from_numpy(g["lens"]).to(DEV), out=out, workspace=ops.attn_workspace(bsz, q.shape[1], hkv, DEV))
-    torch.cuda.synchronize()
-    torch.testing.assert_close(out.cpu().float(), torch.from_numpy(g["attn_out_f32"]), atol=2e-2, rtol=1e-2)
+    # (every head-group size that divides Hkv: a Quest page is 16 consecutive slots, so with all local heads staged
+    # together the producers copy granules of token rows; knob 8 = 2 forces one copy per token row)
+    for hpc in (0, 1, 2, 4, 8):
+        if hpc and hkv % hpc:
+            continue
+        for granule in (0, 2):
+            ops.set_tuning(8, granule)
+            try:
+                out = torch.full_like(q, float("nan"))
+                ops.sparse_decode_attn(q, kc, vc, torch.from_numpy(g["packed_slots"]).to(DEV),
+                                       torch.from_numpy(g["req_out"]).to(DEV), torch.from_numpy(g["lens"]).to(DEV), out=out,
+                                       workspace=ops.attn_workspace(bsz, q.shape[1], hkv, DEV), heads_per_cta=hpc)
+                torch.cuda.synchronize()
+            finally:
+                ops.set_tuning(8, 0)
+            torch.testing.assert_close(out.cpu().float(), torch.from_numpy(g["attn_out_f32"]), atol=2e-2, rtol=1e-2,
+                                       msg=lambda m: f"{name} hpc={hpc} granule knob={granule}: {m}")
 
 
 def test_parity_report(golden):
