@@ -595,6 +595,13 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
           store_kv_token(p.store, tok, hkv, stid, kScoreSelectThreads);
       for (int b = blockIdx.x; b < B; b += gridDim.x) {
         const int need = units_of_row(b);
+        // while the row is being scored: pull its page-table row into L2, so that the look-ups of the selected
+        // pages at the very end of the launch do not pay a DRAM round trip
+        {
+          const char* pt_bytes = reinterpret_cast<const char*>(p.page_table + (int64_t)sReq[b] * p.pt_stride);
+          for (int off = stid * 128; off < (sNv[b] + 1) * 4; off += kScoreSelectThreads * 128)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(pt_bytes + off));
+        }
         if (need > 0 && stid == 0) {
           const volatile int* ctr = units_done + b;
           uint32_t spins = 0;
