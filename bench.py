@@ -439,6 +439,7 @@ def run_b200(args) -> dict:
 
     # ---- (1) device-resident throughput: inputs already in HBM, CUDA-graph replay of one step
     step.prepare()
+    barrier()  # ranks reach their first collective launch together
     stream = torch.cuda.Stream()
     graph = None
     with torch.cuda.stream(stream):

@@ -43,8 +43,8 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sum_bf16_kernel(AllReduc
   if (peer < a.world && peer != a.rank) {
     uint32_t spins = 0;
     while (ld_acquire_sys(local + peer) - e < 0) {
-      __nanosleep(32);
-      if (++spins > kSpinLimit) __trap();
+      __nanosleep(64);
+      if (++spins > kPeerSpinLimit) __trap();
     }
   }
   __syncthreads();

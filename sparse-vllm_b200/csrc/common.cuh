@@ -76,6 +76,9 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
   return t;
 }
 constexpr uint32_t kSpinLimit = 1u << 26;
+// Waiting for ANOTHER GPU (tensor-parallel flags) is bounded much more loosely: ranks may reach their first
+// collective seconds apart (about two minutes of 64 ns naps before the trap).
+constexpr uint32_t kPeerSpinLimit = 1u << 31;
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   uint32_t spins = 0;

@@ -95,8 +95,8 @@ __device__ void push_finish(const PushArgs& ps) {
     if (r == ps.rank) continue;
     uint32_t spins = 0;
     while (ld_acquire_sys(local + r) - e < 0) {
-      __nanosleep(32);
-      if (++spins > kSpinLimit) __trap();
+      __nanosleep(64);
+      if (++spins > kPeerSpinLimit) __trap();
     }
   }
 }
