@@ -109,11 +109,11 @@ def test_h2o_ragged_rows_evict_on_their_own_trigger(tight):
     once (the pressure branch, 1510-1522), including a row that was not scheduled in the step.  Cumulative
     scores follow the oracle step by step; the step-score rows come back pre-filled for the next step."""
     from sparse_vllm_b200.attention_backend import B200AttentionBackend, decode_attention_layer
-    hq, hkv, budget, interval, layers = 8, 2, 64, 16, 2
+    hq, hkv, budget, interval, layers = 8, 2, 48, 16, 2
     width = budget + interval
-    prompt = {0: 40, 1: 64, 2: 57, 3: 64}
+    prompt = {0: 30, 1: 48, 2: 41, 3: 48}
     # tight: exactly enough slots that the stack runs dry before any row reaches budget + interval
-    slots = (40 + 57 + 64) + 3 * 9 if tight else 4 * width + 8
+    slots = (30 + 41 + 48) + 3 * 9 if tight else 4 * width + 8
     mgr = _make(budget, interval, layers, hkv, 4, slots=slots + 64)
     gen = torch.Generator().manual_seed(17)
     for sid, n in prompt.items():
