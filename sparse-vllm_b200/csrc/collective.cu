@@ -41,10 +41,10 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sum_bf16_kernel(AllReduc
   // this rank's input was written by earlier work on the stream: announce it, then wait for everybody's
   if (blockIdx.x == 0 && peer < a.world && peer != a.rank) st_release_sys(a.sync[peer] + a.rank, e);
   if (peer < a.world && peer != a.rank) {
-    uint32_t spins = 0;
+    SpinGuard guard;
     while (ld_acquire_sys(local + peer) - e < 0) {
       __nanosleep(64);
-      if (++spins > kPeerSpinLimit) __trap();
+      guard.tick(kPeerSpinLimitNs);
     }
   }
   __syncthreads();

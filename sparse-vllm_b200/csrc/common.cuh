@@ -66,25 +66,33 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug traps instead of hanging the GPU.  The bound counts failed polls (each
-// try_wait suspends the thread for a hardware time slice), not wall time: %globaltimer keeps running while
-// a context is preempted, time-sliced or stopped under a debugger / profiler replay, and a correct launch
-// must survive that.
+// Bounded waits: a protocol bug traps instead of hanging the GPU.  The bound needs BOTH many failed polls and
+// wall time: %globaltimer keeps running while a context is preempted, time-sliced or stopped under a debugger /
+// profiler replay, and a correct launch must survive that (it stops polling while it is switched out); a poll
+// count alone would depend on how long one try_wait suspends the thread.
 __device__ __forceinline__ uint64_t global_timer_ns() {
   uint64_t t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-constexpr uint32_t kSpinLimit = 1u << 26;
-// Waiting for ANOTHER GPU (tensor-parallel flags) is bounded much more loosely: ranks may reach their first
-// collective seconds apart (about two minutes of 64 ns naps before the trap).
-constexpr uint32_t kPeerSpinLimit = 1u << 31;
+struct SpinGuard {
+  uint32_t spins = 0;
+  uint64_t t0 = 0;
+  // call once per failed poll; traps after >= 2^20 further failed polls spread over more than `limit_ns`
+  __device__ __forceinline__ void tick(uint64_t limit_ns) {
+    if ((++spins & 0xfffffu) == 0) {
+      const uint64_t now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > limit_ns) __trap();
+    }
+  }
+};
+constexpr uint64_t kSpinLimitNs = 10ull * 1000000000ull;       // waits inside one GPU
+constexpr uint64_t kPeerSpinLimitNs = 120ull * 1000000000ull;  // waits for ANOTHER GPU: ranks may arrive seconds apart
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
-  uint32_t spins = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if (++spins > kSpinLimit) __trap();
-  }
+  SpinGuard guard;
+  while (!mbar_try_wait(bar, parity)) guard.tick(kSpinLimitNs);
 }
 // 1-D bulk async copy global -> shared::cta, completion counted on an mbarrier.
 // dst/src 16-byte aligned, bytes a multiple of 16.  SASS: UBLKCP.

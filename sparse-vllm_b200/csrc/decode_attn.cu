@@ -93,10 +93,10 @@ __device__ void push_finish(const PushArgs& ps) {
     if (r != ps.rank) st_release_sys(ps.sync[r] + ps.rank, e);
   for (int r = 0; r < ps.world; ++r) {
     if (r == ps.rank) continue;
-    uint32_t spins = 0;
+    SpinGuard guard;
     while (ld_acquire_sys(local + r) - e < 0) {
       __nanosleep(64);
-      if (++spins > kPeerSpinLimit) __trap();
+      guard.tick(kPeerSpinLimitNs);
     }
   }
 }

@@ -604,10 +604,10 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
         }
         if (need > 0 && stid == 0) {
           const volatile int* ctr = units_done + b;
-          uint32_t spins = 0;
+          SpinGuard guard;
           while (*ctr < need) {
             __nanosleep(64);
-            if (++spins > kSpinLimit) __trap();
+            guard.tick(kSpinLimitNs);
           }
         }
         group_sync<2, kScoreSelectThreads>();
