@@ -287,7 +287,10 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
       if constexpr (G::GRAN > 1) {
         bool contig = gran_ok && my >= 0;
 #pragma unroll
-        for (int x = 1; x < G::GRAN; ++x) contig = contig && (__shfl_down_sync(0xffffffffu, my, x) == my + x);
+        for (int x = 1; x < G::GRAN; ++x) {
+          const int next = __shfl_down_sync(0xffffffffu, my, x);  // every lane takes part (no short-circuit around it)
+          contig = contig && next == my + x;
+        }
         const bool leader = (tok_lane % G::GRAN) == 0;
         const uint32_t gm = __ballot_sync(0xffffffffu, leader && contig);
         lead_bulk = leader && contig;
