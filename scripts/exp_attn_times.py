@@ -1,11 +1,13 @@
 """Experiment: per-CTA timeline of the attention kernel (svb200_debug_times)."""
+import os
 import sys
 import torch
 sys.path.insert(0, ".")
 import svb200_import  # noqa
 from sparse_vllm_b200 import ops, _native
 dev = "cuda:0"
-B, hq, hkv, sel_pages = 32, 28, 4, 256
+B, hq, hkv = (int(x) for x in os.environ.get('SHAPE', '32,28,4').split(','))
+sel_pages = 256
 num_pages = 1 << 16
 k = torch.randn(num_pages * 16, hkv, 128, device=dev, dtype=torch.bfloat16)
 v = torch.randn(num_pages * 16, hkv, 128, device=dev, dtype=torch.bfloat16)
@@ -63,4 +65,5 @@ print("corr by CTA  first/same:", float(torch.corrcoef(torch.stack([dur, durs['s
 print("corr by SM   same/other:", float(torch.corrcoef(torch.stack([durs['same'][1], durs['other'][1]]))[0, 1]),
       " same/same2:", float(torch.corrcoef(torch.stack([durs['same'][1], durs['same2'][1]]))[0, 1]))
 pd = (t[:, 4] - t[:, 0]).float() / 1000.0
-print("producer0 done - by CTA index (first 148):", [round(float(x), 1) for x in pd.tolist()])
+if os.environ.get("VERBOSE"):
+    print("producer0 done - by CTA index (first 148):", [round(float(x), 1) for x in pd.tolist()])
