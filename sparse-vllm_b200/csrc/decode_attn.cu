@@ -102,11 +102,11 @@ __device__ void push_finish(const PushArgs& ps) {
 }
 
 struct AttnSmemLayout {
-  int ring_off, valid_off, bar_off, q_off, merge_off, prefix_off, total;
+  int ring_off, valid_off, bar_off, q_off, merge_off, prefix_off, entry_off, total;
 };
 
 template <int HPC, int NT>
-__host__ __device__ inline AttnSmemLayout attn_smem_layout(int stages, int gsz, int rows) {
+__host__ __device__ inline AttnSmemLayout attn_smem_layout(int stages, int gsz, int rows, int batch) {
   using G = AttnGeom<HPC>;
   AttnSmemLayout L;
   int off = 0;
@@ -116,6 +116,7 @@ __host__ __device__ inline AttnSmemLayout attn_smem_layout(int stages, int gsz, 
   L.bar_off = off;    off += 2 * stages * 8;
   L.valid_off = off;  off += ((stages * 4 + 15) / 16) * 16;
   L.prefix_off = off; off += ((rows + 1) * 4 + 15) / 16 * 16;
+  L.entry_off = off;  off += (2 * batch * 4 + 15) / 16 * 16;  // clamped length, table row of each batch entry
   L.total = off;
   return L;
 }
@@ -130,7 +131,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
   const int HG = p.hkv / HPC;
   const int R = p.batch * HG;
   const int S = p.stages;
-  const AttnSmemLayout L = attn_smem_layout<HPC, NT>(S, gsz, R);
+  const AttnSmemLayout L = attn_smem_layout<HPC, NT>(S, gsz, R, p.batch);
   unsigned char* ring = smem + L.ring_off;
   __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(smem + L.q_off);
   float* sMerge = reinterpret_cast<float*>(smem + L.merge_off);
@@ -138,7 +139,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
   uint64_t* empty_bar = full_bar + S;
   uint32_t* sValid = reinterpret_cast<uint32_t*>(smem + L.valid_off);
   int* sPrefix = reinterpret_cast<int*>(smem + L.prefix_off);
-  __shared__ int s_flag;
+  int* sLen = reinterpret_cast<int*>(smem + L.entry_off);  // min(seq_len, max_len) of batch entry b
+  int* sTab = sLen + p.batch;                              // its row of the slot table
+  __shared__ int s_flag, s_defer;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   unsigned long long* dbg = p.dbg_times ? p.dbg_times + (size_t)blockIdx.x * 8 : nullptr;
@@ -156,10 +159,18 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
       mbar_init(&full_bar[s], 1);  // the producer's expect_tx arrival; the copies' bytes complete the phase
       mbar_init(&empty_bar[s], HPC);
     }
+    s_defer = 0;
     mbar_fence_init();
   }
   pdl_wait();
   const bool push = p.push.world > 1;
+  // the producers' first slot fetch then only depends on shared memory (one DRAM round trip less before the
+  // first copy is issued)
+  if (warp >= 1 && warp < kConsumerWarps)
+    for (int b = tid - 32; b < p.batch; b += kConsumerThreads - 32) {
+      sLen[b] = min(p.seq_lens[b], p.max_len);
+      sTab[b] = p.req_rows[b];
+    }
   if (warp == 0) {
     int carry = 0;
     for (int base = 0; base < R; base += 32) {
@@ -239,8 +250,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
     // prefetch cursor: row / batch entry of the unit whose slots are fetched next; the row's
     // length and table row are reloaded only when the cursor moves to another batch entry
     int r_pf = r_first, b_pf = r_first / HG, hg_pf = r_first % HG;
-    int len_pf = min(p.seq_lens[b_pf], p.max_len);
-    const int32_t* row_pf = p.slot_table + (int64_t)p.req_rows[b_pf] * p.slot_table_stride;
+    int len_pf = sLen[b_pf];
+    const int32_t* row_pf = p.slot_table + (int64_t)sTab[b_pf] * p.slot_table_stride;
     auto fetch = [&](int i) -> int {  // raw slot of token tok_lane in local unit i
       if (i >= n_units) return -1;
       const int u = u0 + i;
@@ -250,8 +261,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
         if (++hg_pf == HG) hg_pf = 0, ++b_pf, moved = true;
       }
       if (moved) {
-        len_pf = min(p.seq_lens[b_pf], p.max_len);
-        row_pf = p.slot_table + (int64_t)p.req_rows[b_pf] * p.slot_table_stride;
+        len_pf = sLen[b_pf];
+        row_pf = p.slot_table + (int64_t)sTab[b_pf] * p.slot_table_stride;
       }
       const int t = (u - sPrefix[r_pf]) * kPage + tok_lane;
       if (t >= len_pf) return -1;
@@ -331,6 +342,87 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
   const float scale_log2 = p.sm_scale * kLog2e;
   const int heads_row = HPC * gsz;
 
+  // Merge of a row that several CTAs contributed to (run by all consumer warps of the CTA whose arrival
+  // completed the row's ticket).
+  auto merge_row = [&](int mr) {
+    const int row_begin = sPrefix[mr], row_end = sPrefix[mr + 1];
+    const int b = mr / HG, hg = mr - b * HG;
+    const int c_first = unit_owner(row_begin, U, Gn), c_last = unit_owner(row_end - 1, U, Gn);
+    const unsigned long long t_cmb = dbg ? global_timer_ns() : 0;
+    // One warp per q head, lane = 4 output dims.  Lane c first fetches the lse of contributor
+    // c (all contributors in parallel), then the partial outputs are read with independent
+    // loads: the merge costs a couple of L2 round trips, not one per contributor.
+    __threadfence();
+    const int nc = c_last - c_first + 1;
+    constexpr int HB = 4;  // heads a warp merges at once: their loads are all independent
+    for (int h0 = warp * HB; h0 < heads_row; h0 += kConsumerWarps * HB) {
+      float m[HB], wsum[HB];
+      float4 acc[HB];
+#pragma unroll
+      for (int x = 0; x < HB; ++x) m[x] = -INFINITY, wsum[x] = 0.f, acc[x] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int c0 = 0; c0 < nc; c0 += 32) {
+        const int c = c_first + c0 + lane;
+        int ps = 0;
+        float lse[HB], wgt[HB];
+        if (c <= c_last) ps = 2 * c + ((int)(U * c / Gn) >= row_begin ? 0 : 1);
+#pragma unroll
+        for (int x = 0; x < HB; ++x)
+          lse[x] = (c <= c_last && h0 + x < heads_row)
+                       ? __ldcg(p.ws_lse + (int64_t)ps * heads_row + h0 + x)
+                       : -INFINITY;
+#pragma unroll
+        for (int x = 0; x < HB; ++x) {
+          float cm = lse[x];
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+          const float mnew = fmaxf(m[x], cm);
+          const float rescale = m[x] == -INFINITY ? 0.f : __expf(m[x] - mnew);
+          acc[x].x *= rescale, acc[x].y *= rescale, acc[x].z *= rescale, acc[x].w *= rescale;
+          wsum[x] *= rescale;
+          wgt[x] = lse[x] == -INFINITY ? 0.f : __expf(lse[x] - mnew);
+          m[x] = mnew;
+        }
+        const int cnt = min(32, nc - c0);
+#pragma unroll 4
+        for (int kc2 = 0; kc2 < cnt; ++kc2) {
+          const int psk = __shfl_sync(0xffffffffu, ps, kc2);
+          const float4* src = reinterpret_cast<const float4*>(
+                                  p.ws_o + ((int64_t)psk * heads_row + h0) * kHeadDim) + lane;
+#pragma unroll
+          for (int x = 0; x < HB; ++x) {
+            const float wk = __shfl_sync(0xffffffffu, wgt[x], kc2);
+            if (wk != 0.f) {
+              const float4 v = __ldcg(src + x * (kHeadDim / 4));
+              acc[x].x += wk * v.x, acc[x].y += wk * v.y, acc[x].z += wk * v.z, acc[x].w += wk * v.w;
+              wsum[x] += wk;
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int x = 0; x < HB; ++x) {
+        if (h0 + x < heads_row) {
+          const float inv = wsum[x] > 0.f ? 1.f / wsum[x] : 0.f;
+          uint2 o2;
+          o2.x = pack_bf16x2(acc[x].x * inv, acc[x].y * inv);
+          o2.y = pack_bf16x2(acc[x].z * inv, acc[x].w * inv);
+          __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
+                                (int64_t)b * p.out_stride_b +
+                                (int64_t)(hg * heads_row + h0 + x) * kHeadDim;
+          *reinterpret_cast<uint2*>(orow + lane * 4) = o2;
+          if (push) {
+            const int64_t off = (int64_t)b * p.push.stride_b +
+                                ((int64_t)p.push.rank * p.hq + hg * heads_row + h0 + x) * kHeadDim + lane * 4;
+            for (int r = 0; r < p.push.world; ++r) *reinterpret_cast<uint2*>(p.push.out[r] + off) = o2;
+          }
+        }
+      }
+    }
+    if (push) __threadfence_system();
+    if (dbg && tid == 0) dbg[5] += global_timer_ns() - t_cmb;
+  };
+
+  int defer_row = -1, defer_total = 0, defer_old = -1;
   int r = r_first;
   int i = 0;  // index of the next unit inside this CTA's range
   while (u0 + i < u1) {
@@ -577,94 +669,47 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
       }
     }
     if (!complete) {
-      // arrival ticket: the last contributor of the row merges every partial
+      // Arrival ticket of the row, counted in KV-head warps (HPC per contributing CTA): whoever completes it merges
+      // every partial.  A segment that is not the CTA's last one (the tail of a row that began in another CTA)
+      // arrives early and is practically never the last: its warps fire their arrival and go on with the next
+      // row at once; the returned count is only looked at when the CTA is done (defer_*).  The CTA's last segment
+      // arrives as a whole and merges right away if it completes the row.
       const int c_first = unit_owner(row_begin, U, Gn), c_last = unit_owner(row_end - 1, U, Gn);
-      __threadfence();
-      consumer_sync();
-      if (tid == 0) {
-        const int ticket = atomicAdd(&p.tickets[r], 1);
-        s_flag = (ticket == c_last - c_first);
-        if (s_flag) p.tickets[r] = 0;  // scratch stays zeroed for the next launch / replay
-      }
-      consumer_sync();
-      const unsigned long long t_cmb = dbg ? global_timer_ns() : 0;
-      if (s_flag) {
-        // One warp per q head, lane = 4 output dims.  Lane c first fetches the lse of contributor
-        // c (all contributors in parallel), then the partial outputs are read with independent
-        // loads: the merge costs a couple of L2 round trips, not one per contributor.
-        __threadfence();
-        const int nc = c_last - c_first + 1;
-        constexpr int HB = 4;  // heads a warp merges at once: their loads are all independent
-        for (int h0 = warp * HB; h0 < heads_row; h0 += kConsumerWarps * HB) {
-          float m[HB], wsum[HB];
-          float4 acc[HB];
-#pragma unroll
-          for (int x = 0; x < HB; ++x) m[x] = -INFINITY, wsum[x] = 0.f, acc[x] = make_float4(0.f, 0.f, 0.f, 0.f);
-          for (int c0 = 0; c0 < nc; c0 += 32) {
-            const int c = c_first + c0 + lane;
-            int ps = 0;
-            float lse[HB], wgt[HB];
-            if (c <= c_last) ps = 2 * c + ((int)(U * c / Gn) >= row_begin ? 0 : 1);
-#pragma unroll
-            for (int x = 0; x < HB; ++x)
-              lse[x] = (c <= c_last && h0 + x < heads_row)
-                           ? __ldcg(p.ws_lse + (int64_t)ps * heads_row + h0 + x)
-                           : -INFINITY;
-#pragma unroll
-            for (int x = 0; x < HB; ++x) {
-              float cm = lse[x];
-#pragma unroll
-              for (int o = 16; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
-              const float mnew = fmaxf(m[x], cm);
-              const float rescale = m[x] == -INFINITY ? 0.f : __expf(m[x] - mnew);
-              acc[x].x *= rescale, acc[x].y *= rescale, acc[x].z *= rescale, acc[x].w *= rescale;
-              wsum[x] *= rescale;
-              wgt[x] = lse[x] == -INFINITY ? 0.f : __expf(lse[x] - mnew);
-              m[x] = mnew;
-            }
-            const int cnt = min(32, nc - c0);
-#pragma unroll 4
-            for (int kc2 = 0; kc2 < cnt; ++kc2) {
-              const int psk = __shfl_sync(0xffffffffu, ps, kc2);
-              const float4* src = reinterpret_cast<const float4*>(
-                                      p.ws_o + ((int64_t)psk * heads_row + h0) * kHeadDim) + lane;
-#pragma unroll
-              for (int x = 0; x < HB; ++x) {
-                const float wk = __shfl_sync(0xffffffffu, wgt[x], kc2);
-                if (wk != 0.f) {
-                  const float4 v = __ldcg(src + x * (kHeadDim / 4));
-                  acc[x].x += wk * v.x, acc[x].y += wk * v.y, acc[x].z += wk * v.z, acc[x].w += wk * v.w;
-                  wsum[x] += wk;
-                }
-              }
-            }
-          }
-#pragma unroll
-          for (int x = 0; x < HB; ++x) {
-            if (h0 + x < heads_row) {
-              const float inv = wsum[x] > 0.f ? 1.f / wsum[x] : 0.f;
-              uint2 o2;
-              o2.x = pack_bf16x2(acc[x].x * inv, acc[x].y * inv);
-              o2.y = pack_bf16x2(acc[x].z * inv, acc[x].w * inv);
-              __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
-                                    (int64_t)b * p.out_stride_b +
-                                    (int64_t)(hg * heads_row + h0 + x) * kHeadDim;
-              *reinterpret_cast<uint2*>(orow + lane * 4) = o2;
-              if (push) {
-                const int64_t off = (int64_t)b * p.push.stride_b +
-                                    ((int64_t)p.push.rank * p.hq + hg * heads_row + h0 + x) * kHeadDim + lane * 4;
-                for (int r = 0; r < p.push.world; ++r) *reinterpret_cast<uint2*>(p.push.out[r] + off) = o2;
-              }
-            }
-          }
+      const int arrivals = (c_last - c_first + 1) * HPC;
+      if (seg_end != u1) {
+        if (tl == 0) {
+          __threadfence();
+          __syncwarp();
+          if (lane == 0) defer_old = atomicAdd(&p.tickets[r], 1);
         }
-        if (push) __threadfence_system();
-        if (dbg && tid == 0) dbg[5] += global_timer_ns() - t_cmb;
+        defer_row = r;
+        defer_total = arrivals;
+      } else {
+        __threadfence();
+        consumer_sync();
+        if (tid == 0) {
+          const int ticket = atomicAdd(&p.tickets[r], HPC);
+          s_flag = (ticket + HPC == arrivals);
+          if (s_flag) p.tickets[r] = 0;  // scratch stays zeroed for the next launch / replay
+        }
+        consumer_sync();
+        if (s_flag) merge_row(r);
       }
     }
     consumer_sync();  // sQ / sMerge / s_flag are reused by the next segment
     if (dbg && tid == 0) dbg[6] += global_timer_ns() - t_epi;
     i += n;
+  }
+  if (defer_row >= 0) {
+    if (tl == 0 && lane == 0 && defer_old == defer_total - 1) {
+      s_defer = 1;
+      p.tickets[defer_row] = 0;
+    }
+    consumer_sync();
+    if (s_defer) {
+      merge_row(defer_row);
+      consumer_sync();
+    }
   }
   if (dbg && tid == 0) dbg[3] = global_timer_ns();
   if (push && tid == 0) push_finish(p.push);  // the loop's last consumer_sync ordered the CTA's peer stores before this
@@ -676,7 +721,7 @@ static int launch_variant(const AttnParams& p_in, cudaStream_t stream) {
   AttnParams p = p_in;
   const int gsz = p.hq / p.hkv;
   const int rows = p.batch * (p.hkv / HPC);
-  const int fixed = attn_smem_layout<HPC, NT>(0, gsz, rows).total + 256;  // + static smem
+  const int fixed = attn_smem_layout<HPC, NT>(0, gsz, rows, p.batch).total + 256;  // + static smem
   int stages = (kMaxSmem - fixed) / (G::STAGE_BYTES + 20);
   if (stages > 24) stages = 24;
   // Unit j is consumed by the warps tl = j % TL; with TL | stages a stage is always drained by the
@@ -693,7 +738,7 @@ static int launch_variant(const AttnParams& p_in, cudaStream_t stream) {
   p.producers = 1;
   for (int d = kProducerWarps; d >= 1; --d)
     if (stages % d == 0) { p.producers = d; break; }
-  const size_t smem = attn_smem_layout<HPC, NT>(stages, gsz, rows).total;
+  const size_t smem = attn_smem_layout<HPC, NT>(stages, gsz, rows, p.batch).total;
   auto kern = sparse_decode_attn_kernel<HPC, NT, WITH_SCORE>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return cuda_error("sparse_decode_attn smem attr", e);

@@ -517,7 +517,7 @@ int launch_h2o_normalize_accumulate(float* score, int64_t score_stride, int batc
   const size_t smem = (size_t)width * sizeof(float);
   if (smem <= 96 * 1024) {
     auto kern = h2o_normalize_accumulate_kernel<true>;
-    if (smem > 48 * 1024) {
+    if (smem > 32 * 1024) {  // static + dynamic shared memory share the 48 KB default limit
       cudaError_t e =
           cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return cuda_error("h2o_normalize smem attr", e);
@@ -541,7 +541,7 @@ int launch_h2o_select_compact(float* cumulative, const int64_t* cum_rows, int32_
   if (num_rows <= 0) return 0;
   const size_t smem = (size_t)kv_len * 12;
   auto kern = h2o_select_compact_kernel;
-  if (smem > 48 * 1024) {
+  if (smem > 32 * 1024) {  // static + dynamic shared memory share the 48 KB default limit
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return cuda_error("h2o_select_compact smem attr", e);
   }

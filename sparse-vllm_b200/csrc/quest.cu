@@ -217,33 +217,59 @@ __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, 
   constexpr int NWARP = NTHR / 32;
   group_sync<BAR, NTHR>();  // sm.wcnt may still be read by a previous call
   uint32_t thresh = 0;
-  for (int bit = 15; bit >= 0; --bit) {
-    const uint32_t cand = thresh | (1u << bit), cand_hi = cand << 16;
-    int c = 0;
-    if constexpr (CACHED) {
-      int ca[4] = {0, 0, 0, 0};  // independent chains: the adds would otherwise serialise
-#pragma unroll
-      for (int vv = 0; vv < VPT; ++vv)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          ca[i] += (kw[vv][i] >= cand_hi) ? 1 : 0;
-          ca[(i + 2) & 3] += ((kw[vv][i] & 0xffffu) >= cand) ? 1 : 0;
-        }
-      c = (ca[0] + ca[1]) + (ca[2] + ca[3]);
-    } else {
-      for_each_word([&](int, uint32_t w) {
-        c += (w >= cand_hi) ? 1 : 0;
-        c += ((w & 0xffffu) >= cand) ? 1 : 0;
-      });
-    }
-    // one slot per (round, warp): no atomics, no reset; every thread sums the warps' counts after the barrier
+  // total of a per-thread count over the group: one slot per (round, warp), no atomics, no reset
+  auto group_total = [&](int bit, int c) {
     c = __reduce_add_sync(0xffffffffu, c);
     if (lane == 0) sm.wcnt[bit][tid >> 5] = c;
     group_sync<BAR, NTHR>();
     int total_c = 0;
 #pragma unroll
     for (int w = 0; w < NWARP; ++w) total_c += sm.wcnt[bit][w];
-    if (total_c >= k) thresh = cand;
+    return total_c;
+  };
+  if constexpr (CACHED) {
+    // Round 15 settles the top bit; the keys then shrink to 15 bits (keys the top bit already decided
+    // become 0 = never counted, or 0x7fff = always counted), which lets one VIADDMNMX.S16x2.RELU
+    // (max(min(key - cand + 1, 1), 0) per 16-bit half, no overflow with 15-bit operands) compare two
+    // keys per instruction: the 16 counting rounds are bound by their barrier, not by the ALU.
+    uint32_t acc = 0;
+#pragma unroll
+    for (int vv = 0; vv < VPT; ++vv)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc += (kw[vv][i] >> 15) & 0x00010001u;
+    const bool top = group_total(15, (int)((acc & 0xffffu) + (acc >> 16))) >= k;
+    uint32_t sub[VPT][4];
+#pragma unroll
+    for (int vv = 0; vv < VPT; ++vv)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t m = ((kw[vv][i] >> 15) & 0x00010001u) * 0x7fffu;
+        sub[vv][i] = top ? (kw[vv][i] & m) : ((kw[vv][i] | m) & 0x7fff7fffu);
+      }
+    uint32_t t15 = 0;
+    for (int bit = 14; bit >= 0; --bit) {
+      const uint32_t cand = t15 | (1u << bit);
+      const uint32_t addend = ((1u - cand) & 0xffffu) * 0x00010001u;
+      uint32_t a0 = 0, a1 = 0;
+#pragma unroll
+      for (int vv = 0; vv < VPT; ++vv) {
+        a0 += __viaddmin_s16x2_relu(sub[vv][0], addend, 0x00010001u) + __viaddmin_s16x2_relu(sub[vv][1], addend, 0x00010001u);
+        a1 += __viaddmin_s16x2_relu(sub[vv][2], addend, 0x00010001u) + __viaddmin_s16x2_relu(sub[vv][3], addend, 0x00010001u);
+      }
+      a0 += a1;
+      if (group_total(bit, (int)((a0 & 0xffffu) + (a0 >> 16))) >= k) t15 = cand;
+    }
+    thresh = (top ? 0x8000u : 0u) | t15;
+  } else {
+    for (int bit = 15; bit >= 0; --bit) {
+      const uint32_t cand = thresh | (1u << bit), cand_hi = cand << 16;
+      int c = 0;
+      for_each_word([&](int, uint32_t w) {
+        c += (w >= cand_hi) ? 1 : 0;
+        c += ((w & 0xffffu) >= cand) ? 1 : 0;
+      });
+      if (group_total(bit, c) >= k) thresh = cand;
+    }
   }
 
   // ---- ordered compaction: keys above thresh, then the lowest-indexed ties
@@ -361,7 +387,8 @@ constexpr int kScoreConsumerWarps = 6;
 constexpr int kScoreConsumerThreads = kScoreConsumerWarps * 32;
 constexpr int kScoreLoaderWarp = kScoreConsumerWarps;      // one loader warp ...
 constexpr int kScoreSchedWarp = kScoreConsumerWarps + 1;   // ... and one scheduler warp
-constexpr int kIdDepth = 2;             // descriptors whose chunk ids are in flight ahead of the copies
+constexpr int kIdDepth = 4;             // descriptors whose chunk ids are in flight ahead of the copies (the table read
+                                        // is an L2 hit at best: ~1 us under load, i.e. 40 KB of streaming per SM)
 constexpr int kScoreSelectWarps = 8;    // dedicated top-k warps: the stream never waits for a selection
 constexpr int kScoreSelectThreads = kScoreSelectWarps * 32;
 constexpr int kScoreThreads = kScoreConsumerThreads + 2 * 32 + kScoreSelectThreads;
@@ -581,6 +608,19 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
 
   if (warp > kScoreSchedWarp) {
     // ============================================================== select warps
+    // First, while the stream starts: pull the unit table of every row into L2 (each 128-byte line by one thread
+    // of the launch).  The loaders read it a few descriptors ahead of their copies; from DRAM that look-ahead
+    // was too short for small units (one KV head per rank: 8 KB per unit, 2.3 units/us per SM).
+    {
+      const int gtid = blockIdx.x * kScoreSelectThreads + (tid - (kScoreThreads - kScoreSelectThreads));
+      const int gthreads = gridDim.x * kScoreSelectThreads;
+      for (int b = 0; b < B; ++b) {
+        const int lines = (units_of_row(b) * 4 + 127) >> 7;
+        const char* row = reinterpret_cast<const char*>(p.unit_table + (int64_t)sReq[b] * p.ut_stride);
+        for (int l = (gtid + b * 61) % gthreads; l < lines; l += gthreads)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(row + (int64_t)l * 128));
+      }
+    }
     // CTA c selects rows c, c + gridDim, ...: it waits until the row's counter shows every unit
     // scored (the consumers of all CTAs add what they scored when they leave a row), then runs the
     // top-k and packing.  The stream (loader / consumers) never waits for a selection.
@@ -888,7 +928,14 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
     if (mb < kMinBatch) mb = kMinBatch;
     p.min_batch = tuning(kTuneMinBatch) > 0 ? tuning(kTuneMinBatch) : mb;
   }
-  p.share_div = tuning(kTuneShareDiv) > 0 ? tuning(kTuneShareDiv) : 4;
+  // Static first piece = 1/share_div of a CTA's fair share of its home row.  A launch that gives a CTA less than
+  // ~1 MB (TP shards, short batches) is over before guided claims could rebalance anything (what a CTA holds in
+  // its ring and descriptor queue is most of its share): cut it statically, claims only move the remainder.
+  {
+    const int64_t per_cta = (int64_t)p.batch * units_row * stage_bytes * p.hsplit / grid;
+    const int auto_div = per_cta < (1 << 20) ? 1 : (per_cta < (2 << 20) ? 2 : 4);
+    p.share_div = tuning(kTuneShareDiv) > 0 ? tuning(kTuneShareDiv) : auto_div;
+  }
   p.no_math = tuning(kTuneNoMath) == 1;
   const size_t smem = score_smem_layout(p.stages, p.hq, p.hkv, p.hsplit, p.batch, FUSED, qsplit ? 2 : 1).total;
   const int64_t max_chunks = (int64_t)p.batch * ((units_row + p.chunk_units - 1) / p.chunk_units);

@@ -21,7 +21,7 @@
 namespace svb200 {
 
 constexpr int kMaxChunkUnits = 8;  // units per claimed chunk at most (a producer lane looks up one unit's chunk id)
-constexpr int kSchedQueue = 16;  // descriptor slots (sched_run's `depth` <= kSchedQueue bounds what is actually posted ahead)
+constexpr int kSchedQueue = 32;  // descriptor slots (sched_run's `depth` <= kSchedQueue bounds what is actually posted ahead)
 constexpr int kMinBatch = 2;     // chunks per claim at least (an atomicAdd costs 3-4 us under load; one more is in flight)
 
 struct ChunkDesc {
