@@ -29,6 +29,8 @@ for it in range(4):
     torch.cuda.synchronize()
 lib.svb200_debug_times(None)
 t = buf.view(148, 8).cpu()
+t = t[t[:, 0] > 0]  # CTAs of the launch (small launches use fewer than 148)
+print("CTAs:", t.shape[0])
 t0 = int(t[:, 0].min())
 rel = (t[:, :5] - t0).float() / 1000.0
 print("cols: entry, setup done, first data, consumers done, producer0 done (us, relative to first CTA entry)")
@@ -56,6 +58,7 @@ for name, tb in (("same", table), ("other", table2), ("same2", table)):
     torch.cuda.synchronize()
     lib.svb200_debug_times(None)
     tt = buf.view(148, 8).cpu()
+    tt = tt[tt[:, 0] > 0]
     d = (tt[:, 3] - tt[:, 0]).float() / 1000.0
     bysm = torch.zeros(148)
     bysm[tt[:, 7].long()] = d

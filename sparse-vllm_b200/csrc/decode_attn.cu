@@ -276,12 +276,18 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
     uint32_t ph = (pw / S) & 1;  // phase parity of stage s at unit i
     // slots are fetched kSlotPrefetch units of this warp ahead: the table comes from DRAM and one
     // unit's copies are issued in far less than a DRAM round trip
+    // pf is a circular FIFO indexed at compile time (the unit loop is unrolled kSlotPrefetch times) and a slot is
+    // refilled only after its value was used: a register that waits for its table load is never copied, so the
+    // load's latency is paid kSlotPrefetch units later and not at a register move right after the load.
     int pf[kSlotPrefetch];
 #pragma unroll
     for (int d = 0; d < kSlotPrefetch; ++d) pf[d] = fetch(pw + d * NP);
-    for (int i = pw; i < n_units; i += NP) {
-      const int slot_new = fetch(i + kSlotPrefetch * NP);
-      const int slot_a = pf[0];
+    for (int i0 = pw; i0 < n_units; i0 += NP * kSlotPrefetch) {
+#pragma unroll
+     for (int d = 0; d < kSlotPrefetch; ++d) {
+      const int i = i0 + d * NP;
+      if (i >= n_units) break;
+      const int slot_a = pf[d];
       const int my = (slot_a >= 0 && slot_a < p.num_slots) ? slot_a : -1;
       const uint32_t mask = __ballot_sync(0xffffffffu, my >= 0) & 0xffffu;
       while (sPrefix[r_is + 1] <= u0 + i) {
@@ -326,11 +332,10 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
         bulk_g2s(dst, base + (int64_t)my * slot_bytes, (uint32_t)(G::GRAN * G::TOK_BYTES), &full_bar[s]);
       else if (my >= 0 && !covered)
         bulk_g2s(dst, base + (int64_t)my * slot_bytes, (uint32_t)G::TOK_BYTES, &full_bar[s]);
-#pragma unroll
-      for (int d = 0; d + 1 < kSlotPrefetch; ++d) pf[d] = pf[d + 1];
-      pf[kSlotPrefetch - 1] = slot_new;
+      pf[d] = fetch(i + kSlotPrefetch * NP);
       s += NP;
       while (s >= S) s -= S, ph ^= 1;
+     }
     }
     if (dbg && pw == 0 && lane == 0) dbg[4] = global_timer_ns();
     return;

@@ -560,8 +560,12 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
     for (int t = 0; t < kIdDepth; ++t) fetch(dq[t], idq[t]);
     const char* bounds_bytes = reinterpret_cast<const char*>(p.bounds);
     // dq / idq form a circular FIFO indexed at compile time (the loop body is unrolled kIdDepth
-    // times): a register that waits for its table load is never moved, so the load's latency is
-    // only paid when the id is finally used, kIdDepth descriptors later.
+    // times) and a slot is refilled only AFTER its id was used: the register that waits for a table
+    // load is then never copied or renamed, so the load's latency is only paid when the id is finally
+    // used, kIdDepth descriptors later.  (Refilling the slot before the use made the compiler keep the
+    // old value and move the new one into place at the loop's back edge: a wait for the load that was
+    // issued last, i.e. one full table-read latency per descriptor, which capped launches with small
+    // units (<= 16 KB, TP shards) at ~2.3 units/us per SM whatever their size.)
     bool done = false;
     while (!done) {
 #pragma unroll
@@ -569,37 +573,40 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
         if (done) break;
         const ChunkDesc cur = dq[u];
         const int ids = idq[u];
-        fetch(dq[u], idq[u]);
         if (cur.row < 0) {
           done = true;
           break;
         }
-        const int nv = sNv[cur.row];
-        for (int j = 0; j < cur.units(); ++j) {
-          const int c = __shfl_sync(0xffffffffu, ids, j);
+        // Lane j feeds unit j of the descriptor (its own table entry, its own stages; a descriptor never holds
+        // more units than the ring has room for, so the lanes' stages are distinct): the instructions of a feed
+        // -- stage arithmetic, barrier poll, tag, expect_tx, copy -- are paid once per descriptor, not once per
+        // unit.  One lane feeding unit after unit took ~0.4 us per unit, which capped launches with 8-16 KB
+        // units (1-2 KV heads per rank) at 2.3 units/us per SM whatever their size.
+        if (lane < cur.units()) {
+          const int c = ids;
           const bool have = c >= 0 && c < p.num_chunks;
-          const int cnt = nv - (cur.unit_begin + j) * kPage;  // valid pages of the unit (> 0)
+          const int cnt = sNv[cur.row] - (cur.unit_begin + lane) * kPage;  // valid pages of the unit (> 0)
           const uint32_t umask = have ? (cnt >= kPage ? 0xffffu : ((1u << max(cnt, 0)) - 1u)) : 0u;
           for (int part = 0; part < hs; ++part) {
-            const int ii = (cur.unit_base + j) * hs + part;
+            const int ii = (cur.unit_base + lane) * hs + part;
             const int s = ii % S;
             const uint32_t round = (uint32_t)(ii / S);
             const unsigned long long te = dbg ? global_timer_ns() : 0;
             mbar_wait(&empty_bar[s], (round & 1u) ^ 1u);
             if (dbg) w_empty += global_timer_ns() - te;
-            if (lane == 0) {
-              // valid pages of the unit | the stage's fill count (the consumer checks it: see there)
-              sValid[s] = umask | ((round & 0x7fffu) << 16);
-              if (have) {
-                mbar_arrive_expect_tx(&full_bar[s], part_bytes);
-                bulk_g2s(smem_u32(ring + s * stage_bytes),
-                         bounds_bytes + ((int64_t)c * hs + part) * (int64_t)part_bytes, part_bytes, &full_bar[s]);
-              } else {
-                mbar_arrive(&full_bar[s]);
-              }
+            // valid pages of the unit | the stage's fill count (the consumer checks it: see there)
+            sValid[s] = umask | ((round & 0x7fffu) << 16);
+            if (have) {
+              mbar_arrive_expect_tx(&full_bar[s], part_bytes);
+              bulk_g2s(smem_u32(ring + s * stage_bytes),
+                       bounds_bytes + ((int64_t)c * hs + part) * (int64_t)part_bytes, part_bytes, &full_bar[s]);
+            } else {
+              mbar_arrive(&full_bar[s]);
             }
           }
         }
+        __syncwarp();
+        fetch(dq[u], idq[u]);
       }
     }
     if (dbg && lane == 0) dbg[4] = global_timer_ns(), dbg[8] = w_desc, dbg[9] = w_empty;
@@ -921,7 +928,13 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
     const int64_t per_cta = (int64_t)p.batch * units_row * unit_bytes / grid;
     int64_t claim = per_cta / 8;
     claim = claim < 32 * 1024 ? 32 * 1024 : (claim > 128 * 1024 ? 128 * 1024 : claim);
-    int cu = tuning(kTuneChunkUnits) > 0 ? tuning(kTuneChunkUnits) : (int)(claim / 2 / unit_bytes);
+    // a chunk (= one descriptor, fed by the loader's lanes in parallel) carries >= 48 KB when units are small
+    int64_t chunk_target = claim / 2;
+    if (chunk_target < 48 * 1024) chunk_target = 48 * 1024;
+    int cu = tuning(kTuneChunkUnits) > 0 ? tuning(kTuneChunkUnits) : (int)((chunk_target + unit_bytes - 1) / unit_bytes);
+    if (unit_bytes >= 32 * 1024 && tuning(kTuneChunkUnits) <= 0) cu = (int)(claim / 2 / unit_bytes);
+    const int ring_units = p.stages / p.hsplit;  // the units of one descriptor occupy distinct ring stages
+    if (cu > ring_units) cu = ring_units;
     p.chunk_units = cu < 1 ? 1 : (cu > kMaxChunkUnits ? kMaxChunkUnits : cu);
     const int64_t chunk_bytes = p.chunk_units * unit_bytes;
     int mb = (int)((claim + chunk_bytes - 1) / chunk_bytes);
