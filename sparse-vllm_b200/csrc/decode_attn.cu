@@ -9,11 +9,17 @@
 // Decomposition (stream-K over token pages instead of the reference's fixed
 // BLOCK_SEQ grid): a "row" is (batch entry b, head group hg of HPC KV heads); a
 // "unit" is one 16-token page of a row.  All units of the launch form one
-// sequence that is cut into gridDim.x equal contiguous ranges, one per persistent
-// CTA, so every SM moves the same number of bytes whatever the batch and the
-// per-row lengths are.  A CTA whose range covers a whole row writes bf16 output
-// directly; otherwise it publishes one fp32 partial (at most two per CTA) and
-// the last contributor of the row (arrival ticket) merges them.
+// sequence that is cut into gridDim.x contiguous ranges, one per persistent CTA,
+// whatever the batch and the per-row lengths are.  The ranges are equal in COST,
+// not in units: a CTA whose range holds a row boundary pays a second epilogue, a
+// q reload, a pipeline bubble and -- arriving last for that reason -- the row's
+// merge (~10 us at cfg5, where they were the launch's tail), so the cut is made
+// in a virtual sequence with `split_pen` padding units at every row boundary:
+// such a CTA streams split_pen units less, and a cut point that falls into the
+// padding becomes a cut exactly at the row boundary (no split at all).  A CTA
+// whose range covers a whole row writes bf16 output directly; otherwise it
+// publishes one fp32 partial (at most two per CTA) and whoever completes the
+// row's arrival ticket merges them.
 //
 // Inside a CTA: warps 8-11 are producers.  A producer reads 16 token slots (prefetched kSlotPrefetch
 // units ahead) and issues bulk async copies (cp.async.bulk, SASS UBLKCP) into a ring of S stages whose
@@ -71,10 +77,35 @@ __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
-// CTA that owns unit u when U units are cut into G ranges [U*c/G, U*(c+1)/G).
+// CTA that owns (virtual) unit u when U units are cut into G ranges [U*c/G, U*(c+1)/G).
 __device__ __forceinline__ int unit_owner(int64_t u, int64_t U, int64_t G) {
   return (int)(((u + 1) * G + U - 1) / U - 1);
 }
+// The cut.  Row r's units sit at virtual positions [prefix[r] + pen*r, prefix[r+1] + pen*r), followed by pen
+// padding positions (none after the last row).  to_unit: virtual position -> unit (padding maps to the next
+// row's first unit).
+struct AttnCut {
+  const int* prefix;  // exclusive prefix of the rows' unit counts, R + 1 entries
+  int R, pen;
+  int64_t U, UV, G;   // units, virtual length, ranges
+  __device__ __forceinline__ int64_t vbegin(int r) const { return prefix[r] + (int64_t)pen * r; }
+  __device__ __forceinline__ int row_of_virtual(int64_t v) const {  // largest r with vbegin(r) <= v
+    int lo = 0, hi = R;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (vbegin(mid) <= v) lo = mid; else hi = mid;
+    }
+    return lo;
+  }
+  __device__ __forceinline__ int to_unit(int64_t v) const {
+    const int r = row_of_virtual(v);
+    return prefix[r] + (int)min(v - vbegin(r), (int64_t)(prefix[r + 1] - prefix[r]));
+  }
+  __device__ __forceinline__ int begin_of(int c) const { return to_unit(UV * c / G); }  // first unit of CTA c
+  __device__ __forceinline__ int owner(int u, int r) const {  // CTA that owns unit u of row r
+    return unit_owner(u + (int64_t)pen * r, UV, G);
+  }
+};
 
 // ---- tensor-parallel push epilogue (see the file header)
 // Called by ONE thread per CTA (every CTA of the grid, exactly once) after the CTA's peer stores were
@@ -212,14 +243,20 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
 
   if (dbg && tid == 0) dbg[1] = global_timer_ns();
   const int64_t U = sPrefix[R];
-  // never more ranges than units: every range is non-empty, so the contributors of a
-  // row are exactly the CTAs unit_owner(first unit) .. unit_owner(last unit)
+  // never more ranges than units.  The contributors of a row are the CTAs owner(first unit) .. owner(last unit):
+  // every CTA between them has units of the row (the padding is at most half a range long, so no range of
+  // theirs is empty).
   const int64_t Gn = U < (int64_t)gridDim.x ? U : (int64_t)gridDim.x;
-  if ((int64_t)blockIdx.x >= Gn) {
+  AttnCut cut;
+  cut.prefix = sPrefix, cut.R = R, cut.U = U, cut.G = Gn;
+  cut.pen = Gn > 0 ? (int)min((int64_t)p.split_pen, U / Gn / 2) : 0;
+  cut.UV = U + (int64_t)cut.pen * (R - 1);
+  const int u0 = (int64_t)blockIdx.x < Gn ? cut.begin_of(blockIdx.x) : 0;
+  const int u1 = (int64_t)blockIdx.x < Gn ? ((int64_t)blockIdx.x + 1 == Gn ? (int)U : cut.begin_of(blockIdx.x + 1)) : 0;
+  if (u0 >= u1) {
     if (push && tid == 0) push_finish(p.push);
     return;
   }
-  const int u0 = (int)(U * blockIdx.x / Gn), u1 = (int)(U * (blockIdx.x + 1) / Gn);
   // first row of the range: largest r with prefix[r] <= u0 and a non-empty row
   int r_first;
   {
@@ -352,7 +389,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
   auto merge_row = [&](int mr) {
     const int row_begin = sPrefix[mr], row_end = sPrefix[mr + 1];
     const int b = mr / HG, hg = mr - b * HG;
-    const int c_first = unit_owner(row_begin, U, Gn), c_last = unit_owner(row_end - 1, U, Gn);
+    const int c_first = cut.owner(row_begin, mr), c_last = cut.owner(row_end - 1, mr);
     const unsigned long long t_cmb = dbg ? global_timer_ns() : 0;
     // One warp per q head, lane = 4 output dims.  Lane c first fetches the lse of contributor
     // c (all contributors in parallel), then the partial outputs are read with independent
@@ -369,7 +406,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
         const int c = c_first + c0 + lane;
         int ps = 0;
         float lse[HB], wgt[HB];
-        if (c <= c_last) ps = 2 * c + ((int)(U * c / Gn) >= row_begin ? 0 : 1);
+        if (c <= c_last) ps = 2 * c + (cut.begin_of(c) >= row_begin ? 0 : 1);
 #pragma unroll
         for (int x = 0; x < HB; ++x)
           lse[x] = (c <= c_last && h0 + x < heads_row)
@@ -679,7 +716,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
       // arrives early and is practically never the last: its warps fire their arrival and go on with the next
       // row at once; the returned count is only looked at when the CTA is done (defer_*).  The CTA's last segment
       // arrives as a whole and merges right away if it completes the row.
-      const int c_first = unit_owner(row_begin, U, Gn), c_last = unit_owner(row_end - 1, U, Gn);
+      const int c_first = cut.owner(row_begin, r), c_last = cut.owner(row_end - 1, r);
       const int arrivals = (c_last - c_first + 1) * HPC;
       if (seg_end != u1) {
         if (tl == 0) {
@@ -754,9 +791,9 @@ static int launch_variant(const AttnParams& p_in, cudaStream_t stream) {
   // Small launches (one short row: cfg2) are latency-bound: every CTA pays the same start-up and the
   // last contributor of a row merges one partial per CTA, so a CTA should stream >= ~256 KB of K/V
   // (bs 1, 2064 tokens, 8 KV heads: 148 CTAs 36 us, 32 CTAs 17 us).  max_len bounds the work from above.
+  const int64_t unit_kb = (int64_t)HPC * 2 * kPage * kHeadDim * 2 / 1024;  // K + V rows of HPC heads, 16 tokens
   {
     int kb = tuning(kTuneAttnMinKB) > 0 ? tuning(kTuneAttnMinKB) : 256;
-    const int64_t unit_kb = (int64_t)HPC * 2 * kPage * kHeadDim * 2 / 1024;  // K + V rows of HPC heads, 16 tokens
     const int64_t min_units = (kb + unit_kb - 1) / unit_kb;
     const int64_t want = (max_units + min_units - 1) / min_units;
     if ((int64_t)grid > want) grid = (int)want;
@@ -764,6 +801,9 @@ static int launch_variant(const AttnParams& p_in, cudaStream_t stream) {
   if (grid < 1) grid = 1;
   p.no_math = tuning(kTuneNoMath) == 2;
   p.granule = tuning(kTuneAttnGranule) != 2;
+  // ~6 us of streaming at ~44 GB/s per SM, in units (the kernel caps it at half a range)
+  p.split_pen = tuning(kTuneAttnSplitPen) > 0 ? tuning(kTuneAttnSplitPen) - 1
+                                               : (int)((6 * 44000 + unit_kb * 512) / (unit_kb * 1024));
   e = launch_kernel(kern, dim3(grid), dim3(kAttnThreads), smem, stream, p);
   if (e != cudaSuccess) return cuda_error("sparse_decode_attn launch", e);
   return check_launch("sparse_decode_attn");

@@ -17,7 +17,9 @@ int max_ctas();  // persistent-grid size: sm_count() unless svb200_set_max_ctas 
 // experiment knobs (svb200_set_tuning); 0 = automatic
 enum {
   kTuneScoreGroups = 0, kTuneAttnMinKB = 1, kTuneMinBatch = 2, kTuneShareDiv = 3, kTuneChunkUnits = 4,
-  kTuneNoMath = 5, kTuneScoreQ = 6, kTunePdl = 7, kTuneAttnGranule = 8, kTuneAttnHpc = 9, kTuneCount = 16
+  kTuneNoMath = 5, kTuneScoreQ = 6, kTunePdl = 7, kTuneAttnGranule = 8, kTuneAttnHpc = 9,
+  kTuneAttnSplitPen = 10,  // attention: units a CTA is charged for a row boundary inside its range, + 1 (0: auto, 1: none)
+  kTuneCount = 16
 };
 int tuning(int which);
 bool pdl_enabled();  // launches carry the programmatic-stream-serialization attribute
@@ -123,6 +125,7 @@ struct AttnParams {
   float sm_scale;
   int no_math;       // experiments: consumers release the stages without the contractions
   int granule;       // copy granules of several token rows where the slots allow it
+  int split_pen;     // units a CTA is charged for a row boundary inside its range (see the kernel's cut); launcher
   PushArgs push;     // tensor-parallel push epilogue (world <= 1: none)
 };
 int attn_auto_heads_per_cta(int hkv);

@@ -231,7 +231,8 @@ __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, 
     // Round 15 settles the top bit; the keys then shrink to 15 bits (keys the top bit already decided
     // become 0 = never counted, or 0x7fff = always counted), which lets one VIADDMNMX.S16x2.RELU
     // (max(min(key - cand + 1, 1), 0) per 16-bit half, no overflow with 15-bit operands) compare two
-    // keys per instruction: the 16 counting rounds are bound by their barrier, not by the ALU.
+    // keys per instruction.  A counting round is then bound by its barrier, not by the ALU, so bits 13..0
+    // are settled two per round (three candidates): 9 barriers instead of 16.
     uint32_t acc = 0;
 #pragma unroll
     for (int vv = 0; vv < VPT; ++vv)
@@ -247,8 +248,7 @@ __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, 
         sub[vv][i] = top ? (kw[vv][i] & m) : ((kw[vv][i] | m) & 0x7fff7fffu);
       }
     uint32_t t15 = 0;
-    for (int bit = 14; bit >= 0; --bit) {
-      const uint32_t cand = t15 | (1u << bit);
+    auto count_ge = [&](uint32_t cand) {  // keys >= cand (15-bit, cand >= 1), packed per 16-bit half of the words
       const uint32_t addend = ((1u - cand) & 0xffffu) * 0x00010001u;
       uint32_t a0 = 0, a1 = 0;
 #pragma unroll
@@ -257,7 +257,21 @@ __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, 
         a1 += __viaddmin_s16x2_relu(sub[vv][2], addend, 0x00010001u) + __viaddmin_s16x2_relu(sub[vv][3], addend, 0x00010001u);
       }
       a0 += a1;
-      if (group_total(bit, (int)((a0 & 0xffffu) + (a0 >> 16))) >= k) t15 = cand;
+      return (int)((a0 & 0xffffu) + (a0 >> 16));
+    };
+    if (group_total(14, count_ge(1u << 14)) >= k) t15 = 1u << 14;
+    // bits 13..0 two at a time: three candidates per barrier (their counts are ordered n1 >= n2 >= n3)
+    for (int lo = 12; lo >= 0; lo -= 2) {
+      const uint32_t c1 = t15 | (1u << lo), c2 = t15 | (2u << lo), c3 = t15 | (3u << lo);
+      int n12 = count_ge(c1) | (count_ge(c2) << 16), n3 = count_ge(c3);
+      n12 = __reduce_add_sync(0xffffffffu, n12);  // <= 1024 per half and warp, <= 8192 per half and group
+      n3 = __reduce_add_sync(0xffffffffu, n3);
+      if (lane == 0) sm.wcnt[lo][tid >> 5] = n12, sm.wcnt[lo + 1][tid >> 5] = n3;
+      group_sync<BAR, NTHR>();
+      int t12 = 0, t3 = 0;
+#pragma unroll
+      for (int w = 0; w < NWARP; ++w) t12 += sm.wcnt[lo][w], t3 += sm.wcnt[lo + 1][w];
+      t15 = t3 >= k ? c3 : ((t12 >> 16) >= k ? c2 : ((t12 & 0xffff) >= k ? c1 : t15));
     }
     thresh = (top ? 0x8000u : 0u) | t15;
   } else {
@@ -928,11 +942,12 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
     const int64_t per_cta = (int64_t)p.batch * units_row * unit_bytes / grid;
     int64_t claim = per_cta / 8;
     claim = claim < 32 * 1024 ? 32 * 1024 : (claim > 128 * 1024 ? 128 * 1024 : claim);
-    // a chunk (= one descriptor, fed by the loader's lanes in parallel) carries >= 48 KB when units are small
-    int64_t chunk_target = claim / 2;
-    if (chunk_target < 48 * 1024) chunk_target = 48 * 1024;
+    // A chunk is one descriptor: the scheduler posts it, every consumer warp reads it and the loader's lanes feed
+    // its units in parallel; that handling costs ~0.4 us per descriptor whatever it carries (one unit per
+    // descriptor: 54.7 us at the TP-8 shard shape, eight: 32.2 us; at cfg5 one 64 KB unit: 98.9 us, three: 95.7 us).
+    // So a chunk carries 64 KB of small units (<= 16 KB: 1-2 KV heads per rank) and 192 KB of large ones.
+    const int64_t chunk_target = unit_bytes < 32 * 1024 ? 64 * 1024 : 192 * 1024;
     int cu = tuning(kTuneChunkUnits) > 0 ? tuning(kTuneChunkUnits) : (int)((chunk_target + unit_bytes - 1) / unit_bytes);
-    if (unit_bytes >= 32 * 1024 && tuning(kTuneChunkUnits) <= 0) cu = (int)(claim / 2 / unit_bytes);
     const int ring_units = p.stages / p.hsplit;  // the units of one descriptor occupy distinct ring stages
     if (cu > ring_units) cu = ring_units;
     p.chunk_units = cu < 1 ? 1 : (cu > kMaxChunkUnits ? kMaxChunkUnits : cu);
@@ -943,15 +958,16 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
   }
   // Static first piece = 1/share_div of a CTA's fair share of its home row.  A launch that gives a CTA less than
   // ~1 MB (TP shards, short batches) is over before guided claims could rebalance anything (what a CTA holds in
-  // its ring and descriptor queue is most of its share): cut it statically, claims only move the remainder.
+  // its ring and descriptor queue is most of its share): its rows are cut statically and evenly in units.
   {
     const int64_t per_cta = (int64_t)p.batch * units_row * stage_bytes * p.hsplit / grid;
-    const int auto_div = per_cta < (1 << 20) ? 1 : (per_cta < (2 << 20) ? 2 : 4);
-    p.share_div = tuning(kTuneShareDiv) > 0 ? tuning(kTuneShareDiv) : auto_div;
+    const int auto_div = per_cta < (1 << 20) ? 0 : (per_cta < (2 << 20) ? 2 : 4);  // 0: even static cut in units
+    p.share_div = tuning(kTuneShareDiv) > 0 ? (tuning(kTuneShareDiv) == 99 ? 0 : tuning(kTuneShareDiv)) : auto_div;
   }
   p.no_math = tuning(kTuneNoMath) == 1;
   const size_t smem = score_smem_layout(p.stages, p.hq, p.hkv, p.hsplit, p.batch, FUSED, qsplit ? 2 : 1).total;
-  const int64_t max_chunks = (int64_t)p.batch * ((units_row + p.chunk_units - 1) / p.chunk_units);
+  // no more CTAs than pieces of work: chunks, or single units when the rows are cut evenly
+  const int64_t max_chunks = (int64_t)p.batch * (p.share_div == 0 ? units_row : (units_row + p.chunk_units - 1) / p.chunk_units);
   if ((int64_t)grid > max_chunks) grid = (int)max_chunks;
   if (grid < 1) grid = 1;
   const cudaError_t e = qsplit ? launch_score_kernel<NT, FUSED, true>(p, grid, smem, stream)

@@ -75,10 +75,27 @@ __device__ __forceinline__ void st_volatile_shared(int* p, int v) {
 struct ReserveNone {
   __device__ __forceinline__ int operator()(int) const { return 0; }
 };
+// share_div == 0: the first home row of every CTA is cut statically and evenly IN UNITS among its `share` home
+// CTAs (descriptors of up to cu units, no counter traffic at all); nothing of those rows is left to claim or steal.
+// For launches that are over before claims could rebalance anything (see the launcher).
 template <class UnitsOfRow, class Reserve = ReserveNone>
 __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int rows, int groups, int cu,
                           int min_batch, int share_div, int depth, UnitsOfRow units_of_row,
                           Reserve reserve = Reserve(), unsigned long long* t_last_claim = nullptr) {
+  bool even = share_div == 0;
+  if (even) {
+    // an even cut gives every row the same number of CTAs: only for rows of (nearly) equal length; ragged batches
+    // need the claims and the stealing (every CTA reaches the same verdict from the same lengths)
+    int64_t total = 0;
+    int longest = 0;
+    for (int r = 0; r < rows; ++r) {
+      const int nu = units_of_row(r);
+      total += nu;
+      longest = max(longest, nu);
+    }
+    even = (int64_t)longest * rows * 4 <= total * 5;
+    share_div = even ? 1 : 2;
+  }
   const int lane = threadIdx.x & 31;
   int n = 0, ubase = 0, aux = 0;
   auto post = [&](int row, int begin, int cnt) {
@@ -109,7 +126,7 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
   auto static_chunks = [&](int row) {
     if (row >= groups || share * groups > (int)gridDim.x) return 0;
     const int d = chunks_of(row);
-    return min(d, share * static_piece(d));
+    return even ? d : min(d, share * static_piece(d));
   };
   auto drain = [&](int row, bool guided, bool first_home) -> bool {  // false: reserve() refused the row
     const int nu = units_of_row(row);
@@ -119,6 +136,16 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
     if (!guided && base + __ldcg(next_chunk + row) >= d) return true;  // thief, nothing left: do not reserve
     aux = reserve(row);
     if (aux < 0) return false;
+    if (even && base == d) {
+      // evenly cut row: only its home CTAs get here (for a thief nothing is left), each posts its own units
+      if (first_home) {
+        const int l = (int)(blockIdx.x / (unsigned)groups);
+        const int u_end = (int)((int64_t)nu * (l + 1) / share);
+        if (t_last_claim && lane == 0) *t_last_claim = global_timer_ns();
+        for (int ub = (int)((int64_t)nu * l / share); ub < u_end; ub += cu) post(row, ub, min(cu, u_end - ub));
+      }
+      return true;
+    }
     auto batch = [&](int left) { return guided ? guided_batch(left) : min_batch; };
     int m = first_home ? static_piece(d) : batch(d), j = 0, taken = 0;
     if (first_home) {

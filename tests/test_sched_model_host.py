@@ -12,8 +12,12 @@ def simulate(rows_units, grid, groups, cu, min_batch, share_div, seed):
     rows = len(rows_units)
     groups = max(1, min(groups, rows))
     share = max(1, grid // groups)
+    even = share_div == 0   # the first home rows are cut evenly in units, nothing of them is claimed
+    if even:
+        even = max(rows_units) * rows * 4 <= sum(rows_units) * 5   # ragged batches keep claims and stealing
+        share_div = 1 if even else 2
     counters = [0] * rows
-    posted = [[0] * ((u + cu - 1) // cu) for u in rows_units]
+    posted = [[0] * u for u in rows_units]
     chunks_of = lambda r: (rows_units[r] + cu - 1) // cu
     guided = lambda left: max(min_batch, left // (share_div * share))
     static_piece = lambda d: max(1, d // (share_div * share))
@@ -21,9 +25,13 @@ def simulate(rows_units, grid, groups, cu, min_batch, share_div, seed):
         if r >= groups or share * groups > grid:
             return 0
         d = chunks_of(r)
-        return min(d, share * static_piece(d))
+        return d if even else min(d, share * static_piece(d))
+    def post_units(r, begin, cnt):
+        assert 1 <= cnt <= cu
+        for u in range(begin, begin + cnt):
+            posted[r][u] += 1
     def post(r, c):
-        posted[r][c] += 1
+        post_units(r, c * cu, min(cu, rows_units[r] - c * cu))
     # each CTA is a generator yielding at every atomic (so interleavings vary)
     def cta(bid):
         def drain(row, is_guided, first_home):
@@ -32,6 +40,13 @@ def simulate(rows_units, grid, groups, cu, min_batch, share_div, seed):
                 return
             base = static_chunks(row)
             if not is_guided and base + counters[row] >= d:
+                return
+            if even and base == d:
+                if first_home:
+                    nu, l = rows_units[row], bid // groups
+                    u_end = nu * (l + 1) // share
+                    for ub in range(nu * l // share, u_end, cu):
+                        post_units(row, ub, min(cu, u_end - ub))
                 return
             batch = (lambda left: guided(left)) if is_guided else (lambda left: min_batch)
             m = static_piece(d) if first_home else batch(d)
@@ -87,11 +102,11 @@ def simulate(rows_units, grid, groups, cu, min_batch, share_div, seed):
 
 
 
-def test_every_chunk_is_posted_exactly_once():
+def test_every_unit_is_posted_exactly_once():
     rnd = random.Random(0)
     for trial in range(600):
         rows = rnd.choice([1, 2, 3, 5, 16, 32])
-        units = [rnd.choice([0, 1, 2, 7, 33, 128, 512]) for _ in range(rows)]
+        units = [rnd.choice([0, 1, 2, 7, 33, 128, 512]) for _ in range(rows)] if trial % 3 else [rnd.choice([1, 7, 100, 512])] * rows
         grid = rnd.choice([1, 2, 7, 16, 37, 128, 148])
         groups = rnd.choice([rows, max(1, rows // 2), 1])
-        simulate(units, grid, groups, rnd.choice([1, 2, 3, 4, 8]), rnd.choice([1, 2, 3]), rnd.choice([2, 4]), trial)
+        simulate(units, grid, groups, rnd.choice([1, 2, 3, 4, 8]), rnd.choice([1, 2, 3]), rnd.choice([0, 1, 2, 4]), trial)
