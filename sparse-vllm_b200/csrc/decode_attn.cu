@@ -39,6 +39,8 @@
 // every rank's gathered [B][world*Hq][128] buffer over NVLink (peer stores), and the last CTA of the
 // launch signals the peers and waits for theirs: when the launch completes, the all-gather of the head
 // shards has completed as well (no NCCL launch per layer).
+#include <type_traits>
+
 #include "common.cuh"
 #include "launch.h"
 
@@ -391,13 +393,72 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
     const int b = mr / HG, hg = mr - b * HG;
     const int c_first = cut.owner(row_begin, mr), c_last = cut.owner(row_end - 1, mr);
     const unsigned long long t_cmb = dbg ? global_timer_ns() : 0;
-    // One warp per q head, lane = 4 output dims.  Lane c first fetches the lse of contributor
-    // c (all contributors in parallel), then the partial outputs are read with independent
-    // loads: the merge costs a couple of L2 round trips, not one per contributor.
+    // One warp per group of q heads, lane = 4 output dims.  Fast path (the usual case: a row has a handful of
+    // contributors): lane c fetches the lse of contributor c AND every lane fetches its 4 dims of every
+    // contributor's partial at once, so the merge costs ONE L2 round trip; the weights are applied when both
+    // have arrived.  HB heads x NCMAX contributors x 4 floats are in flight per lane (96 registers: the
+    // accumulators of the main loop are dead by now).
     __threadfence();
     const int nc = c_last - c_first + 1;
+    auto fast = [&](auto hb_tag, auto nc_tag) {
+      constexpr int HBF = decltype(hb_tag)::value, NCMAX = decltype(nc_tag)::value;
+      int ps = 0;
+      if (lane < nc) ps = 2 * (c_first + lane) + (cut.begin_of(c_first + lane) >= row_begin ? 0 : 1);
+      for (int h0 = warp * HBF; h0 < heads_row; h0 += kConsumerWarps * HBF) {
+        float lse[HBF];
+        float4 v[NCMAX][HBF];
+#pragma unroll
+        for (int x = 0; x < HBF; ++x)
+          lse[x] = (lane < nc && h0 + x < heads_row) ? __ldcg(p.ws_lse + (int64_t)ps * heads_row + h0 + x) : -INFINITY;
+#pragma unroll
+        for (int kc2 = 0; kc2 < NCMAX; ++kc2) {
+          const int psk = __shfl_sync(0xffffffffu, ps, kc2);
+          const float4* src = reinterpret_cast<const float4*>(p.ws_o + ((int64_t)psk * heads_row + h0) * kHeadDim) + lane;
+#pragma unroll
+          for (int x = 0; x < HBF; ++x)
+            v[kc2][x] = (kc2 < nc && h0 + x < heads_row) ? __ldcg(src + x * (kHeadDim / 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int x = 0; x < HBF; ++x) {
+          float cm = lse[x];
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+          const float wgt = lse[x] == -INFINITY ? 0.f : __expf(lse[x] - cm);
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+          float wsum = 0.f;
+#pragma unroll
+          for (int kc2 = 0; kc2 < NCMAX; ++kc2) {
+            const float wk = __shfl_sync(0xffffffffu, wgt, kc2);
+            if (kc2 < nc && wk != 0.f) {
+              acc.x += wk * v[kc2][x].x, acc.y += wk * v[kc2][x].y, acc.z += wk * v[kc2][x].z, acc.w += wk * v[kc2][x].w;
+              wsum += wk;
+            }
+          }
+          if (h0 + x < heads_row) {
+            const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
+            uint2 o2;
+            o2.x = pack_bf16x2(acc.x * inv, acc.y * inv);
+            o2.y = pack_bf16x2(acc.z * inv, acc.w * inv);
+            __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) + (int64_t)b * p.out_stride_b +
+                                  (int64_t)(hg * heads_row + h0 + x) * kHeadDim;
+            *reinterpret_cast<uint2*>(orow + lane * 4) = o2;
+            if (push) {
+              const int64_t off = (int64_t)b * p.push.stride_b +
+                                  ((int64_t)p.push.rank * p.hq + hg * heads_row + h0 + x) * kHeadDim + lane * 4;
+              for (int r = 0; r < p.push.world; ++r) *reinterpret_cast<uint2*>(p.push.out[r] + off) = o2;
+            }
+          }
+        }
+      }
+    };
+    bool merged = true;
+    if (heads_row > 16 && nc <= 6) fast(std::integral_constant<int, 4>(), std::integral_constant<int, 6>());
+    else if (heads_row > 8 && heads_row <= 16 && nc <= 12) fast(std::integral_constant<int, 2>(), std::integral_constant<int, 12>());
+    else if (heads_row <= 8 && nc <= 24) fast(std::integral_constant<int, 1>(), std::integral_constant<int, 24>());
+    else merged = false;
+    // General path (any number of contributors): the lse first, then the partials that carry weight.
     constexpr int HB = 4;  // heads a warp merges at once: their loads are all independent
-    for (int h0 = warp * HB; h0 < heads_row; h0 += kConsumerWarps * HB) {
+    for (int h0 = merged ? heads_row : warp * HB; h0 < heads_row; h0 += kConsumerWarps * HB) {
       float m[HB], wsum[HB];
       float4 acc[HB];
 #pragma unroll
