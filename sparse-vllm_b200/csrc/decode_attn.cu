@@ -110,25 +110,31 @@ struct AttnCut {
 };
 
 // ---- tensor-parallel push epilogue (see the file header)
-// Called by ONE thread per CTA (every CTA of the grid, exactly once) after the CTA's peer stores were
-// fenced (__threadfence_system by the writers) and a CTA barrier.  The last CTA to arrive bumps the epoch,
-// raises this rank's flag on every peer and waits for the peers' flags: the launch does not complete
-// before every rank's rows have landed here.  Flags only grow, peers can be at most one launch ahead.
+// Called by ONE thread per CTA (every CTA of the grid, exactly once) after a CTA barrier that follows the CTA's
+// last peer store.  System-scope fences are the expensive part of the hand-shake (a fence waits for the NVLink
+// acknowledgements of everything outstanding), so there are exactly two on the critical path:
+//   1. this thread's fence before its arrival: the barrier ordered the CTA's peer stores before it, the fence
+//      makes them visible at system scope before the arrival (the writers themselves do not fence);
+//   2. the last CTA's fence after the arrival counter told it that every CTA has arrived: it orders all of
+//      their stores before the flags, which are then plain relaxed stores, one per peer (a release store per
+//      peer would be a fence per peer).
+// The last CTA then waits for the peers' flags: the launch does not complete before every rank's rows have
+// landed here.  Flags only grow, peers can be at most one launch ahead.
 __device__ void push_finish(const PushArgs& ps) {
   int32_t* local = ps.sync[ps.rank];
   __threadfence_system();
   if (atomicAdd(local + kSyncDone, 1) != (int)gridDim.x - 1) return;
   local[kSyncDone] = 0;
-  __threadfence_system();
   const int32_t e = local[kSyncEpoch] + 1;
   local[kSyncEpoch] = e;
+  __threadfence_system();
   for (int r = 0; r < ps.world; ++r)
-    if (r != ps.rank) st_release_sys(ps.sync[r] + ps.rank, e);
+    if (r != ps.rank) st_relaxed_sys(ps.sync[r] + ps.rank, e);
   for (int r = 0; r < ps.world; ++r) {
     if (r == ps.rank) continue;
     SpinGuard guard;
     while (ld_acquire_sys(local + r) - e < 0) {
-      __nanosleep(64);
+      __nanosleep(32);
       guard.tick(kPeerSpinLimitNs);
     }
   }
@@ -236,7 +242,6 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
                                                (int64_t)p.push.rank * p.hq * kHeadDim);
           for (int i = tid; i < p.hq * 16; i += kAttnThreads) g4[i] = make_uint4(0, 0, 0, 0);
         }
-        __threadfence_system();
       }
     }
   }
@@ -521,7 +526,6 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
         }
       }
     }
-    if (push) __threadfence_system();
     if (dbg && tid == 0) dbg[5] += global_timer_ns() - t_cmb;
   };
 
@@ -768,7 +772,6 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
                                                (int64_t)p.push.rank * p.hq * kHeadDim + head0);
           for (int c = tid; c < heads_row * 16; c += kConsumerThreads) g4[c] = src[c];
         }
-        __threadfence_system();
       }
     }
     if (!complete) {

@@ -6,6 +6,8 @@
 //   scoring : _score_pages_batched 1773-1802 (three bf16 roundings per head score)
 //   select  : _build_decode_view_static 1833-1913
 #include "bounds_layout.cuh"
+#include <type_traits>
+
 #include "common.cuh"
 #include "launch.h"
 #include "sched.cuh"
@@ -771,49 +773,50 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
         const uint32_t abase = smem_u32(ring + s * stage_bytes) + lm_row;
         // KV heads two at a time: the two heads' ldmatrix -> mma chains are independent, so the in-order
         // issue of one warp overlaps their latencies (one head at a time left the consumers the bottleneck
-        // at Hkv 8); an odd last head runs alone
+        // at Hkv 8); an odd last head (and the only head of a TP-8 shard) runs alone
         const int hbase = part * hh;  // first KV head of this stage
-        for (int h = 0; h < hh && !p.no_math; h += 2) {
-          const bool two = h + 1 < hh;
-          const int h1 = two ? h + 1 : h;
-          float cp[2][NT][4], cn[2][NT][4];
+        auto score_heads = [&](auto nh_tag, int h) {
+          constexpr int NH = decltype(nh_tag)::value;
+          float cp[NH][NT][4], cn[NH][NT][4];
 #pragma unroll
-          for (int x = 0; x < 2; ++x)
+          for (int x = 0; x < NH; ++x)
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
               for (int e = 0; e < 4; ++e) cp[x][nt][e] = cn[x][nt][e] = 0.f;
-          const uint32_t amax0 = abase + h * kRowBytes, amin0 = amax0 + hh * kRowBytes;
-          const uint32_t amax1 = abase + h1 * kRowBytes, amin1 = amax1 + hh * kRowBytes;
+          uint32_t amax[NH], amin[NH];
+#pragma unroll
+          for (int x = 0; x < NH; ++x) amax[x] = abase + (h + x) * kRowBytes, amin[x] = amax[x] + hh * kRowBytes;
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk) {
             const uint32_t koff = ((uint32_t)(kk * 32) | lm_hi) ^ lm_xor;
-            uint32_t a0x[4], a0n[4], a1x[4], a1n[4];
-            ldmatrix_x4(a0x, amax0 + koff);
-            ldmatrix_x4(a0n, amin0 + koff);
-            ldmatrix_x4(a1x, amax1 + koff);
-            ldmatrix_x4(a1n, amin1 + koff);
+            uint32_t ax[NH][4], an[NH][4];
+#pragma unroll
+            for (int x = 0; x < NH; ++x) {
+              ldmatrix_x4(ax[x], amax[x] + koff);
+              ldmatrix_x4(an[x], amin[x] + koff);
+            }
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
-              const int q0 = (hbase + h) * gsz + min(nt * 8 + g, gsz - 1), q1 = (hbase + h1) * gsz + min(nt * 8 + g, gsz - 1);
-              const int f0 = (q0 * 8 + (kk ^ (q0 & 7))) * 4 + t, f1 = (q1 * 8 + (kk ^ (q1 & 7))) * 4 + t;
-              uint2 bp0 = sq2[f0], bp1 = sq2[f1], bn0, bn1;
-              if constexpr (QSPLIT) {
-                bn0 = sq2[neg_off + f0], bn1 = sq2[neg_off + f1];
-              } else {
-                bn0 = make_uint2(q_neg(bp0.x), q_neg(bp0.y)), bn1 = make_uint2(q_neg(bp1.x), q_neg(bp1.y));
-                bp0 = make_uint2(q_pos(bp0.x), q_pos(bp0.y)), bp1 = make_uint2(q_pos(bp1.x), q_pos(bp1.y));
+#pragma unroll
+              for (int x = 0; x < NH; ++x) {
+                const int qh = (hbase + h + x) * gsz + min(nt * 8 + g, gsz - 1);
+                const int f = (qh * 8 + (kk ^ (qh & 7))) * 4 + t;
+                uint2 bp = sq2[f], bn;
+                if constexpr (QSPLIT) {
+                  bn = sq2[neg_off + f];
+                } else {
+                  bn = make_uint2(q_neg(bp.x), q_neg(bp.y));
+                  bp = make_uint2(q_pos(bp.x), q_pos(bp.y));
+                }
+                mma_16816(cp[x][nt], ax[x], bp.x, bp.y);
+                mma_16816(cn[x][nt], an[x], bn.x, bn.y);
               }
-              mma_16816(cp[0][nt], a0x, bp0.x, bp0.y);
-              mma_16816(cn[0][nt], a0n, bn0.x, bn0.y);
-              mma_16816(cp[1][nt], a1x, bp1.x, bp1.y);
-              mma_16816(cn[1][nt], a1n, bn1.x, bn1.y);
             }
           }
           // c0:(page g, head 2t) c1:(g, 2t+1) c2:(g+8, 2t) c3:(g+8, 2t+1)
 #pragma unroll
-          for (int x = 0; x < 2; ++x) {
-            if (x == 1 && !two) break;
+          for (int x = 0; x < NH; ++x) {
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
               float sc[4];
@@ -824,6 +827,11 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
               if (col0 + 1 < gsz) best0 = fmaxf(best0, sc[1]), best1 = fmaxf(best1, sc[3]);
             }
           }
+        };
+        if (!p.no_math) {
+          int h = 0;
+          for (; h + 1 < hh; h += 2) score_heads(std::integral_constant<int, 2>(), h);
+          if (h < hh) score_heads(std::integral_constant<int, 1>(), h);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty_bar[s]);
