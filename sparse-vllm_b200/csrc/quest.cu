@@ -231,10 +231,12 @@ __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, 
   };
   if constexpr (CACHED) {
     // Round 15 settles the top bit; the keys then shrink to 15 bits (keys the top bit already decided
-    // become 0 = never counted, or 0x7fff = always counted), which lets one VIADDMNMX.S16x2.RELU
-    // (max(min(key - cand + 1, 1), 0) per 16-bit half, no overflow with 15-bit operands) compare two
-    // keys per instruction.  A counting round is then bound by its barrier, not by the ALU, so bits 13..0
-    // are settled two per round (three candidates): 9 barriers instead of 16.
+    // become 0 = never counted, or 0x7fff = always counted) and get a guard bit above them, so that ONE
+    // subtraction compares the two keys of a word with a candidate: (key | 0x8000) - cand keeps bit 15
+    // iff key >= cand, and never borrows across the halves.  Three full-rate integer instructions per
+    // two keys (the packed-halfword min/max instructions, VIADDMNMX.S16x2, do it in one but issue at a
+    // fraction of the integer rate here: measured slower).  A counting round is then bound by its barrier
+    // as much as by the ALU, so bits 13..0 are settled two per round (three candidates): 9 barriers, not 16.
     uint32_t acc = 0;
 #pragma unroll
     for (int vv = 0; vv < VPT; ++vv)
@@ -247,16 +249,16 @@ __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, 
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const uint32_t m = ((kw[vv][i] >> 15) & 0x00010001u) * 0x7fffu;
-        sub[vv][i] = top ? (kw[vv][i] & m) : ((kw[vv][i] | m) & 0x7fff7fffu);
+        sub[vv][i] = (top ? (kw[vv][i] & m) : ((kw[vv][i] | m) & 0x7fff7fffu)) | 0x80008000u;
       }
     uint32_t t15 = 0;
-    auto count_ge = [&](uint32_t cand) {  // keys >= cand (15-bit, cand >= 1), packed per 16-bit half of the words
-      const uint32_t addend = ((1u - cand) & 0xffffu) * 0x00010001u;
+    auto count_ge = [&](uint32_t cand) {  // keys >= cand (15-bit, cand >= 1), both halves of every word at once
+      const uint32_t c2 = cand * 0x00010001u;
       uint32_t a0 = 0, a1 = 0;
 #pragma unroll
       for (int vv = 0; vv < VPT; ++vv) {
-        a0 += __viaddmin_s16x2_relu(sub[vv][0], addend, 0x00010001u) + __viaddmin_s16x2_relu(sub[vv][1], addend, 0x00010001u);
-        a1 += __viaddmin_s16x2_relu(sub[vv][2], addend, 0x00010001u) + __viaddmin_s16x2_relu(sub[vv][3], addend, 0x00010001u);
+        a0 += (((sub[vv][0] - c2) >> 15) & 0x00010001u) + (((sub[vv][1] - c2) >> 15) & 0x00010001u);
+        a1 += (((sub[vv][2] - c2) >> 15) & 0x00010001u) + (((sub[vv][3] - c2) >> 15) & 0x00010001u);
       }
       a0 += a1;
       return (int)((a0 & 0xffffu) + (a0 >> 16));
