@@ -231,12 +231,12 @@ __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, 
   };
   if constexpr (CACHED) {
     // Round 15 settles the top bit; the keys then shrink to 15 bits (keys the top bit already decided
-    // become 0 = never counted, or 0x7fff = always counted) and get a guard bit above them, so that ONE
-    // subtraction compares the two keys of a word with a candidate: (key | 0x8000) - cand keeps bit 15
-    // iff key >= cand, and never borrows across the halves.  Three full-rate integer instructions per
-    // two keys (the packed-halfword min/max instructions, VIADDMNMX.S16x2, do it in one but issue at a
-    // fraction of the integer rate here: measured slower).  A counting round is then bound by its barrier
-    // as much as by the ALU, so bits 13..0 are settled two per round (three candidates): 9 barriers, not 16.
+    // become 0 = never counted, or 0x7fff = always counted), which lets one VIADDMNMX.S16x2.RELU
+    // (max(min(key - cand + 1, 1), 0) per 16-bit half, no overflow with 15-bit operands) compare two
+    // keys per instruction.  Measured on the 8192-column rows of cfg5 (8 warps, 32 keys per thread): compare +
+    // add per key 4.0 us for the 16 rounds, this 2.9 us; two bits per round (three candidates, 9 barriers) 3.0 us
+    // and a guarded subtraction on the integer pipe ((key | 0x8000) - cand keeps bit 15 iff key >= cand) 3.7 us:
+    // the rounds are bound by the instructions of the 8 warps, not by their barriers.
     uint32_t acc = 0;
 #pragma unroll
     for (int vv = 0; vv < VPT; ++vv)
@@ -249,33 +249,20 @@ __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, 
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const uint32_t m = ((kw[vv][i] >> 15) & 0x00010001u) * 0x7fffu;
-        sub[vv][i] = (top ? (kw[vv][i] & m) : ((kw[vv][i] | m) & 0x7fff7fffu)) | 0x80008000u;
+        sub[vv][i] = top ? (kw[vv][i] & m) : ((kw[vv][i] | m) & 0x7fff7fffu);
       }
     uint32_t t15 = 0;
-    auto count_ge = [&](uint32_t cand) {  // keys >= cand (15-bit, cand >= 1), both halves of every word at once
-      const uint32_t c2 = cand * 0x00010001u;
+    for (int bit = 14; bit >= 0; --bit) {
+      const uint32_t cand = t15 | (1u << bit);
+      const uint32_t addend = ((1u - cand) & 0xffffu) * 0x00010001u;
       uint32_t a0 = 0, a1 = 0;
 #pragma unroll
       for (int vv = 0; vv < VPT; ++vv) {
-        a0 += (((sub[vv][0] - c2) >> 15) & 0x00010001u) + (((sub[vv][1] - c2) >> 15) & 0x00010001u);
-        a1 += (((sub[vv][2] - c2) >> 15) & 0x00010001u) + (((sub[vv][3] - c2) >> 15) & 0x00010001u);
+        a0 += __viaddmin_s16x2_relu(sub[vv][0], addend, 0x00010001u) + __viaddmin_s16x2_relu(sub[vv][1], addend, 0x00010001u);
+        a1 += __viaddmin_s16x2_relu(sub[vv][2], addend, 0x00010001u) + __viaddmin_s16x2_relu(sub[vv][3], addend, 0x00010001u);
       }
       a0 += a1;
-      return (int)((a0 & 0xffffu) + (a0 >> 16));
-    };
-    if (group_total(14, count_ge(1u << 14)) >= k) t15 = 1u << 14;
-    // bits 13..0 two at a time: three candidates per barrier (their counts are ordered n1 >= n2 >= n3)
-    for (int lo = 12; lo >= 0; lo -= 2) {
-      const uint32_t c1 = t15 | (1u << lo), c2 = t15 | (2u << lo), c3 = t15 | (3u << lo);
-      int n12 = count_ge(c1) | (count_ge(c2) << 16), n3 = count_ge(c3);
-      n12 = __reduce_add_sync(0xffffffffu, n12);  // <= 1024 per half and warp, <= 8192 per half and group
-      n3 = __reduce_add_sync(0xffffffffu, n3);
-      if (lane == 0) sm.wcnt[lo][tid >> 5] = n12, sm.wcnt[lo + 1][tid >> 5] = n3;
-      group_sync<BAR, NTHR>();
-      int t12 = 0, t3 = 0;
-#pragma unroll
-      for (int w = 0; w < NWARP; ++w) t12 += sm.wcnt[lo][w], t3 += sm.wcnt[lo + 1][w];
-      t15 = t3 >= k ? c3 : ((t12 >> 16) >= k ? c2 : ((t12 & 0xffff) >= k ? c1 : t15));
+      if (group_total(bit, (int)((a0 & 0xffffu) + (a0 >> 16))) >= k) t15 = cand;
     }
     thresh = (top ? 0x8000u : 0u) | t15;
   } else {
