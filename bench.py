@@ -158,7 +158,7 @@ def geometry(w: dict, hkv_local: int, hq_local: int) -> dict:
 def ncu_traffic(workload_key: str, kernel: str):
     """DRAM bytes per launch of `kernel` from the committed ncu capture of this workload, or None."""
     try:
-        return json.loads((ROOT / "profiles" / "r1_traffic.json").read_text())[workload_key][kernel]
+        return json.loads((ROOT / "profiles" / "r2_traffic.json").read_text())[workload_key][kernel]
     except Exception:
         return None
 
@@ -264,6 +264,8 @@ class DecodeStep:
         self.h_out = torch.empty(self.out.shape, dtype=torch.bfloat16).pin_memory()
         self.launches_per_step = 0
         self.timers = None  # optional per-kernel CUDA-event collection
+        self.no_comm = False         # per-kernel timing: the launches without their collective ...
+        self.only_collective = False  # ... and (NCCL arm) the collective without the launches
 
     def prepare(self):
         """Host side of a decode step: allocate one slot per row, fill the static metadata buffers."""
@@ -284,13 +286,17 @@ class DecodeStep:
             mgr.save_rope_kv_if_needed(layer, self.k_new[layer], self.v_new[layer], st.slot_mapping)
             sel = SparseSelection(kind="full", req_indices=st.req_indices, context_lens=st.context_lens,
                                   max_context_len=st.max_context_len)
-            push = self.collective == "push"
+            push = self.collective == "push" and not self.no_comm
+            if self.only_collective:
+                import torch.distributed as dist
+                dist.all_gather_into_tensor(self.gathered[layer & 1].view(-1), self.out[layer].view(-1))
+                continue
             decode_attention_layer(mgr, self.backend, layer, self.q[layer], sel, num_heads=self.hq,
                                    num_kv_heads=self.hkv, out=self.out[layer], tp_comm=self.comm if push else None,
                                    tp_gathered=self.gathered[layer & 1] if push else None)
             # dense layer: store + attention; sparse layer: (store fused into) score/select/pack + attention
             n += 2 if (layer < self.skip or getattr(mgr, "fuse_decode_store", False)) else 3
-            if self.collective == "nccl":
+            if self.collective == "nccl" and not self.no_comm:
                 import torch.distributed as dist
                 dist.all_gather_into_tensor(self.gathered[layer & 1].view(-1), self.out[layer].view(-1))
         if lo == 0 and hi == self.w["layers"]:
@@ -334,10 +340,20 @@ def graph_kernel_times(step, stream, lo: int, hi: int, reps: int = 5) -> dict:
     prov = step.mgr._get_provider(step.hq)
     real_select, real_decode = prov.quest_select, prov.decode
     out = {}
+    # N > 1: the two launches are timed without the collective; then the collective's share of a layer: the attention
+    # launch WITH its push epilogue (every rank replays the same graph, so the hand-shake is the real one), or the
+    # NCCL all-gather alone
+    keys = ["quest_score_select_pack", "sparse_decode_attn"]
+    if step.collective == "push":
+        keys.append("sparse_decode_attn+push")
+    elif step.collective == "nccl":
+        keys.append("nccl_all_gather")
     try:
-        for key in ("quest_score_select_pack", "sparse_decode_attn"):
+        for key in keys:
             prov.quest_select = real_select if key == "quest_score_select_pack" else (lambda *a, **k: None)
-            prov.decode = real_decode if key == "sparse_decode_attn" else (lambda q, *a, out=None, **k: out)
+            prov.decode = real_decode if key.startswith("sparse_decode_attn") else (lambda q, *a, out=None, **k: out)
+            step.no_comm = key in ("quest_score_select_pack", "sparse_decode_attn")
+            step.only_collective = key == "nccl_all_gather"
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=stream):
                 step.layers(lo, hi)
@@ -353,6 +369,7 @@ def graph_kernel_times(step, stream, lo: int, hi: int, reps: int = 5) -> dict:
             g.reset()
     finally:
         prov.quest_select, prov.decode = real_select, real_decode
+        step.no_comm = step.only_collective = False
     return out
 
 
@@ -570,9 +587,24 @@ def run_b200(args) -> dict:
                  "peak": peak, "unit": "GB/s", "bytes_per_launch": attn_bytes, "avg_launch_ms": attn_ms,
                  "traffic": ncu_traffic(w["key"], "sparse_decode_attn_kernel") if world == 1 else None}
     roof_attn["frac"] = roof_attn["achieved"] / peak
+    roof_attn["how"] = ksum["sparse_decode_attn"].get("how", "eager launches, CUDA event pairs") + (
+        " (without the collective: see `collective`)" if world > 1 else "")
     roof_step = {"achieved": step_bytes / (ms_per_step * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                  "bytes_per_step": step_bytes}
     roof_step["frac"] = roof_step["achieved"] / peak
+    collective = None
+    if world > 1 and "sparse_decode_attn+push" in ksum:
+        with_push = ksum["sparse_decode_attn+push"]["avg_ms"]
+        collective = {"kind": "push epilogue of the attention launch (peer stores over NVLink + flag hand-shake)",
+                      "us_per_layer": (with_push - attn_ms) * 1e3, "attention_with_push_ms": with_push}
+    elif world > 1 and "nccl_all_gather" in ksum:
+        collective = {"kind": "ncclAllGather of the head shards, one per layer",
+                      "us_per_layer": ksum["nccl_all_gather"]["avg_ms"] * 1e3}
+    if collective is not None:
+        layer_us = ms_per_step * 1e3 / w["layers"]
+        collective["layer_us"] = layer_us
+        collective["other_us_per_layer"] = layer_us - (sel_ms + attn_ms) * 1e3 - collective["us_per_layer"]
+        collective["other_is"] = "launch gaps of the graph + waiting for the slowest rank of the layer"
     for r_ in (roof, roof_attn, roof_step):  # north_star quotes ~8 TB/s nominal: report against that too
         r_["frac_of_nominal_8tbs"] = r_["achieved"] / NOMINAL_GBS
     roof_dense = None
@@ -632,6 +664,8 @@ def run_b200(args) -> dict:
     }
     if roof_dense is not None:
         line["roofline_dense_layer"] = roof_dense
+    if collective is not None:
+        line["collective"] = collective
     if world > 1:
         print(json.dumps(line), flush=True)  # before clean-up: the line must not depend on it
         line["_printed"] = True
