@@ -400,6 +400,7 @@ class KernelTimers:
 
     def summary(self) -> dict:
         out = {}
+        self.torch.cuda.synchronize()  # the event pairs were recorded on a side stream
         for key, pairs in self.pairs.items():
             ms = [a.elapsed_time(b) for a, b in pairs]
             out[key] = {"launches": len(ms), "avg_ms": sum(ms) / len(ms) if ms else None, "total_ms": sum(ms)}
