@@ -74,11 +74,9 @@ int64_t svb200_sched_scratch_ints(int32_t rows);
 void svb200_debug_times(void* device_buffer);
 
 /*
- * Bytes of scratch svb200_sparse_decode_attn needs: one int32 word per (batch row, KV head)
- * (reserved) followed by two fp32 partial records (lse words, then output rows) per SM.
- * The buffer must be zero-initialised once: a zero lse word means "partial not published yet"
- * (the words double as arrival flags); every launch leaves the words it used zeroed again, so
- * graph replays are idempotent.  One workspace per stream: launches that share one must not overlap.
+ * Bytes of scratch svb200_sparse_decode_attn needs: one int32 arrival ticket per
+ * (batch row, KV head) followed by two fp32 partial records (output + lse) per SM.
+ * The buffer must be zero-initialised once; kernels leave the tickets zeroed.
  * Takes the place of the reference's mid_o / mid_o_logexpsum split-K workspace
  * (layers/attention.py:15-51), whose size grows with batch * context / 256; this one
  * depends on the SM count only.

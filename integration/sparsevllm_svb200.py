@@ -85,7 +85,7 @@ class SVB200AttentionBackend(TritonAttentionBackend):
     def _workspace(self, batch: int, num_heads: int, num_kv_heads: int, device) -> torch.Tensor:
         key = (batch, num_heads, num_kv_heads, str(device))
         ws = self._workspaces.get(key)
-        if ws is None:  # zeroed once per shape, outside graph capture; launches leave the flag words zeroed again
+        if ws is None:  # zeroed once per shape, outside graph capture; launches leave the ticket part zeroed
             nbytes = int(_lib.svb200_workspace_bytes(batch, num_heads, num_kv_heads))
             ws = torch.zeros((nbytes + 3) // 4, dtype=torch.int32, device=device)
             self._workspaces[key] = ws

@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
   int* sPrefix = reinterpret_cast<int*>(smem + L.prefix_off);
   int* sLen = reinterpret_cast<int*>(smem + L.entry_off);  // min(seq_len, max_len) of batch entry b
   int* sTab = sLen + p.batch;                              // its row of the slot table
-  __shared__ int s_flag;
+  __shared__ int s_flag, s_defer;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   unsigned long long* dbg = p.dbg_times ? p.dbg_times + (size_t)blockIdx.x * 8 : nullptr;
@@ -198,6 +198,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
       mbar_init(&full_bar[s], 1);  // the producer's expect_tx arrival; the copies' bytes complete the phase
       mbar_init(&empty_bar[s], HPC);
     }
+    s_defer = 0;
     mbar_fence_init();
   }
   pdl_wait();
@@ -390,97 +391,120 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
   const float scale_log2 = p.sm_scale * kLog2e;
   const int heads_row = HPC * gsz;
 
-  // Merge of a row that several CTAs contributed to, run by all consumer warps of the row's FIRST contributor (the
-  // CTA that owns the row's first unit; the row is its last segment, and the cut gave it less to stream, so it is
-  // early).  A contributor publishes, per KV-head warp, its fp32 partial rows, a fence, then the rows' lse words --
-  // the arrival flags: the workspace is zero between launches and a published lse is never +0.0 (stored as -0.0).
-  // A merging warp owns HB q heads (lane = 4 output dims): it polls the lse words of all contributors (lane c:
-  // contributor c), folds in whoever has arrived since the last look (their partial rows are fetched together: one
-  // L2 round trip per look) and zeroes their flags again.  When the row's last contributor arrives, one partial is
-  // left to fold: the launch ends ~2 us after its slowest CTA instead of a ticket round trip plus a merge of
-  // everything (~6 us at cfg5).  Nobody waits before its own work is published and all CTAs are co-resident
-  // (grid <= SMs, one CTA per SM), so the polling cannot dead-lock.
+  // Merge of a row that several CTAs contributed to (run by all consumer warps of the CTA whose arrival
+  // completed the row's ticket).
   auto merge_row = [&](int mr) {
     const int row_begin = sPrefix[mr], row_end = sPrefix[mr + 1];
     const int b = mr / HG, hg = mr - b * HG;
     const int c_first = cut.owner(row_begin, mr), c_last = cut.owner(row_end - 1, mr);
     const unsigned long long t_cmb = dbg ? global_timer_ns() : 0;
+    // One warp per group of q heads, lane = 4 output dims.  Fast path (the usual case: a row has a handful of
+    // contributors): lane c fetches the lse of contributor c AND every lane fetches its 4 dims of every
+    // contributor's partial at once, so the merge costs ONE L2 round trip; the weights are applied when both
+    // have arrived.  HB heads x NCMAX contributors x 4 floats are in flight per lane (96 registers: the
+    // accumulators of the main loop are dead by now).
+    __threadfence();
     const int nc = c_last - c_first + 1;
+    auto fast = [&](auto hb_tag, auto nc_tag) {
+      constexpr int HBF = decltype(hb_tag)::value, NCMAX = decltype(nc_tag)::value;
+      int ps = 0;
+      if (lane < nc) ps = 2 * (c_first + lane) + (cut.begin_of(c_first + lane) >= row_begin ? 0 : 1);
+      for (int h0 = warp * HBF; h0 < heads_row; h0 += kConsumerWarps * HBF) {
+        float lse[HBF];
+        float4 v[NCMAX][HBF];
+#pragma unroll
+        for (int x = 0; x < HBF; ++x)
+          lse[x] = (lane < nc && h0 + x < heads_row) ? __ldcg(p.ws_lse + (int64_t)ps * heads_row + h0 + x) : -INFINITY;
+#pragma unroll
+        for (int kc2 = 0; kc2 < NCMAX; ++kc2) {
+          const int psk = __shfl_sync(0xffffffffu, ps, kc2);
+          const float4* src = reinterpret_cast<const float4*>(p.ws_o + ((int64_t)psk * heads_row + h0) * kHeadDim) + lane;
+#pragma unroll
+          for (int x = 0; x < HBF; ++x)
+            v[kc2][x] = (kc2 < nc && h0 + x < heads_row) ? __ldcg(src + x * (kHeadDim / 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int x = 0; x < HBF; ++x) {
+          float cm = lse[x];
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+          const float wgt = lse[x] == -INFINITY ? 0.f : __expf(lse[x] - cm);
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+          float wsum = 0.f;
+#pragma unroll
+          for (int kc2 = 0; kc2 < NCMAX; ++kc2) {
+            const float wk = __shfl_sync(0xffffffffu, wgt, kc2);
+            if (kc2 < nc && wk != 0.f) {
+              acc.x += wk * v[kc2][x].x, acc.y += wk * v[kc2][x].y, acc.z += wk * v[kc2][x].z, acc.w += wk * v[kc2][x].w;
+              wsum += wk;
+            }
+          }
+          if (h0 + x < heads_row) {
+            const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
+            uint2 o2;
+            o2.x = pack_bf16x2(acc.x * inv, acc.y * inv);
+            o2.y = pack_bf16x2(acc.z * inv, acc.w * inv);
+            __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) + (int64_t)b * p.out_stride_b +
+                                  (int64_t)(hg * heads_row + h0 + x) * kHeadDim;
+            *reinterpret_cast<uint2*>(orow + lane * 4) = o2;
+            if (push) {
+              const int64_t off = (int64_t)b * p.push.stride_b +
+                                  ((int64_t)p.push.rank * p.hq + hg * heads_row + h0 + x) * kHeadDim + lane * 4;
+              for (int r = 0; r < p.push.world; ++r) *reinterpret_cast<uint2*>(p.push.out[r] + off) = o2;
+            }
+          }
+        }
+      }
+    };
+    bool merged = true;
+    if (heads_row > 16 && nc <= 6) fast(std::integral_constant<int, 4>(), std::integral_constant<int, 6>());
+    else if (heads_row > 8 && heads_row <= 16 && nc <= 12) fast(std::integral_constant<int, 2>(), std::integral_constant<int, 12>());
+    else if (heads_row <= 8 && nc <= 24) fast(std::integral_constant<int, 1>(), std::integral_constant<int, 24>());
+    else merged = false;
+    // General path (any number of contributors): the lse first, then the partials that carry weight.
     constexpr int HB = 4;  // heads a warp merges at once: their loads are all independent
-    for (int h0 = warp * HB; h0 < heads_row; h0 += kConsumerWarps * HB) {
+    for (int h0 = merged ? heads_row : warp * HB; h0 < heads_row; h0 += kConsumerWarps * HB) {
       float m[HB], wsum[HB];
       float4 acc[HB];
 #pragma unroll
       for (int x = 0; x < HB; ++x) m[x] = -INFINITY, wsum[x] = 0.f, acc[x] = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int c0 = 0; c0 < nc; c0 += 32) {
         const int c = c_first + c0 + lane;
-        const bool mine = c <= c_last;
-        const int ps = mine ? 2 * c + (cut.begin_of(c) >= row_begin ? 0 : 1) : 0;
-        volatile float* lse_p = p.ws_lse + (int64_t)ps * heads_row + h0;
-        uint32_t pending = __ballot_sync(0xffffffffu, mine);
-        SpinGuard guard;
-        while (pending) {
-          float lse[HB];
-          bool here = mine && ((pending >> lane) & 1u);
+        int ps = 0;
+        float lse[HB], wgt[HB];
+        if (c <= c_last) ps = 2 * c + (cut.begin_of(c) >= row_begin ? 0 : 1);
+#pragma unroll
+        for (int x = 0; x < HB; ++x)
+          lse[x] = (c <= c_last && h0 + x < heads_row)
+                       ? __ldcg(p.ws_lse + (int64_t)ps * heads_row + h0 + x)
+                       : -INFINITY;
+#pragma unroll
+        for (int x = 0; x < HB; ++x) {
+          float cm = lse[x];
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+          const float mnew = fmaxf(m[x], cm);
+          const float rescale = m[x] == -INFINITY ? 0.f : __expf(m[x] - mnew);
+          acc[x].x *= rescale, acc[x].y *= rescale, acc[x].z *= rescale, acc[x].w *= rescale;
+          wsum[x] *= rescale;
+          wgt[x] = lse[x] == -INFINITY ? 0.f : __expf(lse[x] - mnew);
+          m[x] = mnew;
+        }
+        const int cnt = min(32, nc - c0);
+#pragma unroll 4
+        for (int kc2 = 0; kc2 < cnt; ++kc2) {
+          const int psk = __shfl_sync(0xffffffffu, ps, kc2);
+          const float4* src = reinterpret_cast<const float4*>(
+                                  p.ws_o + ((int64_t)psk * heads_row + h0) * kHeadDim) + lane;
 #pragma unroll
           for (int x = 0; x < HB; ++x) {
-            lse[x] = (here && h0 + x < heads_row) ? lse_p[x] : -INFINITY;
-            if (h0 + x < heads_row && __float_as_uint(lse[x]) == 0u) here = false;
-          }
-          const uint32_t fresh = __ballot_sync(0xffffffffu, here);
-          if (fresh == 0u) {
-            __nanosleep(40);
-            guard.tick(kSpinLimitNs);
-            continue;
-          }
-          __threadfence();  // the flags were seen: the partial rows written before them are visible now
-          float wgt[HB];
-#pragma unroll
-          for (int x = 0; x < HB; ++x) {
-            float cm = here ? lse[x] : -INFINITY;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
-            const float mnew = fmaxf(m[x], cm);
-            const float rescale = m[x] == -INFINITY ? 0.f : __expf(m[x] - mnew);
-            acc[x].x *= rescale, acc[x].y *= rescale, acc[x].z *= rescale, acc[x].w *= rescale;
-            wsum[x] *= rescale;
-            wgt[x] = (!here || lse[x] == -INFINITY) ? 0.f : __expf(lse[x] - mnew);
-            m[x] = mnew;
-          }
-          for (uint32_t todo = fresh; todo;) {
-            // up to four arrivals per pass: their 4 x HB row loads are all in flight together
-            int kc[4];
-            float4 v[4][HB];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              kc[u] = todo ? __ffs(todo) - 1 : -1;
-              if (todo) todo &= todo - 1;
+            const float wk = __shfl_sync(0xffffffffu, wgt[x], kc2);
+            if (wk != 0.f) {
+              const float4 v = __ldcg(src + x * (kHeadDim / 4));
+              acc[x].x += wk * v.x, acc[x].y += wk * v.y, acc[x].z += wk * v.z, acc[x].w += wk * v.w;
+              wsum[x] += wk;
             }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const int psk = __shfl_sync(0xffffffffu, ps, kc[u] < 0 ? 0 : kc[u]);
-              const float4* src = reinterpret_cast<const float4*>(p.ws_o + ((int64_t)psk * heads_row + h0) * kHeadDim) + lane;
-#pragma unroll
-              for (int x = 0; x < HB; ++x)
-                v[u][x] = (kc[u] >= 0 && h0 + x < heads_row) ? __ldcg(src + x * (kHeadDim / 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-#pragma unroll
-              for (int x = 0; x < HB; ++x) {
-                const float wk = __shfl_sync(0xffffffffu, wgt[x], kc[u] < 0 ? 0 : kc[u]);
-                if (kc[u] >= 0 && wk != 0.f) {
-                  acc[x].x += wk * v[u][x].x, acc[x].y += wk * v[u][x].y, acc[x].z += wk * v[u][x].z, acc[x].w += wk * v[u][x].w;
-                  wsum[x] += wk;
-                }
-              }
           }
-          // the flags go back to zero for the next launch / graph replay (only this warp reads these words)
-          if (here)
-#pragma unroll
-            for (int x = 0; x < HB; ++x)
-              if (h0 + x < heads_row) lse_p[x] = 0.f;
-          pending &= ~fresh;
         }
       }
 #pragma unroll
@@ -490,7 +514,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
           uint2 o2;
           o2.x = pack_bf16x2(acc[x].x * inv, acc[x].y * inv);
           o2.y = pack_bf16x2(acc[x].z * inv, acc[x].w * inv);
-          __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) + (int64_t)b * p.out_stride_b +
+          __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
+                                (int64_t)b * p.out_stride_b +
                                 (int64_t)(hg * heads_row + h0 + x) * kHeadDim;
           *reinterpret_cast<uint2*>(orow + lane * 4) = o2;
           if (push) {
@@ -504,6 +529,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
     if (dbg && tid == 0) dbg[5] += global_timer_ns() - t_cmb;
   };
 
+  int defer_row = -1, defer_total = 0, defer_old = -1;
   int r = r_first;
   int i = 0;  // index of the next unit inside this CTA's range
   while (u0 + i < u1) {
@@ -727,28 +753,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
                 orow[dt * 16 + g] = o_acc[nt][dt][e] * inv;
                 orow[dt * 16 + g + 8] = o_acc[nt][dt][2 + e] * inv;
               }
+              if (g == 0)
+                p.ws_lse[(int64_t)pslot * heads_row + head_local] =
+                    l > 0.f ? m_run[nt][e] * kLn2 + __logf(l) : -INFINITY;
             }
           }
         }
-      if (!complete) {
-        // the lse words are the arrival flags of the partial rows (see merge_row): they follow a fence, and a
-        // published word is never +0.0 (the workspace's "not yet" value)
-        __threadfence();
-        __syncwarp();
-        if (g == 0)
-#pragma unroll
-          for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              const int hi = nt * 8 + 2 * t + e;
-              if (hi < gsz) {
-                const float l = l_run[nt][e];
-                const float lse = l > 0.f ? m_run[nt][e] * kLn2 + __logf(l) : -INFINITY;
-                *reinterpret_cast<volatile float*>(p.ws_lse + (int64_t)pslot * heads_row + h_local * gsz + hi) =
-                    lse == 0.f ? -0.f : lse;
-              }
-            }
-      }
     }
     if (complete) {
       consumer_sync();
@@ -764,11 +774,48 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
         }
       }
     }
-    // the row's first contributor merges it (this is then the CTA's last segment)
-    if (!complete && seg_begin == row_begin) merge_row(r);
+    if (!complete) {
+      // Arrival ticket of the row, counted in KV-head warps (HPC per contributing CTA): whoever completes it merges
+      // every partial.  A segment that is not the CTA's last one (the tail of a row that began in another CTA)
+      // arrives early and is practically never the last: its warps fire their arrival and go on with the next
+      // row at once; the returned count is only looked at when the CTA is done (defer_*).  The CTA's last segment
+      // arrives as a whole and merges right away if it completes the row.
+      const int c_first = cut.owner(row_begin, r), c_last = cut.owner(row_end - 1, r);
+      const int arrivals = (c_last - c_first + 1) * HPC;
+      if (seg_end != u1) {
+        if (tl == 0) {
+          __threadfence();
+          __syncwarp();
+          if (lane == 0) defer_old = atomicAdd(&p.tickets[r], 1);
+        }
+        defer_row = r;
+        defer_total = arrivals;
+      } else {
+        __threadfence();
+        consumer_sync();
+        if (tid == 0) {
+          const int ticket = atomicAdd(&p.tickets[r], HPC);
+          s_flag = (ticket + HPC == arrivals);
+          if (s_flag) p.tickets[r] = 0;  // scratch stays zeroed for the next launch / replay
+        }
+        consumer_sync();
+        if (s_flag) merge_row(r);
+      }
+    }
     consumer_sync();  // sQ / sMerge / s_flag are reused by the next segment
     if (dbg && tid == 0) dbg[6] += global_timer_ns() - t_epi;
     i += n;
+  }
+  if (defer_row >= 0) {
+    if (tl == 0 && lane == 0 && defer_old == defer_total - 1) {
+      s_defer = 1;
+      p.tickets[defer_row] = 0;
+    }
+    consumer_sync();
+    if (s_defer) {
+      merge_row(defer_row);
+      consumer_sync();
+    }
   }
   if (dbg && tid == 0) dbg[3] = global_timer_ns();
   if (push && tid == 0) push_finish(p.push);  // the loop's last consumer_sync ordered the CTA's peer stores before this

@@ -301,9 +301,9 @@ def set_max_ctas(n: int) -> int:
 
 # ----------------------------------------------------------------------------- attention
 def attn_workspace(batch: int, num_q_heads: int, num_kv_heads: int, device, max_ctas: int | None = None) -> torch.Tensor:
-    """Zeroed scratch of svb200_workspace_bytes (per-SM fp32 partials whose lse words double as arrival flags).
+    """Zeroed scratch of svb200_workspace_bytes (arrival tickets + per-SM fp32 partials).
 
-    Allocate it once per (batch, heads) shape and stream; launches leave the flag words zeroed again.  ``max_ctas`` sizes it
+    Allocate it once per (batch, heads) shape; kernels leave the ticket part zeroed.  ``max_ctas`` sizes it
     for fewer CTAs than SMs (the launch then uses at most that many; tests use it to vary the decomposition)."""
     lib = _native.load()
     nbytes = int(lib.svb200_workspace_bytes(int(batch), int(num_q_heads), int(num_kv_heads)))
