@@ -90,7 +90,14 @@ struct AttnCut {
   const int* prefix;  // exclusive prefix of the rows' unit counts, R + 1 entries
   int R, pen;
   int64_t U, UV, G;   // units, virtual length, ranges
+  bool small;         // UV * G fits 31 bits: 32-bit divisions (a 64-bit one is ~100 instructions on the start-up path)
   __device__ __forceinline__ int64_t vbegin(int r) const { return prefix[r] + (int64_t)pen * r; }
+  __device__ __forceinline__ int64_t vstart(int c) const {  // first virtual position of CTA c
+    return small ? (int64_t)((uint32_t)UV * (uint32_t)c / (uint32_t)G) : UV * c / G;
+  }
+  __device__ __forceinline__ int unit_at(int r, int64_t v) const {
+    return prefix[r] + (int)min(v - vbegin(r), (int64_t)(prefix[r + 1] - prefix[r]));
+  }
   __device__ __forceinline__ int row_of_virtual(int64_t v) const {  // largest r with vbegin(r) <= v
     int lo = 0, hi = R;
     while (hi - lo > 1) {
@@ -99,13 +106,25 @@ struct AttnCut {
     }
     return lo;
   }
-  __device__ __forceinline__ int to_unit(int64_t v) const {
-    const int r = row_of_virtual(v);
-    return prefix[r] + (int)min(v - vbegin(r), (int64_t)(prefix[r + 1] - prefix[r]));
+  __device__ __forceinline__ int to_unit(int64_t v) const { return unit_at(row_of_virtual(v), v); }
+  __device__ __forceinline__ int begin_of(int c) const { return to_unit(vstart(c)); }  // first unit of CTA c
+  // [u0, u1) of CTA c and the row u0 lies in: the two searches run in one loop (two independent chains)
+  __device__ __forceinline__ void range_of(int c, int& u0, int& u1, int& row0) const {
+    const int64_t v0 = vstart(c), v1 = vstart(c + 1);
+    int lo0 = 0, hi0 = R, lo1 = 0, hi1 = R;
+    while (hi0 - lo0 > 1 || hi1 - lo1 > 1) {
+      const int m0 = (lo0 + hi0) >> 1, m1 = (lo1 + hi1) >> 1;
+      if (hi0 - lo0 > 1) { if (vbegin(m0) <= v0) lo0 = m0; else hi0 = m0; }
+      if (hi1 - lo1 > 1) { if (vbegin(m1) <= v1) lo1 = m1; else hi1 = m1; }
+    }
+    u0 = unit_at(lo0, v0);
+    u1 = c + 1 == G ? (int)U : unit_at(lo1, v1);
+    row0 = lo0;
   }
-  __device__ __forceinline__ int begin_of(int c) const { return to_unit(UV * c / G); }  // first unit of CTA c
   __device__ __forceinline__ int owner(int u, int r) const {  // CTA that owns unit u of row r
-    return unit_owner(u + (int64_t)pen * r, UV, G);
+    const int64_t v = u + (int64_t)pen * r;
+    if (small) return (int)((((uint32_t)v + 1u) * (uint32_t)G + (uint32_t)UV - 1u) / (uint32_t)UV) - 1;
+    return unit_owner(v, UV, G);
   }
 };
 
@@ -258,22 +277,15 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
   cut.prefix = sPrefix, cut.R = R, cut.U = U, cut.G = Gn;
   cut.pen = Gn > 0 ? (int)min((int64_t)p.split_pen, U / Gn / 2) : 0;
   cut.UV = U + (int64_t)cut.pen * (R - 1);
-  const int u0 = (int64_t)blockIdx.x < Gn ? cut.begin_of(blockIdx.x) : 0;
-  const int u1 = (int64_t)blockIdx.x < Gn ? ((int64_t)blockIdx.x + 1 == Gn ? (int)U : cut.begin_of(blockIdx.x + 1)) : 0;
+  cut.small = (cut.UV + 1) * (Gn + 1) < (int64_t)1 << 31;
+  int u0 = 0, u1 = 0, r_first = 0;
+  if ((int64_t)blockIdx.x < Gn) cut.range_of(blockIdx.x, u0, u1, r_first);
   if (u0 >= u1) {
     if (push && tid == 0) push_finish(p.push);
     return;
   }
-  // first row of the range: largest r with prefix[r] <= u0 and a non-empty row
-  int r_first;
-  {
-    int lo = 0, hi = R;  // invariant: prefix[lo] <= u0 < prefix[hi]
-    while (hi - lo > 1) {
-      const int mid = (lo + hi) >> 1;
-      if (sPrefix[mid] <= u0) lo = mid; else hi = mid;
-    }
-    r_first = lo;
-  }
+  // first row of the range: the non-empty row that holds u0 (u0 may sit in the padding before the next row)
+  while (sPrefix[r_first + 1] <= u0) ++r_first;
 
   const __nv_bfloat16* kc = reinterpret_cast<const __nv_bfloat16*>(p.k_cache);
   const __nv_bfloat16* vc = reinterpret_cast<const __nv_bfloat16*>(p.v_cache);
