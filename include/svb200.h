@@ -200,6 +200,29 @@ int svb200_quest_score_select_pack(
     int32_t* selected_pages, int32_t* tickets, void* stream);
 
 /*
+ * No counterpart in the reference: added for callers that cannot allocate
+ * device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * svb200_quest_score_select_pack with the scheduler scratch (`tickets`) inside the library: a file-scope
+ * `static __device__` array of 1 + 2 * SVB200_STATIC_MAX_BATCH int32 (~8 KB, resident on every GPU that loads
+ * the library until the process exits), whose device address the library takes once per device with
+ * cudaGetSymbolAddress.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine);
+ * it clears the part of the array it uses on `stream`, then launches the same kernel.  Inputs, outputs and results
+ * are those of svb200_quest_score_select_pack.
+ *   batch > SVB200_STATIC_MAX_BATCH -> SVB200_EINVAL with a message (use the caller-owned-scratch entry point).
+ * Every call on a device shares the one array: calls that overlap on the GPU (different streams, or graphs replayed
+ * concurrently) race on it; serialise them or use svb200_quest_score_select_pack with one scratch per stream.
+ */
+#define SVB200_STATIC_MAX_BATCH 1024
+int svb200_quest_score_select_pack_static(
+    const void* q, int64_t q_stride_b, const void* bounds_layer, int64_t num_chunks,
+    const int32_t* unit_table, int64_t unit_table_stride,
+    const int32_t* page_table, int64_t page_table_stride, const int32_t* req_rows,
+    const int32_t* context_lens, void* scores, int64_t score_stride, int32_t batch,
+    int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols, int32_t prev_budget,
+    int32_t* packed_slots, int64_t out_stride, int32_t* sparse_lens,
+    int32_t* selected_pages, void* stream);
+
+/*
  * svb200_quest_score_select_pack that also performs the decode step's KV store
  * (svb200_store_kv_minmax for batch tokens, token b = batch row b) inside the same
  * launch: warps that wait for the first row to be scored write the rows.  Legal because

@@ -50,6 +50,9 @@ _SIGNATURES = {
     "svb200_quest_score_select_pack": (
         c_int32, [_P, c_int64, _P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32,
                   c_int32, c_int32, c_int32, _P, c_int64, _P, _P, _P, _P]),
+    "svb200_quest_score_select_pack_static": (  # the one above without `tickets`: the scratch lives in the library
+        c_int32, [_P, c_int64, _P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32,
+                  c_int32, c_int32, c_int32, _P, c_int64, _P, _P, _P]),
     "svb200_quest_store_score_select_pack": (
         c_int32, [_P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, _P,
                   _P, c_int64, _P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32,

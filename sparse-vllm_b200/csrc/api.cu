@@ -250,6 +250,62 @@ int svb200_quest_score_select_pack(const void* q, int64_t q_stride_b, const void
                                         tickets, nullptr, (cudaStream_t)stream);
 }
 
+// ---- svb200_quest_score_select_pack_static: the scheduler scratch lives in the library (no allocation anywhere)
+// The array's name is a host-side stand-in in host code, never a device address: the address a kernel may use is
+// taken once per device with cudaGetSymbolAddress (with that device current) and cached.
+static __device__ __align__(256) int32_t g_static_sched_scratch[1 + 2 * SVB200_STATIC_MAX_BATCH + 15];
+constexpr int kStaticMaxDevices = 64;
+static int32_t* g_static_scratch_ptr[kStaticMaxDevices] = {nullptr};
+
+static int static_sched_scratch(const char* who, int32_t** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_error("cudaGetDevice", e);
+  if (dev < 0 || dev >= kStaticMaxDevices) {
+    set_error("%s: device ordinal %d beyond the %d this library keeps static scratch addresses for", who, dev, kStaticMaxDevices);
+    return SVB200_EUNSUPPORTED;
+  }
+  // (two threads racing here both obtain the same address: the store is idempotent)
+  if (g_static_scratch_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_static_sched_scratch);
+    if (e != cudaSuccess) return cuda_error("cudaGetSymbolAddress(static scheduler scratch)", e);
+    if (ptr == nullptr) {
+      set_error("%s: cudaGetSymbolAddress returned a null device address", who);
+      return SVB200_EINVAL;
+    }
+    g_static_scratch_ptr[dev] = static_cast<int32_t*>(ptr);
+  }
+  *out = g_static_scratch_ptr[dev];
+  return 0;
+}
+
+int svb200_quest_score_select_pack_static(const void* q, int64_t q_stride_b, const void* bounds_layer,
+                                          int64_t num_chunks, const int32_t* unit_table, int64_t unit_table_stride,
+                                          const int32_t* page_table, int64_t page_table_stride,
+                                          const int32_t* req_rows, const int32_t* context_lens,
+                                          void* scores, int64_t score_stride, int32_t batch,
+                                          int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols,
+                                          int32_t prev_budget, int32_t* packed_slots, int64_t out_stride,
+                                          int32_t* sparse_lens, int32_t* selected_pages, void* stream) {
+  const char* who = "quest_score_select_pack_static";
+  SV_REQUIRE(batch >= 0, "%s: batch=%d < 0", who, batch);
+  if (batch == 0) return 0;
+  SV_REQUIRE(batch <= SVB200_STATIC_MAX_BATCH,
+             "%s: batch=%d exceeds SVB200_STATIC_MAX_BATCH=%d rows the library's static scratch holds "
+             "(use svb200_quest_score_select_pack with a caller-owned scratch)", who, batch, SVB200_STATIC_MAX_BATCH);
+  int32_t* scratch = nullptr;
+  if (int rc = static_sched_scratch(who, &scratch)) return rc;
+  // the array keeps what the last call left (a launch leaves it zeroed, an aborted one may not): clear what this
+  // call uses, on the caller's stream (a memset node under graph capture; nothing is allocated)
+  const cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(int32_t) * (size_t)svb200_sched_scratch_ints(batch), (cudaStream_t)stream);
+  if (e != cudaSuccess) return cuda_error("quest_score_select_pack_static: clearing the static scratch", e);
+  return svb200_quest_score_select_pack(q, q_stride_b, bounds_layer, num_chunks, unit_table, unit_table_stride,
+                                        page_table, page_table_stride, req_rows, context_lens, scores, score_stride,
+                                        batch, num_q_heads, num_kv_heads, n_cols, prev_budget, packed_slots,
+                                        out_stride, sparse_lens, selected_pages, scratch, stream);
+}
+
 int svb200_quest_store_score_select_pack(const void* key, int64_t k_stride, const void* value, int64_t v_stride,
                                          void* k_cache, void* v_cache, const int32_t* slot_mapping,
                                          int64_t num_slots, int32_t refresh_bounds, const int32_t* page_rec,

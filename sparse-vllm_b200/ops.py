@@ -229,6 +229,34 @@ class DecodeStore:
         self.slot_mapping, self.refresh_bounds, self.page_rec = slot_mapping, bool(refresh_bounds), page_rec
 
 
+STATIC_MAX_BATCH = 1024  # SVB200_STATIC_MAX_BATCH (include/svb200.h)
+
+
+def quest_score_select_pack_static(q: torch.Tensor, bounds_layer: torch.Tensor, unit_table: torch.Tensor,
+                                   page_table: torch.Tensor, req_rows: torch.Tensor, context_lens: torch.Tensor,
+                                   n_cols: int, num_kv_heads: int, prev_budget: int, scores: torch.Tensor,
+                                   packed_slots: torch.Tensor, sparse_lens: torch.Tensor,
+                                   selected_pages: torch.Tensor | None = None) -> None:
+    """svb200_quest_score_select_pack_static: `quest_score_select_pack` for callers that cannot allocate: the
+    scheduler scratch is a static device array inside the library (batch <= STATIC_MAX_BATCH; calls that overlap
+    on the GPU race on it).  No counterpart in the reference.  This wrapper allocates nothing either."""
+    bsz, hq, qs = _q(q, "q")
+    num_chunks = _bounds_layer(bounds_layer, num_kv_heads)
+    require_cuda(scores, "scores", torch.bfloat16)
+    for t, n in ((unit_table, "unit_table"), (page_table, "page_table"), (req_rows, "req_rows"),
+                 (context_lens, "context_lens"), (packed_slots, "packed_slots"), (sparse_lens, "sparse_lens")):
+        _i32(t, n)
+    if selected_pages is not None:
+        _i32(selected_pages, "selected_pages")
+    lib = _native.load()
+    check(lib.svb200_quest_score_select_pack_static(
+        ptr(q), qs, ptr(bounds_layer), num_chunks, ptr(unit_table), _rows_stride(unit_table, "unit_table"),
+        ptr(page_table), _rows_stride(page_table, "page_table"), ptr(req_rows), ptr(context_lens), ptr(scores),
+        _rows_stride(scores, "scores"), bsz, hq, int(num_kv_heads), int(n_cols), int(prev_budget), ptr(packed_slots),
+        _rows_stride(packed_slots, "packed_slots"), ptr(sparse_lens), ptr(selected_pages),
+        current_stream_ptr(q.device)), "svb200_quest_score_select_pack_static")
+
+
 def quest_score_select_pack(q: torch.Tensor, bounds_layer: torch.Tensor, unit_table: torch.Tensor,
                             page_table: torch.Tensor, req_rows: torch.Tensor, context_lens: torch.Tensor,
                             n_cols: int, num_kv_heads: int,
