@@ -842,6 +842,7 @@ static int launch_variant(const AttnParams& p_in, cudaStream_t stream) {
   const int fixed = attn_smem_layout<HPC, NT>(0, gsz, rows, p.batch).total + 256;  // + static smem
   int stages = (kMaxSmem - fixed) / (G::STAGE_BYTES + 20);
   if (stages > 24) stages = 24;
+  if (tuning(kTuneAttnStages) > 0 && stages > tuning(kTuneAttnStages)) stages = tuning(kTuneAttnStages);
   // Unit j is consumed by the warps tl = j % TL; with TL | stages a stage is always drained by the
   // same warps, so the phase a warp waits for is never more than one ahead of the barrier (parity
   // waits cannot tell a phase from the one two before it).

@@ -19,6 +19,7 @@ enum {
   kTuneScoreGroups = 0, kTuneAttnMinKB = 1, kTuneMinBatch = 2, kTuneShareDiv = 3, kTuneChunkUnits = 4,
   kTuneNoMath = 5, kTuneScoreQ = 6, kTunePdl = 7, kTuneAttnGranule = 8, kTuneAttnHpc = 9,
   kTuneAttnSplitPen = 10,  // attention: units a CTA is charged for a row boundary inside its range, + 1 (0: auto, 1: none)
+  kTuneAttnStages = 11,    // attention: cap of the ring's stages (experiments; 0: as many as fit)
   kTuneCount = 16
 };
 int tuning(int which);
