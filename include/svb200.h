@@ -203,7 +203,7 @@ int svb200_quest_score_select_pack(
  * No counterpart in the reference: added for callers that cannot allocate
  * device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
  * svb200_quest_score_select_pack with the scheduler scratch (`tickets`) inside the library: a file-scope
- * `static __device__` array of 1 + 2 * SVB200_STATIC_MAX_BATCH int32 (~8 KB, resident on every GPU that loads
+ * `static __device__` array of 1 + 3 * SVB200_STATIC_MAX_BATCH int32 (~12 KB, resident on every GPU that loads
  * the library until the process exits), whose device address the library takes once per device with
  * cudaGetSymbolAddress.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine);
  * it clears the part of the array it uses on `stream`, then launches the same kernel.  Inputs, outputs and results
@@ -422,6 +422,33 @@ int svb200_sparse_decode_attn_tp(const void* q, int64_t q_stride_b, const void* 
                                  int64_t workspace_bytes, float sm_scale,
                                  const svb200_comm_t* comm, int64_t gather_offset_bytes,
                                  int64_t gather_stride_b, void* stream);
+
+/*
+ * One launch per sparse decode layer: svb200_quest_store_score_select_pack (key == NULL: no store) followed, inside
+ * the same launch, by svb200_sparse_decode_attn(_tp) over the slots it packed.  Replaces, for a long-text batch,
+ * save_rope_kv_if_needed + _build_decode_view_static (engine/cache_manager/quest.py:1773-1913) + run_decode
+ * (layers/attention_backend.py:217-349) of one layer.  A CTA whose scoring work is done sets the attention up while
+ * the last rows are still being selected, and reads a row's packed slots as soon as that row's selection is
+ * published: the launch gap, the attention's set-up and its ramp overlap the selection tail.
+ * Results are those of the two launches (same kernels' code).  Needs n_cols > 0 and at most 8 q heads per KV head
+ * (else SVB200_EUNSUPPORTED: use the separate entry points).
+ *   sched_scratch svb200_sched_scratch_ints(batch) zero-initialised int32 (left zeroed)
+ *   workspace     as for svb200_sparse_decode_attn
+ *   comm          NULL, or the peers of the tensor-parallel push epilogue (svb200_sparse_decode_attn_tp)
+ */
+int svb200_quest_decode_layer(
+    const void* key, int64_t k_stride, const void* value, int64_t v_stride, const int32_t* slot_mapping,
+    int32_t refresh_bounds, const int32_t* page_rec, void* k_cache, void* v_cache, int64_t num_slots,
+    const void* q, int64_t q_stride_b, void* bounds_layer, int64_t num_chunks,
+    const int32_t* unit_table, int64_t unit_table_stride,
+    const int32_t* page_table, int64_t page_table_stride, const int32_t* req_rows,
+    const int32_t* context_lens, void* scores, int64_t score_stride, int32_t batch,
+    int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols, int32_t prev_budget,
+    int32_t* packed_slots, int64_t out_stride, int32_t* sparse_lens, int32_t* selected_pages,
+    int32_t* sched_scratch, void* out, int64_t out_stride_b, void* workspace, int64_t workspace_bytes,
+    float sm_scale, const svb200_comm_t* comm, int64_t gather_offset_bytes, int64_t gather_stride_b,
+    void* stream);
+
 
 /*
  * One-shot SUM all-reduce of n_elems bf16 (a multiple of 8): rank r's input is

@@ -57,6 +57,11 @@ _SIGNATURES = {
         c_int32, [_P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, _P,
                   _P, c_int64, _P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32,
                   c_int32, c_int32, c_int32, _P, c_int64, _P, _P, _P, _P]),
+    "svb200_quest_decode_layer": (
+        c_int32, [_P, c_int64, _P, c_int64, _P, c_int32, _P, _P, _P, c_int64,
+                  _P, c_int64, _P, c_int64, _P, c_int64, _P, c_int64, _P, _P, _P, c_int64, c_int32, c_int32,
+                  c_int32, c_int32, c_int32, _P, c_int64, _P, _P, _P,
+                  _P, c_int64, _P, c_int64, c_float, POINTER(Comm), c_int64, c_int64, _P]),
     "svb200_sparse_decode_attn": (c_int32, [*_ATTN_ARGS, _P]),
     "svb200_sparse_decode_attn_tp": (c_int32, [*_ATTN_ARGS, POINTER(Comm), c_int64, c_int64, _P]),
     "svb200_allreduce_sum_bf16": (c_int32, [POINTER(Comm), c_int64, c_int64, _P, _P]),

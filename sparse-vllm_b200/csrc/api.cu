@@ -99,7 +99,7 @@ int svb200_set_tuning(int32_t which, int32_t value) {
   g_tuning[which] = value;
   return prev;
 }
-int64_t svb200_sched_scratch_ints(int32_t rows) { return rows < 0 ? -1 : 1 + 2 * (int64_t)rows; }
+int64_t svb200_sched_scratch_ints(int32_t rows) { return rows < 0 ? -1 : 1 + 3 * (int64_t)rows; }
 
 static int64_t ws_ticket_bytes(int64_t batch, int64_t hkv) {
   return ((batch * hkv * (int64_t)sizeof(int32_t) + 255) / 256) * 256;
@@ -253,7 +253,7 @@ int svb200_quest_score_select_pack(const void* q, int64_t q_stride_b, const void
 // ---- svb200_quest_score_select_pack_static: the scheduler scratch lives in the library (no allocation anywhere)
 // The array's name is a host-side stand-in in host code, never a device address: the address a kernel may use is
 // taken once per device with cudaGetSymbolAddress (with that device current) and cached.
-static __device__ __align__(256) int32_t g_static_sched_scratch[1 + 2 * SVB200_STATIC_MAX_BATCH + 15];
+static __device__ __align__(256) int32_t g_static_sched_scratch[1 + 3 * SVB200_STATIC_MAX_BATCH + 15];
 constexpr int kStaticMaxDevices = 64;
 static int32_t* g_static_scratch_ptr[kStaticMaxDevices] = {nullptr};
 
@@ -356,7 +356,7 @@ static int check_comm(const char* who, const svb200_comm_t* comm) {
   return 0;
 }
 
-static int decode_attn_impl(const char* who, const void* q, int64_t q_stride_b, const void* k_cache,
+static int fill_attn_params(AttnParams* p_out, const char* who, const void* q, int64_t q_stride_b, const void* k_cache,
                             const void* v_cache, int64_t num_slots, const int32_t* slot_table,
                             int64_t slot_table_stride, int32_t max_len, const int32_t* req_rows,
                             const int32_t* seq_lens, void* out, int64_t out_stride_b,
@@ -398,6 +398,7 @@ static int decode_attn_impl(const char* who, const void* q, int64_t q_stride_b, 
   p.ws_o = reinterpret_cast<float*>(w + tk + ctas * 2 * num_q_heads * 4 * (int64_t)sizeof(float));
   p.no_math = 0;
   p.granule = 1;
+  p.grid_cap = 0;
   p.push = PushArgs{};
   if (comm != nullptr && comm->world > 1) {
     if (int rc = check_comm(who, comm)) return rc;
@@ -413,7 +414,82 @@ static int decode_attn_impl(const char* who, const void* q, int64_t q_stride_b, 
       p.push.sync[r] = comm->peer_sync[r];
     }
   }
+  *p_out = p;
+  return 0;
+}
+
+static int decode_attn_impl(const char* who, const void* q, int64_t q_stride_b, const void* k_cache,
+                            const void* v_cache, int64_t num_slots, const int32_t* slot_table,
+                            int64_t slot_table_stride, int32_t max_len, const int32_t* req_rows,
+                            const int32_t* seq_lens, void* out, int64_t out_stride_b,
+                            float* attn_score, int64_t score_stride, int32_t batch,
+                            int32_t num_q_heads, int32_t num_kv_heads, int32_t heads_per_cta,
+                            void* workspace, int64_t workspace_bytes, float sm_scale,
+                            const svb200_comm_t* comm, int64_t gather_offset_bytes, int64_t gather_stride_b,
+                            void* stream) {
+  if (batch == 0 && (comm == nullptr || comm->world <= 1)) return 0;
+  AttnParams p;
+  if (int rc = fill_attn_params(&p, who, q, q_stride_b, k_cache, v_cache, num_slots, slot_table, slot_table_stride,
+                                max_len, req_rows, seq_lens, out, out_stride_b, attn_score, score_stride, batch,
+                                num_q_heads, num_kv_heads, heads_per_cta, workspace, workspace_bytes, sm_scale, comm,
+                                gather_offset_bytes, gather_stride_b, stream))
+    return rc;
   return launch_sparse_decode_attn(p, heads_per_cta, (cudaStream_t)stream);
+}
+
+int svb200_quest_decode_layer(const void* key, int64_t k_stride, const void* value, int64_t v_stride,
+                              const int32_t* slot_mapping, int32_t refresh_bounds, const int32_t* page_rec,
+                              void* k_cache, void* v_cache, int64_t num_slots,
+                              const void* q, int64_t q_stride_b, void* bounds_layer,
+                              int64_t num_chunks, const int32_t* unit_table, int64_t unit_table_stride,
+                              const int32_t* page_table, int64_t page_table_stride,
+                              const int32_t* req_rows, const int32_t* context_lens,
+                              void* scores, int64_t score_stride, int32_t batch,
+                              int32_t num_q_heads, int32_t num_kv_heads, int32_t n_cols,
+                              int32_t prev_budget, int32_t* packed_slots, int64_t out_stride,
+                              int32_t* sparse_lens, int32_t* selected_pages, int32_t* sched_scratch,
+                              void* out, int64_t out_stride_b, void* workspace, int64_t workspace_bytes,
+                              float sm_scale, const svb200_comm_t* comm, int64_t gather_offset_bytes,
+                              int64_t gather_stride_b, void* stream) {
+  const char* who = "quest_decode_layer";
+  SV_REQUIRE(batch > 0, "%s: batch=%d must be positive", who, batch);
+  if (int rc = check_score_args(who, q, q_stride_b, bounds_layer, num_chunks, unit_table,
+                                unit_table_stride, req_rows, context_lens, scores, score_stride,
+                                batch, num_q_heads, num_kv_heads, n_cols))
+    return rc;
+  if (int rc = check_select_args(who, n_cols, prev_budget, packed_slots, out_stride, sparse_lens)) return rc;
+  SV_REQUIRE(sched_scratch != nullptr, "%s: scheduler scratch is null", who);
+  SV_REQUIRE(page_table && page_table_stride >= n_cols + 1, "%s: page table (stride %lld) must cover n_cols+1=%d pages", who,
+             (long long)page_table_stride, n_cols + 1);
+  SV_SUPPORTED(num_q_heads / num_kv_heads <= 8 && n_cols > 0,
+                 "%s: needs n_cols > 0 and at most 8 q heads per KV head; use the separate entry points", who);
+  FusedStore st{};
+  if (key != nullptr) {
+    SV_REQUIRE(!refresh_bounds || page_rec, "%s: refresh_bounds needs page_rec", who);
+    SV_REQUIRE(value && slot_mapping, "%s: null store pointer", who);
+    SV_REQUIRE(aligned16(key) && aligned16(value), "%s: key/value must be 16-byte aligned", who);
+    SV_REQUIRE(k_stride >= (int64_t)num_kv_heads * SVB200_HEAD_DIM && k_stride % 8 == 0 &&
+                   v_stride >= (int64_t)num_kv_heads * SVB200_HEAD_DIM && v_stride % 8 == 0,
+               "%s: bad key/value token strides %lld/%lld", who, (long long)k_stride, (long long)v_stride);
+    SV_REQUIRE(num_slots > 0 && (!refresh_bounds || num_slots % SVB200_PAGE == 0),
+               "%s: num_slots=%lld must be positive (and a multiple of %d with refresh_bounds)", who, (long long)num_slots, SVB200_PAGE);
+    st = FusedStore{key, k_stride, value, v_stride, k_cache, v_cache, slot_mapping, num_slots, refresh_bounds, page_rec};
+  }
+  AttnParams ap;
+  // the attention phase reads the slots this launch packs: row b of packed_slots, (prev_budget + 1) pages at most
+  if (int rc = fill_attn_params(&ap, who, q, q_stride_b, k_cache, v_cache, num_slots, packed_slots, out_stride,
+                                (prev_budget + 1) * SVB200_PAGE, context_lens /* placeholders: the phase takes the */,
+                                context_lens /* identity rows and derives the lengths from context_lens */, out,
+                                out_stride_b, nullptr, 0, batch, num_q_heads, num_kv_heads, 0, workspace,
+                                workspace_bytes, sm_scale, comm, gather_offset_bytes, gather_stride_b, stream))
+    return rc;
+  ap.req_rows = nullptr;
+  ap.seq_lens = nullptr;
+  return launch_quest_decode_layer(q, q_stride_b, bounds_layer, num_chunks, unit_table, unit_table_stride, page_table,
+                                   page_table_stride, req_rows, context_lens, scores, score_stride, batch, num_q_heads,
+                                   num_kv_heads, n_cols, prev_budget, packed_slots, out_stride, sparse_lens,
+                                   selected_pages, sched_scratch, key != nullptr ? &st : nullptr, ap,
+                                   (cudaStream_t)stream);
 }
 
 int svb200_sparse_decode_attn(const void* q, int64_t q_stride_b, const void* k_cache,

@@ -126,10 +126,21 @@ struct AttnParams {
   float sm_scale;
   int no_math;       // experiments: consumers release the stages without the contractions
   int granule;       // copy granules of several token rows where the slots allow it
+  int grid_cap;      // CTAs the attention work is cut into at most (0: the whole grid); set by a fused launcher
   int split_pen;     // units a CTA is charged for a row boundary inside its range (see the kernel's cut); launcher
   PushArgs push;     // tensor-parallel push epilogue (world <= 1: none)
 };
 int attn_auto_heads_per_cta(int hkv);
+// launch configuration of the attention phase of a one-launch layer (quest.cu): ring stages inside `region_bytes` of
+// shared memory, producer warps, CTAs the work is cut into (<= grid, <= the workspace's CTAs), knobs
+int attn_configure_fused(AttnParams& p, int heads_per_cta, int region_bytes, int grid);
+int launch_quest_decode_layer(const void* q, int64_t q_stride_b, const void* bounds, int64_t num_chunks,
+                              const int32_t* unit_table, int64_t ut_stride, const int32_t* page_table,
+                              int64_t pt_stride, const int32_t* req_rows, const int32_t* context_lens,
+                              void* scores, int64_t score_stride, int batch, int hq, int hkv, int n_cols, int k,
+                              int32_t* packed_slots, int64_t out_stride, int32_t* sparse_lens,
+                              int32_t* selected_pages, int32_t* sched, const FusedStore* store,
+                              const AttnParams& attn, cudaStream_t stream);
 int launch_sparse_decode_attn(const AttnParams& p, int heads_per_cta, cudaStream_t stream);
 
 // h2o.cu

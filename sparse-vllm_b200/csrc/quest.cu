@@ -9,6 +9,7 @@
 #include <type_traits>
 
 #include "common.cuh"
+#include "decode_attn.cuh"
 #include "launch.h"
 #include "sched.cuh"
 #include "store_kv.cuh"
@@ -430,6 +431,8 @@ struct ScoreParams {
   // fused store of the step's new K/V rows (store.key == null: none), one token per batch row
   StoreArgs store;
   int store_tokens;
+  // attention phase of a one-launch layer (AHPC > 0)
+  AttnParams attn;
 };
 
 struct ScoreSmemLayout {
@@ -460,10 +463,56 @@ __device__ __forceinline__ uint32_t q_neg(uint32_t x) { return x & q_neg_mask(x)
 
 __device__ __forceinline__ void score_consumer_sync() { group_sync<1, kScoreConsumerThreads>(); }
 
+// Attention phase of a one-launch layer (AHPC > 0 in quest_page_score_kernel, whose header describes it); entered by
+// warps 0-11 of a CTA.  Not inlined: its register allocation is then independent of the scoring code's.
+template <int AHPC>
+__device__ __noinline__ void score_attention_phase(const ScoreParams& p, unsigned char* smem, int* s_flag) {
+  const AttnParams& ap = p.attn;
+  const int B = p.batch;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int* sel_done = p.sched + 1 + 2 * B;
+  auto wait_row = [&](int b) {
+    SpinGuard guard;
+    while (ld_acquire_gpu(sel_done + b) == 0) {
+      __nanosleep(32);
+      guard.tick(kSpinLimitNs);
+    }
+  };
+  // tokens of batch entry b the attention reads: what the selection writes to sparse_lens (known up front)
+  auto len_of = [&](int b) {
+    const int ctx = p.context_lens[b];
+    const int pages = (ctx + kPage - 1) / kPage;
+    return ctx > 0 ? min(p.k * kPage + ctx - (pages - 1) * kPage, ap.max_len) : 0;
+  };
+  if (warp <= kScoreSchedWarp) {
+    // this CTA's scoring is over: its consumers drained every stage, its loader and scheduler are done
+    group_sync<3, kConsumerThreads>();
+    attn_setup<AHPC, 1>(ap, smem, len_of);
+    __threadfence_block();
+    asm volatile("bar.arrive 4, %0;" ::"n"(kConsumerThreads + kProducerWarps * 32) : "memory");
+    group_sync<3, kConsumerThreads>();
+    attn_main<AHPC, 1, false, 3>(ap, smem, wait_row, nullptr);
+    if (tid == 0 && atomicAdd(s_flag, 1) == 1) sched_finish(p.sched, B);
+  } else {
+    asm volatile("bar.sync 4, %0;" ::"n"(kConsumerThreads + kProducerWarps * 32) : "memory");
+    attn_main<AHPC, 1, false, 3>(ap, smem, wait_row, nullptr);
+  }
+}
+
 // QSPLIT: q+ and q- are both staged (when that does not cost a ring stage); else q is staged once and
 // split by sign when a fragment is used.
-template <int NT, bool FUSED_SELECT, bool QSPLIT>
-__global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(ScoreParams p) {
+// AHPC > 0 (with FUSED_SELECT): the launch goes on with the layer's sparse decode attention (decode_attn.cuh, AHPC
+// KV heads per CTA) -- one launch per layer.  A CTA whose scoring work is done re-uses its ring + q area for the
+// attention ring: warps 0-7 (consumers, loader, scheduler) become the attention consumers and do its set-up
+// while the selections of the last rows are still running; warps 8-11 become the attention producers once their
+// own selections are done, and wait, per batch entry, for the entry's selection flag (set with release semantics
+// by the entry's selecting CTA) before they read its packed slots.  What is overlapped: the launch gap, the
+// attention's set-up and its ramp with the selection tail of the scoring launch.  Nobody waits before its own
+// scoring / selecting work is done and all CTAs are co-resident (grid <= SMs, one CTA per SM), so the flags
+// cannot dead-lock.
+template <int NT, bool FUSED_SELECT, bool QSPLIT, int AHPC = 0>
+__global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(const __grid_constant__ ScoreParams p) {
+  static_assert(AHPC == 0 || (FUSED_SELECT && NT == 1), "the attention phase follows a fused selection, group size <= 8");
   extern __shared__ __align__(128) unsigned char smem[];
   const int S = p.stages, hq = p.hq, hkv = p.hkv, B = p.batch;
   const int gsz = hq / hkv;
@@ -531,7 +580,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
     const int depth = min(kSchedQueue, (S / hs + p.chunk_units - 1) / p.chunk_units + kIdDepth + 1);
     sched_run(sched, next_chunk, B, p.groups, p.chunk_units, p.min_batch, p.share_div, depth, units_of_row,
               ReserveNone(), (dbg && blockIdx.x >= (unsigned)B) ? dbg + 15 : nullptr);
-    return;
+    if constexpr (AHPC == 0) return;
   }
 
   if (warp == kScoreLoaderWarp) {
@@ -615,7 +664,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
       }
     }
     if (dbg && lane == 0) dbg[4] = global_timer_ns(), dbg[8] = w_desc, dbg[9] = w_empty;
-    return;
+    if constexpr (AHPC == 0) return;
   }
 
   if (warp > kScoreSchedWarp) {
@@ -672,13 +721,22 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
             p.selected_pages ? p.selected_pages + (int64_t)b * (p.k + 1) : nullptr, *sel_sm,
             dbg ? dbg + 13 : nullptr);
         if (dbg && stid == 0) dbg[5] += global_timer_ns() - ts;
+        if constexpr (AHPC > 0) {
+          // the row's packed slots (and this CTA's earlier K/V store) are published: the select group's last barrier
+          // ordered every thread's writes before this thread's fence
+          if (stid == 0) {
+            __threadfence();
+            st_release_gpu(p.sched + 1 + 2 * B + b, 1);
+          }
+        }
       }
       // the CTA's scratch may be recycled once BOTH its consumers and its select warps are done
       if (stid == 0 && atomicAdd(&s_flag, 1) == 1) sched_finish(p.sched, B);
     }
-    return;
+    if constexpr (AHPC == 0) return;
   }
 
+  if (warp < kScoreConsumerWarps) {
   // ================================================================ consumers
   const int g = lane >> 2, t = lane & 3;
   const uint2* sq2 = reinterpret_cast<const uint2*>(sq);
@@ -844,7 +902,13 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(Scor
   }
   if (tid == 0) {
     if (dbg) dbg[3] = global_timer_ns(), dbg[6] = (unsigned long long)total_units, dbg[11] = c_desc, dbg[12] = c_full;
-    if (!FUSED_SELECT || atomicAdd(&s_flag, 1) == 1) sched_finish(p.sched, B);
+    if constexpr (AHPC == 0)
+      if (!FUSED_SELECT || atomicAdd(&s_flag, 1) == 1) sched_finish(p.sched, B);
+  }
+  }  // consumers
+
+  if constexpr (AHPC > 0) {
+    if (warp <= kScoreSchedWarp + kProducerWarps) score_attention_phase<AHPC>(p, smem, &s_flag);
   }
 }
 
@@ -899,15 +963,15 @@ static int score_stages(const ScoreParams& p, bool fused, int q_copies) {
   return stages < 2 ? 0 : stages;
 }
 
-template <int NT, bool FUSED, bool QSPLIT>
+template <int NT, bool FUSED, bool QSPLIT, int AHPC>
 static cudaError_t launch_score_kernel(const ScoreParams& p, int grid, size_t smem, cudaStream_t stream) {
-  auto kern = quest_page_score_kernel<NT, FUSED, QSPLIT>;
+  auto kern = quest_page_score_kernel<NT, FUSED, QSPLIT, AHPC>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   return launch_kernel(kern, dim3(grid), dim3(kScoreThreads), smem, stream, p);
 }
 
-template <int NT, bool FUSED>
+template <int NT, bool FUSED, int AHPC = 0>
 static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
   p.hsplit = bounds_head_split(p.hkv);
   const int stage_bytes = score_stage_bytes(p.hkv, p.hsplit);
@@ -967,10 +1031,15 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
   const int64_t max_chunks = (int64_t)p.batch * (p.share_div == 0 ? units_row : (units_row + p.chunk_units - 1) / p.chunk_units);
   if ((int64_t)grid > max_chunks) grid = (int)max_chunks;
   if (grid < 1) grid = 1;
-  const cudaError_t e = qsplit ? launch_score_kernel<NT, FUSED, true>(p, grid, smem, stream)
-                               : launch_score_kernel<NT, FUSED, false>(p, grid, smem, stream);
+  if constexpr (AHPC > 0) {
+    // the attention phase lives in the ring + q area of the scoring phase (everything below the barriers)
+    const int region = score_smem_layout(p.stages, p.hq, p.hkv, p.hsplit, p.batch, FUSED, qsplit ? 2 : 1).bar_off;
+    if (int rc = attn_configure_fused(p.attn, AHPC, region, grid)) return rc;
+  }
+  const cudaError_t e = qsplit ? launch_score_kernel<NT, FUSED, true, AHPC>(p, grid, smem, stream)
+                               : launch_score_kernel<NT, FUSED, false, AHPC>(p, grid, smem, stream);
   if (e != cudaSuccess) return cuda_error("quest_page_score launch", e);
-  return check_launch(FUSED ? "quest_score_select_pack" : "quest_page_score");
+  return check_launch(AHPC > 0 ? "quest_decode_layer" : (FUSED ? "quest_score_select_pack" : "quest_page_score"));
 }
 
 static ScoreParams make_score_params(const void* q, int64_t q_stride_b, const void* bounds,
@@ -1032,6 +1101,42 @@ int launch_quest_score_select_pack(const void* q, int64_t q_stride_b, const void
   }
   return hq / hkv <= 8 ? launch_score_variant<1, true>(p, stream)
                        : launch_score_variant<2, true>(p, stream);
+}
+
+// One launch per sparse decode layer: (store +) score + select + pack + sparse decode attention.
+int launch_quest_decode_layer(const void* q, int64_t q_stride_b, const void* bounds, int64_t num_chunks,
+                              const int32_t* unit_table, int64_t ut_stride, const int32_t* page_table,
+                              int64_t pt_stride, const int32_t* req_rows, const int32_t* context_lens,
+                              void* scores, int64_t score_stride, int batch, int hq, int hkv, int n_cols, int k,
+                              int32_t* packed_slots, int64_t out_stride, int32_t* sparse_lens,
+                              int32_t* selected_pages, int32_t* sched, const FusedStore* store,
+                              const AttnParams& attn, cudaStream_t stream) {
+  if (batch <= 0) return 0;
+  if (n_cols <= 0 || hq / hkv > 8) {
+    set_error("quest_decode_layer: needs n_cols > 0 and a group size <= 8 (got n_cols=%d, %d q heads per KV head): "
+              "use the separate entry points", n_cols, hq / hkv);
+    return 2;
+  }
+  ScoreParams p = make_score_params(q, q_stride_b, bounds, num_chunks, unit_table, ut_stride, req_rows,
+                                    context_lens, scores, score_stride, batch, hq, hkv, n_cols);
+  p.page_table = page_table; p.pt_stride = pt_stride;
+  p.k = k; p.packed_slots = packed_slots; p.out_stride = out_stride; p.sparse_lens = sparse_lens;
+  p.selected_pages = selected_pages; p.sched = sched;
+  if (store != nullptr) {
+    p.store = StoreArgs{(const __nv_bfloat16*)store->key, store->k_stride, (const __nv_bfloat16*)store->value,
+                        store->v_stride, (__nv_bfloat16*)store->k_cache, (__nv_bfloat16*)store->v_cache,
+                        store->slot_mapping, store->num_slots,
+                        store->refresh_bounds ? (__nv_bfloat16*)const_cast<void*>(bounds) : nullptr,
+                        store->page_rec, num_chunks * kPage};
+    p.store_tokens = batch;
+  }
+  p.attn = attn;
+  p.attn.dbg_times = nullptr;
+  switch (attn_auto_heads_per_cta(hkv)) {
+    case 1: return launch_score_variant<1, true, 1>(p, stream);
+    case 2: return launch_score_variant<1, true, 2>(p, stream);
+    default: return launch_score_variant<1, true, 4>(p, stream);
+  }
 }
 
 }  // namespace svb200

@@ -40,8 +40,9 @@ struct SchedSmem {
 };
 
 // Global scratch of one launch family: ints [0] = finished CTAs, [1 + r] = next chunk of row r,
-// [1 + rows + r] = units of row r done.  Zero-initialised once; the last CTA to finish zeroes it again.
-__host__ __device__ inline int sched_scratch_ints(int rows) { return 1 + 2 * rows; }
+// [1 + rows + r] = units of row r done, [1 + 2 * rows + r] = row r selected (one-launch layer only).
+// Zero-initialised once; the last CTA to finish zeroes it again.
+__host__ __device__ inline int sched_scratch_ints(int rows) { return 1 + 3 * rows; }
 
 __device__ __forceinline__ void sched_init(SchedSmem& q, int readers) {
   for (int s = 0; s < kSchedQueue; ++s) {
