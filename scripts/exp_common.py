@@ -48,6 +48,11 @@ class QuestState:
         ops.sparse_decode_attn(self.q, self.kc[layer % self.layers], self.vc[layer % self.layers], self.packed, self.req,
                                self.lens, out=self.out, workspace=self.ws, heads_per_cta=hpc)
 
+    def fused(self, layer=0):
+        ops.quest_decode_layer(self.q, self.bounds[layer % self.layers], self.ut, self.pt, self.req, self.ctx_lens,
+                               self.n_cols, self.hkv, self.prev, self.scores, self.packed, self.lens, self.tickets,
+                               self.kc[layer % self.layers], self.vc[layer % self.layers], out=self.out, workspace=self.ws)
+
     def both(self, layer=0):
         self.score(layer)
         self.attn(layer)

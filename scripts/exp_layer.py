@@ -25,8 +25,9 @@ for shape in shapes:
         t_s = graph_time_us(st.score, NL)
         t_a = graph_time_us(st.attn, NL)
         t_b = graph_time_us(st.both, NL)
+        t_f = graph_time_us(st.fused, NL) if hq // hkv <= 8 else float("nan")
         print(f"shape {shape:>22s} knobs [{ks:>12s}]  score+select {t_s:7.1f} us ({st.bytes_score() / t_s / 1e3:6.0f} GB/s)  "
-              f"attention {t_a:6.1f} us ({st.bytes_attn() / t_a / 1e3:6.0f} GB/s)  layer {t_b:7.1f} us", flush=True)
+              f"attention {t_a:6.1f} us ({st.bytes_attn() / t_a / 1e3:6.0f} GB/s)  layer {t_b:7.1f} us  one launch {t_f:7.1f} us", flush=True)
         for which, _ in pairs:
             ops.set_tuning(which, 0)
     del st

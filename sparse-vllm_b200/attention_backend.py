@@ -75,6 +75,14 @@ def decode_attention_layer(cache_manager, backend: B200AttentionBackend, layer_i
                            tp_gathered: torch.Tensor | None = None) -> torch.Tensor:
     """Decode branch of the generic ``Attention.forward`` (layers/attention.py:162-250)."""
     context = get_context()
+    one_launch = getattr(cache_manager, "decode_layer_one_launch", None)
+    if one_launch is not None:
+        o = one_launch(layer_idx, q, selection, num_heads=num_heads, num_kv_heads=num_kv_heads, out=out,
+                       workspace=get_decode_workspace(context, q.shape[0], num_heads, num_kv_heads, q.device),
+                       tp_comm=tp_comm, tp_gathered=tp_gathered)
+        if o is not None:
+            cache_manager.on_layer_attention_end(layer_idx)
+            return o
     view = cache_manager.build_decode_compute_view(layer_idx, q, selection, num_heads=num_heads,
                                                    num_kv_heads=num_kv_heads)
     meta = view.meta

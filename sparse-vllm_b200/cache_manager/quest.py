@@ -79,6 +79,7 @@ class QuestCacheManager(CacheManager):
         self._provider = provider
         # decode: the layer's new K/V rows wait here for the layer's scoring launch, which stores them itself
         self.fuse_decode_store = bool(fuse_decode_store)
+        self.fuse_decode_layer = True  # sparse long-text layers: one launch (decode_layer_one_launch)
         self._pending_store: tuple[int, ops.DecodeStore] | None = None
 
     def _alloc_bounds(self) -> torch.Tensor:
@@ -336,6 +337,43 @@ class QuestCacheManager(CacheManager):
         return self._build_decode_view_static(layer_idx, q, active_slots, req_indices, context_lens,
                                               token_budget=token_budget, num_heads=num_heads,
                                               num_kv_heads=num_kv_heads)
+
+    @torch.no_grad()
+    def decode_layer_one_launch(self, layer_idx, q, selection, *, num_heads, num_kv_heads, out, workspace,
+                                tp_comm=None, tp_gathered=None):
+        """A sparse layer of a long-text decode batch in ONE launch (svb200_quest_decode_layer): the pending K/V store,
+        `_build_decode_view_static` and the decode attention.  Returns the attention output, or None when the layer
+        takes the general path (dense / skip layer, mixed batch, group size > 8, `fuse_decode_layer` off)."""
+        if not self.fuse_decode_layer or layer_idx < int(self.config.quest_skip_layers):
+            return None
+        token_budget = int(self.config.quest_token_budget)
+        ctx = get_context()
+        if token_budget <= 0 or ctx.is_prefill or not bool(ctx.is_long_text) or int(num_heads) // int(num_kv_heads) > 8:
+            return None
+        if selection.kind != "full" or int(num_kv_heads) != self.num_kv_heads:
+            return None
+        page_budget_base = max(3, token_budget // PAGE)
+        max_keep = max(token_budget, page_budget_base * PAGE, PAGE)
+        max_context_len = self.layer_batch_state.max_context_len
+        if max_context_len is None or int(max_context_len) <= max_keep:
+            return None
+        max_pages = min(self.max_pages_per_row, (int(max_context_len) + PAGE - 1) // PAGE)
+        _, prev_budget = quest_page_budget(token_budget, PAGE, max_pages)
+        if prev_budget <= 0 or max_pages < 2:
+            return None
+        batch = int(q.shape[0])
+        n_cols = max_pages - 1
+        s = self._get_scratch(batch, n_cols, (prev_budget + 1) * PAGE)
+        store = self._take_pending_store(layer_idx)
+        kv = self.kv_layer_index(layer_idx)
+        if out is None:
+            out = torch.empty_like(q)
+        return self._get_provider(num_heads).quest_decode_layer(
+            q, self.bounds[kv], self.unit_table, self.buffer_req_to_page_slots, selection.req_indices,
+            selection.context_lens, n_cols=n_cols, num_kv_heads=self.num_kv_heads, prev_budget=prev_budget,
+            scores=s.scores, packed_slots=s.packed, sparse_lens=s.lens, tickets=s.tickets,
+            k_cache=self.kv_cache[0, kv], v_cache=self.kv_cache[1, kv], out=out, workspace=workspace, store=store,
+            comm=tp_comm, gathered=tp_gathered)
 
     @torch.no_grad()
     def _build_decode_view_static(self, layer_idx, q, active_slots, req_indices, context_lens, *, token_budget,

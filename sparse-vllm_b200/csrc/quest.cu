@@ -464,19 +464,24 @@ __device__ __forceinline__ uint32_t q_neg(uint32_t x) { return x & q_neg_mask(x)
 __device__ __forceinline__ void score_consumer_sync() { group_sync<1, kScoreConsumerThreads>(); }
 
 // Attention phase of a one-launch layer (AHPC > 0 in quest_page_score_kernel, whose header describes it); entered by
-// warps 0-11 of a CTA.  Not inlined: its register allocation is then independent of the scoring code's.
+// warps 0-11 of a CTA.  dbg (experiments): slots 16.. of the CTA's time stamps.
 template <int AHPC>
-__device__ __noinline__ void score_attention_phase(const ScoreParams& p, unsigned char* smem, int* s_flag) {
+__device__ __forceinline__ void score_attention_phase(const ScoreParams& p, unsigned char* smem, int* s_flag,
+                                                      unsigned long long* dbg) {
   const AttnParams& ap = p.attn;
   const int B = p.batch;
   const int tid = threadIdx.x, warp = tid >> 5;
   const int* sel_done = p.sched + 1 + 2 * B;
-  auto wait_row = [&](int b) {
-    SpinGuard guard;
-    while (ld_acquire_gpu(sel_done + b) == 0) {
-      __nanosleep(32);
-      guard.tick(kSpinLimitNs);
+  auto wait_row = [&](int b) {  // whole warp; one lane polls
+    if ((tid & 31) == 0) {
+      SpinGuard guard;
+      while (ld_acquire_gpu(sel_done + b) == 0) {
+        __nanosleep(32);
+        guard.tick(kSpinLimitNs);
+      }
+      if (dbg && warp == kConsumerWarps && dbg[23] == 0) dbg[23] = global_timer_ns();
     }
+    __syncwarp();
   };
   // tokens of batch entry b the attention reads: what the selection writes to sparse_lens (known up front)
   auto len_of = [&](int b) {
@@ -487,15 +492,17 @@ __device__ __noinline__ void score_attention_phase(const ScoreParams& p, unsigne
   if (warp <= kScoreSchedWarp) {
     // this CTA's scoring is over: its consumers drained every stage, its loader and scheduler are done
     group_sync<3, kConsumerThreads>();
+    if (dbg && tid == 0) dbg[16] = global_timer_ns();
     attn_setup<AHPC, 1>(ap, smem, len_of);
     __threadfence_block();
     asm volatile("bar.arrive 4, %0;" ::"n"(kConsumerThreads + kProducerWarps * 32) : "memory");
     group_sync<3, kConsumerThreads>();
-    attn_main<AHPC, 1, false, 3>(ap, smem, wait_row, nullptr);
+    if (dbg && tid == 0) dbg[17] = global_timer_ns();
+    attn_main<AHPC, 1, false, 3>(ap, smem, wait_row, dbg ? dbg + 16 : nullptr);
     if (tid == 0 && atomicAdd(s_flag, 1) == 1) sched_finish(p.sched, B);
   } else {
     asm volatile("bar.sync 4, %0;" ::"n"(kConsumerThreads + kProducerWarps * 32) : "memory");
-    attn_main<AHPC, 1, false, 3>(ap, smem, wait_row, nullptr);
+    attn_main<AHPC, 1, false, 3>(ap, smem, wait_row, dbg ? dbg + 16 : nullptr);
   }
 }
 
@@ -533,7 +540,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
   __shared__ int s_flag;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  unsigned long long* dbg = p.dbg_times ? p.dbg_times + (size_t)blockIdx.x * 16 : nullptr;
+  unsigned long long* dbg = p.dbg_times ? p.dbg_times + (size_t)blockIdx.x * (AHPC > 0 ? 32 : 16) : nullptr;
 
   // ---- setup that touches no global memory (runs while a programmatic predecessor drains)
   if (tid == 0) {
@@ -555,6 +562,8 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
     dbg[0] = global_timer_ns();
     dbg[7] = smid;
     dbg[2] = dbg[4] = dbg[5] = dbg[6] = dbg[13] = dbg[14] = dbg[15] = 0;
+    if constexpr (AHPC > 0)
+      for (int x = 16; x < 32; ++x) dbg[x] = 0;
   }
   for (int b = tid; b < B; b += kScoreThreads) {
     const int ctx = p.context_lens[b];
@@ -908,7 +917,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
   }  // consumers
 
   if constexpr (AHPC > 0) {
-    if (warp <= kScoreSchedWarp + kProducerWarps) score_attention_phase<AHPC>(p, smem, &s_flag);
+    if (warp <= kScoreSchedWarp + kProducerWarps) score_attention_phase<AHPC>(p, smem, &s_flag, dbg);
   }
 }
 
@@ -1131,7 +1140,7 @@ int launch_quest_decode_layer(const void* q, int64_t q_stride_b, const void* bou
     p.store_tokens = batch;
   }
   p.attn = attn;
-  p.attn.dbg_times = nullptr;
+  p.attn.dbg_times = nullptr;  // (the layer kernel's own time stamps carry the attention phase's: slots 16..)
   switch (attn_auto_heads_per_cta(hkv)) {
     case 1: return launch_score_variant<1, true, 1>(p, stream);
     case 2: return launch_score_variant<1, true, 2>(p, stream);

@@ -115,6 +115,16 @@ class B200SparseDecodeProvider:
             self._count("quest_page_score")
             self._count("quest_select_pack_mixed")
 
+    def quest_decode_layer(self, q, bounds_layer, unit_table, page_table, req_rows, context_lens, *, n_cols,
+                           num_kv_heads, prev_budget, scores, packed_slots, sparse_lens, tickets, k_cache, v_cache,
+                           out, workspace, store: ops.DecodeStore | None = None, comm=None, gathered=None) -> torch.Tensor:
+        """One launch for a sparse long-text decode layer: (store +) score + select + pack + sparse attention."""
+        ops.quest_decode_layer(q, bounds_layer, unit_table, page_table, req_rows, context_lens, n_cols, num_kv_heads,
+                               prev_budget, scores, packed_slots, sparse_lens, tickets, k_cache, v_cache, out=out,
+                               workspace=workspace, store=store, comm=comm, gathered=gathered)
+        self._count("quest_decode_layer_one_launch" + ("_push" if comm is not None and comm.world > 1 else ""))
+        return out
+
     def decode(self, q, k_cache, v_cache, slot_table, req_rows, seq_lens, *, out, workspace, max_len: int,
                attn_score=None, comm=None, gathered=None) -> torch.Tensor:
         """``comm`` / ``gathered``: tensor-parallel push epilogue (ops.sparse_decode_attn)."""

@@ -398,6 +398,77 @@ def sparse_decode_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Te
     return out
 
 
+def quest_decode_layer(q: torch.Tensor, bounds_layer: torch.Tensor, unit_table: torch.Tensor, page_table: torch.Tensor,
+                       req_rows: torch.Tensor, context_lens: torch.Tensor, n_cols: int, num_kv_heads: int,
+                       prev_budget: int, scores: torch.Tensor, packed_slots: torch.Tensor, sparse_lens: torch.Tensor,
+                       sched_scratch: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, *, out: torch.Tensor,
+                       workspace: torch.Tensor, selected_pages: torch.Tensor | None = None,
+                       store: DecodeStore | None = None, sm_scale: float | None = None, comm=None,
+                       gathered: torch.Tensor | None = None) -> torch.Tensor:
+    """One launch per sparse decode layer (svb200_quest_decode_layer): (store +) score + select + pack, then the
+    sparse decode attention over the packed slots inside the same launch.  Same results as
+    `quest_score_select_pack` followed by `sparse_decode_attn`.  Needs n_cols > 0 and <= 8 q heads per KV head."""
+    bsz, hq, qs = _q(q, "q")
+    num_chunks = _bounds_layer(bounds_layer, num_kv_heads)
+    require_cuda(scores, "scores", torch.bfloat16)
+    for t, n in ((unit_table, "unit_table"), (page_table, "page_table"), (req_rows, "req_rows"),
+                 (context_lens, "context_lens"), (packed_slots, "packed_slots"), (sparse_lens, "sparse_lens"),
+                 (sched_scratch, "sched_scratch"), (workspace, "workspace")):
+        _i32(t, n)
+    if sched_scratch.numel() < sched_scratch_ints(bsz):
+        raise ValueError(f"sched_scratch needs >= {sched_scratch_ints(bsz)} int32 entries, got {sched_scratch.numel()}.")
+    if selected_pages is not None:
+        _i32(selected_pages, "selected_pages")
+    num_slots, hkv = _kv_layer(k_cache, "k_cache")
+    if _kv_layer(v_cache, "v_cache") != (num_slots, hkv) or hkv != int(num_kv_heads):
+        raise ValueError("k_cache / v_cache must have identical shapes with num_kv_heads heads.")
+    ob, oh, os_ = _q(out, "out")
+    if (ob, oh) != (bsz, hq):
+        raise ValueError(f"out must be [B, Hq, {HEAD_DIM}] like q, got {tuple(out.shape)}.")
+    key = value = slot_mapping = page_rec = None
+    k_stride = v_stride = refresh = 0
+    if store is not None:
+        if store.k_cache.data_ptr() != k_cache.data_ptr() or store.v_cache.data_ptr() != v_cache.data_ptr():
+            raise ValueError("the fused store must write the caches the attention reads.")
+        for t, n in ((store.key, "key"), (store.value, "value")):
+            require_cuda(t, n, torch.bfloat16)
+            if t.dim() != 3 or tuple(t.shape) != (bsz, hkv, HEAD_DIM) or t.stride(2) != 1 or t.stride(1) != HEAD_DIM:
+                raise ValueError(f"{n} must be [{bsz}, {hkv}, {HEAD_DIM}] with contiguous heads, got {tuple(t.shape)}/{t.stride()}.")
+        _i32(store.slot_mapping, "slot_mapping")
+        if int(store.slot_mapping.numel()) != bsz:
+            raise ValueError(f"slot_mapping must hold one slot per batch row ({bsz}), got {store.slot_mapping.numel()}.")
+        if store.refresh_bounds:
+            if store.page_rec is None:
+                raise ValueError("a store that refreshes bounds needs page_rec.")
+            _page_rec(store.page_rec, num_slots)
+        key, value, slot_mapping, page_rec = store.key, store.value, store.slot_mapping, store.page_rec
+        k_stride, v_stride, refresh = int(store.key.stride(0)), int(store.value.stride(0)), int(store.refresh_bounds)
+    if sm_scale is None:
+        sm_scale = 1.0 / math.sqrt(HEAD_DIM)
+    push = comm is not None and comm.world > 1
+    gather_off = gather_stride = 0
+    if push:
+        if gathered is None:
+            raise ValueError("the tensor-parallel epilogue needs the gathered output view.")
+        require_cuda(gathered, "gathered", torch.bfloat16)
+        gb, gh, gather_stride = _q(gathered, "gathered")
+        if (gb, gh) != (bsz, comm.world * hq):
+            raise ValueError(f"gathered must be [B={bsz}, world*Hq={comm.world * hq}, {HEAD_DIM}], got {tuple(gathered.shape)}.")
+        gather_off = comm.offset_of(gathered)
+    lib = _native.load()
+    check(lib.svb200_quest_decode_layer(
+        ptr(key), k_stride, ptr(value), v_stride, ptr(slot_mapping), refresh, ptr(page_rec),
+        ptr(k_cache), ptr(v_cache), num_slots,
+        ptr(q), qs, ptr(bounds_layer), num_chunks, ptr(unit_table), _rows_stride(unit_table, "unit_table"),
+        ptr(page_table), _rows_stride(page_table, "page_table"), ptr(req_rows), ptr(context_lens), ptr(scores),
+        _rows_stride(scores, "scores"), bsz, hq, hkv, int(n_cols), int(prev_budget), ptr(packed_slots),
+        _rows_stride(packed_slots, "packed_slots"), ptr(sparse_lens), ptr(selected_pages), ptr(sched_scratch),
+        ptr(out), os_, ptr(workspace), int(workspace.numel()) * 4, float(sm_scale),
+        comm.struct_ptr() if push else None, gather_off, gather_stride, current_stream_ptr(q.device)),
+        "svb200_quest_decode_layer")
+    return out
+
+
 def allreduce_sum_bf16(comm, inp: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
     """One-shot NVLink SUM all-reduce (svb200_allreduce_sum_bf16): ``inp`` is a contiguous bf16 view INSIDE
     ``comm``'s local data buffer (every rank passes the view at the same offset), ``out`` a local bf16 tensor."""
