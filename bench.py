@@ -65,6 +65,9 @@ def parse_args():
     ap.add_argument("--collective", default="push", choices=["push", "nccl"],
                     help="N>1: gather of the attention head shards: 'push' = peer stores in the attention epilogue "
                          "(svb200_sparse_decode_attn_tp), 'nccl' = all_gather_into_tensor after every layer")
+    ap.add_argument("--one-launch", default="auto", choices=["auto", "on", "off"],
+                    help="sparse layers as ONE launch (store+score+select+pack+attention, svb200_quest_decode_layer) "
+                         "instead of two; auto = the provider's default")
     ap.add_argument("--pdl", type=int, default=-1, help="programmatic dependent launch: 1 on, 0 off, -1 library default")
     ap.add_argument("--tune", default="", help="experiment knobs 'which=value,...' (svb200_set_tuning)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
@@ -264,8 +267,19 @@ class DecodeStep:
         self.h_out = torch.empty(self.out.shape, dtype=torch.bfloat16).pin_memory()
         self.launches_per_step = 0
         self.timers = None  # optional per-kernel CUDA-event collection
+        self.force_two_launches = False  # per-kernel timing: the two launches of a sparse layer, each alone
         self.no_comm = False         # per-kernel timing: the launches without their collective ...
         self.only_collective = False  # ... and (NCCL arm) the collective without the launches
+
+    def one_launch_active(self) -> bool:
+        """Does the manager run a sparse layer of this workload as one launch (its "auto" rule included)?"""
+        mgr, f = self.mgr, getattr(self.mgr, "fuse_decode_layer", False)
+        if not f or self.hq // self.hkv > 8:
+            return False
+        if f == "auto":
+            bounds_bytes = self.w["bsz"] * mgr.max_pages_per_row * 2 * mgr.num_kv_heads * 128 * 2
+            return mgr.num_kv_heads <= 4 and bounds_bytes >= 148 * (2 << 20)
+        return True
 
     def prepare(self):
         """Host side of a decode step: allocate one slot per row, fill the static metadata buffers."""
@@ -295,7 +309,9 @@ class DecodeStep:
                                    num_kv_heads=self.hkv, out=self.out[layer], tp_comm=self.comm if push else None,
                                    tp_gathered=self.gathered[layer & 1] if push else None)
             # dense layer: store + attention; sparse layer: (store fused into) score/select/pack + attention
-            n += 2 if (layer < self.skip or getattr(mgr, "fuse_decode_store", False)) else 3
+            # dense layer: store + attention; sparse layer: (store fused into) score/select/pack + attention, or ONE launch
+            one = layer >= self.skip and not self.force_two_launches and self.one_launch_active()
+            n += 1 if one else (2 if (layer < self.skip or getattr(mgr, "fuse_decode_store", False)) else 3)
             if self.collective == "nccl" and not self.no_comm:
                 import torch.distributed as dist
                 dist.all_gather_into_tensor(self.gathered[layer & 1].view(-1), self.out[layer].view(-1))
@@ -331,6 +347,10 @@ def verify_gather(step) -> None:
         raise SystemExit("ranks disagree on the gathered attention output")
 
 
+def world_of(step) -> int:
+    return int(step.world)
+
+
 def graph_kernel_times(step, stream, lo: int, hi: int, reps: int = 5) -> dict:
     """Average duration of the score+select launch and of the attention launch of layers [lo, hi): each is
     captured ALONE in a CUDA graph (the other one replaced by a no-op) and replayed, so the figure is the
@@ -348,8 +368,29 @@ def graph_kernel_times(step, stream, lo: int, hi: int, reps: int = 5) -> dict:
         keys.append("sparse_decode_attn+push")
     elif step.collective == "nccl":
         keys.append("nccl_all_gather")
+    fuse_was = getattr(step.mgr, "fuse_decode_layer", False)
     try:
-        for key in keys:
+        for key in keys + (["quest_decode_layer"] if step.hq // step.hkv <= 8 and world_of(step) == 1 else []):
+            # the two launches of a sparse layer, each alone; then (when it is the path in use) the one-launch layer
+            step.mgr.fuse_decode_layer = key == "quest_decode_layer"  # (True: forced, whatever the "auto" rule says)
+            step.force_two_launches = not step.mgr.fuse_decode_layer
+            if key == "quest_decode_layer":
+                prov.quest_select, prov.decode = real_select, real_decode
+                step.no_comm, step.only_collective = True, False
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=stream):
+                    step.layers(lo, hi)
+                g.replay()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                for _ in range(reps):
+                    g.replay()
+                e1.record(stream)
+                stream.synchronize()
+                n = reps * (hi - lo)
+                out[key] = {"launches": n, "avg_ms": e0.elapsed_time(e1) / n, "how": "graph replay of this launch alone"}
+                g.reset()
+                continue
             prov.quest_select = real_select if key == "quest_score_select_pack" else (lambda *a, **k: None)
             prov.decode = real_decode if key.startswith("sparse_decode_attn") else (lambda q, *a, out=None, **k: out)
             step.no_comm = key in ("quest_score_select_pack", "sparse_decode_attn")
@@ -370,6 +411,8 @@ def graph_kernel_times(step, stream, lo: int, hi: int, reps: int = 5) -> dict:
     finally:
         prov.quest_select, prov.decode = real_select, real_decode
         step.no_comm = step.only_collective = False
+        step.mgr.fuse_decode_layer = fuse_was
+        step.force_two_launches = False
     return out
 
 
@@ -446,6 +489,8 @@ def run_b200(args) -> dict:
     for item in filter(None, args.tune.split(",")):
         which, value = item.split("=")
         _ops.set_tuning(int(which), int(value))
+    if args.one_launch != "auto":
+        mgr.fuse_decode_layer = args.one_launch == "on"
     step = DecodeStep(w, mgr, phys, hq, hkv, world, args.skip_layers, collective=args.collective)
     geo = geometry(w, hkv, hq)
     steps, warmup = args.steps, max(args.warmup, 3)
@@ -593,6 +638,14 @@ def run_b200(args) -> dict:
     roof_step = {"achieved": step_bytes / (ms_per_step * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                  "bytes_per_step": step_bytes}
     roof_step["frac"] = roof_step["achieved"] / peak
+    one_launch = None
+    if "quest_decode_layer" in ksum:
+        t = ksum["quest_decode_layer"]["avg_ms"]
+        one_launch = {"kernel": "quest_page_score_kernel<one-launch layer: store+score+select+pack+attention>",
+                      "avg_launch_ms": t, "bytes_per_launch": sel_bytes + attn_bytes,
+                      "achieved": (sel_bytes + attn_bytes) / (t * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                      "frac": (sel_bytes + attn_bytes) / (t * 1e-3) / 1e9 / peak,
+                      "two_launches_ms": sel_ms + attn_ms, "how": "graph replay of this launch alone"}
     collective = None
     if world > 1 and "sparse_decode_attn+push" in ksum:
         with_push = ksum["sparse_decode_attn+push"]["avg_ms"]
@@ -661,12 +714,15 @@ def run_b200(args) -> dict:
                        "run on side streams next to compute, all inside the timed region"},
         "gpu_launches": step.launches_per_step * steps,
         "roofline": roof, "roofline_attention": roof_attn, "roofline_step": roof_step,
+        "launches_per_sparse_layer": 1 if step.one_launch_active() else 2,
         "clocks": clocks,
     }
     if roof_dense is not None:
         line["roofline_dense_layer"] = roof_dense
     if collective is not None:
         line["collective"] = collective
+    if one_launch is not None:
+        line["roofline_one_launch_layer"] = one_launch
     if world > 1:
         print(json.dumps(line), flush=True)  # before clean-up: the line must not depend on it
         line["_printed"] = True

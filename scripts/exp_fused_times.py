@@ -9,6 +9,8 @@ from sparse_vllm_b200 import _native
 f = [int(x) for x in os.environ.get("SHAPE", "16,64,8").split(",")]
 st = QuestState(f[0], f[1], f[2], f[3] if len(f) > 3 else 131072, f[4] if len(f) > 4 else 4096, layers=4)
 lib = _native.load()
+if os.environ.get("NOWAVES"):
+    ops.set_tuning(12, 1)
 buf = torch.zeros(148 * 32, dtype=torch.int64, device="cuda:0")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:0")
 for it in range(4):

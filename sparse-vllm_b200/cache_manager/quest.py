@@ -79,7 +79,11 @@ class QuestCacheManager(CacheManager):
         self._provider = provider
         # decode: the layer's new K/V rows wait here for the layer's scoring launch, which stores them itself
         self.fuse_decode_store = bool(fuse_decode_store)
-        self.fuse_decode_layer = True  # sparse long-text layers: one launch (decode_layer_one_launch)
+        # Sparse long-text layers as ONE launch (decode_layer_one_launch): True / False / "auto".  Measured on B200
+        # (profiles/r2_c_one_launch.txt): the one-launch layer wins where a CTA streams >= ~2 MB of bounds and the rank's
+        # KV heads form a single head group (cfg3: 153.7 vs 160.2 us per layer); it ties at cfg5 / cfg2 and loses on
+        # small TP shards, where the selection tail and the flag -> slots -> data chain are not amortised.
+        self.fuse_decode_layer = "auto"
         self._pending_store: tuple[int, ops.DecodeStore] | None = None
 
     def _alloc_bounds(self) -> torch.Tensor:
@@ -346,6 +350,10 @@ class QuestCacheManager(CacheManager):
         takes the general path (dense / skip layer, mixed batch, group size > 8, `fuse_decode_layer` off)."""
         if not self.fuse_decode_layer or layer_idx < int(self.config.quest_skip_layers):
             return None
+        if self.fuse_decode_layer == "auto":
+            bounds_bytes = int(q.shape[0]) * self.max_pages_per_row * 2 * self.num_kv_heads * 128 * 2
+            if self.num_kv_heads > 4 or bounds_bytes < 148 * (2 << 20):
+                return None
         token_budget = int(self.config.quest_token_budget)
         ctx = get_context()
         if token_budget <= 0 or ctx.is_prefill or not bool(ctx.is_long_text) or int(num_heads) // int(num_kv_heads) > 8:

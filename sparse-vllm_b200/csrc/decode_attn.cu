@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
   __syncthreads();
   pdl_launch_dependents();
   if (dbg && tid == 0) dbg[1] = global_timer_ns();
-  attn_main<HPC, NT, WITH_SCORE, 1>(p, smem, [](int) {}, dbg);
+  attn_main<HPC, NT, WITH_SCORE, 1, false>(p, smem, [](int) {}, dbg);
 }
 
 // Launch configuration shared by the stand-alone kernel and the attention phase of a one-launch layer: ring stages

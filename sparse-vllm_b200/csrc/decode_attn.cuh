@@ -262,9 +262,10 @@ __device__ __forceinline__ void attn_setup(const AttnParams& p, unsigned char* s
 }
 
 // The attention work of one CTA after attn_setup: warps 0-7 consume, warps 8-11 produce (other warps must not
-// call it).  BAR: named barrier of the 256 consumer threads.  wait_row(b): called by a producer warp before it
+// call it).  BAR: named barrier of the 256 consumer threads.  LOWREG: the caller runs under a 128-register cap
+// (smaller batches of loads in the merge).  wait_row(b): called by a producer warp before it
 // reads slots of batch entry b (a fused launch waits there for the entry's selection; stand-alone: nothing).
-template <int HPC, int NT, bool WITH_SCORE, int BAR, class WaitRow>
+template <int HPC, int NT, bool WITH_SCORE, int BAR, bool LOWREG, class WaitRow>
 __device__ __forceinline__ void attn_main(const AttnParams& p, unsigned char* smem, WaitRow wait_row,
                                           unsigned long long* dbg) {
   using G = AttnGeom<HPC>;
@@ -491,9 +492,12 @@ __device__ __forceinline__ void attn_main(const AttnParams& p, unsigned char* sm
       }
     };
     bool merged = true;
-    if (heads_row > 16 && nc <= 6) fast(std::integral_constant<int, 4>(), std::integral_constant<int, 6>());
-    else if (heads_row > 8 && heads_row <= 16 && nc <= 12) fast(std::integral_constant<int, 2>(), std::integral_constant<int, 12>());
-    else if (heads_row <= 8 && nc <= 24) fast(std::integral_constant<int, 1>(), std::integral_constant<int, 24>());
+    if (LOWREG && heads_row > 16 && nc <= 6) fast(std::integral_constant<int, 2>(), std::integral_constant<int, 6>());
+    else if (heads_row > 16 && nc <= 6) fast(std::integral_constant<int, 4>(), std::integral_constant<int, 6>());
+    else if (LOWREG && heads_row > 8 && heads_row <= 16 && nc <= 6) fast(std::integral_constant<int, 2>(), std::integral_constant<int, 6>());
+    else if (LOWREG && heads_row <= 8 && nc <= 12) fast(std::integral_constant<int, 1>(), std::integral_constant<int, 12>());
+    else if (!LOWREG && heads_row > 8 && heads_row <= 16 && nc <= 12) fast(std::integral_constant<int, 2>(), std::integral_constant<int, 12>());
+    else if (!LOWREG && heads_row <= 8 && nc <= 24) fast(std::integral_constant<int, 1>(), std::integral_constant<int, 24>());
     else merged = false;
     // General path (any number of contributors): the lse first, then the partials that carry weight.
     constexpr int HB = 4;  // heads a warp merges at once: their loads are all independent

@@ -463,6 +463,14 @@ __device__ __forceinline__ uint32_t q_neg(uint32_t x) { return x & q_neg_mask(x)
 
 __device__ __forceinline__ void score_consumer_sync() { group_sync<1, kScoreConsumerThreads>(); }
 
+// The select group's selection of one row, as a function of its own (one-launch layer kernels).
+__device__ __noinline__ void fused_select_pack_row(const uint16_t* scores_row, int n_cols, int n_valid, int k,
+                                                   const int32_t* pt_row, int ctx, int32_t* out_row, int32_t* len_out,
+                                                   int32_t* sel_pages_out, SelectSmem* sm, unsigned long long* tdbg) {
+  quest_select_pack_row<2, kScoreSelectThreads, (kScoreThreads - kScoreSelectThreads)>(
+      scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out, sel_pages_out, *sm, tdbg);
+}
+
 // Attention phase of a one-launch layer (AHPC > 0 in quest_page_score_kernel, whose header describes it); entered by
 // warps 0-11 of a CTA.  dbg (experiments): slots 16.. of the CTA's time stamps.
 template <int AHPC>
@@ -476,7 +484,7 @@ __device__ __forceinline__ void score_attention_phase(const ScoreParams& p, unsi
     if ((tid & 31) == 0) {
       SpinGuard guard;
       while (ld_acquire_gpu(sel_done + b) == 0) {
-        __nanosleep(32);
+        __nanosleep(500);  // few pollers, far apart: the flags share cache lines with the rows' counters
         guard.tick(kSpinLimitNs);
       }
       if (dbg && warp == kConsumerWarps && dbg[23] == 0) dbg[23] = global_timer_ns();
@@ -496,13 +504,16 @@ __device__ __forceinline__ void score_attention_phase(const ScoreParams& p, unsi
     attn_setup<AHPC, 1>(ap, smem, len_of);
     __threadfence_block();
     asm volatile("bar.arrive 4, %0;" ::"n"(kConsumerThreads + kProducerWarps * 32) : "memory");
-    group_sync<3, kConsumerThreads>();
+    // ... and wait, blocked in hardware, until the producers are in (in a selecting CTA they are select warps
+    // until their rows are done): the consumers do not poll their ring barriers next to a running selection
+    asm volatile("bar.sync 5, %0;" ::"n"(kConsumerThreads + kProducerWarps * 32) : "memory");
     if (dbg && tid == 0) dbg[17] = global_timer_ns();
-    attn_main<AHPC, 1, false, 3>(ap, smem, wait_row, dbg ? dbg + 16 : nullptr);
+    attn_main<AHPC, 1, false, 3, true>(ap, smem, wait_row, dbg ? dbg + 16 : nullptr);
     if (tid == 0 && atomicAdd(s_flag, 1) == 1) sched_finish(p.sched, B);
   } else {
     asm volatile("bar.sync 4, %0;" ::"n"(kConsumerThreads + kProducerWarps * 32) : "memory");
-    attn_main<AHPC, 1, false, 3>(ap, smem, wait_row, dbg ? dbg + 16 : nullptr);
+    asm volatile("bar.arrive 5, %0;" ::"n"(kConsumerThreads + kProducerWarps * 32) : "memory");
+    attn_main<AHPC, 1, false, 3, true>(ap, smem, wait_row, dbg ? dbg + 16 : nullptr);
   }
 }
 
@@ -723,6 +734,13 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
         group_sync<2, kScoreSelectThreads>();
         __threadfence();
         const unsigned long long ts = dbg ? global_timer_ns() : 0;
+        if constexpr (AHPC > 0)  // (its own register allocation: inlined next to the attention phase it spilled)
+          fused_select_pack_row(p.scores + (int64_t)b * p.score_stride, p.n_cols, sNv[b], p.k,
+                                p.page_table + (int64_t)sReq[b] * p.pt_stride, p.context_lens[b],
+                                p.packed_slots + (int64_t)b * p.out_stride, p.sparse_lens + b,
+                                p.selected_pages ? p.selected_pages + (int64_t)b * (p.k + 1) : nullptr, sel_sm,
+                                dbg ? dbg + 13 : nullptr);
+        else
         quest_select_pack_row<2, kScoreSelectThreads, (kScoreThreads - kScoreSelectThreads)>(
             p.scores + (int64_t)b * p.score_stride, p.n_cols, sNv[b], p.k,
             p.page_table + (int64_t)sReq[b] * p.pt_stride, p.context_lens[b],
