@@ -133,6 +133,35 @@ class QuestCacheManager(CacheManager):
             self.row_seq_lens[row] = 0
         return row
 
+    def _h2d(self, arr, dtype: torch.dtype = torch.int64) -> torch.Tensor:
+        """Small host array -> device tensor WITHOUT synchronising the host with the stream: staged through a ring of
+        pinned buffers and copied non-blocking (a `.to(device)` of pageable memory, or a blocking `copy_`, waits for
+        everything queued on the stream, i.e. for the whole previous decode step: the host and the GPU then take
+        turns).  A staging buffer is reused only after the copy out of it has run (event per buffer)."""
+        a = np.ascontiguousarray(arr)
+        if self.device.type != "cuda":
+            return torch.from_numpy(a).to(dtype).to(self.device)
+        ring = getattr(self, "_stage_ring", None)
+        if ring is None:
+            ring = self._stage_ring = SimpleNamespace(
+                bufs=[torch.empty(8192, dtype=torch.int64).pin_memory() for _ in range(64)],
+                events=[None] * 64, nxt=0)
+        n = int(a.size)
+        if n > ring.bufs[0].numel():
+            return torch.from_numpy(a).to(dtype).to(self.device)  # (not a decode-step size)
+        i = ring.nxt
+        ring.nxt = (i + 1) % len(ring.bufs)
+        if ring.events[i] is not None:
+            ring.events[i].synchronize()
+        view = ring.bufs[i].view(dtype)[:n]
+        view.numpy()[:] = a.reshape(-1)
+        out = torch.empty(n, dtype=dtype, device=self.device)
+        out.copy_(view, non_blocking=True)
+        ev = ring.events[i] or torch.cuda.Event()
+        ev.record()
+        ring.events[i] = ev
+        return out.view(a.shape)
+
     def _pop_pages(self, n: int) -> np.ndarray:
         if self._num_free_pages < n:
             raise RuntimeError(f"Out of QuEST KV pages: need_pages={n}, free_pages={self._num_free_pages}.")
@@ -156,11 +185,10 @@ class QuestCacheManager(CacheManager):
             chunks = self.free_chunks_cpu_stack[ptr - new_unit.size: ptr][::-1].copy()
             self._num_free_chunks -= int(new_unit.size)
             self.unit_table_cpu[rows[new_unit], units[new_unit]] = chunks
-            self.unit_table[torch.from_numpy(rows[new_unit]).to(self.device),
-                            torch.from_numpy(units[new_unit]).to(self.device)] = torch.from_numpy(chunks).to(self.device)
+            self.unit_table[self._h2d(rows[new_unit]), self._h2d(units[new_unit])] = \
+                self._h2d(chunks.astype(np.int32), torch.int32)
         recs = self.unit_table_cpu[rows, units].astype(np.int64) * PAGE + page_idx % PAGE
-        self.page_rec[torch.from_numpy(np.asarray(pages, dtype=np.int64)).to(self.device)] = \
-            torch.from_numpy(recs.astype(np.int32)).to(self.device)
+        self.page_rec[self._h2d(np.asarray(pages, dtype=np.int64))] = self._h2d(recs.astype(np.int32), torch.int32)
 
     def allocate_prefill(self, seq_id: int, num_tokens: int) -> torch.Tensor:
         """Slots for the next ``num_tokens`` tokens of a sequence (chunked prefill, quest.py:1426-1493)."""
@@ -216,14 +244,12 @@ class QuestCacheManager(CacheManager):
         if new_pos.size:
             pages = self._pop_pages(int(new_pos.size))
             self.buffer_req_to_page_slots_cpu[rows[new_pos], page_idx[new_pos]] = pages
-            self.buffer_req_to_page_slots[torch.from_numpy(rows[new_pos]).to(self.device),
-                                          torch.from_numpy(page_idx[new_pos]).to(self.device)] = \
-                torch.from_numpy(pages).to(self.device)
+            self.buffer_req_to_page_slots[self._h2d(rows[new_pos]), self._h2d(page_idx[new_pos])] = \
+                self._h2d(np.asarray(pages, dtype=np.int32), torch.int32)
             self._assign_bounds_records(rows[new_pos], page_idx[new_pos], pages)
         slots = self.buffer_req_to_page_slots_cpu[rows, page_idx].astype(np.int64) * PAGE + page_off
         slots32 = slots.astype(np.int32)
-        self.buffer_req_to_token_slots[torch.from_numpy(rows).to(self.device),
-                                       torch.from_numpy(cur).to(self.device)] = torch.from_numpy(slots32).to(self.device)
+        self.buffer_req_to_token_slots[self._h2d(rows), self._h2d(cur)] = self._h2d(slots32, torch.int32)
         self.row_seq_lens[rows] += 1
         return rows, slots32
 
@@ -248,14 +274,25 @@ class QuestCacheManager(CacheManager):
         host = np.empty((3, graph_bs), dtype=np.int32)
         host[0, :real], host[1, :real], host[2, :real] = slots, lens, rows
         host[0, real:], host[1, real:], host[2, real:] = -1, lens[0], rows[0]
-        packed = torch.from_numpy(host)
-        slot_mapping.copy_(packed[0], non_blocking=True)
-        context_lens.copy_(packed[1], non_blocking=True)
-        req_indices.copy_(packed[2], non_blocking=True)
         ids = [int(s.decode_input_token) for s in seqs] + [int(seqs[0].decode_input_token)] * (graph_bs - real)
         pos = [int(s.decode_input_position) for s in seqs] + [int(seqs[0].decode_input_position)] * (graph_bs - real)
-        input_ids.copy_(torch.tensor(ids, dtype=input_ids.dtype))
-        positions.copy_(torch.tensor(pos, dtype=positions.dtype))
+        if slot_mapping.device.type == "cuda":
+            # one staged, non-blocking copy for the five buffers (see _h2d: nothing here waits for the stream)
+            meta = np.empty((5, graph_bs), dtype=np.int64)
+            meta[:3], meta[3], meta[4] = host, ids, pos
+            dev = self._h2d(meta)
+            slot_mapping.copy_(dev[0])
+            context_lens.copy_(dev[1])
+            req_indices.copy_(dev[2])
+            input_ids.copy_(dev[3])
+            positions.copy_(dev[4])
+        else:
+            packed = torch.from_numpy(host)
+            slot_mapping.copy_(packed[0])
+            context_lens.copy_(packed[1])
+            req_indices.copy_(packed[2])
+            input_ids.copy_(torch.tensor(ids, dtype=input_ids.dtype))
+            positions.copy_(torch.tensor(pos, dtype=positions.dtype))
         st = self.layer_batch_state
         st.slot_mapping, st.context_lens, st.req_indices = slot_mapping, context_lens, req_indices
         st.max_context_len = int(lens.max())
