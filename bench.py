@@ -553,52 +553,72 @@ def run_b200(args) -> dict:
 
         # ---- (3) end to end through the public API with HOST buffers: every step copies its q / new K,V
         # rows from pinned host memory and reads the attention output back.  The layers run in chunks so that
-        # a chunk's input copy (copy stream) and the previous chunk's read-back (third stream) overlap compute.
+        # a chunk's read-back (third stream) overlaps the next chunk's compute; input copies run on a copy stream.
         L = w["layers"]
-        n_chunks = 8 if L % 8 == 0 else 1
+        n_chunks = 2 if L % 2 == 0 else 1  # (two are enough to keep a chunk's read-back off the next step's path)
         per = L // n_chunks
         copy_s, back_s = torch.cuda.Stream(), torch.cuda.Stream()
-        chunk_graphs = []
+        # Two sets of device input buffers: step i + 1's inputs are copied in while step i computes (a serving loop
+        # double-buffers its inputs the same way); the chunk graphs are captured once per set.
+        sets = [(step.q, step.k_new, step.v_new),
+                (torch.empty_like(step.q), torch.empty_like(step.k_new), torch.empty_like(step.v_new))]
+        chunk_graphs = [[], []]
         if graph is not None:
-            for c in range(n_chunks):
-                g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g, stream=stream):
-                    step.layers(c * per, (c + 1) * per)
-                chunk_graphs.append(g)
-        in_ready = [torch.cuda.Event() for _ in range(n_chunks)]
+            for si, (q_, k_, v_) in enumerate(sets):
+                step.q, step.k_new, step.v_new = q_, k_, v_
+                for c in range(n_chunks):
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=stream):
+                        step.layers(c * per, (c + 1) * per)
+                    chunk_graphs[si].append(g)
+        in_ready = [[torch.cuda.Event() for _ in range(n_chunks)] for _ in sets]
         out_ready = [torch.cuda.Event() for _ in range(n_chunks)]
-        step_done = torch.cuda.Event()
+        d2h_done = [torch.cuda.Event() for _ in range(n_chunks)]
+        set_free = [torch.cuda.Event() for _ in sets]
+        e2e_count = [0]
 
         def e2e_step():
+            i = e2e_count[0]
+            e2e_count[0] += 1
+            si = i & 1
+            step.q, step.k_new, step.v_new = sets[si]
             step.prepare()
-            copy_s.wait_event(step_done)  # the previous step's layers have read q / k / v
+            if i >= 2:
+                copy_s.wait_event(set_free[si])  # step i - 2 has read this set of q / k / v
             with torch.cuda.stream(copy_s):
                 for c in range(n_chunks):
                     sl = slice(c * per, (c + 1) * per)
                     step.q[sl].copy_(step.h_q[sl], non_blocking=True)
                     step.k_new[sl].copy_(step.h_k[sl], non_blocking=True)
                     step.v_new[sl].copy_(step.h_v[sl], non_blocking=True)
-                    in_ready[c].record(copy_s)
+                    in_ready[si][c].record(copy_s)
             for c in range(n_chunks):
                 sl = slice(c * per, (c + 1) * per)
-                stream.wait_event(in_ready[c])
-                if chunk_graphs:
-                    chunk_graphs[c].replay()
+                stream.wait_event(in_ready[si][c])
+                if i >= 1:
+                    stream.wait_event(d2h_done[c])  # the previous step's output of this chunk is on the host
+                if chunk_graphs[si]:
+                    chunk_graphs[si][c].replay()
                 else:
                     step.layers(c * per, (c + 1) * per)
                 out_ready[c].record(stream)
                 back_s.wait_event(out_ready[c])
                 with torch.cuda.stream(back_s):
                     step.h_out[sl].copy_(step.out[sl], non_blocking=True)
-            stream.wait_stream(back_s)  # the step ends when its result is on the host
-            step_done.record(stream)
+                    d2h_done[c].record(back_s)
+            set_free[si].record(stream)
+
+        def e2e_drain():
+            stream.wait_stream(back_s)  # the last step's result is on the host
         for _ in range(warmup):
             e2e_step()
+        e2e_drain()
         barrier()
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         f0.record(stream)
         for _ in range(steps):
             e2e_step()
+        e2e_drain()
         f1.record(stream)
         barrier()
         e2e_ms = f0.elapsed_time(f1)
@@ -681,9 +701,10 @@ def run_b200(args) -> dict:
         if graph is not None:
             graph.reset()
             graph = None
-        for g in chunk_graphs:
-            g.reset()
-        chunk_graphs.clear()
+        for gs in chunk_graphs:
+            for g in gs:
+                g.reset()
+            gs.clear()
         torch.cuda.synchronize()
         dist.barrier()
         if step.comm is not None:
@@ -710,8 +731,9 @@ def run_b200(args) -> dict:
                              "capture; only the e2e arm advances the context)") if graph is not None else "eager"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / steps,
-                "how": f"{n_chunks} chunks of {per} layers; a chunk's H2D copy and the previous chunk's D2H read-back "
-                       "run on side streams next to compute, all inside the timed region"},
+                "how": f"{n_chunks} chunks of {per} layers; a chunk's H2D copy (two sets of device input buffers: the next "
+                       "step's inputs arrive while this one computes) and the previous chunk's D2H read-back run on side "
+                       "streams next to compute, all inside the timed region, which ends when the last result is on the host"},
         "gpu_launches": step.launches_per_step * steps,
         "roofline": roof, "roofline_attention": roof_attn, "roofline_step": roof_step,
         "launches_per_sparse_layer": 1 if step.one_launch_active() else 2,

@@ -1,0 +1,16 @@
+#!/bin/bash
+# Multi-GPU bench at N ranks (gpurun --gpus N): push epilogue, PDL off; optional 2-rank parity test first (TEST=1).
+N=${1:-2}
+mkdir -p gpurun_out
+if [ -n "$TEST" ]; then
+  timeout 600 python -m pytest tests/test_gpu_tp2.py -m gpu -q --timeout 500 > gpurun_out/tp2_test.log 2>&1; echo "tp2 test rc=$?"; tail -2 gpurun_out/tp2_test.log
+fi
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
+  bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/bench_scale_n${N}.log 2>&1
+echo "bench N=$N rc=$?"
+grep '^{' gpurun_out/bench_scale_n${N}.log | tail -1 | python -c "
+import json,sys
+d=json.loads(sys.stdin.read())
+c=d.get('collective') or {}
+print(' value', round(d['value'],1), 'ms', round(d['ms_per_step'],3), 'e2e', round(d['e2e']['value'],1), 'score_us', round(d['roofline']['avg_launch_ms']*1e3,1), 'attn_us', round(d['roofline_attention']['avg_launch_ms']*1e3,1), 'coll_us', round(c.get('us_per_layer',0),1), 'other_us', round(c.get('other_us_per_layer',0),1))
+" || tail -20 gpurun_out/bench_scale_n${N}.log
