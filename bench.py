@@ -62,6 +62,8 @@ def parse_args():
     ap.add_argument("--phys-layers", type=int, default=0, help="distinct KV/bounds pools cycled by the layers (0 = auto)")
     ap.add_argument("--skip-layers", type=int, default=0, help="quest_skip_layers (dense layers at the bottom)")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph replay")
+    ap.add_argument("--push-flags", action="store_true",
+                    help="push epilogue with system fences + per-rank flags instead of the flag-in-data staging")
     ap.add_argument("--collective", default="push", choices=["push", "nccl"],
                     help="N>1: gather of the attention head shards: 'push' = peer stores in the attention epilogue "
                          "(svb200_sparse_decode_attn_tp), 'nccl' = all_gather_into_tensor after every layer")
@@ -228,7 +230,7 @@ def build_state(w: dict, rank: int, world: int, phys_layers: int, skip_layers: i
 class DecodeStep:
     """One decode step over all layers through the provider's public API (cache-manager hooks + backend)."""
 
-    def __init__(self, w, mgr, phys_layers, hq, hkv, world, skip_layers, collective="push"):
+    def __init__(self, w, mgr, phys_layers, hq, hkv, world, skip_layers, collective="push", push_flags=False):
         import torch
         from sparse_vllm_b200.attention_backend import B200AttentionBackend
         self.torch = torch
@@ -248,7 +250,7 @@ class DecodeStep:
             if self.collective == "push":
                 from sparse_vllm_b200.parallel import PeerComm
                 nb = B * hq * world * HEAD_DIM * 2
-                self.comm = PeerComm(2 * nb)  # two gathered buffers: a peer may be one layer ahead
+                self.comm = PeerComm(2 * nb, ll_bytes=0 if push_flags else None)  # two gathered buffers: a peer may be one layer ahead
                 self.gathered = [self.comm.view(i * nb, (B, hq * world, HEAD_DIM), torch.bfloat16) for i in range(2)]
             else:
                 self.gathered = [torch.zeros(world, B, hq, HEAD_DIM, device=dev, dtype=torch.bfloat16) for _ in range(2)]
@@ -491,7 +493,7 @@ def run_b200(args) -> dict:
         _ops.set_tuning(int(which), int(value))
     if args.one_launch != "auto":
         mgr.fuse_decode_layer = args.one_launch == "on"
-    step = DecodeStep(w, mgr, phys, hq, hkv, world, args.skip_layers, collective=args.collective)
+    step = DecodeStep(w, mgr, phys, hq, hkv, world, args.skip_layers, collective=args.collective, push_flags=args.push_flags)
     geo = geometry(w, hkv, hq)
     steps, warmup = args.steps, max(args.warmup, 3)
 
@@ -723,7 +725,7 @@ def run_b200(args) -> dict:
                    "batch": w["bsz"], "ctx": w["ctx"], "page": PAGE, "token_budget": w["budget"],
                    "quest_skip_layers": args.skip_layers,
                    "parallelism": f"tp{world} (KV heads sharded"
-                   + (f"; head shards gathered by {'peer stores in the attention epilogue (NVLink)' if args.collective == 'push' else 'NCCL all_gather_into_tensor'})" if world > 1 else ")"),
+                   + (f"; head shards gathered by {('peer stores in the attention epilogue (NVLink), ' + ('fences + flags' if args.push_flags else 'flag-in-data words')) if args.collective == 'push' else 'NCCL all_gather_into_tensor'})" if world > 1 else ")"),
                    "pdl": {1: "on", 0: "off"}.get(args.pdl, "library default"),
                    "physical_kv_pools": phys, "l2": "inputs larger than L2 (>= 0.8 GB touched per layer; layers cycle "
                    f"{phys} distinct KV+bounds pools)",

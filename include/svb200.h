@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SVB200_ABI_VERSION 5
+#define SVB200_ABI_VERSION 6
 
 enum {
   SVB200_OK = 0,
@@ -401,6 +401,13 @@ typedef struct {
   int32_t world, rank;
   void* peer_buf[SVB200_MAX_PEERS];
   int32_t* peer_sync[SVB200_MAX_PEERS];
+  /* Optional staging of the push epilogue's flag-in-data protocol (ll_bytes = 0: none; the epilogue then orders its
+   * peer stores with system-scope fences and per-rank flags).  peer_ll[r]: ll_bytes of zero-initialised,
+   * 16-byte aligned memory of rank r, mapped by every rank.  A launch whose gathered tensor has G bytes needs
+   * ll_bytes >= 4 * G: every 4 payload bytes travel as one 8-byte word {payload, epoch}, which a 64-bit store
+   * makes visible atomically, so the receiver needs no fence and the sender no flag; two areas alternate. */
+  void* peer_ll[SVB200_MAX_PEERS];
+  int64_t ll_bytes;
 } svb200_comm_t;
 
 /*

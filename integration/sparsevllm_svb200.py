@@ -28,7 +28,7 @@ from sparsevllm.utils.profiler import profiler
 
 PAGE = 16
 HEAD_DIM = 128
-ABI_VERSION = 5
+ABI_VERSION = 6
 P, I32, I64, F32 = ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64, ctypes.c_float
 # argument types of the entry points bound here (the complete table is sparse-vllm_b200/_native.py:_SIGNATURES)
 ARGTYPES = {

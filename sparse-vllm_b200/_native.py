@@ -14,7 +14,7 @@ from pathlib import Path
 import torch
 
 _LIB_PATH = Path(__file__).resolve().parent / "lib" / "libsvb200.so"
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 MAX_PEERS = 8
 
@@ -22,7 +22,7 @@ MAX_PEERS = 8
 class Comm(ctypes.Structure):
     """svb200_comm_t: peer-mapped data buffers and sync blocks of every rank."""
     _fields_ = [("world", c_int32), ("rank", c_int32), ("peer_buf", c_void_p * MAX_PEERS),
-                ("peer_sync", c_void_p * MAX_PEERS)]
+                ("peer_sync", c_void_p * MAX_PEERS), ("peer_ll", c_void_p * MAX_PEERS), ("ll_bytes", c_int64)]
 
 
 # name -> (restype, argtypes); mirrors include/svb200.h one to one.

@@ -412,7 +412,13 @@ static int fill_attn_params(AttnParams* p_out, const char* who, const void* q, i
     for (int r = 0; r < comm->world; ++r) {
       p.push.out[r] = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(comm->peer_buf[r]) + gather_offset_bytes);
       p.push.sync[r] = comm->peer_sync[r];
+      p.push.ll[r] = static_cast<unsigned long long*>(comm->peer_ll[r]);
     }
+    // flag-in-data staging, when the communicator has room for two areas of this launch's rows
+    const int64_t words = (int64_t)comm->world * batch * num_q_heads * (SVB200_HEAD_DIM / 2);
+    bool have_ll = comm->ll_bytes >= 2 * words * 8;
+    for (int r = 0; r < comm->world && have_ll; ++r) have_ll = comm->peer_ll[r] != nullptr && aligned16(comm->peer_ll[r]);
+    p.push.ll_words = have_ll ? words : 0;
   }
   *p_out = p;
   return 0;

@@ -164,6 +164,88 @@ static __device__ void push_finish(const PushArgs& ps) {
   }
 }
 
+// ---- flag-in-data variant of the push (PushArgs::ll_words > 0; svb200_comm_t::peer_ll)
+// Every 4 payload bytes (two bf16) travel as one 8-byte word {payload, epoch}; a 64-bit store is visible atomically,
+// so nothing has to order data before a flag: the senders do not fence, there is no flag, and a receiver that reads
+// this launch's epoch in a word has its payload.  Peers write into THIS rank's staging; every CTA of the launch,
+// when its own attention work is done, polls its share of the staging and copies the payload into the local
+// gathered tensor, so the launch still completes only when every rank's rows are here.  The epoch is the sync
+// block's (bumped by the launch's last CTA, local atomics only); two staging areas alternate by its parity (a peer
+// can be one launch ahead).  This takes the two system-scope fences and the flag flight off the critical path.
+__device__ __forceinline__ int32_t push_epoch(const PushArgs& ps) {
+  return *reinterpret_cast<const volatile int32_t*>(ps.sync[ps.rank] + kSyncEpoch) + 1;
+}
+__device__ __forceinline__ void st_ll2(unsigned long long* dst, uint32_t a, uint32_t b, int32_t e) {
+  const unsigned long long hi = (unsigned long long)(uint32_t)e << 32;
+  asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(hi | a), "l"(hi | b) : "memory");
+}
+// elements [d0, d0 + 8) of this rank's row (b, local head h) -> every rank's gathered tensor (d0 % 8 == 0)
+__device__ __forceinline__ void push_row8(const PushArgs& ps, int batch, int hq, int32_t e, int b, int h, int d0, uint4 v) {
+  const int64_t off = (int64_t)b * ps.stride_b + ((int64_t)ps.rank * hq + h) * kHeadDim + d0;
+  if (ps.ll_words == 0) {
+    for (int r = 0; r < ps.world; ++r) *reinterpret_cast<uint4*>(ps.out[r] + off) = v;
+    return;
+  }
+  *reinterpret_cast<uint4*>(ps.out[ps.rank] + off) = v;
+  const int64_t word = (((int64_t)ps.rank * batch + b) * hq + h) * (kHeadDim / 2) + (d0 >> 1) + (int64_t)(e & 1) * ps.ll_words;
+  for (int r = 0; r < ps.world; ++r)
+    if (r != ps.rank) {
+      st_ll2(ps.ll[r] + word, v.x, v.y, e);
+      st_ll2(ps.ll[r] + word + 2, v.z, v.w, e);
+    }
+}
+// elements [d0, d0 + 4) (d0 % 4 == 0)
+__device__ __forceinline__ void push_row4(const PushArgs& ps, int batch, int hq, int32_t e, int b, int h, int d0, uint2 v) {
+  const int64_t off = (int64_t)b * ps.stride_b + ((int64_t)ps.rank * hq + h) * kHeadDim + d0;
+  if (ps.ll_words == 0) {
+    for (int r = 0; r < ps.world; ++r) *reinterpret_cast<uint2*>(ps.out[r] + off) = v;
+    return;
+  }
+  *reinterpret_cast<uint2*>(ps.out[ps.rank] + off) = v;
+  const int64_t word = (((int64_t)ps.rank * batch + b) * hq + h) * (kHeadDim / 2) + (d0 >> 1) + (int64_t)(e & 1) * ps.ll_words;
+  for (int r = 0; r < ps.world; ++r)
+    if (r != ps.rank) st_ll2(ps.ll[r] + word, v.x, v.y, e);
+}
+// End of a CTA's work, called by its 256 consumer threads (every CTA of the grid, exactly once; BAR: their barrier).
+template <int BAR>
+__device__ __forceinline__ void push_complete(const PushArgs& ps, int batch, int hq, int32_t e) {
+  const int tid = threadIdx.x;
+  if (ps.ll_words == 0) {
+    if (tid == 0) push_finish(ps);  // (a consumer barrier ordered the CTA's peer stores before this)
+    return;
+  }
+  const int64_t groups = ps.ll_words / 4;  // 4 words = 8 elements = one 16-byte piece of the gathered tensor
+  const int64_t per_src = groups / ps.world;
+  const unsigned long long* mine = ps.ll[ps.rank] + (int64_t)(e & 1) * ps.ll_words;
+  for (int64_t g = (int64_t)blockIdx.x * kConsumerThreads + tid; g < groups; g += (int64_t)gridDim.x * kConsumerThreads) {
+    const int src = (int)(g / per_src);
+    if (src == ps.rank) continue;
+    unsigned long long w0, w1, w2, w3;
+    SpinGuard guard;
+    while (true) {
+      asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(mine + 4 * g) : "memory");
+      asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w2), "=l"(w3) : "l"(mine + 4 * g + 2) : "memory");
+      if ((int32_t)(w0 >> 32) == e && (int32_t)(w1 >> 32) == e && (int32_t)(w2 >> 32) == e && (int32_t)(w3 >> 32) == e) break;
+      __nanosleep(100);
+      guard.tick(kPeerSpinLimitNs);
+    }
+    const int64_t rem = g - (int64_t)src * per_src;  // (b * hq + h) * 16 + piece
+    const int row = (int)(rem >> 4), piece = (int)(rem & 15);
+    const int b = row / hq, h = row - b * hq;
+    *reinterpret_cast<uint4*>(ps.out[ps.rank] + (int64_t)b * ps.stride_b + ((int64_t)src * hq + h) * kHeadDim + piece * 8) =
+        make_uint4((uint32_t)w0, (uint32_t)w1, (uint32_t)w2, (uint32_t)w3);
+  }
+  consumer_sync<BAR>();
+  if (tid == 0) {
+    int32_t* local = ps.sync[ps.rank];
+    __threadfence();
+    if (atomicAdd(local + kSyncDone, 1) == (int)gridDim.x - 1) {
+      local[kSyncDone] = 0;
+      local[kSyncEpoch] = e;
+    }
+  }
+}
+
 struct AttnSmemLayout {
   int ring_off, valid_off, bar_off, q_off, merge_off, prefix_off, entry_off, total;
 };
@@ -251,11 +333,9 @@ __device__ __forceinline__ void attn_setup(const AttnParams& p, unsigned char* s
                                            (int64_t)b * p.out_stride_b);
       for (int i = tid; i < p.hq * 16; i += kConsumerThreads) o4[i] = make_uint4(0, 0, 0, 0);
       if (push) {
-        for (int r = 0; r < p.push.world; ++r) {
-          uint4* g4 = reinterpret_cast<uint4*>(p.push.out[r] + (int64_t)b * p.push.stride_b +
-                                               (int64_t)p.push.rank * p.hq * kHeadDim);
-          for (int i = tid; i < p.hq * 16; i += kConsumerThreads) g4[i] = make_uint4(0, 0, 0, 0);
-        }
+        const int32_t e = push_epoch(p.push);
+        for (int i = tid; i < p.hq * 16; i += kConsumerThreads)
+          push_row8(p.push, p.batch, p.hq, e, b, i >> 4, (i & 15) * 8, make_uint4(0, 0, 0, 0));
       }
     }
   }
@@ -301,8 +381,9 @@ __device__ __forceinline__ void attn_main(const AttnParams& p, unsigned char* sm
   cut.small = (cut.UV + 1) * (Gn + 1) < (int64_t)1 << 31;
   int u0 = 0, u1 = 0, r_first = 0;
   if ((int64_t)blockIdx.x < Gn) cut.range_of(blockIdx.x, u0, u1, r_first);
+  const int32_t epoch = push ? push_epoch(p.push) : 0;
   if (u0 >= u1) {
-    if (push && tid == 0) push_finish(p.push);
+    if (push && warp < kConsumerWarps) push_complete<BAR>(p.push, p.batch, p.hq, epoch);
     return;
   }
   // first row of the range: the non-empty row that holds u0 (u0 may sit in the padding before the next row)
@@ -482,11 +563,7 @@ __device__ __forceinline__ void attn_main(const AttnParams& p, unsigned char* sm
             __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) + (int64_t)b * p.out_stride_b +
                                   (int64_t)(hg * heads_row + h0 + x) * kHeadDim;
             *reinterpret_cast<uint2*>(orow + lane * 4) = o2;
-            if (push) {
-              const int64_t off = (int64_t)b * p.push.stride_b +
-                                  ((int64_t)p.push.rank * p.hq + hg * heads_row + h0 + x) * kHeadDim + lane * 4;
-              for (int r = 0; r < p.push.world; ++r) *reinterpret_cast<uint2*>(p.push.out[r] + off) = o2;
-            }
+            if (push) push_row4(p.push, p.batch, p.hq, epoch, b, hg * heads_row + h0 + x, lane * 4, o2);
           }
         }
       }
@@ -556,11 +633,7 @@ __device__ __forceinline__ void attn_main(const AttnParams& p, unsigned char* sm
                                 (int64_t)b * p.out_stride_b +
                                 (int64_t)(hg * heads_row + h0 + x) * kHeadDim;
           *reinterpret_cast<uint2*>(orow + lane * 4) = o2;
-          if (push) {
-            const int64_t off = (int64_t)b * p.push.stride_b +
-                                ((int64_t)p.push.rank * p.hq + hg * heads_row + h0 + x) * kHeadDim + lane * 4;
-            for (int r = 0; r < p.push.world; ++r) *reinterpret_cast<uint2*>(p.push.out[r] + off) = o2;
-          }
+          if (push) push_row4(p.push, p.batch, p.hq, epoch, b, hg * heads_row + h0 + x, lane * 4, o2);
         }
       }
     }
@@ -804,13 +877,9 @@ __device__ __forceinline__ void attn_main(const AttnParams& p, unsigned char* sm
       const int64_t head0 = (int64_t)hg * heads_row * kHeadDim;
       uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (int64_t)b * p.out_stride_b + head0);
       for (int c = tid; c < heads_row * 16; c += kConsumerThreads) dst[c] = src[c];
-      if (push) {
-        for (int r = 0; r < p.push.world; ++r) {
-          uint4* g4 = reinterpret_cast<uint4*>(p.push.out[r] + (int64_t)b * p.push.stride_b +
-                                               (int64_t)p.push.rank * p.hq * kHeadDim + head0);
-          for (int c = tid; c < heads_row * 16; c += kConsumerThreads) g4[c] = src[c];
-        }
-      }
+      if (push)
+        for (int c = tid; c < heads_row * 16; c += kConsumerThreads)
+          push_row8(p.push, p.batch, p.hq, epoch, b, hg * heads_row + (c >> 4), (c & 15) * 8, src[c]);
     }
     if (!complete) {
       // Arrival ticket of the row, counted in KV-head warps (HPC per contributing CTA): whoever completes it merges
@@ -856,7 +925,7 @@ __device__ __forceinline__ void attn_main(const AttnParams& p, unsigned char* sm
     }
   }
   if (dbg && tid == 0) dbg[3] = global_timer_ns();
-  if (push && tid == 0) push_finish(p.push);  // the loop's last consumer_sync ordered the CTA's peer stores before this
+  if (push) push_complete<BAR>(p.push, p.batch, p.hq, epoch);  // (the loop's last consumer barrier ordered the CTA's peer stores before this)
 }
 
 }  // namespace svb200

@@ -98,6 +98,10 @@ struct PushArgs {
   __nv_bfloat16* out[kMaxPeers];  // gathered [B][world*Hq][128] bf16 buffer of every rank (own included)
   int64_t stride_b;            // elements between batch rows of the gathered buffers
   int32_t* sync[kMaxPeers];    // sync block of every rank: [r] = arrival flag written by rank r, [8] epoch, [9] finished CTAs
+  // flag-in-data protocol (ll_words > 0): rank r's staging, two areas of ll_words 8-byte words {payload, epoch};
+  // a row [src rank][b][local head] is 64 words
+  unsigned long long* ll[kMaxPeers];
+  int64_t ll_words;
 };
 
 // decode_attn.cu

@@ -91,7 +91,9 @@ class PeerComm:
 
     SYNC_BYTES = 256
 
-    def __init__(self, nbytes: int, *, group=None, device: torch.device | None = None) -> None:
+    def __init__(self, nbytes: int, *, group=None, device: torch.device | None = None, ll_bytes: int | None = None) -> None:
+        """``ll_bytes``: staging of the push epilogue's flag-in-data protocol behind the sync block (default: twice the
+        data buffer, enough when that holds two gathered tensors; 0: none, the epilogue then uses fences and flags)."""
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -104,7 +106,9 @@ class PeerComm:
         lib = _native.load()
         base = ctypes.c_void_p()
         handle = ctypes.create_string_buffer(64)
-        _native.check(lib.svb200_symm_alloc(self.nbytes + self.SYNC_BYTES, ctypes.byref(base), handle), "svb200_symm_alloc")
+        self.ll_bytes = (2 * self.nbytes if ll_bytes is None else int(ll_bytes) + 255) // 256 * 256
+        _native.check(lib.svb200_symm_alloc(self.nbytes + self.SYNC_BYTES + self.ll_bytes, ctypes.byref(base), handle),
+                      "svb200_symm_alloc")
         self._base = int(base.value)
         self._peer_bases: list[int] = [0] * self.world
         self._opened: list[int] = []
@@ -127,6 +131,8 @@ class PeerComm:
         for r in range(self.world):
             self._struct.peer_buf[r] = self._peer_bases[r]
             self._struct.peer_sync[r] = self._peer_bases[r] + self.nbytes
+            self._struct.peer_ll[r] = self._peer_bases[r] + self.nbytes + self.SYNC_BYTES if self.ll_bytes else None
+        self._struct.ll_bytes = self.ll_bytes
         if self.world > 1:
             dist.barrier(group=group)  # every rank has mapped every buffer before anybody launches
 

@@ -85,12 +85,16 @@ def _worker(rank: int, world: int, port: int) -> None:
                                               sel[b, :prev].cpu().tolist(), int(n_valid[b]), ulp_slack=1)
             assert c["bad"] == 0, f"rank {rank} row {b}: {c['detail']}"
         # attention with the push epilogue: every rank ends up with [B, Hq_total, D]
-        comm = PeerComm(2 * bsz * cfg["hq"] * 128 * 2)
-        gathered = [comm.view(i * bsz * cfg["hq"] * 256, (bsz, cfg["hq"], 128), torch.bfloat16) for i in range(2)]
+        # twice: the flag-in-data protocol (staging behind the sync block), then fences + flags (no staging)
+        comm_flags = PeerComm(2 * bsz * cfg["hq"] * 128 * 2, ll_bytes=0)
+        comm_ll = PeerComm(2 * bsz * cfg["hq"] * 128 * 2)
+        assert comm_ll.ll_bytes > 0 and comm_flags.ll_bytes == 0
         out = torch.empty(bsz, hq, 128, dtype=torch.bfloat16, device=dev)
         arange = torch.arange(bsz, dtype=torch.int32, device=dev)
         ws = ops.attn_workspace(bsz, hq, hkv, dev)
-        for it in range(4):  # alternating buffers, flags only grow
+        for it in range(10):  # alternating buffers, epochs / flags only grow
+            comm = comm_flags if it >= 6 else comm_ll
+            gathered = [comm.view(i * bsz * cfg["hq"] * 256, (bsz, cfg["hq"], 128), torch.bfloat16) for i in range(2)]
             gathered[it & 1].fill_(float("nan"))
             dist.barrier()
             torch.cuda.synchronize()
@@ -104,6 +108,22 @@ def _worker(rank: int, world: int, port: int) -> None:
             dist.all_gather(shards, out)
             want = torch.cat(shards, dim=1)  # heads of rank 0, then rank 1: the [B, Hq, D] o_proj reads
             assert torch.equal(gathered[it & 1], want), f"rank {rank} iteration {it}: pushed rows differ from the shards"
+        # the one-launch layer (score + select + pack + attention) with the same epilogue
+        gathered = [comm_ll.view(i * bsz * cfg["hq"] * 256, (bsz, cfg["hq"], 128), torch.bfloat16) for i in range(2)]
+        packed2, lens2 = torch.zeros_like(packed), torch.zeros_like(lens)
+        for it in range(2):
+            gathered[it & 1].fill_(float("nan"))
+            dist.barrier()
+            torch.cuda.synchronize()
+            ops.quest_decode_layer(q.to(dev), bounds, ut, inp["page_table"].to(dev), req, ctx, n_cols, hkv, prev, scores,
+                                   packed2, lens2, ops.sched_scratch(bsz, dev), kc, vc, out=out, workspace=ws,
+                                   comm=comm_ll, gathered=gathered[it & 1])
+            torch.cuda.synchronize()
+            assert torch.equal(packed2, packed) and torch.equal(lens2, lens)
+            shards = [torch.empty_like(out) for _ in range(world)]
+            dist.all_gather(shards, out)
+            assert torch.equal(gathered[it & 1], torch.cat(shards, dim=1)), f"rank {rank}: one-launch layer, push {it}"
+            torch.testing.assert_close(out.cpu().float(), ref.float(), atol=2e-2, rtol=1e-2)
         # ---------------------------------------------------------------- all-reduce provider family
         rows, hidden = 16, 5120
         spec = AllReduceOpSpec(world_size=world, ranks=tuple(range(world)), max_rows=rows, hidden_size=hidden,
@@ -127,7 +147,8 @@ def _worker(rank: int, world: int, port: int) -> None:
             ref2 = nccl.run(x.clone())
             torch.testing.assert_close(got.float(), ref2.float(), atol=2e-2, rtol=2e-2)
         op.close()
-        comm.close()
+        comm_ll.close()
+        comm_flags.close()
     finally:
         dist.destroy_process_group()
 
