@@ -399,6 +399,7 @@ static int fill_attn_params(AttnParams* p_out, const char* who, const void* q, i
   p.no_math = 0;
   p.granule = 1;
   p.grid_cap = 0;
+  p.evict_first = 1;
   p.push = PushArgs{};
   if (comm != nullptr && comm->world > 1) {
     if (int rc = check_comm(who, comm)) return rc;

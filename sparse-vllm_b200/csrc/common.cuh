@@ -96,12 +96,29 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 // 1-D bulk async copy global -> shared::cta, completion counted on an mbarrier.
 // dst/src 16-byte aligned, bytes a multiple of 16.  SASS: UBLKCP.
+// The streams of this library (bounds chunks, K/V rows) are read exactly once per launch and are several times the
+// size of L2: they are tagged evict-first, so that what IS re-used -- the next kernel's code, page / unit tables,
+// q, the attention partials -- survives in L2 (a launch that follows a launch of ANOTHER kernel started ~4 us late,
+// scripts/exp_boundary.py: its code came from DRAM).  Knob kTuneNoEvictFirst restores the default policy.
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes,
                                          uint64_t* bar) {
   asm volatile(
       "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
           "r"(dst),
       "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_hint(uint32_t dst, const void* src, uint32_t bytes,
+                                              uint64_t* bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
+          "r"(dst),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
       : "memory");
 }
 

@@ -69,6 +69,7 @@ static int attn_configure(AttnParams& p, int avail, int grid_in, int* grid_out) 
   p.grid_cap = 0;
   p.no_math = tuning(kTuneNoMath) == 2;
   p.granule = tuning(kTuneAttnGranule) != 2;
+  p.evict_first = tuning(kTuneNoEvictFirst) != 1;
   // ~6 us of streaming at ~44 GB/s per SM, in units (the kernel caps it at half a range)
   p.split_pen = tuning(kTuneAttnSplitPen) > 0 ? tuning(kTuneAttnSplitPen) - 1
                                                : (int)((6 * 44000 + unit_kb * 512) / (unit_kb * 1024));

@@ -429,6 +429,7 @@ __device__ __forceinline__ void attn_main(const AttnParams& p, unsigned char* sm
       return __ldg(row_pf + t);
     };
     const int64_t slot_bytes = slot_elems * 2;
+    const uint64_t l2_policy = l2_evict_first_policy();
     // granule copies need the GRAN token rows contiguous in the cache: every local KV head staged together
     const bool gran_ok = G::GRAN > 1 && p.hkv == HPC && p.granule;
     int r_is = r_first, hg_is = r_first % HG;  // issue cursor
@@ -488,10 +489,17 @@ __device__ __forceinline__ void attn_main(const AttnParams& p, unsigned char* sm
         sValid[s] = mask;
         mbar_arrive_expect_tx(&full_bar[s], (uint32_t)__popc(mask) * 2u * (uint32_t)G::TOK_BYTES);
       }
-      if (lead_bulk)
-        bulk_g2s(dst, base + (int64_t)my * slot_bytes, (uint32_t)(G::GRAN * G::TOK_BYTES), &full_bar[s]);
-      else if (my >= 0 && !covered)
-        bulk_g2s(dst, base + (int64_t)my * slot_bytes, (uint32_t)G::TOK_BYTES, &full_bar[s]);
+      if (p.evict_first) {
+        if (lead_bulk)
+          bulk_g2s_hint(dst, base + (int64_t)my * slot_bytes, (uint32_t)(G::GRAN * G::TOK_BYTES), &full_bar[s], l2_policy);
+        else if (my >= 0 && !covered)
+          bulk_g2s_hint(dst, base + (int64_t)my * slot_bytes, (uint32_t)G::TOK_BYTES, &full_bar[s], l2_policy);
+      } else {
+        if (lead_bulk)
+          bulk_g2s(dst, base + (int64_t)my * slot_bytes, (uint32_t)(G::GRAN * G::TOK_BYTES), &full_bar[s]);
+        else if (my >= 0 && !covered)
+          bulk_g2s(dst, base + (int64_t)my * slot_bytes, (uint32_t)G::TOK_BYTES, &full_bar[s]);
+      }
       pf[d] = fetch(i + kSlotPrefetch * NP);
       s += NP;
       while (s >= S) s -= S, ph ^= 1;

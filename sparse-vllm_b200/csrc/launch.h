@@ -19,6 +19,7 @@ enum {
   kTuneScoreGroups = 0, kTuneAttnMinKB = 1, kTuneMinBatch = 2, kTuneShareDiv = 3, kTuneChunkUnits = 4,
   kTuneNoMath = 5, kTuneScoreQ = 6, kTunePdl = 7, kTuneAttnGranule = 8, kTuneAttnHpc = 9,
   kTuneAttnSplitPen = 10,  // attention: units a CTA is charged for a row boundary inside its range, + 1 (0: auto, 1: none)
+  kTuneNoEvictFirst = 13,  // 1: the streams' bulk copies use the default L2 policy instead of evict-first
   kTuneAttnStages = 11,    // attention: cap of the ring's stages (experiments; 0: as many as fit)
   kTuneCount = 16
 };
@@ -131,6 +132,7 @@ struct AttnParams {
   int no_math;       // experiments: consumers release the stages without the contractions
   int granule;       // copy granules of several token rows where the slots allow it
   int grid_cap;      // CTAs the attention work is cut into at most (0: the whole grid); set by a fused launcher
+  int evict_first;   // the K/V stream's copies are tagged evict-first in L2; launcher
   int split_pen;     // units a CTA is charged for a row boundary inside its range (see the kernel's cut); launcher
   PushArgs push;     // tensor-parallel push epilogue (world <= 1: none)
 };

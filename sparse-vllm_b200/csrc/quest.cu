@@ -421,6 +421,7 @@ struct ScoreParams {
   int chunk_units;                // units per claimed chunk
   int min_batch, share_div;       // guided claim size = max(min_batch, left / (share_div * CTAs per group))
   int no_math;                    // experiments: consumers release the stages without the contractions
+  int evict_first;                // the bounds stream's copies are tagged evict-first in L2
   int32_t* sched;  // sched_scratch_ints(batch) zeroed ints
   // fused select only
   int k;
@@ -633,6 +634,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
 #pragma unroll
     for (int t = 0; t < kIdDepth; ++t) fetch(dq[t], idq[t]);
     const char* bounds_bytes = reinterpret_cast<const char*>(p.bounds);
+    const uint64_t l2_policy = l2_evict_first_policy();
     // dq / idq form a circular FIFO indexed at compile time (the loop body is unrolled kIdDepth
     // times) and a slot is refilled only AFTER its id was used: the register that waits for a table
     // load is then never copied or renamed, so the load's latency is only paid when the id is finally
@@ -672,6 +674,10 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
             sValid[s] = umask | ((round & 0x7fffu) << 16);
             if (have) {
               mbar_arrive_expect_tx(&full_bar[s], part_bytes);
+              if (p.evict_first)
+                bulk_g2s_hint(smem_u32(ring + s * stage_bytes),
+                              bounds_bytes + ((int64_t)c * hs + part) * (int64_t)part_bytes, part_bytes, &full_bar[s], l2_policy);
+              else
               bulk_g2s(smem_u32(ring + s * stage_bytes),
                        bounds_bytes + ((int64_t)c * hs + part) * (int64_t)part_bytes, part_bytes, &full_bar[s]);
             } else {
@@ -1053,6 +1059,7 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
     p.share_div = tuning(kTuneShareDiv) > 0 ? (tuning(kTuneShareDiv) == 99 ? 0 : tuning(kTuneShareDiv)) : auto_div;
   }
   p.no_math = tuning(kTuneNoMath) == 1;
+  p.evict_first = tuning(kTuneNoEvictFirst) != 1;
   const size_t smem = score_smem_layout(p.stages, p.hq, p.hkv, p.hsplit, p.batch, FUSED, qsplit ? 2 : 1).total;
   // no more CTAs than pieces of work: chunks, or single units when the rows are cut evenly
   const int64_t max_chunks = (int64_t)p.batch * (p.share_div == 0 ? units_row : (units_row + p.chunk_units - 1) / p.chunk_units);
