@@ -746,7 +746,16 @@ def run_b200(args) -> dict:
     if collective is not None:
         line["collective"] = collective
     if one_launch is not None:
-        line["roofline_one_launch_layer"] = one_launch
+        one_launch.update({"bound": "hbm", "peak_source": peak_src, "frac_of_nominal_8tbs": one_launch["achieved"] / NOMINAL_GBS,
+                           "traffic": (None if roof["traffic"] is None or roof_attn["traffic"] is None
+                                       else roof["traffic"] + roof_attn["traffic"]),
+                           "traffic_note": "sum of the two kernels' ncu captures (the layer kernel moves the same bytes)"})
+        if step.one_launch_active():
+            # the kernel that runs in the timed step is the one-launch layer: it is the dominant kernel of the line;
+            # its two halves, each timed alone as separate launches, explain it
+            line["roofline"], line["roofline_score_select_pack"] = one_launch, roof
+        else:
+            line["roofline_one_launch_layer"] = one_launch
     if world > 1:
         print(json.dumps(line), flush=True)  # before clean-up: the line must not depend on it
         line["_printed"] = True
@@ -1102,6 +1111,12 @@ def secondary_workload(key: str, args, extra=()) -> dict:
     if "roofline_attention" in d:
         out["roofline_attention_frac"] = d["roofline_attention"]["frac"]
         out["attention_launch_ms"] = d["roofline_attention"]["avg_launch_ms"]
+    if "roofline_score_select_pack" in d:  # the step runs one-launch layers: `roofline` is that kernel
+        out["launches_per_sparse_layer"] = 1
+        out["score_select_pack_frac"] = d["roofline_score_select_pack"]["frac"]
+        out["score_select_pack_launch_ms"] = d["roofline_score_select_pack"]["avg_launch_ms"]
+    elif "launches_per_sparse_layer" in d:
+        out["launches_per_sparse_layer"] = d["launches_per_sparse_layer"]
     if "roofline_dense_layer" in d:
         out["quest_skip_layers"] = d["config"]["quest_skip_layers"]
         out["dense_layer_launch_ms"] = d["roofline_dense_layer"]["avg_launch_ms"]

@@ -24,14 +24,17 @@ def table() -> str:
     if d is None:
         return "(no bench line committed yet)\n"
     out = []
-    r, ra, rs = d["roofline"], d["roofline_attention"], d["roofline_step"]
+    r, ra, rs = d.get("roofline_score_select_pack", d["roofline"]), d["roofline_attention"], d["roofline_step"]
+    one = d["roofline"] if "roofline_score_select_pack" in d else d.get("roofline_one_launch_layer")
     out.append(f"Measured on 1 x B200 (`python bench.py`, CUDA-graph replay, clocks {d['clocks']['sm_mhz']:.0f} MHz, "
                f"no throttle reasons), roofline against the measured copy peak {r['peak']:.0f} GB/s "
                f"(`MEASURED_PEAKS.json`) and, in brackets, against the nominal 8 TB/s:\n")
     out.append("| workload | tok/s (`value`) | ms/step | tok/s end to end (`e2e`) | score+select+pack launch | attention launch | whole step |")
     out.append("|---|---|---|---|---|---|---|")
+    one_txt = (f"; one-launch layer {one['avg_launch_ms'] * 1e3:.1f} us, {pct(one['frac'])} ({pct(one.get('frac_of_nominal_8tbs'))})"
+               if one and "roofline_score_select_pack" in d else "")
     out.append(f"| cfg5 Qwen3-32B shape, bs16, ctx 128K, budget 4096, skip 0 | **{d['value']:.1f}** | {d['ms_per_step']:.3f} | "
-               f"**{d['e2e']['value']:.1f}** | {r['avg_launch_ms'] * 1e3:.1f} us, {pct(r['frac'])} ({pct(r['frac_of_nominal_8tbs'])}) | "
+               f"**{d['e2e']['value']:.1f}** | {r['avg_launch_ms'] * 1e3:.1f} us, {pct(r['frac'])} ({pct(r['frac_of_nominal_8tbs'])}){one_txt} | "
                f"{ra['avg_launch_ms'] * 1e3:.1f} us, {pct(ra['frac'])} ({pct(ra['frac_of_nominal_8tbs'])}) | "
                f"{pct(rs['frac'])} ({pct(rs['frac_of_nominal_8tbs'])}) |")
     names = {"cfg5_skip2": "cfg5, quest_skip_layers = 2 (two dense 128K layers)", "cfg3": "cfg3 Qwen2.5-7B shape, bs32, ctx 128K, budget 4096",
@@ -43,9 +46,18 @@ def table() -> str:
         att = (f"{o['attention_launch_ms'] * 1e3:.1f} us, {pct(o.get('roofline_attention_frac'))}"
                if o.get("attention_launch_ms") else "—")
         dom = f"{o['roofline_launch_ms'] * 1e3:.1f} us, {pct(o.get('roofline_frac'))}"
+        if "score_select_pack_launch_ms" in o:  # one-launch layers: the halves timed alone, then the layer kernel
+            dom = (f"{o['score_select_pack_launch_ms'] * 1e3:.1f} us, {pct(o['score_select_pack_frac'])}; one-launch layer "
+                   f"{o['roofline_launch_ms'] * 1e3:.1f} us, {pct(o.get('roofline_frac'))}")
         if key == "cfg4":
             dom, att = "—", dom + " (scored attention)"
         out.append(f"| {name} | {o['value']:.1f} | {o['ms_per_step']:.3f} | {o['e2e']:.1f} | {dom} | {att} | {pct(o.get('roofline_step_frac'))} |")
+    if one:
+        used = "the path the timed step uses" if "roofline_score_select_pack" in d else "not used at this shape: the two launches are faster"
+        out.append(f"\nOne-launch layer at cfg5 (store + score + select + pack + attention, `svb200_quest_decode_layer`; {used}): "
+                   f"{one['avg_launch_ms'] * 1e3:.1f} us per layer, {pct(one['frac'])} ({pct(one.get('frac_of_nominal_8tbs'))}) "
+                   f"for the {one['bytes_per_launch'] / 1e6:.0f} MB of both halves; the two launches, each alone: "
+                   f"{one['two_launches_ms'] * 1e3:.1f} us.")
     o = d.get("other_workloads", {}).get("cfg5_skip2") or {}
     if o.get("dense_layer_launch_ms"):
         out.append(f"\nDense skip layer at cfg5 (8.6 GB per launch): {o['dense_layer_launch_ms']:.3f} ms, {pct(o.get('dense_layer_frac'))} of the measured copy peak.")
@@ -67,7 +79,7 @@ def table() -> str:
         if x:
             c = x.get("collective") or {}
             rows.append(f"| {n} | {x['value']:.1f} | {x['ms_per_step']:.3f} | {x['e2e']['value']:.1f} | {x['value'] / d['value'] / n:.2f} | "
-                        f"{x['roofline']['avg_launch_ms'] * 1e3:.1f} | {x['roofline_attention']['avg_launch_ms'] * 1e3:.1f} | "
+                        f"{x.get('roofline_score_select_pack', x['roofline'])['avg_launch_ms'] * 1e3:.1f} | {x['roofline_attention']['avg_launch_ms'] * 1e3:.1f} | "
                         f"{c.get('us_per_layer', float('nan')):.1f} | {c.get('other_us_per_layer', float('nan')):.1f} |")
     if rows:
         out.append("\nTensor parallel (cfg5, KV heads sharded, one process per GPU, NVLink push epilogue, max over ranks):\n")
