@@ -9,6 +9,7 @@ from exp_common import QuestState
 f = [int(x) for x in os.environ.get("SHAPE", "16,8,1").split(",")]
 st = QuestState(f[0], f[1], f[2], f[3] if len(f) > 3 else 131072, f[4] if len(f) > 4 else 4096, layers=4)
 for layer in range(int(os.environ.get("LAYERS", "8"))):
-    st.both(layer)
+    st.both(layer)   # the two launches ...
+    st.fused(layer)  # ... and the one-launch layer (three kernels per iteration)
 torch.cuda.synchronize()
 print("ok", f)
