@@ -280,7 +280,7 @@ class DecodeStep:
             return False
         if f == "auto":
             bounds_bytes = self.w["bsz"] * mgr.max_pages_per_row * 2 * mgr.num_kv_heads * 128 * 2
-            return bounds_bytes >= 148 * (2 << 20)
+            return bounds_bytes >= 148 * (3 << 19)
         return True
 
     def prepare(self):

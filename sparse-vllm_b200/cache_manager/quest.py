@@ -80,8 +80,9 @@ class QuestCacheManager(CacheManager):
         # decode: the layer's new K/V rows wait here for the layer's scoring launch, which stores them itself
         self.fuse_decode_store = bool(fuse_decode_store)
         # Sparse long-text layers as ONE launch (decode_layer_one_launch): True / False / "auto".  Measured on B200
-        # (profiles/r2_d_evict_first.txt): the one-launch layer wins where a CTA streams >= ~2 MB of bounds (cfg5: 147.6
-        # vs 152.3 us per layer, cfg3: 143.6 vs 154.4); it loses on small launches (TP shards: 54.0 vs 51.4, cfg2: 40.6
+        # (profiles/r2_d_evict_first.txt): the one-launch layer wins where a CTA streams >= ~1.5 MB of bounds (cfg5: 147.6
+        # vs 152.3 us per layer, cfg3: 143.6 vs 154.4, the N=2 shard of cfg5: 91.7 vs 95.9); it loses on small launches
+        # (N=4 / N=8 shards: 66.4 vs 64.1, 54.0 vs 51.4; cfg2: 40.6
         # vs 39.5), where the selection tail and the flag -> slots -> data chain are not amortised.
         self.fuse_decode_layer = "auto"
         self._pending_store: tuple[int, ops.DecodeStore] | None = None
@@ -389,7 +390,7 @@ class QuestCacheManager(CacheManager):
             return None
         if self.fuse_decode_layer == "auto":
             bounds_bytes = int(q.shape[0]) * self.max_pages_per_row * 2 * self.num_kv_heads * 128 * 2
-            if bounds_bytes < 148 * (2 << 20):
+            if bounds_bytes < 148 * (3 << 19):
                 return None
         token_budget = int(self.config.quest_token_budget)
         ctx = get_context()
