@@ -275,7 +275,10 @@ class DecodeStep:
 
     def one_launch_active(self) -> bool:
         """Does the manager run a sparse layer of this workload as one launch (its "auto" rule included)?"""
-        mgr, f = self.mgr, getattr(self.mgr, "fuse_decode_layer", False)
+        return self.one_launch_active_with(getattr(self.mgr, "fuse_decode_layer", False))
+
+    def one_launch_active_with(self, f) -> bool:
+        mgr = self.mgr
         if not f or self.hq // self.hkv > 8:
             return False
         if f == "auto":
@@ -424,9 +427,10 @@ class KernelTimers:
     def __init__(self, provider):
         import torch
         self.torch = torch
-        self.pairs = {"quest_score_select_pack": [], "sparse_decode_attn": []}
+        self.pairs = {"quest_score_select_pack": [], "sparse_decode_attn": [], "quest_decode_layer": []}
         self.enabled = False
         self._select, self._decode = provider.quest_select, provider.decode
+        provider.quest_decode_layer = self._wrap(provider.quest_decode_layer, "quest_decode_layer")
         provider.quest_select = self._wrap(self._select, "quest_score_select_pack")
         provider.decode = self._wrap(self._decode, "sparse_decode_attn")
 
@@ -448,7 +452,9 @@ class KernelTimers:
         self.torch.cuda.synchronize()  # the event pairs were recorded on a side stream
         for key, pairs in self.pairs.items():
             ms = [a.elapsed_time(b) for a, b in pairs]
-            out[key] = {"launches": len(ms), "avg_ms": sum(ms) / len(ms) if ms else None, "total_ms": sum(ms)}
+            if ms:
+                out[key] = {"launches": len(ms), "avg_ms": sum(ms) / len(ms), "total_ms": sum(ms),
+                            "how": "eager launches, CUDA event pairs"}
         return out
 
 
@@ -548,6 +554,11 @@ def run_b200(args) -> dict:
             timers.enabled = True
             for _ in range(min(steps, 5)):
                 step.layers(skip)
+            fuse_was = getattr(mgr, "fuse_decode_layer", False)
+            mgr.fuse_decode_layer = False  # ... and the two launches of a sparse layer, whatever path the step uses
+            for _ in range(min(steps, 5) if step.one_launch_active_with(fuse_was) else 0):
+                step.layers(skip)
+            mgr.fuse_decode_layer = fuse_was
             timers.enabled = False
             ksum = timers.summary()
         barrier()
