@@ -758,9 +758,7 @@ def run_b200(args) -> dict:
         line["collective"] = collective
     if one_launch is not None:
         one_launch.update({"bound": "hbm", "peak_source": peak_src, "frac_of_nominal_8tbs": one_launch["achieved"] / NOMINAL_GBS,
-                           "traffic": (None if roof["traffic"] is None or roof_attn["traffic"] is None
-                                       else roof["traffic"] + roof_attn["traffic"]),
-                           "traffic_note": "sum of the two kernels' ncu captures (the layer kernel moves the same bytes)"})
+                           "traffic": ncu_traffic(w["key"], "quest_decode_layer_kernel") if world == 1 else None})
         if step.one_launch_active():
             # the kernel that runs in the timed step is the one-launch layer: it is the dominant kernel of the line;
             # its two halves, each timed alone as separate launches, explain it
