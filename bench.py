@@ -838,11 +838,16 @@ def run_h2o(args) -> dict:
     h_q, h_k, h_v = (torch.empty(t.shape, dtype=t.dtype).pin_memory().copy_(t) for t in (q, k_new, v_new))
     h_out = torch.empty(out.shape, dtype=out.dtype).pin_memory()
 
-    def layers():
+    # two sets of device buffers: in the end-to-end arm step i + 1's inputs are copied in (and step i's output is read
+    # back) on side streams while the layers of the other set run
+    sets = [(q, k_new, v_new, out), tuple(torch.empty_like(t) for t in (q, k_new, v_new, out))]
+
+    def layers(si: int = 0):
+        q_, k_, v_, o_ = sets[si]
         for layer in range(L):
-            mgr.save_rope_kv_if_needed(layer, k_new[layer], v_new[layer])
-            decode_attention_layer(mgr, backend, layer, q[layer], mgr.decode_selection(layer), num_heads=hq,
-                                   num_kv_heads=hkv, out=out[layer])
+            mgr.save_rope_kv_if_needed(layer, k_[layer], v_[layer])
+            decode_attention_layer(mgr, backend, layer, q_[layer], mgr.decode_selection(layer), num_heads=hq,
+                                   num_kv_heads=hkv, out=o_[layer])
 
     stream = torch.cuda.Stream()
     evictions = 0
@@ -852,26 +857,52 @@ def run_h2o(args) -> dict:
         evictions += bool(mgr.evict_after_decode())
         stream.synchronize()
         graph = None
+        graphs = []
         if not args.no_graph:
-            mgr.prepare_decode_static(seqs, ids, pos, slot_mapping, ctx, req)
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph, stream=stream):
-                layers()
-            graph.replay()  # capture does not execute: this is the step the prepare above belongs to
-            evictions += bool(mgr.evict_after_decode())
-        run_layers = graph.replay if graph is not None else layers
+            for si in range(2):
+                mgr.prepare_decode_static(seqs, ids, pos, slot_mapping, ctx, req)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=stream):
+                    layers(si)
+                g.replay()  # capture does not execute: this is the step the prepare above belongs to
+                evictions += bool(mgr.evict_after_decode())
+                graphs.append(g)
+            graph = graphs[0]
+        run_layers = (lambda si=0: graphs[si].replay()) if graphs else layers
+        copy_s, back_s = torch.cuda.Stream(), torch.cuda.Stream()
+        in_ready = [torch.cuda.Event() for _ in sets]
+        layers_done = [torch.cuda.Event() for _ in sets]
+        d2h_done = [torch.cuda.Event() for _ in sets]
+        e2e_count = [0]
 
         def step(e2e: bool):
             nonlocal evictions
             mgr.prepare_decode_static(seqs, ids, pos, slot_mapping, ctx, req)
-            if e2e:
-                q.copy_(h_q, non_blocking=True)
-                k_new.copy_(h_k, non_blocking=True)
-                v_new.copy_(h_v, non_blocking=True)
-            run_layers()
+            if not e2e:
+                run_layers(0)
+                evictions += bool(mgr.evict_after_decode())
+                return
+            i = e2e_count[0]
+            e2e_count[0] += 1
+            si = i & 1
+            q_, k_, v_, o_ = sets[si]
+            if i >= 2:
+                copy_s.wait_event(layers_done[si])  # step i - 2 has read this set
+            with torch.cuda.stream(copy_s):
+                q_.copy_(h_q, non_blocking=True)
+                k_.copy_(h_k, non_blocking=True)
+                v_.copy_(h_v, non_blocking=True)
+                in_ready[si].record(copy_s)
+            stream.wait_event(in_ready[si])
+            if i >= 2:
+                stream.wait_event(d2h_done[si])  # step i - 2's output of this set is on the host
+            run_layers(si)
+            layers_done[si].record(stream)
             evictions += bool(mgr.evict_after_decode())
-            if e2e:
-                h_out.copy_(out, non_blocking=True)
+            back_s.wait_event(layers_done[si])
+            with torch.cuda.stream(back_s):
+                h_out.copy_(o_, non_blocking=True)
+                d2h_done[si].record(back_s)
 
         def steps_to_interval_start() -> int:
             return (budget + interval - int(mgr.row_seq_lens[0])) % interval
@@ -911,6 +942,7 @@ def run_h2o(args) -> dict:
         f0.record(stream)
         for _ in range(steps):
             step(True)
+        stream.wait_stream(back_s)  # the last step's result is on the host
         f1.record(stream)
         torch.cuda.synchronize()
         e2e_ms = f0.elapsed_time(f1)
