@@ -31,6 +31,11 @@ for k, name in names.items():
     c = (c[c > 0] - t0).float() / 1000.0
     if c.numel():
         print(f"{name:30s} n {c.numel():3d} min {c.min():7.2f} med {c.median():7.2f} max {c.max():7.2f}")
+ph = t[:, 13:16].float() / 1000.0
+selecting = t[:, 5] > 0
+if selecting.any():
+    m = ph[selecting].mean(dim=0)
+    print(f"select phases us (mean over selecting CTAs): load {m[0]:.1f} search {m[1]:.1f} compact+pack {m[2]:.1f}")
 sel = t[:, 5].float() / 1000.0
 print("select us (selecting CTAs): mean", float(sel[sel > 0].mean()) if (sel > 0).any() else 0)
 print("attn merge us: n", int((t[:, 21] > 0).sum()), "mean", float(t[:, 21][t[:, 21] > 0].float().mean() / 1000.0) if (t[:, 21] > 0).any() else 0,

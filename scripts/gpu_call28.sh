@@ -9,5 +9,4 @@ for l in open('gpurun_out/b28.log'):
         d = json.loads(l)
         print(' value', round(d['value'], 1), 'ms', round(d['ms_per_step'], 3), 'e2e', round(d['e2e']['value'], 1), 'e2e ms', round(d['e2e']['ms_per_step'], 3), 'frac', round(d['roofline']['frac'], 3), 'step frac', round(d['roofline_step']['frac'], 3))
 PY
-timeout 1500 compute-sanitizer --tool memcheck --error-exitcode 9 python -m pytest tests/test_gpu_quest_layer.py tests/test_gpu_attention.py tests/test_zz_no_alloc.py -m gpu -x -q --timeout 1200 -k "not full_size and not baseline" > gpurun_out/sanitizer_r2.log 2>&1; echo "memcheck rc=$?"
-tail -6 gpurun_out/sanitizer_r2.log | cut -c1-200
+# (compute-sanitizer is closed on this pool: no memcheck run)
