@@ -20,6 +20,7 @@ enum {
   kTuneNoMath = 5, kTuneScoreQ = 6, kTunePdl = 7, kTuneAttnGranule = 8, kTuneAttnHpc = 9,
   kTuneAttnSplitPen = 10,  // attention: units a CTA is charged for a row boundary inside its range, + 1 (0: auto, 1: none)
   kTuneNoEvictFirst = 13,  // 1: the streams' bulk copies use the default L2 policy instead of evict-first
+  kTunePollFirstNs = 14,   // one-launch layer: first sleep (ns) of a producer warp whose row is not selected yet
   kTuneAttnStages = 11,    // attention: cap of the ring's stages (experiments; 0: as many as fit)
   kTuneCount = 16
 };

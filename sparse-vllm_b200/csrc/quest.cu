@@ -422,6 +422,7 @@ struct ScoreParams {
   int min_batch, share_div;       // guided claim size = max(min_batch, left / (share_div * CTAs per group))
   int no_math;                    // experiments: consumers release the stages without the contractions
   int evict_first;                // the bounds stream's copies are tagged evict-first in L2
+  int poll_first_ns;              // one-launch layer: first sleep of a producer warp that finds its row not selected yet
   int32_t* sched;  // sched_scratch_ints(batch) zeroed ints
   // fused select only
   int k;
@@ -481,11 +482,16 @@ __device__ __forceinline__ void score_attention_phase(const ScoreParams& p, unsi
   const int B = p.batch;
   const int tid = threadIdx.x, warp = tid >> 5;
   const int* sel_done = p.sched + 1 + 2 * B;
+  const uint32_t tuning_poll_ns = p.poll_first_ns;
   auto wait_row = [&](int b) {  // whole warp; one lane polls
     if ((tid & 31) == 0) {
       SpinGuard guard;
+      // few looks, far apart: a selection takes >= 6 us from the moment the last CTA leaves the row, and hundreds of
+      // warps polling the flags' cache lines (shared with the rows' counters) slowed the running selections down
+      uint32_t ns = tuning_poll_ns;
       while (ld_acquire_gpu(sel_done + b) == 0) {
-        __nanosleep(500);  // few pollers, far apart: the flags share cache lines with the rows' counters
+        __nanosleep(ns);
+        ns = 1000;
         guard.tick(kSpinLimitNs);
       }
       if (dbg && warp == kConsumerWarps && dbg[23] == 0) dbg[23] = global_timer_ns();
@@ -1060,6 +1066,7 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
   }
   p.no_math = tuning(kTuneNoMath) == 1;
   p.evict_first = tuning(kTuneNoEvictFirst) != 1;
+  p.poll_first_ns = tuning(kTunePollFirstNs) > 0 ? tuning(kTunePollFirstNs) : 4000;
   const size_t smem = score_smem_layout(p.stages, p.hq, p.hkv, p.hsplit, p.batch, FUSED, qsplit ? 2 : 1).total;
   // no more CTAs than pieces of work: chunks, or single units when the rows are cut evenly
   const int64_t max_chunks = (int64_t)p.batch * (p.share_div == 0 ? units_row : (units_row + p.chunk_units - 1) / p.chunk_units);
