@@ -11,6 +11,8 @@ st = QuestState(f[0], f[1], f[2], f[3] if len(f) > 3 else 131072, f[4] if len(f)
 lib = _native.load()
 if os.environ.get("NOWAVES"):
     ops.set_tuning(12, 1)
+if os.environ.get("POLL"):
+    ops.set_tuning(14, int(os.environ["POLL"]))
 buf = torch.zeros(148 * 32, dtype=torch.int64, device="cuda:0")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:0")
 for it in range(4):

@@ -466,11 +466,16 @@ __device__ __forceinline__ uint32_t q_neg(uint32_t x) { return x & q_neg_mask(x)
 __device__ __forceinline__ void score_consumer_sync() { group_sync<1, kScoreConsumerThreads>(); }
 
 // The select group's selection of one row, as a function of its own (one-launch layer kernels).
+// (its scratch is named by its offset in the kernel's dynamic shared memory, not by a pointer: through a generic
+// pointer the compiler could neither use shared-memory instructions nor reorder around them, and the selection took
+// twice as long)
 __device__ __noinline__ void fused_select_pack_row(const uint16_t* scores_row, int n_cols, int n_valid, int k,
                                                    const int32_t* pt_row, int ctx, int32_t* out_row, int32_t* len_out,
-                                                   int32_t* sel_pages_out, SelectSmem* sm, unsigned long long* tdbg) {
+                                                   int32_t* sel_pages_out, int select_off, unsigned long long* tdbg) {
+  extern __shared__ __align__(128) unsigned char smem[];
   quest_select_pack_row<2, kScoreSelectThreads, (kScoreThreads - kScoreSelectThreads)>(
-      scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out, sel_pages_out, *sm, tdbg);
+      scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out, sel_pages_out,
+      *reinterpret_cast<SelectSmem*>(smem + select_off), tdbg);
 }
 
 // Attention phase of a one-launch layer (AHPC > 0 in quest_page_score_kernel, whose header describes it); entered by
@@ -515,13 +520,13 @@ __device__ __forceinline__ void score_attention_phase(const ScoreParams& p, unsi
     // until their rows are done): the consumers do not poll their ring barriers next to a running selection
     asm volatile("bar.sync 5, %0;" ::"n"(kConsumerThreads + kProducerWarps * 32) : "memory");
     if (dbg && tid == 0) dbg[17] = global_timer_ns();
-    attn_main<AHPC, 1, false, 3, true>(ap, smem, wait_row, dbg ? dbg + 16 : nullptr);
-    if (tid == 0 && atomicAdd(s_flag, 1) == 1) sched_finish(p.sched, B);
   } else {
     asm volatile("bar.sync 4, %0;" ::"n"(kConsumerThreads + kProducerWarps * 32) : "memory");
     asm volatile("bar.arrive 5, %0;" ::"n"(kConsumerThreads + kProducerWarps * 32) : "memory");
-    attn_main<AHPC, 1, false, 3, true>(ap, smem, wait_row, dbg ? dbg + 16 : nullptr);
   }
+  // one call site for both roles: the kernel holds ONE copy of the attention code (two inlined copies made it 480 KB)
+  attn_main<AHPC, 1, false, 3, true>(ap, smem, wait_row, dbg ? dbg + 16 : nullptr);
+  if (tid == 0 && atomicAdd(s_flag, 1) == 1) sched_finish(p.sched, B);
 }
 
 // QSPLIT: q+ and q- are both staged (when that does not cost a ring stage); else q is staged once and
@@ -750,7 +755,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
           fused_select_pack_row(p.scores + (int64_t)b * p.score_stride, p.n_cols, sNv[b], p.k,
                                 p.page_table + (int64_t)sReq[b] * p.pt_stride, p.context_lens[b],
                                 p.packed_slots + (int64_t)b * p.out_stride, p.sparse_lens + b,
-                                p.selected_pages ? p.selected_pages + (int64_t)b * (p.k + 1) : nullptr, sel_sm,
+                                p.selected_pages ? p.selected_pages + (int64_t)b * (p.k + 1) : nullptr, L.select_off,
                                 dbg ? dbg + 13 : nullptr);
         else
         quest_select_pack_row<2, kScoreSelectThreads, (kScoreThreads - kScoreSelectThreads)>(
