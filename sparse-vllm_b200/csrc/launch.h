@@ -21,8 +21,10 @@ enum {
   kTuneAttnSplitPen = 10,  // attention: units a CTA is charged for a row boundary inside its range, + 1 (0: auto, 1: none)
   kTuneNoEvictFirst = 13,  // 1: the streams' bulk copies use the default L2 policy instead of evict-first
   kTunePollFirstNs = 14,   // one-launch layer: first sleep (ns) of a producer warp whose row is not selected yet
+  kTuneLook = 15,          // score loader look-ahead in descriptors (1, 2, 4; 0: auto)
+  kTuneTailChunks = 16,    // score: chunks of a row's tail that are claimed singly and posted unit by unit, + 1 (0: auto, 1: none)
   kTuneAttnStages = 11,    // attention: cap of the ring's stages (experiments; 0: as many as fit)
-  kTuneCount = 16
+  kTuneCount = 24
 };
 int tuning(int which);
 bool pdl_enabled();  // launches carry the programmatic-stream-serialization attribute

@@ -399,7 +399,7 @@ constexpr int kScoreSelectWarps = 8;    // dedicated top-k warps: the stream nev
 constexpr int kScoreSelectThreads = kScoreSelectWarps * 32;
 constexpr int kScoreThreads = kScoreConsumerThreads + 2 * 32 + kScoreSelectThreads;
 constexpr int kScoreMaxSmem = 227 * 1024;
-static_assert(kIdDepth < kSchedQueue, "the loader reads kIdDepth descriptors ahead of the one it issues");
+static_assert(kIdDepth < kSchedQueue, "the loader reads up to kIdDepth descriptors ahead of the one it issues");
 
 struct ScoreParams {
   const __nv_bfloat16* q;
@@ -423,6 +423,8 @@ struct ScoreParams {
   int no_math;                    // experiments: consumers release the stages without the contractions
   int evict_first;                // the bounds stream's copies are tagged evict-first in L2
   int poll_first_ns;              // one-launch layer: first sleep of a producer warp that finds its row not selected yet
+  int look;                       // loader look-ahead in descriptors (1, 2 or 4)
+  int tail_chunks;                // the last tail_chunks chunks of a row are claimed one at a time and posted unit by unit
   int32_t* sched;  // sched_scratch_ints(batch) zeroed ints
   // fused select only
   int k;
@@ -609,9 +611,9 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
 
   if (warp == kScoreSchedWarp) {
     // ============================================================== scheduler
-    const int depth = min(kSchedQueue, (S / hs + p.chunk_units - 1) / p.chunk_units + kIdDepth + 1);
+    const int depth = min(kSchedQueue, (S / hs + p.chunk_units - 1) / p.chunk_units + p.look + 1);
     sched_run(sched, next_chunk, B, p.groups, p.chunk_units, p.min_batch, p.share_div, depth, units_of_row,
-              ReserveNone(), (dbg && blockIdx.x >= (unsigned)B) ? dbg + 15 : nullptr);
+              ReserveNone(), (dbg && blockIdx.x >= (unsigned)B) ? dbg + 15 : nullptr, p.tail_chunks);
     if constexpr (AHPC == 0) return;
   }
 
@@ -622,9 +624,13 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
     // issues ONE bulk async copy per stage-load.  A partly valid last unit is copied whole (the chunk
     // exists; rows of pages that do not count are masked when the scores are written).
     const uint32_t part_bytes = (uint32_t)stage_bytes;
-    ChunkDesc dq[kIdDepth];
-    int idq[kIdDepth];
     unsigned long long w_desc = 0, w_empty = 0;
+    // LOOK = descriptors whose chunk ids are in flight ahead of the copies: enough to cover a table read (~1 us, i.e.
+    // ~64 KB of streaming per SM) and no more, because what is posted ahead is committed to this CTA
+    auto run_loader = [&](auto look_tag) {
+    constexpr int LOOK = decltype(look_tag)::value;
+    ChunkDesc dq[LOOK];
+    int idq[LOOK];
     int n_read = 0;
     bool ended = false;
     auto fetch = [&](ChunkDesc& d, int& id) {
@@ -643,7 +649,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
       if (lane < d.units()) id = __ldg(p.unit_table + (int64_t)sReq[d.row] * p.ut_stride + d.unit_begin + lane);
     };
 #pragma unroll
-    for (int t = 0; t < kIdDepth; ++t) fetch(dq[t], idq[t]);
+    for (int t = 0; t < LOOK; ++t) fetch(dq[t], idq[t]);
     const char* bounds_bytes = reinterpret_cast<const char*>(p.bounds);
     const uint64_t l2_policy = l2_evict_first_policy();
     // dq / idq form a circular FIFO indexed at compile time (the loop body is unrolled kIdDepth
@@ -656,7 +662,7 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
     bool done = false;
     while (!done) {
 #pragma unroll
-      for (int u = 0; u < kIdDepth; ++u) {
+      for (int u = 0; u < LOOK; ++u) {
         if (done) break;
         const ChunkDesc cur = dq[u];
         const int ids = idq[u];
@@ -700,6 +706,10 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
         fetch(dq[u], idq[u]);
       }
     }
+    };  // run_loader
+    if (p.look >= 4) run_loader(std::integral_constant<int, 4>());
+    else if (p.look >= 2) run_loader(std::integral_constant<int, 2>());
+    else run_loader(std::integral_constant<int, 1>());
     if (dbg && lane == 0) dbg[4] = global_timer_ns(), dbg[8] = w_desc, dbg[9] = w_empty;
     if constexpr (AHPC == 0) return;
   }
@@ -1060,6 +1070,14 @@ static int launch_score_variant(ScoreParams p, cudaStream_t stream) {
     int mb = (int)((claim + chunk_bytes - 1) / chunk_bytes);
     if (mb < kMinBatch) mb = kMinBatch;
     p.min_batch = tuning(kTuneMinBatch) > 0 ? tuning(kTuneMinBatch) : mb;
+    // look-ahead of the loader: ~64 KB of descriptors (a table read is ~1 us), rounded to 1 / 2 / 4
+    const int64_t want_look = (64 * 1024 + chunk_bytes - 1) / chunk_bytes;
+    p.look = tuning(kTuneLook) > 0 ? tuning(kTuneLook) : (want_look >= 3 ? 4 : (want_look >= 2 ? 2 : 1));
+    // Tail of a row (knob 16 = chunks + 1): what a CTA holds (ring + descriptors posted ahead + its claim) cannot be
+    // stolen, and the CTAs' finishing times are 14 us apart at cfg5.  Claiming the last chunks of a row one at a time
+    // and posting them one unit per descriptor was measured and is OFF: the extra descriptors cost more than the
+    // finer tail saves (cfg5 95.1 vs 94.0 us, cfg3 98.7 vs 94.8, N=2 shard 58.5 vs 55.2 with 2 chunks per sharing CTA).
+    p.tail_chunks = tuning(kTuneTailChunks) > 0 ? tuning(kTuneTailChunks) - 1 : 0;
   }
   // Static first piece = 1/share_div of a CTA's fair share of its home row.  A launch that gives a CTA less than
   // ~1 MB (TP shards, short batches) is over before guided claims could rebalance anything (what a CTA holds in

@@ -82,7 +82,8 @@ struct ReserveNone {
 template <class UnitsOfRow, class Reserve = ReserveNone>
 __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int rows, int groups, int cu,
                           int min_batch, int share_div, int depth, UnitsOfRow units_of_row,
-                          Reserve reserve = Reserve(), unsigned long long* t_last_claim = nullptr) {
+                          Reserve reserve = Reserve(), unsigned long long* t_last_claim = nullptr,
+                          int tail_chunks = 0) {
   bool even = share_div == 0;
   if (even) {
     // an even cut gives every row the same number of CTAs: only for rows of (nearly) equal length; ragged batches
@@ -147,7 +148,16 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
       }
       return true;
     }
-    auto batch = [&](int left) { return guided ? guided_batch(left) : min_batch; };
+    // the row's tail (its last tail_chunks chunks): one chunk per claim, one unit per descriptor -- what a CTA holds
+    // cannot be stolen, so it should hold little when the row runs dry
+    auto batch = [&](int left) { return left <= tail_chunks ? 1 : (guided ? guided_batch(left) : min_batch); };
+    auto post_chunk = [&](int c) {
+      const int ub = c * cu, ue = min(ub + cu, nu);
+      if (d - c <= tail_chunks)
+        for (int u = ub; u < ue; ++u) post(row, u, 1);
+      else
+        post(row, ub, ue - ub);
+    };
     int m = first_home ? static_piece(d) : batch(d), j = 0, taken = 0;
     if (first_home) {
       j = (int)(blockIdx.x / (unsigned)groups) * m;  // static: no round trip before the first copy
@@ -170,7 +180,7 @@ __device__ void sched_run(SchedSmem& q, int* next_chunk /* global [rows] */, int
         m2 = batch(left);
         if (lane == 0) j2 = base + atomicAdd(next_chunk + row, m2);
       }
-      for (int c = j; c < end; ++c) post(row, c * cu, min(cu, nu - c * cu));
+      for (int c = j; c < end; ++c) post_chunk(c);
       if (left <= 0) return true;
       j = __shfl_sync(0xffffffffu, j2, 0);
       m = m2;

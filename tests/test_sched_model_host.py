@@ -7,7 +7,7 @@ from __future__ import annotations
 
 import random
 
-def simulate(rows_units, grid, groups, cu, min_batch, share_div, seed):
+def simulate(rows_units, grid, groups, cu, min_batch, share_div, seed, tail_chunks=0):
     rnd = random.Random(seed)
     rows = len(rows_units)
     groups = max(1, min(groups, rows))
@@ -48,7 +48,7 @@ def simulate(rows_units, grid, groups, cu, min_batch, share_div, seed):
                     for ub in range(nu * l // share, u_end, cu):
                         post_units(row, ub, min(cu, u_end - ub))
                 return
-            batch = (lambda left: guided(left)) if is_guided else (lambda left: min_batch)
+            batch = lambda left: 1 if left <= tail_chunks else (guided(left) if is_guided else min_batch)
             m = static_piece(d) if first_home else batch(d)
             taken = 0
             if first_home:
@@ -71,7 +71,11 @@ def simulate(rows_units, grid, groups, cu, min_batch, share_div, seed):
                     j2 = base + counters[row]; counters[row] += m2
                     yield
                 for c in range(j, end):
-                    post(row, c)
+                    if d - c <= tail_chunks:  # the row's tail: one unit per descriptor
+                        for u in range(c * cu, min(c * cu + cu, rows_units[row])):
+                            post_units(row, u, 1)
+                    else:
+                        post(row, c)
                 if left <= 0:
                     return
                 j, m = j2, m2
@@ -109,4 +113,5 @@ def test_every_unit_is_posted_exactly_once():
         units = [rnd.choice([0, 1, 2, 7, 33, 128, 512]) for _ in range(rows)] if trial % 3 else [rnd.choice([1, 7, 100, 512])] * rows
         grid = rnd.choice([1, 2, 7, 16, 37, 128, 148])
         groups = rnd.choice([rows, max(1, rows // 2), 1])
-        simulate(units, grid, groups, rnd.choice([1, 2, 3, 4, 8]), rnd.choice([1, 2, 3]), rnd.choice([0, 1, 2, 4]), trial)
+        simulate(units, grid, groups, rnd.choice([1, 2, 3, 4, 8]), rnd.choice([1, 2, 3]), rnd.choice([0, 1, 2, 4]), trial,
+                 tail_chunks=rnd.choice([0, 0, 1, 5, 40]))
