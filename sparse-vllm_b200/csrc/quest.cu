@@ -381,7 +381,7 @@ __global__ void __launch_bounds__(256) quest_select_pack_kernel(
 // (bounds_layout.cuh), streamed as hs ring stages of hh = Hkv/hs heads each.  Units are handed out
 // dynamically (sched.cuh): a scheduler warp claims chunks of ~64 KB from per-row counters and posts
 // descriptors; ONE loader warp resolves each unit's chunk id through the unit table (fetched
-// kIdDepth descriptors ahead) and issues one bulk async copy (cp.async.bulk, SASS UBLKCP) per ring
+// 1-4 descriptors ahead: ~64 KB worth) and issues one bulk async copy (cp.async.bulk, SASS UBLKCP) per ring
 // stage, 8-32 KB each, counted on the stage's mbarrier.  Consumer warps take units round-robin;
 // per unit and KV head:
 //   A = bounds rows (16 pages x 128, ldmatrix from the swizzled stage), B = q+ / q- (128 x 8 heads)
@@ -393,7 +393,7 @@ constexpr int kScoreConsumerWarps = 6;
 constexpr int kScoreConsumerThreads = kScoreConsumerWarps * 32;
 constexpr int kScoreLoaderWarp = kScoreConsumerWarps;      // one loader warp ...
 constexpr int kScoreSchedWarp = kScoreConsumerWarps + 1;   // ... and one scheduler warp
-constexpr int kIdDepth = 4;             // descriptors whose chunk ids are in flight ahead of the copies (the table read
+constexpr int kIdDepth = 4;             // most descriptors whose chunk ids are in flight ahead of the copies (the table read
                                         // is an L2 hit at best: ~1 us under load, i.e. 40 KB of streaming per SM)
 constexpr int kScoreSelectWarps = 8;    // dedicated top-k warps: the stream never waits for a selection
 constexpr int kScoreSelectThreads = kScoreSelectWarps * 32;
@@ -620,8 +620,8 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
   if (warp == kScoreLoaderWarp) {
     // ============================================================== loader
     // Stage-load ii = i * hs + part (i: CTA-local running unit index) goes into stage ii % S.  Lane l holds
-    // the bounds chunk of unit unit_begin + l of a descriptor, fetched kIdDepth descriptors ahead; lane 0
-    // issues ONE bulk async copy per stage-load.  A partly valid last unit is copied whole (the chunk
+    // the bounds chunk of unit unit_begin + l of a descriptor, fetched LOOK descriptors ahead, and issues ONE bulk
+    // async copy per stage-load of its unit.  A partly valid last unit is copied whole (the chunk
     // exists; rows of pages that do not count are masked when the scores are written).
     const uint32_t part_bytes = (uint32_t)stage_bytes;
     unsigned long long w_desc = 0, w_empty = 0;
@@ -652,10 +652,10 @@ __global__ void __launch_bounds__(kScoreThreads, 1) quest_page_score_kernel(cons
     for (int t = 0; t < LOOK; ++t) fetch(dq[t], idq[t]);
     const char* bounds_bytes = reinterpret_cast<const char*>(p.bounds);
     const uint64_t l2_policy = l2_evict_first_policy();
-    // dq / idq form a circular FIFO indexed at compile time (the loop body is unrolled kIdDepth
+    // dq / idq form a circular FIFO indexed at compile time (the loop body is unrolled LOOK
     // times) and a slot is refilled only AFTER its id was used: the register that waits for a table
     // load is then never copied or renamed, so the load's latency is only paid when the id is finally
-    // used, kIdDepth descriptors later.  (Refilling the slot before the use made the compiler keep the
+    // used, LOOK descriptors later.  (Refilling the slot before the use made the compiler keep the
     // old value and move the new one into place at the loop's back edge: a wait for the load that was
     // issued last, i.e. one full table-read latency per descriptor, which capped launches with small
     // units (<= 16 KB, TP shards) at ~2.3 units/us per SM whatever their size.)
