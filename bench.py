@@ -320,8 +320,8 @@ class DecodeStep:
             if self.collective == "nccl" and not self.no_comm:
                 import torch.distributed as dist
                 dist.all_gather_into_tensor(self.gathered[layer & 1].view(-1), self.out[layer].view(-1))
-        if lo == 0 and hi == self.w["layers"]:
-            self.launches_per_step = n
+        if lo == 0 and hi == self.w["layers"] and not (self.force_two_launches or self.no_comm or self.only_collective):
+            self.launches_per_step = n  # the timed step's own count, not a per-kernel timing pass's
 
 
 def verify_gather(step) -> None:
