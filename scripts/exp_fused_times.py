@@ -10,7 +10,7 @@ f = [int(x) for x in os.environ.get("SHAPE", "16,64,8").split(",")]
 st = QuestState(f[0], f[1], f[2], f[3] if len(f) > 3 else 131072, f[4] if len(f) > 4 else 4096, layers=4)
 lib = _native.load()
 if os.environ.get("NOWAVES"):
-    ops.set_tuning(12, 1)
+    ops.set_tuning(12, int(os.environ["NOWAVES"]))
 if os.environ.get("POLL"):
     ops.set_tuning(14, int(os.environ["POLL"]))
 buf = torch.zeros(148 * 32, dtype=torch.int64, device="cuda:0")
@@ -39,6 +39,10 @@ if selecting.any():
     m = ph[selecting].mean(dim=0)
     print(f"select phases us (mean over selecting CTAs): load {m[0]:.1f} search {m[1]:.1f} compact+pack {m[2]:.1f}")
 sel = t[:, 5].float() / 1000.0
+if selecting.any():
+    for i in torch.nonzero(selecting).flatten().tolist()[:16]:
+        print(f"  selecting cta {i:3d}: score done {(int(t[i, 3]) - t0) / 1000.0:6.2f} select {float(sel[i]):5.1f} = load {float(ph[i, 0]):4.1f} search {float(ph[i, 1]):4.1f} "
+              f"pack {float(ph[i, 2]):4.1f} | attn set-up done {(int(t[i, 17]) - t0) / 1000.0:6.2f} first data {(int(t[i, 18]) - t0) / 1000.0:6.2f}")
 print("select us (selecting CTAs): mean", float(sel[sel > 0].mean()) if (sel > 0).any() else 0)
 print("attn merge us: n", int((t[:, 21] > 0).sum()), "mean", float(t[:, 21][t[:, 21] > 0].float().mean() / 1000.0) if (t[:, 21] > 0).any() else 0,
       "| attn epilogue total us mean", float(t[:, 22].float().mean() / 1000.0))
