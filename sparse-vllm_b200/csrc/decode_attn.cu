@@ -64,6 +64,14 @@ static int attn_configure(AttnParams& p, int avail, int grid_in, int* grid_out) 
     const int64_t want = (max_units + min_units - 1) / min_units;
     if ((int64_t)grid > want) grid = (int)want;
   }
+  // ... and no more than 12 CTAs per row of work on average: the row's last contributor merges one partial per CTA
+  // that had units of it.  Attention launch, us, at 16 (the 256 KB rule alone) / 12 / 10 / 8 CTAs per row: bs 1 ctx 32K
+  // budget 2048 19.4 / 17.5 / 18.8 / 20.1, bs 4 21.0 / 18.3 / 18.9 / 20.2, bs 2 ctx 128K budget 4096 27.1 / 25.3 / 27.6 /
+  // 29.6 (GPU call 49); batches of 16 and the TP shards of cfg5 have fewer than 12 anyway.
+  {
+    const int per_row = tuning(kTuneAttnRowCtas) > 0 ? tuning(kTuneAttnRowCtas) : 12;
+    if ((int64_t)grid > (int64_t)rows * per_row) grid = rows * per_row;
+  }
   if (grid < 1) grid = 1;
   *grid_out = grid;
   p.grid_cap = 0;

@@ -23,6 +23,7 @@ enum {
   kTunePollFirstNs = 14,   // one-launch layer: first sleep (ns) of a producer warp whose row is not selected yet
   kTuneLook = 15,          // score loader look-ahead in descriptors (1, 2, 4; 0: auto)
   kTuneTailChunks = 16,    // score: chunks of a row's tail that are claimed singly and posted unit by unit, + 1 (0: auto, 1: none)
+  kTuneAttnRowCtas = 17,   // attention: most CTAs one row of work is cut over (0: auto)
   kTuneAttnStages = 11,    // attention: cap of the ring's stages (experiments; 0: as many as fit)
   kTuneCount = 24
 };
