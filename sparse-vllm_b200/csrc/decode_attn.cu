@@ -1,5 +1,6 @@
 // Sparse paged GQA decode attention for sm_100a: the stand-alone kernel and its launchers (device code and the
 // description of the decomposition: decode_attn.cuh).
+#include <cmath>
 #include "decode_attn.cuh"
 
 namespace svb200 {
@@ -28,6 +29,18 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
 
 // Launch configuration shared by the stand-alone kernel and the attention phase of a one-launch layer: ring stages
 // that fit `avail` bytes of shared memory, producer warps, CTAs the work is cut into (<= grid_in), knobs.
+// Most CTAs one row of work (HPC KV heads of a batch entry, <= max_len tokens) is cut over.  The row's last
+// contributor merges one partial per CTA that had units of it (~0.65 us each) while a CTA streams ~45 GB/s, so
+// time(G) = bytes / (G * 45 GB/s) + 0.65 us * G is lowest at G = sqrt(row KB / 29).  Attention launch, us, at
+// 16 / 12 / 10 / 8 CTAs per row: bs 1 ctx 32K budget 2048 (4 MB rows) 19.4 / 17.5 / 18.8 / 20.1, bs 4 21.0 / 18.3 /
+// 18.9 / 20.2 (GPU call 49); dense 128K rows (268 MB) get 95, i.e. every SM.
+int attn_row_ctas(int hpc, int max_len) {
+  if (tuning(kTuneAttnRowCtas) > 0) return tuning(kTuneAttnRowCtas);
+  const double row_kb = (double)((max_len + kPage - 1) / kPage) * (hpc * 2 * kPage * kHeadDim * 2 / 1024);
+  const int n = (int)std::ceil(std::sqrt(row_kb / 29.0));
+  return n < 4 ? 4 : n;
+}
+
 template <int HPC, int NT>
 static int attn_configure(AttnParams& p, int avail, int grid_in, int* grid_out) {
   using G = AttnGeom<HPC>;
@@ -64,12 +77,9 @@ static int attn_configure(AttnParams& p, int avail, int grid_in, int* grid_out) 
     const int64_t want = (max_units + min_units - 1) / min_units;
     if ((int64_t)grid > want) grid = (int)want;
   }
-  // ... and no more than 12 CTAs per row of work on average: the row's last contributor merges one partial per CTA
-  // that had units of it.  Attention launch, us, at 16 (the 256 KB rule alone) / 12 / 10 / 8 CTAs per row: bs 1 ctx 32K
-  // budget 2048 19.4 / 17.5 / 18.8 / 20.1, bs 4 21.0 / 18.3 / 18.9 / 20.2, bs 2 ctx 128K budget 4096 27.1 / 25.3 / 27.6 /
-  // 29.6 (GPU call 49); batches of 16 and the TP shards of cfg5 have fewer than 12 anyway.
+  // ... and a row of work is cut over no more CTAs than its bytes pay for (attn_row_ctas)
   {
-    const int per_row = tuning(kTuneAttnRowCtas) > 0 ? tuning(kTuneAttnRowCtas) : 12;
+    const int per_row = attn_row_ctas(HPC, p.max_len);
     if ((int64_t)grid > (int64_t)rows * per_row) grid = rows * per_row;
   }
   if (grid < 1) grid = 1;
@@ -121,10 +131,15 @@ static int launch_hpc(const AttnParams& p, cudaStream_t stream) {
   return score ? launch_variant<HPC, 2, true>(p, stream) : launch_variant<HPC, 2, false>(p, stream);
 }
 
-int attn_auto_heads_per_cta(int hkv) {
+int attn_auto_heads_per_cta(int hkv, int batch, int max_len) {
   // 4 heads = 1 KB token rows and six ring stages.  8 heads (knob 9 = 1): three stages of 64 KB, but with all of a
   // rank's heads staged together the rows of a page are contiguous and a copy moves a granule of them.
   if (tuning(kTuneAttnHpc) > 0 && hkv % tuning(kTuneAttnHpc) == 0) return tuning(kTuneAttnHpc);
+  // Small batches: with 4 heads per CTA there are too few rows of work to occupy the SMs (bs 1, 8 KV heads: 2 rows);
+  // 2 heads per CTA doubles the rows.  Attention launch, us, 4 -> 2 heads per CTA at ctx 128K budget 4096: bs 1
+  // 25.7 -> 20.5, bs 2 25.7 -> 20.6, bs 4 26.6 -> 23.6, bs 8 34.5 -> 33.9 (stays at 4); ctx 32K budget 2048: bs 1-4
+  // unchanged within 0.3 us (GPU call 51).
+  if (hkv % 4 == 0 && (int64_t)batch * (hkv / 4) * attn_row_ctas(4, max_len) < max_ctas()) return 2;
   for (int c = 4; c > 1; c >>= 1)
     if (hkv % c == 0) return c;
   return 1;
@@ -132,7 +147,7 @@ int attn_auto_heads_per_cta(int hkv) {
 
 int launch_sparse_decode_attn(const AttnParams& p, int heads_per_cta, cudaStream_t stream) {
   if (p.batch <= 0) return 0;
-  const int hpc = heads_per_cta > 0 ? heads_per_cta : attn_auto_heads_per_cta(p.hkv);
+  const int hpc = heads_per_cta > 0 ? heads_per_cta : attn_auto_heads_per_cta(p.hkv, p.batch, p.max_len);
   if (p.hkv % hpc) {
     set_error("sparse_decode_attn: heads_per_cta=%d does not divide num_kv_heads=%d", hpc, p.hkv);
     return 1;

@@ -140,7 +140,8 @@ struct AttnParams {
   int split_pen;     // units a CTA is charged for a row boundary inside its range (see the kernel's cut); launcher
   PushArgs push;     // tensor-parallel push epilogue (world <= 1: none)
 };
-int attn_auto_heads_per_cta(int hkv);
+int attn_auto_heads_per_cta(int hkv, int batch, int max_len);
+int attn_row_ctas(int hpc, int max_len);
 // launch configuration of the attention phase of a one-launch layer (quest.cu): ring stages inside `region_bytes` of
 // shared memory, producer warps, CTAs the work is cut into (<= grid, <= the workspace's CTAs), knobs
 int attn_configure_fused(AttnParams& p, int heads_per_cta, int region_bytes, int grid);

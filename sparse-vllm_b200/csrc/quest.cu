@@ -1199,7 +1199,7 @@ int launch_quest_decode_layer(const void* q, int64_t q_stride_b, const void* bou
   }
   p.attn = attn;
   p.attn.dbg_times = nullptr;  // (the layer kernel's own time stamps carry the attention phase's: slots 16..)
-  switch (attn_auto_heads_per_cta(hkv)) {
+  switch (attn_auto_heads_per_cta(hkv, batch, attn.max_len)) {
     case 1: return launch_score_variant<1, true, 1>(p, stream);
     case 2: return launch_score_variant<1, true, 2>(p, stream);
     default: return launch_score_variant<1, true, 4>(p, stream);
