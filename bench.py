@@ -74,6 +74,8 @@ def parse_args():
     ap.add_argument("--tune", default="", help="experiment knobs 'which=value,...' (svb200_set_tuning)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-chunks", type=int, default=2,
+                    help="e2e arm: the step's layers run in this many chunks (a chunk's read-back overlaps the next chunk)")
     ap.add_argument("--verbose", action="store_true", help="phase timestamps on stderr")
     return ap.parse_args()
 
@@ -568,7 +570,7 @@ def run_b200(args) -> dict:
         # rows from pinned host memory and reads the attention output back.  The layers run in chunks so that
         # a chunk's read-back (third stream) overlaps the next chunk's compute; input copies run on a copy stream.
         L = w["layers"]
-        n_chunks = 2 if L % 2 == 0 else 1  # (two are enough to keep a chunk's read-back off the next step's path)
+        n_chunks = args.e2e_chunks if L % max(args.e2e_chunks, 1) == 0 and args.e2e_chunks >= 1 else 1
         per = L // n_chunks
         copy_s, back_s = torch.cuda.Stream(), torch.cuda.Stream()
         # Two sets of device input buffers: step i + 1's inputs are copied in while step i computes (a serving loop
@@ -589,13 +591,17 @@ def run_b200(args) -> dict:
         d2h_done = [torch.cuda.Event() for _ in range(n_chunks)]
         set_free = [torch.cuda.Event() for _ in sets]
         e2e_count = [0]
+        host_t = [0.0, 0.0, 0.0]  # host seconds in prepare / input copies / launches (verbose note)
 
         def e2e_step():
             i = e2e_count[0]
             e2e_count[0] += 1
             si = i & 1
             step.q, step.k_new, step.v_new = sets[si]
+            tp = time.perf_counter()
             step.prepare()
+            host_t[0] += time.perf_counter() - tp
+            tp = time.perf_counter()
             if i >= 2:
                 copy_s.wait_event(set_free[si])  # step i - 2 has read this set of q / k / v
             with torch.cuda.stream(copy_s):
@@ -605,15 +611,18 @@ def run_b200(args) -> dict:
                     step.k_new[sl].copy_(step.h_k[sl], non_blocking=True)
                     step.v_new[sl].copy_(step.h_v[sl], non_blocking=True)
                     in_ready[si][c].record(copy_s)
+            host_t[1] += time.perf_counter() - tp
             for c in range(n_chunks):
                 sl = slice(c * per, (c + 1) * per)
                 stream.wait_event(in_ready[si][c])
                 if i >= 1:
                     stream.wait_event(d2h_done[c])  # the previous step's output of this chunk is on the host
+                tp = time.perf_counter()
                 if chunk_graphs[si]:
                     chunk_graphs[si][c].replay()
                 else:
                     step.layers(c * per, (c + 1) * per)
+                host_t[2] += time.perf_counter() - tp
                 out_ready[c].record(stream)
                 back_s.wait_event(out_ready[c])
                 with torch.cuda.stream(back_s):
@@ -629,13 +638,16 @@ def run_b200(args) -> dict:
         barrier()
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         f0.record(stream)
+        host_t[:] = [0.0, 0.0, 0.0]
+        t_host = time.perf_counter()
         for _ in range(steps):
             e2e_step()
+        t_host = time.perf_counter() - t_host  # host time to enqueue the steps (no sync inside: the host runs ahead)
         e2e_drain()
         f1.record(stream)
         barrier()
         e2e_ms = f0.elapsed_time(f1)
-        note("e2e done")
+        note(f"e2e done: host enqueue {t_host / steps * 1e3:.3f} ms/step (prepare {host_t[0] / steps * 1e3:.3f}, input copies {host_t[1] / steps * 1e3:.3f}, launches {host_t[2] / steps * 1e3:.3f}), device {e2e_ms / steps:.3f} ms/step")
         clocks = sampler.stop()
         note("clock sampler stopped")
 
