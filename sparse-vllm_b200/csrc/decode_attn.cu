@@ -33,7 +33,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) sparse_decode_attn_kernel(Att
 // contributor merges one partial per CTA that had units of it (~0.65 us each) while a CTA streams ~45 GB/s, so
 // time(G) = bytes / (G * 45 GB/s) + 0.65 us * G is lowest at G = sqrt(row KB / 29).  Attention launch, us, at
 // 16 / 12 / 10 / 8 CTAs per row: bs 1 ctx 32K budget 2048 (4 MB rows) 19.4 / 17.5 / 18.8 / 20.1, bs 4 21.0 / 18.3 /
-// 18.9 / 20.2 (GPU call 49); dense 128K rows (268 MB) get 95, i.e. every SM.
+// 18.9 / 20.2 (GPU call 49); dense 128K rows (268 MB) get 95, i.e. every SM; a dense 32K layer at bs 1 (two rows of
+// 34 MB, 74 CTAs each before) went from 61.6 to 48.3 us (calls 57-58).
 int attn_row_ctas(int hpc, int max_len) {
   if (tuning(kTuneAttnRowCtas) > 0) return tuning(kTuneAttnRowCtas);
   const double row_kb = (double)((max_len + kPage - 1) / kPage) * (hpc * 2 * kPage * kHeadDim * 2 / 1024);
