@@ -162,13 +162,14 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* warp_scan, int& 
 // 256 threads); longer rows re-read it every round.
 constexpr int kSelectVecPerThread = 4;
 
-template <int BAR, int NTHR, bool CACHED, int TID0>
+template <int BAR, int NTHR, int CVPT, int TID0>  // CVPT: vectors a thread keeps in registers (0: none, long rows)
 __device__ void quest_select_pack_impl(const uint16_t* __restrict__ scores_row, int n_cols, int n_valid,
                                        int k, const int32_t* __restrict__ pt_row, int ctx,
                                        int32_t* __restrict__ out_row, int32_t* __restrict__ len_out,
                                        int32_t* __restrict__ sel_pages_out, SelectSmem& sm,
                                        unsigned long long* tdbg = nullptr) {
-  constexpr int VPT = kSelectVecPerThread;
+  constexpr bool CACHED = CVPT > 0;
+  constexpr int VPT = CACHED ? CVPT : 1;
   const unsigned long long tq0 = tdbg ? global_timer_ns() : 0;
   const int tid = threadIdx.x - TID0, lane = tid & 31;  // TID0: first thread of the group (a warp boundary)
   const int nvec = (n_cols + 7) >> 3;
@@ -331,12 +332,21 @@ __device__ void quest_select_pack_row(const uint16_t* __restrict__ scores_row, i
                                       int32_t* __restrict__ out_row, int32_t* __restrict__ len_out,
                                       int32_t* __restrict__ sel_pages_out, SelectSmem& sm,
                                       unsigned long long* tdbg = nullptr) {
-  if (((n_cols + 7) >> 3) <= kSelectVecPerThread * NTHR)
-    quest_select_pack_impl<BAR, NTHR, true, TID0>(scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out,
-                                            sel_pages_out, sm, tdbg);
+  // Short rows spread over all threads (1 or 2 vectors each instead of 4 in a quarter of the threads): a search round
+  // costs every warp the instructions of its VPT vectors, whether they hold scores or padding.
+  const int nvec = (n_cols + 7) >> 3;
+  if (nvec <= NTHR)
+    quest_select_pack_impl<BAR, NTHR, 1, TID0>(scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out,
+                                               sel_pages_out, sm, tdbg);
+  else if (nvec <= 2 * NTHR)
+    quest_select_pack_impl<BAR, NTHR, 2, TID0>(scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out,
+                                               sel_pages_out, sm, tdbg);
+  else if (nvec <= kSelectVecPerThread * NTHR)
+    quest_select_pack_impl<BAR, NTHR, kSelectVecPerThread, TID0>(scores_row, n_cols, n_valid, k, pt_row, ctx, out_row,
+                                                                 len_out, sel_pages_out, sm, tdbg);
   else
-    quest_select_pack_impl<BAR, NTHR, false, TID0>(scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out,
-                                             sel_pages_out, sm, tdbg);
+    quest_select_pack_impl<BAR, NTHR, 0, TID0>(scores_row, n_cols, n_valid, k, pt_row, ctx, out_row, len_out,
+                                               sel_pages_out, sm, tdbg);
 }
 
 __global__ void __launch_bounds__(256) quest_select_pack_kernel(
